@@ -1,0 +1,417 @@
+#!/usr/bin/env python
+"""bench.py — MSAC hypothesis x point evaluations / s on the scoring-stress workload.
+
+One "step" = one pass of the hot path over one batch of synthetic input:
+  P3P on K seeded 4-samples  ->  K x N MSAC sweep (score + inlier count)  ->  argmin
+  ->  [N>1: one NCCL all_gather of (score, id, model) per rank]  ->  ordered inlier list of
+  the winning hypothesis.
+Workload (BASELINE.json configs[4], "scoring stress"): N = 1,000,000 2D-3D correspondences
+(50 % outliers, camera_pose_estimation.cc:52-127 distributions), K = 65,536 P3P hypotheses
+drawn by the reference's seeded UniformSampling (seed 42), hypotheses sharded K/G per GPU
+(points replicated), so scaling is STRONG. configs[1] (N = 10k x K = 10k) is 1e8 evaluations
+= ~0.1 ms of GPU work, i.e. a launch-latency measurement; it is a parity-test case and the
+``--workload c2`` option here.
+
+Usage:  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                        [--workload c5|c2] [--precision f32|f64]
+Under torchrun (N > 1) one process per GPU; rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_EVAL = 29.0  # pose evaluation incl. min + accumulate
+THR = 144.0           # 12 px squared, camera_pose_estimation.cc:154-156
+WORKLOADS = {
+    "c5": dict(n=1_000_000, k=65_536, name="scoring stress N=1M x K=65536 P3P hypotheses (configs[4])"),
+    "c2": dict(n=10_000, k=10_000, name="camera_pose_estimation N=10k x K=10k (configs[1])"),
+}
+
+
+def make_instance(n, data_seed=9000):
+    from ransaclib_b200 import synth
+
+    inst = synth.pose_instance(data_seed, n // 2, n - n // 2)
+    return inst["points2D"], inst["points3D"], inst["focal"], inst
+
+
+def make_samples(n, k, seed=42):
+    from ransaclib_b200.sampling import UniformSampling
+
+    return UniformSampling(seed, n, 4).sample_fast(k)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append((time.time(), ln.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ts, ln in self.lines:
+            if ts < t0 or ts > t1 + 0.2:
+                continue
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                               p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+# ------------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch
+
+    import ransaclib_b200 as rlb
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+    wl = WORKLOADS[args.workload]
+    n, k_total = wl["n"], wl["k"]
+    prec = rlb.RLB_F32 if args.precision == "f32" else rlb.RLB_F64
+    assert k_total % world == 0
+    k = k_total // world
+
+    p2, p3, f, inst = make_instance(n)
+    samples_all = make_samples(n, k_total)
+    my_samples = np.ascontiguousarray(samples_all[rank * k:(rank + 1) * k])  # contiguous id ranges per rank
+
+    ctx = rlb.Context(local)
+    stream = torch.cuda.current_stream(dev)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_timing(True)
+    scorer = ctx.pose_scorer(p2, p3, f, f)  # points resident in HBM before the timed region
+
+    d_samples = torch.from_numpy(my_samples).to(dev)
+    d_models = torch.empty((k, 12), dtype=torch.float64, device=dev)
+    d_valid = torch.empty(k, dtype=torch.uint8, device=dev)
+    d_scores = torch.empty(k, dtype=torch.float64, device=dev)
+    d_counts = torch.empty(k, dtype=torch.int32, device=dev)
+    d_best = torch.zeros(2, dtype=torch.float64, device=dev)  # {double score; int64 id}
+    d_pack = torch.zeros(14, dtype=torch.float64, device=dev)  # score, global id, model[12]
+    d_gather = torch.zeros((world, 14), dtype=torch.float64, device=dev)
+    d_win = torch.zeros(12, dtype=torch.float64, device=dev)
+    d_idx = torch.empty(n, dtype=torch.int32, device=dev)
+    d_hdr = torch.zeros(4, dtype=torch.float64, device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step():
+        scorer.hypothesize_and_score_dev(d_samples.data_ptr(), k, THR, None, d_models.data_ptr(),
+                                         d_valid.data_ptr(), d_scores.data_ptr(), d_counts.data_ptr(),
+                                         d_best.data_ptr(), precision=prec)
+        # pack (score, global hypothesis id, model) -- torch is plumbing here, not the hot path
+        lid = d_best.view(torch.int64)[1]
+        d_pack[0] = d_best[0]
+        d_pack[1] = (lid + rank * k).to(torch.float64)
+        d_pack[2:] = d_models[lid.clamp(min=0)]
+        if world > 1:
+            dist.all_gather_into_tensor(d_gather, d_pack)  # the single collective of the round
+            g = d_gather
+        else:
+            g = d_pack.view(1, 14)
+        # lexicographic (score, id) min: lowest id wins ties; ranks own ascending id ranges
+        smin = g[:, 0].min()
+        cand = torch.where(g[:, 0] == smin, g[:, 1], torch.full_like(g[:, 1], float("inf")))
+        w = torch.argmin(cand)
+        d_win.copy_(g[w, 2:])
+        scorer.get_inliers_dev(d_win.data_ptr(), THR, THR, None, d_idx.data_ptr(), d_hdr.data_ptr())
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+
+    # ---- timed region: device-resident inputs ------------------------------------
+    launches0 = ctx.launch_count
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    time.sleep(0.25)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sweep_ms, inl_ms = [], []
+    wall0 = time.time()
+    for s0, s1 in evs:
+        flush.zero_()  # L2 flush between timed iterations (untimed)
+        s0.record(stream)
+        step()
+        s1.record(stream)
+        s1.synchronize()
+        sweep_ms.append(ctx.kernel_time_ms(0))
+        inl_ms.append(ctx.kernel_time_ms(1))
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall1 = time.time()
+    launches = ctx.launch_count - launches0
+    clk = clocks.stop(wall0, wall1)
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # max over ranks
+    total_ms = float(t.item())
+    value = k_total * n * args.steps / (total_ms * 1e-3)
+
+    hdr = d_hdr.cpu().numpy()
+    n_inl = int(hdr.view(np.int32)[3])
+    best_score = float(d_hdr[0].item())
+
+    # ---- e2e: the same step through the host-buffer C ABI, copies inside the timed region ----
+    pin = lambda a: torch.from_numpy(a).pin_memory().numpy()  # noqa: E731
+    h_p2, h_p3, h_s = pin(p2), pin(p3), pin(my_samples)
+    e2e_steps = max(1, min(args.steps, 5))
+
+    def e2e_step():
+        sc = ctx.pose_scorer(h_p2, h_p3, f, f)  # H2D of the correspondences + SoA repack
+        r = sc.hypothesize_and_score(h_s, THR, precision=prec, want_models=False)
+        bm = r["best_model"]
+        if world > 1:
+            pk = torch.tensor([r["best_score"], float(r["best_id"] + rank * k), *bm], dtype=torch.float64,
+                              device=dev)
+            dist.all_gather_into_tensor(d_gather, pk)
+            g = d_gather.cpu().numpy()
+            order = np.lexsort((g[:, 1], g[:, 0]))
+            bm = g[order[0], 2:]
+        lists, counts, score = sc.get_inliers(bm, THR, THR)
+        sc.close()
+        return r, counts
+
+    e2e_step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        r_e2e, c_e2e = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = k_total * n * e2e_steps / float(te.item())
+    h2d = p2.nbytes + p3.nbytes + my_samples.nbytes + 12 * 8
+    d2h = k * 8 + k * 4 + 16 + 96 + 16 + 4 * int(c_e2e[0])
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (the K x N sweep) ------------------------
+    peaks, peak_kind = measured_peaks()
+    fma_dtype = 1 if prec == rlb.RLB_F32 else 0
+    fma_peak = ctx.measure_fma_peak(fma_dtype)
+    ffma2_peak = ctx.measure_fma_peak(2) if prec == rlb.RLB_F32 else None
+    sweep_avg_ms = float(np.mean(sweep_ms))
+    evals_per_launch = k * n
+    achieved_tflops = evals_per_launch * FLOP_PER_EVAL / (sweep_avg_ms * 1e-3) / 1e12
+    bpp = 20 if prec == rlb.RLB_F32 else 40
+    algo_bytes = n * bpp + k * 96 + k * 12
+    inl_avg_ms = float(np.mean(inl_ms))
+    inl_bytes = n * 40 + 4 * n_inl
+    roofline = {
+        "bound": "fma", "kernel": "sweep_kernel<PoseF,%s>" % ("float" if prec == rlb.RLB_F32 else "double"),
+        "achieved": achieved_tflops, "peak": fma_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fma_peak,
+        "peak_source": "rlb_measure_fma_peak: register-resident %s microbenchmark on this GPU, same run "
+                       "(MEASURED_PEAKS.json has no FMA-pipe figure)" % ("FFMA" if fma_dtype else "DFMA"),
+        "ffma2_peak_tflops": ffma2_peak,
+        "flop_per_eval": FLOP_PER_EVAL, "evals_per_launch": evals_per_launch, "launch_ms": sweep_avg_ms,
+        "evals_per_s": evals_per_launch / (sweep_avg_ms * 1e-3),
+        "share_of_step": sweep_avg_ms * args.steps / total_ms,
+        "traffic": None,
+        "hbm": {"algorithmic_bytes": algo_bytes, "achieved_gbs": algo_bytes / (sweep_avg_ms * 1e-3) / 1e9,
+                "peak_gbs": peaks.get("hbm_gbs"), "peak_kind": peak_kind,
+                "note": "arithmetic intensity ~%.0f FLOP/B: HBM is not the bound of this kernel"
+                        % (evals_per_launch * FLOP_PER_EVAL / algo_bytes)},
+        "inlier_pass": {"bound": "hbm", "launch_ms": inl_avg_ms, "algorithmic_bytes": inl_bytes,
+                        "achieved": inl_bytes / (inl_avg_ms * 1e-3) / 1e9, "peak": peaks.get("hbm_gbs"),
+                        "unit": "GB/s", "frac": inl_bytes / (inl_avg_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0)},
+    }
+
+    # ---- cpu baseline: the reference's loops on ONE host core, bounded sample -------
+    cpu = cpu_baseline(p2, p3, f, d_models[:64].cpu().numpy(), d_valid[:64].cpu().numpy(), threads=1,
+                       budget_s=12.0) if world == 1 else None
+
+    line = {
+        "metric": "MSAC hypothesis x point evals/sec", "value": value, "unit": "evals/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32" if prec == rlb.RLB_F32 else "f64", "data": "synthetic",
+        "config": {"workload": wl["name"], "n_points": n, "k_hypotheses": k_total, "k_per_gpu": k,
+                   "sq_thr": THR, "partitioning": "hypothesis-sharded, points replicated, 1 all_gather/step"
+                   if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
+                   "step": "P3P solve + KxN MSAC sweep + argmin + ordered inlier list of the winner"},
+        "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                "path": "rlb_scorer_create_pose + rlb_hypothesize_and_score + rlb_get_inliers with pinned host buffers"},
+        "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+        "result": {"num_inliers": n_inl, "best_score": best_score},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------- CPU baselines
+def _load_ref():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+
+    lib = ol.reference(fast=True)
+    kind = "reference"
+    if lib is None:
+        lib, kind = ol.oracle(), "port"
+    return ol, lib, kind
+
+
+def cpu_baseline(p2, p3, f, models, valid, threads, budget_s):
+    """Times the reference's own ScoreModel loop (RansacLib/ransac.h:295-303, compiled from
+    /root/reference into oracle/_ref with the reference's flags) on `threads` host threads over a
+    bounded sample: all N points x as many hypotheses as fit the budget."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    ol, lib, kind = _load_ref()
+    models = np.ascontiguousarray(models[valid == 1] if (valid == 1).any() else models)
+    n = len(p2)
+    p2c, p3c = ol.c64(p2), ol.c64(p3)
+    t_probe = lib.time_pose_scoring(f, f, n, p2c, p3c, 1, models[:1], THR, 1, None)
+    k_each = int(max(1, min(4096, budget_s / max(t_probe, 1e-6))))
+    reps = (k_each + len(models) - 1) // len(models)
+    ms = np.ascontiguousarray(np.tile(models, (reps, 1))[:k_each])
+
+    def work(_):
+        return lib.time_pose_scoring(f, f, n, p2c, p3c, k_each, ms, THR, 1, None)
+
+    t0 = time.perf_counter()
+    if threads == 1:
+        work(0)
+    else:
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(work, range(threads)))
+    dt = time.perf_counter() - t0
+    return {"value": threads * k_each * n / dt, "unit": "evals/s", "cores": threads, "kind": kind,
+            "sample": f"ScoreModel over all {n} points x {k_each} hypotheses per thread, "
+                      f"{threads} thread(s), {dt:.1f} s; reference ransac.h loops + Eigen-free solver "
+                      f"restatement (Eigen/PoseLib/Ceres absent), -O3 -march=x86-64-v3, "
+                      f"EvaluateModelOnPoint out-of-line as in the reference", "seconds": dt}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    wl = WORKLOADS[args.workload]
+    n, k_total = wl["n"], wl["k"]
+    p2, p3, f, inst = make_instance(n)
+    from ransaclib_b200 import synth
+
+    models = synth.perturbed_poses(1, inst["R_gt"], inst["c_gt"], 64)
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    # bounded sample per step: ~0.7 s of work per thread
+    per_step_budget = 0.7
+    res = []
+    for i in range(args.warmup + args.steps):
+        r = cpu_baseline(p2, p3, f, models, np.ones(len(models), np.uint8), threads=cores,
+                         budget_s=per_step_budget)
+        if i >= args.warmup:
+            res.append(r)
+    evals = sum(r["value"] * r["seconds"] for r in res)
+    secs = sum(r["seconds"] for r in res)
+    value = evals / secs
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    line = {
+        "impl": "reference", "metric": "MSAC hypothesis x point evals/sec", "value": value, "unit": "evals/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl["name"], "n_points": n, "k_hypotheses": k_total,
+                   "note": "CPU reference: each step is a bounded sample of the workload (all N points x a "
+                           "subset of hypotheses) on every host core"},
+        "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": res[-1]["kind"],
+                         "sample": res[-1]["sample"]},
+        "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c5", choices=list(WORKLOADS))
+    ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

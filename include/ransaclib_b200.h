@@ -1,0 +1,175 @@
+/*
+ * ransaclib_b200 — C ABI of the B200-native MSAC scoring path.
+ *
+ * This is the drop-in boundary for ONE path of tsattler/RansacLib: hypothesis
+ * scoring / inlier collection (RansacLib/ransac.h:278-336, hybrid_ransac.h:386-462)
+ * evaluating the example solvers' EvaluateModelOnPoint
+ * (examples/calibrated_absolute_pose_estimator.cc:154-167, line_estimator.cc:110-114,
+ * hybrid_line_estimator.cc:100-109) plus the batched minimal solvers that produce
+ * the hypotheses (calibrated_absolute_pose_estimator.cc:111-137, line_estimator.cc:53-72,
+ * hybrid_line_estimator.cc:111-152). The reference has no FFI for this path (it is
+ * a header-only C++ template library); the entry points below are what the
+ * template layer in include/RansacLib/ and a pybind/ctypes module bind instead of
+ * the CPU loops. See INTEGRATION.md for the reference-side binding.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no C++ or torch types cross this boundary;
+ *  - every function returns RLB_OK (0) or a negative RLB_E_* code; the message is
+ *    available from rlb_last_error() (thread-local);
+ *  - there is NO CPU fallback: without a CUDA device every call fails loudly;
+ *  - host layouts are the reference's: points (n,2)/(n,3)/(n,4) row-major doubles
+ *    (== column-major Eigen::Matrix2Xd/Matrix4Xd, std::vector<Eigen::Vector3d>),
+ *    line model = 3 doubles (a,b,c), pose model = 12 doubles = column-major 3x4
+ *    [R | c] (calibrated_absolute_pose_estimator.h:55,68-70);
+ *  - functions ending in _dev take DEVICE pointers and only enqueue work on the
+ *    context's stream (inputs already resident in HBM); all others take HOST
+ *    pointers and return after the results are on the host.
+ */
+#ifndef RANSACLIB_B200_H_
+#define RANSACLIB_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RLB_OK 0
+#define RLB_E_CUDA -1     /* CUDA runtime error (no device, launch failure, ...) */
+#define RLB_E_ARG -2      /* invalid argument */
+#define RLB_E_KIND -3     /* operation not defined for this scorer kind */
+#define RLB_E_NOMEM -4
+
+/* arithmetic the K x N sweep runs in. Inlier lists are always collected in f64. */
+#define RLB_F64 0 /* reference-exact semantics, scores within 1e-9 rel */
+#define RLB_F32 1 /* recentred f32 inner sums, f64 outer sums; within 1e-4 rel */
+
+#define RLB_KIND_LINE 0        /* examples/line_estimator */
+#define RLB_KIND_HYBRID_LINE 1 /* examples/hybrid_line_estimator (2 data types) */
+#define RLB_KIND_POSE 2        /* examples/calibrated_absolute_pose_estimator */
+
+typedef struct rlb_ctx rlb_ctx;       /* one device + one stream + scratch; not thread-safe */
+typedef struct rlb_scorer rlb_scorer; /* one data set resident in HBM; immutable */
+
+const char* rlb_last_error(void);
+int rlb_version(void);
+
+/* ---- context ------------------------------------------------------------- */
+int rlb_ctx_create(int device, rlb_ctx** ctx);
+int rlb_ctx_destroy(rlb_ctx* ctx);
+/* Use an existing cudaStream_t (e.g. torch's current stream); NULL restores the
+ * context's own stream. */
+int rlb_ctx_set_stream(rlb_ctx* ctx, void* cuda_stream);
+int rlb_ctx_synchronize(rlb_ctx* ctx);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+int64_t rlb_ctx_launch_count(const rlb_ctx* ctx);
+/* Number of SMs of the context's device. */
+int rlb_ctx_sm_count(const rlb_ctx* ctx);
+
+/* ---- data sets ("the solver owns the data", README.md:157) --------------- */
+/* LineEstimator(data): xy = n x 2 (line_estimator.cc:47-50). */
+int rlb_scorer_create_line(rlb_ctx* ctx, int n, const double* xy, rlb_scorer** out);
+/* HybridLineEstimator(points, points_with_normals, .): xy0 = n0 x 2, xynn1 = n1 x 4
+ * (hybrid_line_estimator.cc:47-56). */
+int rlb_scorer_create_hybrid_line(rlb_ctx* ctx, int n0, const double* xy0, int n1,
+                                  const double* xynn1, rlb_scorer** out);
+/* CalibratedAbsolutePoseEstimator(fx, fy, ., points2D, rays, points3D)
+ * (calibrated_absolute_pose_estimator.cc:99-109); rays are derived on the device
+ * as PixelsToViewingRays does (.cc:214-227). */
+int rlb_scorer_create_pose(rlb_ctx* ctx, int n, const double* points2D,
+                           const double* points3D, double fx, double fy, rlb_scorer** out);
+int rlb_scorer_destroy(rlb_scorer* s);
+int rlb_scorer_kind(const rlb_scorer* s);
+int rlb_scorer_num_types(const rlb_scorer* s);
+int rlb_scorer_num_data(const rlb_scorer* s, int type);
+int rlb_scorer_model_size(const rlb_scorer* s); /* doubles per model: 3 or 12 */
+/* Copies the device-computed viewing rays (n x 3) back; pose scorers only. */
+int rlb_scorer_get_rays(const rlb_scorer* s, double* rays);
+
+/* ---- the hot path --------------------------------------------------------- */
+/* ScoreModel + inlier count for K models and the cross-hypothesis argmin
+ * (ransac.h:278-303, 311-323; hybrid_ransac.h:386-421).
+ *   models  K x model_size doubles
+ *   valid   K bytes or NULL; valid[k]==0 means MinimalSolver returned no model
+ *           (ransac.h:185): score = DBL_MAX, count = 0, never wins
+ *   sq_thr  one squared threshold per data type; weights one per type or NULL (=1)
+ *   scores  K doubles (out, may be NULL); counts K int32 (out, may be NULL)
+ *   best_id lowest k with the smallest score < DBL_MAX, or -1; best_score its score
+ * A model with a non-finite entry scores NaN and never wins. */
+int rlb_score_models(rlb_scorer* s, int precision, int k, const double* models,
+                     const uint8_t* valid, const double* sq_thr, const double* weights,
+                     double* scores, int32_t* counts, int32_t* best_id, double* best_score);
+
+/* Same with device pointers; asynchronous on the context stream. best is a device
+ * pointer to {double score; int64 id} (16 bytes). */
+int rlb_score_models_dev(rlb_scorer* s, int precision, int k, const double* d_models,
+                         const uint8_t* d_valid, const double* sq_thr, const double* weights,
+                         double* d_scores, int32_t* d_counts, void* d_best);
+
+/* GetInliers fused with ScoreModel for ONE model (ransac.h:311-336 and the LO
+ * pattern ransac.h:386->391, 401->399, 364->369):
+ *   sq_thr_inl    per-type squared threshold for the inlier test (strict <)
+ *   sq_thr_score  per-type threshold for the MSAC score, or NULL (no score)
+ *   idx           out, ascending indices; type-0 list first, then type-1 list; capacity
+ *                 sum of num_data; may be NULL to only count
+ *   counts        out, inliers per type
+ *   score         out or NULL
+ * Always f64. */
+int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl,
+                    const double* sq_thr_score, const double* weights, int32_t* idx,
+                    int32_t* counts, double* score);
+/* Device-output variant: d_idx (capacity sum num_data), d_header = {double score;
+ * int32 count[2]; int32 pad} on the device; asynchronous. */
+int rlb_get_inliers_dev(rlb_scorer* s, const double* d_model, const double* sq_thr_inl,
+                        const double* sq_thr_score, const double* weights, int32_t* d_idx,
+                        void* d_header);
+
+/* Squared residuals of ONE model on every point of one data type (debug / functor
+ * parity tests; EvaluateModelOnPoint itself). err: num_data(type) doubles. */
+int rlb_eval_errors(rlb_scorer* s, int precision, const double* model, int type, double* err);
+
+/* ---- batched minimal solvers (one sample per thread) ---------------------- */
+/* LineEstimator::MinimalSolver / HybridLineEstimator::TwoPointSolver: samples K x 2
+ * indices into data type 0 -> K x 3 lines. */
+int rlb_solve_line2pt_batch(rlb_scorer* s, int k, const int32_t* samples, double* models,
+                            uint8_t* valid);
+/* HybridLineEstimator::PointNormalSolver: samples K indices into data type 1. */
+int rlb_solve_point_normal_batch(rlb_scorer* s, int k, const int32_t* samples, double* models,
+                                 uint8_t* valid);
+/* CalibratedAbsolutePoseEstimator::MinimalSolver: samples K x 4; P3P on the first 3,
+ * first solution whose error on the 4th is < sq_thr wins. */
+int rlb_solve_p3p_batch(rlb_scorer* s, int k, const int32_t* samples, double sq_thr,
+                        double* models, uint8_t* valid);
+
+/* Hypothesise + score in one call: samples go up, hypotheses stay on the device.
+ *   solver: 0 = the kind's first minimal solver (2-point line / P3P+4th point),
+ *           1 = point+normal (hybrid only)
+ *   samples: K x sample_size int32 (sample_size 2, 1 or 4)
+ *   models/valid/scores/counts: optional host outputs (may be NULL). */
+int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
+                              const int32_t* samples, const double* sq_thr,
+                              const double* weights, double* models, uint8_t* valid,
+                              double* scores, int32_t* counts, int32_t* best_id,
+                              double* best_score, double* best_model);
+/* Device-pointer variant (samples already in HBM, outputs stay in HBM). */
+int rlb_hypothesize_and_score_dev(rlb_scorer* s, int precision, int solver, int k,
+                                  const int32_t* d_samples, const double* sq_thr,
+                                  const double* weights, double* d_models, uint8_t* d_valid,
+                                  double* d_scores, int32_t* d_counts, void* d_best);
+
+/* ---- measurement helpers --------------------------------------------------- */
+/* When enabled, the context brackets every sweep kernel and every inlier kernel with
+ * CUDA events on its stream; rlb_ctx_kernel_time_ms waits for the LAST such kernel
+ * and returns its device time (which: 0 = K x N sweep, 1 = inlier pass). */
+int rlb_ctx_set_timing(rlb_ctx* ctx, int enabled);
+int rlb_ctx_kernel_time_ms(rlb_ctx* ctx, int which, double* ms);
+/* Register-resident FMA microbenchmark: returns achieved TFLOP/s of the FP32
+ * (dtype 1: FFMA, 2: packed FFMA2) or FP64 (dtype 0: DFMA) pipe on this device.
+ * Used by bench.py for the FMA-pipe roofline denominator ("of measured"). */
+int rlb_measure_fma_peak(rlb_ctx* ctx, int dtype, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* RANSACLIB_B200_H_ */

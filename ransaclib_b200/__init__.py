@@ -1,0 +1,244 @@
+"""ransaclib_b200 — B200-native MSAC hypothesis scoring behind the RansacLib API.
+
+Python mirror of the drop-in surface. Everything numerical happens in hand-written
+CUDA kernels (``csrc/``) reached through the C ABI of ``include/ransaclib_b200.h``;
+this package only marshals numpy buffers. No CPU fallback exists.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import KIND_HYBRID_LINE, KIND_LINE, KIND_POSE, RLB_F32, RLB_F64, RlbError
+
+__all__ = ["Context", "Scorer", "RLB_F64", "RLB_F32", "RlbError", "KIND_LINE", "KIND_HYBRID_LINE", "KIND_POSE"]
+
+DBL_MAX = float(np.finfo(np.float64).max)
+
+
+class Context:
+    """One device + one stream + scratch memory (``rlb_ctx``)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _capi.load()
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_ctx_create(device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rlb_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream: int | None):
+        _capi.check(self._lib.rlb_ctx_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
+
+    def synchronize(self):
+        _capi.check(self._lib.rlb_ctx_synchronize(self._h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.rlb_ctx_launch_count(self._h))
+
+    @property
+    def sm_count(self) -> int:
+        return int(self._lib.rlb_ctx_sm_count(self._h))
+
+    def set_timing(self, enabled: bool):
+        _capi.check(self._lib.rlb_ctx_set_timing(self._h, int(enabled)))
+
+    def kernel_time_ms(self, which: int) -> float:
+        """Device time of the last sweep (0) / inlier (1) kernel; needs set_timing(True)."""
+        out = C.c_double()
+        _capi.check(self._lib.rlb_ctx_kernel_time_ms(self._h, which, C.byref(out)))
+        return out.value
+
+    def measure_fma_peak(self, dtype: int) -> float:
+        """TFLOP/s of the DFMA (0), FFMA (1) or packed FFMA2 (2) pipe, register-resident."""
+        out = C.c_double()
+        _capi.check(self._lib.rlb_measure_fma_peak(self._h, dtype, C.byref(out)))
+        return out.value
+
+    # -- data sets -----------------------------------------------------------
+    def line_scorer(self, xy) -> "Scorer":
+        xy = _capi.f64a(xy, (-1, 2))
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_scorer_create_line(self._h, len(xy), _capi.ptr(xy), C.byref(h)))
+        return Scorer(self, h)
+
+    def hybrid_line_scorer(self, xy0, xynn1) -> "Scorer":
+        xy0 = _capi.f64a(xy0, (-1, 2))
+        xynn1 = _capi.f64a(xynn1, (-1, 4))
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_scorer_create_hybrid_line(self._h, len(xy0), _capi.ptr(xy0), len(xynn1),
+                                                            _capi.ptr(xynn1), C.byref(h)))
+        return Scorer(self, h)
+
+    def pose_scorer(self, points2D, points3D, fx: float, fy: float) -> "Scorer":
+        p2 = _capi.f64a(points2D, (-1, 2))
+        p3 = _capi.f64a(points3D, (-1, 3))
+        if len(p2) != len(p3):
+            raise ValueError("points2D and points3D must have the same length")
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_scorer_create_pose(self._h, len(p2), _capi.ptr(p2), _capi.ptr(p3), float(fx),
+                                                     float(fy), C.byref(h)))
+        return Scorer(self, h)
+
+
+class Scorer:
+    """A data set resident in HBM plus the functor that scores models on it (``rlb_scorer``)."""
+
+    def __init__(self, ctx: Context, handle):
+        self.ctx = ctx
+        self._lib = ctx._lib
+        self._h = handle
+        self.kind = self._lib.rlb_scorer_kind(handle)
+        self.num_types = self._lib.rlb_scorer_num_types(handle)
+        self.num_data = [self._lib.rlb_scorer_num_data(handle, t) for t in range(self.num_types)]
+        self.model_size = self._lib.rlb_scorer_model_size(handle)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rlb_scorer_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _thr(self, v):
+        a = np.atleast_1d(np.asarray(v, dtype=np.float64))
+        if len(a) == 1 and self.num_types == 2:
+            a = np.repeat(a, 2)
+        if len(a) != self.num_types:
+            raise ValueError("need one value per data type")
+        return np.ascontiguousarray(a)
+
+    def rays(self):
+        out = np.empty((self.num_data[0], 3))
+        _capi.check(self._lib.rlb_scorer_get_rays(self._h, _capi.ptr(out)))
+        return out
+
+    def score_models(self, models, sq_thr, weights=None, valid=None, precision=RLB_F64):
+        """-> (scores[K], counts[K], best_id, best_score)."""
+        models = _capi.f64a(models, (-1, self.model_size))
+        k = len(models)
+        thr = self._thr(sq_thr)
+        w = None if weights is None else self._thr(weights)
+        v = None if valid is None else np.ascontiguousarray(valid, dtype=np.uint8)
+        scores = np.empty(k)
+        counts = np.empty(k, np.int32)
+        bid = C.c_int32()
+        bsc = C.c_double()
+        _capi.check(self._lib.rlb_score_models(self._h, precision, k, _capi.ptr(models), _capi.ptr(v),
+                                               _capi.ptr(thr), _capi.ptr(w), _capi.ptr(scores), _capi.ptr(counts),
+                                               C.addressof(bid), C.addressof(bsc)))
+        return scores, counts, bid.value, bsc.value
+
+    def get_inliers(self, model, sq_thr_inl, sq_thr_score=None, weights=None, want_indices=True):
+        """-> (list of per-type ascending index arrays, per-type counts, score or None)."""
+        model = _capi.f64a(model, (self.model_size,))
+        ti = self._thr(sq_thr_inl)
+        ts = None if sq_thr_score is None else self._thr(sq_thr_score)
+        w = None if weights is None else self._thr(weights)
+        idx = np.empty(max(sum(self.num_data), 1), np.int32) if want_indices else None
+        counts = np.zeros(2, np.int32)
+        score = C.c_double()
+        _capi.check(self._lib.rlb_get_inliers(self._h, _capi.ptr(model), _capi.ptr(ti), _capi.ptr(ts), _capi.ptr(w),
+                                              _capi.ptr(idx), _capi.ptr(counts), C.addressof(score)))
+        lists = None
+        if want_indices:
+            lists, p = [], 0
+            for t in range(self.num_types):
+                lists.append(idx[p:p + counts[t]].copy())
+                p += counts[t]
+        return lists, counts[:self.num_types].copy(), (score.value if ts is not None else None)
+
+    def eval_errors(self, model, type_: int = 0, precision=RLB_F64):
+        model = _capi.f64a(model, (self.model_size,))
+        err = np.empty(self.num_data[type_])
+        _capi.check(self._lib.rlb_eval_errors(self._h, precision, _capi.ptr(model), type_, _capi.ptr(err)))
+        return err
+
+    def solve_line2pt(self, samples):
+        s = _capi.i32a(samples, (-1, 2))
+        models = np.empty((len(s), 3))
+        valid = np.empty(len(s), np.uint8)
+        _capi.check(self._lib.rlb_solve_line2pt_batch(self._h, len(s), _capi.ptr(s), _capi.ptr(models),
+                                                      _capi.ptr(valid)))
+        return models, valid
+
+    def solve_point_normal(self, samples):
+        s = _capi.i32a(samples, (-1,))
+        models = np.empty((len(s), 3))
+        valid = np.empty(len(s), np.uint8)
+        _capi.check(self._lib.rlb_solve_point_normal_batch(self._h, len(s), _capi.ptr(s), _capi.ptr(models),
+                                                           _capi.ptr(valid)))
+        return models, valid
+
+    def solve_p3p(self, samples, sq_thr: float):
+        s = _capi.i32a(samples, (-1, 4))
+        models = np.empty((len(s), 12))
+        valid = np.empty(len(s), np.uint8)
+        _capi.check(self._lib.rlb_solve_p3p_batch(self._h, len(s), _capi.ptr(s), float(sq_thr), _capi.ptr(models),
+                                                  _capi.ptr(valid)))
+        return models, valid
+
+    # -- device-pointer entry points (inputs resident in HBM; asynchronous) ----
+    def hypothesize_and_score_dev(self, d_samples: int, k: int, sq_thr, weights, d_models: int, d_valid: int,
+                                  d_scores: int, d_counts: int, d_best: int, solver: int = 0, precision=RLB_F64):
+        thr = self._thr(sq_thr)
+        w = None if weights is None else self._thr(weights)
+        _capi.check(self._lib.rlb_hypothesize_and_score_dev(
+            self._h, precision, solver, k, C.c_void_p(d_samples), _capi.ptr(thr), _capi.ptr(w),
+            C.c_void_p(d_models), C.c_void_p(d_valid), C.c_void_p(d_scores or 0), C.c_void_p(d_counts or 0),
+            C.c_void_p(d_best)))
+
+    def score_models_dev(self, d_models: int, k: int, sq_thr, weights, d_valid: int, d_scores: int, d_counts: int,
+                         d_best: int, precision=RLB_F64):
+        thr = self._thr(sq_thr)
+        w = None if weights is None else self._thr(weights)
+        _capi.check(self._lib.rlb_score_models_dev(
+            self._h, precision, k, C.c_void_p(d_models), C.c_void_p(d_valid or 0), _capi.ptr(thr), _capi.ptr(w),
+            C.c_void_p(d_scores or 0), C.c_void_p(d_counts or 0), C.c_void_p(d_best)))
+
+    def get_inliers_dev(self, d_model: int, sq_thr_inl, sq_thr_score, weights, d_idx: int, d_header: int):
+        ti = self._thr(sq_thr_inl)
+        ts = None if sq_thr_score is None else self._thr(sq_thr_score)
+        w = None if weights is None else self._thr(weights)
+        _capi.check(self._lib.rlb_get_inliers_dev(self._h, C.c_void_p(d_model), _capi.ptr(ti), _capi.ptr(ts),
+                                                  _capi.ptr(w), C.c_void_p(d_idx or 0), C.c_void_p(d_header)))
+
+    def hypothesize_and_score(self, samples, sq_thr, weights=None, solver: int = 0, precision=RLB_F64,
+                              want_models=True, want_scores=True):
+        """Samples up, hypotheses stay on the device. -> dict."""
+        ss = {(KIND_POSE, 0): 4, (KIND_LINE, 0): 2, (KIND_HYBRID_LINE, 0): 2, (KIND_HYBRID_LINE, 1): 1}[
+            (self.kind, solver)]
+        s = _capi.i32a(samples, (-1, ss))
+        k = len(s)
+        thr = self._thr(sq_thr)
+        w = None if weights is None else self._thr(weights)
+        models = np.empty((k, self.model_size)) if want_models else None
+        valid = np.empty(k, np.uint8) if want_models else None
+        scores = np.empty(k) if want_scores else None
+        counts = np.empty(k, np.int32) if want_scores else None
+        bid = C.c_int32()
+        bsc = C.c_double()
+        bm = np.zeros(self.model_size)
+        _capi.check(self._lib.rlb_hypothesize_and_score(
+            self._h, precision, solver, k, _capi.ptr(s), _capi.ptr(thr), _capi.ptr(w), _capi.ptr(models),
+            _capi.ptr(valid), _capi.ptr(scores), _capi.ptr(counts), C.addressof(bid), C.addressof(bsc),
+            _capi.ptr(bm)))
+        return {"models": models, "valid": valid, "scores": scores, "counts": counts, "best_id": bid.value,
+                "best_score": bsc.value, "best_model": bm if bid.value >= 0 else None}

@@ -1,0 +1,767 @@
+// C ABI of ransaclib_b200 (see include/ransaclib_b200.h). Host-side plumbing only:
+// device memory, the stream, scratch buffers and launch sequencing. There is no CPU
+// implementation of any entry point: if CUDA is unavailable every call fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "rlb_internal.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define RLB_CUDA(call)                                                                      \
+  do {                                                                                      \
+    cudaError_t e__ = (call);                                                               \
+    if (e__ != cudaSuccess)                                                                 \
+      return fail(RLB_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),      \
+                  __FILE__, __LINE__);                                                      \
+  } while (0)
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max<size_t>(bytes, 256);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T>
+  T* as() const {
+    return static_cast<T*>(p);
+  }
+};
+
+}  // namespace
+
+struct rlb_ctx {
+  int device = 0;
+  int sms = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  int launches_i = 0;  // per-call counter target for the launch_* helpers
+  int64_t launches = 0;
+  unsigned int epoch = 0;
+  // sweep scratch
+  DevBuf models, valid, samples, scores, counts, part_score, part_count, block_best, small;
+  // inlier scratch
+  DevBuf one_model, idx, tile_score, status, header;
+  // pinned host staging for tiny results
+  void* h_small = nullptr;
+  // optional per-kernel timing (bench.py's roofline numbers)
+  bool timing = false;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // sweep begin/end, inlier begin/end
+  bool ev_valid[2] = {false, false};
+};
+
+struct rlb_scorer {
+  rlb_ctx* ctx = nullptr;
+  rlb::DeviceData d;
+  void* raw0 = nullptr;
+  void* raw1 = nullptr;
+  void* rays = nullptr;
+  void* soa64 = nullptr;
+  void* soa32 = nullptr;
+};
+
+namespace {
+
+using rlb::BestRec;
+using rlb::DeviceData;
+using rlb::InlierArgs;
+using rlb::InlierHeader;
+using rlb::SweepArgs;
+
+// layout of ctx->small: [0] BestRec best, [64] uint ticket, [128] uint control[2], [192] best model (12 d)
+constexpr size_t kSmallBest = 0, kSmallTicket = 64, kSmallControl = 128, kSmallBestModel = 192,
+                 kSmallBytes = 512;
+
+inline int pad_to(int n, int a) { return (n + a - 1) / a * a; }
+
+void account(rlb_ctx* c) {
+  c->launches += c->launches_i;
+  c->launches_i = 0;
+}
+
+int ctx_use(rlb_ctx* c) {
+  RLB_CUDA(cudaSetDevice(c->device));
+  return RLB_OK;
+}
+
+// Sub-sampled mean as the recentring point (any point inside the cloud works; it only
+// has to make |X - centre| small so f32 keeps its 24 bits for the part that matters).
+void subsampled_mean(const double* p, int n, int stride, int dims, double* out) {
+  for (int c = 0; c < 3; ++c) out[c] = 0.0;
+  if (n <= 0) return;
+  const int step = std::max(1, n / 4096);
+  int m = 0;
+  for (int i = 0; i < n; i += step, ++m)
+    for (int c = 0; c < dims; ++c) out[c] += p[static_cast<size_t>(i) * stride + c];
+  for (int c = 0; c < dims; ++c) {
+    out[c] /= static_cast<double>(m);
+    if (!(out[c] - out[c] == 0.0)) out[c] = 0.0;
+  }
+}
+
+int finish_scorer(rlb_scorer* s) {
+  rlb_ctx* c = s->ctx;
+  DeviceData& d = s->d;
+  const size_t ch = static_cast<size_t>(d.channels) * d.npad;
+  RLB_CUDA(cudaMalloc(&s->soa64, ch * sizeof(double)));
+  RLB_CUDA(cudaMalloc(&s->soa32, ch * sizeof(float)));
+  d.soa64 = static_cast<const double*>(s->soa64);
+  d.soa32 = static_cast<const float*>(s->soa32);
+  RLB_CUDA(rlb::launch_repack(d, static_cast<double*>(s->soa64), static_cast<float*>(s->soa32),
+                              c->stream, &c->launches_i));
+  if (d.kind == RLB_KIND_POSE) {
+    RLB_CUDA(cudaMalloc(&s->rays, static_cast<size_t>(std::max(d.n[0], 1)) * 3 * sizeof(double)));
+    d.rays = static_cast<const double*>(s->rays);
+    RLB_CUDA(rlb::launch_rays(d, static_cast<double*>(s->rays), c->stream, &c->launches_i));
+  }
+  account(c);
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  return RLB_OK;
+}
+
+int upload(void** dst, const double* src, size_t count, cudaStream_t st) {
+  RLB_CUDA(cudaMalloc(dst, std::max<size_t>(count, 1) * sizeof(double)));
+  if (count) RLB_CUDA(cudaMemcpyAsync(*dst, src, count * sizeof(double), cudaMemcpyHostToDevice, st));
+  return RLB_OK;
+}
+
+int check_scorer(const rlb_scorer* s) {
+  if (!s || !s->ctx) return fail(RLB_E_ARG, "null scorer");
+  return RLB_OK;
+}
+
+void fill_thr(const DeviceData& d, const double* thr, const double* w, double* thr_out,
+              double* w_out) {
+  for (int t = 0; t < rlb::kMaxTypes; ++t) {
+    thr_out[t] = thr ? thr[std::min(t, d.num_types - 1)] : 0.0;
+    w_out[t] = w ? w[std::min(t, d.num_types - 1)] : 1.0;
+  }
+}
+
+int ensure_first_use(rlb_ctx* c) {
+  if (c->small.cap == 0) {
+    RLB_CUDA(c->small.ensure(kSmallBytes));
+    RLB_CUDA(cudaMemsetAsync(c->small.p, 0, kSmallBytes, c->stream));
+  }
+  return RLB_OK;
+}
+
+// Enqueue sweep + finalize for K models that are already on the device.
+int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const uint8_t* d_valid,
+              const double* thr, const double* w, double* d_scores, int32_t* d_counts,
+              BestRec* d_best, double* d_best_model) {
+  rlb_ctx* c = s->ctx;
+  const DeviceData& d = s->d;
+  if (precision != RLB_F64 && precision != RLB_F32) return fail(RLB_E_ARG, "bad precision %d", precision);
+  if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
+  if (!thr) return fail(RLB_E_ARG, "sq_thr is required");
+  {
+    const int rc0 = ensure_first_use(c);
+    if (rc0) return rc0;
+  }
+
+  SweepArgs a;
+  a.k = k;
+  a.models = d_models;
+  a.valid = d_valid;
+  fill_thr(d, thr, w, a.thr, a.w);
+  const int H = (precision == RLB_F32) ? 4 : (d.kind == RLB_KIND_POSE ? 2 : 4);
+  const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
+  const int total_stages = d.npad / rlb::kStage;
+  // Aim for ~8 waves of 4 resident CTAs per SM so the tail wave is short; never split finer
+  // than one stage, never more than 64 ways (partials are [splits][k]).
+  const int target = c->sms * 4 * 8;
+  int splits = std::max(1, std::min({(target + k_tiles - 1) / k_tiles, total_stages, 64}));
+  const int sps = (total_stages + splits - 1) / splits;
+  splits = (total_stages + sps - 1) / sps;
+  a.n_splits = splits;
+  a.stages_per_split = sps;
+  RLB_CUDA(c->part_score.ensure(static_cast<size_t>(splits) * k * sizeof(double)));
+  RLB_CUDA(c->part_count.ensure(static_cast<size_t>(splits) * k * sizeof(int32_t)));
+  a.part_score = c->part_score.as<double>();
+  a.part_count = c->part_count.as<int32_t>();
+  const int fblocks = (k + 255) / 256;
+  RLB_CUDA(c->block_best.ensure(static_cast<size_t>(fblocks) * sizeof(BestRec)));
+
+  if (c->timing) RLB_CUDA(cudaEventRecord(c->ev[0], c->stream));
+  RLB_CUDA(rlb::launch_sweep(d, a, precision, c->stream, &c->launches_i));
+  if (c->timing) {
+    RLB_CUDA(cudaEventRecord(c->ev[1], c->stream));
+    c->ev_valid[0] = true;
+  }
+  RLB_CUDA(rlb::launch_finalize(
+      d, a, d_scores, d_counts, c->block_best.as<BestRec>(),
+      reinterpret_cast<unsigned int*>(c->small.as<char>() + kSmallTicket), d_best, d_best_model,
+      c->stream, &c->launches_i));
+  account(c);
+  return RLB_OK;
+}
+
+int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, const double* thr_score,
+                const double* w, int32_t* d_idx, void* d_header) {
+  rlb_ctx* c = s->ctx;
+  const DeviceData& d = s->d;
+  if (!thr_inl) return fail(RLB_E_ARG, "sq_thr_inl is required");
+  const int tiles = d.npad / rlb::kInlTile;
+  int rc = ensure_first_use(c);
+  if (rc) return rc;
+  if (static_cast<size_t>(tiles) * 8 > c->status.cap) {
+    RLB_CUDA(c->status.ensure(static_cast<size_t>(tiles) * 8));
+    RLB_CUDA(cudaMemsetAsync(c->status.p, 0, c->status.cap, c->stream));
+  }
+  RLB_CUDA(c->tile_score.ensure(static_cast<size_t>(tiles) * sizeof(double)));
+  InlierArgs a;
+  a.model = d_model;
+  fill_thr(d, thr_inl, w, a.thr_inl, a.w);
+  double dummy[rlb::kMaxTypes];
+  fill_thr(d, thr_score ? thr_score : thr_inl, w, a.thr_score, dummy);
+  a.want_score = thr_score ? 1 : 0;
+  a.idx = d_idx;
+  a.tile_score = c->tile_score.as<double>();
+  a.status = c->status.as<unsigned long long>();
+  a.control = reinterpret_cast<unsigned int*>(c->small.as<char>() + kSmallControl);
+  c->epoch = (c->epoch % 0x3fffffffu) + 1u;
+  a.epoch = c->epoch;
+  a.header = d_header;
+  if (c->timing) RLB_CUDA(cudaEventRecord(c->ev[2], c->stream));
+  RLB_CUDA(rlb::launch_inliers(d, a, c->stream, &c->launches_i));
+  if (c->timing) {
+    RLB_CUDA(cudaEventRecord(c->ev[3], c->stream));
+    c->ev_valid[1] = true;
+  }
+  account(c);
+  return RLB_OK;
+}
+
+int solver_sample_size(const DeviceData& d, int solver) {
+  if (d.kind == RLB_KIND_POSE) return solver == 0 ? 4 : -1;
+  if (d.kind == RLB_KIND_LINE) return solver == 0 ? 2 : -1;
+  return solver == 0 ? 2 : (solver == 1 ? 1 : -1);
+}
+
+int solve_dev(rlb_scorer* s, int solver, int k, const int32_t* d_samples, double sq_thr,
+              double* d_models, uint8_t* d_valid) {
+  rlb_ctx* c = s->ctx;
+  const DeviceData& d = s->d;
+  if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
+  if (solver_sample_size(d, solver) < 0) return fail(RLB_E_KIND, "solver %d undefined for kind %d", solver, d.kind);
+  if (d.kind == RLB_KIND_POSE) {
+    RLB_CUDA(rlb::launch_solve_p3p(d, k, d_samples, sq_thr, d_models, d_valid, c->stream, &c->launches_i));
+  } else if (solver == 0) {
+    RLB_CUDA(rlb::launch_solve_line2pt(d, k, d_samples, d_models, d_valid, c->stream, &c->launches_i));
+  } else {
+    RLB_CUDA(rlb::launch_solve_point_normal(d, k, d_samples, d_models, d_valid, c->stream, &c->launches_i));
+  }
+  account(c);
+  return RLB_OK;
+}
+
+int check_samples(const DeviceData& d, int solver, int k, const int32_t* samples) {
+  const int ss = solver_sample_size(d, solver);
+  if (ss < 0) return fail(RLB_E_KIND, "solver %d undefined for kind %d", solver, d.kind);
+  const int type = (d.kind == RLB_KIND_HYBRID_LINE && solver == 1) ? 1 : 0;
+  const int n = d.n[type];
+  for (size_t i = 0; i < static_cast<size_t>(k) * ss; ++i)
+    if (samples[i] < 0 || samples[i] >= n)
+      return fail(RLB_E_ARG, "sample index %d out of range [0,%d)", samples[i], n);
+  return RLB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rlb_last_error(void) { return g_err; }
+int rlb_version(void) { return 100; }
+
+int rlb_ctx_create(int device, rlb_ctx** out) {
+  if (!out) return fail(RLB_E_ARG, "null out pointer");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return fail(RLB_E_CUDA, "no CUDA device available (%s); ransaclib_b200 has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= count) return fail(RLB_E_ARG, "device %d out of range [0,%d)", device, count);
+  RLB_CUDA(cudaSetDevice(device));
+  rlb_ctx* c = new (std::nothrow) rlb_ctx();
+  if (!c) return fail(RLB_E_NOMEM, "out of host memory");
+  c->device = device;
+  cudaDeviceProp prop;
+  RLB_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sms = prop.multiProcessorCount;
+  RLB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  RLB_CUDA(cudaMallocHost(&c->h_small, 4096));
+  for (int i = 0; i < 4; ++i) RLB_CUDA(cudaEventCreate(&c->ev[i]));
+  *out = c;
+  return RLB_OK;
+}
+
+int rlb_ctx_destroy(rlb_ctx* c) {
+  if (!c) return RLB_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  DevBuf* bufs[] = {&c->models, &c->valid, &c->samples, &c->scores, &c->counts, &c->part_score,
+                    &c->part_count, &c->block_best, &c->small, &c->one_model, &c->idx,
+                    &c->tile_score, &c->status, &c->header};
+  for (DevBuf* b : bufs) b->release();
+  if (c->h_small) cudaFreeHost(c->h_small);
+  for (int i = 0; i < 4; ++i)
+    if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+  return RLB_OK;
+}
+
+int rlb_ctx_set_stream(rlb_ctx* c, void* stream) {
+  if (!c) return fail(RLB_E_ARG, "null ctx");
+  c->stream = stream ? static_cast<cudaStream_t>(stream) : c->own_stream;
+  return RLB_OK;
+}
+
+int rlb_ctx_synchronize(rlb_ctx* c) {
+  if (!c) return fail(RLB_E_ARG, "null ctx");
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  return RLB_OK;
+}
+
+int64_t rlb_ctx_launch_count(const rlb_ctx* c) { return c ? c->launches : 0; }
+int rlb_ctx_sm_count(const rlb_ctx* c) { return c ? c->sms : 0; }
+
+int rlb_scorer_create_line(rlb_ctx* c, int n, const double* xy, rlb_scorer** out) {
+  if (!c || !out || n < 0 || (n > 0 && !xy)) return fail(RLB_E_ARG, "bad arguments");
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  rlb_scorer* s = new (std::nothrow) rlb_scorer();
+  if (!s) return fail(RLB_E_NOMEM, "out of host memory");
+  s->ctx = c;
+  DeviceData& d = s->d;
+  memset(&d, 0, sizeof(d));
+  d.kind = RLB_KIND_LINE;
+  d.num_types = 1;
+  d.n[0] = n;
+  d.off[0] = 0;
+  d.off[1] = d.npad = std::max(pad_to(n, rlb::kSegAlign), rlb::kSegAlign);
+  d.channels = 2;
+  subsampled_mean(xy, n, 2, 2, d.centre);
+  rc = upload(&s->raw0, xy, static_cast<size_t>(n) * 2, c->stream);
+  if (!rc) {
+    d.raw0 = static_cast<const double*>(s->raw0);
+    rc = finish_scorer(s);
+  }
+  if (rc) {
+    rlb_scorer_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return RLB_OK;
+}
+
+int rlb_scorer_create_hybrid_line(rlb_ctx* c, int n0, const double* xy0, int n1,
+                                  const double* xynn1, rlb_scorer** out) {
+  if (!c || !out || n0 < 0 || n1 < 0 || (n0 > 0 && !xy0) || (n1 > 0 && !xynn1))
+    return fail(RLB_E_ARG, "bad arguments");
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  rlb_scorer* s = new (std::nothrow) rlb_scorer();
+  if (!s) return fail(RLB_E_NOMEM, "out of host memory");
+  s->ctx = c;
+  DeviceData& d = s->d;
+  memset(&d, 0, sizeof(d));
+  d.kind = RLB_KIND_HYBRID_LINE;
+  d.num_types = 2;
+  d.n[0] = n0;
+  d.n[1] = n1;
+  d.off[0] = 0;
+  d.off[1] = pad_to(n0, rlb::kSegAlign);
+  d.npad = std::max(d.off[1] + pad_to(n1, rlb::kSegAlign), rlb::kSegAlign);
+  d.channels = 2;
+  if (n0 > 0)
+    subsampled_mean(xy0, n0, 2, 2, d.centre);
+  else
+    subsampled_mean(xynn1, n1, 4, 2, d.centre);
+  rc = upload(&s->raw0, xy0, static_cast<size_t>(n0) * 2, c->stream);
+  if (!rc) rc = upload(&s->raw1, xynn1, static_cast<size_t>(n1) * 4, c->stream);
+  if (!rc) {
+    d.raw0 = static_cast<const double*>(s->raw0);
+    d.raw1 = static_cast<const double*>(s->raw1);
+    rc = finish_scorer(s);
+  }
+  if (rc) {
+    rlb_scorer_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return RLB_OK;
+}
+
+int rlb_scorer_create_pose(rlb_ctx* c, int n, const double* p2d, const double* p3d, double fx,
+                           double fy, rlb_scorer** out) {
+  if (!c || !out || n < 0 || (n > 0 && (!p2d || !p3d))) return fail(RLB_E_ARG, "bad arguments");
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  rlb_scorer* s = new (std::nothrow) rlb_scorer();
+  if (!s) return fail(RLB_E_NOMEM, "out of host memory");
+  s->ctx = c;
+  DeviceData& d = s->d;
+  memset(&d, 0, sizeof(d));
+  d.kind = RLB_KIND_POSE;
+  d.num_types = 1;
+  d.n[0] = n;
+  d.off[0] = 0;
+  d.off[1] = d.npad = std::max(pad_to(n, rlb::kSegAlign), rlb::kSegAlign);
+  d.channels = 5;
+  d.fx = fx;
+  d.fy = fy;
+  subsampled_mean(p3d, n, 3, 3, d.centre);
+  rc = upload(&s->raw0, p2d, static_cast<size_t>(n) * 2, c->stream);
+  if (!rc) rc = upload(&s->raw1, p3d, static_cast<size_t>(n) * 3, c->stream);
+  if (!rc) {
+    d.raw0 = static_cast<const double*>(s->raw0);
+    d.raw1 = static_cast<const double*>(s->raw1);
+    rc = finish_scorer(s);
+  }
+  if (rc) {
+    rlb_scorer_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return RLB_OK;
+}
+
+int rlb_scorer_destroy(rlb_scorer* s) {
+  if (!s) return RLB_OK;
+  if (s->ctx) {
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+  }
+  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  delete s;
+  return RLB_OK;
+}
+
+int rlb_scorer_kind(const rlb_scorer* s) { return s ? s->d.kind : RLB_E_ARG; }
+int rlb_scorer_num_types(const rlb_scorer* s) { return s ? s->d.num_types : RLB_E_ARG; }
+int rlb_scorer_num_data(const rlb_scorer* s, int type) {
+  if (!s || type < 0 || type >= s->d.num_types) return RLB_E_ARG;
+  return s->d.n[type];
+}
+int rlb_scorer_model_size(const rlb_scorer* s) { return s ? rlb::model_size_of(s->d.kind) : RLB_E_ARG; }
+
+int rlb_scorer_get_rays(const rlb_scorer* s, double* rays) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  if (s->d.kind != RLB_KIND_POSE) return fail(RLB_E_KIND, "rays exist for pose scorers only");
+  if (!rays) return fail(RLB_E_ARG, "null rays");
+  RLB_CUDA(cudaSetDevice(s->ctx->device));
+  RLB_CUDA(cudaMemcpyAsync(rays, s->rays, static_cast<size_t>(s->d.n[0]) * 3 * sizeof(double),
+                           cudaMemcpyDeviceToHost, s->ctx->stream));
+  RLB_CUDA(cudaStreamSynchronize(s->ctx->stream));
+  return RLB_OK;
+}
+
+int rlb_score_models_dev(rlb_scorer* s, int precision, int k, const double* d_models,
+                         const uint8_t* d_valid, const double* sq_thr, const double* weights,
+                         double* d_scores, int32_t* d_counts, void* d_best) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rc = ctx_use(s->ctx);
+  if (rc) return rc;
+  if (!d_models || !d_best) return fail(RLB_E_ARG, "d_models and d_best are required");
+  rc = ensure_first_use(s->ctx);
+  if (rc) return rc;
+  return score_dev(s, precision, k, d_models, d_valid, sq_thr, weights, d_scores, d_counts,
+                   static_cast<BestRec*>(d_best), nullptr);
+}
+
+int rlb_score_models(rlb_scorer* s, int precision, int k, const double* models,
+                     const uint8_t* valid, const double* sq_thr, const double* weights,
+                     double* scores, int32_t* counts, int32_t* best_id, double* best_score) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
+  if (!models) return fail(RLB_E_ARG, "null models");
+  rc = ensure_first_use(c);
+  if (rc) return rc;
+  const int md = rlb::model_size_of(s->d.kind);
+  RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
+  RLB_CUDA(c->scores.ensure(static_cast<size_t>(k) * sizeof(double)));
+  RLB_CUDA(c->counts.ensure(static_cast<size_t>(k) * sizeof(int32_t)));
+  RLB_CUDA(cudaMemcpyAsync(c->models.p, models, static_cast<size_t>(k) * md * sizeof(double),
+                           cudaMemcpyHostToDevice, c->stream));
+  const uint8_t* d_valid = nullptr;
+  if (valid) {
+    RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));
+    RLB_CUDA(cudaMemcpyAsync(c->valid.p, valid, static_cast<size_t>(k), cudaMemcpyHostToDevice, c->stream));
+    d_valid = c->valid.as<uint8_t>();
+  }
+  BestRec* d_best = reinterpret_cast<BestRec*>(c->small.as<char>() + kSmallBest);
+  rc = score_dev(s, precision, k, c->models.as<double>(), d_valid, sq_thr, weights,
+                 c->scores.as<double>(), c->counts.as<int32_t>(), d_best, nullptr);
+  if (rc) return rc;
+  if (scores)
+    RLB_CUDA(cudaMemcpyAsync(scores, c->scores.p, static_cast<size_t>(k) * sizeof(double),
+                             cudaMemcpyDeviceToHost, c->stream));
+  if (counts)
+    RLB_CUDA(cudaMemcpyAsync(counts, c->counts.p, static_cast<size_t>(k) * sizeof(int32_t),
+                             cudaMemcpyDeviceToHost, c->stream));
+  BestRec* h_best = static_cast<BestRec*>(c->h_small);
+  RLB_CUDA(cudaMemcpyAsync(h_best, d_best, sizeof(BestRec), cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  if (best_id) *best_id = static_cast<int32_t>(h_best->id);
+  if (best_score) *best_score = h_best->score;
+  return RLB_OK;
+}
+
+int rlb_get_inliers_dev(rlb_scorer* s, const double* d_model, const double* sq_thr_inl,
+                        const double* sq_thr_score, const double* weights, int32_t* d_idx,
+                        void* d_header) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rc = ctx_use(s->ctx);
+  if (rc) return rc;
+  if (!d_model || !d_header) return fail(RLB_E_ARG, "d_model and d_header are required");
+  return inliers_dev(s, d_model, sq_thr_inl, sq_thr_score, weights, d_idx, d_header);
+}
+
+int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl,
+                    const double* sq_thr_score, const double* weights, int32_t* idx,
+                    int32_t* counts, double* score) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (!model) return fail(RLB_E_ARG, "null model");
+  const DeviceData& d = s->d;
+  const int md = rlb::model_size_of(d.kind);
+  const int ntot = d.n[0] + (d.num_types > 1 ? d.n[1] : 0);
+  RLB_CUDA(c->one_model.ensure(12 * sizeof(double)));
+  RLB_CUDA(c->header.ensure(sizeof(InlierHeader)));
+  if (idx) RLB_CUDA(c->idx.ensure(static_cast<size_t>(std::max(ntot, 1)) * sizeof(int32_t)));
+  RLB_CUDA(cudaMemcpyAsync(c->one_model.p, model, md * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  rc = inliers_dev(s, c->one_model.as<double>(), sq_thr_inl, sq_thr_score, weights,
+                   idx ? c->idx.as<int32_t>() : nullptr, c->header.p);
+  if (rc) return rc;
+  InlierHeader* h = reinterpret_cast<InlierHeader*>(static_cast<char*>(c->h_small) + 64);
+  RLB_CUDA(cudaMemcpyAsync(h, c->header.p, sizeof(InlierHeader), cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  const int total = h->count[1];
+  if (idx && total > 0) {
+    RLB_CUDA(cudaMemcpyAsync(idx, c->idx.p, static_cast<size_t>(total) * sizeof(int32_t),
+                             cudaMemcpyDeviceToHost, c->stream));
+    RLB_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  if (counts) {
+    counts[0] = h->count[0];
+    if (d.num_types > 1) counts[1] = total - h->count[0];
+  }
+  if (score) *score = h->score;
+  return RLB_OK;
+}
+
+int rlb_eval_errors(rlb_scorer* s, int precision, const double* model, int type, double* err) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  const DeviceData& d = s->d;
+  if (!model || !err) return fail(RLB_E_ARG, "null pointer");
+  if (type < 0 || type >= d.num_types) return fail(RLB_E_ARG, "bad data type %d", type);
+  const int md = rlb::model_size_of(d.kind);
+  const int n = d.n[type];
+  if (n == 0) return RLB_OK;
+  RLB_CUDA(c->one_model.ensure(12 * sizeof(double)));
+  RLB_CUDA(c->scores.ensure(static_cast<size_t>(n) * sizeof(double)));
+  RLB_CUDA(cudaMemcpyAsync(c->one_model.p, model, md * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  RLB_CUDA(rlb::launch_eval_errors(d, precision, c->one_model.as<double>(), type,
+                                   c->scores.as<double>(), c->stream, &c->launches_i));
+  account(c);
+  RLB_CUDA(cudaMemcpyAsync(err, c->scores.p, static_cast<size_t>(n) * sizeof(double),
+                           cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  return RLB_OK;
+}
+
+static int solve_host(rlb_scorer* s, int solver, int k, const int32_t* samples, double sq_thr,
+                      double* models, uint8_t* valid) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
+  if (!samples || !models || !valid) return fail(RLB_E_ARG, "null pointer");
+  rc = check_samples(s->d, solver, k, samples);
+  if (rc) return rc;
+  const int ss = solver_sample_size(s->d, solver);
+  const int md = rlb::model_size_of(s->d.kind);
+  RLB_CUDA(c->samples.ensure(static_cast<size_t>(k) * ss * sizeof(int32_t)));
+  RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
+  RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));
+  RLB_CUDA(cudaMemcpyAsync(c->samples.p, samples, static_cast<size_t>(k) * ss * sizeof(int32_t),
+                           cudaMemcpyHostToDevice, c->stream));
+  rc = solve_dev(s, solver, k, c->samples.as<int32_t>(), sq_thr, c->models.as<double>(),
+                 c->valid.as<uint8_t>());
+  if (rc) return rc;
+  RLB_CUDA(cudaMemcpyAsync(models, c->models.p, static_cast<size_t>(k) * md * sizeof(double),
+                           cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaMemcpyAsync(valid, c->valid.p, static_cast<size_t>(k), cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  return RLB_OK;
+}
+
+int rlb_solve_line2pt_batch(rlb_scorer* s, int k, const int32_t* samples, double* models,
+                            uint8_t* valid) {
+  if (s && s->d.kind == RLB_KIND_POSE) return fail(RLB_E_KIND, "2-point line solver on a pose scorer");
+  return solve_host(s, 0, k, samples, 0.0, models, valid);
+}
+int rlb_solve_point_normal_batch(rlb_scorer* s, int k, const int32_t* samples, double* models,
+                                 uint8_t* valid) {
+  if (s && s->d.kind != RLB_KIND_HYBRID_LINE)
+    return fail(RLB_E_KIND, "point+normal solver needs a hybrid line scorer");
+  return solve_host(s, 1, k, samples, 0.0, models, valid);
+}
+int rlb_solve_p3p_batch(rlb_scorer* s, int k, const int32_t* samples, double sq_thr,
+                        double* models, uint8_t* valid) {
+  if (s && s->d.kind != RLB_KIND_POSE) return fail(RLB_E_KIND, "P3P needs a pose scorer");
+  return solve_host(s, 0, k, samples, sq_thr, models, valid);
+}
+
+int rlb_hypothesize_and_score_dev(rlb_scorer* s, int precision, int solver, int k,
+                                  const int32_t* d_samples, const double* sq_thr,
+                                  const double* weights, double* d_models, uint8_t* d_valid,
+                                  double* d_scores, int32_t* d_counts, void* d_best) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rc = ctx_use(s->ctx);
+  if (rc) return rc;
+  if (!d_samples || !d_models || !d_valid || !d_best || !sq_thr)
+    return fail(RLB_E_ARG, "d_samples, d_models, d_valid, d_best, sq_thr are required");
+  rc = ensure_first_use(s->ctx);
+  if (rc) return rc;
+  rc = solve_dev(s, solver, k, d_samples, sq_thr[0], d_models, d_valid);
+  if (rc) return rc;
+  return score_dev(s, precision, k, d_models, d_valid, sq_thr, weights, d_scores, d_counts,
+                   static_cast<BestRec*>(d_best), nullptr);
+}
+
+int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
+                              const int32_t* samples, const double* sq_thr, const double* weights,
+                              double* models, uint8_t* valid, double* scores, int32_t* counts,
+                              int32_t* best_id, double* best_score, double* best_model) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
+  if (!samples || !sq_thr) return fail(RLB_E_ARG, "samples and sq_thr are required");
+  rc = check_samples(s->d, solver, k, samples);
+  if (rc) return rc;
+  rc = ensure_first_use(c);
+  if (rc) return rc;
+  const int ss = solver_sample_size(s->d, solver);
+  const int md = rlb::model_size_of(s->d.kind);
+  RLB_CUDA(c->samples.ensure(static_cast<size_t>(k) * ss * sizeof(int32_t)));
+  RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
+  RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));
+  RLB_CUDA(c->scores.ensure(static_cast<size_t>(k) * sizeof(double)));
+  RLB_CUDA(c->counts.ensure(static_cast<size_t>(k) * sizeof(int32_t)));
+  RLB_CUDA(cudaMemcpyAsync(c->samples.p, samples, static_cast<size_t>(k) * ss * sizeof(int32_t),
+                           cudaMemcpyHostToDevice, c->stream));
+  rc = solve_dev(s, solver, k, c->samples.as<int32_t>(), sq_thr[0], c->models.as<double>(),
+                 c->valid.as<uint8_t>());
+  if (rc) return rc;
+  BestRec* d_best = reinterpret_cast<BestRec*>(c->small.as<char>() + kSmallBest);
+  double* d_best_model = reinterpret_cast<double*>(c->small.as<char>() + kSmallBestModel);
+  rc = score_dev(s, precision, k, c->models.as<double>(), c->valid.as<uint8_t>(), sq_thr, weights,
+                 c->scores.as<double>(), c->counts.as<int32_t>(), d_best, d_best_model);
+  if (rc) return rc;
+  if (models)
+    RLB_CUDA(cudaMemcpyAsync(models, c->models.p, static_cast<size_t>(k) * md * sizeof(double),
+                             cudaMemcpyDeviceToHost, c->stream));
+  if (valid)
+    RLB_CUDA(cudaMemcpyAsync(valid, c->valid.p, static_cast<size_t>(k), cudaMemcpyDeviceToHost, c->stream));
+  if (scores)
+    RLB_CUDA(cudaMemcpyAsync(scores, c->scores.p, static_cast<size_t>(k) * sizeof(double),
+                             cudaMemcpyDeviceToHost, c->stream));
+  if (counts)
+    RLB_CUDA(cudaMemcpyAsync(counts, c->counts.p, static_cast<size_t>(k) * sizeof(int32_t),
+                             cudaMemcpyDeviceToHost, c->stream));
+  char* hs = static_cast<char*>(c->h_small);
+  RLB_CUDA(cudaMemcpyAsync(hs, c->small.as<char>() + kSmallBest, sizeof(BestRec), cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaMemcpyAsync(hs + 128, d_best_model, 12 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  const BestRec* hb = reinterpret_cast<const BestRec*>(hs);
+  if (best_id) *best_id = static_cast<int32_t>(hb->id);
+  if (best_score) *best_score = hb->score;
+  if (best_model && hb->id >= 0) memcpy(best_model, hs + 128, md * sizeof(double));
+  return RLB_OK;
+}
+
+int rlb_ctx_set_timing(rlb_ctx* c, int enabled) {
+  if (!c) return fail(RLB_E_ARG, "null ctx");
+  c->timing = enabled != 0;
+  c->ev_valid[0] = c->ev_valid[1] = false;
+  return RLB_OK;
+}
+
+int rlb_ctx_kernel_time_ms(rlb_ctx* c, int which, double* ms) {
+  if (!c || !ms || which < 0 || which > 1) return fail(RLB_E_ARG, "bad arguments");
+  if (!c->ev_valid[which]) return fail(RLB_E_ARG, "no timed kernel of kind %d yet (enable timing first)", which);
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  RLB_CUDA(cudaEventSynchronize(c->ev[2 * which + 1]));
+  float t = 0.f;
+  RLB_CUDA(cudaEventElapsedTime(&t, c->ev[2 * which], c->ev[2 * which + 1]));
+  *ms = t;
+  return RLB_OK;
+}
+
+int rlb_measure_fma_peak(rlb_ctx* c, int dtype, double* tflops) {
+  if (!c || !tflops || dtype < 0 || dtype > 2) return fail(RLB_E_ARG, "bad arguments");
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  float ms = 0;
+  double flops = 0;
+  RLB_CUDA(rlb::launch_fma_peak(dtype, c->sms, &ms, &flops, c->stream));
+  *tflops = flops / (static_cast<double>(ms) * 1e-3) / 1e12;
+  return RLB_OK;
+}
+
+}  // extern "C"

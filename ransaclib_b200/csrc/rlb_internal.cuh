@@ -1,0 +1,106 @@
+// Internal declarations shared by the kernel translation units and the C ABI.
+#ifndef RLB_INTERNAL_CUH_
+#define RLB_INTERNAL_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ransaclib_b200.h"
+
+namespace rlb {
+
+// Points of every data type are stored channel-major (SoA) and zero-padded so that
+// each type segment starts at a multiple of kSegAlign points. Stages of the K x N
+// sweep (kStage points) and tiles of the inlier pass (kInlTile points) therefore
+// never straddle two data types.
+constexpr int kSegAlign = 1024;
+constexpr int kStage = 512;      // points per shared-memory stage of the sweep
+constexpr int kNumStages = 3;    // TMA ring depth
+constexpr int kSweepThreads = 128;
+constexpr int kInlTile = 1024;   // points per CTA of the inlier pass
+constexpr int kInlThreads = 256;
+constexpr int kMaxTypes = 2;
+
+struct DeviceData {
+  int kind;                 // RLB_KIND_*
+  int num_types;            // 1 or 2
+  int n[kMaxTypes];         // points per type
+  int off[kMaxTypes];       // padded start of each type segment (multiple of kSegAlign)
+  int npad;                 // total padded points
+  int channels;             // 2 (line kinds) or 5 (pose: X,Y,Z,u,v)
+  const double* soa64;      // [channels][npad]
+  const float* soa32;       // [channels][npad]   (pose: recentred)
+  double fx, fy;            // pose intrinsics
+  double centre[3];         // f64 point subtracted from the coordinates before the SoA repack
+  // raw reference-layout copies for the minimal solvers (f64)
+  const double* raw0;       // line: xy (n0 x 2); pose: points2D (n x 2)
+  const double* raw1;       // hybrid: xynn (n1 x 4); pose: points3D (n x 3)
+  const double* rays;       // pose: n x 3 unit bearings
+};
+
+struct SweepArgs {
+  int k;                       // hypotheses
+  const double* models;        // K x model_size (device)
+  const uint8_t* valid;        // K or nullptr
+  double thr[kMaxTypes];
+  double w[kMaxTypes];
+  int n_splits;                // CTAs along the point axis
+  int stages_per_split;        // stages each split covers
+  double* part_score;          // [n_splits][k]
+  int32_t* part_count;         // [n_splits][k]
+};
+
+struct BestRec {
+  double score;
+  long long id;
+};
+
+struct InlierArgs {
+  const double* model;     // device, model_size doubles
+  double thr_inl[kMaxTypes];
+  double thr_score[kMaxTypes];
+  double w[kMaxTypes];
+  int want_score;
+  int32_t* idx;            // device out or nullptr
+  double* tile_score;      // [tiles] scratch
+  unsigned long long* status;  // [tiles] look-back words (epoch-tagged)
+  unsigned int* control;   // [0]=ticket, [1]=done
+  unsigned int epoch;
+  void* header;            // {double score; int32 count[2]; int32 pad}
+};
+
+struct InlierHeader {
+  double score;
+  int32_t count[2];
+  int32_t pad[2];
+};
+
+// launchers (score_kernels.cu)
+cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision, cudaStream_t st,
+                         int* launches);
+cudaError_t launch_finalize(const DeviceData& d, const SweepArgs& a, double* scores,
+                            int32_t* counts, BestRec* block_best, unsigned int* ticket,
+                            BestRec* best, double* best_model, cudaStream_t st, int* launches);
+cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_t st,
+                           int* launches);
+cudaError_t launch_eval_errors(const DeviceData& d, int precision, const double* model, int type,
+                               double* err, cudaStream_t st, int* launches);
+cudaError_t launch_repack(const DeviceData& d, double* soa64, float* soa32, cudaStream_t st,
+                          int* launches);
+cudaError_t launch_fma_peak(int dtype, int sms, float* ms, double* flops, cudaStream_t st);
+
+// launchers (solver_kernels.cu, compiled with -fmad=false)
+cudaError_t launch_rays(const DeviceData& d, double* rays, cudaStream_t st, int* launches);
+cudaError_t launch_solve_line2pt(const DeviceData& d, int k, const int32_t* samples, double* models,
+                                 uint8_t* valid, cudaStream_t st, int* launches);
+cudaError_t launch_solve_point_normal(const DeviceData& d, int k, const int32_t* samples,
+                                      double* models, uint8_t* valid, cudaStream_t st,
+                                      int* launches);
+cudaError_t launch_solve_p3p(const DeviceData& d, int k, const int32_t* samples, double sq_thr,
+                             double* models, uint8_t* valid, cudaStream_t st, int* launches);
+
+inline int model_size_of(int kind) { return kind == RLB_KIND_POSE ? 12 : 3; }
+
+}  // namespace rlb
+
+#endif  // RLB_INTERNAL_CUH_

@@ -1,0 +1,859 @@
+// K-hypothesis x N-point MSAC sweep, score finalisation / argmin, and the ordered
+// inlier pass. Hand-written for sm_100a.
+//
+// Replaces (reference, /root/reference): RansacLib/ransac.h:278-336 (ScoreModel,
+// ComputeScore, GetInliers, GetBestEstimatedModelId), hybrid_ransac.h:386-462, and
+// the EvaluateModelOnPoint bodies of examples/calibrated_absolute_pose_estimator.cc:154-167,
+// line_estimator.cc:110-114, hybrid_line_estimator.cc:100-109.
+//
+// Sweep layout: one thread owns H hypotheses in registers for the whole pass;
+// a CTA streams its slice of the points through a kNumStages-deep shared-memory
+// ring filled by 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx);
+// every lane reads the SAME point (LDS broadcast, vectorised float4/double2), so
+// the inner loop is pure register FMA work. Per-stage f32 partial sums are
+// flushed into f64 accumulators ("f32 inner, f64 outer"). No floating-point
+// atomics anywhere: partial sums go to [split][k] and are combined in a fixed
+// order, so results are bit-reproducible run to run.
+#include <cfloat>
+#include <climits>
+
+#include "rlb_internal.cuh"
+
+namespace rlb {
+
+// ------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(dst_smem)),
+      "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  const uint32_t a = smem_u32(bar);
+  while (!done) {
+    asm volatile(
+        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, "
+        "p; }"
+        : "=r"(done)
+        : "r"(a), "r"(parity)
+        : "memory");
+  }
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// ---------------------------------------------------------------------- functors
+// Each functor: C channels per point, MD doubles per model, a register-resident
+// Model, load() from the reference's host model layout, eval() = squared residual.
+
+template <typename T>
+struct LineF {
+  static constexpr int C = 2;
+  static constexpr int MD = 3;
+  struct Model {
+    T a, b, c;
+  };
+  // Points are stored relative to d.centre: a x + b y + c = a x' + b y' + (c + a cx + b cy),
+  // the shifted offset being formed in f64.
+  __device__ static void load(const double* m, const DeviceData& d, Model& o) {
+    o.a = static_cast<T>(m[0]);
+    o.b = static_cast<T>(m[1]);
+    o.c = static_cast<T>(m[2] + m[0] * d.centre[0] + m[1] * d.centre[1]);
+  }
+  __device__ static void zero(Model& o) { o.a = o.b = o.c = T(0); }
+  // line_estimator.cc:110-114 / hybrid_line_estimator.cc:100-109
+  __device__ __forceinline__ static T eval(const Model& m, const T* p) {
+    const T r = fma(m.a, p[0], fma(m.b, p[1], m.c));
+    return r * r;
+  }
+};
+
+template <typename T>
+struct PoseF {
+  static constexpr int C = 5;
+  static constexpr int MD = 12;
+  struct Model {
+    T r[9];  // row-major; rows 0/1 pre-scaled by fx/fy
+    T t[3];  // R (centre - c), rows 0/1 pre-scaled
+  };
+  // m: column-major 3x4 [R | c] (calibrated_absolute_pose_estimator.h:55,68-70).
+  // p = R (X - c) = R (X - centre) + R (centre - c); the second term is formed in f64.
+  __device__ static void load(const double* m, const DeviceData& d, Model& o) {
+    const double dc[3] = {d.centre[0] - m[9], d.centre[1] - m[10], d.centre[2] - m[11]};
+    const double sc[3] = {d.fx, d.fy, 1.0};
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const double r0 = m[r], r1 = m[r + 3], r2 = m[r + 6];
+      const double t = r0 * dc[0] + r1 * dc[1] + r2 * dc[2];
+      o.r[3 * r + 0] = static_cast<T>(r0 * sc[r]);
+      o.r[3 * r + 1] = static_cast<T>(r1 * sc[r]);
+      o.r[3 * r + 2] = static_cast<T>(r2 * sc[r]);
+      o.t[r] = static_cast<T>(t * sc[r]);
+    }
+  }
+  __device__ static void zero(Model& o) {
+#pragma unroll
+    for (int i = 0; i < 9; ++i) o.r[i] = T(0);
+    o.t[0] = o.t[1] = T(0);
+    o.t[2] = T(1);
+  }
+  __device__ __forceinline__ static T eval(const Model& m, const T* p);
+};
+
+// calibrated_absolute_pose_estimator.cc:154-167, f64: behind-camera -> DBL_MAX,
+// z == 0 falls through to inf/NaN like the reference.
+template <>
+__device__ __forceinline__ double PoseF<double>::eval(const Model& m, const double* p) {
+  const double pz = fma(m.r[6], p[0], fma(m.r[7], p[1], fma(m.r[8], p[2], m.t[2])));
+  const double px = fma(m.r[0], p[0], fma(m.r[1], p[1], fma(m.r[2], p[2], m.t[0])));
+  const double py = fma(m.r[3], p[0], fma(m.r[4], p[1], fma(m.r[5], p[2], m.t[1])));
+  const double inv = 1.0 / pz;
+  const double du = fma(px, inv, -p[3]);
+  const double dv = fma(py, inv, -p[4]);
+  const double e = fma(du, du, dv * dv);
+  return (pz < 0.0) ? DBL_MAX : e;
+}
+// f32: 13 FMA-pipe ops + MUFU.RCP + FMNMX. pz < 0 -> rcp(0) = +inf -> e = inf/NaN,
+// which fails the (e < thr) test exactly like the reference's DBL_MAX sentinel.
+template <>
+__device__ __forceinline__ float PoseF<float>::eval(const Model& m, const float* p) {
+  const float pz = fmaf(m.r[6], p[0], fmaf(m.r[7], p[1], fmaf(m.r[8], p[2], m.t[2])));
+  const float px = fmaf(m.r[0], p[0], fmaf(m.r[1], p[1], fmaf(m.r[2], p[2], m.t[0])));
+  const float py = fmaf(m.r[3], p[0], fmaf(m.r[4], p[1], fmaf(m.r[5], p[2], m.t[1])));
+  const float inv = rcp_approx(fmaxf(pz, 0.0f));
+  const float du = fmaf(px, inv, -p[3]);
+  const float dv = fmaf(py, inv, -p[4]);
+  return fmaf(du, du, dv * dv);
+}
+
+// MSAC accumulation. f64 keeps the reference's exact semantics
+// (ransac.h:306-309: std::min(e,thr) == (thr < e) ? thr : e, NaN-propagating; strict
+// e < thr for inliers). f32 accumulates only inlier errors and the inlier count;
+// the outlier mass thr * (#points - #inliers) is added in f64 at the stage flush.
+template <typename T>
+struct Acc;
+template <>
+struct Acc<double> {
+  double s;
+  int c;
+  __device__ __forceinline__ void reset() {
+    s = 0.0;
+    c = 0;
+  }
+  __device__ __forceinline__ void add(double e, double thr) {
+    s += (thr < e) ? thr : e;
+    c += (e < thr) ? 1 : 0;
+  }
+  __device__ __forceinline__ double flush(double, int) const { return s; }
+};
+template <>
+struct Acc<float> {
+  float s;
+  int c;
+  __device__ __forceinline__ void reset() {
+    s = 0.0f;
+    c = 0;
+  }
+  __device__ __forceinline__ void add(float e, float thr) {
+    if (e < thr) {
+      s += e;
+      c += 1;
+    }
+  }
+  __device__ __forceinline__ double flush(double thr, int npts) const {
+    return static_cast<double>(s) + thr * static_cast<double>(npts - c);
+  }
+};
+
+template <typename T>
+struct VecOf;
+template <>
+struct VecOf<float> {
+  typedef float4 type;
+  static constexpr int V = 4;
+};
+template <>
+struct VecOf<double> {
+  typedef double2 type;
+  static constexpr int V = 2;
+};
+__device__ __forceinline__ void unpack(const float4& v, float* o) {
+  o[0] = v.x;
+  o[1] = v.y;
+  o[2] = v.z;
+  o[3] = v.w;
+}
+__device__ __forceinline__ void unpack(const double2& v, double* o) {
+  o[0] = v.x;
+  o[1] = v.y;
+}
+
+template <typename T>
+__device__ __forceinline__ const T* soa_of(const DeviceData& d);
+template <>
+__device__ __forceinline__ const float* soa_of<float>(const DeviceData& d) {
+  return d.soa32;
+}
+template <>
+__device__ __forceinline__ const double* soa_of<double>(const DeviceData& d) {
+  return d.soa64;
+}
+
+// ------------------------------------------------------------------ sweep kernel
+template <template <typename> class FT, typename T, int H>
+__global__ void __launch_bounds__(kSweepThreads)
+    sweep_kernel(const DeviceData d, const SweepArgs a) {
+  typedef FT<T> F;
+  typedef typename VecOf<T>::type Vec;
+  constexpr int V = VecOf<T>::V;
+  constexpr int C = F::C;
+  constexpr uint32_t kChanBytes = kStage * sizeof(T);
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  T* ring = reinterpret_cast<T*>(smem_raw);  // [kNumStages][C][kStage]
+  __shared__ __align__(8) uint64_t full[kNumStages];
+
+  const int tid = threadIdx.x;
+  const int kbase = blockIdx.x * (kSweepThreads * H);
+  const int split = blockIdx.y;
+  const T* soa = soa_of<T>(d);
+
+  const int total_stages = d.npad / kStage;
+  const int s_begin = split * a.stages_per_split;
+  const int s_end = min(total_stages, s_begin + a.stages_per_split);
+  const int nst = max(0, s_end - s_begin);
+
+  typename F::Model m[H];
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    const int k = kbase + h * kSweepThreads + tid;
+    if (k < a.k) {
+      F::load(a.models + static_cast<size_t>(k) * F::MD, d, m[h]);
+    } else {
+      F::zero(m[h]);
+    }
+  }
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kNumStages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](int it) {
+    const int slot = it % kNumStages;
+    const size_t g0 = static_cast<size_t>(s_begin + it) * kStage;
+    T* dst = ring + static_cast<size_t>(slot) * C * kStage;
+    mbar_expect_tx(&full[slot], C * kChanBytes);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      tma_load_1d(dst + c * kStage, soa + static_cast<size_t>(c) * d.npad + g0, kChanBytes,
+                  &full[slot]);
+    }
+  };
+  if (tid == 0) {
+    for (int it = 0; it < kNumStages && it < nst; ++it) issue(it);
+  }
+
+  double dacc[H];
+  int dcnt[H];
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    dacc[h] = 0.0;
+    dcnt[h] = 0;
+  }
+
+  for (int it = 0; it < nst; ++it) {
+    const int slot = it % kNumStages;
+    mbar_wait(&full[slot], (it / kNumStages) & 1);
+
+    const int g0 = (s_begin + it) * kStage;
+    const int t = (d.num_types > 1 && g0 >= d.off[1]) ? 1 : 0;
+    const int cnt = max(0, min(kStage, d.off[t] + d.n[t] - g0));
+    const double thr64 = a.thr[t];
+    const T thr = static_cast<T>(thr64);
+    const T* sb = ring + static_cast<size_t>(slot) * C * kStage;
+
+    Acc<T> acc[H];
+#pragma unroll
+    for (int h = 0; h < H; ++h) acc[h].reset();
+
+    int j = 0;
+#pragma unroll 1
+    for (; j + V <= cnt; j += V) {
+      T ch[C][V];
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        unpack(*reinterpret_cast<const Vec*>(sb + c * kStage + j), ch[c]);
+      }
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        T p[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) p[c] = ch[c][v];
+#pragma unroll
+        for (int h = 0; h < H; ++h) acc[h].add(F::eval(m[h], p), thr);
+      }
+    }
+    for (; j < cnt; ++j) {
+      T p[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) p[c] = sb[c * kStage + j];
+#pragma unroll
+      for (int h = 0; h < H; ++h) acc[h].add(F::eval(m[h], p), thr);
+    }
+
+    const double w = a.w[t];
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      dacc[h] += w * acc[h].flush(thr64, cnt);
+      dcnt[h] += acc[h].c;
+    }
+
+    __syncthreads();  // everyone is done reading this slot
+    if (tid == 0 && it + kNumStages < nst) issue(it + kNumStages);
+  }
+
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    const int k = kbase + h * kSweepThreads + tid;
+    if (k < a.k) {
+      a.part_score[static_cast<size_t>(split) * a.k + k] = dacc[h];
+      a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt[h];
+    }
+  }
+}
+
+template <template <typename> class FT, typename T, int H>
+static cudaError_t launch_sweep_t(const DeviceData& d, const SweepArgs& a, cudaStream_t st) {
+  const size_t smem = static_cast<size_t>(kNumStages) * FT<T>::C * kStage * sizeof(T);
+  auto kern = sweep_kernel<FT, T, H>;
+  static bool configured = false;  // per template instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid((a.k + kSweepThreads * H - 1) / (kSweepThreads * H), a.n_splits);
+  kern<<<grid, kSweepThreads, smem, st>>>(d, a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision, cudaStream_t st,
+                         int* launches) {
+  ++*launches;
+  if (d.kind == RLB_KIND_POSE) {
+    if (precision == RLB_F32) return launch_sweep_t<PoseF, float, 4>(d, a, st);
+    return launch_sweep_t<PoseF, double, 2>(d, a, st);
+  }
+  if (precision == RLB_F32) return launch_sweep_t<LineF, float, 4>(d, a, st);
+  return launch_sweep_t<LineF, double, 4>(d, a, st);
+}
+
+// ------------------------------------------------------------- finalize + argmin
+__device__ __forceinline__ bool better(double s, long long i, double bs, long long bi) {
+  return (s < bs) || (s == bs && i < bi);
+}
+
+__global__ void __launch_bounds__(256)
+    finalize_kernel(const DeviceData d, const SweepArgs a, double* __restrict__ scores,
+                    int32_t* __restrict__ counts, BestRec* __restrict__ block_best,
+                    unsigned int* __restrict__ ticket, BestRec* __restrict__ best,
+                    double* __restrict__ best_model) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int md = (d.kind == RLB_KIND_POSE) ? 12 : 3;
+  double s = DBL_MAX;
+  long long id = LLONG_MAX;
+  if (k < a.k) {
+    double sum = 0.0;
+    int cnt = 0;
+    for (int sp = 0; sp < a.n_splits; ++sp) {  // fixed order: deterministic
+      sum += a.part_score[static_cast<size_t>(sp) * a.k + k];
+      cnt += a.part_count[static_cast<size_t>(sp) * a.k + k];
+    }
+    const bool is_valid = (a.valid == nullptr) || (a.valid[k] != 0);
+    bool finite = true;
+    for (int i = 0; i < md; ++i) {
+      const double v = a.models[static_cast<size_t>(k) * md + i];
+      finite = finite && (v - v == 0.0);
+    }
+    if (!is_valid) {
+      sum = DBL_MAX;  // ransac.h:185-188: never scored, can never win
+      cnt = 0;
+    } else if (!finite) {
+      sum = __longlong_as_double(0x7ff8000000000000LL);  // NaN propagates (ransac.h:308)
+      cnt = 0;
+    }
+    if (scores) scores[k] = sum;
+    if (counts) counts[k] = cnt;
+    if (sum < DBL_MAX) {
+      s = sum;
+      id = k;
+    }
+  }
+  // lexicographic (score, id) min: lowest id wins ties (ransac.h:195,288).
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double os = __shfl_down_sync(0xffffffffu, s, o);
+    const long long oi = __shfl_down_sync(0xffffffffu, id, o);
+    if (better(os, oi, s, id)) {
+      s = os;
+      id = oi;
+    }
+  }
+  __shared__ double ws[8];
+  __shared__ long long wi[8];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) {
+    ws[wid] = s;
+    wi[wid] = id;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w)
+      if (better(ws[w], wi[w], s, id)) {
+        s = ws[w];
+        id = wi[w];
+      }
+    block_best[blockIdx.x].score = s;
+    block_best[blockIdx.x].id = id;
+    __threadfence();
+    const unsigned int t = atomicAdd(ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  s = DBL_MAX;
+  id = LLONG_MAX;
+  for (int b = threadIdx.x; b < static_cast<int>(gridDim.x); b += blockDim.x) {
+    const double bs = block_best[b].score;
+    const long long bi = block_best[b].id;
+    if (better(bs, bi, s, id)) {
+      s = bs;
+      id = bi;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double os = __shfl_down_sync(0xffffffffu, s, o);
+    const long long oi = __shfl_down_sync(0xffffffffu, id, o);
+    if (better(os, oi, s, id)) {
+      s = os;
+      id = oi;
+    }
+  }
+  __syncthreads();
+  if (lane == 0) {
+    ws[wid] = s;
+    wi[wid] = id;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w)
+      if (better(ws[w], wi[w], s, id)) {
+        s = ws[w];
+        id = wi[w];
+      }
+    best->score = s;
+    best->id = (id == LLONG_MAX) ? -1 : id;
+    *ticket = 0u;  // self-cleaning for the next launch on this stream
+    if (best_model != nullptr && id != LLONG_MAX) {
+      for (int i = 0; i < md; ++i) best_model[i] = a.models[static_cast<size_t>(id) * md + i];
+    }
+  }
+}
+
+cudaError_t launch_finalize(const DeviceData& d, const SweepArgs& a, double* scores,
+                            int32_t* counts, BestRec* block_best, unsigned int* ticket,
+                            BestRec* best, double* best_model, cudaStream_t st, int* launches) {
+  ++*launches;
+  const int blocks = (a.k + 255) / 256;
+  finalize_kernel<<<blocks, 256, 0, st>>>(d, a, scores, counts, block_best, ticket, best,
+                                          best_model);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------- inlier pass
+// One launch: evaluate, MSAC-score and stream-compact the ascending inlier list
+// (ransac.h:311-336; list order matters because local optimisation shuffles it,
+// ransac.h:380-381,414-418). Tiles take tickets in launch order and resolve their
+// output offset by a decoupled look-back over epoch-tagged status words, so no
+// memset or second pass is needed.
+constexpr unsigned long long kFlagAgg = 1ull;
+constexpr unsigned long long kFlagIncl = 2ull;
+__device__ __forceinline__ unsigned long long pack_status(unsigned int epoch,
+                                                          unsigned long long flag,
+                                                          unsigned int value) {
+  return (static_cast<unsigned long long>(epoch) << 34) | (flag << 32) | value;
+}
+
+template <template <typename> class FT>
+__global__ void __launch_bounds__(kInlThreads) inlier_kernel(const DeviceData d, const InlierArgs a) {
+  typedef FT<double> F;
+  constexpr int C = F::C;
+  constexpr int PPT = kInlTile / kInlThreads;  // 4 consecutive points per thread
+  __shared__ unsigned int s_tile;
+  __shared__ int s_wsum[kInlThreads / 32];
+  __shared__ double s_wscore[kInlThreads / 32];
+  __shared__ int s_tile_excl;
+  __shared__ bool s_last;
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) s_tile = atomicAdd(&a.control[0], 1u);
+  __syncthreads();
+  const int tile = static_cast<int>(s_tile);
+  const int num_tiles = static_cast<int>(gridDim.x);
+  const int g0 = tile * kInlTile;
+  const int t = (d.num_types > 1 && g0 >= d.off[1]) ? 1 : 0;
+  const int seg_n = d.n[t], seg_off = d.off[t];
+  const double thr_in = a.thr_inl[t];
+  const double thr_sc = a.thr_score[t];
+  const double w = a.w[t];
+
+  typename F::Model m;
+  F::load(a.model, d, m);
+
+  const int i0 = g0 + tid * PPT;
+  double ch[C][PPT];
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const double2* src =
+        reinterpret_cast<const double2*>(d.soa64 + static_cast<size_t>(c) * d.npad + i0);
+    const double2 v0 = src[0], v1 = src[1];
+    ch[c][0] = v0.x;
+    ch[c][1] = v0.y;
+    ch[c][2] = v1.x;
+    ch[c][3] = v1.y;
+  }
+  bool in[PPT];
+  int my = 0;
+  double sc = 0.0;
+#pragma unroll
+  for (int j = 0; j < PPT; ++j) {
+    double p[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) p[c] = ch[c][j];
+    const double e = F::eval(m, p);
+    const bool live = (i0 + j - seg_off) < seg_n;
+    in[j] = live && (e < thr_in);
+    my += in[j] ? 1 : 0;
+    if (live) sc += ((thr_sc < e) ? thr_sc : e) * w;  // hybrid_ransac.h:416-418
+  }
+
+  // block-wide exclusive scan of `my`, deterministic tree sum of `sc`
+  int incl = my;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  double wsc = sc;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wsc += __shfl_down_sync(0xffffffffu, wsc, o);
+  if (lane == 31) s_wsum[wid] = incl;
+  if (lane == 0) s_wscore[wid] = wsc;
+  __syncthreads();
+  int warp_excl = 0, tile_total = 0;
+#pragma unroll
+  for (int q = 0; q < kInlThreads / 32; ++q) {
+    if (q < wid) warp_excl += s_wsum[q];
+    tile_total += s_wsum[q];
+  }
+  const int thread_excl = warp_excl + incl - my;
+
+  // publish aggregate, then look back (warp 0)
+  if (wid == 0) {
+    if (lane == 0) {
+      double ts = 0.0;
+#pragma unroll
+      for (int q = 0; q < kInlThreads / 32; ++q) ts += s_wscore[q];
+      a.tile_score[tile] = ts;
+      const unsigned long long word =
+          pack_status(a.epoch, tile == 0 ? kFlagIncl : kFlagAgg, static_cast<unsigned int>(tile_total));
+      atomicExch(&a.status[tile], word);
+    }
+    int excl = 0;
+    if (tile > 0) {
+      int look = tile - 1;
+      bool done = false;
+      while (!done) {
+        const int idx = look - lane;
+        // Lanes that would look before tile 0 act as "inclusive prefix 0".
+        unsigned long long word = pack_status(a.epoch, kFlagIncl, 0u);
+        bool ready;
+        do {
+          ready = true;
+          if (idx >= 0) {
+            word = *reinterpret_cast<volatile unsigned long long*>(&a.status[idx]);
+            ready = (static_cast<unsigned int>(word >> 34) == a.epoch) &&
+                    (((word >> 32) & 3ull) != 0ull);
+          }
+        } while (!__all_sync(0xffffffffu, ready));
+        const unsigned long long flag = (word >> 32) & 3ull;
+        const unsigned int val = static_cast<unsigned int>(word & 0xffffffffull);
+        // first lane (closest predecessor first) holding an inclusive prefix
+        const unsigned int incl_mask = __ballot_sync(0xffffffffu, flag == kFlagIncl);
+        const int first = __ffs(incl_mask) - 1;  // >= 0 eventually (tile 0 or idx<0 lanes)
+        int contrib = (first < 0 || lane <= first) ? static_cast<int>(val) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) contrib += __shfl_down_sync(0xffffffffu, contrib, o);
+        contrib = __shfl_sync(0xffffffffu, contrib, 0);
+        excl += contrib;
+        if (first >= 0) {
+          done = true;
+        } else {
+          look -= 32;
+        }
+      }
+      if (lane == 0) {
+        atomicExch(&a.status[tile],
+                   pack_status(a.epoch, kFlagIncl, static_cast<unsigned int>(excl + tile_total)));
+      }
+    }
+    if (lane == 0) {
+      s_tile_excl = excl;
+      InlierHeader* hdr = reinterpret_cast<InlierHeader*>(a.header);
+      if (d.num_types > 1 && g0 == d.off[1]) hdr->count[0] = excl;  // #type-0 inliers
+      if (tile == num_tiles - 1) {
+        hdr->count[1] = excl + tile_total;  // total over all types
+        if (d.num_types == 1 || d.off[1] >= d.npad) hdr->count[0] = excl + tile_total;
+      }
+    }
+  }
+  __syncthreads();
+
+  if (a.idx != nullptr) {
+    int pos = s_tile_excl + thread_excl;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+      if (in[j]) a.idx[pos++] = i0 + j - seg_off;
+    }
+  }
+
+  // last CTA to finish sums the tile scores in index order and resets the counters
+  if (tid == 0) {
+    __threadfence();
+    const unsigned int fin = atomicAdd(&a.control[1], 1u);
+    s_last = (fin == static_cast<unsigned int>(num_tiles) - 1u);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double part = 0.0;
+  // fixed assignment tile -> thread and fixed tree: deterministic
+  for (int q = tid; q < num_tiles; q += kInlThreads)
+    part += *reinterpret_cast<volatile double*>(&a.tile_score[q]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_down_sync(0xffffffffu, part, o);
+  __syncthreads();
+  if (lane == 0) s_wscore[wid] = part;
+  __syncthreads();
+  if (tid == 0) {
+    double total = 0.0;
+#pragma unroll
+    for (int q = 0; q < kInlThreads / 32; ++q) total += s_wscore[q];
+    InlierHeader* hdr = reinterpret_cast<InlierHeader*>(a.header);
+    hdr->score = total;
+    a.control[0] = 0u;
+    a.control[1] = 0u;
+  }
+}
+
+cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_t st,
+                           int* launches) {
+  ++*launches;
+  const int tiles = d.npad / kInlTile;
+  if (d.kind == RLB_KIND_POSE) {
+    inlier_kernel<PoseF><<<tiles, kInlThreads, 0, st>>>(d, a);
+  } else {
+    inlier_kernel<LineF><<<tiles, kInlThreads, 0, st>>>(d, a);
+  }
+  return cudaGetLastError();
+}
+
+// ----------------------------------------------------------- per-point residuals
+template <template <typename> class FT, typename T>
+__global__ void eval_errors_kernel(const DeviceData d, const double* __restrict__ model, int type,
+                                   double* __restrict__ err) {
+  typedef FT<T> F;
+  typename F::Model m;
+  F::load(model, d, m);
+  const T* soa = soa_of<T>(d);
+  const int n = d.n[type];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    T p[F::C];
+#pragma unroll
+    for (int c = 0; c < F::C; ++c) p[c] = soa[static_cast<size_t>(c) * d.npad + d.off[type] + i];
+    err[i] = static_cast<double>(F::eval(m, p));
+  }
+}
+
+cudaError_t launch_eval_errors(const DeviceData& d, int precision, const double* model, int type,
+                               double* err, cudaStream_t st, int* launches) {
+  ++*launches;
+  const int n = d.n[type];
+  const int blocks = max(1, min(1024, (n + 255) / 256));
+  if (d.kind == RLB_KIND_POSE) {
+    if (precision == RLB_F32)
+      eval_errors_kernel<PoseF, float><<<blocks, 256, 0, st>>>(d, model, type, err);
+    else
+      eval_errors_kernel<PoseF, double><<<blocks, 256, 0, st>>>(d, model, type, err);
+  } else {
+    if (precision == RLB_F32)
+      eval_errors_kernel<LineF, float><<<blocks, 256, 0, st>>>(d, model, type, err);
+    else
+      eval_errors_kernel<LineF, double><<<blocks, 256, 0, st>>>(d, model, type, err);
+  }
+  return cudaGetLastError();
+}
+
+// --------------------------------------------------- AoS (reference) -> SoA repack
+__global__ void repack_kernel(const DeviceData d, double* __restrict__ soa64,
+                              float* __restrict__ soa32) {
+  const int total = d.npad;
+  for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
+    const int t = (d.num_types > 1 && g >= d.off[1]) ? 1 : 0;
+    const int i = g - d.off[t];
+    const bool live = i < d.n[t];
+    double v[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    if (live) {
+      if (d.kind == RLB_KIND_POSE) {
+        v[0] = d.raw1[3 * static_cast<size_t>(i) + 0] - d.centre[0];
+        v[1] = d.raw1[3 * static_cast<size_t>(i) + 1] - d.centre[1];
+        v[2] = d.raw1[3 * static_cast<size_t>(i) + 2] - d.centre[2];
+        v[3] = d.raw0[2 * static_cast<size_t>(i) + 0];
+        v[4] = d.raw0[2 * static_cast<size_t>(i) + 1];
+      } else if (t == 0) {
+        v[0] = d.raw0[2 * static_cast<size_t>(i) + 0] - d.centre[0];
+        v[1] = d.raw0[2 * static_cast<size_t>(i) + 1] - d.centre[1];
+      } else {
+        v[0] = d.raw1[4 * static_cast<size_t>(i) + 0] - d.centre[0];
+        v[1] = d.raw1[4 * static_cast<size_t>(i) + 1] - d.centre[1];
+      }
+    }
+    for (int c = 0; c < d.channels; ++c) {
+      soa64[static_cast<size_t>(c) * total + g] = v[c];
+      soa32[static_cast<size_t>(c) * total + g] = static_cast<float>(v[c]);
+    }
+  }
+}
+
+cudaError_t launch_repack(const DeviceData& d, double* soa64, float* soa32, cudaStream_t st,
+                          int* launches) {
+  ++*launches;
+  const int blocks = max(1, min(2048, (d.npad + 255) / 256));
+  repack_kernel<<<blocks, 256, 0, st>>>(d, soa64, soa32);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------ FMA-pipe peak microbench
+template <int MODE>
+__global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters, float seed) {
+  if (MODE == 0) {
+    double a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = seed + i + threadIdx.x;
+    const double x = 1.000001, y = 1e-9 * seed;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = fma(a[i], x, y);
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += a[i];
+    if (s == 12345.678) out[0] = static_cast<float>(s);
+  } else if (MODE == 1) {
+    float a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = seed + i + threadIdx.x;
+    const float x = 1.000001f, y = 1e-9f * seed;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) a[i] = fmaf(a[i], x, y);
+    }
+    float s = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += a[i];
+    if (s == 12345.678f) out[0] = s;
+  } else {
+    unsigned long long a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float2 v = make_float2(seed + i + threadIdx.x, seed - i);
+      a[i] = *reinterpret_cast<unsigned long long*>(&v);
+    }
+    float2 xv = make_float2(1.000001f, 0.999999f), yv = make_float2(1e-9f * seed, 1e-9f);
+    const unsigned long long x = *reinterpret_cast<unsigned long long*>(&xv);
+    const unsigned long long y = *reinterpret_cast<unsigned long long*>(&yv);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a[i]) : "l"(x), "l"(y));
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s ^= a[i];
+    if (s == 0x1234567812345678ull) out[0] = 1.0f;
+  }
+}
+
+cudaError_t launch_fma_peak(int dtype, int sms, float* ms, double* flops, cudaStream_t st) {
+  float* d_out = nullptr;
+  cudaError_t e = cudaMalloc(&d_out, 4);
+  if (e != cudaSuccess) return e;
+  const int blocks = sms * 8, threads = 256, iters = 8192;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(e0, st);
+    if (dtype == 0)
+      fma_peak_kernel<0><<<blocks, threads, 0, st>>>(d_out, iters, 1.0f);
+    else if (dtype == 1)
+      fma_peak_kernel<1><<<blocks, threads, 0, st>>>(d_out, iters, 1.0f);
+    else
+      fma_peak_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters, 1.0f);
+    cudaEventRecord(e1, st);
+    e = cudaEventSynchronize(e1);
+    if (e != cudaSuccess) break;
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    if (rep > 0 && t < best) best = t;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d_out);
+  if (e != cudaSuccess) return e;
+  const double per_thread = (dtype == 0) ? 8.0 * 2 : (dtype == 1 ? 16.0 * 2 : 8.0 * 4);
+  *flops = static_cast<double>(blocks) * threads * iters * per_thread;
+  *ms = best;
+  return cudaGetLastError();
+}
+
+}  // namespace rlb

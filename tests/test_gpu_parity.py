@@ -1,0 +1,292 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the pinned oracle
+on the same seeded inputs. Tolerances are BASELINE.json's: f64 scores <= 1e-9 relative,
+counts / inlier sets / best id exact (points within 1e-9 relative of the threshold are
+excused); f32 scores <= 1e-4 relative with the same selected model."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from ransaclib_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+F64_RTOL = 1e-9
+F32_RTOL = 1e-4
+
+
+def rlb():
+    import ransaclib_b200
+
+    return ransaclib_b200
+
+
+def assert_same_inliers(got, want, errs, thr):
+    """Exact set equality, except indices whose squared error is within 1e-9 rel of thr."""
+    got, want = set(map(int, got)), set(map(int, want))
+    for i in got ^ want:
+        assert abs(errs[i] - thr) <= 1e-9 * thr, f"index {i}: err {errs[i]} vs thr {thr}"
+
+
+@pytest.fixture(scope="module")
+def G():
+    with open(os.path.join(HERE, "golden", "reference_vectors.json")) as fh:
+        return json.load(fh)
+
+
+@pytest.fixture(scope="module")
+def pose_case():
+    inst = synth.pose_instance(123, 1500, 1573)  # n = 3073: not a multiple of any tile size
+    f = inst["focal"]
+    O = ol.oracle()
+    samples = ol.sample_uniform(O, 42, len(inst["points2D"]), 4, 3000)
+    models, valid = ol.pose_minimal(O, f, f, 144.0, inst["points2D"], inst["points3D"], samples)
+    return inst, f, samples, models, valid
+
+
+# ------------------------------------------------------------------ golden fixtures
+def test_golden_pose_scores(ctx, G):
+    p = G["pose"]
+    sc = ctx.pose_scorer(p["points2D"], p["points3D"], p["fx"], p["fy"])
+    s, c, bid, bsc = sc.score_models(p["models"], p["sq_thr"], precision=rlb().RLB_F64)
+    np.testing.assert_allclose(s, p["scores"], rtol=F64_RTOL)
+    assert c.tolist() == p["counts"]
+    assert bid == int(np.argmin(p["scores"])) and bsc == s[bid]
+    s32, c32, bid32, _ = sc.score_models(p["models"], p["sq_thr"], precision=rlb().RLB_F32)
+    np.testing.assert_allclose(s32, p["scores"], rtol=F32_RTOL)
+    assert bid32 == bid
+    for m, want in zip(p["models"][:3], p["inliers_first3"]):
+        lists, counts, score = sc.get_inliers(m, p["sq_thr"], p["sq_thr"])
+        assert lists[0].tolist() == want and counts[0] == len(want)
+    np.testing.assert_allclose(sc.eval_errors(p["models"][1]), p["errors_model1"], rtol=1e-9)
+
+
+def test_golden_line(ctx, G):
+    l = G["line"]
+    sc = ctx.line_scorer(l["xy"])
+    m, v = sc.solve_line2pt(l["samples"])
+    assert m.tolist() == l["models"] and v.tolist() == l["valid"]  # bit-exact (fmad off)
+    s, c, bid, _ = sc.score_models(l["models"], l["sq_thr"])
+    np.testing.assert_allclose(s, l["scores"], rtol=F64_RTOL)
+    assert c.tolist() == l["counts"] and bid == l["best"]
+    s32, _, bid32, _ = sc.score_models(l["models"], l["sq_thr"], precision=rlb().RLB_F32)
+    np.testing.assert_allclose(s32, l["scores"], rtol=F32_RTOL)
+    assert bid32 == l["best"]
+    lists, counts, _ = sc.get_inliers(l["models"][l["best"]], l["sq_thr"])
+    assert lists[0].tolist() == l["inliers_best"]
+
+
+def test_golden_hybrid(ctx, G):
+    h = G["hybrid"]
+    sc = ctx.hybrid_line_scorer(h["xy0"], h["xynn1"])
+    m0, v0 = sc.solve_line2pt(h["samples0"])
+    m1, v1 = sc.solve_point_normal(h["samples1"])
+    assert np.concatenate([m0, m1]).tolist() == h["models"]
+    assert np.concatenate([v0, v1]).tolist() == h["valid"]
+    s, c, bid, _ = sc.score_models(h["models"], h["sq_thr"], weights=h["weights"])
+    np.testing.assert_allclose(s, h["scores"], rtol=F64_RTOL)
+    assert c.tolist() == h["counts"] and bid == h["best"]
+    s32, _, bid32, _ = sc.score_models(h["models"], h["sq_thr"], weights=h["weights"], precision=rlb().RLB_F32)
+    np.testing.assert_allclose(s32, h["scores"], rtol=F32_RTOL)
+    assert bid32 == h["best"]
+    lists, counts, score = sc.get_inliers(h["models"][h["best"]], h["sq_thr"], h["sq_thr"], weights=h["weights"])
+    assert lists[0].tolist() == h["inliers0"] and lists[1].tolist() == h["inliers1"]
+    np.testing.assert_allclose(score, h["scores"][h["best"]], rtol=F64_RTOL)
+
+
+# ------------------------------------------------------------- functor-level parity
+def test_pose_errors_functor(ctx, pose_case):
+    inst, f, _, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    O = ol.oracle()
+    n = len(inst["points2D"])
+    for m in list(models[valid == 1][:5]) + [synth.pose_to_model(inst["R_gt"], inst["c_gt"])]:
+        want = np.empty(n)
+        O.pose_errors(ol.c64(m), f, f, n, inst["points2D"], inst["points3D"], want)
+        got = sc.eval_errors(m)
+        front = want < 1e300
+        np.testing.assert_allclose(got[front], want[front], rtol=1e-9, atol=1e-12)
+        assert (got[~front] > 1e300).all()  # behind-camera sentinel (DBL_MAX)
+        got32 = sc.eval_errors(m, precision=rlb().RLB_F32)
+        near = front & (want < 1e4)
+        np.testing.assert_allclose(got32[near], want[near], rtol=2e-4, atol=1e-3)
+        assert not (got32[~front] < 144.0).any()
+
+
+def test_pose_sweep_f64_and_f32(ctx, pose_case):
+    inst, f, _, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    O = ol.oracle()
+    want_s, want_c = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], models, 144.0)
+    s, c, bid, bsc = sc.score_models(models, 144.0, valid=valid)
+    ok = valid == 1
+    np.testing.assert_allclose(s[ok], want_s[ok], rtol=F64_RTOL)
+    assert (c[ok] == want_c[ok]).all()
+    assert (s[~ok] == np.finfo(np.float64).max).all() and (c[~ok] == 0).all()
+    masked = np.where(ok, want_s, np.inf)
+    assert bid == int(np.argmin(masked)) and bsc == s[bid]
+    s32, c32, bid32, _ = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F32)
+    np.testing.assert_allclose(s32[ok], want_s[ok], rtol=F32_RTOL)
+    assert bid32 == bid
+    assert np.abs(c32[ok] - want_c[ok]).max() <= 2  # only points numerically on the threshold
+
+
+def test_pose_inliers_ordered_and_fused_score(ctx, pose_case):
+    inst, f, _, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    O = ol.oracle()
+    n = len(inst["points2D"])
+    best = models[valid == 1][0]
+    for m in [best, synth.pose_to_model(inst["R_gt"], inst["c_gt"])]:
+        for thr_inl, thr_sc in [(144.0, 144.0), (144.0 * 2 ** 0.5, 144.0), (1.0, 144.0)]:
+            lists, counts, score = sc.get_inliers(m, thr_inl, thr_sc)
+            want = ol.pose_inliers(O, f, f, inst["points2D"], inst["points3D"], m, thr_inl)
+            errs = np.empty(n)
+            O.pose_errors(ol.c64(m), f, f, n, inst["points2D"], inst["points3D"], errs)
+            assert_same_inliers(lists[0], want, errs, thr_inl)
+            assert (np.diff(lists[0]) > 0).all()  # ascending (ransac.h:327-333)
+            assert counts[0] == len(lists[0])
+            ws, _ = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], m[None], thr_sc)
+            np.testing.assert_allclose(score, ws[0], rtol=F64_RTOL)
+    # count-only mode
+    _, counts, _ = sc.get_inliers(best, 144.0, want_indices=False)
+    assert counts[0] == len(ol.pose_inliers(O, f, f, inst["points2D"], inst["points3D"], best, 144.0))
+
+
+def test_p3p_batch_bit_exact(ctx, pose_case):
+    inst, f, samples, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    O = ol.oracle()
+    rays = np.empty((len(inst["points2D"]), 3))
+    O.pixels_to_rays(f, f, len(rays), inst["points2D"], rays)
+    assert sc.rays().tolist() == rays.tolist()
+    gm, gv = sc.solve_p3p(samples, 144.0)
+    assert gv.tolist() == valid.tolist()
+    assert gm.tolist() == models.tolist()  # no FMA contraction on either side: identical bits
+
+
+def test_hypothesize_and_score(ctx, pose_case):
+    inst, f, samples, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    O = ol.oracle()
+    want_s, want_c = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], models, 144.0)
+    masked = np.where(valid == 1, want_s, np.inf)
+    for prec, rtol in [(rlb().RLB_F64, F64_RTOL), (rlb().RLB_F32, F32_RTOL)]:
+        r = sc.hypothesize_and_score(samples, 144.0, precision=prec)
+        assert r["valid"].tolist() == valid.tolist()
+        assert r["models"].tolist() == models.tolist()
+        ok = valid == 1
+        np.testing.assert_allclose(r["scores"][ok], want_s[ok], rtol=rtol)
+        assert r["best_id"] == int(np.argmin(masked))
+        assert r["best_model"].tolist() == models[r["best_id"]].tolist()
+
+
+# --------------------------------------------------------------------- edge cases
+def test_ties_invalid_nan_and_tiny_inputs(ctx):
+    R = rlb()
+    inst = synth.pose_instance(5, 4, 1)  # n = 5 (< one vector group, < one stage)
+    f = inst["focal"]
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    gt = synth.pose_to_model(inst["R_gt"], inst["c_gt"])
+    bad = gt.copy()
+    bad[3] = np.nan
+    models = np.stack([bad, gt, gt, gt])  # NaN model first, then a three-way tie
+    s, c, bid, bsc = sc.score_models(models, 144.0)
+    assert np.isnan(s[0]) and c[0] == 0  # NaN propagates and never wins (ransac.h:308)
+    assert bid == 1 and s[1] == s[2] == s[3]  # lowest id wins ties (ransac.h:288)
+    s, c, bid, _ = sc.score_models(models, 144.0, valid=np.array([1, 0, 0, 1], np.uint8))
+    assert bid == 3
+    s, c, bid, bsc = sc.score_models(models, 144.0, valid=np.zeros(4, np.uint8))
+    assert bid == -1 and bsc == np.finfo(np.float64).max
+    O = ol.oracle()
+    ws, wc = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], gt[None], 144.0)
+    s1, c1, b1, _ = sc.score_models(gt[None], 144.0)  # K = 1
+    np.testing.assert_allclose(s1, ws, rtol=F64_RTOL)
+    assert c1.tolist() == wc.tolist() and b1 == 0
+    with pytest.raises(R.RlbError):
+        sc.solve_p3p(np.array([[0, 1, 2, 5]], np.int32), 144.0)  # index out of range
+
+
+def test_empty_and_ragged_hybrid(ctx):
+    xy0, p1 = synth.hybrid_line_instance(3, 700, 500, 10, 7)  # 1200 / 17 points: ragged segments
+    sc = ctx.hybrid_line_scorer(xy0, p1)
+    O = ol.oracle()
+    smp = ol.sample_uniform(O, 1, len(xy0), 2, 64)
+    models, valid = sc.solve_line2pt(smp)
+    thr, w = np.array([1e-4, 3e-4]), np.array([2.0, 0.5])
+    ws, wc = np.empty(64), np.empty(64, np.int32)
+    O.hybrid_line_score_models(len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), 64, ol.c64(models), thr, w, ws, wc)
+    s, c, bid, _ = sc.score_models(models, thr, weights=w)
+    np.testing.assert_allclose(s, ws, rtol=F64_RTOL)
+    assert c.tolist() == wc.tolist() and bid == int(np.argmin(ws))
+    # second data type empty
+    sc2 = ctx.hybrid_line_scorer(xy0, np.zeros((0, 4)))
+    s2, c2, _, _ = sc2.score_models(models, thr, weights=w)
+    ws2, wc2 = np.empty(64), np.empty(64, np.int32)
+    O.line_score_models(len(xy0), ol.c64(xy0), 64, ol.c64(models), thr[0], ws2, wc2)
+    np.testing.assert_allclose(s2, 2.0 * ws2, rtol=F64_RTOL)
+    lists, counts, _ = sc2.get_inliers(models[int(np.argmin(ws))], thr)
+    assert counts.tolist() == [len(lists[0]), 0]
+
+
+def test_far_from_origin_f32_recentring(ctx):
+    """Scene 1e5 units from the origin: the f32 path must still meet 1e-4 (points are
+    recentred in f64 before the f32 conversion)."""
+    inst = synth.pose_instance(9, 1000, 1000)
+    shift = np.array([1.2e5, -3.4e5, 5.6e4])
+    p3 = inst["points3D"] + shift
+    f = inst["focal"]
+    sc = ctx.pose_scorer(inst["points2D"], p3, f, f)
+    models = synth.perturbed_poses(2, inst["R_gt"], inst["c_gt"] + shift, 64, rot_sigma=0.003, trans_sigma=0.01)
+    O = ol.oracle()
+    ws, wc = ol.pose_score(O, f, f, inst["points2D"], p3, models, 144.0)
+    s, c, bid, _ = sc.score_models(models, 144.0)
+    np.testing.assert_allclose(s, ws, rtol=1e-7)  # f64 input coordinates only carry ~1e-11 rel here
+    s32, _, bid32, _ = sc.score_models(models, 144.0, precision=rlb().RLB_F32)
+    np.testing.assert_allclose(s32, ws, rtol=F32_RTOL)
+    assert bid32 == int(np.argmin(ws))
+
+
+def test_determinism(ctx, pose_case):
+    inst, f, _, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    a = sc.score_models(models, 144.0, precision=rlb().RLB_F32)
+    b = sc.score_models(models, 144.0, precision=rlb().RLB_F32)
+    assert a[0].tolist() == b[0].tolist() and a[1].tolist() == b[1].tolist()
+    l1 = sc.get_inliers(models[valid == 1][0], 144.0, 144.0)
+    l2 = sc.get_inliers(models[valid == 1][0], 144.0, 144.0)
+    assert l1[0][0].tolist() == l2[0][0].tolist() and l1[2] == l2[2]
+
+
+# ------------------------------------------- full-size, size-independent properties
+def test_full_size_properties(ctx):
+    """BASELINE config sizes (N = 1M points) are too slow for the scalar oracle on all K;
+    check (a) a sampled subset of hypotheses against the oracle, (b) linearity: scoring the
+    two halves of the point set separately sums to the whole, (c) idempotence."""
+    n, k = 1_000_000, 4096
+    inst = synth.pose_instance(9000, n // 2, n // 2)
+    f = inst["focal"]
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    models = synth.perturbed_poses(1, inst["R_gt"], inst["c_gt"], k)
+    s, c, bid, bsc = sc.score_models(models, 144.0, precision=rlb().RLB_F32)
+    s64, c64_, bid64, _ = sc.score_models(models, 144.0)
+    np.testing.assert_allclose(s, s64, rtol=F32_RTOL)
+    assert bid == bid64
+    O = ol.oracle()
+    pick = np.array([0, 1, 7, bid, k - 1])
+    ws, wc = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], models[pick], 144.0)
+    np.testing.assert_allclose(s64[pick], ws, rtol=F64_RTOL)
+    assert c64_[pick].tolist() == wc.tolist()
+    h = n // 2 + 137
+    sa = ctx.pose_scorer(inst["points2D"][:h], inst["points3D"][:h], f, f)
+    sb = ctx.pose_scorer(inst["points2D"][h:], inst["points3D"][h:], f, f)
+    a = sa.score_models(models[:256], 144.0)
+    b = sb.score_models(models[:256], 144.0)
+    np.testing.assert_allclose(a[0] + b[0], s64[:256], rtol=1e-9)
+    assert (a[1] + b[1]).tolist() == c64_[:256].tolist()
+    lists, counts, score = sc.get_inliers(models[bid64], 144.0, 144.0)
+    assert counts[0] == c64_[bid64] and (np.diff(lists[0]) > 0).all()
+    np.testing.assert_allclose(score, s64[bid64], rtol=F64_RTOL)

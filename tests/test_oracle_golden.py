@@ -1,0 +1,211 @@
+"""CPU tests: the restated oracle (oracle/liboracle.so, built from committed sources)
+against the golden vectors produced by the reference's own headers (oracle/_ref) and
+against OpenCV's P3P. These pin the oracle; the GPU parity tests then compare the
+CUDA path with the pinned oracle."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def G():
+    with open(os.path.join(HERE, "golden", "reference_vectors.json")) as fh:
+        return json.load(fh)
+
+
+@pytest.fixture(scope="module")
+def O():
+    return ol.oracle()
+
+
+def test_survey_known_answers(O):
+    # vectors produced by the unmodified reference headers.
+    assert ol.sample_uniform(O, 0, 10000, 4, 3).tolist() == [[5488, 5928, 7151, 8442], [6027, 8579, 5448, 8472],
+                                                           [4236, 6235, 6458, 3843]]
+    assert ol.sample_uniform(O, 42, 10000, 4, 3).tolist() == [[3745, 7965, 9507, 1834], [7319, 7796, 5986, 5968],
+                                                            [1560, 4458, 1559, 999]]
+    assert ol.sample_uniform(O, 42, 5, 4, 3).tolist() == [[1, 4, 0, 3], [3, 4, 0, 1], [0, 2, 1, 3]]
+    assert O.num_required_iterations(0.5, 1e-4, 4, 100, 10000) == 144
+    assert O.num_required_iterations(0.1, 1e-4, 4, 100, 1000000) == 92100
+
+
+def test_uniform_sampling(G, O):
+    for c in G["uniform_sampling"]:
+        got = ol.sample_uniform(O, c["seed"], c["n"], c["s"], c["k"])
+        assert got.tolist() == c["samples"]
+
+
+def test_hybrid_sampling(G, O):
+    for c in G["hybrid_sampling"]:
+        k = len(c["sizes"])
+        o = np.empty((k, 2), np.int32)
+        O.sample_hybrid(c["seed"], 2, np.asarray(c["num_data"], np.int32), k,
+                        np.asarray(c["sizes"], np.int32).reshape(-1), 2, o.reshape(-1))
+        assert o.tolist() == c["samples"]
+
+
+def test_num_required_iterations(G, O):
+    for c in G["num_required_iterations"]:
+        assert O.num_required_iterations(*c["args"]) == c["value"]
+    for c in G["num_required_iterations_hybrid"]:
+        v = O.num_required_iterations_hybrid(2, np.asarray(c["ratios"], np.float64), 1e-4,
+                                             np.asarray(c["sizes"], np.int32), c["min"], c["max"])
+        assert v == c["value"]
+
+
+def test_shuffle_consumes_same_draws(G, O):
+    for c in G["shuffle_and_resize"]:
+        o = np.empty(c["target"], np.int32)
+        nxt = C.c_uint32()
+        O.shuffle_and_resize(c["seed"], c["n"], c["target"], o, C.byref(nxt))
+        assert o.tolist() == c["out"]
+        assert nxt.value == c["next_draw"]
+
+
+def test_pose_scoring_and_inliers(G, O):
+    p = G["pose"]
+    p2, p3, models = np.array(p["points2D"]), np.array(p["points3D"]), np.array(p["models"])
+    s, c = ol.pose_score(O, p["fx"], p["fy"], p2, p3, models, p["sq_thr"])
+    assert s.tolist() == p["scores"]  # same compiler flags, same operation order: bit-exact
+    assert c.tolist() == p["counts"]
+    assert c[-1] == 0 and s[-1] == p["sq_thr"] * len(p2)  # behind the camera: all outliers
+    for m, want in zip(models[:3], p["inliers_first3"]):
+        assert ol.pose_inliers(O, p["fx"], p["fy"], p2, p3, m, p["sq_thr"]).tolist() == want
+    err = np.empty(len(p2))
+    O.pose_errors(ol.c64(models[1]), p["fx"], p["fy"], len(p2), ol.c64(p2), ol.c64(p3), err)
+    assert err.tolist() == p["errors_model1"]
+
+
+def test_pose_lomsac_end_to_end(G, O):
+    p = G["pose"]
+    p2, p3 = np.array(p["points2D"]), np.array(p["points3D"])
+    for c in p["lomsac"]:
+        o = ol.Options.default(sq_thr=p["sq_thr"], seed=c["seed"], final_lsq=c["final_lsq"], lo_steps=c["lo_steps"],
+                               min_iters=c["min_iters"], max_iters=c["max_iters"])
+        st = ol.Stats()
+        model = np.zeros(12)
+        inl = np.zeros(len(p2), np.int32)
+        O.lomsac_pose(C.byref(o), p["fx"], p["fy"], len(p2), ol.c64(p2), ol.c64(p3), model, C.byref(st), inl)
+        assert st.num_iterations == c["num_iterations"]
+        assert st.best_num_inliers == c["best_num_inliers"]
+        assert st.number_lo_iterations == c["number_lo_iterations"]
+        assert st.best_model_score == c["best_model_score"]
+        assert st.inlier_ratio == c["inlier_ratio"]
+        assert model.tolist() == c["model"]
+        assert inl[:st.best_num_inliers].tolist() == c["inliers"]
+
+
+def test_line_paths(G, O):
+    l = G["line"]
+    xy = np.array(l["xy"])
+    smp = np.asarray(l["samples"], np.int32)
+    m, v = np.empty((len(smp), 3)), np.empty(len(smp), np.uint8)
+    O.line_minimal_batch(len(xy), ol.c64(xy), len(smp), smp, m, v)
+    assert m.tolist() == l["models"] and v.tolist() == l["valid"]
+    s, c = np.empty(len(m)), np.empty(len(m), np.int32)
+    O.line_score_models(len(xy), ol.c64(xy), len(m), m, l["sq_thr"], s, c)
+    assert s.tolist() == l["scores"] and c.tolist() == l["counts"]
+    idx = np.empty(len(xy), np.int32)
+    n = O.line_inliers(len(xy), ol.c64(xy), ol.c64(m[l["best"]]), l["sq_thr"], idx)
+    assert idx[:n].tolist() == l["inliers_best"]
+    for c in l["lomsac"]:
+        o = ol.Options.default(sq_thr=l["sq_thr"], seed=c["seed"], final_lsq=c["final_lsq"], min_iters=100,
+                               max_iters=100000)
+        st = ol.Stats()
+        model = np.zeros(3)
+        inl = np.zeros(len(xy), np.int32)
+        O.lomsac_line(C.byref(o), len(xy), ol.c64(xy), model, C.byref(st), inl)
+        assert (st.num_iterations, st.best_num_inliers, st.number_lo_iterations) == (
+            c["num_iterations"], c["best_num_inliers"], c["number_lo_iterations"])
+        assert st.best_model_score == c["best_model_score"]
+        assert model.tolist() == c["model"]
+        assert inl[:st.best_num_inliers].tolist() == c["inliers"]
+
+
+def test_hybrid_paths(G, O):
+    h = G["hybrid"]
+    xy0, p1, hm = np.array(h["xy0"]), np.array(h["xynn1"]), np.array(h["models"])
+    s1 = np.asarray(h["samples1"], np.int32)
+    m1, v1 = np.empty((len(s1), 3)), np.empty(len(s1), np.uint8)
+    O.point_normal_batch(len(p1), ol.c64(p1), len(s1), s1, m1, v1)
+    assert m1.tolist() == h["models"][6:]
+    s, c = np.empty(len(hm)), np.empty(len(hm), np.int32)
+    O.hybrid_line_score_models(len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), len(hm), ol.c64(hm),
+                               np.array(h["sq_thr"]), np.array(h["weights"]), s, c)
+    assert s.tolist() == h["scores"] and c.tolist() == h["counts"]
+    i0, i1, cc = np.empty(len(xy0), np.int32), np.empty(len(p1), np.int32), np.empty(2, np.int32)
+    O.hybrid_line_inliers(len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), ol.c64(hm[h["best"]]), np.array(h["sq_thr"]),
+                          i0, i1, cc)
+    assert i0[:cc[0]].tolist() == h["inliers0"] and i1[:cc[1]].tolist() == h["inliers1"]
+    for c in h["lomsac"]:
+        o = ol.HybridOptions.default(sq_thr=[1e-4, 1e-4], weights=[2.0, 0.5], seed=c["seed"],
+                                     final_lsq=c["final_lsq"], min_iters=100, max_iters=10000,
+                                     max_iters_per_solver=1000)
+        st = ol.HybridStats()
+        model = np.zeros(3)
+        a, b = np.zeros(len(xy0), np.int32), np.zeros(len(p1), np.int32)
+        O.hybrid_lomsac_line(C.byref(o), len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), np.array([0.2, 0.8]), model,
+                             C.byref(st), a, b)
+        assert st.num_iterations_total == c["num_iterations_total"]
+        assert list(st.num_iterations_per_solver) == c["num_iterations_per_solver"]
+        assert st.best_num_inliers == c["best_num_inliers"]
+        assert st.best_solver_type == c["best_solver_type"]
+        assert st.best_model_score == c["best_model_score"]
+        assert list(st.inlier_ratios) == c["inlier_ratios"]
+        assert st.number_lo_iterations == c["number_lo_iterations"]
+        assert model.tolist() == c["model"]
+        assert a[:st.num_inliers_per_type[0]].tolist() == c["inliers0"]
+        assert b[:st.num_inliers_per_type[1]].tolist() == c["inliers1"]
+
+
+def test_p3p_against_opencv(O):
+    with open(os.path.join(HERE, "golden", "p3p_cv2.json")) as fh:
+        cases = json.load(fh)["cases"]
+    for c in cases:
+        y, X = np.array(c["y"]), np.array(c["X"])
+        Rs, ts = np.zeros(36), np.zeros(12)
+        n = O.p3p(y, X, Rs, ts)
+        ours = [(Rs[9 * i:9 * i + 9], ts[3 * i:3 * i + 3]) for i in range(n)]
+        # ground truth among ours
+        assert min(np.abs(R - np.array(c["R_gt"])).max() + np.abs(t - np.array(c["t_gt"])).max()
+                   for R, t in ours) < 1e-7
+        # same solution set as OpenCV (positive-depth solutions)
+        assert n == len(c["cv2_solutions"])
+        for s in c["cv2_solutions"]:
+            assert min(np.abs(R - np.array(s["R"])).max() + np.abs(t - np.array(s["t"])).max()
+                       for R, t in ours) < 1e-5
+        # invariants: proper rotations that reproduce the bearings
+        for R, t in ours:
+            R = R.reshape(3, 3)
+            assert abs(np.linalg.det(R) - 1) < 1e-8 and np.abs(R @ R.T - np.eye(3)).max() < 1e-8
+            P = X.reshape(3, 3) @ R.T + t
+            assert (P[:, 2] > 0).all()
+            assert np.abs(P / np.linalg.norm(P, axis=1, keepdims=True) - y.reshape(3, 3)).max() < 1e-8
+
+
+def test_reference_build_agrees_when_present(G, O):
+    """In the build container oracle/_ref exists: oracle == reference on fresh random input."""
+    ref = ol.reference()
+    if ref is None:
+        pytest.skip("oracle/_ref not built here")
+    from ransaclib_b200 import synth
+
+    inst = synth.pose_instance(77, 300, 300)
+    f = inst["focal"]
+    o = ol.Options.default(sq_thr=144.0, seed=5, final_lsq=1, min_iters=100, max_iters=5000)
+    res = []
+    for lib in (O, ref):
+        st = ol.Stats()
+        model = np.zeros(12)
+        inl = np.zeros(600, np.int32)
+        lib.lomsac_pose(C.byref(o), f, f, 600, inst["points2D"], inst["points3D"], model, C.byref(st), inl)
+        res.append((st.num_iterations, st.best_num_inliers, st.best_model_score, model.tolist(),
+                    inl[:st.best_num_inliers].tolist()))
+    assert res[0] == res[1]
