@@ -57,9 +57,11 @@ int rlb_version(void);
 /* ---- context ------------------------------------------------------------- */
 int rlb_ctx_create(int device, rlb_ctx** ctx);
 int rlb_ctx_destroy(rlb_ctx* ctx);
-/* Use an existing cudaStream_t (e.g. torch's current stream); NULL restores the
- * context's own stream. */
+/* Run on an existing cudaStream_t (e.g. torch's current stream). The handle is used
+ * as given: NULL is CUDA's legacy default stream. rlb_ctx_use_own_stream goes back to
+ * the non-blocking stream the context created for itself. */
 int rlb_ctx_set_stream(rlb_ctx* ctx, void* cuda_stream);
+int rlb_ctx_use_own_stream(rlb_ctx* ctx);
 int rlb_ctx_synchronize(rlb_ctx* ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 int64_t rlb_ctx_launch_count(const rlb_ctx* ctx);

@@ -40,7 +40,11 @@ class Context:
             pass
 
     def set_stream(self, cuda_stream: int | None):
-        _capi.check(self._lib.rlb_ctx_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
+        """Run on the given cudaStream_t handle (0 = legacy default stream); None = own stream."""
+        if cuda_stream is None:
+            _capi.check(self._lib.rlb_ctx_use_own_stream(self._h))
+        else:
+            _capi.check(self._lib.rlb_ctx_set_stream(self._h, C.c_void_p(cuda_stream)))
 
     def synchronize(self):
         _capi.check(self._lib.rlb_ctx_synchronize(self._h))

@@ -19,7 +19,7 @@ KIND_LINE, KIND_HYBRID_LINE, KIND_POSE = 0, 1, 2
 
 # every symbol include/ransaclib_b200.h declares (tests check the .so exports all of them)
 SYMBOLS = [
-    "rlb_last_error", "rlb_version", "rlb_ctx_create", "rlb_ctx_destroy", "rlb_ctx_set_stream",
+    "rlb_last_error", "rlb_version", "rlb_ctx_create", "rlb_ctx_destroy", "rlb_ctx_set_stream", "rlb_ctx_use_own_stream",
     "rlb_ctx_synchronize", "rlb_ctx_launch_count", "rlb_ctx_sm_count", "rlb_scorer_create_line",
     "rlb_scorer_create_hybrid_line", "rlb_scorer_create_pose", "rlb_scorer_destroy", "rlb_scorer_kind",
     "rlb_scorer_num_types", "rlb_scorer_num_data", "rlb_scorer_model_size", "rlb_scorer_get_rays",
@@ -51,6 +51,7 @@ def load():
     lib.rlb_ctx_create.argtypes = [i32, C.POINTER(vp)]
     lib.rlb_ctx_destroy.argtypes = [vp]
     lib.rlb_ctx_set_stream.argtypes = [vp, vp]
+    lib.rlb_ctx_use_own_stream.argtypes = [vp]
     lib.rlb_ctx_synchronize.argtypes = [vp]
     lib.rlb_ctx_launch_count.argtypes = [vp]
     lib.rlb_ctx_launch_count.restype = C.c_int64

@@ -343,7 +343,13 @@ int rlb_ctx_destroy(rlb_ctx* c) {
 
 int rlb_ctx_set_stream(rlb_ctx* c, void* stream) {
   if (!c) return fail(RLB_E_ARG, "null ctx");
-  c->stream = stream ? static_cast<cudaStream_t>(stream) : c->own_stream;
+  c->stream = static_cast<cudaStream_t>(stream);
+  return RLB_OK;
+}
+
+int rlb_ctx_use_own_stream(rlb_ctx* c) {
+  if (!c) return fail(RLB_E_ARG, "null ctx");
+  c->stream = c->own_stream;
   return RLB_OK;
 }
 
