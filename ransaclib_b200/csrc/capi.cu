@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -192,6 +193,13 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   a.models = d_models;
   a.valid = d_valid;
   fill_thr(d, thr, w, a.thr, a.w);
+  {
+    static const int variant = [] {
+      const char* v = getenv("RLB_SWEEP_VARIANT");
+      return v ? atoi(v) : 0;
+    }();
+    a.variant = variant;
+  }
   const int H = (precision == RLB_F32) ? 4 : (d.kind == RLB_KIND_POSE ? 2 : 4);
   const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
   const int total_stages = d.npad / rlb::kStage;

@@ -29,7 +29,7 @@ struct DeviceData {
   int npad;                 // total padded points
   int channels;             // 2 (line kinds) or 5 (pose: X,Y,Z,u,v)
   const double* soa64;      // [channels][npad]
-  const float* soa32;       // [channels][npad]   (pose: recentred)
+  const float* soa32;       // [channels][npad]; pose: channels 3,4 hold -u,-v, NaN in the padding
   double fx, fy;            // pose intrinsics
   double centre[3];         // f64 point subtracted from the coordinates before the SoA repack
   // raw reference-layout copies for the minimal solvers (f64)
@@ -48,6 +48,7 @@ struct SweepArgs {
   int stages_per_split;        // stages each split covers
   double* part_score;          // [n_splits][k]
   int32_t* part_count;         // [n_splits][k]
+  int variant;                 // 0 = default kernels, 1 = scalar-FFMA sweep (A/B timing)
 };
 
 struct BestRec {

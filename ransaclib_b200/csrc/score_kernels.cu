@@ -141,8 +141,8 @@ __device__ __forceinline__ float PoseF<float>::eval(const Model& m, const float*
   const float px = fmaf(m.r[0], p[0], fmaf(m.r[1], p[1], fmaf(m.r[2], p[2], m.t[0])));
   const float py = fmaf(m.r[3], p[0], fmaf(m.r[4], p[1], fmaf(m.r[5], p[2], m.t[1])));
   const float inv = rcp_approx(fmaxf(pz, 0.0f));
-  const float du = fmaf(px, inv, -p[3]);
-  const float dv = fmaf(py, inv, -p[4]);
+  const float du = fmaf(px, inv, p[3]);  // the f32 stage stores -u, -v
+  const float dv = fmaf(py, inv, p[4]);
   return fmaf(du, du, dv * dv);
 }
 
@@ -361,10 +361,197 @@ static cudaError_t launch_sweep_t(const DeviceData& d, const SweepArgs& a, cudaS
   return cudaGetLastError();
 }
 
+// ------------------------------------------- pose f32 sweep on packed FFMA2 (sm_100)
+// Blackwell's fma.rn.f32x2 issues two f32 FMAs per instruction slot. The scalar sweep
+// above is bound by ISSUE slots (~18 per evaluation, 14 of them on the FMA pipe); here
+// two consecutive POINTS share every instruction of the projection (the SoA stage layout
+// makes {X_j, X_j+1} a natural 64-bit pair) while the hypothesis coefficients are
+// scalar-broadcast operands (ptxas folds mov.b64 {r,r} into the FFMA2 .F32 operand form),
+// so model registers are not duplicated. Per pair of evaluations: 13 FFMA2/FMUL2 +
+// 2 FMNMX + 2 MUFU.RCP + 2 FSETP + 2 predicated FADD + 2 predicated IADD.
+// The f32 stage stores -u,-v (so the residual is one FMA) and NaN in the padding, which
+// makes padded points fail (e < thr) without any bounds test in the inner loop.
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
+  u64 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+#define RLB_B2(x) pack2((x), (x))
+
+template <int H>
+__global__ void __launch_bounds__(kSweepThreads)
+    sweep_pose_f32x2_kernel(const DeviceData d, const SweepArgs a) {
+  typedef PoseF<float> F;
+  constexpr int C = F::C;
+  constexpr uint32_t kChanBytes = kStage * sizeof(float);
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* ring = reinterpret_cast<float*>(smem_raw);  // [kNumStages][C][kStage]
+  __shared__ __align__(8) uint64_t full[kNumStages];
+
+  const int tid = threadIdx.x;
+  const int kbase = blockIdx.x * (kSweepThreads * H);
+  const int split = blockIdx.y;
+  const float* soa = d.soa32;
+  const int npad = d.npad;
+  const int n_live = d.n[0];
+
+  const int total_stages = npad / kStage;
+  const int s_begin = split * a.stages_per_split;
+  const int s_end = min(total_stages, s_begin + a.stages_per_split);
+  const int nst = max(0, s_end - s_begin);
+
+  F::Model m[H];
+  u64 t2[H][3];  // translation as real pairs (FFMA2 addend)
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    const int k = kbase + h * kSweepThreads + tid;
+    if (k < a.k) {
+      F::load(a.models + static_cast<size_t>(k) * F::MD, d, m[h]);
+    } else {
+      F::zero(m[h]);
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) t2[h][r] = pack2(m[h].t[r], m[h].t[r]);
+  }
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kNumStages; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](int it) {
+    const int slot = it % kNumStages;
+    const size_t g0 = static_cast<size_t>(s_begin + it) * kStage;
+    float* dst = ring + static_cast<size_t>(slot) * C * kStage;
+    mbar_expect_tx(&full[slot], C * kChanBytes);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      tma_load_1d(dst + c * kStage, soa + static_cast<size_t>(c) * npad + g0, kChanBytes, &full[slot]);
+    }
+  };
+  if (tid == 0) {
+    for (int it = 0; it < kNumStages && it < nst; ++it) issue(it);
+  }
+
+  const double thr64 = a.thr[0];
+  const float thr = static_cast<float>(thr64);
+  const double w = a.w[0];
+  double dacc[H];
+  int dcnt[H];
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    dacc[h] = 0.0;
+    dcnt[h] = 0;
+  }
+
+  for (int it = 0; it < nst; ++it) {
+    const int slot = it % kNumStages;
+    mbar_wait(&full[slot], (it / kNumStages) & 1);
+    const int g0 = (s_begin + it) * kStage;
+    const int cnt = max(0, min(kStage, n_live - g0));
+    const float* sb = ring + static_cast<size_t>(slot) * C * kStage;
+
+    float s[H];
+    int c[H];
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      s[h] = 0.0f;
+      c[h] = 0;
+    }
+    const int groups = (cnt + 3) >> 2;
+#pragma unroll 1
+    for (int g = 0; g < groups; ++g) {
+      const ulonglong2 X = *reinterpret_cast<const ulonglong2*>(sb + 0 * kStage + 4 * g);
+      const ulonglong2 Y = *reinterpret_cast<const ulonglong2*>(sb + 1 * kStage + 4 * g);
+      const ulonglong2 Z = *reinterpret_cast<const ulonglong2*>(sb + 2 * kStage + 4 * g);
+      const ulonglong2 U = *reinterpret_cast<const ulonglong2*>(sb + 3 * kStage + 4 * g);
+      const ulonglong2 V = *reinterpret_cast<const ulonglong2*>(sb + 4 * kStage + 4 * g);
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const u64 x = q ? X.y : X.x, y = q ? Y.y : Y.x, z = q ? Z.y : Z.x;
+        const u64 nu = q ? U.y : U.x, nv = q ? V.y : V.x;
+#pragma unroll
+        for (int h = 0; h < H; ++h) {
+          const F::Model& mm = m[h];
+          const u64 pz = ffma2(RLB_B2(mm.r[6]), x, ffma2(RLB_B2(mm.r[7]), y, ffma2(RLB_B2(mm.r[8]), z, t2[h][2])));
+          const u64 px = ffma2(RLB_B2(mm.r[0]), x, ffma2(RLB_B2(mm.r[1]), y, ffma2(RLB_B2(mm.r[2]), z, t2[h][0])));
+          const u64 py = ffma2(RLB_B2(mm.r[3]), x, ffma2(RLB_B2(mm.r[4]), y, ffma2(RLB_B2(mm.r[5]), z, t2[h][1])));
+          float pza, pzb;
+          unpack2(pz, pza, pzb);
+          const u64 inv = pack2(rcp_approx(fmaxf(pza, 0.0f)), rcp_approx(fmaxf(pzb, 0.0f)));
+          const u64 du = ffma2(px, inv, nu);
+          const u64 dv = ffma2(py, inv, nv);
+          const u64 e = ffma2(du, du, fmul2(dv, dv));
+          float ea, eb;
+          unpack2(e, ea, eb);
+          if (ea < thr) {
+            s[h] += ea;
+            c[h] += 1;
+          }
+          if (eb < thr) {
+            s[h] += eb;
+            c[h] += 1;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      dacc[h] += w * (static_cast<double>(s[h]) + thr64 * static_cast<double>(cnt - c[h]));
+      dcnt[h] += c[h];
+    }
+    __syncthreads();
+    if (tid == 0 && it + kNumStages < nst) issue(it + kNumStages);
+  }
+
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    const int k = kbase + h * kSweepThreads + tid;
+    if (k < a.k) {
+      a.part_score[static_cast<size_t>(split) * a.k + k] = dacc[h];
+      a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt[h];
+    }
+  }
+}
+
+template <int H>
+static cudaError_t launch_sweep_pose_x2(const DeviceData& d, const SweepArgs& a, cudaStream_t st) {
+  const size_t smem = static_cast<size_t>(kNumStages) * 5 * kStage * sizeof(float);
+  auto kern = sweep_pose_f32x2_kernel<H>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid((a.k + kSweepThreads * H - 1) / (kSweepThreads * H), a.n_splits);
+  kern<<<grid, kSweepThreads, smem, st>>>(d, a);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision, cudaStream_t st,
                          int* launches) {
   ++*launches;
   if (d.kind == RLB_KIND_POSE) {
+    if (precision == RLB_F32 && a.variant == 0) return launch_sweep_pose_x2<4>(d, a, st);
     if (precision == RLB_F32) return launch_sweep_t<PoseF, float, 4>(d, a, st);
     return launch_sweep_t<PoseF, double, 2>(d, a, st);
   }
@@ -758,7 +945,13 @@ __global__ void repack_kernel(const DeviceData d, double* __restrict__ soa64,
     }
     for (int c = 0; c < d.channels; ++c) {
       soa64[static_cast<size_t>(c) * total + g] = v[c];
-      soa32[static_cast<size_t>(c) * total + g] = static_cast<float>(v[c]);
+      float f = static_cast<float>(v[c]);
+      if (d.kind == RLB_KIND_POSE && c >= 3) {
+        // f32 pose stage: negated pixel coordinates (residual = one FMA); NaN in the padding
+        // so that padded points can never pass (e < thr) in the unguarded FFMA2 loop.
+        f = live ? -f : __int_as_float(0x7fc00000);
+      }
+      soa32[static_cast<size_t>(c) * total + g] = f;
     }
   }
 }
