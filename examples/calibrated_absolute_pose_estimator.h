@@ -1,0 +1,128 @@
+// CalibratedAbsolutePoseEstimator — the reference's P3P + 4th-point absolute pose solver
+// (examples/calibrated_absolute_pose_estimator.{h,cc}) with the 2D-3D matches resident on
+// the GPU. EvaluateModelOnPoint over all matches (scoring, inliers) and the batched P3P
+// minimal solver run on the device; the non-linear refinement stays on the host.
+#ifndef RANSACLIB_B200_EXAMPLES_CALIBRATED_ABSOLUTE_POSE_ESTIMATOR_H_
+#define RANSACLIB_B200_EXAMPLES_CALIBRATED_ABSOLUTE_POSE_ESTIMATOR_H_
+
+#include <cmath>
+#include <cstdint>
+#include <limits>
+#include <vector>
+
+#include <RansacLib/gpu_scorer.h>
+
+#include "model_types.h"
+#include "pose_refinement.h"
+
+namespace ransac_lib {
+namespace calibrated_absolute_pose {
+
+class CalibratedAbsolutePoseEstimator {
+ public:
+  // points2D: n x 2 (centred on the principal point, undistorted); points3D: n x 3.
+  // The viewing rays of the reference's constructor (.cc:99-109) are derived on the device
+  // exactly as PixelsToViewingRays does (.cc:214-227).
+  CalibratedAbsolutePoseEstimator(double f_x, double f_y, double squared_inlier_threshold, int n,
+                                  const double* points2D, const double* points3D,
+                                  gpu::Context* ctx = nullptr)
+      : focal_x_(f_x),
+        focal_y_(f_y),
+        squared_inlier_threshold_(squared_inlier_threshold),
+        points2D_(points2D, points2D + 2 * static_cast<size_t>(n)),
+        points3D_(points3D, points3D + 3 * static_cast<size_t>(n)),
+        num_data_(n) {
+    scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), n, points2D_.data(),
+                     points3D_.data(), f_x, f_y);
+  }
+
+  inline int min_sample_size() const { return 4; }          // reference .h:88
+  inline int non_minimal_sample_size() const { return 6; }  // reference .h:90
+  inline int num_data() const { return num_data_; }
+
+  // One sample through the device P3P kernel (K = 1). The batched driver does not use this;
+  // it exists for NonMinimalSolver and for API completeness (.cc:111-137).
+  int MinimalSolver(const std::vector<int>& sample, CameraPoses* poses) const {
+    poses->clear();
+    if (sample.size() < 4u) return 0;
+    const int32_t s4[4] = {sample[0], sample[1], sample[2], sample[3]};
+    CameraPose P;
+    uint8_t ok = 0;
+    gpu::Check(rlb_solve_p3p_batch(scorer_.get(), 1, s4, squared_inlier_threshold_, P.m, &ok),
+               "rlb_solve_p3p_batch");
+    if (ok) poses->push_back(P);
+    return static_cast<int>(poses->size());
+  }
+
+  // .cc:141-151
+  int NonMinimalSolver(const std::vector<int>& sample, CameraPose* pose) const {
+    CameraPoses poses;
+    if (MinimalSolver(sample, &poses) == 1) {
+      *pose = poses[0];
+      LeastSquares(sample, pose);
+      return 1;
+    }
+    return 0;
+  }
+
+  // Host evaluation of ONE match (.cc:154-167); the drivers never call it.
+  double EvaluateModelOnPoint(const CameraPose& P, int i) const {
+    const double d0 = points3D_[3 * i] - P.m[9];
+    const double d1 = points3D_[3 * i + 1] - P.m[10];
+    const double d2 = points3D_[3 * i + 2] - P.m[11];
+    const double pz = P.m[2] * d0 + P.m[5] * d1 + P.m[8] * d2;
+    if (pz < 0.0) return std::numeric_limits<double>::max();
+    const double px = P.m[0] * d0 + P.m[3] * d1 + P.m[6] * d2;
+    const double py = P.m[1] * d0 + P.m[4] * d1 + P.m[7] * d2;
+    const double du = (px / pz) * focal_x_ - points2D_[2 * i];
+    const double dv = (py / pz) * focal_y_ - points2D_[2 * i + 1];
+    return du * du + dv * dv;
+  }
+
+  // .cc:170-212
+  void LeastSquares(const std::vector<int>& sample, CameraPose* pose) const {
+    double R[9];
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) R[3 * r + c] = (*pose)(r, c);
+    double cam[6];
+    refine::RotationToAngleAxis(R, cam);
+    cam[3] = pose->m[9];
+    cam[4] = pose->m[10];
+    cam[5] = pose->m[11];
+    if (!refine::RefinePose(static_cast<int>(sample.size()), sample.data(), points2D_.data(),
+                            points3D_.data(), focal_x_, focal_y_, cam))
+      return;
+    refine::AngleAxisToRotation(cam, R);
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) (*pose)(r, c) = R[3 * r + c];
+    pose->m[9] = cam[3];
+    pose->m[10] = cam[4];
+    pose->m[11] = cam[5];
+  }
+
+  // ---- GPU opt-in ----
+  const gpu::DeviceScorer& device_scorer() const { return scorer_; }
+  gpu::DeviceScorer& device_scorer() { return scorer_; }
+  int device_minimal_solver() const { return 0; }
+  double device_minimal_solver_threshold() const { return squared_inlier_threshold_; }
+  static void PackModel(const CameraPose& P, double* out) {
+    for (int i = 0; i < 12; ++i) out[i] = P.m[i];
+  }
+  static void UnpackModel(const double* in, CameraPose* P) {
+    for (int i = 0; i < 12; ++i) P->m[i] = in[i];
+  }
+
+  double focal_x() const { return focal_x_; }
+  double focal_y() const { return focal_y_; }
+
+ protected:
+  double focal_x_, focal_y_, squared_inlier_threshold_;
+  std::vector<double> points2D_, points3D_;
+  int num_data_;
+  gpu::DeviceScorer scorer_;
+};
+
+}  // namespace calibrated_absolute_pose
+}  // namespace ransac_lib
+
+#endif  // RANSACLIB_B200_EXAMPLES_CALIBRATED_ABSOLUTE_POSE_ESTIMATOR_H_

@@ -1,0 +1,286 @@
+// C entry points over the drop-in template layer (include/RansacLib/*.h) instantiated with
+// the three example solvers. This is what the Python mirror (ransaclib_b200/host.py,
+// ransaclib_b200/pyransaclib.py) binds; C++ users include the headers directly, exactly as
+// they include the reference's (examples/line_estimation.cc:133-143,
+// camera_pose_estimation.cc:172-192, hybrid_line_estimation.cc:175-186,
+// ransaclib_localization.cc:58-165).
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <exception>
+#include <string>
+
+#include <RansacLib/hybrid_ransac.h>
+#include <RansacLib/ransac.h>
+
+#include "calibrated_absolute_pose_estimator.h"
+#include "hybrid_line_estimator.h"
+#include "line_estimator.h"
+
+using namespace ransac_lib;
+using calibrated_absolute_pose::CalibratedAbsolutePoseEstimator;
+using calibrated_absolute_pose::CameraPose;
+using calibrated_absolute_pose::CameraPoses;
+
+extern "C" {
+
+struct rlbh_options {
+  uint32_t min_iters, max_iters;
+  double success_prob;
+  double sq_thr;
+  uint32_t seed;
+  int32_t lo_steps;
+  double thr_mult;
+  int32_t lsq_iters;
+  int32_t min_sample_mult;
+  int32_t non_min_sample_mult;
+  uint32_t lo_start;
+  int32_t final_lsq;
+};
+
+struct rlbh_stats {
+  uint32_t num_iterations;
+  int32_t best_num_inliers;
+  double best_model_score;
+  double inlier_ratio;
+  int32_t number_lo_iterations;
+  int32_t found;
+  // driver counters (not in the reference)
+  uint64_t batches, hypotheses_scored, single_passes;
+  double seconds;  // wall time of EstimateModel
+};
+
+struct rlbh_hybrid_options {
+  uint32_t min_iters, max_iters, max_iters_per_solver;
+  double success_prob;
+  double sq_thr[2];
+  double weights[2];
+  uint32_t seed;
+  int32_t lo_steps;
+  double thr_mult;
+  int32_t lsq_iters;
+  int32_t min_sample_mult;
+  uint32_t lo_start;
+  int32_t final_lsq;
+};
+
+struct rlbh_hybrid_stats {
+  uint32_t num_iterations_total;
+  uint32_t num_iterations_per_solver[2];
+  int32_t best_num_inliers;
+  int32_t best_solver_type;
+  double best_model_score;
+  double inlier_ratios[2];
+  int32_t num_inliers_per_type[2];
+  int32_t number_lo_iterations;
+};
+
+}  // extern "C"
+
+namespace {
+
+thread_local std::string g_error;
+
+LORansacOptions ToOptions(const rlbh_options& o) {
+  LORansacOptions r;
+  r.min_num_iterations_ = o.min_iters;
+  r.max_num_iterations_ = o.max_iters;
+  r.success_probability_ = o.success_prob;
+  r.squared_inlier_threshold_ = o.sq_thr;
+  r.random_seed_ = o.seed;
+  r.num_lo_steps_ = o.lo_steps;
+  r.threshold_multiplier_ = o.thr_mult;
+  r.num_lsq_iterations_ = o.lsq_iters;
+  r.min_sample_multiplicator_ = o.min_sample_mult;
+  r.non_min_sample_multiplier_ = o.non_min_sample_mult;
+  r.lo_starting_iterations_ = o.lo_start;
+  r.final_least_squares_ = o.final_lsq != 0;
+  return r;
+}
+
+template <class Model, class ModelVector, class Solver>
+void Run(const rlbh_options& o, Solver& solver, int precision, Model* model, rlbh_stats* st,
+         int32_t* inliers) {
+  if (precision >= 0) solver.device_scorer().set_precision(precision);
+  LocallyOptimizedMSAC<Model, ModelVector, Solver> lomsac;
+  GpuRunCounters counters;
+  lomsac.counters = &counters;
+  RansacStatistics rs;
+  const auto t0 = std::chrono::steady_clock::now();
+  lomsac.EstimateModel(ToOptions(o), solver, model, &rs);
+  const auto t1 = std::chrono::steady_clock::now();
+  st->num_iterations = rs.num_iterations;
+  st->best_num_inliers = rs.best_num_inliers;
+  st->best_model_score = rs.best_model_score;
+  st->inlier_ratio = rs.inlier_ratio;
+  st->number_lo_iterations = rs.number_lo_iterations;
+  st->found = rs.best_model_score < std::numeric_limits<double>::max() ? 1 : 0;
+  st->batches = counters.batches;
+  st->hypotheses_scored = counters.hypotheses_scored;
+  st->single_passes = counters.single_passes;
+  st->seconds = std::chrono::duration<double>(t1 - t0).count();
+  if (inliers)
+    for (size_t i = 0; i < rs.inlier_indices.size(); ++i) inliers[i] = rs.inlier_indices[i];
+}
+
+template <class F>
+int Guard(F f) {
+  try {
+    f();
+    return 0;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return -1;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rlbh_last_error(void) { return g_error.c_str(); }
+
+// precision: RLB_F64 / RLB_F32, or -1 for the default (env RLB_PRECISION, else f64).
+int rlbh_lomsac_line(const rlbh_options* o, int device, int precision, int n, const double* xy,
+                     double* model, rlbh_stats* st, int32_t* inliers) {
+  return Guard([&] {
+    LineEstimator solver(n, xy, &gpu::Context::ThreadDefault(device));
+    Run<Line2D, Lines2D, LineEstimator>(*o, solver, precision, reinterpret_cast<Line2D*>(model), st,
+                                        inliers);
+  });
+}
+
+int rlbh_lomsac_pose(const rlbh_options* o, int device, int precision, double fx, double fy, int n,
+                     const double* p2d, const double* p3d, double* model, rlbh_stats* st,
+                     int32_t* inliers) {
+  return Guard([&] {
+    CalibratedAbsolutePoseEstimator solver(fx, fy, o->sq_thr, n, p2d, p3d,
+                                           &gpu::Context::ThreadDefault(device));
+    Run<CameraPose, CameraPoses, CalibratedAbsolutePoseEstimator>(
+        *o, solver, precision, reinterpret_cast<CameraPose*>(model), st, inliers);
+  });
+}
+
+int rlbh_hybrid_lomsac_line(const rlbh_hybrid_options* o, int device, int precision, int n0,
+                            const double* xy0, int n1, const double* xynn1, const double* priors,
+                            double* model, rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
+  return Guard([&] {
+    HybridLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]},
+                               &gpu::Context::ThreadDefault(device));
+    if (precision >= 0) solver.device_scorer().set_precision(precision);
+    HybridLORansacOptions ho;
+    ho.min_num_iterations_ = o->min_iters;
+    ho.max_num_iterations_ = o->max_iters;
+    ho.max_num_iterations_per_solver_ = o->max_iters_per_solver;
+    ho.success_probability_ = o->success_prob;
+    ho.squared_inlier_thresholds_ = {o->sq_thr[0], o->sq_thr[1]};
+    ho.data_type_weights_ = {o->weights[0], o->weights[1]};
+    ho.random_seed_ = o->seed;
+    ho.num_lo_steps_ = o->lo_steps;
+    ho.threshold_multiplier_ = o->thr_mult;
+    ho.num_lsq_iterations_ = o->lsq_iters;
+    ho.min_sample_multiplicator_ = o->min_sample_mult;
+    ho.lo_starting_iterations_ = o->lo_start;
+    ho.final_least_squares_ = o->final_lsq != 0;
+    HybridLocallyOptimizedMSAC<Line2D, Lines2D, HybridLineEstimator> lomsac;
+    HybridRansacStatistics hs;
+    lomsac.EstimateModel(ho, solver, reinterpret_cast<Line2D*>(model), &hs);
+    st->num_iterations_total = hs.num_iterations_total;
+    for (int i = 0; i < 2; ++i) {
+      st->num_iterations_per_solver[i] = hs.num_iterations_per_solver[i];
+      st->inlier_ratios[i] = hs.inlier_ratios[i];
+      st->num_inliers_per_type[i] = static_cast<int32_t>(hs.inlier_indices[i].size());
+    }
+    st->best_num_inliers = hs.best_num_inliers;
+    st->best_solver_type = hs.best_solver_type;
+    st->best_model_score = hs.best_model_score;
+    st->number_lo_iterations = hs.number_lo_iterations;
+    if (inl0) std::copy(hs.inlier_indices[0].begin(), hs.inlier_indices[0].end(), inl0);
+    if (inl1) std::copy(hs.inlier_indices[1].begin(), hs.inlier_indices[1].end(), inl1);
+  });
+}
+
+// pyransaclib.ransaclib_localization (reference examples/ransaclib_localization.cc:58-165):
+// float focals / threshold, fixed options (:100-107), [R|c] -> (qvec w,x,y,z ; tvec = -R c)
+// (:147-150). The reference seeds from std::random_device (:109-110); here the seed is an
+// argument so runs are reproducible. Returns 1 on success, 0 for <= 3 matches (:86-92).
+int rlbh_localize(int device, int precision, float focal_x, float focal_y, int n, const double* p2d,
+                  const double* p3d, float inlier_threshold, int number_lo_steps,
+                  uint32_t min_num_iterations, uint32_t max_num_iterations, uint32_t seed,
+                  double* qvec, double* tvec, int32_t* num_inliers, int32_t* inliers,
+                  rlbh_stats* st) {
+  if (n <= 3) return 0;
+  int success = 0;
+  const int rc = Guard([&] {
+    rlbh_options o;
+    o.min_iters = min_num_iterations;
+    o.max_iters = max_num_iterations;
+    o.success_prob = 0.9999;
+    const double thr_px = static_cast<double>(inlier_threshold);
+    o.sq_thr = thr_px * thr_px;
+    o.seed = seed;
+    o.lo_steps = number_lo_steps;
+    o.thr_mult = std::sqrt(2.0);
+    o.lsq_iters = 4;
+    o.min_sample_mult = 7;
+    o.non_min_sample_mult = 3;
+    o.lo_start = 60;
+    o.final_lsq = 1;
+    CalibratedAbsolutePoseEstimator solver(focal_x, focal_y, o.sq_thr, n, p2d, p3d,
+                                           &gpu::Context::ThreadDefault(device));
+    CameraPose best;
+    std::memset(&best, 0, sizeof(best));
+    rlbh_stats local;
+    Run<CameraPose, CameraPoses, CalibratedAbsolutePoseEstimator>(o, solver, precision, &best,
+                                                                  st ? st : &local, inliers);
+    const rlbh_stats& s = st ? *st : local;
+    *num_inliers = s.best_num_inliers;
+    // t = -R c
+    for (int r = 0; r < 3; ++r)
+      tvec[r] = -(best(r, 0) * best.m[9] + best(r, 1) * best.m[10] + best(r, 2) * best.m[11]);
+    // Quaternion of R (Eigen::Quaterniond(R), then normalize()).
+    double R[9];
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) R[3 * r + c] = best(r, c);
+    double w, x, y, z;
+    const double trace = R[0] + R[4] + R[8];
+    if (trace > 0.0) {
+      double t = std::sqrt(trace + 1.0);
+      w = 0.5 * t;
+      t = 0.5 / t;
+      x = (R[7] - R[5]) * t;
+      y = (R[2] - R[6]) * t;
+      z = (R[3] - R[1]) * t;
+    } else {
+      int i = 0;
+      if (R[4] > R[0]) i = 1;
+      if (R[8] > R[4 * i]) i = 2;
+      const int j = (i + 1) % 3, k = (j + 1) % 3;
+      double t = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
+      double q[3];
+      q[i] = 0.5 * t;
+      t = 0.5 / t;
+      w = (R[3 * k + j] - R[3 * j + k]) * t;
+      q[j] = (R[3 * j + i] + R[3 * i + j]) * t;
+      q[k] = (R[3 * k + i] + R[3 * i + k]) * t;
+      x = q[0];
+      y = q[1];
+      z = q[2];
+    }
+    const double nq = std::sqrt(w * w + x * x + y * y + z * z);
+    if (nq > 0.0) {
+      w /= nq;
+      x /= nq;
+      y /= nq;
+      z /= nq;
+    }
+    qvec[0] = w;
+    qvec[1] = x;
+    qvec[2] = y;
+    qvec[3] = z;
+    success = 1;
+  });
+  return rc == 0 ? success : -1;
+}
+
+}  // extern "C"

@@ -1,0 +1,315 @@
+// Host-side non-linear pose refinement for CalibratedAbsolutePoseEstimator::LeastSquares.
+//
+// The reference builds a Ceres problem (AutoDiffCostFunction<ReprojectionError,2,6>,
+// DENSE_QR, default Levenberg-Marquardt; examples/calibrated_absolute_pose_estimator.cc:43-97,
+// 170-212). Ceres and Eigen are not available in this image, so this file carries a small
+// dense LM over the same 6 parameters (angle-axis, camera centre), the same residual and
+// forward-mode derivatives, and Ceres' default trust-region constants. It stays on the
+// host by design (north_star: "Local optimisation keeps its least-squares refinement on
+// the host, but all of its rescoring goes through the GPU scorer").
+#ifndef RANSACLIB_B200_EXAMPLES_POSE_REFINEMENT_H_
+#define RANSACLIB_B200_EXAMPLES_POSE_REFINEMENT_H_
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <limits>
+
+namespace ransac_lib {
+namespace calibrated_absolute_pose {
+namespace refine {
+
+// Row-major rotation -> angle-axis through the quaternion, as Eigen::AngleAxisd(Matrix3d)
+// does (calibrated_absolute_pose_estimator.cc:172-173).
+inline void RotationToAngleAxis(const double* R, double* aa) {
+  double w, x, y, z;
+  const double trace = R[0] + R[4] + R[8];
+  if (trace > 0.0) {
+    double t = std::sqrt(trace + 1.0);
+    w = 0.5 * t;
+    t = 0.5 / t;
+    x = (R[7] - R[5]) * t;
+    y = (R[2] - R[6]) * t;
+    z = (R[3] - R[1]) * t;
+  } else {
+    int i = 0;
+    if (R[4] > R[0]) i = 1;
+    if (R[8] > R[4 * i]) i = 2;
+    const int j = (i + 1) % 3, k = (j + 1) % 3;
+    double t = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
+    double q[3];
+    q[i] = 0.5 * t;
+    t = 0.5 / t;
+    w = (R[3 * k + j] - R[3 * j + k]) * t;
+    q[j] = (R[3 * j + i] + R[3 * i + j]) * t;
+    q[k] = (R[3 * k + i] + R[3 * i + k]) * t;
+    x = q[0];
+    y = q[1];
+    z = q[2];
+  }
+  double n = std::sqrt(x * x + y * y + z * z);
+  if (n < DBL_MIN) {
+    aa[0] = aa[1] = aa[2] = 0.0;
+    return;
+  }
+  if (w < 0.0) n = -n;
+  const double angle = 2.0 * std::atan2(n, std::fabs(w));
+  aa[0] = x / n * angle;
+  aa[1] = y / n * angle;
+  aa[2] = z / n * angle;
+}
+
+// Angle-axis -> row-major rotation (Rodrigues; .cc:204-210).
+inline void AngleAxisToRotation(const double* aa, double* R) {
+  const double angle = std::sqrt(aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2]);
+  double ax = aa[0], ay = aa[1], az = aa[2];
+  if (angle > 0.0) {
+    ax /= angle;
+    ay /= angle;
+    az /= angle;
+  }
+  const double s = std::sin(angle), c = std::cos(angle);
+  const double tx = (1.0 - c) * ax, ty = (1.0 - c) * ay, tz = (1.0 - c) * az;
+  const double sx = s * ax, sy = s * ay, sz = s * az;
+  R[0] = tx * ax + c;
+  R[1] = tx * ay - sz;
+  R[2] = tx * az + sy;
+  R[3] = tx * ay + sz;
+  R[4] = ty * ay + c;
+  R[5] = ty * az - sx;
+  R[6] = tx * az - sy;
+  R[7] = ty * az + sx;
+  R[8] = tz * az + c;
+}
+
+// Value + 6 partial derivatives (the role ceres::Jet<double,6> plays in the reference).
+struct Dual {
+  double a;
+  double d[6];
+  static Dual Constant(double v) {
+    Dual r;
+    r.a = v;
+    for (int i = 0; i < 6; ++i) r.d[i] = 0.0;
+    return r;
+  }
+  static Dual Variable(double v, int k) {
+    Dual r = Constant(v);
+    r.d[k] = 1.0;
+    return r;
+  }
+};
+inline Dual operator+(const Dual& x, const Dual& y) {
+  Dual r;
+  r.a = x.a + y.a;
+  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] + y.d[i];
+  return r;
+}
+inline Dual operator-(const Dual& x, const Dual& y) {
+  Dual r;
+  r.a = x.a - y.a;
+  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] - y.d[i];
+  return r;
+}
+inline Dual operator*(const Dual& x, const Dual& y) {
+  Dual r;
+  r.a = x.a * y.a;
+  for (int i = 0; i < 6; ++i) r.d[i] = x.a * y.d[i] + x.d[i] * y.a;
+  return r;
+}
+inline Dual operator/(const Dual& x, const Dual& y) {
+  Dual r;
+  const double inv = 1.0 / y.a;
+  r.a = x.a * inv;
+  for (int i = 0; i < 6; ++i) r.d[i] = (x.d[i] - r.a * y.d[i]) * inv;
+  return r;
+}
+inline Dual Sqrt(const Dual& x) {
+  Dual r;
+  r.a = std::sqrt(x.a);
+  const double g = 0.5 / r.a;
+  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] * g;
+  return r;
+}
+inline Dual Sin(const Dual& x) {
+  Dual r;
+  r.a = std::sin(x.a);
+  const double g = std::cos(x.a);
+  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] * g;
+  return r;
+}
+inline Dual Cos(const Dual& x) {
+  Dual r;
+  r.a = std::cos(x.a);
+  const double g = -std::sin(x.a);
+  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] * g;
+  return r;
+}
+
+// ReprojectionError::operator() (.cc:55-74) with ceres::AngleAxisRotatePoint's two branches.
+inline void Residual(const Dual* cam, double u, double v, double X, double Y, double Z, double fx,
+                     double fy, Dual* res) {
+  const Dual one = Dual::Constant(1.0);
+  Dual p[3] = {Dual::Constant(X) - cam[3], Dual::Constant(Y) - cam[4], Dual::Constant(Z) - cam[5]};
+  Dual q[3];
+  const Dual theta2 = cam[0] * cam[0] + cam[1] * cam[1] + cam[2] * cam[2];
+  if (theta2.a > std::numeric_limits<double>::epsilon()) {
+    const Dual theta = Sqrt(theta2);
+    const Dual ct = Cos(theta), st = Sin(theta);
+    const Dual inv = one / theta;
+    const Dual w[3] = {cam[0] * inv, cam[1] * inv, cam[2] * inv};
+    const Dual wxp[3] = {w[1] * p[2] - w[2] * p[1], w[2] * p[0] - w[0] * p[2],
+                         w[0] * p[1] - w[1] * p[0]};
+    const Dual tmp = (w[0] * p[0] + w[1] * p[1] + w[2] * p[2]) * (one - ct);
+    for (int i = 0; i < 3; ++i) q[i] = p[i] * ct + wxp[i] * st + w[i] * tmp;
+  } else {
+    const Dual wxp[3] = {cam[1] * p[2] - cam[2] * p[1], cam[2] * p[0] - cam[0] * p[2],
+                         cam[0] * p[1] - cam[1] * p[0]};
+    for (int i = 0; i < 3; ++i) q[i] = p[i] + wxp[i];
+  }
+  const Dual xp = Dual::Constant(fx) * q[0] / q[2];
+  const Dual yp = Dual::Constant(fy) * q[1] / q[2];
+  res[0] = Dual::Constant(u) - xp;
+  res[1] = Dual::Constant(v) - yp;
+}
+
+inline bool SolveSpd6(const double* A, const double* b, double* x) {
+  double L[36];
+  for (int i = 0; i < 6; ++i) {
+    for (int j = 0; j <= i; ++j) {
+      double s = A[6 * i + j];
+      for (int k = 0; k < j; ++k) s -= L[6 * i + k] * L[6 * j + k];
+      if (i == j) {
+        if (!(s > 0.0)) return false;
+        L[6 * i + i] = std::sqrt(s);
+      } else {
+        L[6 * i + j] = s / L[6 * j + j];
+      }
+    }
+  }
+  double y[6];
+  for (int i = 0; i < 6; ++i) {
+    double s = b[i];
+    for (int k = 0; k < i; ++k) s -= L[6 * i + k] * y[k];
+    y[i] = s / L[6 * i + i];
+  }
+  for (int i = 5; i >= 0; --i) {
+    double s = y[i];
+    for (int k = i + 1; k < 6; ++k) s -= L[6 * k + i] * x[k];
+    x[i] = s / L[6 * i + i];
+  }
+  return true;
+}
+
+// Cost, J^T J and J^T r over the sample.
+inline double Linearise(int k, const int* idx, const double* p2d, const double* p3d, double fx,
+                        double fy, const double* c, double* JtJ, double* Jtr) {
+  Dual cam[6];
+  for (int i = 0; i < 6; ++i) cam[i] = Dual::Variable(c[i], i);
+  double cost = 0.0;
+  if (JtJ) {
+    for (int i = 0; i < 36; ++i) JtJ[i] = 0.0;
+    for (int i = 0; i < 6; ++i) Jtr[i] = 0.0;
+  }
+  for (int s = 0; s < k; ++s) {
+    const int i = idx[s];
+    Dual r[2];
+    Residual(cam, p2d[2 * i], p2d[2 * i + 1], p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2], fx, fy, r);
+    cost += 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
+    if (JtJ) {
+      for (int e = 0; e < 2; ++e) {
+        for (int a = 0; a < 6; ++a) {
+          Jtr[a] += r[e].d[a] * r[e].a;
+          for (int b = 0; b <= a; ++b) JtJ[6 * a + b] += r[e].d[a] * r[e].d[b];
+        }
+      }
+    }
+  }
+  if (JtJ) {
+    for (int a = 0; a < 6; ++a)
+      for (int b = a + 1; b < 6; ++b) JtJ[6 * a + b] = JtJ[6 * b + a];
+  }
+  return cost;
+}
+
+// Levenberg-Marquardt with Ceres' defaults: initial radius 1e4, at most 50 iterations,
+// function tolerance 1e-6, gradient tolerance 1e-10, parameter tolerance 1e-8, minimum
+// relative decrease 1e-3, diagonal scaling clamped to [1e-6, 1e32]. Returns false when the
+// result is not usable (non-finite), like !summary.IsSolutionUsable() (.cc:202).
+inline bool RefinePose(int k, const int* idx, const double* p2d, const double* p3d, double fx,
+                       double fy, double* cam) {
+  double x[6];
+  for (int i = 0; i < 6; ++i) x[i] = cam[i];
+  double JtJ[36], g[6];
+  double cost = Linearise(k, idx, p2d, p3d, fx, fy, x, JtJ, g);
+  if (!(cost == cost) || cost > DBL_MAX) return false;
+  double radius = 1e4;
+  double shrink = 2.0;
+  for (int iter = 0; iter < 50; ++iter) {
+    double gmax = 0.0;
+    for (int i = 0; i < 6; ++i) gmax = std::max(gmax, std::fabs(g[i]));
+    if (gmax <= 1e-10) break;
+    double A[36], rhs[6], step[6];
+    for (int i = 0; i < 36; ++i) A[i] = JtJ[i];
+    for (int i = 0; i < 6; ++i) {
+      double dgl = JtJ[7 * i];
+      dgl = std::min(std::max(dgl, 1e-6), 1e32);
+      A[7 * i] += dgl / radius;
+      rhs[i] = -g[i];
+    }
+    bool ok = SolveSpd6(A, rhs, step);
+    double model_decrease = 0.0;
+    if (ok) {
+      double gs = 0.0, sJs = 0.0;
+      for (int i = 0; i < 6; ++i) {
+        gs += g[i] * step[i];
+        double t = 0.0;
+        for (int j = 0; j < 6; ++j) t += JtJ[6 * i + j] * step[j];
+        sJs += step[i] * t;
+      }
+      model_decrease = -(gs + 0.5 * sJs);
+      ok = model_decrease > 0.0;
+    }
+    if (!ok) {
+      radius /= shrink;
+      shrink *= 2.0;
+      if (radius < 1e-32) break;
+      continue;
+    }
+    double xn[6], sn = 0.0, xnorm = 0.0;
+    for (int i = 0; i < 6; ++i) {
+      xn[i] = x[i] + step[i];
+      sn += step[i] * step[i];
+      xnorm += x[i] * x[i];
+    }
+    sn = std::sqrt(sn);
+    xnorm = std::sqrt(xnorm);
+    if (sn <= 1e-8 * (xnorm + 1e-8)) break;
+    const double cost_new = Linearise(k, idx, p2d, p3d, fx, fy, xn, nullptr, nullptr);
+    const double rho = (cost - cost_new) / model_decrease;
+    if (cost_new == cost_new && rho > 1e-3) {
+      const double delta = cost - cost_new;
+      for (int i = 0; i < 6; ++i) x[i] = xn[i];
+      const double prev = cost;
+      cost = Linearise(k, idx, p2d, p3d, fx, fy, x, JtJ, g);
+      const double t = 2.0 * rho - 1.0;
+      radius = radius / std::max(1.0 / 3.0, 1.0 - t * t * t);
+      radius = std::min(radius, 1e16);
+      shrink = 2.0;
+      if (std::fabs(delta) <= 1e-6 * prev) break;
+    } else {
+      radius /= shrink;
+      shrink *= 2.0;
+      if (radius < 1e-32) break;
+    }
+  }
+  for (int i = 0; i < 6; ++i)
+    if (!(x[i] - x[i] == 0.0)) return false;
+  for (int i = 0; i < 6; ++i) cam[i] = x[i];
+  return true;
+}
+
+}  // namespace refine
+}  // namespace calibrated_absolute_pose
+}  // namespace ransac_lib
+
+#endif  // RANSACLIB_B200_EXAMPLES_POSE_REFINEMENT_H_

@@ -1,0 +1,161 @@
+// ransaclib_b200 — C++ convenience layer over the C ABI (include/ransaclib_b200.h) and
+// the opt-in protocol by which a Solver hands its data set to the GPU scorer.
+//
+// A solver opts in by exposing
+//     const ransac_lib::gpu::DeviceScorer& device_scorer() const;
+//     static void PackModel(const Model&, double* out);     // model_size doubles
+//     static void UnpackModel(const double* in, Model* m);
+// and, optionally, a device-side batched minimal solver:
+//     int device_minimal_solver() const;           // solver id for rlb_hypothesize_and_score
+//     double device_minimal_solver_threshold() const;   // P3P's 4th-point threshold
+// Solvers that do not opt in do not compile against LocallyOptimizedMSAC: there is no
+// CPU scoring path in this library.
+#ifndef RANSACLIB_B200_RANSACLIB_GPU_SCORER_H_
+#define RANSACLIB_B200_RANSACLIB_GPU_SCORER_H_
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <limits>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include "../ransaclib_b200.h"
+
+namespace ransac_lib {
+namespace gpu {
+
+// Failures of the device path are loud: the reference's API has no error channel
+// (EstimateModel returns an inlier count), and silently returning 0 would look like
+// "no model found".
+inline void Check(int rc, const char* what) {
+  if (rc != RLB_OK) {
+    std::string msg = std::string("ransaclib_b200: ") + what + " failed: " + rlb_last_error();
+    throw std::runtime_error(msg);
+  }
+}
+
+class Context {
+ public:
+  explicit Context(int device = 0) { Check(rlb_ctx_create(device, &ctx_), "rlb_ctx_create"); }
+  ~Context() { rlb_ctx_destroy(ctx_); }
+  Context(const Context&) = delete;
+  Context& operator=(const Context&) = delete;
+  rlb_ctx* get() const { return ctx_; }
+  // One lazily created context per host thread and device (contexts are not thread-safe).
+  static Context& ThreadDefault(int device = 0) {
+    thread_local std::vector<std::unique_ptr<Context>> per_device;
+    if (static_cast<int>(per_device.size()) <= device) per_device.resize(device + 1);
+    if (!per_device[device]) per_device[device].reset(new Context(device));
+    return *per_device[device];
+  }
+
+ private:
+  rlb_ctx* ctx_ = nullptr;
+};
+
+inline int PrecisionFromEnv() {
+  const char* p = std::getenv("RLB_PRECISION");
+  return (p && (p[0] == 'f' || p[0] == 'F') && p[1] == '3') ? RLB_F32 : RLB_F64;
+}
+
+// Owns one rlb_scorer (a data set resident in HBM).
+class DeviceScorer {
+ public:
+  DeviceScorer() = default;
+  ~DeviceScorer() { reset(); }
+  DeviceScorer(const DeviceScorer&) = delete;
+  DeviceScorer& operator=(const DeviceScorer&) = delete;
+  DeviceScorer(DeviceScorer&& o) noexcept : s_(o.s_), precision_(o.precision_) { o.s_ = nullptr; }
+  DeviceScorer& operator=(DeviceScorer&& o) noexcept {
+    if (this != &o) {
+      reset();
+      s_ = o.s_;
+      precision_ = o.precision_;
+      o.s_ = nullptr;
+    }
+    return *this;
+  }
+  void reset() {
+    if (s_) rlb_scorer_destroy(s_);
+    s_ = nullptr;
+  }
+
+  void InitLine(Context& c, int n, const double* xy) {
+    reset();
+    Check(rlb_scorer_create_line(c.get(), n, xy, &s_), "rlb_scorer_create_line");
+  }
+  void InitHybridLine(Context& c, int n0, const double* xy0, int n1, const double* xynn1) {
+    reset();
+    Check(rlb_scorer_create_hybrid_line(c.get(), n0, xy0, n1, xynn1, &s_),
+          "rlb_scorer_create_hybrid_line");
+  }
+  void InitPose(Context& c, int n, const double* p2d, const double* p3d, double fx, double fy) {
+    reset();
+    Check(rlb_scorer_create_pose(c.get(), n, p2d, p3d, fx, fy, &s_), "rlb_scorer_create_pose");
+  }
+
+  bool valid() const { return s_ != nullptr; }
+  rlb_scorer* get() const { return s_; }
+  int model_size() const { return rlb_scorer_model_size(s_); }
+  int num_types() const { return rlb_scorer_num_types(s_); }
+  // Arithmetic of the K x N sweep: RLB_F64 (default) or RLB_F32 (env RLB_PRECISION=f32 or
+  // set_precision). With f32 the driver re-scores near-best hypotheses in f64, so the
+  // selected models are the same either way.
+  int precision() const { return precision_; }
+  void set_precision(int p) { precision_ = p; }
+
+  // ScoreModel for K packed models (+ optional validity mask).
+  void ScoreModels(int k, const double* models, const uint8_t* valid, const double* sq_thr,
+                   const double* weights, double* scores, int precision) const {
+    int32_t best_id;
+    double best_score;
+    Check(rlb_score_models(s_, precision, k, models, valid, sq_thr, weights, scores, nullptr,
+                           &best_id, &best_score),
+          "rlb_score_models");
+  }
+
+  // Samples in, hypotheses + scores out (device-side minimal solver).
+  void HypothesizeAndScore(int solver, int k, const int32_t* samples, const double* sq_thr,
+                           const double* weights, double* models, uint8_t* valid, double* scores,
+                           int precision) const {
+    int32_t best_id;
+    double best_score;
+    Check(rlb_hypothesize_and_score(s_, precision, solver, k, samples, sq_thr, weights, models,
+                                    valid, scores, nullptr, &best_id, &best_score, nullptr),
+          "rlb_hypothesize_and_score");
+  }
+
+  // Fused K=1 pass: inliers at sq_thr_inl (ascending, per type) and, if sq_thr_score is
+  // given, the MSAC score at sq_thr_score. idx may be null (count only).
+  void InliersAndScore(const double* model, const double* sq_thr_inl, const double* sq_thr_score,
+                       const double* weights, int32_t* idx, int32_t* counts, double* score) const {
+    Check(rlb_get_inliers(s_, model, sq_thr_inl, sq_thr_score, weights, idx, counts, score),
+          "rlb_get_inliers");
+  }
+
+ private:
+  rlb_scorer* s_ = nullptr;
+  int precision_ = PrecisionFromEnv();
+};
+
+// ---- opt-in detection ----------------------------------------------------------
+template <class S, class = void>
+struct HasDeviceScorer : std::false_type {};
+template <class S>
+struct HasDeviceScorer<S, decltype(void(std::declval<const S&>().device_scorer()))>
+    : std::true_type {};
+
+template <class S, class = void>
+struct HasDeviceMinimalSolver : std::false_type {};
+template <class S>
+struct HasDeviceMinimalSolver<S, decltype(void(std::declval<const S&>().device_minimal_solver()))>
+    : std::true_type {};
+
+}  // namespace gpu
+}  // namespace ransac_lib
+
+#endif  // RANSACLIB_B200_RANSACLIB_GPU_SCORER_H_

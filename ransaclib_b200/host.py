@@ -1,0 +1,197 @@
+"""Python mirror of the drop-in template layer: LO-MSAC / Hybrid LO-MSAC ``EstimateModel``
+for the three example solvers, executed by ``libransaclib_b200_host.so`` (include/RansacLib/*.h
+over the CUDA C ABI). Same option names as the reference's ``LORansacOptions`` /
+``HybridLORansacOptions`` (RansacLib/ransac.h:47-92, hybrid_ransac.h:47-93)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _capi
+
+_HOST_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libransaclib_b200_host.so")
+
+
+class _Options(C.Structure):
+    _fields_ = [("min_iters", C.c_uint32), ("max_iters", C.c_uint32), ("success_prob", C.c_double),
+                ("sq_thr", C.c_double), ("seed", C.c_uint32), ("lo_steps", C.c_int32),
+                ("thr_mult", C.c_double), ("lsq_iters", C.c_int32), ("min_sample_mult", C.c_int32),
+                ("non_min_sample_mult", C.c_int32), ("lo_start", C.c_uint32), ("final_lsq", C.c_int32)]
+
+
+class _Stats(C.Structure):
+    _fields_ = [("num_iterations", C.c_uint32), ("best_num_inliers", C.c_int32),
+                ("best_model_score", C.c_double), ("inlier_ratio", C.c_double),
+                ("number_lo_iterations", C.c_int32), ("found", C.c_int32), ("batches", C.c_uint64),
+                ("hypotheses_scored", C.c_uint64), ("single_passes", C.c_uint64), ("seconds", C.c_double)]
+
+
+class _HybridOptions(C.Structure):
+    _fields_ = [("min_iters", C.c_uint32), ("max_iters", C.c_uint32), ("max_iters_per_solver", C.c_uint32),
+                ("success_prob", C.c_double), ("sq_thr", C.c_double * 2), ("weights", C.c_double * 2),
+                ("seed", C.c_uint32), ("lo_steps", C.c_int32), ("thr_mult", C.c_double),
+                ("lsq_iters", C.c_int32), ("min_sample_mult", C.c_int32), ("lo_start", C.c_uint32),
+                ("final_lsq", C.c_int32)]
+
+
+class _HybridStats(C.Structure):
+    _fields_ = [("num_iterations_total", C.c_uint32), ("num_iterations_per_solver", C.c_uint32 * 2),
+                ("best_num_inliers", C.c_int32), ("best_solver_type", C.c_int32),
+                ("best_model_score", C.c_double), ("inlier_ratios", C.c_double * 2),
+                ("num_inliers_per_type", C.c_int32 * 2), ("number_lo_iterations", C.c_int32)]
+
+
+_lib = None
+
+
+def _load():
+    global _lib
+    if _lib is None:
+        _capi.load()  # the CUDA library first (the host library links against it)
+        if not os.path.exists(_HOST_PATH):
+            raise _capi.RlbError(f"{_HOST_PATH} is missing: run __graft_entry__.build()")
+        _lib = C.CDLL(_HOST_PATH)
+        _lib.rlbh_last_error.restype = C.c_char_p
+    return _lib
+
+
+def _check(rc):
+    if rc < 0:
+        raise _capi.RlbError(_load().rlbh_last_error().decode())
+
+
+class LORansacOptions:
+    """Defaults of reference ransac.h:47-92."""
+
+    def __init__(self, **kw):
+        self.min_num_iterations_ = 100
+        self.max_num_iterations_ = 10000
+        self.success_probability_ = 0.9999
+        self.squared_inlier_threshold_ = 1.0
+        self.random_seed_ = 0
+        self.num_lo_steps_ = 10
+        self.threshold_multiplier_ = 2.0 ** 0.5
+        self.num_lsq_iterations_ = 4
+        self.min_sample_multiplicator_ = 7
+        self.non_min_sample_multiplier_ = 3
+        self.lo_starting_iterations_ = 50
+        self.final_least_squares_ = False
+        for k, v in kw.items():
+            if not hasattr(self, k):
+                raise AttributeError(k)
+            setattr(self, k, v)
+
+    def _c(self):
+        return _Options(self.min_num_iterations_, self.max_num_iterations_, self.success_probability_,
+                        self.squared_inlier_threshold_, self.random_seed_, self.num_lo_steps_,
+                        self.threshold_multiplier_, self.num_lsq_iterations_, self.min_sample_multiplicator_,
+                        self.non_min_sample_multiplier_, self.lo_starting_iterations_,
+                        int(self.final_least_squares_))
+
+
+class HybridLORansacOptions:
+    """Defaults of reference hybrid_ransac.h:47-93."""
+
+    def __init__(self, **kw):
+        self.min_num_iterations_ = 100
+        self.max_num_iterations_ = 10000
+        self.max_num_iterations_per_solver_ = 10000
+        self.success_probability_ = 0.9999
+        self.squared_inlier_thresholds_ = [1.0, 1.0]
+        self.data_type_weights_ = [1.0, 1.0]
+        self.random_seed_ = 0
+        self.num_lo_steps_ = 10
+        self.threshold_multiplier_ = 2.0 ** 0.5
+        self.num_lsq_iterations_ = 4
+        self.min_sample_multiplicator_ = 7
+        self.lo_starting_iterations_ = 50
+        self.final_least_squares_ = False
+        for k, v in kw.items():
+            if not hasattr(self, k):
+                raise AttributeError(k)
+            setattr(self, k, v)
+
+    def _c(self):
+        return _HybridOptions(self.min_num_iterations_, self.max_num_iterations_,
+                              self.max_num_iterations_per_solver_, self.success_probability_,
+                              (C.c_double * 2)(*self.squared_inlier_thresholds_),
+                              (C.c_double * 2)(*self.data_type_weights_), self.random_seed_, self.num_lo_steps_,
+                              self.threshold_multiplier_, self.num_lsq_iterations_,
+                              self.min_sample_multiplicator_, self.lo_starting_iterations_,
+                              int(self.final_least_squares_))
+
+
+def _stats_dict(st, inliers):
+    return {"num_iterations": st.num_iterations, "best_num_inliers": st.best_num_inliers,
+            "best_model_score": st.best_model_score, "inlier_ratio": st.inlier_ratio,
+            "number_lo_iterations": st.number_lo_iterations, "found": bool(st.found),
+            "inlier_indices": inliers[:st.best_num_inliers].copy(), "batches": st.batches,
+            "hypotheses_scored": st.hypotheses_scored, "single_passes": st.single_passes,
+            "seconds": st.seconds}
+
+
+def estimate_line(options: LORansacOptions, xy, device=0, precision=-1):
+    """LocallyOptimizedMSAC<Line, ., LineEstimator>::EstimateModel -> (model[3], stats)."""
+    xy = _capi.f64a(xy, (-1, 2))
+    o, st = options._c(), _Stats()
+    model = np.zeros(3)
+    inl = np.zeros(max(len(xy), 1), np.int32)
+    _check(_load().rlbh_lomsac_line(C.byref(o), device, precision, len(xy), _capi.ptr(xy), _capi.ptr(model),
+                                    C.byref(st), _capi.ptr(inl)))
+    return model, _stats_dict(st, inl)
+
+
+def estimate_pose(options: LORansacOptions, fx, fy, points2D, points3D, device=0, precision=-1):
+    """LocallyOptimizedMSAC<CameraPose, ., CalibratedAbsolutePoseEstimator>::EstimateModel."""
+    p2 = _capi.f64a(points2D, (-1, 2))
+    p3 = _capi.f64a(points3D, (-1, 3))
+    o, st = options._c(), _Stats()
+    model = np.zeros(12)
+    inl = np.zeros(max(len(p2), 1), np.int32)
+    _check(_load().rlbh_lomsac_pose(C.byref(o), device, precision, C.c_double(fx), C.c_double(fy), len(p2),
+                                    _capi.ptr(p2), _capi.ptr(p3), _capi.ptr(model), C.byref(st), _capi.ptr(inl)))
+    return model, _stats_dict(st, inl)
+
+
+def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, device=0, precision=-1):
+    """HybridLocallyOptimizedMSAC<Line, ., HybridLineEstimator>::EstimateModel."""
+    xy0 = _capi.f64a(xy0, (-1, 2))
+    p1 = _capi.f64a(xynn1, (-1, 4))
+    pr = _capi.f64a(priors, (2,))
+    o, st = options._c(), _HybridStats()
+    model = np.zeros(3)
+    a = np.zeros(max(len(xy0), 1), np.int32)
+    b = np.zeros(max(len(p1), 1), np.int32)
+    _check(_load().rlbh_hybrid_lomsac_line(C.byref(o), device, precision, len(xy0), _capi.ptr(xy0), len(p1),
+                                           _capi.ptr(p1), _capi.ptr(pr), _capi.ptr(model), C.byref(st),
+                                           _capi.ptr(a), _capi.ptr(b)))
+    return model, {
+        "num_iterations_total": st.num_iterations_total,
+        "num_iterations_per_solver": list(st.num_iterations_per_solver),
+        "best_num_inliers": st.best_num_inliers, "best_solver_type": st.best_solver_type,
+        "best_model_score": st.best_model_score, "inlier_ratios": list(st.inlier_ratios),
+        "number_lo_iterations": st.number_lo_iterations,
+        "inlier_indices": [a[:st.num_inliers_per_type[0]].copy(), b[:st.num_inliers_per_type[1]].copy()]}
+
+
+def localize(focal_x, focal_y, points2D, points3D, inlier_threshold, number_lo_steps, min_num_iterations,
+             max_num_iterations, random_seed=0, device=0, precision=-1):
+    """Core of pyransaclib.ransaclib_localization -> dict (see ransaclib_b200/pyransaclib.py)."""
+    p2 = _capi.f64a(points2D, (-1, 2))
+    p3 = _capi.f64a(points3D, (-1, 3))
+    n = len(p2)
+    q, t = np.zeros(4), np.zeros(3)
+    ninl = C.c_int32()
+    inl = np.zeros(max(n, 1), np.int32)
+    st = _Stats()
+    rc = _load().rlbh_localize(device, precision, C.c_float(focal_x), C.c_float(focal_y), n, _capi.ptr(p2),
+                               _capi.ptr(p3), C.c_float(inlier_threshold), int(number_lo_steps),
+                               int(min_num_iterations), int(max_num_iterations), int(random_seed), _capi.ptr(q),
+                               _capi.ptr(t), C.byref(ninl), _capi.ptr(inl), C.byref(st))
+    _check(rc)
+    if rc == 0:
+        return {"success": False}
+    return {"success": True, "qvec": q, "tvec": t, "num_inliers": int(ninl.value),
+            "inliers": inl[:ninl.value].tolist(), "_stats": _stats_dict(st, inl)}

@@ -1,0 +1,44 @@
+"""Drop-in for the reference's Python module ``pyransaclib`` (examples/pyransaclib.cc:38-46,
+examples/ransaclib_localization.cc:58-165): same function name, keyword arguments and result
+dictionary. Usage:  ``from ransaclib_b200 import pyransaclib``.
+
+Additions allowed by the survey: an optional trailing ``random_seed`` (the reference seeds from
+std::random_device, ransaclib_localization.cc:109-110, so it is not reproducible) and the batched
+sibling ``ransaclib_localization_batch``.
+"""
+from __future__ import annotations
+
+from . import host
+
+
+def ransaclib_localization(query_name, focal_x, focal_y, points2D_vec, points3D_vec, inlier_threshold,
+                           number_lo_steps, min_num_iterations, max_num_iterations, random_seed=None,
+                           device=0):
+    """Absolute pose estimation with non-linear refinement.
+
+    Returns ``{"success": False}`` for <= 3 matches, else ``{"success", "qvec" [w,x,y,z], "tvec",
+    "num_inliers", "inliers"}`` (ransaclib_localization.cc:86-92,157-162)."""
+    if random_seed is None:
+        import random
+
+        random_seed = random.SystemRandom().getrandbits(32)
+    r = host.localize(focal_x, focal_y, points2D_vec, points3D_vec, inlier_threshold, number_lo_steps,
+                      min_num_iterations, max_num_iterations, random_seed=random_seed, device=device)
+    r.pop("_stats", None)
+    return r
+
+
+def ransaclib_localization_batch(query_names, focal_x, focal_y, points2D_list, points3D_list, inlier_threshold,
+                                 number_lo_steps, min_num_iterations, max_num_iterations, random_seeds=None,
+                                 device=0):
+    """Independent queries, one result dict per query (queries share nothing:
+    examples/localization.cc:190)."""
+    out = []
+    for i, name in enumerate(query_names):
+        fx = focal_x[i] if hasattr(focal_x, "__len__") else focal_x
+        fy = focal_y[i] if hasattr(focal_y, "__len__") else focal_y
+        seed = None if random_seeds is None else random_seeds[i]
+        out.append(ransaclib_localization(name, fx, fy, points2D_list[i], points3D_list[i], inlier_threshold,
+                                          number_lo_steps, min_num_iterations, max_num_iterations,
+                                          random_seed=seed, device=device))
+    return out

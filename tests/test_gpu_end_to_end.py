@@ -1,0 +1,164 @@
+"""GPU end-to-end parity: the drop-in template layer (include/RansacLib/*.h, speculative
+batches + sequential replay, fused LO passes) against the oracle's sequential LO-MSAC on the
+same seeds. Same seed => same iteration count, LO count, inlier count, inlier index set and
+model as the (pinned) oracle, which is bit-identical to the reference's own headers."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from ransaclib_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def host():
+    from ransaclib_b200 import host as h
+
+    return h
+
+
+def oracle_line(xy, **kw):
+    O = ol.oracle()
+    o = ol.Options.default(**kw)
+    st = ol.Stats()
+    model = np.zeros(3)
+    inl = np.zeros(len(xy), np.int32)
+    O.lomsac_line(C.byref(o), len(xy), ol.c64(xy), model, C.byref(st), inl)
+    return model, st, inl[:st.best_num_inliers].copy()
+
+
+def oracle_pose(p2, p3, f, **kw):
+    O = ol.oracle()
+    o = ol.Options.default(**kw)
+    st = ol.Stats()
+    model = np.zeros(12)
+    inl = np.zeros(len(p2), np.int32)
+    O.lomsac_pose(C.byref(o), f, f, len(p2), ol.c64(p2), ol.c64(p3), model, C.byref(st), inl)
+    return model, st, inl[:st.best_num_inliers].copy()
+
+
+def check_same(stats, model, ost, omodel, oinl, model_rtol=1e-9):
+    assert stats["num_iterations"] == ost.num_iterations
+    assert stats["number_lo_iterations"] == ost.number_lo_iterations
+    assert stats["best_num_inliers"] == ost.best_num_inliers
+    assert stats["inlier_indices"].tolist() == oinl.tolist()
+    np.testing.assert_allclose(stats["best_model_score"], ost.best_model_score, rtol=1e-9)
+    np.testing.assert_allclose(model, omodel, rtol=model_rtol, atol=1e-12)
+    assert stats["inlier_ratio"] == ost.inlier_ratio
+
+
+@pytest.mark.parametrize("outlier_ratio,seed", [(0.1, 42), (0.5, 7), (0.9, 3), (0.99, 11)])
+def test_line_estimation_config(outlier_ratio, seed):
+    """BASELINE configs[0]: examples/line_estimation.cc (N = 10,000, thr^2 = 1e-4, max 100k)."""
+    H = host()
+    n = 10000
+    n_out = int(n * outlier_ratio)
+    xy = synth.line_instance(1000 + seed, n - n_out, n_out)
+    kw = dict(sq_thr=1e-4, seed=seed, min_iters=100, max_iters=100000)
+    om, ost, oinl = oracle_line(xy, **kw)
+    opts = H.LORansacOptions(squared_inlier_threshold_=1e-4, random_seed_=seed, min_num_iterations_=100,
+                             max_num_iterations_=100000)
+    m, st = H.estimate_line(opts, xy)
+    check_same(st, m, ost, om, oinl)
+    m32, st32 = H.estimate_line(opts, xy, precision=1)  # f32 sweep + f64 verification: same run
+    check_same(st32, m32, ost, om, oinl)
+
+
+@pytest.mark.parametrize("seed,final_lsq,lo_steps", [(42, 0, 10), (5, 1, 10), (9, 0, 0)])
+def test_camera_pose_estimation_config(seed, final_lsq, lo_steps):
+    """BASELINE configs[1] shape: N = 10k matches, 50 % outliers, thr = 12 px, adaptive stop."""
+    H = host()
+    inst = synth.pose_instance(2000 + seed, 5000, 5000)
+    f = inst["focal"]
+    kw = dict(sq_thr=144.0, seed=seed, final_lsq=final_lsq, lo_steps=lo_steps, min_iters=100, max_iters=10000)
+    om, ost, oinl = oracle_pose(inst["points2D"], inst["points3D"], f, **kw)
+    opts = H.LORansacOptions(squared_inlier_threshold_=144.0, random_seed_=seed, final_least_squares_=bool(final_lsq),
+                             num_lo_steps_=lo_steps, min_num_iterations_=100, max_num_iterations_=10000)
+    m, st = H.estimate_pose(opts, f, f, inst["points2D"], inst["points3D"])
+    check_same(st, m, ost, om, oinl)
+    assert st["best_num_inliers"] >= 4900
+    # fused passes: far fewer than the reference's ~105 per LO call
+    assert st["single_passes"] < 80 * max(1, st["number_lo_iterations"]) + 20
+    m32, st32 = H.estimate_pose(opts, f, f, inst["points2D"], inst["points3D"], precision=1)
+    check_same(st32, m32, ost, om, oinl)
+
+
+def test_pose_forced_10k_hypotheses():
+    """configs[1] exactly: min = max = 10,000 iterations forces all 10k hypotheses."""
+    H = host()
+    inst = synth.pose_instance(4242, 5000, 5000)
+    f = inst["focal"]
+    kw = dict(sq_thr=144.0, seed=42, min_iters=10000, max_iters=10000)
+    om, ost, oinl = oracle_pose(inst["points2D"], inst["points3D"], f, **kw)
+    opts = H.LORansacOptions(squared_inlier_threshold_=144.0, random_seed_=42, min_num_iterations_=10000,
+                             max_num_iterations_=10000)
+    m, st = H.estimate_pose(opts, f, f, inst["points2D"], inst["points3D"])
+    assert st["num_iterations"] == 10000
+    check_same(st, m, ost, om, oinl)
+
+
+def test_hybrid_line_estimation_config():
+    """BASELINE configs[2]: hybrid line, N0 = N1 = 100k (also the example's 100 + 100)."""
+    H = host()
+    O = ol.oracle()
+    for n, seed in [(100, 42), (100000, 6)]:
+        n_out = n // 2
+        xy0, p1 = synth.hybrid_line_instance(300 + seed, n - n_out, n_out, n - n_out, n_out)
+        o = ol.HybridOptions.default(sq_thr=[1e-4, 1e-4], weights=[2.0, 0.5], seed=seed, min_iters=100,
+                                     max_iters=10000, max_iters_per_solver=1000)
+        ost = ol.HybridStats()
+        om = np.zeros(3)
+        a, b = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        O.hybrid_lomsac_line(C.byref(o), n, ol.c64(xy0), n, ol.c64(p1), np.array([0.2, 0.8]), om, C.byref(ost), a, b)
+        opts = H.HybridLORansacOptions(squared_inlier_thresholds_=[1e-4, 1e-4], data_type_weights_=[2.0, 0.5],
+                                       random_seed_=seed, min_num_iterations_=100, max_num_iterations_=10000,
+                                       max_num_iterations_per_solver_=1000)
+        m, st = H.estimate_hybrid_line(opts, xy0, p1, [0.2, 0.8])
+        assert st["num_iterations_total"] == ost.num_iterations_total
+        assert st["num_iterations_per_solver"] == list(ost.num_iterations_per_solver)
+        assert st["best_num_inliers"] == ost.best_num_inliers
+        assert st["best_solver_type"] == ost.best_solver_type
+        assert st["number_lo_iterations"] == ost.number_lo_iterations
+        assert st["inlier_ratios"] == list(ost.inlier_ratios)
+        np.testing.assert_allclose(st["best_model_score"], ost.best_model_score, rtol=1e-9)
+        np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+        assert st["inlier_indices"][0].tolist() == a[:ost.num_inliers_per_type[0]].tolist()
+        assert st["inlier_indices"][1].tolist() == b[:ost.num_inliers_per_type[1]].tolist()
+
+
+def test_too_little_data_and_untouched_model():
+    H = host()
+    m, st = H.estimate_line(H.LORansacOptions(), np.array([[0.0, 1.0]]))  # 1 point < sample size 2
+    assert st["best_num_inliers"] == 0 and not st["found"] and m.tolist() == [0, 0, 0]
+    # coincident points: no minimal model exists -> nothing found, model left untouched
+    m, st = H.estimate_line(H.LORansacOptions(max_num_iterations_=200), np.ones((50, 2)))
+    assert st["best_num_inliers"] == 0 and not st["found"] and m.tolist() == [0, 0, 0]
+
+
+def test_pyransaclib_localization():
+    """pyransaclib.ransaclib_localization drop-in (examples/ransaclib_localization.cc:58-165)."""
+    from ransaclib_b200 import pyransaclib
+
+    assert pyransaclib.ransaclib_localization("q", 500.0, 500.0, np.zeros((3, 2)), np.zeros((3, 3)), 12.0, 10, 100,
+                                              1000) == {"success": False}
+    inst = synth.pose_instance(5000, 1000, 1000)
+    f = np.float32(inst["focal"])
+    r = pyransaclib.ransaclib_localization("q0", f, f, inst["points2D"], inst["points3D"], 12.0, 10, 100, 10000,
+                                           random_seed=42)
+    assert r["success"] and set(r) == {"success", "qvec", "tvec", "num_inliers", "inliers"}
+    assert r["num_inliers"] == len(r["inliers"]) >= 990
+    # pose close to ground truth: t = -R c
+    R, c = inst["R_gt"], inst["c_gt"]
+    np.testing.assert_allclose(r["tvec"], -R @ c, atol=0.02)
+    w, x, y, z = r["qvec"]
+    Rq = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                   [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                   [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    np.testing.assert_allclose(Rq, R, atol=5e-3)
+    # same options + seed through the oracle: identical inlier set
+    kw = dict(sq_thr=float(np.float32(12.0)) ** 2, seed=42, final_lsq=1, lo_steps=10, min_iters=100, max_iters=10000,
+              lo_start=60)
+    om, ost, oinl = oracle_pose(inst["points2D"], inst["points3D"], float(f), **kw)
+    assert r["inliers"] == oinl.tolist()
