@@ -116,6 +116,7 @@ def run_ours(args):
     import torch
 
     import ransaclib_b200 as rlb
+    from ransaclib_b200 import sharding
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -130,12 +131,12 @@ def run_ours(args):
     wl = WORKLOADS[args.workload]
     n, k_total = wl["n"], wl["k"]
     prec = rlb.RLB_F32 if args.precision == "f32" else rlb.RLB_F64
-    assert k_total % world == 0
-    k = k_total // world
+    id_lo, id_hi = sharding.hypothesis_range(k_total, rank, world)
+    k = id_hi - id_lo
 
     p2, p3, f, inst = make_instance(n)
     samples_all = make_samples(n, k_total)
-    my_samples = np.ascontiguousarray(samples_all[rank * k:(rank + 1) * k])  # contiguous id ranges per rank
+    my_samples = np.ascontiguousarray(samples_all[id_lo:id_hi])  # contiguous id ranges per rank
 
     ctx = rlb.Context(local)
     stream = torch.cuda.Stream(dev)  # one explicit stream for our kernels, torch's glue and NCCL
@@ -150,7 +151,6 @@ def run_ours(args):
     d_scores = torch.empty(k, dtype=torch.float64, device=dev)
     d_counts = torch.empty(k, dtype=torch.int32, device=dev)
     d_best = torch.zeros(2, dtype=torch.float64, device=dev)  # {double score; int64 id}
-    d_pack = torch.zeros(14, dtype=torch.float64, device=dev)  # score, global id, model[12]
     d_gather = torch.zeros((world, 14), dtype=torch.float64, device=dev)
     d_win = torch.zeros(12, dtype=torch.float64, device=dev)
     d_idx = torch.empty(n, dtype=torch.int32, device=dev)
@@ -161,20 +161,12 @@ def run_ours(args):
         scorer.hypothesize_and_score_dev(d_samples.data_ptr(), k, THR, None, d_models.data_ptr(),
                                          d_valid.data_ptr(), d_scores.data_ptr(), d_counts.data_ptr(),
                                          d_best.data_ptr(), precision=prec)
-        # pack (score, global hypothesis id, model) -- torch is plumbing here, not the hot path
+        # (score, global hypothesis id, model) record; ONE all_gather per round; lexicographic argmin
+        # (ransaclib_b200/sharding.py) -- torch is plumbing here, not the hot path
         lid = d_best.view(torch.int64)[1]
-        d_pack[0] = d_best[0]
-        d_pack[1] = (lid + rank * k).to(torch.float64)
-        d_pack[2:] = d_models[lid.clamp(min=0)]
-        if world > 1:
-            dist.all_gather_into_tensor(d_gather, d_pack)  # the single collective of the round
-            g = d_gather
-        else:
-            g = d_pack.view(1, 14)
-        # lexicographic (score, id) min: lowest id wins ties; ranks own ascending id ranges
-        smin = g[:, 0].min()
-        cand = torch.where(g[:, 0] == smin, g[:, 1], torch.full_like(g[:, 1], float("inf")))
-        w = torch.argmin(cand)
+        rec = sharding.pack_record(d_best[0], lid, id_lo, d_models[lid.clamp(min=0)])
+        g = sharding.all_gather_records(rec, world)
+        w, _ = sharding.select_winner(g)
         d_win.copy_(g[w, 2:])
         scorer.get_inliers_dev(d_win.data_ptr(), THR, THR, None, d_idx.data_ptr(), d_hdr.data_ptr())
 
@@ -228,7 +220,7 @@ def run_ours(args):
         r = sc.hypothesize_and_score(h_s, THR, precision=prec, want_models=False)
         bm = r["best_model"]
         if world > 1:
-            pk = torch.tensor([r["best_score"], float(r["best_id"] + rank * k), *bm], dtype=torch.float64,
+            pk = torch.tensor([r["best_score"], float(r["best_id"] + id_lo), *bm], dtype=torch.float64,
                               device=dev)
             dist.all_gather_into_tensor(d_gather, pk)
             g = d_gather.cpu().numpy()
