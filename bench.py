@@ -152,23 +152,25 @@ def run_ours(args):
     d_counts = torch.empty(k, dtype=torch.int32, device=dev)
     d_best = torch.zeros(2, dtype=torch.float64, device=dev)  # {double score; int64 id}
     d_gather = torch.zeros((world, 14), dtype=torch.float64, device=dev)
-    d_win = torch.zeros(12, dtype=torch.float64, device=dev)
     d_idx = torch.empty(n, dtype=torch.int32, device=dev)
     d_hdr = torch.zeros(4, dtype=torch.float64, device=dev)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
+    d_rec = torch.zeros(14, dtype=torch.float64, device=dev)   # this rank's record
+    d_winner = torch.zeros(14, dtype=torch.float64, device=dev)  # {score, global id, model[12]}
+
     def step():
-        scorer.hypothesize_and_score_dev(d_samples.data_ptr(), k, THR, None, d_models.data_ptr(),
-                                         d_valid.data_ptr(), d_scores.data_ptr(), d_counts.data_ptr(),
-                                         d_best.data_ptr(), precision=prec)
-        # (score, global hypothesis id, model) record; ONE all_gather per round; lexicographic argmin
-        # (ransaclib_b200/sharding.py) -- torch is plumbing here, not the hot path
-        lid = d_best.view(torch.int64)[1]
-        rec = sharding.pack_record(d_best[0], lid, id_lo, d_models[lid.clamp(min=0)])
-        g = sharding.all_gather_records(rec, world)
-        w, _ = sharding.select_winner(g)
-        d_win.copy_(g[w, 2:])
-        scorer.get_inliers_dev(d_win.data_ptr(), THR, THR, None, d_idx.data_ptr(), d_hdr.data_ptr())
+        # solve + sweep + argmin; the shard's (score, global id, model) record lands in d_rec
+        scorer.sharded_round_dev(d_samples.data_ptr(), k, THR, None, id_lo, d_models.data_ptr(),
+                                 d_valid.data_ptr(), d_scores.data_ptr(), d_counts.data_ptr(),
+                                 d_rec.data_ptr(), precision=prec)
+        if world > 1:
+            dist.all_gather_into_tensor(d_gather, d_rec)  # the single collective of the round
+            g = d_gather
+        else:
+            g = d_rec
+        ctx.select_winner_dev(g.data_ptr(), world, 14, d_winner.data_ptr())
+        scorer.get_inliers_dev(d_winner.data_ptr() + 16, THR, THR, None, d_idx.data_ptr(), d_hdr.data_ptr())
 
     for _ in range(args.warmup):
         step()
@@ -272,7 +274,7 @@ def run_ours(args):
     inl_avg_ms = float(np.mean(inl_ms))
     inl_bytes = n * 40 + 4 * n_inl
     roofline = {
-        "bound": "fma", "kernel": "sweep_kernel<PoseF,%s>" % ("float" if prec == rlb.RLB_F32 else "double"),
+        "bound": "fma", "kernel": "sweep_pose_f32x2_kernel<4>" if prec == rlb.RLB_F32 else "sweep_kernel<PoseF,double,2>",
         "achieved": achieved_tflops, "peak": fma_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fma_peak,
         "peak_source": "rlb_measure_fma_peak: register-resident %s microbenchmark on this GPU, same run "
                        "(MEASURED_PEAKS.json has no FMA-pipe figure)" % ("FFMA" if fma_dtype else "DFMA"),

@@ -159,6 +159,21 @@ int rlb_hypothesize_and_score_dev(rlb_scorer* s, int precision, int solver, int 
                                   const double* weights, double* d_models, uint8_t* d_valid,
                                   double* d_scores, int32_t* d_counts, void* d_best);
 
+/* ---- hypothesis-sharded rounds (one process per GPU; the collective itself is the caller's:
+ *      NCCL all_gather of one record per rank) ------------------------------------------- */
+/* rlb_hypothesize_and_score_dev for this rank's shard; additionally writes the shard's
+ * record = {double score; double global_id (= local id + id_offset, -1 if none);
+ * double model[model_size]} to d_record. Ranks must own ascending contiguous id ranges so
+ * the lowest-id tie-break of ransac.h:195,288 survives the reduction. */
+int rlb_sharded_round_dev(rlb_scorer* s, int precision, int solver, int k, const int32_t* d_samples,
+                          const double* sq_thr, const double* weights, int64_t id_offset,
+                          double* d_models, uint8_t* d_valid, double* d_scores, int32_t* d_counts,
+                          double* d_record);
+/* Lexicographic (score, global id) minimum over `world` gathered records -> d_winner (one
+ * record; id = -1 when no rank had a model). NaN / DBL_MAX scores never win. */
+int rlb_select_winner_dev(rlb_ctx* ctx, const double* d_records, int world, int record_doubles,
+                          double* d_winner);
+
 /* ---- measurement helpers --------------------------------------------------- */
 /* When enabled, the context brackets every sweep kernel and every inlier kernel with
  * CUDA events on its stream; rlb_ctx_kernel_time_ms waits for the LAST such kernel

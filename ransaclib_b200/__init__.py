@@ -66,6 +66,10 @@ class Context:
         _capi.check(self._lib.rlb_ctx_kernel_time_ms(self._h, which, C.byref(out)))
         return out.value
 
+    def select_winner_dev(self, d_records: int, world: int, record_doubles: int, d_winner: int):
+        _capi.check(self._lib.rlb_select_winner_dev(self._h, C.c_void_p(d_records), world, record_doubles,
+                                                    C.c_void_p(d_winner)))
+
     def measure_fma_peak(self, dtype: int) -> float:
         """TFLOP/s of the DFMA (0), FFMA (1) or packed FFMA2 (2) pipe, register-resident."""
         out = C.c_double()
@@ -208,6 +212,17 @@ class Scorer:
             self._h, precision, solver, k, C.c_void_p(d_samples), _capi.ptr(thr), _capi.ptr(w),
             C.c_void_p(d_models), C.c_void_p(d_valid), C.c_void_p(d_scores or 0), C.c_void_p(d_counts or 0),
             C.c_void_p(d_best)))
+
+    def sharded_round_dev(self, d_samples: int, k: int, sq_thr, weights, id_offset: int, d_models: int,
+                          d_valid: int, d_scores: int, d_counts: int, d_record: int, solver: int = 0,
+                          precision=RLB_F64):
+        """One hypothesis-sharded round: solve + sweep + argmin, local winner record -> d_record."""
+        thr = self._thr(sq_thr)
+        w = None if weights is None else self._thr(weights)
+        _capi.check(self._lib.rlb_sharded_round_dev(
+            self._h, precision, solver, k, C.c_void_p(d_samples), _capi.ptr(thr), _capi.ptr(w), int(id_offset),
+            C.c_void_p(d_models), C.c_void_p(d_valid), C.c_void_p(d_scores or 0), C.c_void_p(d_counts or 0),
+            C.c_void_p(d_record)))
 
     def score_models_dev(self, d_models: int, k: int, sq_thr, weights, d_valid: int, d_scores: int, d_counts: int,
                          d_best: int, precision=RLB_F64):

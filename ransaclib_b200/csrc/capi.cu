@@ -76,6 +76,9 @@ struct rlb_ctx {
   bool timing = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // sweep begin/end, inlier begin/end
   bool ev_valid[2] = {false, false};
+  // set by rlb_sharded_round_dev for the next score_dev call
+  double* pending_record = nullptr;
+  long long pending_offset = 0;
 };
 
 struct rlb_scorer {
@@ -200,6 +203,10 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     }();
     a.variant = variant;
   }
+  a.record = c->pending_record;
+  a.id_offset = c->pending_offset;
+  c->pending_record = nullptr;
+  c->pending_offset = 0;
   const int H = (precision == RLB_F32) ? 4 : (d.kind == RLB_KIND_POSE ? 2 : 4);
   const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
   const int total_stages = d.npad / rlb::kStage;
@@ -692,6 +699,35 @@ int rlb_hypothesize_and_score_dev(rlb_scorer* s, int precision, int solver, int 
   if (rc) return rc;
   return score_dev(s, precision, k, d_models, d_valid, sq_thr, weights, d_scores, d_counts,
                    static_cast<BestRec*>(d_best), nullptr);
+}
+
+int rlb_sharded_round_dev(rlb_scorer* s, int precision, int solver, int k, const int32_t* d_samples,
+                          const double* sq_thr, const double* weights, int64_t id_offset,
+                          double* d_models, uint8_t* d_valid, double* d_scores, int32_t* d_counts,
+                          double* d_record) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  if (!d_record) return fail(RLB_E_ARG, "d_record is required");
+  rc = ensure_first_use(s->ctx);
+  if (rc) return rc;
+  s->ctx->pending_record = d_record;
+  s->ctx->pending_offset = id_offset;
+  void* d_best = s->ctx->small.as<char>() + kSmallBest;
+  rc = rlb_hypothesize_and_score_dev(s, precision, solver, k, d_samples, sq_thr, weights, d_models, d_valid,
+                                     d_scores, d_counts, d_best);
+  s->ctx->pending_record = nullptr;
+  return rc;
+}
+
+int rlb_select_winner_dev(rlb_ctx* c, const double* d_records, int world, int record_doubles,
+                          double* d_winner) {
+  if (!c || !d_records || !d_winner || world <= 0 || record_doubles < 3)
+    return fail(RLB_E_ARG, "bad arguments");
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  RLB_CUDA(rlb::launch_select_winner(d_records, world, record_doubles, d_winner, c->stream, &c->launches_i));
+  account(c);
+  return RLB_OK;
 }
 
 int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,

@@ -49,6 +49,8 @@ struct SweepArgs {
   double* part_score;          // [n_splits][k]
   int32_t* part_count;         // [n_splits][k]
   int variant;                 // 0 = default kernels, 1 = scalar-FFMA sweep (A/B timing)
+  double* record;              // optional {score, global id (as f64), model...} of the local winner
+  long long id_offset;         // first global hypothesis id of this shard
 };
 
 struct BestRec {
@@ -88,6 +90,8 @@ cudaError_t launch_eval_errors(const DeviceData& d, int precision, const double*
                                double* err, cudaStream_t st, int* launches);
 cudaError_t launch_repack(const DeviceData& d, double* soa64, float* soa32, cudaStream_t st,
                           int* launches);
+cudaError_t launch_select_winner(const double* records, int world, int rec_doubles, double* winner,
+                                 cudaStream_t st, int* launches);
 cudaError_t launch_fma_peak(int dtype, int sms, float* ms, double* flops, cudaStream_t st);
 
 // launchers (solver_kernels.cu, compiled with -fmad=false)

@@ -671,6 +671,13 @@ __global__ void __launch_bounds__(256)
     if (best_model != nullptr && id != LLONG_MAX) {
       for (int i = 0; i < md; ++i) best_model[i] = a.models[static_cast<size_t>(id) * md + i];
     }
+    if (a.record != nullptr) {  // the record a sharded round contributes to its one all_gather
+      const bool has = (id != LLONG_MAX);
+      a.record[0] = has ? s : DBL_MAX;
+      a.record[1] = has ? static_cast<double>(id + a.id_offset) : -1.0;
+      for (int i = 0; i < md; ++i)
+        a.record[2 + i] = has ? a.models[static_cast<size_t>(id) * md + i] : 0.0;
+    }
   }
 }
 
@@ -681,6 +688,37 @@ cudaError_t launch_finalize(const DeviceData& d, const SweepArgs& a, double* sco
   const int blocks = (a.k + 255) / 256;
   finalize_kernel<<<blocks, 256, 0, st>>>(d, a, scores, counts, block_best, ticket, best,
                                           best_model);
+  return cudaGetLastError();
+}
+
+// Cross-rank winner of a sharded round: lexicographic (score, global id) minimum over the
+// gathered records; NaN / DBL_MAX scores never win. winner = {score, id, model...}; id = -1 if none.
+__global__ void select_winner_kernel(const double* __restrict__ records, int world, int rec_doubles,
+                                     double* __restrict__ winner) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double bs = DBL_MAX;
+  double bid = -1.0;
+  int brow = -1;
+  for (int r = 0; r < world; ++r) {
+    const double s = records[static_cast<size_t>(r) * rec_doubles];
+    const double id = records[static_cast<size_t>(r) * rec_doubles + 1];
+    if (!(s < DBL_MAX) || id < 0.0) continue;
+    if (brow < 0 || s < bs || (s == bs && id < bid)) {
+      bs = s;
+      bid = id;
+      brow = r;
+    }
+  }
+  winner[0] = bs;
+  winner[1] = bid;
+  for (int i = 2; i < rec_doubles; ++i)
+    winner[i] = brow >= 0 ? records[static_cast<size_t>(brow) * rec_doubles + i] : 0.0;
+}
+
+cudaError_t launch_select_winner(const double* records, int world, int rec_doubles, double* winner,
+                                 cudaStream_t st, int* launches) {
+  ++*launches;
+  select_winner_kernel<<<1, 32, 0, st>>>(records, world, rec_doubles, winner);
   return cudaGetLastError();
 }
 

@@ -290,3 +290,41 @@ def test_full_size_properties(ctx):
     lists, counts, score = sc.get_inliers(models[bid64], 144.0, 144.0)
     assert counts[0] == c64_[bid64] and (np.diff(lists[0]) > 0).all()
     np.testing.assert_allclose(score, s64[bid64], rtol=F64_RTOL)
+
+
+def test_sharded_round_emulated_ranks(ctx, pose_case):
+    """Hypothesis sharding with fewer GPUs than ranks: the ranks' shards run one
+    after the other on this GPU, their records are stacked as the all_gather would, and the winner
+    must be the single-GPU winner (same global id, same model) for every world size."""
+    import torch
+
+    from ransaclib_b200 import sharding
+
+    inst, f, samples, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    ref = sc.hypothesize_and_score(samples, 144.0)
+    dev = torch.device("cuda", 0)
+    k_total = len(samples)
+    for world in (1, 2, 3, 8):
+        recs = torch.zeros((world, 14), dtype=torch.float64, device=dev)
+        for rank in range(world):
+            lo, hi = sharding.hypothesis_range(k_total, rank, world)
+            k = hi - lo
+            d_s = torch.from_numpy(np.ascontiguousarray(samples[lo:hi])).to(dev)
+            d_m = torch.empty((k, 12), dtype=torch.float64, device=dev)
+            d_v = torch.empty(k, dtype=torch.uint8, device=dev)
+            d_sc = torch.empty(k, dtype=torch.float64, device=dev)
+            d_c = torch.empty(k, dtype=torch.int32, device=dev)
+            torch.cuda.synchronize()
+            sc.sharded_round_dev(d_s.data_ptr(), k, 144.0, None, lo, d_m.data_ptr(), d_v.data_ptr(),
+                                 d_sc.data_ptr(), d_c.data_ptr(), recs[rank].data_ptr())
+            ctx.synchronize()
+        win = torch.zeros(14, dtype=torch.float64, device=dev)
+        ctx.select_winner_dev(recs.data_ptr(), world, 14, win.data_ptr())
+        ctx.synchronize()
+        w = win.cpu().numpy()
+        assert int(w[1]) == ref["best_id"] and w[0] == ref["best_score"]
+        assert w[2:].tolist() == ref["best_model"].tolist()
+        # the torch-side selection used under gloo/NCCL agrees with the kernel
+        row, ok = sharding.select_winner(recs)
+        assert bool(ok) and int(recs[row, 1].item()) == ref["best_id"]
