@@ -80,6 +80,7 @@ int rlb_scorer_create_hybrid_line(rlb_ctx* ctx, int n0, const double* xy0, int n
  * as PixelsToViewingRays does (.cc:214-227). */
 int rlb_scorer_create_pose(rlb_ctx* ctx, int n, const double* points2D,
                            const double* points3D, double fx, double fy, rlb_scorer** out);
+/* Destroy every scorer BEFORE its context: the data-set memory returns to the context's pool. */
 int rlb_scorer_destroy(rlb_scorer* s);
 int rlb_scorer_kind(const rlb_scorer* s);
 int rlb_scorer_num_types(const rlb_scorer* s);

@@ -7,6 +7,7 @@ this package only marshals numpy buffers. No CPU fallback exists.
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -27,9 +28,12 @@ class Context:
         _capi.check(self._lib.rlb_ctx_create(device, C.byref(h)))
         self._h = h
         self.device = device
+        self._scorers = weakref.WeakSet()  # scorers must be released before their context
 
     def close(self):
         if getattr(self, "_h", None):
+            for sc in list(self._scorers):
+                sc.close()
             self._lib.rlb_ctx_destroy(self._h)
             self._h = None
 
@@ -109,6 +113,7 @@ class Scorer:
         self.ctx = ctx
         self._lib = ctx._lib
         self._h = handle
+        ctx._scorers.add(self)
         self.kind = self._lib.rlb_scorer_kind(handle)
         self.num_types = self._lib.rlb_scorer_num_types(handle)
         self.num_data = [self._lib.rlb_scorer_num_data(handle, t) for t in range(self.num_types)]

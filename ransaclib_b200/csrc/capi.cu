@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <new>
 #include <vector>
 
@@ -76,6 +77,12 @@ struct rlb_ctx {
   bool timing = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // sweep begin/end, inlier begin/end
   bool ev_valid[2] = {false, false};
+  // Data-set memory pool: scorers are created and destroyed per query (batched localization, the
+  // e2e path), and cudaMalloc/cudaFree cost milliseconds and synchronise the device. Freed blocks
+  // are kept (up to kPoolLimit bytes) and reused by the next scorer of a similar size.
+  std::multimap<size_t, void*> pool_free_blocks;
+  std::map<void*, size_t> pool_sizes;
+  size_t pool_idle_bytes = 0;
   // set by rlb_sharded_round_dev for the next score_dev call
   double* pending_record = nullptr;
   long long pending_offset = 0;
@@ -130,18 +137,63 @@ void subsampled_mean(const double* p, int n, int stride, int dims, double* out) 
   }
 }
 
+constexpr size_t kPoolLimit = size_t(2) << 30;
+
+int pool_alloc(rlb_ctx* c, size_t bytes, void** out) {
+  bytes = std::max<size_t>((bytes + 511) / 512 * 512, 512);
+  auto it = c->pool_free_blocks.lower_bound(bytes);
+  if (it != c->pool_free_blocks.end() && it->first <= bytes * 2) {
+    *out = it->second;
+    c->pool_idle_bytes -= it->first;
+    c->pool_free_blocks.erase(it);
+    return RLB_OK;
+  }
+  RLB_CUDA(cudaMalloc(out, bytes));
+  c->pool_sizes[*out] = bytes;
+  return RLB_OK;
+}
+
+void pool_release(rlb_ctx* c, void* p) {
+  if (!p) return;
+  auto it = c->pool_sizes.find(p);
+  if (it == c->pool_sizes.end()) {
+    cudaFree(p);
+    return;
+  }
+  if (c->pool_idle_bytes + it->second > kPoolLimit) {
+    cudaFree(p);
+    c->pool_sizes.erase(it);
+    return;
+  }
+  c->pool_free_blocks.emplace(it->second, p);
+  c->pool_idle_bytes += it->second;
+}
+
+void pool_drain(rlb_ctx* c) {
+  for (auto& kv : c->pool_free_blocks) cudaFree(kv.second);
+  c->pool_free_blocks.clear();
+  c->pool_sizes.clear();
+  c->pool_idle_bytes = 0;
+}
+
 int finish_scorer(rlb_scorer* s) {
   rlb_ctx* c = s->ctx;
   DeviceData& d = s->d;
   const size_t ch = static_cast<size_t>(d.channels) * d.npad;
-  RLB_CUDA(cudaMalloc(&s->soa64, ch * sizeof(double)));
-  RLB_CUDA(cudaMalloc(&s->soa32, ch * sizeof(float)));
+  {
+    int rc = pool_alloc(c, ch * sizeof(double), &s->soa64);
+    if (!rc) rc = pool_alloc(c, ch * sizeof(float), &s->soa32);
+    if (rc) return rc;
+  }
   d.soa64 = static_cast<const double*>(s->soa64);
   d.soa32 = static_cast<const float*>(s->soa32);
   RLB_CUDA(rlb::launch_repack(d, static_cast<double*>(s->soa64), static_cast<float*>(s->soa32),
                               c->stream, &c->launches_i));
   if (d.kind == RLB_KIND_POSE) {
-    RLB_CUDA(cudaMalloc(&s->rays, static_cast<size_t>(std::max(d.n[0], 1)) * 3 * sizeof(double)));
+    {
+      const int rc = pool_alloc(c, static_cast<size_t>(std::max(d.n[0], 1)) * 3 * sizeof(double), &s->rays);
+      if (rc) return rc;
+    }
     d.rays = static_cast<const double*>(s->rays);
     RLB_CUDA(rlb::launch_rays(d, static_cast<double*>(s->rays), c->stream, &c->launches_i));
   }
@@ -150,8 +202,11 @@ int finish_scorer(rlb_scorer* s) {
   return RLB_OK;
 }
 
-int upload(void** dst, const double* src, size_t count, cudaStream_t st) {
-  RLB_CUDA(cudaMalloc(dst, std::max<size_t>(count, 1) * sizeof(double)));
+int upload(rlb_ctx* c, void** dst, const double* src, size_t count, cudaStream_t st) {
+  {
+    const int rc = pool_alloc(c, std::max<size_t>(count, 1) * sizeof(double), dst);
+    if (rc) return rc;
+  }
   if (count) RLB_CUDA(cudaMemcpyAsync(*dst, src, count * sizeof(double), cudaMemcpyHostToDevice, st));
   return RLB_OK;
 }
@@ -348,6 +403,7 @@ int rlb_ctx_destroy(rlb_ctx* c) {
                     &c->part_count, &c->block_best, &c->small, &c->one_model, &c->idx,
                     &c->tile_score, &c->status, &c->header};
   for (DevBuf* b : bufs) b->release();
+  pool_drain(c);
   if (c->h_small) cudaFreeHost(c->h_small);
   for (int i = 0; i < 4; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -393,7 +449,7 @@ int rlb_scorer_create_line(rlb_ctx* c, int n, const double* xy, rlb_scorer** out
   d.off[1] = d.npad = std::max(pad_to(n, rlb::kSegAlign), rlb::kSegAlign);
   d.channels = 2;
   subsampled_mean(xy, n, 2, 2, d.centre);
-  rc = upload(&s->raw0, xy, static_cast<size_t>(n) * 2, c->stream);
+  rc = upload(c, &s->raw0, xy, static_cast<size_t>(n) * 2, c->stream);
   if (!rc) {
     d.raw0 = static_cast<const double*>(s->raw0);
     rc = finish_scorer(s);
@@ -429,8 +485,8 @@ int rlb_scorer_create_hybrid_line(rlb_ctx* c, int n0, const double* xy0, int n1,
     subsampled_mean(xy0, n0, 2, 2, d.centre);
   else
     subsampled_mean(xynn1, n1, 4, 2, d.centre);
-  rc = upload(&s->raw0, xy0, static_cast<size_t>(n0) * 2, c->stream);
-  if (!rc) rc = upload(&s->raw1, xynn1, static_cast<size_t>(n1) * 4, c->stream);
+  rc = upload(c, &s->raw0, xy0, static_cast<size_t>(n0) * 2, c->stream);
+  if (!rc) rc = upload(c, &s->raw1, xynn1, static_cast<size_t>(n1) * 4, c->stream);
   if (!rc) {
     d.raw0 = static_cast<const double*>(s->raw0);
     d.raw1 = static_cast<const double*>(s->raw1);
@@ -463,8 +519,8 @@ int rlb_scorer_create_pose(rlb_ctx* c, int n, const double* p2d, const double* p
   d.fx = fx;
   d.fy = fy;
   subsampled_mean(p3d, n, 3, 3, d.centre);
-  rc = upload(&s->raw0, p2d, static_cast<size_t>(n) * 2, c->stream);
-  if (!rc) rc = upload(&s->raw1, p3d, static_cast<size_t>(n) * 3, c->stream);
+  rc = upload(c, &s->raw0, p2d, static_cast<size_t>(n) * 2, c->stream);
+  if (!rc) rc = upload(c, &s->raw1, p3d, static_cast<size_t>(n) * 3, c->stream);
   if (!rc) {
     d.raw0 = static_cast<const double*>(s->raw0);
     d.raw1 = static_cast<const double*>(s->raw1);
@@ -485,8 +541,11 @@ int rlb_scorer_destroy(rlb_scorer* s) {
     cudaStreamSynchronize(s->ctx->stream);
   }
   void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32};
-  for (void* p : ptrs)
-    if (p) cudaFree(p);
+  for (void* p : ptrs) {
+    if (!p) continue;
+    if (s->ctx) pool_release(s->ctx, p);
+    else cudaFree(p);
+  }
   delete s;
   return RLB_OK;
 }
