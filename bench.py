@@ -274,7 +274,7 @@ def run_ours(args):
     inl_avg_ms = float(np.mean(inl_ms))
     inl_bytes = n * 40 + 4 * n_inl
     roofline = {
-        "bound": "fma", "kernel": "sweep_pose_f32x2_kernel<4>" if prec == rlb.RLB_F32 else "sweep_kernel<PoseF,double,2>",
+        "bound": "fma", "kernel": "sweep_pose_f32x2_kernel<8>" if prec == rlb.RLB_F32 else "sweep_kernel<PoseF,double,2>",
         "achieved": achieved_tflops, "peak": fma_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fma_peak,
         "peak_source": "rlb_measure_fma_peak: register-resident %s microbenchmark on this GPU, same run "
                        "(MEASURED_PEAKS.json has no FMA-pipe figure)" % ("FFMA" if fma_dtype else "DFMA"),

@@ -547,12 +547,37 @@ static cudaError_t launch_sweep_pose_x2(const DeviceData& d, const SweepArgs& a,
   return cudaGetLastError();
 }
 
+// Hypotheses per thread of the sweep that launch_sweep will pick (the host sizes the grid with it).
+int sweep_hyps_per_thread(int kind, int precision, int variant) {
+  if (kind == RLB_KIND_POSE) {
+    if (precision != RLB_F32) return 2;
+    switch (variant) {
+      case 2: return 2;
+      case 3: return 8;
+      case 4: return 6;
+      case 5: return 12;
+      case 6: return 10;
+      default: return 4;
+    }
+  }
+  return 4;
+}
+
 cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision, cudaStream_t st,
                          int* launches) {
   ++*launches;
   if (d.kind == RLB_KIND_POSE) {
-    if (precision == RLB_F32 && a.variant == 0) return launch_sweep_pose_x2<4>(d, a, st);
-    if (precision == RLB_F32) return launch_sweep_t<PoseF, float, 4>(d, a, st);
+    if (precision == RLB_F32) {
+      switch (a.variant) {
+        case 1: return launch_sweep_t<PoseF, float, 4>(d, a, st);  // scalar FFMA (v1), A/B only
+        case 2: return launch_sweep_pose_x2<2>(d, a, st);
+        case 3: return launch_sweep_pose_x2<8>(d, a, st);
+        case 4: return launch_sweep_pose_x2<6>(d, a, st);
+        case 5: return launch_sweep_pose_x2<12>(d, a, st);
+        case 6: return launch_sweep_pose_x2<10>(d, a, st);
+        default: return launch_sweep_pose_x2<4>(d, a, st);
+      }
+    }
     return launch_sweep_t<PoseF, double, 2>(d, a, st);
   }
   if (precision == RLB_F32) return launch_sweep_t<LineF, float, 4>(d, a, st);
