@@ -83,6 +83,11 @@ struct rlb_ctx {
   std::multimap<size_t, void*> pool_free_blocks;
   std::map<void*, size_t> pool_sizes;
   size_t pool_idle_bytes = 0;
+  // zero-copy result buffer of the K=1 pass for small data sets: {InlierHeader; int32 idx[]} in
+  // mapped pinned host memory, written by the kernel itself (one launch + one sync per pass)
+  void* h_result = nullptr;
+  void* d_result = nullptr;  // device alias of h_result
+  size_t result_cap = 0;
   // set by rlb_sharded_round_dev for the next score_dev call
   double* pending_record = nullptr;
   long long pending_offset = 0;
@@ -308,7 +313,7 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
 }
 
 int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, const double* thr_score,
-                const double* w, int32_t* d_idx, void* d_header) {
+                const double* w, int32_t* d_idx, void* d_header, const double* host_model = nullptr) {
   rlb_ctx* c = s->ctx;
   const DeviceData& d = s->d;
   if (!thr_inl) return fail(RLB_E_ARG, "sq_thr_inl is required");
@@ -322,6 +327,10 @@ int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, con
   RLB_CUDA(c->tile_score.ensure(static_cast<size_t>(tiles) * sizeof(double)));
   InlierArgs a;
   a.model = d_model;
+  if (host_model) {
+    a.model = nullptr;
+    for (int i = 0; i < rlb::model_size_of(d.kind); ++i) a.model_v[i] = host_model[i];
+  }
   fill_thr(d, thr_inl, w, a.thr_inl, a.w);
   double dummy[rlb::kMaxTypes];
   fill_thr(d, thr_score ? thr_score : thr_inl, w, a.thr_score, dummy);
@@ -418,6 +427,7 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   pool_drain(c);
   if (c->h_small) cudaFreeHost(c->h_small);
+  if (c->h_result) cudaFreeHost(c->h_result);
   for (int i = 0; i < 4; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -662,22 +672,46 @@ int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl
   const DeviceData& d = s->d;
   const int md = rlb::model_size_of(d.kind);
   const int ntot = d.n[0] + (d.num_types > 1 ? d.n[1] : 0);
-  RLB_CUDA(c->one_model.ensure(12 * sizeof(double)));
-  RLB_CUDA(c->header.ensure(sizeof(InlierHeader)));
-  if (idx) RLB_CUDA(c->idx.ensure(static_cast<size_t>(std::max(ntot, 1)) * sizeof(int32_t)));
-  RLB_CUDA(cudaMemcpyAsync(c->one_model.p, model, md * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  rc = inliers_dev(s, c->one_model.as<double>(), sq_thr_inl, sq_thr_score, weights,
-                   idx ? c->idx.as<int32_t>() : nullptr, c->header.p);
-  if (rc) return rc;
-  InlierHeader* h = reinterpret_cast<InlierHeader*>(static_cast<char*>(c->h_small) + 64);
-  RLB_CUDA(cudaMemcpyAsync(h, c->header.p, sizeof(InlierHeader), cudaMemcpyDeviceToHost, c->stream));
-  RLB_CUDA(cudaStreamSynchronize(c->stream));
-  const int total = h->count[1];
-  if (idx && total > 0) {
-    RLB_CUDA(cudaMemcpyAsync(idx, c->idx.p, static_cast<size_t>(total) * sizeof(int32_t),
-                             cudaMemcpyDeviceToHost, c->stream));
+  constexpr int kZeroCopyMax = 65536;  // points; above this the list is fetched by DMA
+  InlierHeader* h = nullptr;
+  if (ntot <= kZeroCopyMax) {
+    // Small data sets (the latency-critical LO chains): the kernel writes header + list straight
+    // into mapped pinned memory; the model travels in the launch parameters. 1 launch + 1 sync.
+    const size_t need = sizeof(InlierHeader) + static_cast<size_t>(std::max(ntot, 1)) * sizeof(int32_t);
+    if (need > c->result_cap) {
+      if (c->h_result) cudaFreeHost(c->h_result);
+      c->h_result = nullptr;
+      c->result_cap = 0;
+      const size_t cap = std::max<size_t>(need, 64 * 1024);
+      RLB_CUDA(cudaHostAlloc(&c->h_result, cap, cudaHostAllocMapped));
+      RLB_CUDA(cudaHostGetDevicePointer(&c->d_result, c->h_result, 0));
+      c->result_cap = cap;
+    }
+    char* dres = static_cast<char*>(c->d_result);
+    rc = inliers_dev(s, nullptr, sq_thr_inl, sq_thr_score, weights,
+                     idx ? reinterpret_cast<int32_t*>(dres + sizeof(InlierHeader)) : nullptr, dres, model);
+    if (rc) return rc;
     RLB_CUDA(cudaStreamSynchronize(c->stream));
+    h = static_cast<InlierHeader*>(c->h_result);
+    if (idx && h->count[1] > 0)
+      memcpy(idx, static_cast<char*>(c->h_result) + sizeof(InlierHeader),
+             static_cast<size_t>(h->count[1]) * sizeof(int32_t));
+  } else {
+    RLB_CUDA(c->header.ensure(sizeof(InlierHeader)));
+    if (idx) RLB_CUDA(c->idx.ensure(static_cast<size_t>(std::max(ntot, 1)) * sizeof(int32_t)));
+    rc = inliers_dev(s, nullptr, sq_thr_inl, sq_thr_score, weights, idx ? c->idx.as<int32_t>() : nullptr,
+                     c->header.p, model);
+    if (rc) return rc;
+    h = reinterpret_cast<InlierHeader*>(static_cast<char*>(c->h_small) + 64);
+    RLB_CUDA(cudaMemcpyAsync(h, c->header.p, sizeof(InlierHeader), cudaMemcpyDeviceToHost, c->stream));
+    RLB_CUDA(cudaStreamSynchronize(c->stream));
+    if (idx && h->count[1] > 0) {
+      RLB_CUDA(cudaMemcpyAsync(idx, c->idx.p, static_cast<size_t>(h->count[1]) * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, c->stream));
+      RLB_CUDA(cudaStreamSynchronize(c->stream));
+    }
   }
+  const int total = h->count[1];
   if (counts) {
     counts[0] = h->count[0];
     if (d.num_types > 1) counts[1] = total - h->count[0];

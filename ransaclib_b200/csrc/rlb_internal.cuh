@@ -59,7 +59,8 @@ struct BestRec {
 };
 
 struct InlierArgs {
-  const double* model;     // device, model_size doubles
+  const double* model;     // device, model_size doubles (nullptr: use model_v)
+  double model_v[12];      // model passed by value with the launch (host-pointer API: no H2D copy)
   double thr_inl[kMaxTypes];
   double thr_score[kMaxTypes];
   double w[kMaxTypes];

@@ -786,7 +786,7 @@ __global__ void __launch_bounds__(kInlThreads) inlier_kernel(const DeviceData d,
   const double w = a.w[t];
 
   typename F::Model m;
-  F::load(a.model, d, m);
+  F::load(a.model != nullptr ? a.model : a.model_v, d, m);
 
   const int i0 = g0 + tid * PPT;
   double ch[C][PPT];
