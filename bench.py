@@ -282,7 +282,9 @@ def run_ours(args):
         "flop_per_eval": FLOP_PER_EVAL, "evals_per_launch": evals_per_launch, "launch_ms": sweep_avg_ms,
         "evals_per_s": evals_per_launch / (sweep_avg_ms * 1e-3),
         "share_of_step": sweep_avg_ms * args.steps / total_ms,
-        "traffic": None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, one launch, from the ncu --set full
+        # capture of the same command (profiles/r01b_ncu_sweep_h8.csv); only valid for the default f32 C5 run.
+        "traffic": 33.1e6 if (prec == rlb.RLB_F32 and args.workload == "c5" and world == 1) else None,
         "hbm": {"algorithmic_bytes": algo_bytes, "achieved_gbs": algo_bytes / (sweep_avg_ms * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs"), "peak_kind": peak_kind,
                 "note": "arithmetic intensity ~%.0f FLOP/B: HBM is not the bound of this kernel"
