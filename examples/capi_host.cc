@@ -123,6 +123,51 @@ void Run(const rlbh_options& o, Solver& solver, int precision, Model* model, rlb
     for (size_t i = 0; i < rs.inlier_indices.size(); ++i) inliers[i] = rs.inlier_indices[i];
 }
 
+// [R|c] -> (qvec w,x,y,z ; tvec = -R c) as ransaclib_localization.cc:147-150
+// (Eigen::Quaterniond(R), then normalize()).
+void PoseToQvecTvec(const double* m /* column-major 3x4 */, double* qvec, double* tvec) {
+  double R[9];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) R[3 * r + c] = m[r + 3 * c];
+  for (int r = 0; r < 3; ++r) tvec[r] = -(R[3 * r] * m[9] + R[3 * r + 1] * m[10] + R[3 * r + 2] * m[11]);
+  double w, x, y, z;
+  const double trace = R[0] + R[4] + R[8];
+  if (trace > 0.0) {
+    double t = std::sqrt(trace + 1.0);
+    w = 0.5 * t;
+    t = 0.5 / t;
+    x = (R[7] - R[5]) * t;
+    y = (R[2] - R[6]) * t;
+    z = (R[3] - R[1]) * t;
+  } else {
+    int i = 0;
+    if (R[4] > R[0]) i = 1;
+    if (R[8] > R[4 * i]) i = 2;
+    const int j = (i + 1) % 3, k = (j + 1) % 3;
+    double t = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
+    double q[3];
+    q[i] = 0.5 * t;
+    t = 0.5 / t;
+    w = (R[3 * k + j] - R[3 * j + k]) * t;
+    q[j] = (R[3 * j + i] + R[3 * i + j]) * t;
+    q[k] = (R[3 * k + i] + R[3 * i + k]) * t;
+    x = q[0];
+    y = q[1];
+    z = q[2];
+  }
+  const double nq = std::sqrt(w * w + x * x + y * y + z * z);
+  if (nq > 0.0) {
+    w /= nq;
+    x /= nq;
+    y /= nq;
+    z /= nq;
+  }
+  qvec[0] = w;
+  qvec[1] = x;
+  qvec[2] = y;
+  qvec[3] = z;
+}
+
 template <class F>
 int Guard(F f) {
   try {
@@ -235,52 +280,50 @@ int rlbh_localize(int device, int precision, float focal_x, float focal_y, int n
                                                                   st ? st : &local, inliers);
     const rlbh_stats& s = st ? *st : local;
     *num_inliers = s.best_num_inliers;
-    // t = -R c
-    for (int r = 0; r < 3; ++r)
-      tvec[r] = -(best(r, 0) * best.m[9] + best(r, 1) * best.m[10] + best(r, 2) * best.m[11]);
-    // Quaternion of R (Eigen::Quaterniond(R), then normalize()).
-    double R[9];
-    for (int r = 0; r < 3; ++r)
-      for (int c = 0; c < 3; ++c) R[3 * r + c] = best(r, c);
-    double w, x, y, z;
-    const double trace = R[0] + R[4] + R[8];
-    if (trace > 0.0) {
-      double t = std::sqrt(trace + 1.0);
-      w = 0.5 * t;
-      t = 0.5 / t;
-      x = (R[7] - R[5]) * t;
-      y = (R[2] - R[6]) * t;
-      z = (R[3] - R[1]) * t;
-    } else {
-      int i = 0;
-      if (R[4] > R[0]) i = 1;
-      if (R[8] > R[4 * i]) i = 2;
-      const int j = (i + 1) % 3, k = (j + 1) % 3;
-      double t = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
-      double q[3];
-      q[i] = 0.5 * t;
-      t = 0.5 / t;
-      w = (R[3 * k + j] - R[3 * j + k]) * t;
-      q[j] = (R[3 * j + i] + R[3 * i + j]) * t;
-      q[k] = (R[3 * k + i] + R[3 * i + k]) * t;
-      x = q[0];
-      y = q[1];
-      z = q[2];
-    }
-    const double nq = std::sqrt(w * w + x * x + y * y + z * z);
-    if (nq > 0.0) {
-      w /= nq;
-      x /= nq;
-      y /= nq;
-      z /= nq;
-    }
-    qvec[0] = w;
-    qvec[1] = x;
-    qvec[2] = y;
-    qvec[3] = z;
+    PoseToQvecTvec(best.m, qvec, tvec);
     success = 1;
   });
   return rc == 0 ? success : -1;
+}
+
+// Batched ransaclib_localization: Q independent queries in ONE launch of the device-resident
+// LO-MSAC (rlb_localize_batch); per-query semantics are those of rlbh_localize above (float
+// focals / threshold, fixed options, <= 3 matches -> success 0). Queries are concatenated:
+// query q owns matches [offsets[q], offsets[q+1]). inliers (optional): `total` int32, query q's
+// ascending inlier indices start at offsets[q].
+int rlbh_localize_batch(int device, int num_queries, const int64_t* offsets, const double* p2d,
+                        const double* p3d, const float* focal_x, const float* focal_y,
+                        float inlier_threshold, int number_lo_steps, uint32_t min_num_iterations,
+                        uint32_t max_num_iterations, const uint32_t* seeds, int32_t* success,
+                        double* qvecs, double* tvecs, int32_t* num_inliers, int32_t* inliers,
+                        rlb_localize_result* results_out) {
+  return Guard([&] {
+    gpu::Context& ctx = gpu::Context::ThreadDefault(device);
+    rlb_localize_options o;
+    rlb_localize_default_options(&o, static_cast<double>(inlier_threshold), number_lo_steps,
+                                 min_num_iterations, max_num_iterations);
+    std::vector<double> fx(num_queries), fy(num_queries), poses(static_cast<size_t>(num_queries) * 12);
+    for (int q = 0; q < num_queries; ++q) {
+      fx[q] = static_cast<double>(focal_x[q]);
+      fy[q] = static_cast<double>(focal_y[q]);
+    }
+    std::vector<rlb_localize_result> res(num_queries);
+    gpu::Check(rlb_localize_batch(ctx.get(), num_queries, offsets, p2d, p3d, fx.data(), fy.data(), seeds, &o,
+                                  poses.data(), res.data(), inliers),
+               "rlb_localize_batch");
+    for (int q = 0; q < num_queries; ++q) {
+      success[q] = res[q].success;
+      num_inliers[q] = res[q].num_inliers;
+      if (res[q].success) {
+        PoseToQvecTvec(&poses[static_cast<size_t>(q) * 12], qvecs + 4 * static_cast<size_t>(q),
+                       tvecs + 3 * static_cast<size_t>(q));
+      } else {
+        for (int i = 0; i < 4; ++i) qvecs[4 * static_cast<size_t>(q) + i] = 0.0;
+        for (int i = 0; i < 3; ++i) tvecs[3 * static_cast<size_t>(q) + i] = 0.0;
+      }
+      if (results_out) results_out[q] = res[q];
+    }
+  });
 }
 
 }  // extern "C"

@@ -10,18 +10,30 @@
 #ifndef RANSACLIB_B200_EXAMPLES_POSE_REFINEMENT_H_
 #define RANSACLIB_B200_EXAMPLES_POSE_REFINEMENT_H_
 
-#include <algorithm>
 #include <cfloat>
 #include <cmath>
-#include <limits>
+
+// The same arithmetic also runs inside the device-resident localization kernel
+// (ransaclib_b200/csrc/localize_kernels.cu, compiled with -fmad=false): every function here is
+// host+device, and the LM loop is a template over the "lineariser" so that the device can form
+// cost / J^T J / J^T r with one point per lane while keeping the host's summation order.
+#if defined(__CUDACC__)
+#define RLB_HD __host__ __device__
+#else
+#define RLB_HD
+#endif
 
 namespace ransac_lib {
 namespace calibrated_absolute_pose {
 namespace refine {
 
+// std::min / std::max semantics (usable in device code).
+RLB_HD inline double Max(double a, double b) { return (a < b) ? b : a; }
+RLB_HD inline double Min(double a, double b) { return (b < a) ? b : a; }
+
 // Row-major rotation -> angle-axis through the quaternion, as Eigen::AngleAxisd(Matrix3d)
 // does (calibrated_absolute_pose_estimator.cc:172-173).
-inline void RotationToAngleAxis(const double* R, double* aa) {
+RLB_HD inline void RotationToAngleAxis(const double* R, double* aa) {
   double w, x, y, z;
   const double trace = R[0] + R[4] + R[8];
   if (trace > 0.0) {
@@ -60,7 +72,7 @@ inline void RotationToAngleAxis(const double* R, double* aa) {
 }
 
 // Angle-axis -> row-major rotation (Rodrigues; .cc:204-210).
-inline void AngleAxisToRotation(const double* aa, double* R) {
+RLB_HD inline void AngleAxisToRotation(const double* aa, double* R) {
   const double angle = std::sqrt(aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2]);
   double ax = aa[0], ay = aa[1], az = aa[2];
   if (angle > 0.0) {
@@ -82,97 +94,111 @@ inline void AngleAxisToRotation(const double* aa, double* R) {
   R[8] = tz * az + c;
 }
 
-// Value + 6 partial derivatives (the role ceres::Jet<double,6> plays in the reference).
-struct Dual {
+// Value + ND partial derivatives (the role ceres::Jet<double,6> plays in the reference).
+// ND = 0 carries the value only: its arithmetic on `.a` is the same sequence of operations,
+// so a cost-only evaluation returns bit-identical residuals without the derivative work.
+template <int ND>
+struct DualN {
   double a;
-  double d[6];
-  static Dual Constant(double v) {
-    Dual r;
+  double d[ND > 0 ? ND : 1];
+  RLB_HD static DualN Constant(double v) {
+    DualN r;
     r.a = v;
-    for (int i = 0; i < 6; ++i) r.d[i] = 0.0;
+    for (int i = 0; i < ND; ++i) r.d[i] = 0.0;
     return r;
   }
-  static Dual Variable(double v, int k) {
-    Dual r = Constant(v);
-    r.d[k] = 1.0;
+  RLB_HD static DualN Variable(double v, int k) {
+    DualN r = Constant(v);
+    if (k < ND) r.d[k] = 1.0;
     return r;
   }
 };
-inline Dual operator+(const Dual& x, const Dual& y) {
-  Dual r;
+typedef DualN<6> Dual;
+typedef DualN<0> Value;
+
+template <int ND>
+RLB_HD inline DualN<ND> operator+(const DualN<ND>& x, const DualN<ND>& y) {
+  DualN<ND> r;
   r.a = x.a + y.a;
-  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] + y.d[i];
+  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] + y.d[i];
   return r;
 }
-inline Dual operator-(const Dual& x, const Dual& y) {
-  Dual r;
+template <int ND>
+RLB_HD inline DualN<ND> operator-(const DualN<ND>& x, const DualN<ND>& y) {
+  DualN<ND> r;
   r.a = x.a - y.a;
-  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] - y.d[i];
+  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] - y.d[i];
   return r;
 }
-inline Dual operator*(const Dual& x, const Dual& y) {
-  Dual r;
+template <int ND>
+RLB_HD inline DualN<ND> operator*(const DualN<ND>& x, const DualN<ND>& y) {
+  DualN<ND> r;
   r.a = x.a * y.a;
-  for (int i = 0; i < 6; ++i) r.d[i] = x.a * y.d[i] + x.d[i] * y.a;
+  for (int i = 0; i < ND; ++i) r.d[i] = x.a * y.d[i] + x.d[i] * y.a;
   return r;
 }
-inline Dual operator/(const Dual& x, const Dual& y) {
-  Dual r;
+template <int ND>
+RLB_HD inline DualN<ND> operator/(const DualN<ND>& x, const DualN<ND>& y) {
+  DualN<ND> r;
   const double inv = 1.0 / y.a;
   r.a = x.a * inv;
-  for (int i = 0; i < 6; ++i) r.d[i] = (x.d[i] - r.a * y.d[i]) * inv;
+  for (int i = 0; i < ND; ++i) r.d[i] = (x.d[i] - r.a * y.d[i]) * inv;
   return r;
 }
-inline Dual Sqrt(const Dual& x) {
-  Dual r;
+template <int ND>
+RLB_HD inline DualN<ND> Sqrt(const DualN<ND>& x) {
+  DualN<ND> r;
   r.a = std::sqrt(x.a);
   const double g = 0.5 / r.a;
-  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] * g;
+  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] * g;
   return r;
 }
-inline Dual Sin(const Dual& x) {
-  Dual r;
+template <int ND>
+RLB_HD inline DualN<ND> Sin(const DualN<ND>& x) {
+  DualN<ND> r;
   r.a = std::sin(x.a);
   const double g = std::cos(x.a);
-  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] * g;
+  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] * g;
   return r;
 }
-inline Dual Cos(const Dual& x) {
-  Dual r;
+template <int ND>
+RLB_HD inline DualN<ND> Cos(const DualN<ND>& x) {
+  DualN<ND> r;
   r.a = std::cos(x.a);
   const double g = -std::sin(x.a);
-  for (int i = 0; i < 6; ++i) r.d[i] = x.d[i] * g;
+  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] * g;
   return r;
 }
 
 // ReprojectionError::operator() (.cc:55-74) with ceres::AngleAxisRotatePoint's two branches.
-inline void Residual(const Dual* cam, double u, double v, double X, double Y, double Z, double fx,
-                     double fy, Dual* res) {
-  const Dual one = Dual::Constant(1.0);
-  Dual p[3] = {Dual::Constant(X) - cam[3], Dual::Constant(Y) - cam[4], Dual::Constant(Z) - cam[5]};
-  Dual q[3];
-  const Dual theta2 = cam[0] * cam[0] + cam[1] * cam[1] + cam[2] * cam[2];
-  if (theta2.a > std::numeric_limits<double>::epsilon()) {
-    const Dual theta = Sqrt(theta2);
-    const Dual ct = Cos(theta), st = Sin(theta);
-    const Dual inv = one / theta;
-    const Dual w[3] = {cam[0] * inv, cam[1] * inv, cam[2] * inv};
-    const Dual wxp[3] = {w[1] * p[2] - w[2] * p[1], w[2] * p[0] - w[0] * p[2],
-                         w[0] * p[1] - w[1] * p[0]};
-    const Dual tmp = (w[0] * p[0] + w[1] * p[1] + w[2] * p[2]) * (one - ct);
+template <class D>
+RLB_HD inline void Residual(const D* cam, double u, double v, double X, double Y, double Z,
+                            double fx, double fy, D* res) {
+  const D one = D::Constant(1.0);
+  D p[3] = {D::Constant(X) - cam[3], D::Constant(Y) - cam[4], D::Constant(Z) - cam[5]};
+  D q[3];
+  const D theta2 = cam[0] * cam[0] + cam[1] * cam[1] + cam[2] * cam[2];
+  if (theta2.a > DBL_EPSILON) {
+    const D theta = Sqrt(theta2);
+    const D ct = Cos(theta), st = Sin(theta);
+    const D inv = one / theta;
+    const D w[3] = {cam[0] * inv, cam[1] * inv, cam[2] * inv};
+    const D wxp[3] = {w[1] * p[2] - w[2] * p[1], w[2] * p[0] - w[0] * p[2],
+                      w[0] * p[1] - w[1] * p[0]};
+    const D tmp = (w[0] * p[0] + w[1] * p[1] + w[2] * p[2]) * (one - ct);
     for (int i = 0; i < 3; ++i) q[i] = p[i] * ct + wxp[i] * st + w[i] * tmp;
   } else {
-    const Dual wxp[3] = {cam[1] * p[2] - cam[2] * p[1], cam[2] * p[0] - cam[0] * p[2],
-                         cam[0] * p[1] - cam[1] * p[0]};
+    const D wxp[3] = {cam[1] * p[2] - cam[2] * p[1], cam[2] * p[0] - cam[0] * p[2],
+                      cam[0] * p[1] - cam[1] * p[0]};
     for (int i = 0; i < 3; ++i) q[i] = p[i] + wxp[i];
   }
-  const Dual xp = Dual::Constant(fx) * q[0] / q[2];
-  const Dual yp = Dual::Constant(fy) * q[1] / q[2];
-  res[0] = Dual::Constant(u) - xp;
-  res[1] = Dual::Constant(v) - yp;
+  const D xp = D::Constant(fx) * q[0] / q[2];
+  const D yp = D::Constant(fy) * q[1] / q[2];
+  res[0] = D::Constant(u) - xp;
+  res[1] = D::Constant(v) - yp;
 }
 
-inline bool SolveSpd6(const double* A, const double* b, double* x) {
+RLB_HD inline bool SolveSpd6(const double* A, const double* b, double* x) {
   double L[36];
   for (int i = 0; i < 6; ++i) {
     for (int j = 0; j <= i; ++j) {
@@ -200,22 +226,40 @@ inline bool SolveSpd6(const double* A, const double* b, double* x) {
   return true;
 }
 
-// Cost, J^T J and J^T r over the sample.
-inline double Linearise(int k, const int* idx, const double* p2d, const double* p3d, double fx,
-                        double fy, const double* c, double* JtJ, double* Jtr) {
-  Dual cam[6];
-  for (int i = 0; i < 6; ++i) cam[i] = Dual::Variable(c[i], i);
-  double cost = 0.0;
-  if (JtJ) {
+// Sequential lineariser (host): cost, J^T J and J^T r over the sample, points in sample order,
+// per point the two residual rows in order, entries accumulated as acc += d[a] * d[b].
+struct SequentialLineariser {
+  int k;
+  const int* idx;
+  const double* p2d;
+  const double* p3d;
+  double fx, fy;
+
+  // Cost only: value arithmetic without derivatives (bit-identical residuals).
+  RLB_HD double Cost(const double* c) const {
+    Value cam[6];
+    for (int i = 0; i < 6; ++i) cam[i] = Value::Constant(c[i]);
+    double cost = 0.0;
+    for (int s = 0; s < k; ++s) {
+      const int i = idx[s];
+      Value r[2];
+      Residual(cam, p2d[2 * i], p2d[2 * i + 1], p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2], fx, fy, r);
+      cost += 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
+    }
+    return cost;
+  }
+
+  RLB_HD double Full(const double* c, double* JtJ, double* Jtr) const {
+    Dual cam[6];
+    for (int i = 0; i < 6; ++i) cam[i] = Dual::Variable(c[i], i);
+    double cost = 0.0;
     for (int i = 0; i < 36; ++i) JtJ[i] = 0.0;
     for (int i = 0; i < 6; ++i) Jtr[i] = 0.0;
-  }
-  for (int s = 0; s < k; ++s) {
-    const int i = idx[s];
-    Dual r[2];
-    Residual(cam, p2d[2 * i], p2d[2 * i + 1], p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2], fx, fy, r);
-    cost += 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
-    if (JtJ) {
+    for (int s = 0; s < k; ++s) {
+      const int i = idx[s];
+      Dual r[2];
+      Residual(cam, p2d[2 * i], p2d[2 * i + 1], p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2], fx, fy, r);
+      cost += 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
       for (int e = 0; e < 2; ++e) {
         for (int a = 0; a < 6; ++a) {
           Jtr[a] += r[e].d[a] * r[e].a;
@@ -223,36 +267,35 @@ inline double Linearise(int k, const int* idx, const double* p2d, const double* 
         }
       }
     }
-  }
-  if (JtJ) {
     for (int a = 0; a < 6; ++a)
       for (int b = a + 1; b < 6; ++b) JtJ[6 * a + b] = JtJ[6 * b + a];
+    return cost;
   }
-  return cost;
-}
+};
 
 // Levenberg-Marquardt with Ceres' defaults: initial radius 1e4, at most 50 iterations,
 // function tolerance 1e-6, gradient tolerance 1e-10, parameter tolerance 1e-8, minimum
 // relative decrease 1e-3, diagonal scaling clamped to [1e-6, 1e32]. Returns false when the
 // result is not usable (non-finite), like !summary.IsSolutionUsable() (.cc:202).
-inline bool RefinePose(int k, const int* idx, const double* p2d, const double* p3d, double fx,
-                       double fy, double* cam) {
+// Lin provides Cost(x) and Full(x, JtJ, g) (see SequentialLineariser).
+template <class Lin>
+RLB_HD inline bool RefinePoseWith(const Lin& lin, double* cam) {
   double x[6];
   for (int i = 0; i < 6; ++i) x[i] = cam[i];
   double JtJ[36], g[6];
-  double cost = Linearise(k, idx, p2d, p3d, fx, fy, x, JtJ, g);
+  double cost = lin.Full(x, JtJ, g);
   if (!(cost == cost) || cost > DBL_MAX) return false;
   double radius = 1e4;
   double shrink = 2.0;
   for (int iter = 0; iter < 50; ++iter) {
     double gmax = 0.0;
-    for (int i = 0; i < 6; ++i) gmax = std::max(gmax, std::fabs(g[i]));
+    for (int i = 0; i < 6; ++i) gmax = Max(gmax, std::fabs(g[i]));
     if (gmax <= 1e-10) break;
     double A[36], rhs[6], step[6];
     for (int i = 0; i < 36; ++i) A[i] = JtJ[i];
     for (int i = 0; i < 6; ++i) {
       double dgl = JtJ[7 * i];
-      dgl = std::min(std::max(dgl, 1e-6), 1e32);
+      dgl = Min(Max(dgl, 1e-6), 1e32);
       A[7 * i] += dgl / radius;
       rhs[i] = -g[i];
     }
@@ -284,16 +327,16 @@ inline bool RefinePose(int k, const int* idx, const double* p2d, const double* p
     sn = std::sqrt(sn);
     xnorm = std::sqrt(xnorm);
     if (sn <= 1e-8 * (xnorm + 1e-8)) break;
-    const double cost_new = Linearise(k, idx, p2d, p3d, fx, fy, xn, nullptr, nullptr);
+    const double cost_new = lin.Cost(xn);
     const double rho = (cost - cost_new) / model_decrease;
     if (cost_new == cost_new && rho > 1e-3) {
       const double delta = cost - cost_new;
       for (int i = 0; i < 6; ++i) x[i] = xn[i];
       const double prev = cost;
-      cost = Linearise(k, idx, p2d, p3d, fx, fy, x, JtJ, g);
+      cost = lin.Full(x, JtJ, g);
       const double t = 2.0 * rho - 1.0;
-      radius = radius / std::max(1.0 / 3.0, 1.0 - t * t * t);
-      radius = std::min(radius, 1e16);
+      radius = radius / Max(1.0 / 3.0, 1.0 - t * t * t);
+      radius = Min(radius, 1e16);
       shrink = 2.0;
       if (std::fabs(delta) <= 1e-6 * prev) break;
     } else {
@@ -306,6 +349,34 @@ inline bool RefinePose(int k, const int* idx, const double* p2d, const double* p
     if (!(x[i] - x[i] == 0.0)) return false;
   for (int i = 0; i < 6; ++i) cam[i] = x[i];
   return true;
+}
+
+inline bool RefinePose(int k, const int* idx, const double* p2d, const double* p3d, double fx,
+                       double fy, double* cam) {
+  const SequentialLineariser lin = {k, idx, p2d, p3d, fx, fy};
+  return RefinePoseWith(lin, cam);
+}
+
+// CalibratedAbsolutePoseEstimator::LeastSquares around the LM (.cc:170-212): column-major
+// [R | c] -> (angle-axis, c) -> refine -> back. The pose is left untouched when the refinement
+// is not usable.
+template <class Lin>
+RLB_HD inline void LeastSquaresWith(const Lin& lin, double* pose /* col-major 3x4 [R|c] */) {
+  double R[9];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) R[3 * r + c] = pose[r + 3 * c];
+  double cam[6];
+  RotationToAngleAxis(R, cam);
+  cam[3] = pose[9];
+  cam[4] = pose[10];
+  cam[5] = pose[11];
+  if (!RefinePoseWith(lin, cam)) return;
+  AngleAxisToRotation(cam, R);
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) pose[r + 3 * c] = R[3 * r + c];
+  pose[9] = cam[3];
+  pose[10] = cam[4];
+  pose[11] = cam[5];
 }
 
 }  // namespace refine

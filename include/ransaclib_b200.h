@@ -175,6 +175,61 @@ int rlb_sharded_round_dev(rlb_scorer* s, int precision, int solver, int k, const
 int rlb_select_winner_dev(rlb_ctx* ctx, const double* d_records, int world, int record_doubles,
                           double* d_winner);
 
+/* ---- device-resident batched localization ------------------------------------
+ * Q independent P3P LO-MSAC runs (pyransaclib.ransaclib_localization,
+ * examples/ransaclib_localization.cc:58-165, one call per query image) in ONE launch: each
+ * warp of a persistent grid runs the whole of LocallyOptimizedMSAC::EstimateModel
+ * (ransac.h:128-275) for one query at a time — seeded std::mt19937 sampling and shuffles,
+ * P3P + 4th-point test, MSAC scoring, local optimisation with the Levenberg-Marquardt pose
+ * refinement (calibrated_absolute_pose_estimator.cc:170-212) — without host round trips.
+ * Queries are concatenated: query q owns matches [offsets[q], offsets[q+1]). */
+typedef struct rlb_localize_options {
+  uint32_t min_iters, max_iters;   /* RansacOptions (ransac.h:47-60) */
+  double success_prob;
+  double sq_thr;                   /* squared inlier threshold, also the P3P 4th-point test */
+  int32_t lo_steps;                /* LORansacOptions (ransac.h:64-92) */
+  double thr_mult;
+  int32_t lsq_iters;
+  int32_t min_sample_mult;         /* x4 must be <= 32 */
+  int32_t non_min_sample_mult;     /* x4 must be <= 32 */
+  uint32_t lo_start;
+  int32_t final_lsq;
+  int32_t debug_flags;             /* bit 0: force the sequential path of every shuffle (tests) */
+} rlb_localize_options;
+
+typedef struct rlb_localize_result {
+  int32_t success;        /* 0 for queries with <= 3 matches (ransaclib_localization.cc:86-92) */
+  int32_t num_inliers;    /* RansacStatistics::best_num_inliers */
+  uint32_t num_iterations;
+  int32_t num_lo;         /* number_lo_iterations */
+  double score;           /* best_model_score */
+  double inlier_ratio;
+  int32_t passes;         /* driver counters: f64 passes over the matches, LM refinements */
+  int32_t lsq_calls;
+} rlb_localize_result;
+
+/* ransaclib_localization's fixed options (ransaclib_localization.cc:100-107). */
+void rlb_localize_default_options(rlb_localize_options* opt, double inlier_threshold_px,
+                                  int number_lo_steps, uint32_t min_num_iterations,
+                                  uint32_t max_num_iterations);
+
+/* HOST pointers. offsets: num_queries + 1 entries; points2D: total x 2; points3D: total x 3;
+ * fx, fy, seeds: one per query (the reference seeds from std::random_device; here the seed is an
+ * argument so runs are reproducible). Outputs: poses = num_queries x 12 (column-major [R | c]),
+ * results = num_queries records, inliers = `total` int32 (ascending inlier indices of query q
+ * start at offsets[q]) or NULL. Uploads are pipelined with the kernel in chunks of queries. */
+int rlb_localize_batch(rlb_ctx* ctx, int num_queries, const int64_t* offsets,
+                       const double* points2D, const double* points3D, const double* fx,
+                       const double* fy, const uint32_t* seeds, const rlb_localize_options* opt,
+                       double* poses, rlb_localize_result* results, int32_t* inliers);
+/* DEVICE pointers (everything already in HBM, outputs stay in HBM); asynchronous on the
+ * context stream. max_matches = largest offsets[q+1]-offsets[q] (sizes the scratch). */
+int rlb_localize_batch_dev(rlb_ctx* ctx, int num_queries, int max_matches, const int64_t* d_offsets,
+                           const double* d_points2D, const double* d_points3D, const double* d_fx,
+                           const double* d_fy, const uint32_t* d_seeds,
+                           const rlb_localize_options* opt, double* d_poses,
+                           rlb_localize_result* d_results, int32_t* d_inliers);
+
 /* ---- measurement helpers --------------------------------------------------- */
 /* When enabled, the context brackets every sweep kernel and every inlier kernel with
  * CUDA events on its stream; rlb_ctx_kernel_time_ms waits for the LAST such kernel

@@ -80,6 +80,45 @@ class Context:
         _capi.check(self._lib.rlb_measure_fma_peak(self._h, dtype, C.byref(out)))
         return out.value
 
+    # -- device-resident batched localization ---------------------------------
+    def localize_options(self, inlier_threshold: float, number_lo_steps: int, min_num_iterations: int,
+                         max_num_iterations: int) -> "_capi.LocalizeOptions":
+        """ransaclib_localization's fixed options (ransaclib_localization.cc:100-107)."""
+        o = _capi.LocalizeOptions()
+        self._lib.rlb_localize_default_options(C.byref(o), float(np.float32(inlier_threshold)), int(number_lo_steps),
+                                               int(min_num_iterations), int(max_num_iterations))
+        return o
+
+    def localize_batch(self, offsets, points2D, points3D, fx, fy, seeds, options, want_inliers=True):
+        """Q independent P3P LO-MSAC runs in one launch (host buffers; upload pipelined with the
+        kernel). -> (poses [Q,12] column-major [R|c], results record array, inliers or None)."""
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        nq = len(off) - 1
+        p2 = _capi.f64a(points2D, (-1, 2))
+        p3 = _capi.f64a(points3D, (-1, 3))
+        if len(p2) != len(p3) or len(p2) != off[-1]:
+            raise ValueError("points2D / points3D / offsets disagree")
+        fx = np.ascontiguousarray(np.broadcast_to(np.asarray(fx, np.float64), (nq,)))
+        fy = np.ascontiguousarray(np.broadcast_to(np.asarray(fy, np.float64), (nq,)))
+        seeds = np.ascontiguousarray(seeds, dtype=np.uint32)
+        if len(seeds) != nq:
+            raise ValueError("need one seed per query")
+        poses = np.zeros((nq, 12))
+        res = np.zeros(nq, _capi.LOCALIZE_RESULT)
+        inl = np.zeros(max(int(off[-1]), 1), np.int32) if want_inliers else None
+        _capi.check(self._lib.rlb_localize_batch(self._h, nq, _capi.ptr(off), _capi.ptr(p2), _capi.ptr(p3),
+                                                 _capi.ptr(fx), _capi.ptr(fy), _capi.ptr(seeds), C.byref(options),
+                                                 _capi.ptr(poses), _capi.ptr(res), _capi.ptr(inl)))
+        return poses, res, inl
+
+    def localize_batch_dev(self, nq: int, max_matches: int, d_offsets: int, d_p2d: int, d_p3d: int, d_fx: int,
+                           d_fy: int, d_seeds: int, options, d_poses: int, d_results: int, d_inliers: int = 0):
+        """Device-pointer variant: enqueues the persistent kernel on the context stream."""
+        _capi.check(self._lib.rlb_localize_batch_dev(
+            self._h, nq, max_matches, C.c_void_p(d_offsets), C.c_void_p(d_p2d), C.c_void_p(d_p3d),
+            C.c_void_p(d_fx), C.c_void_p(d_fy), C.c_void_p(d_seeds), C.byref(options), C.c_void_p(d_poses),
+            C.c_void_p(d_results), C.c_void_p(d_inliers or 0)))
+
     # -- data sets -----------------------------------------------------------
     def line_scorer(self, xy) -> "Scorer":
         xy = _capi.f64a(xy, (-1, 2))

@@ -26,7 +26,22 @@ SYMBOLS = [
     "rlb_score_models", "rlb_score_models_dev", "rlb_get_inliers", "rlb_get_inliers_dev",
     "rlb_eval_errors", "rlb_solve_line2pt_batch", "rlb_solve_point_normal_batch", "rlb_solve_p3p_batch",
     "rlb_hypothesize_and_score", "rlb_hypothesize_and_score_dev", "rlb_measure_fma_peak", "rlb_sharded_round_dev", "rlb_select_winner_dev", "rlb_ctx_set_timing", "rlb_ctx_kernel_time_ms",
+    "rlb_localize_default_options", "rlb_localize_batch", "rlb_localize_batch_dev",
 ]
+
+
+class LocalizeOptions(C.Structure):
+    """rlb_localize_options (include/ransaclib_b200.h)."""
+    _fields_ = [("min_iters", C.c_uint32), ("max_iters", C.c_uint32), ("success_prob", C.c_double),
+                ("sq_thr", C.c_double), ("lo_steps", C.c_int32), ("thr_mult", C.c_double),
+                ("lsq_iters", C.c_int32), ("min_sample_mult", C.c_int32), ("non_min_sample_mult", C.c_int32),
+                ("lo_start", C.c_uint32), ("final_lsq", C.c_int32), ("debug_flags", C.c_int32)]
+
+
+# rlb_localize_result as a numpy record (40 bytes)
+LOCALIZE_RESULT = np.dtype([("success", np.int32), ("num_inliers", np.int32), ("num_iterations", np.uint32),
+                            ("num_lo", np.int32), ("score", np.float64), ("inlier_ratio", np.float64),
+                            ("passes", np.int32), ("lsq_calls", np.int32)], align=True)
 
 
 class RlbError(RuntimeError):
@@ -79,6 +94,11 @@ def load():
     lib.rlb_select_winner_dev.argtypes = [vp, vp, i32, i32, vp]
     lib.rlb_ctx_set_timing.argtypes = [vp, i32]
     lib.rlb_ctx_kernel_time_ms.argtypes = [vp, i32, C.POINTER(f64)]
+    lib.rlb_localize_default_options.argtypes = [C.POINTER(LocalizeOptions), f64, i32, C.c_uint32, C.c_uint32]
+    lib.rlb_localize_default_options.restype = None
+    lib.rlb_localize_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, C.POINTER(LocalizeOptions), vp, vp, vp]
+    lib.rlb_localize_batch_dev.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, C.POINTER(LocalizeOptions), vp,
+                                           vp, vp]
     _lib = lib
     return lib
 

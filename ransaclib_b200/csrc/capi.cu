@@ -88,6 +88,12 @@ struct rlb_ctx {
   void* h_result = nullptr;
   void* d_result = nullptr;  // device alias of h_result
   size_t result_cap = 0;
+  // device-resident batched localization: per-warp-slot scratch, ticket / ready / abort words,
+  // a copy stream + pinned progress words for the pipelined host API
+  DevBuf loc_soa, loc_lists, loc_words;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t loc_ev[2] = {nullptr, nullptr};
+  unsigned int* h_ready = nullptr;  // pinned, kMaxChunks entries
   // set by rlb_sharded_round_dev for the next score_dev call
   double* pending_record = nullptr;
   long long pending_offset = 0;
@@ -428,6 +434,13 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   pool_drain(c);
   if (c->h_small) cudaFreeHost(c->h_small);
   if (c->h_result) cudaFreeHost(c->h_result);
+  if (c->h_ready) cudaFreeHost(c->h_ready);
+  c->loc_soa.release();
+  c->loc_lists.release();
+  c->loc_words.release();
+  for (int i = 0; i < 2; ++i)
+    if (c->loc_ev[i]) cudaEventDestroy(c->loc_ev[i]);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   for (int i = 0; i < 4; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -887,6 +900,209 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
   if (best_id) *best_id = static_cast<int32_t>(hb->id);
   if (best_score) *best_score = hb->score;
   if (best_model && hb->id >= 0) memcpy(best_model, hs + 128, md * sizeof(double));
+  return RLB_OK;
+}
+
+// ---- device-resident batched localization -------------------------------------------------
+namespace {
+
+constexpr int kMaxChunks = 64;
+
+int check_localize_options(const rlb_localize_options* o) {
+  if (!o) return fail(RLB_E_ARG, "null options");
+  if (o->min_sample_mult < 1 || o->min_sample_mult * 4 > 32)
+    return fail(RLB_E_ARG, "min_sample_mult * 4 must be in [4, 32] (got %d)", o->min_sample_mult);
+  if (o->non_min_sample_mult < 0 || o->non_min_sample_mult * 4 > 32)
+    return fail(RLB_E_ARG, "non_min_sample_mult * 4 must be <= 32 (got %d)", o->non_min_sample_mult);
+  if (!(o->sq_thr > 0.0)) return fail(RLB_E_ARG, "sq_thr must be positive");
+  if (o->lo_steps < 0 || o->lsq_iters < 0) return fail(RLB_E_ARG, "negative lo_steps / lsq_iters");
+  return RLB_OK;
+}
+
+// Enqueues the persistent kernel on `st`. d_ready == nullptr: everything is resident.
+int localize_enqueue(rlb_ctx* c, cudaStream_t st, int nq, int max_matches, const int64_t* d_offsets,
+                     const double* d_p2d, const double* d_p3d, const double* d_fx, const double* d_fy,
+                     const uint32_t* d_seeds, const rlb_localize_options* opt, double* d_poses,
+                     rlb_localize_result* d_results, int32_t* d_inliers, bool pipelined) {
+  const int wpc = rlb::localize_warps_per_cta();
+  const int nmax = std::max(max_matches, 4);
+  const int npad = pad_to(nmax, 4);
+  const size_t per_slot = static_cast<size_t>(5) * npad * sizeof(float) + static_cast<size_t>(3) * nmax * 4;
+  int ctas = std::min((nq + wpc - 1) / wpc, c->sms * 3);
+  const size_t budget = size_t(8) << 30;  // scratch cap; fewer resident warps for huge queries
+  while (ctas > 1 && static_cast<size_t>(ctas) * wpc * per_slot > budget) ctas /= 2;
+  const size_t slots = static_cast<size_t>(ctas) * wpc;
+  RLB_CUDA(c->loc_soa.ensure(slots * 5 * npad * sizeof(float)));
+  RLB_CUDA(c->loc_lists.ensure(slots * 3 * nmax * sizeof(int32_t)));
+  RLB_CUDA(c->loc_words.ensure(64));
+  unsigned int* words = c->loc_words.as<unsigned int>();  // [0] ticket, [1] ready, [2] abort
+  if (pipelined) {
+    RLB_CUDA(cudaMemsetAsync(words, 0, 4, st));  // ready/abort were reset by the caller
+  } else {
+    RLB_CUDA(cudaMemsetAsync(words, 0, 16, st));
+  }
+  rlb::LocalizeArgs a;
+  a.num_queries = nq;
+  a.offsets = reinterpret_cast<const long long*>(d_offsets);
+  a.p2d = d_p2d;
+  a.p3d = d_p3d;
+  a.fx = d_fx;
+  a.fy = d_fy;
+  a.seeds = d_seeds;
+  a.opt = *opt;
+  a.poses = d_poses;
+  a.results = d_results;
+  a.inliers = d_inliers;
+  a.soa32 = c->loc_soa.as<float>();
+  a.lists = c->loc_lists.as<int32_t>();
+  a.npad_max = npad;
+  a.nmax = nmax;
+  a.ticket = words;
+  a.ready = pipelined ? words + 1 : nullptr;
+  a.abort_flag = words + 2;
+  RLB_CUDA(rlb::launch_localize(a, ctas, st, &c->launches_i));
+  account(c);
+  return RLB_OK;
+}
+
+}  // namespace
+
+void rlb_localize_default_options(rlb_localize_options* o, double inlier_threshold_px,
+                                  int number_lo_steps, uint32_t min_num_iterations,
+                                  uint32_t max_num_iterations) {
+  // examples/ransaclib_localization.cc:100-107
+  o->min_iters = min_num_iterations;
+  o->max_iters = max_num_iterations;
+  o->success_prob = 0.9999;
+  o->sq_thr = inlier_threshold_px * inlier_threshold_px;
+  o->lo_steps = number_lo_steps;
+  o->thr_mult = std::sqrt(2.0);
+  o->lsq_iters = 4;
+  o->min_sample_mult = 7;
+  o->non_min_sample_mult = 3;
+  o->lo_start = 60u;
+  o->final_lsq = 1;
+  o->debug_flags = 0;
+}
+
+int rlb_localize_batch_dev(rlb_ctx* c, int nq, int max_matches, const int64_t* d_offsets,
+                           const double* d_p2d, const double* d_p3d, const double* d_fx,
+                           const double* d_fy, const uint32_t* d_seeds, const rlb_localize_options* opt,
+                           double* d_poses, rlb_localize_result* d_results, int32_t* d_inliers) {
+  if (!c) return fail(RLB_E_ARG, "null context");
+  if (nq <= 0) return fail(RLB_E_ARG, "num_queries must be positive (got %d)", nq);
+  if (!d_offsets || !d_p2d || !d_p3d || !d_fx || !d_fy || !d_seeds || !d_poses || !d_results)
+    return fail(RLB_E_ARG, "null device pointer");
+  int rc = check_localize_options(opt);
+  if (rc) return rc;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  return localize_enqueue(c, c->stream, nq, max_matches, d_offsets, d_p2d, d_p3d, d_fx, d_fy, d_seeds,
+                          opt, d_poses, d_results, d_inliers, false);
+}
+
+int rlb_localize_batch(rlb_ctx* c, int nq, const int64_t* offsets, const double* p2d, const double* p3d,
+                       const double* fx, const double* fy, const uint32_t* seeds,
+                       const rlb_localize_options* opt, double* poses, rlb_localize_result* results,
+                       int32_t* inliers) {
+  if (!c) return fail(RLB_E_ARG, "null context");
+  if (nq <= 0) return fail(RLB_E_ARG, "num_queries must be positive (got %d)", nq);
+  if (!offsets || !p2d || !p3d || !fx || !fy || !seeds || !poses || !results)
+    return fail(RLB_E_ARG, "null pointer");
+  int rc = check_localize_options(opt);
+  if (rc) return rc;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (offsets[0] != 0) return fail(RLB_E_ARG, "offsets[0] must be 0");
+  int64_t max_matches = 0;
+  for (int q = 0; q < nq; ++q) {
+    const int64_t n = offsets[q + 1] - offsets[q];
+    if (n < 0 || n > 0x7fffffff) return fail(RLB_E_ARG, "query %d has %lld matches", q, (long long)n);
+    max_matches = std::max(max_matches, n);
+  }
+  const int64_t total = offsets[nq];
+  if (!c->copy_stream) {
+    RLB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    RLB_CUDA(cudaEventCreateWithFlags(&c->loc_ev[0], cudaEventDisableTiming));
+    RLB_CUDA(cudaEventCreateWithFlags(&c->loc_ev[1], cudaEventDisableTiming));
+    RLB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_ready), kMaxChunks * sizeof(unsigned int)));
+  }
+  void *d_off = nullptr, *d_p2 = nullptr, *d_p3 = nullptr, *d_f = nullptr, *d_seed = nullptr,
+       *d_pose = nullptr, *d_res = nullptr, *d_inl = nullptr;
+  auto release = [&]() {
+    for (void* p : {d_off, d_p2, d_p3, d_f, d_seed, d_pose, d_res, d_inl}) pool_release(c, p);
+  };
+  const size_t tot = static_cast<size_t>(std::max<int64_t>(total, 1));
+  rc = pool_alloc(c, (nq + 1) * sizeof(int64_t), &d_off);
+  if (!rc) rc = pool_alloc(c, tot * 2 * sizeof(double), &d_p2);
+  if (!rc) rc = pool_alloc(c, tot * 3 * sizeof(double), &d_p3);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(nq) * 2 * sizeof(double), &d_f);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(nq) * sizeof(uint32_t), &d_seed);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(nq) * 12 * sizeof(double), &d_pose);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(nq) * sizeof(rlb_localize_result), &d_res);
+  if (!rc && inliers) rc = pool_alloc(c, tot * sizeof(int32_t), &d_inl);
+  if (rc) {
+    release();
+    return rc;
+  }
+  cudaStream_t cs = c->copy_stream;
+  double* d_fx = static_cast<double*>(d_f);
+  double* d_fy = d_fx + nq;
+  RLB_CUDA(c->loc_words.ensure(64));
+  unsigned int* words = c->loc_words.as<unsigned int>();
+  // Order: whatever ran before on the compute stream -> reset of the progress words -> copies.
+  RLB_CUDA(cudaMemsetAsync(words, 0, 16, c->stream));
+  RLB_CUDA(cudaEventRecord(c->loc_ev[0], c->stream));
+  RLB_CUDA(cudaStreamWaitEvent(cs, c->loc_ev[0], 0));
+  RLB_CUDA(cudaMemcpyAsync(d_off, offsets, (nq + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, cs));
+  RLB_CUDA(cudaMemcpyAsync(d_fx, fx, nq * sizeof(double), cudaMemcpyHostToDevice, cs));
+  RLB_CUDA(cudaMemcpyAsync(d_fy, fy, nq * sizeof(double), cudaMemcpyHostToDevice, cs));
+  RLB_CUDA(cudaMemcpyAsync(d_seed, seeds, nq * sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
+  RLB_CUDA(cudaEventRecord(c->loc_ev[1], cs));
+  RLB_CUDA(cudaStreamWaitEvent(c->stream, c->loc_ev[1], 0));
+  // The kernel starts as soon as the small arrays are there; it waits per query on words[1].
+  rc = localize_enqueue(c, c->stream, nq, static_cast<int>(max_matches), static_cast<int64_t*>(d_off),
+                        static_cast<double*>(d_p2), static_cast<double*>(d_p3), d_fx, d_fy,
+                        static_cast<uint32_t*>(d_seed), opt, static_cast<double*>(d_pose),
+                        static_cast<rlb_localize_result*>(d_res), static_cast<int32_t*>(d_inl), true);
+  if (rc) {
+    cudaStreamSynchronize(cs);
+    release();
+    return rc;
+  }
+  // Upload the matches in chunks of queries (~8 MB each), publishing progress behind each chunk.
+  const int64_t chunk_rows = std::max<int64_t>((total + kMaxChunks - 1) / kMaxChunks, 200000);
+  int q0 = 0, nchunks = 0;
+  while (q0 < nq) {
+    int q1 = q0 + 1;
+    while (q1 < nq && offsets[q1 + 1] - offsets[q0] <= chunk_rows) ++q1;
+    if (nchunks == kMaxChunks - 1) q1 = nq;
+    const int64_t r0 = offsets[q0], r1 = offsets[q1];
+    if (r1 > r0) {
+      RLB_CUDA(cudaMemcpyAsync(static_cast<double*>(d_p2) + 2 * r0, p2d + 2 * r0, (r1 - r0) * 2 * sizeof(double),
+                               cudaMemcpyHostToDevice, cs));
+      RLB_CUDA(cudaMemcpyAsync(static_cast<double*>(d_p3) + 3 * r0, p3d + 3 * r0, (r1 - r0) * 3 * sizeof(double),
+                               cudaMemcpyHostToDevice, cs));
+    }
+    c->h_ready[nchunks] = static_cast<unsigned int>(q1);
+    RLB_CUDA(cudaMemcpyAsync(words + 1, &c->h_ready[nchunks], sizeof(unsigned int), cudaMemcpyHostToDevice, cs));
+    ++nchunks;
+    q0 = q1;
+  }
+  RLB_CUDA(cudaStreamSynchronize(cs));
+  RLB_CUDA(cudaMemcpyAsync(poses, d_pose, static_cast<size_t>(nq) * 12 * sizeof(double), cudaMemcpyDeviceToHost,
+                           c->stream));
+  RLB_CUDA(cudaMemcpyAsync(results, d_res, static_cast<size_t>(nq) * sizeof(rlb_localize_result),
+                           cudaMemcpyDeviceToHost, c->stream));
+  if (inliers && total > 0)
+    RLB_CUDA(cudaMemcpyAsync(inliers, d_inl, static_cast<size_t>(total) * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                             c->stream));
+  unsigned int aborted = 0;
+  RLB_CUDA(cudaMemcpyAsync(c->h_small, words + 2, 4, cudaMemcpyDeviceToHost, c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  aborted = *static_cast<unsigned int*>(c->h_small);
+  release();
+  if (aborted) return fail(RLB_E_CUDA, "localization kernel gave up waiting for the upload");
   return RLB_OK;
 }
 

@@ -1,0 +1,871 @@
+// Device-resident batched localization: whole P3P LO-MSAC runs, one query per WARP.
+//
+// SURVEY.md section 8(f) ranks 1 and 2 (device-side refinement, bit-exact device sampler) for the
+// batched ransaclib_localization workload (BASELINE configs[3]): 4096 independent queries of
+// ~2k matches each. A per-query host loop is a chain of ~100 dependent K=1 passes and ~50
+// tiny least-squares problems per local optimisation and is bound by launch + sync latency;
+// here each warp of a persistent grid takes queries from a ticket counter and runs the
+// complete control flow of LocallyOptimizedMSAC::EstimateModel on the device:
+//
+//   reference                                              here
+//   ------------------------------------------------------ --------------------------------
+//   UniformSampling (sampling.h:47-135), std::mt19937      Mt (warp-parallel twist), lemire()
+//   utils::RandomShuffleAndResize (utils.h:48-73)          shuffle_resize (sparse Fisher-Yates)
+//   MinimalSolver = P3P + 4th point (.cc:111-137)          p3pdev::p3p_pick, one sample per lane
+//   ScoreModel / GetInliers (ransac.h:295-336)             sweep32 (32 hypotheses x N, f32) +
+//                                                          fused_pass (f64, reference formula)
+//   LocalOptimization / LeastSquaresFit (ransac.h:341-420) local_optimization / score_then_fit
+//   LeastSquares (Ceres LM, .cc:170-212)                   refine::LeastSquaresWith<WarpLineariser>
+//   NumRequiredIterations (utils.h:110-140)                num_required_iterations
+//   ransaclib_localization.cc:58-165                       localize_kernel (options, <=3 matches)
+//
+// The sequence of decisions is the one of include/RansacLib/ransac.h (the host template layer):
+// speculative batches of 32 hypotheses scored in f32, every "maybe better" hypothesis settled
+// by an exact f64 pass, sequential replay of ransac.h:158-240. All f64 arithmetic is compiled
+// with -fmad=false and written in the reference's formulation, so per-point errors, inlier
+// sets, samples, shuffles and refinements are those of a strict-IEEE CPU run (sin/cos/atan2/
+// log/pow come from the CUDA math library instead of glibc: <= 2 ulp apart).
+#include <cfloat>
+#include <climits>
+
+#include "../../examples/pose_refinement.h"
+#include "p3p_device.cuh"
+#include "rlb_internal.cuh"
+
+namespace rlb {
+
+namespace {
+
+namespace refine = ransac_lib::calibrated_absolute_pose::refine;
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kWarpsPerCta = 4;
+constexpr int kSlabDoubles = 32 * 14;  // residual rows of one 32-point chunk: 2 x (value + 6 partials)
+
+// ----------------------------------------------------------------- std::mt19937
+struct Mt {
+  uint32_t* s;  // 624 words of shared memory
+  int idx;      // next word to temper; 624 = exhausted (state right after seed())
+};
+
+// std::mt19937::seed(value): s[i] = 1812433253 * (s[i-1] ^ (s[i-1] >> 30)) + i.
+__device__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
+  if (lane == 0) {
+    uint32_t x = seed;
+    s[0] = x;
+    for (int i = 1; i < 624; ++i) {
+      x = 1812433253u * (x ^ (x >> 30)) + static_cast<uint32_t>(i);
+      s[i] = x;
+    }
+  }
+  __syncwarp();
+}
+
+// Regenerates the 624 words in place, 32 per round: word k needs the OLD k, k+1 and either the
+// old k+397 (k < 227) or the NEW k-227, which earlier rounds have already written.
+__device__ void mt_twist(uint32_t* s, int lane) {
+  for (int base = 0; base < 623; base += 32) {
+    const int k = base + lane;
+    uint32_t v = 0;
+    if (k < 623) {
+      const uint32_t y = (s[k] & 0x80000000u) | (s[k + 1] & 0x7fffffffu);
+      const uint32_t src = (k < 227) ? s[k + 397] : s[k - 227];
+      v = src ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+    }
+    __syncwarp();
+    if (k < 623) s[k] = v;
+    __syncwarp();
+  }
+  if (lane == 0) {
+    const uint32_t y = (s[623] & 0x80000000u) | (s[0] & 0x7fffffffu);
+    s[623] = s[396] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
+  y ^= y >> 11;
+  y ^= (y << 7) & 0x9d2c5680u;
+  y ^= (y << 15) & 0xefc60000u;
+  y ^= y >> 18;
+  return y;
+}
+
+// Next 32-bit draw; warp-uniform (every lane reads the same word).
+__device__ uint32_t mt_next(Mt& r, int lane) {
+  if (r.idx >= 624) {
+    mt_twist(r.s, lane);
+    r.idx = 0;
+  }
+  return mt_temper(r.s[r.idx++]);
+}
+
+// libstdc++ std::uniform_int_distribution<int> on a 32-bit engine (bits/uniform_int_dist.h,
+// GCC >= 11): Lemire's multiply-shift with rejection. Returns a value in [0, range).
+__device__ uint32_t lemire(Mt& r, uint32_t range, int lane) {
+  unsigned long long prod = static_cast<unsigned long long>(mt_next(r, lane)) * range;
+  uint32_t low = static_cast<uint32_t>(prod);
+  if (low < range) {
+    const uint32_t thresh = (0u - range) % range;
+    while (low < thresh) {
+      prod = static_cast<unsigned long long>(mt_next(r, lane)) * range;
+      low = static_cast<uint32_t>(prod);
+    }
+  }
+  return static_cast<uint32_t>(prod >> 32);
+}
+
+// One minimal sample of 4 distinct indices (sampling.h:58-110), warp-uniform.
+__device__ void draw_sample4(Mt& r, int n, int* s, int lane) {
+  const double ratio = static_cast<double>(n) / static_cast<double>(n - 4);
+  if (ratio < 2.718281828459045235360287471352662498 /* M_E */) {
+    for (int i = 0; i < 4; ++i) {
+      bool again = true;
+      while (again) {
+        s[i] = static_cast<int>(lemire(r, static_cast<uint32_t>(n), lane));
+        again = false;
+        for (int j = 0; j < i; ++j) again = again || (s[j] == s[i]);
+      }
+    }
+    return;
+  }
+  // Shuffle path: only n in {4, 5, 6} gets here (n / (n - 4) >= e).
+  int a[8];
+  for (int i = 0; i < 8; ++i) a[i] = i;
+  if (n != 4) {
+    for (int i = 0; i + 1 < n; ++i) {
+      const int j = i + static_cast<int>(lemire(r, static_cast<uint32_t>(n - i), lane));
+      int ai = 0, aj = 0;
+      for (int q = 0; q < 8; ++q) {  // register-resident: no dynamic indexing
+        ai = (q == i) ? a[q] : ai;
+        aj = (q == j) ? a[q] : aj;
+      }
+      for (int q = 0; q < 8; ++q) a[q] = (q == i) ? aj : ((q == j) ? ai : a[q]);
+    }
+  }
+  for (int i = 0; i < 4; ++i) s[i] = a[i];
+}
+
+// utils::RandomShuffleAndResize(target, rng, &copy_of(list[0..n))) -> samp[0..target) (shared).
+// The reference shuffles the WHOLE list (n-1 draws, Fisher-Yates from the front) and keeps the
+// first `target` entries; only the first min(target, n-1) steps can touch those, so they are
+// resolved on a sparse view of the list (lane l holds head position l; positions beyond the
+// head live in at most one (pos,val) entry per step), and the remaining steps only consume
+// their draws: 32 steps per round, each lane testing its own draw for a Lemire rejection
+// (probability range / 2^32); a rejection drops that one step to the sequential path.
+// target <= 32. Entries past n (resize growing the vector) are 0 like std::vector::resize.
+__device__ void shuffle_resize(Mt& r, const int32_t* list, int n, int target, int32_t* samp,
+                               int lane, bool force_slow) {
+  const int steps = (n > 0) ? n - 1 : 0;
+  const int head_n = min(target, n);
+  const int t_steps = min(target, steps);
+  int my_j = -1;
+  for (int i = 0; i < t_steps; ++i) {
+    const int j = i + static_cast<int>(lemire(r, static_cast<uint32_t>(n - i), lane));
+    if (lane == i) my_j = j;
+  }
+  int head = (lane < head_n) ? list[lane] : 0;
+  const int pre = (lane < t_steps && my_j >= head_n) ? list[my_j] : 0;
+  int pos = -1, val = 0;
+  for (int i = 0; i < t_steps; ++i) {
+    const int j = __shfl_sync(kFull, my_j, i);
+    const int a = __shfl_sync(kFull, head, i);
+    int b;
+    if (j < head_n) {
+      b = __shfl_sync(kFull, head, j);
+      if (lane == j) head = a;
+    } else {
+      const unsigned match = __ballot_sync(kFull, pos == j);
+      if (match) {
+        const int m = __ffs(match) - 1;
+        b = __shfl_sync(kFull, val, m);
+        if (lane == m) val = a;
+      } else {
+        b = __shfl_sync(kFull, pre, i);
+        if (lane == i) {
+          pos = j;
+          val = a;
+        }
+      }
+    }
+    if (lane == i) head = b;
+  }
+  // draws of the steps that cannot reach the kept prefix
+  int i = t_steps;
+  int remaining = steps - t_steps;
+  while (remaining > 0) {
+    if (r.idx >= 624) {
+      mt_twist(r.s, lane);
+      r.idx = 0;
+    }
+    const int chunk = min(min(32, remaining), 624 - r.idx);
+    bool rej = false;
+    if (lane < chunk) {
+      const uint32_t range = static_cast<uint32_t>(n - (i + lane));
+      const unsigned long long prod =
+          static_cast<unsigned long long>(mt_temper(r.s[r.idx + lane])) * range;
+      const uint32_t low = static_cast<uint32_t>(prod);
+      if (low < range) rej = low < ((0u - range) % range);
+    }
+    unsigned m = __ballot_sync(kFull, rej);
+    if (force_slow) m |= 1u;
+    if (m == 0u) {
+      r.idx += chunk;
+      i += chunk;
+      remaining -= chunk;
+    } else {
+      const int f = __ffs(m) - 1;
+      r.idx += f;
+      i += f;
+      remaining -= f;
+      (void)lemire(r, static_cast<uint32_t>(n - i), lane);  // this step, exactly
+      i += 1;
+      remaining -= 1;
+    }
+  }
+  __syncwarp();
+  if (lane < target) samp[lane] = (lane < head_n) ? head : 0;
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------ one query
+struct Query {
+  int n;
+  const double* p2;  // n x 2 (reference layout)
+  const double* p3;  // n x 3
+  double fx, fy;
+  float* soa32;      // [5][npad]: X-cx, Y-cy, Z-cz, -u, -v; padding 0,0,0,NaN,NaN
+  int npad;          // multiple of 4
+  double centre[3];
+};
+
+struct WarpShared {
+  uint32_t mt_sampler[624];
+  uint32_t mt_lo[624];
+  double slab[kSlabDoubles];
+  double sums[32];
+  int32_t samp[32];
+};
+
+constexpr double kNever = DBL_MAX;
+
+// Warp-wide sum, identical bits in every lane (commutative butterfly).
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  return v;
+}
+
+
+// Recentred f32 copy of the query's matches for the 32-hypothesis sweeps.
+__device__ void prepare_soa32(Query& q, int lane) {
+  double c[3] = {0.0, 0.0, 0.0};
+  const int take = min(q.n, 32);
+  if (lane < take) {
+    const int i = static_cast<int>(static_cast<long long>(lane) * q.n / take);
+    c[0] = q.p3[3 * static_cast<size_t>(i)];
+    c[1] = q.p3[3 * static_cast<size_t>(i) + 1];
+    c[2] = q.p3[3 * static_cast<size_t>(i) + 2];
+  }
+  for (int k = 0; k < 3; ++k) q.centre[k] = warp_sum(c[k]) / static_cast<double>(take);
+  for (int i = lane; i < q.npad; i += 32) {
+    const bool live = i < q.n;
+    const float nanv = __int_as_float(0x7fc00000);
+    q.soa32[0 * q.npad + i] = live ? static_cast<float>(q.p3[3 * static_cast<size_t>(i)] - q.centre[0]) : 0.0f;
+    q.soa32[1 * q.npad + i] = live ? static_cast<float>(q.p3[3 * static_cast<size_t>(i) + 1] - q.centre[1]) : 0.0f;
+    q.soa32[2 * q.npad + i] = live ? static_cast<float>(q.p3[3 * static_cast<size_t>(i) + 2] - q.centre[2]) : 0.0f;
+    q.soa32[3 * q.npad + i] = live ? -static_cast<float>(q.p2[2 * static_cast<size_t>(i)]) : nanv;
+    q.soa32[4 * q.npad + i] = live ? -static_cast<float>(q.p2[2 * static_cast<size_t>(i) + 1]) : nanv;
+  }
+  __syncwarp();
+}
+
+// MSAC score of THIS LANE's hypothesis over all matches in f32 (ransac.h:295-309 with the
+// f32 deviations documented in DESIGN.md section 3): every lane reads the same match
+// (broadcast), 4 matches per vector load; f32 sums are flushed into f64 every 512 matches.
+__device__ double sweep32(const Query& q, const double* P, double thr64) {
+  // p = R (X - c) = R (X - centre) + R (centre - c); rows 0/1 pre-scaled by fx/fy.
+  const double dc[3] = {q.centre[0] - P[9], q.centre[1] - P[10], q.centre[2] - P[11]};
+  const double sc[3] = {q.fx, q.fy, 1.0};
+  float r[9], t[3];
+#pragma unroll
+  for (int row = 0; row < 3; ++row) {
+    const double r0 = P[row], r1 = P[row + 3], r2 = P[row + 6];
+    r[3 * row + 0] = static_cast<float>(r0 * sc[row]);
+    r[3 * row + 1] = static_cast<float>(r1 * sc[row]);
+    r[3 * row + 2] = static_cast<float>(r2 * sc[row]);
+    t[row] = static_cast<float>((r0 * dc[0] + r1 * dc[1] + r2 * dc[2]) * sc[row]);
+  }
+  const float thr = static_cast<float>(thr64);
+  const int groups = q.npad >> 2;
+  const float4* X = reinterpret_cast<const float4*>(q.soa32);
+  const float4* Y = reinterpret_cast<const float4*>(q.soa32 + q.npad);
+  const float4* Z = reinterpret_cast<const float4*>(q.soa32 + 2 * q.npad);
+  const float4* U = reinterpret_cast<const float4*>(q.soa32 + 3 * q.npad);
+  const float4* V = reinterpret_cast<const float4*>(q.soa32 + 4 * q.npad);
+  double total = 0.0;
+  for (int g0 = 0; g0 < groups; g0 += 128) {
+    const int g1 = min(groups, g0 + 128);
+    float s = 0.0f;
+    int c = 0;
+    for (int g = g0; g < g1; ++g) {
+      const float4 x = X[g], y = Y[g], z = Z[g], u = U[g], v = V[g];
+      const float xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
+      const float zs[4] = {z.x, z.y, z.z, z.w}, us[4] = {u.x, u.y, u.z, u.w};
+      const float vs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float pz = fmaf(r[6], xs[e], fmaf(r[7], ys[e], fmaf(r[8], zs[e], t[2])));
+        const float px = fmaf(r[0], xs[e], fmaf(r[1], ys[e], fmaf(r[2], zs[e], t[0])));
+        const float py = fmaf(r[3], xs[e], fmaf(r[4], ys[e], fmaf(r[5], zs[e], t[1])));
+        float inv;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(fmaxf(pz, 0.0f)));
+        const float du = fmaf(px, inv, us[e]);
+        const float dv = fmaf(py, inv, vs[e]);
+        const float err = fmaf(du, du, dv * dv);
+        if (err < thr) {
+          s += err;
+          c += 1;
+        }
+      }
+    }
+    const int live = max(0, min(q.n, 4 * g1) - 4 * g0);
+    total += static_cast<double>(s) + thr64 * static_cast<double>(live - c);
+  }
+  return total;
+}
+
+// ScoreModel fused with GetInliers for ONE model (ransac.h:295-336), reference formulation
+// (calibrated_absolute_pose_estimator.cc:154-167): lane l evaluates matches l, l+32, ...;
+// the ascending inlier list is compacted with a ballot per 32 matches.
+__device__ int fused_pass(const Query& q, const double* P, double thr_inl, bool want_score,
+                          double thr_score, int32_t* list, double* score, int lane) {
+  int off = 0;
+  double sc = 0.0;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int base = 0; base < q.n; base += 32) {
+    const int i = base + lane;
+    const bool live = i < q.n;
+    double e = DBL_MAX;
+    if (live) {
+      e = p3pdev::reproj_sq_error(P, q.p3 + 3 * static_cast<size_t>(i), q.p2 + 2 * static_cast<size_t>(i),
+                                  q.fx, q.fy);
+      if (want_score) sc += (thr_score < e) ? thr_score : e;  // std::min(e, thr): NaN propagates
+    }
+    const bool in = live && (e < thr_inl);
+    const unsigned mask = __ballot_sync(kFull, in);
+    if (in && list != nullptr) list[off + __popc(mask & lt)] = i;
+    off += __popc(mask);
+  }
+  if (want_score) *score = warp_sum(sc);
+  __syncwarp();
+  return off;
+}
+
+// Lineariser of the pose LM with one match per lane (see refine::SequentialLineariser for the
+// arithmetic it reproduces): residual rows go to the shared slab, then lane e < 27 owns one
+// entry of (J^T r, lower triangle of J^T J) and lane 27 the cost, each adding the chunk's
+// contributions in match order, so every sum has the host's order of operations.
+struct WarpLineariser {
+  int k;
+  const int32_t* idx;  // sample (shared or global), k entries
+  const double* p2d;
+  const double* p3d;
+  double fx, fy;
+  double* slab;  // [32][14]
+  double* sums;  // [28]
+  int lane;
+
+  RLB_HD double Cost(const double* c) const {
+#ifdef __CUDA_ARCH__
+    refine::Value cam[6];
+    for (int i = 0; i < 6; ++i) cam[i] = refine::Value::Constant(c[i]);
+    double cost = 0.0;
+    for (int base = 0; base < k; base += 32) {
+      const int s = base + lane;
+      double mine = 0.0;
+      if (s < k) {
+        const int i = idx[s];
+        refine::Value r[2];
+        refine::Residual(cam, p2d[2 * static_cast<size_t>(i)], p2d[2 * static_cast<size_t>(i) + 1],
+                         p3d[3 * static_cast<size_t>(i)], p3d[3 * static_cast<size_t>(i) + 1],
+                         p3d[3 * static_cast<size_t>(i) + 2], fx, fy, r);
+        mine = 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
+      }
+      const int m = min(32, k - base);
+      for (int j = 0; j < m; ++j) cost += __shfl_sync(kFull, mine, j);
+    }
+    return cost;
+#else
+    (void)c;
+    return 0.0;
+#endif
+  }
+
+  RLB_HD double Full(const double* c, double* JtJ, double* Jtr) const {
+#ifdef __CUDA_ARCH__
+    refine::Dual cam[6];
+    for (int i = 0; i < 6; ++i) cam[i] = refine::Dual::Variable(c[i], i);
+    // entry owned by this lane: 0..5 = Jtr[a]; 6..26 = JtJ[a][b], b <= a; 27 = cost
+    int ea = 0, eb = 0;
+    if (lane < 6) {
+      ea = lane;
+    } else if (lane < 27) {
+      int t = lane - 6;
+      while (t >= ea + 1) {
+        t -= ea + 1;
+        ++ea;
+      }
+      eb = t;
+    }
+    double acc = 0.0;
+    for (int base = 0; base < k; base += 32) {
+      const int s = base + lane;
+      __syncwarp();
+      if (s < k) {
+        const int i = idx[s];
+        refine::Dual r[2];
+        refine::Residual(cam, p2d[2 * static_cast<size_t>(i)], p2d[2 * static_cast<size_t>(i) + 1],
+                         p3d[3 * static_cast<size_t>(i)], p3d[3 * static_cast<size_t>(i) + 1],
+                         p3d[3 * static_cast<size_t>(i) + 2], fx, fy, r);
+        double* row = slab + 14 * lane;
+        for (int e = 0; e < 2; ++e) {
+          row[7 * e] = r[e].a;
+          for (int a = 0; a < 6; ++a) row[7 * e + 1 + a] = r[e].d[a];
+        }
+      }
+      __syncwarp();
+      const int m = min(32, k - base);
+      if (lane < 6) {
+        for (int j = 0; j < m; ++j) {
+          const double* row = slab + 14 * j;
+          acc += row[1 + ea] * row[0];
+          acc += row[8 + ea] * row[7];
+        }
+      } else if (lane < 27) {
+        for (int j = 0; j < m; ++j) {
+          const double* row = slab + 14 * j;
+          acc += row[1 + ea] * row[1 + eb];
+          acc += row[8 + ea] * row[8 + eb];
+        }
+      } else if (lane == 27) {
+        for (int j = 0; j < m; ++j) {
+          const double* row = slab + 14 * j;
+          acc += 0.5 * (row[0] * row[0] + row[7] * row[7]);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane < 28) sums[lane] = acc;
+    __syncwarp();
+    for (int a = 0; a < 6; ++a) Jtr[a] = sums[a];
+    int t = 6;
+    for (int a = 0; a < 6; ++a)
+      for (int b = 0; b <= a; ++b) {
+        const double v = sums[t++];
+        JtJ[6 * a + b] = v;
+        JtJ[6 * b + a] = v;
+      }
+    const double cost = sums[27];
+    __syncwarp();
+    return cost;
+#else
+    (void)c;
+    (void)JtJ;
+    (void)Jtr;
+    return 0.0;
+#endif
+  }
+};
+
+// --------------------------------------------------------- LO-MSAC control flow
+struct Run {
+  Query q;
+  rlb_localize_options opt;
+  Mt sampler;
+  Mt lo_rng;
+  WarpShared* sh;
+  int32_t* list_best;  // stats.inlier_indices
+  int32_t* list_base;  // LocalOptimization's inliers_base
+  int32_t* list_fit;   // inliers of the current fit / scratch
+  int lane;
+  bool force_slow;
+  // counters (reported per query)
+  int passes;
+  int lsq_calls;
+};
+
+// utils.h:110-140.
+__device__ uint32_t num_required_iterations(double inlier_ratio, double prob_missing, int sample_size,
+                                            uint32_t min_it, uint32_t max_it) {
+  if (inlier_ratio <= 0.0) return max_it;
+  if (inlier_ratio >= 1.0) return min_it;
+  const double prob_bad = 1.0 - pow(inlier_ratio, static_cast<double>(sample_size));
+  if (prob_bad >= 0.99999999999999) return max_it;
+  const double needed = ceil(log(prob_missing) / log(prob_bad) + 0.5);
+  const uint32_t nd = static_cast<uint32_t>(needed);
+  return max(min_it, min(nd, max_it));
+}
+
+__device__ __forceinline__ void update_best(double score, const double* m, double* best_score,
+                                            double* best) {
+  if (score < *best_score) {  // strict: the earlier model keeps ties (ransac.h:422-428)
+    *best_score = score;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) best[i] = m[i];
+  }
+}
+
+// CalibratedAbsolutePoseEstimator::LeastSquares on sample idx[0..k).
+__device__ void least_squares(Run& R, const int32_t* idx, int k, double* pose) {
+  WarpLineariser lin;
+  lin.k = k;
+  lin.idx = idx;
+  lin.p2d = R.q.p2;
+  lin.p3d = R.q.p3;
+  lin.fx = R.q.fx;
+  lin.fy = R.q.fy;
+  lin.slab = R.sh->slab;
+  lin.sums = R.sh->sums;
+  lin.lane = R.lane;
+  refine::LeastSquaresWith(lin, pose);
+  ++R.lsq_calls;
+}
+
+// P3P on sample[0..2] + consistency with sample[3] (calibrated_absolute_pose_estimator.cc:111-137).
+__device__ bool minimal_solver(const Query& q, const int* s, double sq_thr, double* P) {
+  double y[9], x[9];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    // PixelsToViewingRays (.cc:214-227)
+    const double rx = q.p2[2 * static_cast<size_t>(s[j])] / q.fx;
+    const double ry = q.p2[2 * static_cast<size_t>(s[j]) + 1] / q.fy;
+    const double rz = 1.0;
+    const double nrm = sqrt(rx * rx + ry * ry + rz * rz);
+    y[3 * j] = rx / nrm;
+    y[3 * j + 1] = ry / nrm;
+    y[3 * j + 2] = rz / nrm;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) x[3 * j + c] = q.p3[3 * static_cast<size_t>(s[j]) + c];
+  }
+  const double* X4 = q.p3 + 3 * static_cast<size_t>(s[3]);
+  const double* uv4 = q.p2 + 2 * static_cast<size_t>(s[3]);
+  return p3pdev::p3p_pick(y, x, X4, uv4, q.fx, q.fy, sq_thr, P);
+}
+
+// [ScoreModel(m) + UpdateBestModel] fused with the LeastSquaresFit(fit_thr, m) that follows it
+// (ransac.h:409-420; include/RansacLib/ransac.h ScoreThenFit).
+__device__ void score_then_fit(Run& R, bool want_score, double fit_thr, double* m, double* best_score,
+                               double* best) {
+  const double thr = R.opt.sq_thr;
+  double score = kNever;
+  const int n_inl = fused_pass(R.q, m, fit_thr, want_score, thr, R.list_fit, &score, R.lane);
+  ++R.passes;
+  if (want_score) update_best(score, m, best_score, best);
+  if (n_inl < 4) return;
+  const int cap = R.opt.min_sample_mult * 4;
+  const int target = min(cap, n_inl);
+  shuffle_resize(R.lo_rng, R.list_fit, n_inl, target, R.sh->samp, R.lane, R.force_slow);
+  least_squares(R, R.sh->samp, target, m);
+}
+
+// Algorithms 2 and 3 of Lebeda et al. in the order of ransac.h:341-407.
+__device__ void local_optimization(Run& R, double* best_minimal_model, double* score_best_minimal) {
+  const int n = R.q.n;
+  if (6 > n) return;  // non_minimal_sample_size() (.h:90)
+  const double thr = R.opt.sq_thr;
+  const double mult = R.opt.thr_mult;
+
+  double m_init[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) m_init[i] = best_minimal_model[i];
+  score_then_fit(R, false, thr * mult, m_init, nullptr, nullptr);
+
+  double score = kNever;
+  const int n_base = fused_pass(R.q, m_init, thr * mult, true, thr, R.list_base, &score, R.lane);
+  ++R.passes;
+  update_best(score, m_init, score_best_minimal, best_minimal_model);
+
+  const int non_min_size = max(6, min(4 * R.opt.non_min_sample_mult, n_base / 2));
+  for (int r = 0; r < R.opt.lo_steps; ++r) {
+    shuffle_resize(R.lo_rng, R.list_base, n_base, non_min_size, R.sh->samp, R.lane, R.force_slow);
+    // NonMinimalSolver (.cc:141-151): minimal solver on the first four, then LeastSquares.
+    int s4[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s4[i] = R.sh->samp[i];
+    double m[12];
+    if (!minimal_solver(R.q, s4, thr, m)) continue;
+    least_squares(R, R.sh->samp, non_min_size, m);
+
+    score_then_fit(R, true, thr, m, score_best_minimal, best_minimal_model);  // ransac.h:386-391
+    double fit_thr = mult * thr;
+    // Reference divides by (num_lsq_iterations_ - 1) as an int (ransac.h:395-397).
+    const double step = (mult - 1.0) * thr / static_cast<double>(R.opt.lsq_iters - 1);
+    if (R.opt.lsq_iters <= 0) continue;
+    score_then_fit(R, false, fit_thr, m, nullptr, nullptr);
+    for (int i = 0; i < R.opt.lsq_iters; ++i) {
+      fit_thr -= step;
+      if (i + 1 < R.opt.lsq_iters) {
+        score_then_fit(R, true, fit_thr, m, score_best_minimal, best_minimal_model);
+      } else {
+        double sc = kNever;
+        fused_pass(R.q, m, thr, true, thr, nullptr, &sc, R.lane);
+        ++R.passes;
+        update_best(sc, m, score_best_minimal, best_minimal_model);
+      }
+    }
+  }
+}
+
+// LocallyOptimizedMSAC::EstimateModel (ransac.h:128-275) as driven by
+// ransaclib_localization (examples/ransaclib_localization.cc:58-165), for one query.
+__device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) {
+  const int lane = R.lane;
+  const rlb_localize_options& o = R.opt;
+  const int n = R.q.n;
+  const double thr = o.sq_thr;
+
+  uint32_t num_iterations = 0u;
+  int best_num_inliers = 0;
+  double best_model_score = kNever;
+  double inlier_ratio = 0.0;
+  int num_lo = 0;
+
+  uint32_t max_iters = max(o.max_iters, o.min_iters);
+  double best_minimal_model[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) best_minimal_model[i] = 0.0;
+  double best_minimal_score = kNever;
+
+  // this lane's hypothesis of the current speculative batch
+  uint32_t batch_first = 0u, batch_count = 0u;
+  double my_model[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) my_model[i] = 0.0;
+  bool my_valid = false;
+  double my_score = kNever;
+
+  auto refresh_termination = [&]() {  // ransac.h:170-177, 231-238
+    best_num_inliers = fused_pass(R.q, best_model, thr, false, thr, R.list_best, nullptr, lane);
+    ++R.passes;
+    inlier_ratio = static_cast<double>(best_num_inliers) / static_cast<double>(n);
+    max_iters = num_required_iterations(inlier_ratio, 1.0 - o.success_prob, 4, o.min_iters, o.max_iters);
+  };
+
+  for (num_iterations = 0u; num_iterations < max_iters; ++num_iterations) {
+    const uint32_t it = num_iterations;
+    if (it == o.lo_start && best_minimal_score < kNever) {  // ransac.h:163-178
+      ++num_lo;
+      local_optimization(R, best_model, &best_model_score);
+      refresh_termination();
+    }
+
+    if (it >= batch_first + batch_count) {
+      // Speculate on the next (up to) 32 iterations: samples are a pure function of the
+      // sampler stream, hypotheses do not depend on the LO stream.
+      const uint32_t bound = max(max_iters, it + 1u);
+      batch_first = it;
+      batch_count = min(32u, bound - it);
+      int mine[4] = {0, 0, 0, 0};
+      for (uint32_t k = 0; k < batch_count; ++k) {
+        int s[4];
+        draw_sample4(R.sampler, n, s, lane);
+        if (static_cast<uint32_t>(lane) == k) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mine[j] = s[j];
+        }
+      }
+      my_valid = false;
+      my_score = kNever;
+      if (static_cast<uint32_t>(lane) < batch_count) {
+        my_valid = minimal_solver(R.q, mine, thr, my_model);
+        if (my_valid) {
+          bool finite = true;
+#pragma unroll
+          for (int i = 0; i < 12; ++i) finite = finite && (my_model[i] - my_model[i] == 0.0);
+          // a model with a non-finite entry scores NaN and never wins (finalize_kernel)
+          my_score = finite ? sweep32(R.q, my_model, thr) : __longlong_as_double(0x7ff8000000000000LL);
+        }
+      }
+      __syncwarp();
+    }
+
+    const int slot = static_cast<int>(it - batch_first);
+    if (!__shfl_sync(kFull, my_valid ? 1 : 0, slot)) continue;  // ransac.h:185
+
+    double local_score = kNever;
+    const double s32 = __shfl_sync(kFull, my_score, slot);
+    const bool have = s32 < kNever;  // GetBestEstimatedModelId: NaN never becomes the local best
+    if (have) local_score = s32;
+    const bool forced = (it == o.lo_start);
+    double cand[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) cand[i] = __shfl_sync(kFull, my_model[i], slot);
+    if (have && (forced || local_score <= best_minimal_score * (1.0 + 4e-4) ||
+                 best_minimal_score == kNever)) {
+      // the f32 sweep says "maybe better": settle it with the exact f64 score
+      fused_pass(R.q, cand, thr, true, thr, nullptr, &local_score, lane);
+      ++R.passes;
+    }
+
+    if (local_score < best_minimal_score || forced) {  // ransac.h:195-196
+      const bool new_best = local_score < best_minimal_score;
+      if (new_best) {
+        best_minimal_score = local_score;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) best_minimal_model[i] = cand[i];
+        update_best(best_minimal_score, best_minimal_model, &best_model_score, best_model);
+      }
+      const bool run_lo = (it >= o.lo_start && best_minimal_score < kNever);
+      if (!new_best && !run_lo) continue;
+      if (run_lo) {
+        ++num_lo;
+        double score = best_minimal_score;
+        local_optimization(R, best_minimal_model, &score);
+        update_best(score, best_minimal_model, &best_model_score, best_model);
+      }
+      refresh_termination();
+    }
+  }
+
+  // LO for runs that ended before the start iteration (ransac.h:245-255).
+  if (num_iterations <= o.lo_start && best_model_score < kNever) {
+    ++num_lo;
+    local_optimization(R, best_model, &best_model_score);
+    best_num_inliers = fused_pass(R.q, best_model, thr, false, thr, R.list_best, nullptr, lane);
+    ++R.passes;
+    inlier_ratio = static_cast<double>(best_num_inliers) / static_cast<double>(n);
+  }
+
+  if (o.final_lsq) {  // ransac.h:257-272
+    double refined[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) refined[i] = best_model[i];
+    least_squares(R, R.list_best, best_num_inliers, refined);
+    double score = kNever;
+    const int n_inl = fused_pass(R.q, refined, thr, true, thr, R.list_fit, &score, lane);
+    ++R.passes;
+    if (score < best_model_score) {
+      best_model_score = score;
+#pragma unroll
+      for (int i = 0; i < 12; ++i) best_model[i] = refined[i];
+      best_num_inliers = n_inl;
+      for (int i = lane; i < n_inl; i += 32) R.list_best[i] = R.list_fit[i];
+      inlier_ratio = static_cast<double>(n_inl) / static_cast<double>(n);
+    }
+  }
+  __syncwarp();
+  if (lane == 0) {
+    res->success = 1;
+    res->num_inliers = best_num_inliers;
+    res->num_iterations = num_iterations;
+    res->num_lo = num_lo;
+    res->score = best_model_score;
+    res->inlier_ratio = inlier_ratio;
+    res->passes = R.passes;
+    res->lsq_calls = R.lsq_calls;
+  }
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) localize_kernel(const LocalizeArgs A) {
+  __shared__ WarpShared shared[kWarpsPerCta];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int slot = blockIdx.x * kWarpsPerCta + warp;
+
+  Run R;
+  R.opt = A.opt;
+  R.sh = &shared[warp];
+  R.lane = lane;
+  R.force_slow = (A.opt.debug_flags & 1) != 0;
+  R.q.soa32 = A.soa32 + static_cast<size_t>(slot) * 5 * A.npad_max;
+  int32_t* lists = A.lists + static_cast<size_t>(slot) * 3 * A.nmax;
+  R.list_base = lists;
+  R.list_fit = lists + A.nmax;
+
+  for (;;) {
+    int qi = 0;
+    if (lane == 0) qi = static_cast<int>(atomicAdd(A.ticket, 1u));
+    qi = __shfl_sync(kFull, qi, 0);
+    if (qi >= A.num_queries) break;
+    if (A.ready != nullptr) {
+      // The upload of this query's matches may still be in flight (pipelined host API).
+      bool ok = true;
+      if (lane == 0) {
+        const long long t0 = clock64();
+        while (*A.ready <= static_cast<unsigned int>(qi)) {
+          __nanosleep(2000);
+          if (clock64() - t0 > 20000000000LL) {  // ~10 s: the host side died, do not hang the GPU
+            ok = false;
+            atomicExch(A.abort_flag, 1u);
+            break;
+          }
+        }
+        __threadfence();
+      }
+      ok = __shfl_sync(kFull, ok ? 1 : 0, 0) != 0;
+      if (!ok) break;
+    }
+
+    const long long o0 = A.offsets[qi], o1 = A.offsets[qi + 1];
+    const int n = static_cast<int>(o1 - o0);
+    rlb_localize_result* res = A.results + qi;
+    double* pose_out = A.poses + 12 * static_cast<size_t>(qi);
+    if (n <= 3) {  // ransaclib_localization.cc:86-92: nothing to estimate
+      if (lane == 0) {
+        res->success = 0;
+        res->num_inliers = 0;
+        res->num_iterations = 0u;
+        res->num_lo = 0;
+        res->score = kNever;
+        res->inlier_ratio = 0.0;
+        res->passes = 0;
+        res->lsq_calls = 0;
+      }
+      if (lane < 12) pose_out[lane] = 0.0;
+      continue;
+    }
+    R.q.n = n;
+    R.q.p2 = A.p2d + 2 * static_cast<size_t>(o0);
+    R.q.p3 = A.p3d + 3 * static_cast<size_t>(o0);
+    R.q.fx = A.fx[qi];
+    R.q.fy = A.fy[qi];
+    R.q.npad = (n + 3) & ~3;
+    R.list_best = (A.inliers != nullptr) ? A.inliers + o0 : lists + 2 * A.nmax;
+    R.passes = 0;
+    R.lsq_calls = 0;
+    prepare_soa32(R.q, lane);
+
+    // Sampler and local optimisation own separate engines seeded alike (ransac.h:142-144,
+    // sampling.h:49-55).
+    mt_seed(R.sh->mt_sampler, A.seeds[qi], lane);
+    for (int i = lane; i < 624; i += 32) R.sh->mt_lo[i] = R.sh->mt_sampler[i];
+    __syncwarp();
+    R.sampler.s = R.sh->mt_sampler;
+    R.sampler.idx = 624;
+    R.lo_rng.s = R.sh->mt_lo;
+    R.lo_rng.idx = 624;
+
+    double best_model[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) best_model[i] = 0.0;
+    run_query(R, best_model, res);
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 12; ++i) pose_out[i] = best_model[i];
+    }
+    __syncwarp();
+  }
+}
+
+cudaError_t launch_localize(const LocalizeArgs& a, int ctas, cudaStream_t st, int* launches) {
+  ++*launches;
+  localize_kernel<<<ctas, kWarpsPerCta * 32, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+int localize_warps_per_cta() { return kWarpsPerCta; }
+
+}  // namespace rlb

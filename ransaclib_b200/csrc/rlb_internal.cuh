@@ -106,6 +106,32 @@ cudaError_t launch_solve_point_normal(const DeviceData& d, int k, const int32_t*
 cudaError_t launch_solve_p3p(const DeviceData& d, int k, const int32_t* samples, double sq_thr,
                              double* models, uint8_t* valid, cudaStream_t st, int* launches);
 
+// Device-resident batched localization (localize_kernels.cu, -fmad=false).
+struct LocalizeArgs {
+  int num_queries;
+  const long long* offsets;  // [Q + 1]
+  const double* p2d;         // [total][2]
+  const double* p3d;         // [total][3]
+  const double* fx;          // [Q]
+  const double* fy;
+  const uint32_t* seeds;
+  rlb_localize_options opt;
+  double* poses;                 // [Q][12]
+  rlb_localize_result* results;  // [Q]
+  int32_t* inliers;              // [total] or nullptr
+  // scratch, one slot per resident warp
+  float* soa32;    // [slots][5][npad_max]
+  int32_t* lists;  // [slots][3][nmax]
+  int npad_max, nmax;
+  unsigned int* ticket;  // query counter, zero before the launch
+  // Host-pointer API: number of queries whose matches have landed in HBM so far (written by
+  // stream-ordered 4-byte copies behind each chunk of the upload); nullptr = all resident.
+  const volatile unsigned int* ready;
+  unsigned int* abort_flag;  // set when a warp gave up waiting for `ready`
+};
+cudaError_t launch_localize(const LocalizeArgs& a, int ctas, cudaStream_t st, int* launches);
+int localize_warps_per_cta();
+
 inline int model_size_of(int kind) { return kind == RLB_KIND_POSE ? 12 : 3; }
 
 }  // namespace rlb

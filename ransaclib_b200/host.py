@@ -195,3 +195,46 @@ def localize(focal_x, focal_y, points2D, points3D, inlier_threshold, number_lo_s
         return {"success": False}
     return {"success": True, "qvec": q, "tvec": t, "num_inliers": int(ninl.value),
             "inliers": inl[:ninl.value].tolist(), "_stats": _stats_dict(st, inl)}
+
+
+def localize_batch(focal_x, focal_y, points2D_list, points3D_list, inlier_threshold, number_lo_steps,
+                   min_num_iterations, max_num_iterations, random_seeds, device=0):
+    """Q independent queries through ONE launch of the device-resident LO-MSAC
+    (rlbh_localize_batch -> rlb_localize_batch). -> list of dicts like ``localize``."""
+    nq = len(points2D_list)
+    p2s = [_capi.f64a(a, (-1, 2)) for a in points2D_list]
+    p3s = [_capi.f64a(a, (-1, 3)) for a in points3D_list]
+    off = np.zeros(nq + 1, np.int64)
+    for q in range(nq):
+        if len(p2s[q]) != len(p3s[q]):
+            raise ValueError(f"query {q}: points2D and points3D differ in length")
+        off[q + 1] = off[q] + len(p2s[q])
+    total = int(off[-1])
+    p2 = np.concatenate(p2s) if total else np.zeros((0, 2))
+    p3 = np.concatenate(p3s) if total else np.zeros((0, 3))
+    fx = np.ascontiguousarray(np.broadcast_to(np.asarray(focal_x, np.float32), (nq,)))
+    fy = np.ascontiguousarray(np.broadcast_to(np.asarray(focal_y, np.float32), (nq,)))
+    seeds = np.ascontiguousarray(random_seeds, dtype=np.uint32)
+    if len(seeds) != nq:
+        raise ValueError("need one seed per query")
+    success = np.zeros(nq, np.int32)
+    q4, t3 = np.zeros((nq, 4)), np.zeros((nq, 3))
+    ninl = np.zeros(nq, np.int32)
+    inl = np.zeros(max(total, 1), np.int32)
+    res = np.zeros(nq, _capi.LOCALIZE_RESULT)
+    rc = _load().rlbh_localize_batch(device, nq, _capi.ptr(off), _capi.ptr(p2), _capi.ptr(p3), _capi.ptr(fx),
+                                     _capi.ptr(fy), C.c_float(inlier_threshold), int(number_lo_steps),
+                                     int(min_num_iterations), int(max_num_iterations), _capi.ptr(seeds),
+                                     _capi.ptr(success), _capi.ptr(q4), _capi.ptr(t3), _capi.ptr(ninl),
+                                     _capi.ptr(inl), _capi.ptr(res))
+    _check(rc)
+    out = []
+    for q in range(nq):
+        if not success[q]:
+            out.append({"success": False})
+            continue
+        a = int(off[q])
+        out.append({"success": True, "qvec": q4[q].copy(), "tvec": t3[q].copy(), "num_inliers": int(ninl[q]),
+                    "inliers": inl[a:a + ninl[q]].tolist(),
+                    "_stats": {k: res[q][k].item() for k in res.dtype.names}})
+    return out

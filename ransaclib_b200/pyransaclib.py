@@ -31,14 +31,19 @@ def ransaclib_localization(query_name, focal_x, focal_y, points2D_vec, points3D_
 def ransaclib_localization_batch(query_names, focal_x, focal_y, points2D_list, points3D_list, inlier_threshold,
                                  number_lo_steps, min_num_iterations, max_num_iterations, random_seeds=None,
                                  device=0):
-    """Independent queries, one result dict per query (queries share nothing:
-    examples/localization.cc:190)."""
-    out = []
-    for i, name in enumerate(query_names):
-        fx = focal_x[i] if hasattr(focal_x, "__len__") else focal_x
-        fy = focal_y[i] if hasattr(focal_y, "__len__") else focal_y
-        seed = None if random_seeds is None else random_seeds[i]
-        out.append(ransaclib_localization(name, fx, fy, points2D_list[i], points3D_list[i], inlier_threshold,
-                                          number_lo_steps, min_num_iterations, max_num_iterations,
-                                          random_seed=seed, device=device))
+    """Independent queries (they share nothing: examples/localization.cc:190), one result dict per
+    query, all of them estimated by ONE launch of the device-resident LO-MSAC kernel
+    (``rlb_localize_batch``: one warp per query, no host round trips)."""
+    nq = len(query_names)
+    if random_seeds is None:
+        import random
+
+        rng = random.SystemRandom()
+        random_seeds = [rng.getrandbits(32) for _ in range(nq)]
+    fx = focal_x if hasattr(focal_x, "__len__") else [focal_x] * nq
+    fy = focal_y if hasattr(focal_y, "__len__") else [focal_y] * nq
+    out = host.localize_batch(fx, fy, points2D_list, points3D_list, inlier_threshold, number_lo_steps,
+                              min_num_iterations, max_num_iterations, random_seeds, device=device)
+    for r in out:
+        r.pop("_stats", None)
     return out

@@ -1,0 +1,177 @@
+"""GPU parity of the device-resident batched localization (rlb_localize_batch: one warp runs the
+whole LO-MSAC of one query) against the oracle's sequential LO-MSAC, query by query, on the
+same seeds: identical iteration count, LO count, inlier count and inlier index set; score within
+1e-9 relative; pose within 1e-9 (sin/cos/atan2 come from the CUDA math library on the device and
+from glibc in the oracle, everything else is the same strict-IEEE arithmetic)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from ransaclib_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+THR_PX = 12.0
+
+
+def oracle_localize(p2, p3, f, seed, lo_steps=10, min_iters=100, max_iters=10000, final_lsq=1, lo_start=60):
+    """The oracle's EstimateModel with ransaclib_localization's options
+    (examples/ransaclib_localization.cc:100-107)."""
+    O = ol.oracle()
+    o = ol.Options.default(sq_thr=float(np.float32(THR_PX)) ** 2, seed=seed, final_lsq=final_lsq,
+                           lo_steps=lo_steps, min_iters=min_iters, max_iters=max_iters, lo_start=lo_start)
+    st = ol.Stats()
+    model = np.zeros(12)
+    inl = np.zeros(max(len(p2), 1), np.int32)
+    O.lomsac_pose(C.byref(o), float(f), float(f), len(p2), ol.c64(p2), ol.c64(p3), model, C.byref(st), inl)
+    return model, st, inl[:st.best_num_inliers].copy()
+
+
+def make_queries(specs):
+    """specs: list of (data_seed, n_inliers, n_outliers) -> concatenated arrays."""
+    p2s, p3s, fs, off = [], [], [], [0]
+    for seed, n_in, n_out in specs:
+        if n_in + n_out == 0:
+            p2s.append(np.zeros((0, 2)))
+            p3s.append(np.zeros((0, 3)))
+            fs.append(184.752)
+        else:
+            inst = synth.pose_instance(seed, n_in, n_out)
+            p2s.append(inst["points2D"])
+            p3s.append(inst["points3D"])
+            fs.append(float(np.float32(inst["focal"])))
+        off.append(off[-1] + n_in + n_out)
+    return np.concatenate(p2s), np.concatenate(p3s), np.array(fs), np.array(off, np.int64)
+
+
+def run_batch(ctx, p2, p3, f, off, seeds, debug_flags=0, **kw):
+    o = ctx.localize_options(THR_PX, kw.get("lo_steps", 10), kw.get("min_iters", 100), kw.get("max_iters", 10000))
+    if "final_lsq" in kw:
+        o.final_lsq = kw["final_lsq"]
+    if "lo_start" in kw:
+        o.lo_start = kw["lo_start"]
+    o.debug_flags = debug_flags
+    return ctx.localize_batch(off, p2, p3, f, f, seeds, o)
+
+
+def check_against_oracle(p2, p3, f, off, seeds, poses, res, inl, **kw):
+    for q in range(len(off) - 1):
+        a, b = int(off[q]), int(off[q + 1])
+        if b - a <= 3:
+            assert res["success"][q] == 0  # ransaclib_localization.cc:86-92
+            continue
+        om, ost, oinl = oracle_localize(p2[a:b], p3[a:b], f[q], int(seeds[q]), **kw)
+        tag = f"query {q} (n={b - a}, seed={seeds[q]})"
+        assert res["success"][q] == 1, tag
+        assert res["num_iterations"][q] == ost.num_iterations, tag
+        assert res["num_lo"][q] == ost.number_lo_iterations, tag
+        assert res["num_inliers"][q] == ost.best_num_inliers, tag
+        assert inl[a:a + res["num_inliers"][q]].tolist() == oinl.tolist(), tag
+        np.testing.assert_allclose(res["score"][q], ost.best_model_score, rtol=1e-9, err_msg=tag)
+        np.testing.assert_allclose(poses[q], om, rtol=1e-9, atol=1e-9, err_msg=tag)
+        assert res["inlier_ratio"][q] == ost.inlier_ratio, tag
+
+
+def test_c4_shape_queries_match_the_oracle(ctx):
+    """BASELINE configs[3] shape: 2k matches, 50 % outliers, seeds 42+q, data seeds 5000+q."""
+    specs = [(5000 + q, 1000, 1000) for q in range(24)]
+    p2, p3, f, off = make_queries(specs)
+    seeds = np.arange(42, 42 + len(specs), dtype=np.uint32)
+    poses, res, inl = run_batch(ctx, p2, p3, f, off, seeds)
+    check_against_oracle(p2, p3, f, off, seeds, poses, res, inl)
+    assert (res["passes"] > 0).all() and (res["lsq_calls"] > 0).all()
+
+
+def test_ragged_and_degenerate_queries(ctx):
+    """Empty, <= 3 matches, the sampler's shuffle path (n = 4, 5, 6), tiny and odd sizes, outlier
+    ratios from 0 to 0.9, one query without any consensus (iteration cap)."""
+    specs = [(11, 0, 0), (12, 3, 0), (13, 4, 0), (14, 5, 0), (15, 6, 0), (16, 7, 2), (17, 20, 17), (18, 33, 0),
+             (19, 100, 233), (20, 50, 450), (21, 1500, 1501), (22, 3000, 1000), (23, 1, 2), (24, 64, 64),
+             (25, 0, 40)]
+    p2, p3, f, off = make_queries(specs)
+    seeds = np.array([7 + 3 * i for i in range(len(specs))], np.uint32)
+    poses, res, inl = run_batch(ctx, p2, p3, f, off, seeds, max_iters=2000)
+    check_against_oracle(p2, p3, f, off, seeds, poses, res, inl, max_iters=2000)
+
+
+@pytest.mark.parametrize("kw", [dict(lo_steps=0), dict(final_lsq=0), dict(lo_start=0), dict(lo_start=100000),
+                                dict(min_iters=500, max_iters=500), dict(lo_steps=3, min_iters=10)])
+def test_option_variants(ctx, kw):
+    """num_lo_steps_ = 0, no final least squares, LO from the first iteration / never during the
+    loop (ransac.h:245-255), forced iteration counts."""
+    specs = [(300 + q, 400, 400 + 50 * q) for q in range(6)]
+    p2, p3, f, off = make_queries(specs)
+    seeds = np.arange(1, 1 + len(specs), dtype=np.uint32)
+    poses, res, inl = run_batch(ctx, p2, p3, f, off, seeds, **kw)
+    check_against_oracle(p2, p3, f, off, seeds, poses, res, inl, **kw)
+
+
+def test_sequential_shuffle_path_is_identical(ctx):
+    """debug bit 0 forces every shuffle step through the sequential Lemire path that normally only
+    handles a rejected draw (probability ~ n / 2^32 per step): results must not change at all."""
+    specs = [(700 + q, 800, 600) for q in range(8)]
+    p2, p3, f, off = make_queries(specs)
+    seeds = np.arange(100, 100 + len(specs), dtype=np.uint32)
+    a = run_batch(ctx, p2, p3, f, off, seeds)
+    b = run_batch(ctx, p2, p3, f, off, seeds, debug_flags=1)
+    assert a[0].tobytes() == b[0].tobytes()
+    assert a[1].tobytes() == b[1].tobytes()
+    assert a[2].tobytes() == b[2].tobytes()
+
+
+def test_many_queries_deterministic_and_independent(ctx):
+    """More queries than resident warps: every query's result is independent of its neighbours and
+    of scheduling (same bytes when run alone)."""
+    specs = [(900 + (q % 16), 150, 150) for q in range(2500)]
+    base_specs = specs[:16]
+    p2, p3, f, off = make_queries(base_specs)
+    reps = len(specs) // 16 + 1
+    P2 = np.concatenate([p2] * reps)[: 300 * len(specs)]
+    P3 = np.concatenate([p3] * reps)[: 300 * len(specs)]
+    F = np.concatenate([f] * reps)[: len(specs)]
+    OFF = np.arange(len(specs) + 1, dtype=np.int64) * 300
+    seeds = np.array([5 + (q % 16) for q in range(len(specs))], np.uint32)
+    poses, res, inl = run_batch(ctx, P2, P3, F, OFF, seeds)
+    p1, r1, i1 = run_batch(ctx, p2, p3, f, off, seeds[:16])
+    for q in range(len(specs)):
+        assert poses[q].tobytes() == p1[q % 16].tobytes()
+        assert res[q]["num_inliers"] == r1[q % 16]["num_inliers"]
+    check_against_oracle(p2, p3, f, off, seeds[:16], p1, r1, i1)
+
+
+def test_pyransaclib_batch_matches_single_query_api(ctx):
+    """pyransaclib.ransaclib_localization_batch returns the dicts of the per-query function."""
+    from ransaclib_b200 import pyransaclib
+
+    specs = [(40 + q, 300, 300) for q in range(5)] + [(50, 2, 1)]
+    p2, p3, f, off = make_queries(specs)
+    lists2 = [p2[off[q]:off[q + 1]] for q in range(len(specs))]
+    lists3 = [p3[off[q]:off[q + 1]] for q in range(len(specs))]
+    seeds = [9 + q for q in range(len(specs))]
+    names = [f"q{q}" for q in range(len(specs))]
+    out = pyransaclib.ransaclib_localization_batch(names, list(f), list(f), lists2, lists3, THR_PX, 10, 100, 10000,
+                                                   random_seeds=seeds)
+    for q in range(len(specs)):
+        one = pyransaclib.ransaclib_localization(names[q], f[q], f[q], lists2[q], lists3[q], THR_PX, 10, 100, 10000,
+                                                 random_seed=seeds[q])
+        assert out[q]["success"] == one["success"]
+        if not one["success"]:
+            assert set(out[q]) == {"success"}
+            continue
+        assert set(out[q]) == {"success", "qvec", "tvec", "num_inliers", "inliers"}
+        assert out[q]["num_inliers"] == one["num_inliers"]
+        assert out[q]["inliers"] == one["inliers"]
+        np.testing.assert_allclose(out[q]["qvec"], one["qvec"], atol=1e-9)
+        np.testing.assert_allclose(out[q]["tvec"], one["tvec"], atol=1e-8)
+
+
+def test_bad_options_fail_loudly(ctx):
+    from ransaclib_b200 import RlbError
+
+    p2, p3, f, off = make_queries([(1, 50, 50)])
+    o = ctx.localize_options(THR_PX, 10, 100, 1000)
+    o.min_sample_mult = 9  # 36 > 32 lanes
+    with pytest.raises(RlbError):
+        ctx.localize_batch(off, p2, p3, f, f, np.array([1], np.uint32), o)
