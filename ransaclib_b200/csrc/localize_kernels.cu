@@ -49,7 +49,7 @@ struct Mt {
 };
 
 // std::mt19937::seed(value): s[i] = 1812433253 * (s[i-1] ^ (s[i-1] >> 30)) + i.
-__device__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
+__device__ __noinline__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
   if (lane == 0) {
     uint32_t x = seed;
     s[0] = x;
@@ -63,7 +63,7 @@ __device__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
 
 // Regenerates the 624 words in place, 32 per round: word k needs the OLD k, k+1 and either the
 // old k+397 (k < 227) or the NEW k-227, which earlier rounds have already written.
-__device__ void mt_twist(uint32_t* s, int lane) {
+__device__ __noinline__ void mt_twist(uint32_t* s, int lane) {
   for (int base = 0; base < 623; base += 32) {
     const int k = base + lane;
     uint32_t v = 0;
@@ -116,7 +116,7 @@ __device__ uint32_t lemire(Mt& r, uint32_t range, int lane) {
 }
 
 // One minimal sample of 4 distinct indices (sampling.h:58-110), warp-uniform.
-__device__ void draw_sample4(Mt& r, int n, int* s, int lane) {
+__device__ __noinline__ void draw_sample4(Mt& r, int n, int* s, int lane) {
   const double ratio = static_cast<double>(n) / static_cast<double>(n - 4);
   if (ratio < 2.718281828459045235360287471352662498 /* M_E */) {
     for (int i = 0; i < 4; ++i) {
@@ -154,7 +154,7 @@ __device__ void draw_sample4(Mt& r, int n, int* s, int lane) {
 // their draws: 32 steps per round, each lane testing its own draw for a Lemire rejection
 // (probability range / 2^32); a rejection drops that one step to the sequential path.
 // target <= 32. Entries past n (resize growing the vector) are 0 like std::vector::resize.
-__device__ void shuffle_resize(Mt& r, const int32_t* list, int n, int target, int32_t* samp,
+__device__ __noinline__ void shuffle_resize(Mt& r, const int32_t* list, int n, int target, int32_t* samp,
                                int lane, bool force_slow) {
   const int steps = (n > 0) ? n - 1 : 0;
   const int head_n = min(target, n);
@@ -258,7 +258,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 
 
 // Recentred f32 copy of the query's matches for the 32-hypothesis sweeps.
-__device__ void prepare_soa32(Query& q, int lane) {
+__device__ __noinline__ void prepare_soa32(Query& q, int lane) {
   double c[3] = {0.0, 0.0, 0.0};
   const int take = min(q.n, 32);
   if (lane < take) {
@@ -283,7 +283,7 @@ __device__ void prepare_soa32(Query& q, int lane) {
 // MSAC score of THIS LANE's hypothesis over all matches in f32 (ransac.h:295-309 with the
 // f32 deviations documented in DESIGN.md section 3): every lane reads the same match
 // (broadcast), 4 matches per vector load; f32 sums are flushed into f64 every 512 matches.
-__device__ double sweep32(const Query& q, const double* P, double thr64) {
+__device__ __noinline__ double sweep32(const Query& q, const double* P, double thr64) {
   // p = R (X - c) = R (X - centre) + R (centre - c); rows 0/1 pre-scaled by fx/fy.
   const double dc[3] = {q.centre[0] - P[9], q.centre[1] - P[10], q.centre[2] - P[11]};
   const double sc[3] = {q.fx, q.fy, 1.0};
@@ -338,7 +338,7 @@ __device__ double sweep32(const Query& q, const double* P, double thr64) {
 // ScoreModel fused with GetInliers for ONE model (ransac.h:295-336), reference formulation
 // (calibrated_absolute_pose_estimator.cc:154-167): lane l evaluates matches l, l+32, ...;
 // the ascending inlier list is compacted with a ballot per 32 matches.
-__device__ int fused_pass(const Query& q, const double* P, double thr_inl, bool want_score,
+__device__ __noinline__ int fused_pass(const Query& q, const double* P, double thr_inl, bool want_score,
                           double thr_score, int32_t* list, double* score, int lane) {
   int off = 0;
   double sc = 0.0;
@@ -376,7 +376,7 @@ struct WarpLineariser {
   double* sums;  // [28]
   int lane;
 
-  RLB_HD double Cost(const double* c) const {
+  RLB_HD __noinline__ double Cost(const double* c) const {
 #ifdef __CUDA_ARCH__
     refine::Value cam[6];
     for (int i = 0; i < 6; ++i) cam[i] = refine::Value::Constant(c[i]);
@@ -393,6 +393,7 @@ struct WarpLineariser {
         mine = 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
       }
       const int m = min(32, k - base);
+#pragma unroll 1
       for (int j = 0; j < m; ++j) cost += __shfl_sync(kFull, mine, j);
     }
     return cost;
@@ -402,7 +403,7 @@ struct WarpLineariser {
 #endif
   }
 
-  RLB_HD double Full(const double* c, double* JtJ, double* Jtr) const {
+  RLB_HD __noinline__ double Full(const double* c, double* JtJ, double* Jtr) const {
 #ifdef __CUDA_ARCH__
     refine::Dual cam[6];
     for (int i = 0; i < 6; ++i) cam[i] = refine::Dual::Variable(c[i], i);
@@ -437,18 +438,21 @@ struct WarpLineariser {
       __syncwarp();
       const int m = min(32, k - base);
       if (lane < 6) {
+#pragma unroll 1
         for (int j = 0; j < m; ++j) {
           const double* row = slab + 14 * j;
           acc += row[1 + ea] * row[0];
           acc += row[8 + ea] * row[7];
         }
       } else if (lane < 27) {
+#pragma unroll 1
         for (int j = 0; j < m; ++j) {
           const double* row = slab + 14 * j;
           acc += row[1 + ea] * row[1 + eb];
           acc += row[8 + ea] * row[8 + eb];
         }
       } else if (lane == 27) {
+#pragma unroll 1
         for (int j = 0; j < m; ++j) {
           const double* row = slab + 14 * j;
           acc += 0.5 * (row[0] * row[0] + row[7] * row[7]);
@@ -496,7 +500,7 @@ struct Run {
 };
 
 // utils.h:110-140.
-__device__ uint32_t num_required_iterations(double inlier_ratio, double prob_missing, int sample_size,
+__device__ __noinline__ uint32_t num_required_iterations(double inlier_ratio, double prob_missing, int sample_size,
                                             uint32_t min_it, uint32_t max_it) {
   if (inlier_ratio <= 0.0) return max_it;
   if (inlier_ratio >= 1.0) return min_it;
@@ -517,7 +521,7 @@ __device__ __forceinline__ void update_best(double score, const double* m, doubl
 }
 
 // CalibratedAbsolutePoseEstimator::LeastSquares on sample idx[0..k).
-__device__ void least_squares(Run& R, const int32_t* idx, int k, double* pose) {
+__device__ __noinline__ void least_squares(Run& R, const int32_t* idx, int k, double* pose) {
   WarpLineariser lin;
   lin.k = k;
   lin.idx = idx;
@@ -533,7 +537,7 @@ __device__ void least_squares(Run& R, const int32_t* idx, int k, double* pose) {
 }
 
 // P3P on sample[0..2] + consistency with sample[3] (calibrated_absolute_pose_estimator.cc:111-137).
-__device__ bool minimal_solver(const Query& q, const int* s, double sq_thr, double* P) {
+__device__ __noinline__ bool minimal_solver(const Query& q, const int* s, double sq_thr, double* P) {
   double y[9], x[9];
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
@@ -555,7 +559,7 @@ __device__ bool minimal_solver(const Query& q, const int* s, double sq_thr, doub
 
 // [ScoreModel(m) + UpdateBestModel] fused with the LeastSquaresFit(fit_thr, m) that follows it
 // (ransac.h:409-420; include/RansacLib/ransac.h ScoreThenFit).
-__device__ void score_then_fit(Run& R, bool want_score, double fit_thr, double* m, double* best_score,
+__device__ __noinline__ void score_then_fit(Run& R, bool want_score, double fit_thr, double* m, double* best_score,
                                double* best) {
   const double thr = R.opt.sq_thr;
   double score = kNever;
@@ -570,7 +574,7 @@ __device__ void score_then_fit(Run& R, bool want_score, double fit_thr, double* 
 }
 
 // Algorithms 2 and 3 of Lebeda et al. in the order of ransac.h:341-407.
-__device__ void local_optimization(Run& R, double* best_minimal_model, double* score_best_minimal) {
+__device__ __noinline__ void local_optimization(Run& R, double* best_minimal_model, double* score_best_minimal) {
   const int n = R.q.n;
   if (6 > n) return;  // non_minimal_sample_size() (.h:90)
   const double thr = R.opt.sq_thr;
