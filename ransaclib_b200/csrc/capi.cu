@@ -928,7 +928,7 @@ int localize_enqueue(rlb_ctx* c, cudaStream_t st, int nq, int max_matches, const
   const int nmax = std::max(max_matches, 4);
   const int npad = pad_to(nmax, 4);
   const size_t per_slot = static_cast<size_t>(5) * npad * sizeof(float) + static_cast<size_t>(3) * nmax * 4;
-  int ctas = std::min((nq + wpc - 1) / wpc, c->sms * 3);
+  int ctas = std::min((nq + wpc - 1) / wpc, c->sms * rlb::localize_ctas_per_sm());
   const size_t budget = size_t(8) << 30;  // scratch cap; fewer resident warps for huge queries
   while (ctas > 1 && static_cast<size_t>(ctas) * wpc * per_slot > budget) ctas /= 2;
   const size_t slots = static_cast<size_t>(ctas) * wpc;

@@ -343,19 +343,45 @@ __device__ __noinline__ int fused_pass(const Query& q, const double* P, double t
   int off = 0;
   double sc = 0.0;
   const unsigned lt = (1u << lane) - 1u;
+  // software pipeline: the next match is in flight while the current one is evaluated
+  double c0 = 0.0, c1 = 0.0, c2 = 0.0, cu = 0.0, cv = 0.0;
+  if (lane < q.n) {
+    const double* X = q.p3 + 3 * static_cast<size_t>(lane);
+    const double* uv = q.p2 + 2 * static_cast<size_t>(lane);
+    c0 = X[0];
+    c1 = X[1];
+    c2 = X[2];
+    cu = uv[0];
+    cv = uv[1];
+  }
+#pragma unroll 1
   for (int base = 0; base < q.n; base += 32) {
     const int i = base + lane;
     const bool live = i < q.n;
+    double n0 = 0.0, n1 = 0.0, n2 = 0.0, nu = 0.0, nv = 0.0;
+    if (i + 32 < q.n) {
+      const double* X = q.p3 + 3 * static_cast<size_t>(i + 32);
+      const double* uv = q.p2 + 2 * static_cast<size_t>(i + 32);
+      n0 = X[0];
+      n1 = X[1];
+      n2 = X[2];
+      nu = uv[0];
+      nv = uv[1];
+    }
     double e = DBL_MAX;
     if (live) {
-      e = p3pdev::reproj_sq_error(P, q.p3 + 3 * static_cast<size_t>(i), q.p2 + 2 * static_cast<size_t>(i),
-                                  q.fx, q.fy);
+      e = p3pdev::reproj_sq_error_v(P, c0, c1, c2, cu, cv, q.fx, q.fy);
       if (want_score) sc += (thr_score < e) ? thr_score : e;  // std::min(e, thr): NaN propagates
     }
     const bool in = live && (e < thr_inl);
     const unsigned mask = __ballot_sync(kFull, in);
     if (in && list != nullptr) list[off + __popc(mask & lt)] = i;
     off += __popc(mask);
+    c0 = n0;
+    c1 = n1;
+    c2 = n2;
+    cu = nu;
+    cv = nv;
   }
   if (want_score) *score = warp_sum(sc);
   __syncwarp();
@@ -419,6 +445,9 @@ struct WarpLineariser {
       }
       eb = t;
     }
+    // slab columns multiplied by this lane: Jtr[a] = d[a] * value, JtJ[a][b] = d[a] * d[b]
+    const int ia = (lane < 27) ? 1 + ea : 0;
+    const int ib = (lane < 6) ? 0 : ((lane < 27) ? 1 + eb : 0);
     double acc = 0.0;
     for (int base = 0; base < k; base += 32) {
       const int s = base + lane;
@@ -437,25 +466,20 @@ struct WarpLineariser {
       }
       __syncwarp();
       const int m = min(32, k - base);
-      if (lane < 6) {
+      if (lane < 28) {
+        // one loop for all 28 entries: acc += row[ia] * row[ib] for residual row 0, then row 1
+        // (the cost lane has ia = ib = 0 and adds 0.5 * (r0^2 + r1^2) per match)
 #pragma unroll 1
         for (int j = 0; j < m; ++j) {
           const double* row = slab + 14 * j;
-          acc += row[1 + ea] * row[0];
-          acc += row[8 + ea] * row[7];
-        }
-      } else if (lane < 27) {
-#pragma unroll 1
-        for (int j = 0; j < m; ++j) {
-          const double* row = slab + 14 * j;
-          acc += row[1 + ea] * row[1 + eb];
-          acc += row[8 + ea] * row[8 + eb];
-        }
-      } else if (lane == 27) {
-#pragma unroll 1
-        for (int j = 0; j < m; ++j) {
-          const double* row = slab + 14 * j;
-          acc += 0.5 * (row[0] * row[0] + row[7] * row[7]);
+          const double t0 = row[ia] * row[ib];
+          const double t1 = row[7 + ia] * row[7 + ib];
+          if (lane == 27) {
+            acc += 0.5 * (t0 + t1);
+          } else {
+            acc += t0;
+            acc += t1;
+          }
         }
       }
     }
@@ -773,7 +797,10 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
 
 }  // namespace
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) localize_kernel(const LocalizeArgs A) {
+#ifndef RLB_LOC_MINB
+#define RLB_LOC_MINB 4
+#endif
+__global__ void __launch_bounds__(kWarpsPerCta * 32, RLB_LOC_MINB) localize_kernel(const LocalizeArgs A) {
   __shared__ WarpShared shared[kWarpsPerCta];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -871,5 +898,6 @@ cudaError_t launch_localize(const LocalizeArgs& a, int ctas, cudaStream_t st, in
 }
 
 int localize_warps_per_cta() { return kWarpsPerCta; }
+int localize_ctas_per_sm() { return RLB_LOC_MINB; }
 
 }  // namespace rlb

@@ -126,17 +126,22 @@ static __device__ void refine_lambda(double* L, double a12, double a13, double a
 
 // Reference-exact residual on ONE point in the reference's own formulation
 // (calibrated_absolute_pose_estimator.cc:154-167): used for the 4th-point test.
-static __device__ double reproj_sq_error(const double* P /*col-major 3x4 [R|c]*/, const double* X,
-                                  const double* uv, double fx, double fy) {
-  const double d0 = X[0] - P[9], d1 = X[1] - P[10], d2 = X[2] - P[11];
+static __device__ __forceinline__ double reproj_sq_error_v(const double* P /*col-major 3x4 [R|c]*/,
+                                                           double X0, double X1, double X2, double u0,
+                                                           double v0, double fx, double fy) {
+  const double d0 = X0 - P[9], d1 = X1 - P[10], d2 = X2 - P[11];
   const double pz = P[2] * d0 + P[5] * d1 + P[8] * d2;
   if (pz < 0.0) return DBL_MAX;
   const double px = P[0] * d0 + P[3] * d1 + P[6] * d2;
   const double py = P[1] * d0 + P[4] * d1 + P[7] * d2;
   const double u = (px / pz) * fx;
   const double v = (py / pz) * fy;
-  const double du = u - uv[0], dv = v - uv[1];
+  const double du = u - u0, dv = v - v0;
   return du * du + dv * dv;
+}
+static __device__ double reproj_sq_error(const double* P /*col-major 3x4 [R|c]*/, const double* X,
+                                         const double* uv, double fx, double fy) {
+  return reproj_sq_error_v(P, X[0], X[1], X[2], uv[0], uv[1], fx, fy);
 }
 
 // Lambda Twist + "first solution consistent with the 4th point wins"

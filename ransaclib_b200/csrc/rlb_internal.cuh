@@ -131,6 +131,7 @@ struct LocalizeArgs {
 };
 cudaError_t launch_localize(const LocalizeArgs& a, int ctas, cudaStream_t st, int* launches);
 int localize_warps_per_cta();
+int localize_ctas_per_sm();
 
 inline int model_size_of(int kind) { return kind == RLB_KIND_POSE ? 12 : 3; }
 
