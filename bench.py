@@ -256,6 +256,16 @@ def run_ours(args):
     h2d = p2.nbytes + p3.nbytes + my_samples.nbytes + 12 * 8
     d2h = k * 8 + k * 4 + 16 + 96 + 16 + 4 * int(c_e2e[0])
 
+    # ---- second half of BASELINE.json's metric: batched localization (configs[3]) on the same GPUs ----
+    loc = None
+    if args.workload == "c5" and not args.no_localization:
+        scorer.close()
+        del flush
+        torch.cuda.empty_cache()
+        loc = measure_c4(args, rank, world, local, dist, steps=max(1, min(args.steps, 5)),
+                         warmup=max(1, min(args.warmup, 3)))
+        torch.cuda.set_stream(stream)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -313,6 +323,10 @@ def run_ours(args):
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
         "result": {"num_inliers": n_inl, "best_score": best_score},
     }
+    if loc is not None:
+        if world == 1:
+            loc["cpu_baseline"] = cpu_baseline_c4(budget_queries=64, threads=1)
+        line["localization"] = loc  # "P3P LO-MSAC localizations/sec" at this N (same run, same GPUs)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -400,6 +414,12 @@ def run_reference(args):
                          "sample": res[-1]["sample"]},
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    if args.workload == "c5" and not args.no_localization:
+        r = cpu_baseline_c4(max(cores * 4, 32), cores)
+        line["localization"] = {"impl": "reference", "metric": "P3P LO-MSAC localizations/sec", "value": r["value"],
+                                "unit": "localizations/s", "cpu_baseline": r,
+                                "e2e": {"value": r["value"], "unit": "localizations/s", "h2d_bytes_per_step": 0,
+                                        "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 # ------------------------------------------------- C4: batched localization (query-sharded)
@@ -424,15 +444,137 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def run_ours_c4(args):
-    """Queries are independent (examples/localization.cc:190): query q runs on rank q mod world, end to
-    end, with NO collective. Each rank drives its GPU from several host threads (one rlb_ctx + stream per
-    thread); the least-squares refinement of local optimisation runs on those host threads."""
-    from concurrent.futures import ThreadPoolExecutor
+def c4_arrays(indices):
+    """Concatenated (offsets, points2D, points3D, focal, seeds) of the given query indices."""
+    data = c4_queries(indices)
+    off = np.zeros(len(data) + 1, np.int64)
+    for i, d in enumerate(data):
+        off[i + 1] = off[i] + len(d[0])
+    p2 = np.concatenate([d[0] for d in data])
+    p3 = np.concatenate([d[1] for d in data])
+    f = np.array([float(d[2]) for d in data])
+    seeds = np.array([42 + q for q in indices], np.uint32)
+    return off, p2, p3, f, seeds
 
+
+def measure_c4(args, rank, world, local, dist, steps, warmup, q_total=None):
+    """Batched localization on this rank's shard of the queries (query q on rank q mod world, NO
+    collective: examples/localization.cc:190 has no cross-query state). Every query runs wholly on the
+    device (rlb_localize_batch: one warp per query). Returns the JSON-ready dict on rank 0."""
     import torch
 
-    from ransaclib_b200 import host, sharding
+    import ransaclib_b200 as rlb
+    from ransaclib_b200 import _capi, sharding
+
+    dev = torch.device("cuda", local)
+    q_total = q_total or args.queries or C4["q"]
+    mine = sharding.query_indices(q_total, rank, world)
+    off, p2, p3, f, seeds = c4_arrays(mine)
+    nq = len(mine)
+    pin = lambda a: torch.from_numpy(a).pin_memory().numpy()  # noqa: E731
+    off, p2, p3, f, seeds_h = pin(off), pin(p2), pin(p3), pin(f), pin(seeds)
+
+    ctx = rlb.Context(local)
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    opt = ctx.localize_options(C4["thr_px"], C4["lo_steps"], C4["min_iters"], C4["max_iters"])
+    max_matches = int(np.max(np.diff(off)))
+
+    # ---- value: matches already resident in HBM, CUDA events on the launching stream ----------
+    d_off, d_p2, d_p3, d_f = (torch.from_numpy(a).to(dev) for a in (off, p2, p3, f))
+    d_seeds = torch.from_numpy(seeds_h.view(np.int32)).to(dev)
+    d_poses = torch.zeros((nq, 12), dtype=torch.float64, device=dev)
+    d_res = torch.zeros(nq * _capi.LOCALIZE_RESULT.itemsize, dtype=torch.uint8, device=dev)
+    d_inl = torch.zeros(int(off[-1]), dtype=torch.int32, device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    def step_dev():
+        ctx.localize_batch_dev(nq, max_matches, d_off.data_ptr(), d_p2.data_ptr(), d_p3.data_ptr(), d_f.data_ptr(),
+                               d_f.data_ptr(), d_seeds.data_ptr(), opt, d_poses.data_ptr(), d_res.data_ptr(),
+                               d_inl.data_ptr())
+
+    for _ in range(warmup):
+        step_dev()
+    torch.cuda.synchronize()
+    launches0 = ctx.launch_count
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    time.sleep(0.25)
+    w0 = time.time()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for e0, e1 in evs:
+        flush.zero_()  # L2 flush between timed steps (untimed)
+        e0.record(stream)
+        step_dev()
+        e1.record(stream)
+        e1.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    w1 = time.time()
+    launches = ctx.launch_count - launches0
+    clk = clocks.stop(w0, w1)
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # timing only; the data path has no collective
+    total_ms = float(t.item())
+    value = q_total * steps / (total_ms * 1e-3)
+    res_dev = d_res.cpu().numpy().view(_capi.LOCALIZE_RESULT)
+
+    # ---- e2e: pinned host buffers through rlb_localize_batch (upload pipelined with the kernel,
+    #      poses / results / inlier lists copied back), wall clock ------------------------------
+    e2e_steps = max(1, min(steps, 5))
+    ctx.localize_batch(off, p2, p3, f, f, seeds_h, opt)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        poses, res, inl = ctx.localize_batch(off, p2, p3, f, f, seeds_h, opt)
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = q_total * e2e_steps / float(te.item())
+    assert (res["num_inliers"] == res_dev["num_inliers"]).all(), "host and device entry points disagree"
+    if rank != 0:
+        return None
+    h2d = p2.nbytes + p3.nbytes + off.nbytes + 2 * f.nbytes + seeds_h.nbytes
+    d2h = poses.nbytes + res.nbytes + inl.nbytes
+    return {
+        "metric": "P3P LO-MSAC localizations/sec", "value": value, "unit": "localizations/s", "n_gpus": world,
+        "steps": steps, "warmup": warmup, "ms_per_step": total_ms / steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": C4["name"], "queries": q_total, "queries_per_gpu": nq,
+                   "matches_per_query": C4["n"], "partitioning": "query q on rank q mod world, no collective",
+                   "options": "ransaclib_localization.cc:100-107 (lo_start 60, final LSQ), seed 42+q, data seed 5000+q",
+                   "l2": "flushed (256 MiB write) between timed steps",
+                   "step": "one launch of the device-resident LO-MSAC kernel over all of this rank's queries"},
+        "e2e": {"value": e2e_value, "unit": "localizations/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                "path": "rlb_localize_batch with pinned host buffers (pyransaclib.ransaclib_localization_batch): "
+                        "chunked upload behind a ready counter, kernel, poses + stats + inlier lists back"},
+        "gpu_launches": int(launches), "clocks": clk,
+        "roofline": {"bound": "latency", "kernel": "localize_kernel", "achieved": None, "peak": None, "unit": None,
+                     "frac": None, "traffic": None,
+                     "note": "control-flow kernel (one warp = one whole LO-MSAC run); per query on average "
+                             "%.0f f64 passes over the matches, %.0f LM refinements, %.1f iterations, %.2f LO calls; "
+                             "ncu: profiles/r01e_ncu_localize.csv (issue active 22%%, fp64 pipe 11%%, stalls: "
+                             "long scoreboard / fixed-latency wait / instruction fetch)"
+                             % (res["passes"].mean(), res["lsq_calls"].mean(), res["num_iterations"].mean(),
+                                res["num_lo"].mean())},
+        "result": {"mean_inliers": float(res["num_inliers"].mean()), "min_inliers": int(res["num_inliers"].min()),
+                   "success": int(res["success"].sum())},
+    }
+
+
+def run_ours_c4(args):
+    import torch
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -443,67 +585,9 @@ def run_ours_c4(args):
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    q_total = args.queries or C4["q"]
-    mine = sharding.query_indices(q_total, rank, world)
-    data = c4_queries(mine)
-    threads = max(1, min(args.threads or max(1, host_threads() // world), len(mine)))
-
-    def one(i):
-        p2, p3, f = data[i]
-        r = host.localize(f, f, p2, p3, C4["thr_px"], C4["lo_steps"], C4["min_iters"], C4["max_iters"],
-                          random_seed=42 + mine[i], device=local)
-        return r["num_inliers"] if r["success"] else 0, r["_stats"]
-
-    def sweep_all(ex):
-        return list(ex.map(one, range(len(mine))))
-
-    with ThreadPoolExecutor(threads) as ex:
-        for _ in range(args.warmup):
-            sweep_all(ex)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        clocks = ClockSampler(local)
-        clocks.start()
-        time.sleep(0.2)
-        w0 = time.time()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            res = sweep_all(ex)
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        w1 = time.time()
-    clk = clocks.stop(w0, w1)
-    t = torch.tensor([dt], dtype=torch.float64, device=torch.device("cuda", local))
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # timing only; the data path has no collective
-    dt = float(t.item())
-    value = q_total * args.steps / dt
+    line = measure_c4(args, rank, world, local, dist, args.steps, args.warmup)
     if rank == 0:
-        inl = [r[0] for r in res]
-        passes = sum(r[1]["single_passes"] for r in res)
-        batches = sum(r[1]["batches"] for r in res)
-        hyps = sum(r[1]["hypotheses_scored"] for r in res)
-        line = {
-            "metric": "P3P LO-MSAC localizations/sec", "value": value, "unit": "localizations/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": C4["name"], "queries": q_total, "queries_per_gpu": len(mine),
-                       "matches_per_query": C4["n"], "host_threads_per_gpu": threads,
-                       "partitioning": "query q on rank q mod world, no collective",
-                       "options": "ransaclib_localization.cc:100-107 (lo_start 60, final LSQ), seed 42+q",
-                       "l2": "each query uploads its own data set (inputs change every call)"},
-            "e2e": {"value": value, "unit": "localizations/s",
-                    "h2d_bytes_per_step": len(mine) * C4["n"] * 40, "d2h_bytes_per_step": int(sum(inl)) * 4,
-                    "path": "pyransaclib-equivalent rlbh_localize per query with host buffers (this IS the e2e path)"},
-            "gpu_launches": int(passes + 3 * batches), "clocks": clk,
-            "roofline": {"bound": "latency", "note": "adaptive LO-MSAC at N=2k is a chain of dependent K=1 passes "
-                         "(DESIGN.md section 4); per query: %.0f fused passes, %.1f batches, %.0f hypotheses"
-                         % (passes / len(res), batches / len(res), hyps / len(res)), "achieved": None,
-                         "peak": None, "unit": None, "frac": None, "traffic": None},
-            "cpu_baseline": cpu_baseline_c4(budget_queries=64, threads=1) if world == 1 else None,
-            "result": {"mean_inliers": float(np.mean(inl)), "min_inliers": int(np.min(inl))},
-        }
+        line["cpu_baseline"] = cpu_baseline_c4(budget_queries=64, threads=1) if world == 1 else None
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -574,6 +658,8 @@ def main():
     ap.add_argument("--queries", type=int, default=0, help="c4: total number of queries (default 4096)")
     ap.add_argument("--threads", type=int, default=0, help="c4: host threads per GPU (default: cores / gpus)")
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--no-localization", action="store_true",
+                    help="c5: skip the batched-localization leg that is reported under 'localization'")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: skips the e2e leg, the CPU baseline and the peak microbenchmarks")
     args = ap.parse_args()

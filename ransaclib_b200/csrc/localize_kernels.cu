@@ -338,11 +338,14 @@ __device__ __noinline__ double sweep32(const Query& q, const double* P, double t
 // ScoreModel fused with GetInliers for ONE model (ransac.h:295-336), reference formulation
 // (calibrated_absolute_pose_estimator.cc:154-167): lane l evaluates matches l, l+32, ...;
 // the ascending inlier list is compacted with a ballot per 32 matches.
-__device__ __noinline__ int fused_pass(const Query& q, const double* P, double thr_inl, bool want_score,
-                          double thr_score, int32_t* list, double* score, int lane) {
+__device__ __noinline__ int fused_pass(const Query& q, const double* __restrict__ Pin, double thr_inl, bool want_score,
+                          double thr_score, int32_t* __restrict__ list, double* score, int lane) {
   int off = 0;
   double sc = 0.0;
   const unsigned lt = (1u << lane) - 1u;
+  double P[12];  // the model lives in registers for the whole pass (the caller's copy is in local memory)
+#pragma unroll
+  for (int i = 0; i < 12; ++i) P[i] = Pin[i];
   // software pipeline: the next match is in flight while the current one is evaluated
   double c0 = 0.0, c1 = 0.0, c2 = 0.0, cu = 0.0, cv = 0.0;
   if (lane < q.n) {

@@ -12,7 +12,7 @@ timeout 120 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "sm
 timeout 400 python bench.py > $O/${TAG}_bench_c5.json 2> $O/${TAG}_bench_c5.err; echo "bench c5 rc=$?"
 timeout 300 python bench.py --precision f64 --steps 3 > $O/${TAG}_bench_c5_f64.json 2> $O/${TAG}_bench_c5_f64.err; echo "bench c5 f64 rc=$?"
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_c5_ref.json 2>&1; echo "bench ref rc=$?"
-timeout 400 python bench.py --workload c4 --queries 512 --steps 2 --warmup 1 > $O/${TAG}_bench_c4.json 2> $O/${TAG}_bench_c4.err; echo "bench c4 rc=$?"
+timeout 400 python bench.py --workload c4 --steps 5 --warmup 2 > $O/${TAG}_bench_c4.json 2> $O/${TAG}_bench_c4.err; echo "bench c4 rc=$?"
 timeout 300 python bench.py --workload c4 --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_c4_ref.json 2>&1; echo "bench c4 ref rc=$?"
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
   python bench.py --profile --steps 2 --warmup 1 > $O/${TAG}_ncu_launches.log 2>&1; echo "ncu launches rc=$?"
@@ -20,5 +20,8 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:swee
   python bench.py --profile --steps 1 --warmup 1 > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:inlier -c 2 -f -o $O/${TAG}_inlier \
   python bench.py --profile --steps 1 --warmup 1 > $O/${TAG}_ncu_inl.log 2>&1; echo "ncu inlier rc=$?"
+# device-pointer entry point only: under ncu the pipelined host API would wait for copies that never start
+timeout 400 ncu --set full --clock-control none --import-source on -k regex:localize -c 1 -f -o $O/${TAG}_localize \
+  python tools/time_localize.py 2368 dev 1 > $O/${TAG}_ncu_localize.log 2>&1; echo "ncu localize rc=$?"
 head -c 600 $O/${TAG}_bench_c5.json; echo
 head -c 600 $O/${TAG}_bench_c4.json; echo
