@@ -81,23 +81,10 @@ class CalibratedAbsolutePoseEstimator {
 
   // .cc:170-212
   void LeastSquares(const std::vector<int>& sample, CameraPose* pose) const {
-    double R[9];
-    for (int r = 0; r < 3; ++r)
-      for (int c = 0; c < 3; ++c) R[3 * r + c] = (*pose)(r, c);
-    double cam[6];
-    refine::RotationToAngleAxis(R, cam);
-    cam[3] = pose->m[9];
-    cam[4] = pose->m[10];
-    cam[5] = pose->m[11];
-    if (!refine::RefinePose(static_cast<int>(sample.size()), sample.data(), points2D_.data(),
-                            points3D_.data(), focal_x_, focal_y_, cam))
-      return;
-    refine::AngleAxisToRotation(cam, R);
-    for (int r = 0; r < 3; ++r)
-      for (int c = 0; c < 3; ++c) (*pose)(r, c) = R[3 * r + c];
-    pose->m[9] = cam[3];
-    pose->m[10] = cam[4];
-    pose->m[11] = cam[5];
+    const refine::SequentialLineariser lin = {static_cast<int>(sample.size()), sample.data(), points2D_.data(),
+                                              points3D_.data(), focal_x_, focal_y_};
+    refine::LmWorkspace w;
+    refine::LeastSquaresWith(lin, pose->m, &w);
   }
 
   // ---- GPU opt-in ----

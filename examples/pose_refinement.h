@@ -22,6 +22,20 @@
 #else
 #define RLB_HD
 #endif
+// On the device the LM state below is ONE copy per warp in shared memory that all 32 lanes
+// read and (redundantly, with identical values) write; the barrier keeps a lane from
+// overwriting state another lane of the warp has not consumed yet. No-op on the host.
+#if defined(__CUDA_ARCH__)
+#define RLB_WARP_SYNC() __syncwarp()
+#else
+#define RLB_WARP_SYNC() ((void)0)
+#endif
+// Small dense loops stay rolled on the device (instruction-cache footprint); plain loops on the host.
+#if defined(__CUDACC__) && defined(RLB_ROLL_LM) && RLB_ROLL_LM
+#define RLB_ROLLED _Pragma("unroll 1")
+#else
+#define RLB_ROLLED
+#endif
 
 namespace ransac_lib {
 namespace calibrated_absolute_pose {
@@ -107,9 +121,11 @@ struct DualN {
     for (int i = 0; i < ND; ++i) r.d[i] = 0.0;
     return r;
   }
+  // d/dx_k = 1; a k outside [0, ND) gives a constant (used when the partials are formed in slices).
   RLB_HD static DualN Variable(double v, int k) {
-    DualN r = Constant(v);
-    if (k < ND) r.d[k] = 1.0;
+    DualN r;
+    r.a = v;
+    for (int i = 0; i < ND; ++i) r.d[i] = (i == k) ? 1.0 : 0.0;
     return r;
   }
 };
@@ -153,21 +169,17 @@ RLB_HD inline DualN<ND> Sqrt(const DualN<ND>& x) {
   for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] * g;
   return r;
 }
+// sin and cos of the same argument: each libm function is evaluated once and serves both the
+// value of one result and the derivative of the other.
 template <int ND>
-RLB_HD inline DualN<ND> Sin(const DualN<ND>& x) {
-  DualN<ND> r;
-  r.a = std::sin(x.a);
-  const double g = std::cos(x.a);
-  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] * g;
-  return r;
-}
-template <int ND>
-RLB_HD inline DualN<ND> Cos(const DualN<ND>& x) {
-  DualN<ND> r;
-  r.a = std::cos(x.a);
-  const double g = -std::sin(x.a);
-  for (int i = 0; i < ND; ++i) r.d[i] = x.d[i] * g;
-  return r;
+RLB_HD inline void SinCos(const DualN<ND>& x, DualN<ND>* sn, DualN<ND>* cs) {
+  const double s = std::sin(x.a);
+  const double c = std::cos(x.a);
+  sn->a = s;
+  cs->a = c;
+  const double ms = -s;
+  for (int i = 0; i < ND; ++i) sn->d[i] = x.d[i] * c;
+  for (int i = 0; i < ND; ++i) cs->d[i] = x.d[i] * ms;
 }
 
 // ReprojectionError::operator() (.cc:55-74) with ceres::AngleAxisRotatePoint's two branches.
@@ -180,7 +192,8 @@ RLB_HD inline void Residual(const D* cam, double u, double v, double X, double Y
   const D theta2 = cam[0] * cam[0] + cam[1] * cam[1] + cam[2] * cam[2];
   if (theta2.a > DBL_EPSILON) {
     const D theta = Sqrt(theta2);
-    const D ct = Cos(theta), st = Sin(theta);
+    D ct, st;
+    SinCos(theta, &st, &ct);
     const D inv = one / theta;
     const D w[3] = {cam[0] * inv, cam[1] * inv, cam[2] * inv};
     const D wxp[3] = {w[1] * p[2] - w[2] * p[1], w[2] * p[0] - w[0] * p[2],
@@ -198,11 +211,13 @@ RLB_HD inline void Residual(const D* cam, double u, double v, double X, double Y
   res[1] = D::Constant(v) - yp;
 }
 
-RLB_HD inline bool SolveSpd6(const double* A, const double* b, double* x) {
-  double L[36];
+RLB_HD inline bool SolveSpd6(const double* A, const double* b, double* x, double* L, double* y) {
+  RLB_ROLLED
   for (int i = 0; i < 6; ++i) {
+    RLB_ROLLED
     for (int j = 0; j <= i; ++j) {
       double s = A[6 * i + j];
+      RLB_ROLLED
       for (int k = 0; k < j; ++k) s -= L[6 * i + k] * L[6 * j + k];
       if (i == j) {
         if (!(s > 0.0)) return false;
@@ -212,23 +227,34 @@ RLB_HD inline bool SolveSpd6(const double* A, const double* b, double* x) {
       }
     }
   }
-  double y[6];
+  RLB_ROLLED
   for (int i = 0; i < 6; ++i) {
     double s = b[i];
+    RLB_ROLLED
     for (int k = 0; k < i; ++k) s -= L[6 * i + k] * y[k];
     y[i] = s / L[6 * i + i];
   }
+  RLB_ROLLED
   for (int i = 5; i >= 0; --i) {
     double s = y[i];
+    RLB_ROLLED
     for (int k = i + 1; k < 6; ++k) s -= L[6 * k + i] * x[k];
     x[i] = s / L[6 * i + i];
   }
   return true;
 }
 
+// Vectors and matrices of one LM run (host: on the stack; device: one per warp in shared memory).
+struct LmWorkspace {
+  double x[6], xn[6], g[6], g2[6], rhs[6], step[6], y[6];
+  double JtJ[36], JtJ2[36], A[36], L[36];
+  double R[9], cam[6];
+};
+
 // Sequential lineariser (host): cost, J^T J and J^T r over the sample, points in sample order,
 // per point the two residual rows in order, entries accumulated as acc += d[a] * d[b].
 struct SequentialLineariser {
+  static constexpr bool kSpeculativeFull = false;  // the host follows Ceres' evaluation order
   int k;
   const int* idx;
   const double* p2d;
@@ -279,33 +305,49 @@ struct SequentialLineariser {
 // result is not usable (non-finite), like !summary.IsSolutionUsable() (.cc:202).
 // Lin provides Cost(x) and Full(x, JtJ, g) (see SequentialLineariser).
 template <class Lin>
-RLB_HD inline bool RefinePoseWith(const Lin& lin, double* cam) {
-  double x[6];
+RLB_HD inline bool RefinePoseWith(const Lin& lin, double* cam, LmWorkspace* w) {
+  double* x = w->x;
+  double* xn = w->xn;
+  double* JtJ = w->JtJ;
+  double* g = w->g;
+  double* JtJ_next = w->JtJ2;  // linearisation at the trial point; becomes current when accepted
+  double* g_next = w->g2;
+  double* A = w->A;
+  double* rhs = w->rhs;
+  double* step = w->step;
   for (int i = 0; i < 6; ++i) x[i] = cam[i];
-  double JtJ[36], g[6];
+  RLB_WARP_SYNC();
   double cost = lin.Full(x, JtJ, g);
   if (!(cost == cost) || cost > DBL_MAX) return false;
   double radius = 1e4;
   double shrink = 2.0;
   for (int iter = 0; iter < 50; ++iter) {
+    RLB_WARP_SYNC();
     double gmax = 0.0;
     for (int i = 0; i < 6; ++i) gmax = Max(gmax, std::fabs(g[i]));
     if (gmax <= 1e-10) break;
-    double A[36], rhs[6], step[6];
-    for (int i = 0; i < 36; ++i) A[i] = JtJ[i];
-    for (int i = 0; i < 6; ++i) {
-      double dgl = JtJ[7 * i];
-      dgl = Min(Max(dgl, 1e-6), 1e32);
-      A[7 * i] += dgl / radius;
-      rhs[i] = -g[i];
+    // A = JtJ + diag(clamp(diag JtJ)) / radius; every entry is written exactly once
+    RLB_ROLLED
+    for (int i = 0; i < 36; ++i) {
+      double v = JtJ[i];
+      if (i % 7 == 0) {
+        const double dgl = Min(Max(v, 1e-6), 1e32);
+        v += dgl / radius;
+      }
+      A[i] = v;
     }
-    bool ok = SolveSpd6(A, rhs, step);
+    for (int i = 0; i < 6; ++i) rhs[i] = -g[i];
+    RLB_WARP_SYNC();
+    bool ok = SolveSpd6(A, rhs, step, w->L, w->y);
+    RLB_WARP_SYNC();
     double model_decrease = 0.0;
     if (ok) {
       double gs = 0.0, sJs = 0.0;
+      RLB_ROLLED
       for (int i = 0; i < 6; ++i) {
         gs += g[i] * step[i];
         double t = 0.0;
+        RLB_ROLLED
         for (int j = 0; j < 6; ++j) t += JtJ[6 * i + j] * step[j];
         sJs += step[i] * t;
       }
@@ -318,22 +360,42 @@ RLB_HD inline bool RefinePoseWith(const Lin& lin, double* cam) {
       if (radius < 1e-32) break;
       continue;
     }
-    double xn[6], sn = 0.0, xnorm = 0.0;
+    double sn = 0.0, xnorm = 0.0;
     for (int i = 0; i < 6; ++i) {
       xn[i] = x[i] + step[i];
       sn += step[i] * step[i];
       xnorm += x[i] * x[i];
     }
+    RLB_WARP_SYNC();
     sn = std::sqrt(sn);
     xnorm = std::sqrt(xnorm);
     if (sn <= 1e-8 * (xnorm + 1e-8)) break;
-    const double cost_new = lin.Cost(xn);
+    // Ceres evaluates the cost at the trial point and, if the step is accepted, the Jacobian
+    // there. Most steps are accepted, so the trial point is linearised right away: its cost is
+    // the same number (same value arithmetic, same summation order), and an accepted step only
+    // swaps the buffers instead of evaluating every residual a second time.
+    const double cost_new = Lin::kSpeculativeFull ? lin.Full(xn, JtJ_next, g_next) : lin.Cost(xn);
     const double rho = (cost - cost_new) / model_decrease;
     if (cost_new == cost_new && rho > 1e-3) {
       const double delta = cost - cost_new;
-      for (int i = 0; i < 6; ++i) x[i] = xn[i];
       const double prev = cost;
-      cost = lin.Full(x, JtJ, g);
+      if (Lin::kSpeculativeFull) {
+        double* t = x;
+        x = xn;
+        xn = t;
+        t = JtJ;
+        JtJ = JtJ_next;
+        JtJ_next = t;
+        t = g;
+        g = g_next;
+        g_next = t;
+        cost = cost_new;
+      } else {
+        RLB_WARP_SYNC();
+        for (int i = 0; i < 6; ++i) x[i] = xn[i];
+        RLB_WARP_SYNC();
+        cost = lin.Full(x, JtJ, g);
+      }
       const double t = 2.0 * rho - 1.0;
       radius = radius / Max(1.0 / 3.0, 1.0 - t * t * t);
       radius = Min(radius, 1e16);
@@ -345,6 +407,7 @@ RLB_HD inline bool RefinePoseWith(const Lin& lin, double* cam) {
       if (radius < 1e-32) break;
     }
   }
+  RLB_WARP_SYNC();
   for (int i = 0; i < 6; ++i)
     if (!(x[i] - x[i] == 0.0)) return false;
   for (int i = 0; i < 6; ++i) cam[i] = x[i];
@@ -354,29 +417,37 @@ RLB_HD inline bool RefinePoseWith(const Lin& lin, double* cam) {
 inline bool RefinePose(int k, const int* idx, const double* p2d, const double* p3d, double fx,
                        double fy, double* cam) {
   const SequentialLineariser lin = {k, idx, p2d, p3d, fx, fy};
-  return RefinePoseWith(lin, cam);
+  LmWorkspace w;
+  return RefinePoseWith(lin, cam, &w);
 }
 
 // CalibratedAbsolutePoseEstimator::LeastSquares around the LM (.cc:170-212): column-major
 // [R | c] -> (angle-axis, c) -> refine -> back. The pose is left untouched when the refinement
 // is not usable.
 template <class Lin>
-RLB_HD inline void LeastSquaresWith(const Lin& lin, double* pose /* col-major 3x4 [R|c] */) {
-  double R[9];
+RLB_HD inline void LeastSquaresWith(const Lin& lin, double* pose /* col-major 3x4 [R|c] */,
+                                    LmWorkspace* w) {
+  double* R = w->R;
+  double* cam = w->cam;
+  RLB_WARP_SYNC();
   for (int r = 0; r < 3; ++r)
     for (int c = 0; c < 3; ++c) R[3 * r + c] = pose[r + 3 * c];
-  double cam[6];
+  RLB_WARP_SYNC();
   RotationToAngleAxis(R, cam);
   cam[3] = pose[9];
   cam[4] = pose[10];
   cam[5] = pose[11];
-  if (!RefinePoseWith(lin, cam)) return;
+  RLB_WARP_SYNC();
+  if (!RefinePoseWith(lin, cam, w)) return;
+  RLB_WARP_SYNC();
   AngleAxisToRotation(cam, R);
+  RLB_WARP_SYNC();
   for (int r = 0; r < 3; ++r)
     for (int c = 0; c < 3; ++c) pose[r + 3 * c] = R[3 * r + c];
   pose[9] = cam[3];
   pose[10] = cam[4];
   pose[11] = cam[5];
+  RLB_WARP_SYNC();
 }
 
 }  // namespace refine

@@ -28,6 +28,17 @@
 #include <cfloat>
 #include <climits>
 
+// A/B switches of the LM inner code (see DESIGN.md 3b for the measurements)
+#ifndef RLB_LM_SMEM
+#define RLB_LM_SMEM 0   // LM vectors/matrices: one copy per warp in shared memory (else per lane, local)
+#endif
+#ifndef RLB_ROLL_LM
+#define RLB_ROLL_LM 0   // keep the 6x6 loops rolled
+#endif
+#ifndef RLB_FULL_SLICES
+#define RLB_FULL_SLICES 0  // form the 6 partials in two slices of 3 (smaller body, more instructions)
+#endif
+
 #include "../../examples/pose_refinement.h"
 #include "p3p_device.cuh"
 #include "rlb_internal.cuh"
@@ -53,6 +64,7 @@ __device__ __noinline__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
   if (lane == 0) {
     uint32_t x = seed;
     s[0] = x;
+#pragma unroll 1
     for (int i = 1; i < 624; ++i) {
       x = 1812433253u * (x ^ (x >> 30)) + static_cast<uint32_t>(i);
       s[i] = x;
@@ -64,6 +76,7 @@ __device__ __noinline__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
 // Regenerates the 624 words in place, 32 per round: word k needs the OLD k, k+1 and either the
 // old k+397 (k < 227) or the NEW k-227, which earlier rounds have already written.
 __device__ __noinline__ void mt_twist(uint32_t* s, int lane) {
+#pragma unroll 1
   for (int base = 0; base < 623; base += 32) {
     const int k = base + lane;
     uint32_t v = 0;
@@ -244,6 +257,13 @@ struct WarpShared {
   uint32_t mt_lo[624];
   double slab[kSlabDoubles];
   double sums[32];
+  // Warp-uniform state lives here ONCE per warp instead of 32 times in local memory (every lane
+  // executes the same scalar code and writes identical values): the LM vectors / matrices and
+  // the models handed between the phases.
+#if RLB_LM_SMEM
+  refine::LmWorkspace lm;
+#endif
+  double models[5][12];  // 0 best, 1 best minimal, 2 candidate, 3 LO initial / final refit, 4 LO step
   int32_t samp[32];
 };
 
@@ -338,53 +358,64 @@ __device__ __noinline__ double sweep32(const Query& q, const double* P, double t
 // ScoreModel fused with GetInliers for ONE model (ransac.h:295-336), reference formulation
 // (calibrated_absolute_pose_estimator.cc:154-167): lane l evaluates matches l, l+32, ...;
 // the ascending inlier list is compacted with a ballot per 32 matches.
-__device__ __noinline__ int fused_pass(const Query& q, const double* __restrict__ Pin, double thr_inl, bool want_score,
+__device__ __noinline__ int fused_pass(const Query& qr, const double* __restrict__ Pin, double thr_inl, bool want_score,
                           double thr_score, int32_t* __restrict__ list, double* score, int lane) {
+  // Query fields live in the caller's local memory: read them once (stores to `list` could alias)
+  const int qn = qr.n;
+  const double* __restrict__ qp2 = qr.p2;
+  const double* __restrict__ qp3 = qr.p3;
+  const double qfx = qr.fx, qfy = qr.fy;
   int off = 0;
   double sc = 0.0;
   const unsigned lt = (1u << lane) - 1u;
   double P[12];  // the model lives in registers for the whole pass (the caller's copy is in local memory)
 #pragma unroll
   for (int i = 0; i < 12; ++i) P[i] = Pin[i];
-  // software pipeline: the next match is in flight while the current one is evaluated
-  double c0 = 0.0, c1 = 0.0, c2 = 0.0, cu = 0.0, cv = 0.0;
-  if (lane < q.n) {
-    const double* X = q.p3 + 3 * static_cast<size_t>(lane);
-    const double* uv = q.p2 + 2 * static_cast<size_t>(lane);
-    c0 = X[0];
-    c1 = X[1];
-    c2 = X[2];
-    cu = uv[0];
-    cv = uv[1];
-  }
+  // Two matches per lane and iteration (i and i + 32): f64 results take ~18 cycles to come
+  // back, so the two independent error chains overlap; the loads of the next pair are in flight
+  // while the current pair is evaluated. Sums and lists keep the order of the 32-wide loop
+  // (lane l adds matches l, l + 32, l + 64, ... in that order; the list is compacted per 32).
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, au = 0.0, av = 0.0;
+  double b0 = 0.0, b1 = 0.0, b2 = 0.0, bu = 0.0, bv = 0.0;
+  auto load = [&](int i, double& x0, double& x1, double& x2, double& u, double& v) {
+    if (i < qn) {
+      const double* X = qp3 + 3 * static_cast<size_t>(i);
+      const double* uv = qp2 + 2 * static_cast<size_t>(i);
+      x0 = X[0];
+      x1 = X[1];
+      x2 = X[2];
+      u = uv[0];
+      v = uv[1];
+    }
+  };
+  load(lane, a0, a1, a2, au, av);
+  load(lane + 32, b0, b1, b2, bu, bv);
 #pragma unroll 1
-  for (int base = 0; base < q.n; base += 32) {
-    const int i = base + lane;
-    const bool live = i < q.n;
-    double n0 = 0.0, n1 = 0.0, n2 = 0.0, nu = 0.0, nv = 0.0;
-    if (i + 32 < q.n) {
-      const double* X = q.p3 + 3 * static_cast<size_t>(i + 32);
-      const double* uv = q.p2 + 2 * static_cast<size_t>(i + 32);
-      n0 = X[0];
-      n1 = X[1];
-      n2 = X[2];
-      nu = uv[0];
-      nv = uv[1];
+  for (int base = 0; base < qn; base += 64) {
+    const int ia = base + lane, ib = ia + 32;
+    const bool live_a = ia < qn, live_b = ib < qn;
+    double na0 = 0.0, na1 = 0.0, na2 = 0.0, nau = 0.0, nav = 0.0;
+    double nb0 = 0.0, nb1 = 0.0, nb2 = 0.0, nbu = 0.0, nbv = 0.0;
+    load(ia + 64, na0, na1, na2, nau, nav);
+    load(ib + 64, nb0, nb1, nb2, nbu, nbv);
+    double ea = DBL_MAX, eb = DBL_MAX;
+    if (live_a) ea = p3pdev::reproj_sq_error_v(P, a0, a1, a2, au, av, qfx, qfy);
+    if (live_b) eb = p3pdev::reproj_sq_error_v(P, b0, b1, b2, bu, bv, qfx, qfy);
+    if (want_score) {  // std::min(e, thr): NaN propagates
+      if (live_a) sc += (thr_score < ea) ? thr_score : ea;
+      if (live_b) sc += (thr_score < eb) ? thr_score : eb;
     }
-    double e = DBL_MAX;
-    if (live) {
-      e = p3pdev::reproj_sq_error_v(P, c0, c1, c2, cu, cv, q.fx, q.fy);
-      if (want_score) sc += (thr_score < e) ? thr_score : e;  // std::min(e, thr): NaN propagates
+    const bool in_a = live_a && (ea < thr_inl);
+    const bool in_b = live_b && (eb < thr_inl);
+    const unsigned mask_a = __ballot_sync(kFull, in_a);
+    const unsigned mask_b = __ballot_sync(kFull, in_b);
+    if (list != nullptr) {
+      if (in_a) list[off + __popc(mask_a & lt)] = ia;
+      if (in_b) list[off + __popc(mask_a) + __popc(mask_b & lt)] = ib;
     }
-    const bool in = live && (e < thr_inl);
-    const unsigned mask = __ballot_sync(kFull, in);
-    if (in && list != nullptr) list[off + __popc(mask & lt)] = i;
-    off += __popc(mask);
-    c0 = n0;
-    c1 = n1;
-    c2 = n2;
-    cu = nu;
-    cv = nv;
+    off += __popc(mask_a) + __popc(mask_b);
+    a0 = na0; a1 = na1; a2 = na2; au = nau; av = nav;
+    b0 = nb0; b1 = nb1; b2 = nb2; bu = nbu; bv = nbv;
   }
   if (want_score) *score = warp_sum(sc);
   __syncwarp();
@@ -396,6 +427,7 @@ __device__ __noinline__ int fused_pass(const Query& q, const double* __restrict_
 // entry of (J^T r, lower triangle of J^T J) and lane 27 the cost, each adding the chunk's
 // contributions in match order, so every sum has the host's order of operations.
 struct WarpLineariser {
+  static constexpr bool kSpeculativeFull = true;  // see refine::RefinePoseWith
   int k;
   const int32_t* idx;  // sample (shared or global), k entries
   const double* p2d;
@@ -404,9 +436,11 @@ struct WarpLineariser {
   double* slab;  // [32][14]
   double* sums;  // [28]
   int lane;
+  long long* prof;
 
   RLB_HD __noinline__ double Cost(const double* c) const {
 #ifdef __CUDA_ARCH__
+    const long long t0 = clock64();
     refine::Value cam[6];
     for (int i = 0; i < 6; ++i) cam[i] = refine::Value::Constant(c[i]);
     double cost = 0.0;
@@ -422,9 +456,11 @@ struct WarpLineariser {
         mine = 0.5 * (r[0].a * r[0].a + r[1].a * r[1].a);
       }
       const int m = min(32, k - base);
-#pragma unroll 1
+#pragma unroll 4
       for (int j = 0; j < m; ++j) cost += __shfl_sync(kFull, mine, j);
     }
+    prof[5] += clock64() - t0;
+    prof[11] += 1;
     return cost;
 #else
     (void)c;
@@ -434,8 +470,7 @@ struct WarpLineariser {
 
   RLB_HD __noinline__ double Full(const double* c, double* JtJ, double* Jtr) const {
 #ifdef __CUDA_ARCH__
-    refine::Dual cam[6];
-    for (int i = 0; i < 6; ++i) cam[i] = refine::Dual::Variable(c[i], i);
+    const long long t0 = clock64();
     // entry owned by this lane: 0..5 = Jtr[a]; 6..26 = JtJ[a][b], b <= a; 27 = cost
     int ea = 0, eb = 0;
     if (lane < 6) {
@@ -457,22 +492,48 @@ struct WarpLineariser {
       __syncwarp();
       if (s < k) {
         const int i = idx[s];
-        refine::Dual r[2];
-        refine::Residual(cam, p2d[2 * static_cast<size_t>(i)], p2d[2 * static_cast<size_t>(i) + 1],
-                         p3d[3 * static_cast<size_t>(i)], p3d[3 * static_cast<size_t>(i) + 1],
-                         p3d[3 * static_cast<size_t>(i) + 2], fx, fy, r);
+        const double u = p2d[2 * static_cast<size_t>(i)], v = p2d[2 * static_cast<size_t>(i) + 1];
+        const double X = p3d[3 * static_cast<size_t>(i)], Y = p3d[3 * static_cast<size_t>(i) + 1],
+                     Z = p3d[3 * static_cast<size_t>(i) + 2];
         double* row = slab + 14 * lane;
+#if RLB_FULL_SLICES
+        // The six partials in two slices of three (rotation, centre): each partial is the same
+        // sequence of operations as in the host's 6-wide dual numbers.
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          typedef refine::DualN<3> D3;
+          D3 cam[6];
+#pragma unroll
+          for (int a = 0; a < 6; ++a) cam[a] = D3::Variable(c[a], a - 3 * half);
+          D3 r[2];
+          refine::Residual(cam, u, v, X, Y, Z, fx, fy, r);
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            row[7 * e] = r[e].a;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) row[7 * e + 1 + 3 * half + a] = r[e].d[a];
+          }
+        }
+#else
+        refine::Dual cam[6];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) cam[a] = refine::Dual::Variable(c[a], a);
+        refine::Dual r[2];
+        refine::Residual(cam, u, v, X, Y, Z, fx, fy, r);
+#pragma unroll
         for (int e = 0; e < 2; ++e) {
           row[7 * e] = r[e].a;
+#pragma unroll
           for (int a = 0; a < 6; ++a) row[7 * e + 1 + a] = r[e].d[a];
         }
+#endif
       }
       __syncwarp();
       const int m = min(32, k - base);
       if (lane < 28) {
         // one loop for all 28 entries: acc += row[ia] * row[ib] for residual row 0, then row 1
         // (the cost lane has ia = ib = 0 and adds 0.5 * (r0^2 + r1^2) per match)
-#pragma unroll 1
+#pragma unroll 4
         for (int j = 0; j < m; ++j) {
           const double* row = slab + 14 * j;
           const double t0 = row[ia] * row[ib];
@@ -499,6 +560,8 @@ struct WarpLineariser {
       }
     const double cost = sums[27];
     __syncwarp();
+    prof[4] += clock64() - t0;
+    prof[10] += 1;
     return cost;
 #else
     (void)c;
@@ -524,7 +587,26 @@ struct Run {
   // counters (reported per query)
   int passes;
   int lsq_calls;
+  // debug_flags bit 1: cycles per phase (0 hypothesis batches, 1 sweep32, 2 fused_pass, 3 shuffles,
+  // 4 Full, 5 Cost, 6 least_squares, 7 whole query, 8 LO minimal solver, 9 setup, 10 #Full, 11 #Cost)
+  long long prof[12];
 };
+#define RLB_PROF_BEGIN(R) const long long prof_t0__ = clock64()
+#define RLB_PROF_END(R, slot) (R).prof[slot] += clock64() - prof_t0__
+
+__device__ __forceinline__ int timed_pass(Run& R, const double* P, double thr_inl, bool want_score,
+                                          double thr_score, int32_t* list, double* score) {
+  RLB_PROF_BEGIN(R);
+  const int n = fused_pass(R.q, P, thr_inl, want_score, thr_score, list, score, R.lane);
+  RLB_PROF_END(R, 2);
+  ++R.passes;
+  return n;
+}
+__device__ __forceinline__ void timed_shuffle(Run& R, const int32_t* list, int n, int target) {
+  RLB_PROF_BEGIN(R);
+  shuffle_resize(R.lo_rng, list, n, target, R.sh->samp, R.lane, R.force_slow);
+  RLB_PROF_END(R, 3);
+}
 
 // utils.h:110-140.
 __device__ __noinline__ uint32_t num_required_iterations(double inlier_ratio, double prob_missing, int sample_size,
@@ -545,6 +627,7 @@ __device__ __forceinline__ void update_best(double score, const double* m, doubl
 #pragma unroll
     for (int i = 0; i < 12; ++i) best[i] = m[i];
   }
+  __syncwarp();
 }
 
 // CalibratedAbsolutePoseEstimator::LeastSquares on sample idx[0..k).
@@ -559,7 +642,15 @@ __device__ __noinline__ void least_squares(Run& R, const int32_t* idx, int k, do
   lin.slab = R.sh->slab;
   lin.sums = R.sh->sums;
   lin.lane = R.lane;
-  refine::LeastSquaresWith(lin, pose);
+  lin.prof = R.prof;
+  RLB_PROF_BEGIN(R);
+#if RLB_LM_SMEM
+  refine::LeastSquaresWith(lin, pose, &R.sh->lm);
+#else
+  refine::LmWorkspace w;
+  refine::LeastSquaresWith(lin, pose, &w);
+#endif
+  RLB_PROF_END(R, 6);
   ++R.lsq_calls;
 }
 
@@ -590,13 +681,12 @@ __device__ __noinline__ void score_then_fit(Run& R, bool want_score, double fit_
                                double* best) {
   const double thr = R.opt.sq_thr;
   double score = kNever;
-  const int n_inl = fused_pass(R.q, m, fit_thr, want_score, thr, R.list_fit, &score, R.lane);
-  ++R.passes;
+  const int n_inl = timed_pass(R, m, fit_thr, want_score, thr, R.list_fit, &score);
   if (want_score) update_best(score, m, best_score, best);
   if (n_inl < 4) return;
   const int cap = R.opt.min_sample_mult * 4;
   const int target = min(cap, n_inl);
-  shuffle_resize(R.lo_rng, R.list_fit, n_inl, target, R.sh->samp, R.lane, R.force_slow);
+  timed_shuffle(R, R.list_fit, n_inl, target);
   least_squares(R, R.sh->samp, target, m);
 }
 
@@ -607,25 +697,34 @@ __device__ __noinline__ void local_optimization(Run& R, double* best_minimal_mod
   const double thr = R.opt.sq_thr;
   const double mult = R.opt.thr_mult;
 
-  double m_init[12];
+  double* m_init = R.sh->models[3];
+  __syncwarp();
 #pragma unroll
   for (int i = 0; i < 12; ++i) m_init[i] = best_minimal_model[i];
+  __syncwarp();
   score_then_fit(R, false, thr * mult, m_init, nullptr, nullptr);
 
   double score = kNever;
-  const int n_base = fused_pass(R.q, m_init, thr * mult, true, thr, R.list_base, &score, R.lane);
-  ++R.passes;
+  const int n_base = timed_pass(R, m_init, thr * mult, true, thr, R.list_base, &score);
   update_best(score, m_init, score_best_minimal, best_minimal_model);
 
   const int non_min_size = max(6, min(4 * R.opt.non_min_sample_mult, n_base / 2));
   for (int r = 0; r < R.opt.lo_steps; ++r) {
-    shuffle_resize(R.lo_rng, R.list_base, n_base, non_min_size, R.sh->samp, R.lane, R.force_slow);
+    timed_shuffle(R, R.list_base, n_base, non_min_size);
     // NonMinimalSolver (.cc:141-151): minimal solver on the first four, then LeastSquares.
     int s4[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) s4[i] = R.sh->samp[i];
-    double m[12];
-    if (!minimal_solver(R.q, s4, thr, m)) continue;
+    double* m = R.sh->models[4];
+    __syncwarp();
+    bool solved;
+    {
+      RLB_PROF_BEGIN(R);
+      solved = minimal_solver(R.q, s4, thr, m);
+      RLB_PROF_END(R, 8);
+    }
+    if (!solved) continue;
+    __syncwarp();
     least_squares(R, R.sh->samp, non_min_size, m);
 
     score_then_fit(R, true, thr, m, score_best_minimal, best_minimal_model);  // ransac.h:386-391
@@ -640,8 +739,7 @@ __device__ __noinline__ void local_optimization(Run& R, double* best_minimal_mod
         score_then_fit(R, true, fit_thr, m, score_best_minimal, best_minimal_model);
       } else {
         double sc = kNever;
-        fused_pass(R.q, m, thr, true, thr, nullptr, &sc, R.lane);
-        ++R.passes;
+        timed_pass(R, m, thr, true, thr, nullptr, &sc);
         update_best(sc, m, score_best_minimal, best_minimal_model);
       }
     }
@@ -663,9 +761,9 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
   int num_lo = 0;
 
   uint32_t max_iters = max(o.max_iters, o.min_iters);
-  double best_minimal_model[12];
-#pragma unroll
-  for (int i = 0; i < 12; ++i) best_minimal_model[i] = 0.0;
+  double* best_minimal_model = R.sh->models[1];
+  if (lane < 12) best_minimal_model[lane] = 0.0;
+  __syncwarp();
   double best_minimal_score = kNever;
 
   // this lane's hypothesis of the current speculative batch
@@ -677,8 +775,7 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
   double my_score = kNever;
 
   auto refresh_termination = [&]() {  // ransac.h:170-177, 231-238
-    best_num_inliers = fused_pass(R.q, best_model, thr, false, thr, R.list_best, nullptr, lane);
-    ++R.passes;
+    best_num_inliers = timed_pass(R, best_model, thr, false, thr, R.list_best, nullptr);
     inlier_ratio = static_cast<double>(best_num_inliers) / static_cast<double>(n);
     max_iters = num_required_iterations(inlier_ratio, 1.0 - o.success_prob, 4, o.min_iters, o.max_iters);
   };
@@ -695,6 +792,7 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
       // Speculate on the next (up to) 32 iterations: samples are a pure function of the
       // sampler stream, hypotheses do not depend on the LO stream.
       const uint32_t bound = max(max_iters, it + 1u);
+      RLB_PROF_BEGIN(R);
       batch_first = it;
       batch_count = min(32u, bound - it);
       int mine[4] = {0, 0, 0, 0};
@@ -715,10 +813,13 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
 #pragma unroll
           for (int i = 0; i < 12; ++i) finite = finite && (my_model[i] - my_model[i] == 0.0);
           // a model with a non-finite entry scores NaN and never wins (finalize_kernel)
+          const long long ts = clock64();
           my_score = finite ? sweep32(R.q, my_model, thr) : __longlong_as_double(0x7ff8000000000000LL);
+          R.prof[1] += clock64() - ts;
         }
       }
       __syncwarp();
+      RLB_PROF_END(R, 0);
     }
 
     const int slot = static_cast<int>(it - batch_first);
@@ -729,14 +830,18 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
     const bool have = s32 < kNever;  // GetBestEstimatedModelId: NaN never becomes the local best
     if (have) local_score = s32;
     const bool forced = (it == o.lo_start);
-    double cand[12];
+    double* cand = R.sh->models[2];
+    __syncwarp();
 #pragma unroll
-    for (int i = 0; i < 12; ++i) cand[i] = __shfl_sync(kFull, my_model[i], slot);
+    for (int i = 0; i < 12; ++i) {
+      const double v = __shfl_sync(kFull, my_model[i], slot);
+      cand[i] = v;
+    }
+    __syncwarp();
     if (have && (forced || local_score <= best_minimal_score * (1.0 + 4e-4) ||
                  best_minimal_score == kNever)) {
       // the f32 sweep says "maybe better": settle it with the exact f64 score
-      fused_pass(R.q, cand, thr, true, thr, nullptr, &local_score, lane);
-      ++R.passes;
+      timed_pass(R, cand, thr, true, thr, nullptr, &local_score);
     }
 
     if (local_score < best_minimal_score || forced) {  // ransac.h:195-196
@@ -745,6 +850,7 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
         best_minimal_score = local_score;
 #pragma unroll
         for (int i = 0; i < 12; ++i) best_minimal_model[i] = cand[i];
+        __syncwarp();
         update_best(best_minimal_score, best_minimal_model, &best_model_score, best_model);
       }
       const bool run_lo = (it >= o.lo_start && best_minimal_score < kNever);
@@ -763,23 +869,24 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
   if (num_iterations <= o.lo_start && best_model_score < kNever) {
     ++num_lo;
     local_optimization(R, best_model, &best_model_score);
-    best_num_inliers = fused_pass(R.q, best_model, thr, false, thr, R.list_best, nullptr, lane);
-    ++R.passes;
+    best_num_inliers = timed_pass(R, best_model, thr, false, thr, R.list_best, nullptr);
     inlier_ratio = static_cast<double>(best_num_inliers) / static_cast<double>(n);
   }
 
   if (o.final_lsq) {  // ransac.h:257-272
-    double refined[12];
+    double* refined = R.sh->models[3];
+    __syncwarp();
 #pragma unroll
     for (int i = 0; i < 12; ++i) refined[i] = best_model[i];
+    __syncwarp();
     least_squares(R, R.list_best, best_num_inliers, refined);
     double score = kNever;
-    const int n_inl = fused_pass(R.q, refined, thr, true, thr, R.list_fit, &score, lane);
-    ++R.passes;
+    const int n_inl = timed_pass(R, refined, thr, true, thr, R.list_fit, &score);
     if (score < best_model_score) {
       best_model_score = score;
 #pragma unroll
       for (int i = 0; i < 12; ++i) best_model[i] = refined[i];
+      __syncwarp();
       best_num_inliers = n_inl;
       for (int i = lane; i < n_inl; i += 32) R.list_best[i] = R.list_fit[i];
       inlier_ratio = static_cast<double>(n_inl) / static_cast<double>(n);
@@ -801,7 +908,7 @@ __device__ void run_query(Run& R, double* best_model, rlb_localize_result* res) 
 }  // namespace
 
 #ifndef RLB_LOC_MINB
-#define RLB_LOC_MINB 4
+#define RLB_LOC_MINB 3
 #endif
 __global__ void __launch_bounds__(kWarpsPerCta * 32, RLB_LOC_MINB) localize_kernel(const LocalizeArgs A) {
   __shared__ WarpShared shared[kWarpsPerCta];
@@ -870,6 +977,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, RLB_LOC_MINB) localize_kern
     R.list_best = (A.inliers != nullptr) ? A.inliers + o0 : lists + 2 * A.nmax;
     R.passes = 0;
     R.lsq_calls = 0;
+    for (int i = 0; i < 12; ++i) R.prof[i] = 0;
+    const long long t_query = clock64();
     prepare_soa32(R.q, lane);
 
     // Sampler and local optimisation own separate engines seeded alike (ransac.h:142-144,
@@ -882,14 +991,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, RLB_LOC_MINB) localize_kern
     R.lo_rng.s = R.sh->mt_lo;
     R.lo_rng.idx = 624;
 
-    double best_model[12];
-#pragma unroll
-    for (int i = 0; i < 12; ++i) best_model[i] = 0.0;
+    double* best_model = R.sh->models[0];
+    if (lane < 12) best_model[lane] = 0.0;
+    __syncwarp();
+    R.prof[9] = clock64() - t_query;
     run_query(R, best_model, res);
-    if (lane == 0) {
-#pragma unroll
-      for (int i = 0; i < 12; ++i) pose_out[i] = best_model[i];
+    __syncwarp();
+    R.prof[7] = clock64() - t_query;
+    if ((A.opt.debug_flags & 2) && A.inliers != nullptr && n >= 64 && lane == 0) {
+      // debug: lane 0's cycle counters replace the tail of this query's inlier region
+      long long* out = reinterpret_cast<long long*>(A.inliers + ((o0 + n - 24) & ~1LL));
+      for (int i = 0; i < 12; ++i) out[i] = R.prof[i];
     }
+    if (lane < 12) pose_out[lane] = best_model[lane];
     __syncwarp();
   }
 }

@@ -56,7 +56,9 @@ print(f"total warp-instructions {ti}  samples {ts}")
 print("stall totals:", ", ".join(f"{h[6:]} {100*v/ts:.1f}%" for h, v in st_tot.most_common(8)))
 print("--- by function")
 for f, v in fsamp.most_common(16):
-    print(f"{100*v/ts:6.2f}% samples {100*finst[f]/ti:6.2f}% inst  {str(f)[:100]}")
+    d = subprocess.run(["c++filt", str(f)], capture_output=True, text=True).stdout.strip()
+    d = re.sub(r"\(anonymous namespace\)::|_INTERNAL_[0-9a-f_]+localize_kernels_cu_[0-9a-f]+::", "", d)
+    print(f"{100*v/ts:6.2f}% samples {100*finst[f]/ti:6.2f}% inst  {d[:90]}")
 print("--- by line")
 for l, v in samp.most_common(top):
     tops = ", ".join(f"{h[6:]} {100*x/max(v,1):.0f}%" for h, x in st_line[l].most_common(3))
