@@ -39,6 +39,27 @@ WORKLOADS = {
 }
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout. Libraries print there too (NCCL's version banner, for one), so
+    fd 1 is pointed at stderr for the duration of the run and the line goes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(text):
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        print(text, flush=True)
+    else:
+        os.write(_REAL_STDOUT, (text + "\n").encode())
+
+
 def make_instance(n, data_seed=9000):
     from ransaclib_b200 import synth
 
@@ -234,7 +255,7 @@ def run_ours(args):
 
     if args.profile:
         if rank == 0:
-            print(json.dumps({"profile_run": True, "value": value, "ms_per_step": total_ms / args.steps,
+            emit(json.dumps({"profile_run": True, "value": value, "ms_per_step": total_ms / args.steps,
                               "sweep_ms": float(np.mean(sweep_ms)), "inlier_ms": float(np.mean(inl_ms)),
                               "gpu_launches": int(launches)}))
         if world > 1:
@@ -327,7 +348,7 @@ def run_ours(args):
         if world == 1:
             loc["cpu_baseline"] = cpu_baseline_c4(budget_queries=64, threads=1)
         line["localization"] = loc  # "P3P LO-MSAC localizations/sec" at this N (same run, same GPUs)
-    print(json.dumps(line))
+    emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
@@ -420,7 +441,7 @@ def run_reference(args):
                                 "unit": "localizations/s", "cpu_baseline": r,
                                 "e2e": {"value": r["value"], "unit": "localizations/s", "h2d_bytes_per_step": 0,
                                         "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(json.dumps(line))
 
 # ------------------------------------------------- C4: batched localization (query-sharded)
 C4 = dict(q=4096, n=2000, thr_px=12.0, lo_steps=10, min_iters=100, max_iters=10000,
@@ -588,7 +609,7 @@ def run_ours_c4(args):
     line = measure_c4(args, rank, world, local, dist, args.steps, args.warmup)
     if rank == 0:
         line["cpu_baseline"] = cpu_baseline_c4(budget_queries=64, threads=1) if world == 1 else None
-        print(json.dumps(line))
+        emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
@@ -637,7 +658,7 @@ def run_reference_c4(args):
         if i >= args.warmup:
             res.append(r)
     value = sum(per_step for _ in res) / sum(r["seconds"] for r in res)
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "P3P LO-MSAC localizations/sec", "value": value, "unit": "localizations/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", 1)), "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": sum(r["seconds"] for r in res) / args.steps * 1e3, "higher_is_better": True,
@@ -663,6 +684,7 @@ def main():
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: skips the e2e leg, the CPU baseline and the peak microbenchmarks")
     args = ap.parse_args()
+    claim_stdout()
     if args.workload == "c4":
         (run_reference_c4 if args.impl == "reference" else run_ours_c4)(args)
     elif args.impl == "reference":
