@@ -56,6 +56,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
   }
 }
+// 1 / x in f64 without the IEEE division routine. `1.0 / pz` compiles to MUFU.RCP64H + ~10
+// dependent DFMA + a range test that branches to a slow-path CALL; the branch structure (not the
+// arithmetic) halved the f64 sweep: 3.07e11 -> 6.2e11 evals/s without it. The 20-bit seed and
+// two Newton steps are within 1 ulp of the exact reciprocal, far inside the 1e-9 parity band.
+// x == 0 returns the seed itself (+-inf), so z == 0 still falls through to inf / NaN exactly like
+// the reference's px / pz (calibrated_absolute_pose_estimator.cc:160-165); subnormal |x| counts as 0.
+__device__ __forceinline__ double rcp_f64(double x) {
+  double r0;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r0) : "d"(x));
+  double r = fma(fma(-x, r0, 1.0), r0, r0);
+  r = fma(fma(-x, r, 1.0), r, r);
+  return (x == 0.0) ? r0 : r;
+}
 __device__ __forceinline__ float rcp_approx(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -127,7 +140,7 @@ __device__ __forceinline__ double PoseF<double>::eval(const Model& m, const doub
   const double pz = fma(m.r[6], p[0], fma(m.r[7], p[1], fma(m.r[8], p[2], m.t[2])));
   const double px = fma(m.r[0], p[0], fma(m.r[1], p[1], fma(m.r[2], p[2], m.t[0])));
   const double py = fma(m.r[3], p[0], fma(m.r[4], p[1], fma(m.r[5], p[2], m.t[1])));
-  const double inv = 1.0 / pz;
+  const double inv = rcp_f64(pz);
   const double du = fma(px, inv, -p[3]);
   const double dv = fma(py, inv, -p[4]);
   const double e = fma(du, du, dv * dv);
@@ -550,7 +563,7 @@ static cudaError_t launch_sweep_pose_x2(const DeviceData& d, const SweepArgs& a,
 // Hypotheses per thread of the sweep that launch_sweep will pick (the host sizes the grid with it).
 int sweep_hyps_per_thread(int kind, int precision, int variant) {
   if (kind == RLB_KIND_POSE) {
-    if (precision != RLB_F32) return 2;
+    if (precision != RLB_F32) return variant == 7 ? 4 : (variant == 8 ? 1 : 2);
     switch (variant) {
       case 2: return 2;
       case 3: return 8;
@@ -578,6 +591,8 @@ cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision,
         default: return launch_sweep_pose_x2<4>(d, a, st);
       }
     }
+    if (a.variant == 7) return launch_sweep_t<PoseF, double, 4>(d, a, st);  // A/B only
+    if (a.variant == 8) return launch_sweep_t<PoseF, double, 1>(d, a, st);  // A/B only
     return launch_sweep_t<PoseF, double, 2>(d, a, st);
   }
   if (precision == RLB_F32) return launch_sweep_t<LineF, float, 4>(d, a, st);

@@ -328,3 +328,31 @@ def test_sharded_round_emulated_ranks(ctx, pose_case):
         # the torch-side selection used under gloo/NCCL agrees with the kernel
         row, ok = sharding.select_winner(recs)
         assert bool(ok) and int(recs[row, 1].item()) == ref["best_id"]
+
+
+def test_zero_depth_falls_through_like_the_reference(ctx):
+    """p.z == 0 is NOT behind the camera (`p.z < 0` only): the reference divides by
+    zero, so the error is +inf (px != 0: contributes thr, not an inlier) or NaN (px == py == 0: 0/0,
+    which poisons the score through std::min). The f64 kernels replace the IEEE division by a seeded
+    reciprocal and must keep exactly this behaviour. One-point data sets make the recentred depth an
+    exact zero."""
+    O = ol.oracle()
+    f = 100.0
+    R = np.eye(3)
+    for X, want_nan in (((1.0, 2.0, 5.0), False), ((0.0, 0.0, 5.0), True)):
+        p2 = np.array([[3.0, 4.0]])
+        p3 = np.array([X])
+        model = synth.pose_to_model(R, np.array([0.0, 0.0, 5.0]))  # depth of the point: exactly 0
+        want_s, want_c = ol.pose_score(O, f, f, p2, p3, model[None, :], 144.0)
+        sc = ctx.pose_scorer(p2, p3, f, f)
+        s, c, bid, bsc = sc.score_models(model[None, :], 144.0)
+        err = sc.eval_errors(model)
+        lists, counts, score = sc.get_inliers(model, 144.0, 144.0)
+        assert counts[0] == 0 and want_c[0] == 0 and c[0] == 0
+        if want_nan:
+            assert np.isnan(want_s[0]) and np.isnan(s[0]) and np.isnan(err[0]) and np.isnan(score)
+            assert bid == -1  # a NaN score never wins (ransac.h:195 is a strict <)
+        else:
+            assert want_s[0] == 144.0 and s[0] == 144.0 and score == 144.0
+            assert np.isinf(err[0]) and err[0] > 0
+        sc.close()
