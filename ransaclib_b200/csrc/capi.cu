@@ -329,8 +329,10 @@ int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, con
   const int tiles = d.npad / rlb::kInlTile;
   int rc = ensure_first_use(c);
   if (rc) return rc;
-  if (static_cast<size_t>(tiles) * 8 > c->status.cap) {
-    RLB_CUDA(c->status.ensure(static_cast<size_t>(tiles) * 8));
+  // status words: one per tile + one per group of 256 tiles
+  const size_t status_words = static_cast<size_t>(tiles) + (tiles + 255) / 256;
+  if (status_words * 8 > c->status.cap) {
+    RLB_CUDA(c->status.ensure(status_words * 8));
     RLB_CUDA(cudaMemsetAsync(c->status.p, 0, c->status.cap, c->stream));
   }
   RLB_CUDA(c->tile_score.ensure(static_cast<size_t>(tiles) * sizeof(double)));
