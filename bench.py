@@ -150,7 +150,7 @@ def run_ours(args):
 
         dist.init_process_group("nccl", device_id=dev)
     wl = WORKLOADS[args.workload]
-    n, k_total = wl["n"], wl["k"]
+    n, k_total = wl["n"], (args.k_override or wl["k"])
     prec = rlb.RLB_F32 if args.precision == "f32" else rlb.RLB_F64
     id_lo, id_hi = sharding.hypothesis_range(k_total, rank, world)
     k = id_hi - id_lo
@@ -681,6 +681,7 @@ def main():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--no-localization", action="store_true",
                     help="c5: skip the batched-localization leg that is reported under 'localization'")
+    ap.add_argument("--k-override", type=int, default=0, help="tuning only: total number of hypotheses")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: skips the e2e leg, the CPU baseline and the peak microbenchmarks")
     args = ap.parse_args()

@@ -262,42 +262,75 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   a.models = d_models;
   a.valid = d_valid;
   fill_thr(d, thr, w, a.thr, a.w);
-  {
-    static const int variant = [] {
-      const char* v = getenv("RLB_SWEEP_VARIANT");
-      return v ? atoi(v) : -1;
-    }();
-    a.variant = variant;
-    if (variant < 0) {
-      // Auto: the widest register tile (8, 4 or 2 hypotheses per thread) that still yields at
-      // least two CTAs per SM together with the point-axis splits; wide tiles amortise the
-      // shared-memory reads and loop overhead (H=8: 1.90e12 evals/s vs 1.75e12 for H=4 on C5).
-      const int max_splits = std::min(d.npad / rlb::kStage, 64);
-      a.variant = 2;  // H = 2
-      if (((k + rlb::kSweepThreads * 4 - 1) / (rlb::kSweepThreads * 4)) * max_splits >= c->sms * 2) a.variant = 0;
-      if (((k + rlb::kSweepThreads * 8 - 1) / (rlb::kSweepThreads * 8)) * max_splits >= c->sms * 2) a.variant = 3;
-      // f64 pose sweep: 4 hypotheses per thread when there are enough tiles (6.4e11 vs 6.2e11 evals/s)
-      if (precision == RLB_F64 && d.kind == RLB_KIND_POSE)
-        a.variant = (((k + rlb::kSweepThreads * 4 - 1) / (rlb::kSweepThreads * 4)) * max_splits >= c->sms * 2) ? 7 : 2;
-    }
-  }
+  // Grid plan. Every CTA of a sweep does the same amount of work, so CTAs run in waves of
+  // (resident CTAs per SM) x (SMs); the plan picks the register tile H (hypotheses per thread) and
+  // the number of point-axis splits that fill whole waves: score = fill of the last wave x balance
+  // of the stages over the splits x relative speed of the tile. (K = 65,536 on one GPU: 62 instead
+  // of 64 splits; K = 8192 per GPU at 8 GPUs: 55 splits = 440 CTAs for 444 slots instead of 512.)
+  static const int forced_variant = [] {
+    const char* v = getenv("RLB_SWEEP_VARIANT");
+    return v ? atoi(v) : -1;
+  }();
+  static const int forced_splits = [] {
+    const char* v = getenv("RLB_SWEEP_SPLITS");
+    return v ? atoi(v) : 0;
+  }();
   a.record = c->pending_record;
   a.id_offset = c->pending_offset;
   c->pending_record = nullptr;
   c->pending_offset = 0;
-  const int H = rlb::sweep_hyps_per_thread(d.kind, precision, a.variant);
-  const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
   const int total_stages = d.npad / rlb::kStage;
-  // Aim for ~8 waves of 4 resident CTAs per SM so the tail wave is short; never split finer
-  // than one stage, never more than 64 ways (partials are [splits][k]).
-  static const int waves = [] {
-    const char* v = getenv("RLB_SWEEP_WAVES");
-    return v ? std::max(1, atoi(v)) : 8;
-  }();
-  const int target = c->sms * 4 * waves;
-  int splits = std::max(1, std::min({(target + k_tiles - 1) / k_tiles, total_stages, 64}));
-  const int sps = (total_stages + splits - 1) / splits;
-  splits = (total_stages + sps - 1) / sps;
+  struct Cand {
+    int variant;
+    double speed;
+  };
+  Cand cands[3];
+  int ncand = 0;
+  if (forced_variant >= 0) {
+    cands[ncand++] = {forced_variant, 1.0};
+  } else if (d.kind == RLB_KIND_POSE && precision == RLB_F32) {
+    cands[ncand++] = {3, 1.00};  // H = 8: 1.90e12 evals/s on C5
+    cands[ncand++] = {0, 0.92};  // H = 4
+    cands[ncand++] = {2, 0.80};  // H = 2
+  } else if (d.kind == RLB_KIND_POSE) {
+    cands[ncand++] = {7, 1.00};  // f64, H = 4
+    cands[ncand++] = {-1, 0.96};  // f64, H = 2
+  } else {
+    cands[ncand++] = {-1, 1.0};
+  }
+  double best_score = -1.0;
+  int splits = 1, sps = total_stages;
+  a.variant = cands[0].variant;
+  for (int ci = 0; ci < ncand; ++ci) {
+    const int H = rlb::sweep_hyps_per_thread(d.kind, precision, cands[ci].variant);
+    static std::map<int, int> occ_cache;  // (kind, precision, variant) -> resident CTAs per SM
+    const int occ_key = (d.kind * 4 + precision) * 64 + (cands[ci].variant + 1);
+    auto occ_it = occ_cache.find(occ_key);
+    if (occ_it == occ_cache.end())
+      occ_it = occ_cache.emplace(occ_key, rlb::sweep_resident_ctas(d.kind, precision, cands[ci].variant)).first;
+    const int slots = c->sms * occ_it->second;
+    const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
+    const int max_s = std::max(1, std::min(total_stages, 64));  // partials are [splits][k]
+    for (int s0 = 1; s0 <= max_s; ++s0) {
+      if (forced_splits > 0 && s0 != std::min(forced_splits, max_s)) continue;
+      const int sp = (total_stages + s0 - 1) / s0;
+      const int s_eff = (total_stages + sp - 1) / sp;
+      const long long ctas = static_cast<long long>(k_tiles) * s_eff;
+      const long long waves = (ctas + slots - 1) / slots;
+      const double fill = static_cast<double>(ctas) / static_cast<double>(waves * slots);
+      const double balance = static_cast<double>(total_stages) / (static_cast<double>(s_eff) * sp);
+      // lanes of the last hypothesis tile that carry no hypothesis
+      const double tile_use = static_cast<double>(k) / (static_cast<double>(k_tiles) * rlb::kSweepThreads * H);
+      // a few more, shorter CTAs are preferred on ties (shorter tail)
+      const double sc = fill * balance * tile_use * cands[ci].speed * (1.0 + 1e-4 * s_eff);
+      if (sc > best_score) {
+        best_score = sc;
+        a.variant = cands[ci].variant;
+        splits = s_eff;
+        sps = sp;
+      }
+    }
+  }
   a.n_splits = splits;
   a.stages_per_split = sps;
   RLB_CUDA(c->part_score.ensure(static_cast<size_t>(splits) * k * sizeof(double)));

@@ -83,6 +83,7 @@ struct InlierHeader {
 cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision, cudaStream_t st,
                          int* launches);
 int sweep_hyps_per_thread(int kind, int precision, int variant);
+int sweep_resident_ctas(int kind, int precision, int variant);
 cudaError_t launch_finalize(const DeviceData& d, const SweepArgs& a, double* scores,
                             int32_t* counts, BestRec* block_best, unsigned int* ticket,
                             BestRec* best, double* best_model, cudaStream_t st, int* launches);

@@ -576,6 +576,40 @@ int sweep_hyps_per_thread(int kind, int precision, int variant) {
   return 4;
 }
 
+// Resident CTAs per SM of the sweep kernel a (kind, precision, variant) triple selects
+// (registers / shared memory of that instantiation), for the grid planner in capi.cu.
+template <class K>
+static int occupancy_of(K kern, size_t smem) {
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kSweepThreads, smem) != cudaSuccess) n = 1;
+  return n > 0 ? n : 1;
+}
+int sweep_resident_ctas(int kind, int precision, int variant) {
+  const size_t s32 = static_cast<size_t>(kNumStages) * 5 * kStage * sizeof(float);
+  const size_t s64 = static_cast<size_t>(kNumStages) * 5 * kStage * sizeof(double);
+  const size_t l32 = static_cast<size_t>(kNumStages) * 2 * kStage * sizeof(float);
+  const size_t l64 = static_cast<size_t>(kNumStages) * 2 * kStage * sizeof(double);
+  if (kind == RLB_KIND_POSE) {
+    if (precision == RLB_F32) {
+      switch (variant) {
+        case 1: return occupancy_of(sweep_kernel<PoseF, float, 4>, s32);
+        case 2: return occupancy_of(sweep_pose_f32x2_kernel<2>, s32);
+        case 3: return occupancy_of(sweep_pose_f32x2_kernel<8>, s32);
+        case 4: return occupancy_of(sweep_pose_f32x2_kernel<6>, s32);
+        case 5: return occupancy_of(sweep_pose_f32x2_kernel<12>, s32);
+        case 6: return occupancy_of(sweep_pose_f32x2_kernel<10>, s32);
+        default: return occupancy_of(sweep_pose_f32x2_kernel<4>, s32);
+      }
+    }
+    if (variant == 7) return occupancy_of(sweep_kernel<PoseF, double, 4>, s64);
+    if (variant == 8) return occupancy_of(sweep_kernel<PoseF, double, 1>, s64);
+    return occupancy_of(sweep_kernel<PoseF, double, 2>, s64);
+  }
+  if (precision == RLB_F32) return occupancy_of(sweep_kernel<LineF, float, 4>, l32);
+  return occupancy_of(sweep_kernel<LineF, double, 4>, l64);
+}
+
 cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision, cudaStream_t st,
                          int* launches) {
   ++*launches;
