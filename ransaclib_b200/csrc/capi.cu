@@ -107,6 +107,7 @@ struct rlb_scorer {
   void* rays = nullptr;
   void* soa64 = nullptr;
   void* soa32 = nullptr;
+  void* tc_tiles = nullptr;  // tensor-core operand tiles of the points, packed on first use
 };
 
 namespace {
@@ -333,6 +334,36 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   }
   a.n_splits = splits;
   a.stages_per_split = sps;
+  // Tensor-core sweep (pose, f32 arithmetic class): the projection runs as tcgen05.mma on TF32x2-split
+  // operands. Its unit along the point axis is a 32-point tile.
+  const bool use_tc = (d.kind == RLB_KIND_POSE && precision == RLB_F32 && a.variant == 9);
+  if (use_tc) {
+    if (!s->tc_tiles) {
+      const int rc = pool_alloc(c, rlb::tc_tiles_bytes(d.npad), &s->tc_tiles);
+      if (rc) return rc;
+      RLB_CUDA(rlb::launch_tc_pack(d, static_cast<float*>(s->tc_tiles), c->stream, &c->launches_i));
+    }
+    const int total_tiles = d.npad / rlb::tc_tile_points();
+    const int slots = c->sms * rlb::tc_resident_ctas();
+    const int k_tiles = (k + rlb::tc_hyps_per_cta() - 1) / rlb::tc_hyps_per_cta();
+    double best = -1.0;
+    for (int s0 = 1; s0 <= std::min(total_tiles, 64); ++s0) {
+      if (forced_splits > 0 && s0 != std::min(forced_splits, std::min(total_tiles, 64))) continue;
+      const int tp = (total_tiles + s0 - 1) / s0;
+      const int s_eff = (total_tiles + tp - 1) / tp;
+      const long long ctas = static_cast<long long>(k_tiles) * s_eff;
+      const long long waves = (ctas + slots - 1) / slots;
+      const double fill = static_cast<double>(ctas) / static_cast<double>(waves * slots);
+      const double balance = static_cast<double>(total_tiles) / (static_cast<double>(s_eff) * tp);
+      const double sc = fill * balance * (1.0 + 1e-4 * s_eff);
+      if (sc > best) {
+        best = sc;
+        a.n_splits = s_eff;
+        a.stages_per_split = tp;
+      }
+    }
+    splits = a.n_splits;
+  }
   RLB_CUDA(c->part_score.ensure(static_cast<size_t>(splits) * k * sizeof(double)));
   RLB_CUDA(c->part_count.ensure(static_cast<size_t>(splits) * k * sizeof(int32_t)));
   a.part_score = c->part_score.as<double>();
@@ -341,7 +372,11 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   RLB_CUDA(c->block_best.ensure(static_cast<size_t>(fblocks) * sizeof(BestRec)));
 
   if (c->timing) RLB_CUDA(cudaEventRecord(c->ev[0], c->stream));
-  RLB_CUDA(rlb::launch_sweep(d, a, precision, c->stream, &c->launches_i));
+  if (use_tc) {
+    RLB_CUDA(rlb::launch_sweep_tc(d, a, static_cast<const float*>(s->tc_tiles), c->stream, &c->launches_i));
+  } else {
+    RLB_CUDA(rlb::launch_sweep(d, a, precision, c->stream, &c->launches_i));
+  }
   if (c->timing) {
     RLB_CUDA(cudaEventRecord(c->ev[1], c->stream));
     c->ev_valid[0] = true;
@@ -614,7 +649,7 @@ int rlb_scorer_destroy(rlb_scorer* s) {
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
   }
-  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32};
+  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32, s->tc_tiles};
   for (void* p : ptrs) {
     if (!p) continue;
     if (s->ctx) pool_release(s->ctx, p);

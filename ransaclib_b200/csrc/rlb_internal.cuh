@@ -97,6 +97,15 @@ cudaError_t launch_select_winner(const double* records, int world, int rec_doubl
                                  cudaStream_t st, int* launches);
 cudaError_t launch_fma_peak(int dtype, int sms, float* ms, double* flops, cudaStream_t st);
 
+// tensor-core sweep (sweep_tc_kernel.cu)
+cudaError_t launch_tc_pack(const DeviceData& d, float* tiles, cudaStream_t st, int* launches);
+cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
+                            int* launches);
+int tc_tile_points();
+size_t tc_tiles_bytes(int npad);
+int tc_hyps_per_cta();
+int tc_resident_ctas();
+
 // launchers (solver_kernels.cu, compiled with -fmad=false)
 cudaError_t launch_rays(const DeviceData& d, double* rays, cudaStream_t st, int* launches);
 cudaError_t launch_solve_line2pt(const DeviceData& d, int k, const int32_t* samples, double* models,

@@ -1,0 +1,353 @@
+// K x N pose MSAC sweep with the 3x4 projection on the 5th-generation tensor cores.
+//
+// Why: ncu on the FFMA2 sweep (profiles/r01f_ncu_sweep_h8.csv) shows the FMA pipe 78 % busy with
+// math-pipe throttle as the top stall, and 9 of the 14 FMA-pipe operations of an evaluation are the
+// projection p = R' X' + t' (BASELINE north_star: "tensor cores only if ncu shows the 3x4 projection
+// contraction to be FMA-issue-bound"). Here the projection of 128 hypotheses x 32 points is six
+// tcgen05.mma (kind::tf32, M = 128, N = 32, K = 8) into TMEM, and the CUDA cores keep the part
+// that is not a contraction: reciprocal, residual, MSAC test and the per-hypothesis sums.
+//
+// Precision: TF32 keeps 11 significant bits, so both operands are split, x = hi + lo with hi = x
+// with the low 13 mantissa bits cleared (exactly what the tensor core reads) and lo = x - hi (exact
+// in f32). K = 16 carries all four partial products,
+//     A row (hypothesis): [ rh0 rh1 rh2 th | rl0 rl1 rl2 tl | rh0 rh1 rh2 0 | rl0 rl1 rl2 0 ]
+//     B col (point)     : [ Xh  Yh  Zh  1  | Xh  Yh  Zh  1  | Xl  Yl  Zl  0 | Xl  Yl  Zl  0 ]
+// accumulated in f32 by the tensor core: the result differs from the f32 FMA chain by the second
+// truncation of the lo parts (<= 2^-22 relative per term), i.e. it is an f32-class projection.
+//
+// Operand layout: UMMA K-major, SWIZZLE_NONE canonical layout (core matrix = 8 rows x 16 bytes,
+// rows 16 B apart; SBO = byte distance between core matrices along M/N, LBO = along K). The points
+// are pre-packed in global memory in exactly the shared-memory image of a tile (32 points: 4 K-chunks
+// x 4 cores x 128 B = 2 KB, followed by 32 x (-u) and 32 x (-v)), so one 1-D bulk TMA copy per tile
+// brings everything in. The hypotheses of a CTA are written to shared memory once.
+#include <cfloat>
+
+#include "rlb_internal.cuh"
+
+namespace rlb {
+
+namespace {
+
+constexpr int kTcThreads = 128;            // 4 warps = the 128 TMEM lanes = 128 hypotheses
+constexpr int kTcTile = 32;                // points per MMA tile (N)
+constexpr int kTcTileFloats = 512 + 64;    // 16 x 32 operand floats + 32 x (-u) + 32 x (-v)
+constexpr int kTcTileBytes = kTcTileFloats * 4;
+constexpr int kTcRing = 8;                 // TMA ring depth (tiles)
+constexpr int kTcCols = 128;               // TMEM columns: px [0,32) py [32,64) pz [64,96)
+constexpr int kTcFlush = 16;               // tiles (512 points) per f32 -> f64 flush
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// Bounded wait: a protocol error must fault, not hang the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  uint32_t done = 0;
+  for (long long spins = 0; !done; ++spins) {
+    asm volatile(
+        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+        : "=r"(done)
+        : "r"(a), "r"(parity)
+        : "memory");
+    if (spins > 200000000LL) __trap();
+  }
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_NONE, sm_100 (version 1).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3ffffu) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fffu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= 1ull << 46;  // descriptor version for Blackwell
+  return d;         // base offset 0, LBO mode 0, layout type SWIZZLE_NONE
+}
+
+// Instruction descriptor: D = f32, A = B = tf32, both K-major, M = 128, N = 32, dense.
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((kTcTile >> 3) << 17) | ((128u >> 4) << 24);
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+
+}  // namespace
+
+// ---------------------------------------------------------------- point pre-pack
+// tiles: [npad / 32][kTcTileFloats]; inputs are the recentred f32 stage values (the same numbers the
+// FFMA2 sweep reads), padding = X 0, -u/-v NaN.
+__global__ void tc_pack_kernel(const DeviceData d, float* __restrict__ tiles) {
+  const int total = d.npad;
+  for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
+    const float x = d.soa32[0 * static_cast<size_t>(total) + g];
+    const float y = d.soa32[1 * static_cast<size_t>(total) + g];
+    const float z = d.soa32[2 * static_cast<size_t>(total) + g];
+    const float nu = d.soa32[3 * static_cast<size_t>(total) + g];
+    const float nv = d.soa32[4 * static_cast<size_t>(total) + g];
+    const float xh = tf32_hi(x), yh = tf32_hi(y), zh = tf32_hi(z);
+    const float xl = x - xh, yl = y - yh, zl = z - zh;
+    float* t = tiles + static_cast<size_t>(g / kTcTile) * kTcTileFloats;
+    const int n = g % kTcTile;
+    const int core = n >> 3, row = n & 7;
+    const float ch[4][4] = {{xh, yh, zh, 1.0f}, {xh, yh, zh, 1.0f}, {xl, yl, zl, 0.0f}, {xl, yl, zl, 0.0f}};
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float4* dst = reinterpret_cast<float4*>(t + ((c * 4 + core) * 8 + row) * 4);
+      *dst = make_float4(ch[c][0], ch[c][1], ch[c][2], ch[c][3]);
+    }
+    t[512 + n] = nu;
+    t[512 + 32 + n] = nv;
+  }
+}
+
+cudaError_t launch_tc_pack(const DeviceData& d, float* tiles, cudaStream_t st, int* launches) {
+  ++*launches;
+  const int blocks = max(1, min(2048, (d.npad + 255) / 256));
+  tc_pack_kernel<<<blocks, 256, 0, st>>>(d, tiles);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ sweep kernel
+struct TcSmem {
+  float a[3][2048];                       // hypotheses: px / py / pz operand matrices (8 KB each)
+  float ring[kTcRing][kTcTileFloats];     // point tiles
+  uint64_t full[kTcRing];                 // TMA -> MMA
+  uint64_t mma_done;                      // MMA -> epilogue
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kTcThreads, 4)
+    sweep_pose_tc_kernel(const DeviceData d, const SweepArgs a, const float* __restrict__ tiles) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  TcSmem& S = *reinterpret_cast<TcSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int k = blockIdx.x * kTcThreads + tid;
+  const int split = blockIdx.y;
+  const int n_live = d.n[0];
+
+  const int total_tiles = d.npad / kTcTile;
+  const int t_begin = split * a.stages_per_split;  // here: tiles per split
+  const int t_end = min(total_tiles, t_begin + a.stages_per_split);
+  const int ntiles = max(0, t_end - t_begin);
+
+  // ---- one-time setup -----------------------------------------------------------------
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)),
+                 "r"(static_cast<uint32_t>(kTcCols))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 32) {
+#pragma unroll
+    for (int s = 0; s < kTcRing; ++s) mbar_init(&S.full[s], 1);
+    mbar_init(&S.mma_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  {
+    // this thread's hypothesis -> one row of each operand matrix (PoseF<float>::load arithmetic)
+    float r[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float t[3] = {0.f, 0.f, 1.f};
+    if (k < a.k) {
+      const double* m = a.models + static_cast<size_t>(k) * 12;
+      const double dc[3] = {d.centre[0] - m[9], d.centre[1] - m[10], d.centre[2] - m[11]};
+      const double sc[3] = {d.fx, d.fy, 1.0};
+#pragma unroll
+      for (int row = 0; row < 3; ++row) {
+        const double r0 = m[row], r1 = m[row + 3], r2 = m[row + 6];
+        r[3 * row + 0] = static_cast<float>(r0 * sc[row]);
+        r[3 * row + 1] = static_cast<float>(r1 * sc[row]);
+        r[3 * row + 2] = static_cast<float>(r2 * sc[row]);
+        t[row] = static_cast<float>((r0 * dc[0] + r1 * dc[1] + r2 * dc[2]) * sc[row]);
+      }
+    }
+    const int core = tid >> 3, row8 = tid & 7;
+#pragma unroll
+    for (int mat = 0; mat < 3; ++mat) {
+      const float v[4] = {r[3 * mat], r[3 * mat + 1], r[3 * mat + 2], t[mat]};
+      float h[4], l[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        h[j] = tf32_hi(v[j]);
+        l[j] = v[j] - h[j];
+      }
+      float* A = S.a[mat];
+      *reinterpret_cast<float4*>(A + ((0 * 16 + core) * 8 + row8) * 4) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(A + ((1 * 16 + core) * 8 + row8) * 4) = make_float4(l[0], l[1], l[2], l[3]);
+      *reinterpret_cast<float4*>(A + ((2 * 16 + core) * 8 + row8) * 4) = make_float4(h[0], h[1], h[2], 0.f);
+      *reinterpret_cast<float4*>(A + ((3 * 16 + core) * 8 + row8) * 4) = make_float4(l[0], l[1], l[2], 0.f);
+    }
+  }
+  // generic-proxy writes (operand matrices) must be visible to the tensor core (async proxy)
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = S.tmem_base;
+
+  auto issue_tma = [&](int it) {
+    const int slot = it % kTcRing;
+    mbar_expect_tx(&S.full[slot], kTcTileBytes);
+    tma_load_1d(S.ring[slot], tiles + static_cast<size_t>(t_begin + it) * kTcTileFloats, kTcTileBytes,
+                &S.full[slot]);
+  };
+  if (tid == 0) {
+    for (int it = 0; it < kTcRing && it < ntiles; ++it) issue_tma(it);
+  }
+
+  const double thr64 = a.thr[0];
+  const float thr = static_cast<float>(thr64);
+  const double w = a.w[0];
+  double dacc = 0.0;
+  int dcnt = 0;
+  float s = 0.0f;
+  int c = 0;
+  int live_in_chunk = 0;
+
+  for (int it = 0; it < ntiles; ++it) {
+    const int slot = it % kTcRing;
+    if (tid == 0) {
+      mbar_wait(&S.full[slot], (it / kTcRing) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t b_addr = smem_u32(S.ring[slot]);
+#pragma unroll
+      for (int mat = 0; mat < 3; ++mat) {
+        const uint32_t a_addr = smem_u32(S.a[mat]);
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          // one MMA covers K = 8 = two 16-byte chunks; chunks are LBO apart
+          const uint64_t da = umma_desc(a_addr + kk * 2 * 2048, 2048, 128);
+          const uint64_t db = umma_desc(b_addr + kk * 2 * 512, 512, 128);
+          umma_tf32(tmem + mat * kTcTile, da, db, kk);
+        }
+      }
+      umma_commit(&S.mma_done);
+    }
+    mbar_wait(&S.mma_done, it & 1);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+    const float* nu = S.ring[slot] + 512;
+    const float* nv = nu + 32;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      float px[16], py[16], pz[16];
+      tmem_ld16(lane_addr + 0 * kTcTile + 16 * half, px);
+      tmem_ld16(lane_addr + 1 * kTcTile + 16 * half, py);
+      tmem_ld16(lane_addr + 2 * kTcTile + 16 * half, pz);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 u4 = *reinterpret_cast<const float4*>(nu + 16 * half + 4 * q);
+        const float4 v4 = *reinterpret_cast<const float4*>(nv + 16 * half + 4 * q);
+        const float us[4] = {u4.x, u4.y, u4.z, u4.w}, vs[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+        for (int e4 = 0; e4 < 4; ++e4) {
+          const int j = 4 * q + e4;
+          float inv;
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(fmaxf(pz[j], 0.0f)));
+          const float du = fmaf(px[j], inv, us[e4]);
+          const float dv = fmaf(py[j], inv, vs[e4]);
+          const float e = fmaf(du, du, dv * dv);
+          if (e < thr) {
+            s += e;
+            c += 1;
+          }
+        }
+      }
+    }
+    live_in_chunk += max(0, min(kTcTile, n_live - (t_begin + it) * kTcTile));
+    if (((it + 1) % kTcFlush) == 0 || it + 1 == ntiles) {
+      dacc += w * (static_cast<double>(s) + thr64 * static_cast<double>(live_in_chunk - c));
+      dcnt += c;
+      s = 0.0f;
+      c = 0;
+      live_in_chunk = 0;
+    }
+    // everyone is done with TMEM and with this ring slot
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (tid == 0 && it + kTcRing < ntiles) issue_tma(it + kTcRing);
+  }
+
+  if (k < a.k) {
+    a.part_score[static_cast<size_t>(split) * a.k + k] = dacc;
+    a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
+                 "r"(static_cast<uint32_t>(kTcCols))
+                 : "memory");
+  }
+}
+
+int tc_tile_points() { return kTcTile; }
+size_t tc_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * kTcTileBytes; }
+int tc_hyps_per_cta() { return kTcThreads; }
+
+int tc_resident_ctas() {
+  static int cached = 0;
+  if (cached) return cached;
+  cudaFuncSetAttribute(sweep_pose_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(sizeof(TcSmem)));
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel, kTcThreads, sizeof(TcSmem)) !=
+      cudaSuccess)
+    n = 1;
+  cached = max(1, min(n, 512 / kTcCols));  // TMEM: 512 columns per SM
+  return cached;
+}
+
+cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
+                            int* launches) {
+  ++*launches;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(sizeof(TcSmem)));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid((a.k + kTcThreads - 1) / kTcThreads, a.n_splits);
+  sweep_pose_tc_kernel<<<grid, kTcThreads, sizeof(TcSmem), st>>>(d, a, tiles);
+  return cudaGetLastError();
+}
+
+}  // namespace rlb
