@@ -105,6 +105,37 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
+  u64 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float rsq_approx(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// MSAC accumulation of one evaluation: s += e and c += 1 when e < thr (one FSETP + two predicated adds).
+__device__ __forceinline__ void msac_add(float e, float thr, float& s, int& c) {
+  asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %2, %3;\n\t@p add.f32 %0, %0, %2;\n\t@p add.s32 %1, %1, 1;\n\t}"
+      : "+f"(s), "+r"(c)
+      : "f"(e), "f"(thr));
+}
+
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
 
 }  // namespace
@@ -272,23 +303,25 @@ __global__ void __launch_bounds__(kTcThreads, 4)
       tmem_ld16(lane_addr + 1 * kTcTile + 16 * half, py);
       tmem_ld16(lane_addr + 2 * kTcTile + 16 * half, pz);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      // Two points per instruction (packed f32x2): TMEM columns j, j+1 land in adjacent registers.
+      // 1 / pz = rsqrt(pz)^2: one MUFU, NaN for pz < 0 and +inf for pz == 0, so points behind the
+      // camera fail (e < thr) without a clamp; 2 ulp of rsqrt squared stay inside the f32 class.
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const float4 u4 = *reinterpret_cast<const float4*>(nu + 16 * half + 4 * q);
-        const float4 v4 = *reinterpret_cast<const float4*>(nv + 16 * half + 4 * q);
-        const float us[4] = {u4.x, u4.y, u4.z, u4.w}, vs[4] = {v4.x, v4.y, v4.z, v4.w};
+        const ulonglong2 u4 = *reinterpret_cast<const ulonglong2*>(nu + 16 * half + 4 * q);
+        const ulonglong2 v4 = *reinterpret_cast<const ulonglong2*>(nv + 16 * half + 4 * q);
 #pragma unroll
-        for (int e4 = 0; e4 < 4; ++e4) {
-          const int j = 4 * q + e4;
-          float inv;
-          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(fmaxf(pz[j], 0.0f)));
-          const float du = fmaf(px[j], inv, us[e4]);
-          const float dv = fmaf(py[j], inv, vs[e4]);
-          const float e = fmaf(du, du, dv * dv);
-          if (e < thr) {
-            s += e;
-            c += 1;
-          }
+        for (int pr = 0; pr < 2; ++pr) {
+          const int j = 4 * q + 2 * pr;
+          const u64 rs = pack2(rsq_approx(pz[j]), rsq_approx(pz[j + 1]));
+          const u64 inv = fmul2(rs, rs);
+          const u64 du = ffma2(pack2(px[j], px[j + 1]), inv, pr ? u4.y : u4.x);
+          const u64 dv = ffma2(pack2(py[j], py[j + 1]), inv, pr ? v4.y : v4.x);
+          const u64 e2 = ffma2(du, du, fmul2(dv, dv));
+          float ea, eb;
+          unpack2(e2, ea, eb);
+          msac_add(ea, thr, s, c);
+          msac_add(eb, thr, s, c);
         }
       }
     }
