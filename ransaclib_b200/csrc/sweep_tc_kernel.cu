@@ -89,6 +89,25 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
       "l"(desc_a), "l"(desc_b), "r"(kIdesc), "r"(accumulate)
       : "memory");
 }
+// A operand from TMEM (lane = hypothesis, 8 consecutive 32-bit columns = K), B from shared memory.
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float* v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+               "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+               "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+               "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7]))
+               : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
@@ -176,7 +195,6 @@ cudaError_t launch_tc_pack(const DeviceData& d, float* tiles, cudaStream_t st, i
 
 // ------------------------------------------------------------------ sweep kernel
 struct TcSmem {
-  float a[3][2048];                       // hypotheses: px / py / pz operand matrices (8 KB each)
   float ring[kTcRing][kTcTileFloats];     // point tiles
   uint64_t full[kTcRing];                 // TMA -> MMA
   uint64_t mma_done;                      // MMA -> epilogue
@@ -211,8 +229,16 @@ __global__ void __launch_bounds__(kTcThreads, 4)
     mbar_init(&S.mma_done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  // TMEM base address must be visible before anyone uses it
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = S.tmem_base;
+  const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
   {
-    // this thread's hypothesis -> one row of each operand matrix (PoseF<float>::load arithmetic)
+    // this thread's hypothesis -> its TMEM lane of each operand matrix (PoseF<float>::load arithmetic).
+    // Columns [8 mat, 8 mat + 8) = [rh0 rh1 rh2 th | rl0 rl1 rl2 tl]; the same eight columns serve both
+    // K steps: the second multiplies the points' lo parts, whose fourth component is 0.
     float r[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float t[3] = {0.f, 0.f, 1.f};
     if (k < a.k) {
@@ -228,29 +254,23 @@ __global__ void __launch_bounds__(kTcThreads, 4)
         t[row] = static_cast<float>((r0 * dc[0] + r1 * dc[1] + r2 * dc[2]) * sc[row]);
       }
     }
-    const int core = tid >> 3, row8 = tid & 7;
 #pragma unroll
     for (int mat = 0; mat < 3; ++mat) {
       const float v[4] = {r[3 * mat], r[3 * mat + 1], r[3 * mat + 2], t[mat]};
-      float h[4], l[4];
+      float hl[8];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        h[j] = tf32_hi(v[j]);
-        l[j] = v[j] - h[j];
+        hl[j] = tf32_hi(v[j]);
+        hl[4 + j] = v[j] - hl[j];
       }
-      float* A = S.a[mat];
-      *reinterpret_cast<float4*>(A + ((0 * 16 + core) * 8 + row8) * 4) = make_float4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<float4*>(A + ((1 * 16 + core) * 8 + row8) * 4) = make_float4(l[0], l[1], l[2], l[3]);
-      *reinterpret_cast<float4*>(A + ((2 * 16 + core) * 8 + row8) * 4) = make_float4(h[0], h[1], h[2], 0.f);
-      *reinterpret_cast<float4*>(A + ((3 * 16 + core) * 8 + row8) * 4) = make_float4(l[0], l[1], l[2], 0.f);
+      tmem_st8(lane_addr + 8 * mat, hl);
     }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
-  // generic-proxy writes (operand matrices) must be visible to the tensor core (async proxy)
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem = S.tmem_base;
+
 
   auto issue_tma = [&](int it) {
     const int slot = it % kTcRing;
@@ -278,30 +298,25 @@ __global__ void __launch_bounds__(kTcThreads, 4)
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t b_addr = smem_u32(S.ring[slot]);
 #pragma unroll
-      for (int mat = 0; mat < 3; ++mat) {
-        const uint32_t a_addr = smem_u32(S.a[mat]);
+      for (int kk = 0; kk < 2; ++kk) {
+        // one MMA covers K = 8 = two 16-byte chunks of the points (hi parts, then lo parts), LBO apart
+        const uint64_t db = umma_desc(b_addr + kk * 2 * 512, 512, 128);
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk) {
-          // one MMA covers K = 8 = two 16-byte chunks; chunks are LBO apart
-          const uint64_t da = umma_desc(a_addr + kk * 2 * 2048, 2048, 128);
-          const uint64_t db = umma_desc(b_addr + kk * 2 * 512, 512, 128);
-          umma_tf32(tmem + mat * kTcTile, da, db, kk);
-        }
+        for (int mat = 0; mat < 3; ++mat) umma_tf32_ts(tmem + 32 + mat * kTcTile, tmem + 8 * mat, db, kk);
       }
       umma_commit(&S.mma_done);
     }
     mbar_wait(&S.mma_done, it & 1);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
-    const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
     const float* nu = S.ring[slot] + 512;
     const float* nv = nu + 32;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       float px[16], py[16], pz[16];
-      tmem_ld16(lane_addr + 0 * kTcTile + 16 * half, px);
-      tmem_ld16(lane_addr + 1 * kTcTile + 16 * half, py);
-      tmem_ld16(lane_addr + 2 * kTcTile + 16 * half, pz);
+      tmem_ld16(lane_addr + 32 + 0 * kTcTile + 16 * half, px);
+      tmem_ld16(lane_addr + 32 + 1 * kTcTile + 16 * half, py);
+      tmem_ld16(lane_addr + 32 + 2 * kTcTile + 16 * half, pz);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       // Two points per instruction (packed f32x2): TMEM columns j, j+1 land in adjacent registers.
       // 1 / pz = rsqrt(pz)^2: one MUFU, NaN for pz < 0 and +inf for pz == 0, so points behind the
