@@ -183,7 +183,8 @@ def run_ours(args):
     def step():
         # solve + sweep + argmin; the shard's (score, global id, model) record lands in d_rec
         scorer.sharded_round_dev(d_samples.data_ptr(), k, THR, None, id_lo, d_models.data_ptr(),
-                                 d_valid.data_ptr(), d_scores.data_ptr(), d_counts.data_ptr(),
+                                 d_valid.data_ptr(), d_scores.data_ptr(),
+                                 d_counts.data_ptr() if args.counts else 0,
                                  d_rec.data_ptr(), precision=prec)
         if world > 1:
             dist.all_gather_into_tensor(d_gather, d_rec)  # the single collective of the round
@@ -335,6 +336,7 @@ def run_ours(args):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32" if prec == rlb.RLB_F32 else "f64", "data": "synthetic",
         "config": {"workload": wl["name"], "n_points": n, "k_hypotheses": k_total, "k_per_gpu": k,
+                   "per_hypothesis_counts": bool(args.counts),
                    "sq_thr": THR, "partitioning": "hypothesis-sharded, points replicated, 1 all_gather/step"
                    if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
                    "step": "P3P solve + KxN MSAC sweep + argmin + ordered inlier list of the winner"},
@@ -681,6 +683,9 @@ def main():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--no-localization", action="store_true",
                     help="c5: skip the batched-localization leg that is reported under 'localization'")
+    ap.add_argument("--counts", action="store_true",
+                    help="also return an inlier count for every hypothesis (ScoreModel in ransac.h returns "
+                         "only the score; the winner's inliers come from the GetInliers pass either way)")
     ap.add_argument("--k-override", type=int, default=0, help="tuning only: total number of hypotheses")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: skips the e2e leg, the CPU baseline and the peak microbenchmarks")

@@ -182,15 +182,16 @@ class Scorer:
         _capi.check(self._lib.rlb_scorer_get_rays(self._h, _capi.ptr(out)))
         return out
 
-    def score_models(self, models, sq_thr, weights=None, valid=None, precision=RLB_F64):
-        """-> (scores[K], counts[K], best_id, best_score)."""
+    def score_models(self, models, sq_thr, weights=None, valid=None, precision=RLB_F64, want_counts=True):
+        """-> (scores[K], counts[K] or None, best_id, best_score). want_counts=False passes a NULL counts
+        array, i.e. asks for what ScoreModel (ransac.h) computes; the sweep then skips the counting."""
         models = _capi.f64a(models, (-1, self.model_size))
         k = len(models)
         thr = self._thr(sq_thr)
         w = None if weights is None else self._thr(weights)
         v = None if valid is None else np.ascontiguousarray(valid, dtype=np.uint8)
         scores = np.empty(k)
-        counts = np.empty(k, np.int32)
+        counts = np.empty(k, np.int32) if want_counts else None
         bid = C.c_int32()
         bsc = C.c_double()
         _capi.check(self._lib.rlb_score_models(self._h, precision, k, _capi.ptr(models), _capi.ptr(v),

@@ -278,6 +278,7 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   }();
   a.record = c->pending_record;
   a.id_offset = c->pending_offset;
+  a.want_counts = (d_counts != nullptr) ? 1 : 0;
   c->pending_record = nullptr;
   c->pending_offset = 0;
   const int total_stages = d.npad / rlb::kStage;
@@ -719,7 +720,7 @@ int rlb_score_models(rlb_scorer* s, int precision, int k, const double* models,
   }
   BestRec* d_best = reinterpret_cast<BestRec*>(c->small.as<char>() + kSmallBest);
   rc = score_dev(s, precision, k, c->models.as<double>(), d_valid, sq_thr, weights,
-                 c->scores.as<double>(), c->counts.as<int32_t>(), d_best, nullptr);
+                 c->scores.as<double>(), counts ? c->counts.as<int32_t>() : nullptr, d_best, nullptr);
   if (rc) return rc;
   if (scores)
     RLB_CUDA(cudaMemcpyAsync(scores, c->scores.p, static_cast<size_t>(k) * sizeof(double),
@@ -952,7 +953,7 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
   BestRec* d_best = reinterpret_cast<BestRec*>(c->small.as<char>() + kSmallBest);
   double* d_best_model = reinterpret_cast<double*>(c->small.as<char>() + kSmallBestModel);
   rc = score_dev(s, precision, k, c->models.as<double>(), c->valid.as<uint8_t>(), sq_thr, weights,
-                 c->scores.as<double>(), c->counts.as<int32_t>(), d_best, d_best_model);
+                 c->scores.as<double>(), counts ? c->counts.as<int32_t>() : nullptr, d_best, d_best_model);
   if (rc) return rc;
   if (models)
     RLB_CUDA(cudaMemcpyAsync(models, c->models.p, static_cast<size_t>(k) * md * sizeof(double),

@@ -51,6 +51,7 @@ struct SweepArgs {
   int variant;                 // 0 = default kernels, 1 = scalar-FFMA sweep (A/B timing)
   double* record;              // optional {score, global id (as f64), model...} of the local winner
   long long id_offset;         // first global hypothesis id of this shard
+  int want_counts;             // 0: the caller passed no counts array, part_count may be left unwritten
 };
 
 struct BestRec {

@@ -652,7 +652,7 @@ __global__ void __launch_bounds__(256)
     int cnt = 0;
     for (int sp = 0; sp < a.n_splits; ++sp) {  // fixed order: deterministic
       sum += a.part_score[static_cast<size_t>(sp) * a.k + k];
-      cnt += a.part_count[static_cast<size_t>(sp) * a.k + k];
+      if (counts) cnt += a.part_count[static_cast<size_t>(sp) * a.k + k];
     }
     const bool is_valid = (a.valid == nullptr) || (a.valid[k] != 0);
     bool finite = true;

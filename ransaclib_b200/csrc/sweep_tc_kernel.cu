@@ -108,6 +108,14 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const float* v) {
                "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7]))
                : "memory");
 }
+// One lane of a converged warp. tcgen05.mma / commit issued under elect.sync compile to a single UTCHMMA;
+// under `if (tid == 0)` ptxas wraps every MMA in a per-lane serialisation loop (~109 cycles per MMA
+// measured with tools/probes/umma_probe.cu against ~40 for the elected form).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{ .reg .pred p; elect.sync _|p, 0xffffffff; selp.u32 %0, 1, 0, p; }" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
@@ -124,6 +132,25 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+// tcgen05.wait::ld with the loaded registers as in/out operands: nothing that reads them can be
+// scheduled above the wait.
+__device__ __forceinline__ void tmem_wait_ld8x3(float* a, float* b, float* c) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7]),
+                 "+f"(b[0]), "+f"(b[1]), "+f"(b[2]), "+f"(b[3]), "+f"(b[4]), "+f"(b[5]), "+f"(b[6]), "+f"(b[7]),
+                 "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]), "+f"(c[4]), "+f"(c[5]), "+f"(c[6]), "+f"(c[7])
+               :
+               : "memory");
+}
+
 typedef unsigned long long u64;
 __device__ __forceinline__ u64 pack2(float lo, float hi) {
   u64 r;
@@ -136,6 +163,11 @@ __device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
 __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
   u64 d;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b) {
+  u64 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
 __device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
@@ -201,6 +233,9 @@ struct TcSmem {
   uint32_t tmem_base;
 };
 
+// COUNT = false (the caller did not ask for per-hypothesis inlier counts, as ScoreModel in ransac.h
+// never does): the score is accumulated as sum min(e, thr), two instructions fewer per evaluation.
+template <bool COUNT>
 __global__ void __launch_bounds__(kTcThreads, 4)
     sweep_pose_tc_kernel(const DeviceData d, const SweepArgs a, const float* __restrict__ tiles) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -289,61 +324,88 @@ __global__ void __launch_bounds__(kTcThreads, 4)
   int dcnt = 0;
   float s = 0.0f;
   int c = 0;
+  u64 s2 = 0ull;  // COUNT = false: two running sums of min(e, thr)
   int live_in_chunk = 0;
 
   for (int it = 0; it < ntiles; ++it) {
     const int slot = it % kTcRing;
-    if (tid == 0) {
+    if (warp == 0) {
       mbar_wait(&S.full[slot], (it / kTcRing) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t b_addr = smem_u32(S.ring[slot]);
+      if (elect_one()) {
+        const uint32_t b_addr = smem_u32(S.ring[slot]);
 #pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
-        // one MMA covers K = 8 = two 16-byte chunks of the points (hi parts, then lo parts), LBO apart
-        const uint64_t db = umma_desc(b_addr + kk * 2 * 512, 512, 128);
+        for (int kk = 0; kk < 2; ++kk) {
+          // one MMA covers K = 8 = two 16-byte chunks of the points (hi parts, then lo parts), LBO apart
+          const uint64_t db = umma_desc(b_addr + kk * 2 * 512, 512, 128);
 #pragma unroll
-        for (int mat = 0; mat < 3; ++mat) umma_tf32_ts(tmem + 32 + mat * kTcTile, tmem + 8 * mat, db, kk);
+          for (int mat = 0; mat < 3; ++mat) umma_tf32_ts(tmem + 32 + mat * kTcTile, tmem + 8 * mat, db, kk);
+        }
+        umma_commit(&S.mma_done);
       }
-      umma_commit(&S.mma_done);
+      __syncwarp();
     }
     mbar_wait(&S.mma_done, it & 1);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
     const float* nu = S.ring[slot] + 512;
     const float* nv = nu + 32;
+    // Quarter-tiles of 8 points: the TMEM loads of the next quarter are in flight while this one is
+    // reduced (tcgen05.ld latency is ~110 cycles; a tile-wide load-then-wait exposed it twice per tile).
+    float px[2][8], py[2][8], pz[2][8];
+    tmem_ld8(lane_addr + 32 + 0 * kTcTile, px[0]);
+    tmem_ld8(lane_addr + 32 + 1 * kTcTile, py[0]);
+    tmem_ld8(lane_addr + 32 + 2 * kTcTile, pz[0]);
+    tmem_wait_ld8x3(px[0], py[0], pz[0]);
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      float px[16], py[16], pz[16];
-      tmem_ld16(lane_addr + 32 + 0 * kTcTile + 16 * half, px);
-      tmem_ld16(lane_addr + 32 + 1 * kTcTile + 16 * half, py);
-      tmem_ld16(lane_addr + 32 + 2 * kTcTile + 16 * half, pz);
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    for (int qd = 0; qd < 4; ++qd) {
+      const int cur = qd & 1, nxt = cur ^ 1;
+      if (qd < 3) {
+        tmem_ld8(lane_addr + 32 + 0 * kTcTile + 8 * (qd + 1), px[nxt]);
+        tmem_ld8(lane_addr + 32 + 1 * kTcTile + 8 * (qd + 1), py[nxt]);
+        tmem_ld8(lane_addr + 32 + 2 * kTcTile + 8 * (qd + 1), pz[nxt]);
+      }
       // Two points per instruction (packed f32x2): TMEM columns j, j+1 land in adjacent registers.
       // 1 / pz = rsqrt(pz)^2: one MUFU, NaN for pz < 0 and +inf for pz == 0, so points behind the
       // camera fail (e < thr) without a clamp; 2 ulp of rsqrt squared stay inside the f32 class.
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const ulonglong2 u4 = *reinterpret_cast<const ulonglong2*>(nu + 16 * half + 4 * q);
-        const ulonglong2 v4 = *reinterpret_cast<const ulonglong2*>(nv + 16 * half + 4 * q);
+      for (int q = 0; q < 2; ++q) {
+        const ulonglong2 u4 = *reinterpret_cast<const ulonglong2*>(nu + 8 * qd + 4 * q);
+        const ulonglong2 v4 = *reinterpret_cast<const ulonglong2*>(nv + 8 * qd + 4 * q);
 #pragma unroll
         for (int pr = 0; pr < 2; ++pr) {
           const int j = 4 * q + 2 * pr;
-          const u64 rs = pack2(rsq_approx(pz[j]), rsq_approx(pz[j + 1]));
+          const u64 rs = pack2(rsq_approx(pz[cur][j]), rsq_approx(pz[cur][j + 1]));
           const u64 inv = fmul2(rs, rs);
-          const u64 du = ffma2(pack2(px[j], px[j + 1]), inv, pr ? u4.y : u4.x);
-          const u64 dv = ffma2(pack2(py[j], py[j + 1]), inv, pr ? v4.y : v4.x);
+          const u64 du = ffma2(pack2(px[cur][j], px[cur][j + 1]), inv, pr ? u4.y : u4.x);
+          const u64 dv = ffma2(pack2(py[cur][j], py[cur][j + 1]), inv, pr ? v4.y : v4.x);
           const u64 e2 = ffma2(du, du, fmul2(dv, dv));
           float ea, eb;
           unpack2(e2, ea, eb);
-          msac_add(ea, thr, s, c);
-          msac_add(eb, thr, s, c);
+          if (COUNT) {
+            msac_add(ea, thr, s, c);
+            msac_add(eb, thr, s, c);
+          } else {
+            s2 = fadd2(s2, pack2(fminf(ea, thr), fminf(eb, thr)));  // NaN / inf -> thr
+          }
         }
       }
+      if (qd < 3) tmem_wait_ld8x3(px[nxt], py[nxt], pz[nxt]);
     }
     live_in_chunk += max(0, min(kTcTile, n_live - (t_begin + it) * kTcTile));
     if (((it + 1) % kTcFlush) == 0 || it + 1 == ntiles) {
-      dacc += w * (static_cast<double>(s) + thr64 * static_cast<double>(live_in_chunk - c));
-      dcnt += c;
+      if (COUNT) {
+        dacc += w * (static_cast<double>(s) + thr64 * static_cast<double>(live_in_chunk - c));
+        dcnt += c;
+      } else {
+        // every processed point added min(e, thr); padding (NaN residual) added thr and is taken out again
+        float sa, sb;
+        unpack2(s2, sa, sb);
+        const int processed = (it % kTcFlush + 1) * kTcTile;
+        dacc += w * (static_cast<double>(sa) + static_cast<double>(sb) -
+                     static_cast<double>(thr) * static_cast<double>(processed - live_in_chunk));
+        s2 = 0ull;
+      }
       s = 0.0f;
       c = 0;
       live_in_chunk = 0;
@@ -351,12 +413,15 @@ __global__ void __launch_bounds__(kTcThreads, 4)
     // everyone is done with TMEM and with this ring slot
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (tid == 0 && it + kTcRing < ntiles) issue_tma(it + kTcRing);
+    if (warp == 0 && it + kTcRing < ntiles) {
+      if (elect_one()) issue_tma(it + kTcRing);
+      __syncwarp();
+    }
   }
 
   if (k < a.k) {
     a.part_score[static_cast<size_t>(split) * a.k + k] = dacc;
-    a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt;
+    if (COUNT) a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt;
   }
   __syncthreads();
   if (warp == 0) {
@@ -373,10 +438,10 @@ int tc_hyps_per_cta() { return kTcThreads; }
 int tc_resident_ctas() {
   static int cached = 0;
   if (cached) return cached;
-  cudaFuncSetAttribute(sweep_pose_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaFuncSetAttribute(sweep_pose_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(TcSmem)));
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel, kTcThreads, sizeof(TcSmem)) !=
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel<true>, kTcThreads, sizeof(TcSmem)) !=
       cudaSuccess)
     n = 1;
   cached = max(1, min(n, 512 / kTcCols));  // TMEM: 512 columns per SM
@@ -388,13 +453,19 @@ cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float
   ++*launches;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(sizeof(TcSmem)));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(sweep_pose_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(sizeof(TcSmem)));
     if (e != cudaSuccess) return e;
     configured = true;
   }
   dim3 grid((a.k + kTcThreads - 1) / kTcThreads, a.n_splits);
-  sweep_pose_tc_kernel<<<grid, kTcThreads, sizeof(TcSmem), st>>>(d, a, tiles);
+  if (a.want_counts)
+    sweep_pose_tc_kernel<true><<<grid, kTcThreads, sizeof(TcSmem), st>>>(d, a, tiles);
+  else
+    sweep_pose_tc_kernel<false><<<grid, kTcThreads, sizeof(TcSmem), st>>>(d, a, tiles);
   return cudaGetLastError();
 }
 

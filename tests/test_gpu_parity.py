@@ -134,6 +134,22 @@ def test_pose_sweep_f64_and_f32(ctx, pose_case):
     assert np.abs(c32[ok] - want_c[ok]).max() <= 2  # only points numerically on the threshold
 
 
+def test_pose_sweep_without_counts(ctx, pose_case):
+    """counts == NULL (what ScoreModel computes, ransac.h:300-312): same scores and winner as with counts."""
+    inst, f, _, models, valid = pose_case
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    O = ol.oracle()
+    want_s, _ = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], models, 144.0)
+    ok = valid == 1
+    for prec, tol in ((rlb().RLB_F64, F64_RTOL), (rlb().RLB_F32, F32_RTOL)):
+        s, c, bid, bsc = sc.score_models(models, 144.0, valid=valid, precision=prec, want_counts=False)
+        assert c is None
+        np.testing.assert_allclose(s[ok], want_s[ok], rtol=tol)
+        s2, _, bid2, bsc2 = sc.score_models(models, 144.0, valid=valid, precision=prec)
+        np.testing.assert_allclose(s[ok], s2[ok], rtol=1e-6 if prec == rlb().RLB_F32 else 0)
+        assert bid == bid2 == int(np.argmin(np.where(ok, want_s, np.inf)))
+
+
 def test_pose_inliers_ordered_and_fused_score(ctx, pose_case):
     inst, f, _, models, valid = pose_case
     sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
