@@ -32,6 +32,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLOP_PER_EVAL = 29.0  # pose evaluation incl. min + accumulate
+# dram__bytes_read.sum + dram__bytes_write.sum of one sweep_pose_tc_kernel launch on the default C5 run
+# (ncu --set full, profiles/r01r_ncu_sweep_tc.csv): 80.3 MB read (72 MB of operand tiles) + 28.0 MB written
+# (the [splits][K] partials)
+TC_TRAFFIC = 108.3e6
 THR = 144.0           # 12 px squared, camera_pose_estimation.cc:154-156
 WORKLOADS = {
     "c5": dict(n=1_000_000, k=65_536, name="scoring stress N=1M x K=65536 P3P hypotheses (configs[4])"),
@@ -302,21 +306,43 @@ def run_ours(args):
     evals_per_launch = k * n
     achieved_tflops = evals_per_launch * FLOP_PER_EVAL / (sweep_avg_ms * 1e-3) / 1e12
     bpp = 20 if prec == rlb.RLB_F32 else 40
+    if prec == rlb.RLB_F32 and ctx.last_sweep_plan()[0] == 9:
+        bpp = 72  # tensor-core operand tiles: 16 + 2 floats per point
     algo_bytes = n * bpp + k * 96 + k * 12
     inl_avg_ms = float(np.mean(inl_ms))
     inl_bytes = n * 40 + 4 * n_inl
+    variant, splits = ctx.last_sweep_plan()
+    ffma_names = {0: "sweep_pose_f32x2_kernel<4>", 2: "sweep_pose_f32x2_kernel<2>", 3: "sweep_pose_f32x2_kernel<8>",
+                  7: "sweep_kernel<PoseF,double,4>", -1: "sweep_kernel<PoseF,double,2>"}
+    tc = (variant == 9)
+    kernel_name = ("sweep_pose_tc_kernel<%s>" % ("true" if args.counts else "false")) if tc \
+        else ffma_names.get(variant, "sweep variant %d" % variant)
+    tensor = None
+    if tc:
+        # the projection of one evaluation is 3 rows x K = 16 TF32 MACs on the tensor core (hi/lo split)
+        tf32 = evals_per_launch * 96.0 / (sweep_avg_ms * 1e-3) / 1e12
+        tf32_peak = peaks.get("bf16_tflops", 0.0) / 2.0 if peaks.get("bf16_tflops") else None
+        tensor = {"achieved_tf32_tflops": tf32, "peak_tf32_tflops": tf32_peak,
+                  "frac": (tf32 / tf32_peak) if tf32_peak else None,
+                  "note": "tcgen05.mma kind::tf32 M128 N32 K8; peak = MEASURED_PEAKS bf16 / 2. The tensor pipe is "
+                          "not the bound: the CUDA-core epilogue (rsqrt, residual, MSAC test, sums; ~9 issue "
+                          "slots per evaluation-warp) and the TMEM read-back are (DESIGN.md section 3c)"}
     roofline = {
-        "bound": "fma", "kernel": "sweep_pose_f32x2_kernel<8>" if prec == rlb.RLB_F32 else "sweep_kernel<PoseF,double,2>",
+        "bound": "fma", "kernel": kernel_name, "sweep_variant": variant, "splits": splits, "tensor": tensor,
         "achieved": achieved_tflops, "peak": fma_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fma_peak,
         "peak_source": "rlb_measure_fma_peak: register-resident %s microbenchmark on this GPU, same run "
                        "(MEASURED_PEAKS.json has no FMA-pipe figure)" % ("FFMA" if fma_dtype else "DFMA"),
         "ffma2_peak_tflops": ffma2_peak,
+        "frac_note": ("29 algorithmic flop per evaluation against the FFMA-pipe peak; with the tensor-core sweep "
+                      "18 of them (the 3x4 projection) run on the tensor pipe, so the fraction is work-equivalent, "
+                      "not FMA-pipe occupancy") if tc else None,
         "flop_per_eval": FLOP_PER_EVAL, "evals_per_launch": evals_per_launch, "launch_ms": sweep_avg_ms,
         "evals_per_s": evals_per_launch / (sweep_avg_ms * 1e-3),
         "share_of_step": sweep_avg_ms * args.steps / total_ms,
         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, one launch, from the ncu --set full
         # capture of the same command (profiles/r01b_ncu_sweep_h8.csv); only valid for the default f32 C5 run.
-        "traffic": 33.1e6 if (prec == rlb.RLB_F32 and args.workload == "c5" and world == 1) else None,
+        "traffic": (TC_TRAFFIC if tc else 33.1e6) if (prec == rlb.RLB_F32 and args.workload == "c5" and world == 1)
+        else None,
         "hbm": {"algorithmic_bytes": algo_bytes, "achieved_gbs": algo_bytes / (sweep_avg_ms * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs"), "peak_kind": peak_kind,
                 "note": "arithmetic intensity ~%.0f FLOP/B: HBM is not the bound of this kernel"

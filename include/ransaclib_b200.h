@@ -236,6 +236,10 @@ int rlb_localize_batch_dev(rlb_ctx* ctx, int num_queries, int max_matches, const
  * and returns its device time (which: 0 = K x N sweep, 1 = inlier pass). */
 int rlb_ctx_set_timing(rlb_ctx* ctx, int enabled);
 int rlb_ctx_kernel_time_ms(rlb_ctx* ctx, int which, double* ms);
+/* Plan of the LAST K x N sweep of this context: kernel variant (9 = tensor-core sweep sweep_pose_tc_kernel,
+ * 0..3 = FFMA2 sweeps with 4/1/2/8 hypotheses per thread, 7/8 = f64 sweeps, -1 = generic) and the number of
+ * point-axis splits. Reporting only; the planner (capi.cu, score_dev) picks both per call. */
+int rlb_ctx_last_sweep_plan(rlb_ctx* ctx, int* variant, int* splits);
 /* Register-resident FMA microbenchmark: returns achieved TFLOP/s of the FP32
  * (dtype 1: FFMA, 2: packed FFMA2) or FP64 (dtype 0: DFMA) pipe on this device.
  * Used by bench.py for the FMA-pipe roofline denominator ("of measured"). */

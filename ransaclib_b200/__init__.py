@@ -64,6 +64,12 @@ class Context:
     def set_timing(self, enabled: bool):
         _capi.check(self._lib.rlb_ctx_set_timing(self._h, int(enabled)))
 
+    def last_sweep_plan(self):
+        """-> (variant, splits) of the last K x N sweep (9 = tensor-core sweep)."""
+        v, sp = C.c_int32(), C.c_int32()
+        _capi.check(self._lib.rlb_ctx_last_sweep_plan(self._h, C.byref(v), C.byref(sp)))
+        return v.value, sp.value
+
     def kernel_time_ms(self, which: int) -> float:
         """Device time of the last sweep (0) / inlier (1) kernel; needs set_timing(True)."""
         out = C.c_double()

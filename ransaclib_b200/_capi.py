@@ -25,7 +25,7 @@ SYMBOLS = [
     "rlb_scorer_num_types", "rlb_scorer_num_data", "rlb_scorer_model_size", "rlb_scorer_get_rays",
     "rlb_score_models", "rlb_score_models_dev", "rlb_get_inliers", "rlb_get_inliers_dev",
     "rlb_eval_errors", "rlb_solve_line2pt_batch", "rlb_solve_point_normal_batch", "rlb_solve_p3p_batch",
-    "rlb_hypothesize_and_score", "rlb_hypothesize_and_score_dev", "rlb_measure_fma_peak", "rlb_sharded_round_dev", "rlb_select_winner_dev", "rlb_ctx_set_timing", "rlb_ctx_kernel_time_ms",
+    "rlb_hypothesize_and_score", "rlb_hypothesize_and_score_dev", "rlb_measure_fma_peak", "rlb_sharded_round_dev", "rlb_select_winner_dev", "rlb_ctx_set_timing", "rlb_ctx_kernel_time_ms", "rlb_ctx_last_sweep_plan",
     "rlb_localize_default_options", "rlb_localize_batch", "rlb_localize_batch_dev",
 ]
 
@@ -94,6 +94,7 @@ def load():
     lib.rlb_select_winner_dev.argtypes = [vp, vp, i32, i32, vp]
     lib.rlb_ctx_set_timing.argtypes = [vp, i32]
     lib.rlb_ctx_kernel_time_ms.argtypes = [vp, i32, C.POINTER(f64)]
+    lib.rlb_ctx_last_sweep_plan.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
     lib.rlb_localize_default_options.argtypes = [C.POINTER(LocalizeOptions), f64, i32, C.c_uint32, C.c_uint32]
     lib.rlb_localize_default_options.restype = None
     lib.rlb_localize_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, C.POINTER(LocalizeOptions), vp, vp, vp]

@@ -65,6 +65,7 @@ struct rlb_ctx {
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   int launches_i = 0;  // per-call counter target for the launch_* helpers
+  int last_variant = -1, last_splits = 0;  // plan of the last sweep (rlb_ctx_last_sweep_plan)
   int64_t launches = 0;
   unsigned int epoch = 0;
   // sweep scratch
@@ -336,18 +337,19 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   a.n_splits = splits;
   a.stages_per_split = sps;
   // Tensor-core sweep (pose, f32 arithmetic class): the projection runs as tcgen05.mma on TF32x2-split
-  // operands. Its unit along the point axis is a 32-point tile.
-  const bool use_tc = (d.kind == RLB_KIND_POSE && precision == RLB_F32 && a.variant == 9);
-  if (use_tc) {
-    if (!s->tc_tiles) {
-      const int rc = pool_alloc(c, rlb::tc_tiles_bytes(d.npad), &s->tc_tiles);
-      if (rc) return rc;
-      RLB_CUDA(rlb::launch_tc_pack(d, static_cast<float*>(s->tc_tiles), c->stream, &c->launches_i));
-    }
+  // operands. Its unit along the point axis is a 32-point tile. Measured 2.40e12 evals/s with counts and
+  // 2.51e12 without on C5 against 1.90e12 for the FFMA2 sweep (profiles/r01r_*), so it is planned with the
+  // same fill / balance score and wins unless the batch is too small to pay for packing the tiles.
+  bool use_tc = false;
+  if (d.kind == RLB_KIND_POSE && precision == RLB_F32 && (forced_variant == 9 || (forced_variant < 0 && k >= 512))) {
     const int total_tiles = d.npad / rlb::tc_tile_points();
     const int slots = c->sms * rlb::tc_resident_ctas();
-    const int k_tiles = (k + rlb::tc_hyps_per_cta() - 1) / rlb::tc_hyps_per_cta();
+    const int hpc = rlb::tc_hyps_per_cta();
+    const int k_tiles = (k + hpc - 1) / hpc;
+    const double tile_use = static_cast<double>(k) / (static_cast<double>(k_tiles) * hpc);
+    const double speed = (d_counts != nullptr) ? 1.26 : 1.32;
     double best = -1.0;
+    int tc_splits = 1, tc_tps = total_tiles;
     for (int s0 = 1; s0 <= std::min(total_tiles, 64); ++s0) {
       if (forced_splits > 0 && s0 != std::min(forced_splits, std::min(total_tiles, 64))) continue;
       const int tp = (total_tiles + s0 - 1) / s0;
@@ -356,15 +358,27 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
       const long long waves = (ctas + slots - 1) / slots;
       const double fill = static_cast<double>(ctas) / static_cast<double>(waves * slots);
       const double balance = static_cast<double>(total_tiles) / (static_cast<double>(s_eff) * tp);
-      const double sc = fill * balance * (1.0 + 1e-4 * s_eff);
+      const double sc = fill * balance * tile_use * speed * (1.0 + 1e-4 * s_eff);
       if (sc > best) {
         best = sc;
-        a.n_splits = s_eff;
-        a.stages_per_split = tp;
+        tc_splits = s_eff;
+        tc_tps = tp;
       }
     }
-    splits = a.n_splits;
+    if (forced_variant == 9 || best > best_score) {
+      use_tc = true;
+      a.variant = 9;
+      a.n_splits = splits = tc_splits;
+      a.stages_per_split = tc_tps;
+    }
   }
+  if (use_tc && !s->tc_tiles) {
+    const int rc = pool_alloc(c, rlb::tc_tiles_bytes(d.npad), &s->tc_tiles);
+    if (rc) return rc;
+    RLB_CUDA(rlb::launch_tc_pack(d, static_cast<float*>(s->tc_tiles), c->stream, &c->launches_i));
+  }
+  c->last_variant = a.variant;
+  c->last_splits = splits;
   RLB_CUDA(c->part_score.ensure(static_cast<size_t>(splits) * k * sizeof(double)));
   RLB_CUDA(c->part_count.ensure(static_cast<size_t>(splits) * k * sizeof(int32_t)));
   a.part_score = c->part_score.as<double>();
@@ -1196,6 +1210,13 @@ int rlb_ctx_kernel_time_ms(rlb_ctx* c, int which, double* ms) {
   float t = 0.f;
   RLB_CUDA(cudaEventElapsedTime(&t, c->ev[2 * which], c->ev[2 * which + 1]));
   *ms = t;
+  return RLB_OK;
+}
+
+int rlb_ctx_last_sweep_plan(rlb_ctx* c, int* variant, int* splits) {
+  if (!c) return fail(RLB_E_ARG, "null context");
+  if (variant) *variant = c->last_variant;
+  if (splits) *splits = c->last_splits;
   return RLB_OK;
 }
 

@@ -148,7 +148,7 @@ struct Smem2 {
   uint32_t tmem;
 };
 // `issuers` warps each issue n_mma MMAs (straight-line groups of 6, elected lane), own barrier, own D columns.
-template <int N, int M, int KIND>
+template <int N, int M, int KIND, int TS>
 __global__ void probe2(long long* out, int n_groups, int issuers, int reps) {
   extern __shared__ __align__(128) unsigned char raw[];
   Smem2& S = *reinterpret_cast<Smem2*>(raw);
@@ -182,12 +182,21 @@ __global__ void probe2(long long* out, int n_groups, int issuers, int reps) {
       const long long t0 = clock64();
       if (elect_one()) {
         for (int g = 0; g < n_groups; ++g) {
-          mma_ss_k<KIND>(d0, da, db, idesc, 0);
-          mma_ss_k<KIND>(d0 + N % 128, da, db, idesc, 0);
-          mma_ss_k<KIND>(d0, da, db, idesc, 1);
-          mma_ss_k<KIND>(d0 + N % 128, da, db, idesc, 1);
-          mma_ss_k<KIND>(d0, da, db, idesc, 1);
-          mma_ss_k<KIND>(d0 + N % 128, da, db, idesc, 1);
+          if (TS) {
+            mma_ts(d0, tmem + 480, db, idesc, 0);
+            mma_ts(d0 + N % 128, tmem + 488, db, idesc, 0);
+            mma_ts(d0, tmem + 496, db, idesc, 1);
+            mma_ts(d0 + N % 128, tmem + 480, db, idesc, 1);
+            mma_ts(d0, tmem + 488, db, idesc, 1);
+            mma_ts(d0 + N % 128, tmem + 496, db, idesc, 1);
+          } else {
+            mma_ss_k<KIND>(d0, da, db, idesc, 0);
+            mma_ss_k<KIND>(d0 + N % 128, da, db, idesc, 0);
+            mma_ss_k<KIND>(d0, da, db, idesc, 1);
+            mma_ss_k<KIND>(d0 + N % 128, da, db, idesc, 1);
+            mma_ss_k<KIND>(d0, da, db, idesc, 1);
+            mma_ss_k<KIND>(d0 + N % 128, da, db, idesc, 1);
+          }
         }
         commit(&S.bar[warp]);
       }
@@ -207,13 +216,13 @@ __global__ void probe2(long long* out, int n_groups, int issuers, int reps) {
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
 }
-template <int N, int M, int KIND>
+template <int N, int M, int KIND, int TS>
 void run2(long long* d_out) {
-  cudaFuncSetAttribute(probe2<N, M, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2));
+  cudaFuncSetAttribute(probe2<N, M, KIND, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2));
   for (int issuers = 1; issuers <= 2; ++issuers) {
-    printf("probe2 %s M=%d N=%d issuers=%d (total/issue cycles):", KIND ? "bf16" : "tf32", M, N, issuers);
+    printf("probe2 %s %s M=%d N=%d issuers=%d (total/issue cycles):", KIND ? "bf16" : "tf32", TS ? "TS" : "SS", M, N, issuers);
     for (int g : {1, 2, 4, 8}) {
-      probe2<N, M, KIND><<<1, 128, sizeof(Smem2)>>>(d_out, g, issuers, 20);
+      probe2<N, M, KIND, TS><<<1, 128, sizeof(Smem2)>>>(d_out, g, issuers, 20);
       long long h[4];
       cudaMemcpy(h, d_out, sizeof(h), cudaMemcpyDeviceToHost);
       printf("  n%d=%lld/%lld", 6 * g, h[0], h[1]);
@@ -242,13 +251,14 @@ void run(long long* d_out, const char* name) {
 int main() {
   long long* d_out;
   cudaMalloc(&d_out, 64 * sizeof(long long));
-  run<32>(d_out, "mma");
-  run2<16, 128, 0>(d_out);
-  run2<64, 128, 0>(d_out);
-  run2<128, 128, 0>(d_out);
-  run2<64, 64, 0>(d_out);
-  run2<64, 128, 1>(d_out);
-  run2<256, 128, 1>(d_out);
+  run2<16, 128, 0, 0>(d_out);
+  run2<16, 128, 0, 1>(d_out);
+  run2<32, 128, 0, 0>(d_out);
+  run2<32, 128, 0, 1>(d_out);
+  run2<64, 128, 0, 0>(d_out);
+  run2<64, 128, 0, 1>(d_out);
+  run2<128, 128, 0, 0>(d_out);
+  run2<128, 128, 0, 1>(d_out);
   for (int n : {1, 2, 3, 6, 12}) {
     probe_ld<<<1, 128>>>(d_out, n, 20);
     long long h[4];
