@@ -33,9 +33,9 @@ sys.path.insert(0, ROOT)
 
 FLOP_PER_EVAL = 29.0  # pose evaluation incl. min + accumulate
 # dram__bytes_read.sum + dram__bytes_write.sum of one sweep_pose_tc_kernel launch on the default C5 run
-# (ncu --set full, profiles/r01r_ncu_sweep_tc.csv): 80.3 MB read (72 MB of operand tiles) + 28.0 MB written
-# (the [splits][K] partials)
-TC_TRAFFIC = 108.3e6
+# (ncu --set full): 80.2 MB read (72 MB of operand tiles) + the [splits][K] partials written: 18.4 MB scores only
+# (profiles/r01s_ncu_sweep_tc.csv), 28.0 MB with counts (profiles/r01r_ncu_sweep_tc.csv)
+TC_TRAFFIC = {False: 98.6e6, True: 108.3e6}
 THR = 144.0           # 12 px squared, camera_pose_estimation.cc:154-156
 WORKLOADS = {
     "c5": dict(n=1_000_000, k=65_536, name="scoring stress N=1M x K=65536 P3P hypotheses (configs[4])"),
@@ -341,7 +341,7 @@ def run_ours(args):
         "share_of_step": sweep_avg_ms * args.steps / total_ms,
         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, one launch, from the ncu --set full
         # capture of the same command (profiles/r01b_ncu_sweep_h8.csv); only valid for the default f32 C5 run.
-        "traffic": (TC_TRAFFIC if tc else 33.1e6) if (prec == rlb.RLB_F32 and args.workload == "c5" and world == 1)
+        "traffic": (TC_TRAFFIC[bool(args.counts)] if tc else 33.1e6) if (prec == rlb.RLB_F32 and args.workload == "c5" and world == 1)
         else None,
         "hbm": {"algorithmic_bytes": algo_bytes, "achieved_gbs": algo_bytes / (sweep_avg_ms * 1e-3) / 1e9,
                 "peak_gbs": peaks.get("hbm_gbs"), "peak_kind": peak_kind,
