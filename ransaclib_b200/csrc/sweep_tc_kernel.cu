@@ -4,22 +4,27 @@
 // math-pipe throttle as the top stall, and 9 of the 14 FMA-pipe operations of an evaluation are the
 // projection p = R' X' + t' (BASELINE north_star: "tensor cores only if ncu shows the 3x4 projection
 // contraction to be FMA-issue-bound"). Here the projection of 128 hypotheses x 32 points is six
-// tcgen05.mma (kind::tf32, M = 128, N = 32, K = 8) into TMEM, and the CUDA cores keep the part
-// that is not a contraction: reciprocal, residual, MSAC test and the per-hypothesis sums.
+// tcgen05.mma (kind::tf32, M = 128, N = 32, K = 8, A from TMEM) into TMEM, and the CUDA cores keep
+// the part that is not a contraction: reciprocal, residual, MSAC test and the per-hypothesis sums.
+// Replaces, for f32 pose sweeps, the N x K loop of LocallyOptimizedMSAC::ScoreModel (ransac.h:295-303)
+// over EvaluateModelOnPoint (calibrated_absolute_pose_estimator.cc:154-167).
 //
 // Precision: TF32 keeps 11 significant bits, so both operands are split, x = hi + lo with hi = x
 // with the low 13 mantissa bits cleared (exactly what the tensor core reads) and lo = x - hi (exact
 // in f32). K = 16 carries all four partial products,
-//     A row (hypothesis): [ rh0 rh1 rh2 th | rl0 rl1 rl2 tl | rh0 rh1 rh2 0 | rl0 rl1 rl2 0 ]
+//     A row (hypothesis): [ rh0 rh1 rh2 th | rl0 rl1 rl2 tl ]   (the same 8 TMEM columns for both K steps)
 //     B col (point)     : [ Xh  Yh  Zh  1  | Xh  Yh  Zh  1  | Xl  Yl  Zl  0 | Xl  Yl  Zl  0 ]
 // accumulated in f32 by the tensor core: the result differs from the f32 FMA chain by the second
 // truncation of the lo parts (<= 2^-22 relative per term), i.e. it is an f32-class projection.
 //
 // Operand layout: UMMA K-major, SWIZZLE_NONE canonical layout (core matrix = 8 rows x 16 bytes,
-// rows 16 B apart; SBO = byte distance between core matrices along M/N, LBO = along K). The points
+// rows 16 B apart; SBO = byte distance between core matrices along N, LBO = along K). The points
 // are pre-packed in global memory in exactly the shared-memory image of a tile (32 points: 4 K-chunks
 // x 4 cores x 128 B = 2 KB, followed by 32 x (-u) and 32 x (-v)), so one 1-D bulk TMA copy per tile
-// brings everything in. The hypotheses of a CTA are written to shared memory once.
+// brings everything in. The hypotheses of a CTA are written to TMEM once (tcgen05.st): the A operand
+// is re-read by every MMA, and the TS form runs at the N/2-cycle floor where the SS form streams 4 KB
+// of A from shared memory per MMA (tools/probes/umma_probe.cu). What was measured on the way, and what
+// bounds the kernel now, is in profiles/r01r_tc_experiments.md and DESIGN.md section 3.
 #include <cfloat>
 
 #include "rlb_internal.cuh"
@@ -33,8 +38,8 @@ constexpr int kTcTile = 32;                // points per MMA tile (N)
 constexpr int kTcTileFloats = 512 + 64;    // 16 x 32 operand floats + 32 x (-u) + 32 x (-v)
 constexpr int kTcTileBytes = kTcTileFloats * 4;
 constexpr int kTcRing = 8;                 // TMA ring depth (tiles)
-constexpr int kTcCols = 128;               // TMEM columns: px [0,32) py [32,64) pz [64,96)
-constexpr int kTcFlush = 16;               // tiles (512 points) per f32 -> f64 flush
+constexpr int kTcCols = 128;               // TMEM columns: A operand [0,24), px [32,64) py [64,96) pz [96,128)
+constexpr int kTcFlush = 16;               // tiles (512 evaluations per thread) per f32 -> f64 flush
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -79,16 +84,6 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_b
 // Instruction descriptor: D = f32, A = B = tf32, both K-major, M = 128, N = 32, dense.
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((kTcTile >> 3) << 17) | ((128u >> 4) << 24);
 
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-      "}\n" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(kIdesc), "r"(accumulate)
-      : "memory");
-}
 // A operand from TMEM (lane = hypothesis, 8 consecutive 32-bit columns = K), B from shared memory.
 __device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
                                              uint32_t accumulate) {
@@ -120,18 +115,6 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
   uint32_t r[8];
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"

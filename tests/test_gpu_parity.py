@@ -266,6 +266,37 @@ def test_far_from_origin_f32_recentring(ctx):
     assert bid32 == int(np.argmin(ws))
 
 
+@pytest.mark.parametrize("n", [5, 31, 32, 33, 700, 4097])
+def test_tensor_core_sweep_edges(ctx, n):
+    """The tensor-core sweep (f32 pose, K >= 512) on point counts around its 32-point tile, with hypotheses
+    that put every point behind the camera, and against the FFMA2 sweep (K < 512) on the same models."""
+    n_in = max(3, n // 2)
+    inst = synth.pose_instance(77 + n, n_in, n - n_in)
+    f = inst["focal"]
+    p2, p3 = inst["points2D"], inst["points3D"]
+    sc = ctx.pose_scorer(p2, p3, f, f)
+    models = synth.perturbed_poses(3, inst["R_gt"], inst["c_gt"], 640, rot_sigma=0.01, trans_sigma=0.05)
+    behind = models[:8].copy().reshape(8, 4, 3)  # column-major [R | c]: behind[m, j] is column j
+    behind[:, :3, 1:] *= -1.0  # R' = diag(1, -1, -1) R, half a turn about x: every depth changes sign
+    models[100:108] = behind.reshape(8, 12)
+    O = ol.oracle()
+    ws, wc = ol.pose_score(O, f, f, p2, p3, models, 144.0)
+    assert (wc[100:108] == 0).all() and np.allclose(ws[100:108], 144.0 * n)
+    for k in (640, 513, 512):
+        s, c, bid, _ = sc.score_models(models[:k], 144.0, precision=rlb().RLB_F32)
+        assert ctx.last_sweep_plan()[0] == 9
+        np.testing.assert_allclose(s, ws[:k], rtol=F32_RTOL)
+        assert np.abs(c - wc[:k]).max() <= 2 and (c[100:108] == 0).all()
+        assert bid == int(np.argmin(ws[:k]))
+        s_nc, c_nc, bid_nc, _ = sc.score_models(models[:k], 144.0, precision=rlb().RLB_F32, want_counts=False)
+        np.testing.assert_allclose(s_nc, s, rtol=1e-6)
+        assert c_nc is None and bid_nc == bid
+    s_f, c_f, _, _ = sc.score_models(models[:500], 144.0, precision=rlb().RLB_F32)
+    assert ctx.last_sweep_plan()[0] != 9  # below 512 hypotheses the FFMA2 sweep runs
+    np.testing.assert_allclose(s_f, s[:500], rtol=2e-5)
+    assert np.abs(c_f - c[:500]).max() <= 2
+
+
 def test_determinism(ctx, pose_case):
     inst, f, _, models, valid = pose_case
     sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
