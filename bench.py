@@ -709,9 +709,10 @@ def main():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--no-localization", action="store_true",
                     help="c5: skip the batched-localization leg that is reported under 'localization'")
-    ap.add_argument("--counts", action="store_true",
-                    help="also return an inlier count for every hypothesis (ScoreModel in ransac.h returns "
-                         "only the score; the winner's inliers come from the GetInliers pass either way)")
+    ap.add_argument("--no-counts", dest="counts", action="store_false",
+                    help="scores only: pass no counts array to the sweep, which is what ScoreModel in ransac.h "
+                         "computes (the winner's inliers come from the GetInliers pass either way). Default: "
+                         "score AND inlier count per hypothesis, as BASELINE.json's north_star describes")
     ap.add_argument("--k-override", type=int, default=0, help="tuning only: total number of hypotheses")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: skips the e2e leg, the CPU baseline and the peak microbenchmarks")

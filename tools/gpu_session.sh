@@ -10,8 +10,8 @@ timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; ech
 tail -3 $O/${TAG}_pytest.log
 timeout 120 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 $O/${TAG}_smoke.log
 timeout 400 python bench.py > $O/${TAG}_bench_c5.json 2> $O/${TAG}_bench_c5.err; echo "bench c5 rc=$?"
-timeout 200 python bench.py --no-localization --counts > $O/${TAG}_bench_c5_counts.json 2> $O/${TAG}_bench_c5_counts.err; echo "bench c5 counts rc=$?"
-RLB_SWEEP_VARIANT=3 timeout 200 python bench.py --no-localization --counts > $O/${TAG}_bench_c5_ffma2.json 2> $O/${TAG}_bench_c5_ffma2.err; echo "bench c5 ffma2 rc=$?"
+timeout 200 python bench.py --no-localization --no-counts > $O/${TAG}_bench_c5_nocounts.json 2> $O/${TAG}_bench_c5_nocounts.err; echo "bench c5 no-counts rc=$?"
+RLB_SWEEP_VARIANT=3 timeout 200 python bench.py --no-localization > $O/${TAG}_bench_c5_ffma2.json 2> $O/${TAG}_bench_c5_ffma2.err; echo "bench c5 ffma2 rc=$?"
 timeout 300 python bench.py --precision f64 --steps 3 > $O/${TAG}_bench_c5_f64.json 2> $O/${TAG}_bench_c5_f64.err; echo "bench c5 f64 rc=$?"
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_c5_ref.json 2>&1; echo "bench ref rc=$?"
 timeout 400 python bench.py --workload c4 --steps 5 --warmup 2 > $O/${TAG}_bench_c4.json 2> $O/${TAG}_bench_c4.err; echo "bench c4 rc=$?"
