@@ -98,6 +98,14 @@ class DeviceScorer {
     Check(rlb_scorer_create_pose(c.get(), n, p2d, p3d, fx, fy, &s_), "rlb_scorer_create_pose");
   }
 
+  // Any other solver of the concept: data is n x dims (row i = what EvaluateModelOnPoint(model, i) reads),
+  // eval_source defines `__device__ double rlb_eval(const double* model, const double* point)`.
+  void InitCustom(Context& c, int n, int dims, const double* data, int model_doubles, const char* eval_source) {
+    reset();
+    Check(rlb_scorer_create_custom(c.get(), n, dims, data, model_doubles, eval_source, &s_),
+          "rlb_scorer_create_custom");
+  }
+
   bool valid() const { return s_ != nullptr; }
   rlb_scorer* get() const { return s_; }
   int model_size() const { return rlb_scorer_model_size(s_); }

@@ -28,6 +28,7 @@
 #ifndef RANSACLIB_B200_H_
 #define RANSACLIB_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -47,6 +48,7 @@ extern "C" {
 #define RLB_KIND_LINE 0        /* examples/line_estimator */
 #define RLB_KIND_HYBRID_LINE 1 /* examples/hybrid_line_estimator (2 data types) */
 #define RLB_KIND_POSE 2        /* examples/calibrated_absolute_pose_estimator */
+#define RLB_KIND_CUSTOM 3      /* user-defined EvaluateModelOnPoint (rlb_scorer_create_custom) */
 
 typedef struct rlb_ctx rlb_ctx;       /* one device + one stream + scratch; not thread-safe */
 typedef struct rlb_scorer rlb_scorer; /* one data set resident in HBM; immutable */
@@ -80,12 +82,27 @@ int rlb_scorer_create_hybrid_line(rlb_ctx* ctx, int n0, const double* xy0, int n
  * as PixelsToViewingRays does (.cc:214-227). */
 int rlb_scorer_create_pose(rlb_ctx* ctx, int n, const double* points2D,
                            const double* points3D, double fx, double fy, rlb_scorer** out);
+/* Any other solver of the README's concept (reference README.md:105-154): its
+ *   double EvaluateModelOnPoint(const Model& model, int i) const
+ * is handed over as CUDA source defining
+ *   __device__ double rlb_eval(const double* model, const double* point);   // squared residual
+ * where `model` is the model packed into model_doubles (1..12) doubles and `point` is row i of data
+ * (dims doubles, 1..8). The source is compiled once, at creation, with NVRTC for sm_100a (-fmad=false, so the
+ * arithmetic is what a strict-IEEE C++ build of the same expression does); a compile error is returned as
+ * RLB_E_ARG with the compiler log in rlb_last_error(). The scorer then works with rlb_score_models[_dev],
+ * rlb_get_inliers[_dev] and rlb_eval_errors in f64 (RLB_F32 is accepted and runs the same f64 kernel); the
+ * device minimal solvers are not available for it (hypotheses come from the host MinimalSolver). */
+int rlb_scorer_create_custom(rlb_ctx* ctx, int n, int dims, const double* data, int model_doubles,
+                             const char* eval_source, rlb_scorer** out);
+/* Compiles eval_source exactly as rlb_scorer_create_custom would, without touching a device (usable on a
+ * machine with no GPU): RLB_OK and the size of the sm_100a cubin, or the compiler log as above. */
+int rlb_custom_compile_check(const char* eval_source, int dims, int model_doubles, size_t* cubin_bytes);
 /* Destroy every scorer BEFORE its context: the data-set memory returns to the context's pool. */
 int rlb_scorer_destroy(rlb_scorer* s);
 int rlb_scorer_kind(const rlb_scorer* s);
 int rlb_scorer_num_types(const rlb_scorer* s);
 int rlb_scorer_num_data(const rlb_scorer* s, int type);
-int rlb_scorer_model_size(const rlb_scorer* s); /* doubles per model: 3 or 12 */
+int rlb_scorer_model_size(const rlb_scorer* s); /* doubles per model: 3, 12 or the custom model_doubles */
 /* Copies the device-computed viewing rays (n x 3) back; pose scorers only. */
 int rlb_scorer_get_rays(const rlb_scorer* s, double* rays);
 

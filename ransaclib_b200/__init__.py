@@ -140,6 +140,19 @@ class Context:
                                                             _capi.ptr(xynn1), C.byref(h)))
         return Scorer(self, h)
 
+    def custom_scorer(self, data, model_doubles: int, eval_source: str) -> "Scorer":
+        """Any other solver of the reference's concept: ``data`` is n x dims (one point per row) and
+        ``eval_source`` is CUDA source defining
+        ``__device__ double rlb_eval(const double* model, const double* point)`` = the squared residual
+        (the body of EvaluateModelOnPoint). Compiled with NVRTC at creation."""
+        data = np.ascontiguousarray(data, dtype=np.float64)
+        if data.ndim != 2:
+            raise ValueError("data must be n x dims")
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_scorer_create_custom(self._h, data.shape[0], data.shape[1], _capi.ptr(data),
+                                                       int(model_doubles), eval_source.encode(), C.byref(h)))
+        return Scorer(self, h)
+
     def pose_scorer(self, points2D, points3D, fx: float, fy: float) -> "Scorer":
         p2 = _capi.f64a(points2D, (-1, 2))
         p3 = _capi.f64a(points3D, (-1, 3))
@@ -149,6 +162,15 @@ class Context:
         _capi.check(self._lib.rlb_scorer_create_pose(self._h, len(p2), _capi.ptr(p2), _capi.ptr(p3), float(fx),
                                                      float(fy), C.byref(h)))
         return Scorer(self, h)
+
+
+def custom_compile_check(eval_source: str, dims: int, model_doubles: int) -> int:
+    """Compiles a user functor the way ``Context.custom_scorer`` would (NVRTC, sm_100a) without touching a
+    device; -> size of the cubin. A compile error raises RlbError carrying the compiler log."""
+    lib = _capi.load()
+    n = C.c_size_t()
+    _capi.check(lib.rlb_custom_compile_check(eval_source.encode(), int(dims), int(model_doubles), C.byref(n)))
+    return int(n.value)
 
 
 class Scorer:

@@ -109,6 +109,8 @@ struct rlb_scorer {
   void* soa64 = nullptr;
   void* soa32 = nullptr;
   void* tc_tiles = nullptr;  // tensor-core operand tiles of the points, packed on first use
+  rlb::CustomModule* custom = nullptr;  // RLB_KIND_CUSTOM: the NVRTC-compiled functor kernels
+  void* custom_err = nullptr;           // RLB_KIND_CUSTOM: [npad] per-point errors of the K = 1 passes
 };
 
 namespace {
@@ -377,6 +379,22 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     if (rc) return rc;
     RLB_CUDA(rlb::launch_tc_pack(d, static_cast<float*>(s->tc_tiles), c->stream, &c->launches_i));
   }
+  int custom_pps = 128;
+  if (d.kind == RLB_KIND_CUSTOM) {
+    // user functor (custom_functor.cu): 128 hypotheses per CTA, whole 128-point chunks per split, ~8 CTAs per SM
+    const int k_tiles = (k + 127) / 128;
+    const int chunks = (d.n[0] + 127) / 128;
+    if (chunks > 0) {
+      const int want = std::max(1, std::min(std::min(64, chunks), (c->sms * 8 + k_tiles - 1) / k_tiles));
+      custom_pps = ((chunks + want - 1) / want) * 128;
+      splits = (d.n[0] + custom_pps - 1) / custom_pps;
+    } else {
+      splits = 1;
+    }
+    a.n_splits = splits;
+    a.stages_per_split = custom_pps;
+    a.variant = -2;
+  }
   c->last_variant = a.variant;
   c->last_splits = splits;
   RLB_CUDA(c->part_score.ensure(static_cast<size_t>(splits) * k * sizeof(double)));
@@ -387,7 +405,11 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   RLB_CUDA(c->block_best.ensure(static_cast<size_t>(fblocks) * sizeof(BestRec)));
 
   if (c->timing) RLB_CUDA(cudaEventRecord(c->ev[0], c->stream));
-  if (use_tc) {
+  if (d.kind == RLB_KIND_CUSTOM) {
+    std::string err;
+    if (!rlb::launch_custom_sweep(s->custom, d, a, custom_pps, c->stream, &c->launches_i, &err))
+      return fail(RLB_E_CUDA, "custom sweep: %s", err.c_str());
+  } else if (use_tc) {
     RLB_CUDA(rlb::launch_sweep_tc(d, a, static_cast<const float*>(s->tc_tiles), c->stream, &c->launches_i));
   } else {
     RLB_CUDA(rlb::launch_sweep(d, a, precision, c->stream, &c->launches_i));
@@ -423,7 +445,7 @@ int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, con
   a.model = d_model;
   if (host_model) {
     a.model = nullptr;
-    for (int i = 0; i < rlb::model_size_of(d.kind); ++i) a.model_v[i] = host_model[i];
+    for (int i = 0; i < rlb::model_size_of(d); ++i) a.model_v[i] = host_model[i];
   }
   fill_thr(d, thr_inl, w, a.thr_inl, a.w);
   double dummy[rlb::kMaxTypes];
@@ -437,7 +459,26 @@ int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, con
   a.epoch = c->epoch;
   a.header = d_header;
   if (c->timing) RLB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  RLB_CUDA(rlb::launch_inliers(d, a, c->stream, &c->launches_i));
+  if (d.kind == RLB_KIND_CUSTOM) {
+    // the user's functor fills the error array, the shared compaction kernel reads it as a 1-channel data set
+    const double* dm = d_model;
+    if (host_model) {
+      RLB_CUDA(c->one_model.ensure(12 * sizeof(double)));
+      RLB_CUDA(cudaMemcpyAsync(c->one_model.p, host_model, d.model_doubles * sizeof(double), cudaMemcpyHostToDevice,
+                               c->stream));
+      dm = c->one_model.as<double>();
+    }
+    std::string err;
+    if (!rlb::launch_custom_errors(s->custom, d, dm, static_cast<double*>(s->custom_err), c->stream,
+                                   &c->launches_i, &err))
+      return fail(RLB_E_CUDA, "custom errors: %s", err.c_str());
+    DeviceData de = d;
+    de.soa64 = static_cast<const double*>(s->custom_err);
+    de.channels = 1;
+    RLB_CUDA(rlb::launch_inliers(de, a, c->stream, &c->launches_i));
+  } else {
+    RLB_CUDA(rlb::launch_inliers(d, a, c->stream, &c->launches_i));
+  }
   if (c->timing) {
     RLB_CUDA(cudaEventRecord(c->ev[3], c->stream));
     c->ev_valid[1] = true;
@@ -447,6 +488,7 @@ int inliers_dev(rlb_scorer* s, const double* d_model, const double* thr_inl, con
 }
 
 int solver_sample_size(const DeviceData& d, int solver) {
+  if (d.kind == RLB_KIND_CUSTOM) return -1;  // hypotheses of a user-defined solver come from its host MinimalSolver
   if (d.kind == RLB_KIND_POSE) return solver == 0 ? 4 : -1;
   if (d.kind == RLB_KIND_LINE) return solver == 0 ? 2 : -1;
   return solver == 0 ? 2 : (solver == 1 ? 1 : -1);
@@ -658,13 +700,73 @@ int rlb_scorer_create_pose(rlb_ctx* c, int n, const double* p2d, const double* p
   return RLB_OK;
 }
 
+int rlb_custom_compile_check(const char* eval_source, int dims, int model_doubles, size_t* cubin_bytes) {
+  if (!eval_source) return fail(RLB_E_ARG, "null source");
+  if (dims < 1 || dims > 8) return fail(RLB_E_ARG, "dims must be 1..8 (got %d)", dims);
+  if (model_doubles < 1 || model_doubles > 12) return fail(RLB_E_ARG, "model_doubles must be 1..12 (got %d)", model_doubles);
+  std::string cubin, err;
+  if (!rlb::custom_compile(eval_source, dims, model_doubles, &cubin, &err)) return fail(RLB_E_ARG, "%s", err.c_str());
+  if (cubin_bytes) *cubin_bytes = cubin.size();
+  return RLB_OK;
+}
+
+int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, int model_doubles,
+                             const char* eval_source, rlb_scorer** out) {
+  if (!c || !out || n < 0 || (n > 0 && !data) || !eval_source) return fail(RLB_E_ARG, "bad arguments");
+  if (dims < 1 || dims > 8) return fail(RLB_E_ARG, "dims must be 1..8 (got %d)", dims);
+  if (model_doubles < 1 || model_doubles > 12) return fail(RLB_E_ARG, "model_doubles must be 1..12 (got %d)", model_doubles);
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  std::string cubin, err;
+  if (!rlb::custom_compile(eval_source, dims, model_doubles, &cubin, &err)) return fail(RLB_E_ARG, "%s", err.c_str());
+  rc = ensure_first_use(c);  // a runtime call: the primary context the driver-API module is loaded into exists
+  if (rc) return rc;
+  rlb_scorer* s = new (std::nothrow) rlb_scorer();
+  if (!s) return fail(RLB_E_NOMEM, "out of host memory");
+  s->ctx = c;
+  DeviceData& d = s->d;
+  memset(&d, 0, sizeof(d));
+  d.kind = RLB_KIND_CUSTOM;
+  d.num_types = 1;
+  d.n[0] = n;
+  d.off[0] = 0;
+  d.off[1] = d.npad = std::max(pad_to(n, rlb::kSegAlign), rlb::kSegAlign);
+  d.channels = dims;
+  d.model_doubles = model_doubles;
+  s->custom = rlb::custom_load(cubin, dims, model_doubles, &err);
+  if (!s->custom) {
+    rlb_scorer_destroy(s);
+    return fail(RLB_E_CUDA, "loading the compiled functor: %s", err.c_str());
+  }
+  rc = upload(c, &s->raw0, data, static_cast<size_t>(n) * dims, c->stream);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(dims) * d.npad * sizeof(double), &s->soa64);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(d.npad) * sizeof(double), &s->custom_err);
+  if (rc) {
+    rlb_scorer_destroy(s);
+    return rc;
+  }
+  d.raw0 = static_cast<const double*>(s->raw0);
+  d.soa64 = static_cast<const double*>(s->soa64);
+  cudaError_t ce = rlb::launch_custom_repack(d.raw0, n, dims, d.npad, static_cast<double*>(s->soa64), c->stream,
+                                             &c->launches_i);
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);
+  account(c);
+  if (ce != cudaSuccess) {
+    rlb_scorer_destroy(s);
+    return fail(RLB_E_CUDA, "custom repack: %s", cudaGetErrorString(ce));
+  }
+  *out = s;
+  return RLB_OK;
+}
+
 int rlb_scorer_destroy(rlb_scorer* s) {
   if (!s) return RLB_OK;
   if (s->ctx) {
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
   }
-  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32, s->tc_tiles};
+  rlb::custom_unload(s->custom);
+  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32, s->tc_tiles, s->custom_err};
   for (void* p : ptrs) {
     if (!p) continue;
     if (s->ctx) pool_release(s->ctx, p);
@@ -680,7 +782,7 @@ int rlb_scorer_num_data(const rlb_scorer* s, int type) {
   if (!s || type < 0 || type >= s->d.num_types) return RLB_E_ARG;
   return s->d.n[type];
 }
-int rlb_scorer_model_size(const rlb_scorer* s) { return s ? rlb::model_size_of(s->d.kind) : RLB_E_ARG; }
+int rlb_scorer_model_size(const rlb_scorer* s) { return s ? rlb::model_size_of(s->d) : RLB_E_ARG; }
 
 int rlb_scorer_get_rays(const rlb_scorer* s, double* rays) {
   int rc = check_scorer(s);
@@ -720,7 +822,7 @@ int rlb_score_models(rlb_scorer* s, int precision, int k, const double* models,
   if (!models) return fail(RLB_E_ARG, "null models");
   rc = ensure_first_use(c);
   if (rc) return rc;
-  const int md = rlb::model_size_of(s->d.kind);
+  const int md = rlb::model_size_of(s->d);
   RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
   RLB_CUDA(c->scores.ensure(static_cast<size_t>(k) * sizeof(double)));
   RLB_CUDA(c->counts.ensure(static_cast<size_t>(k) * sizeof(int32_t)));
@@ -771,7 +873,7 @@ int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl
   if (rc) return rc;
   if (!model) return fail(RLB_E_ARG, "null model");
   const DeviceData& d = s->d;
-  const int md = rlb::model_size_of(d.kind);
+  const int md = rlb::model_size_of(d);
   const int ntot = d.n[0] + (d.num_types > 1 ? d.n[1] : 0);
   constexpr int kZeroCopyMax = 65536;  // points; above this the list is fetched by DMA
   InlierHeader* h = nullptr;
@@ -830,14 +932,23 @@ int rlb_eval_errors(rlb_scorer* s, int precision, const double* model, int type,
   const DeviceData& d = s->d;
   if (!model || !err) return fail(RLB_E_ARG, "null pointer");
   if (type < 0 || type >= d.num_types) return fail(RLB_E_ARG, "bad data type %d", type);
-  const int md = rlb::model_size_of(d.kind);
+  const int md = rlb::model_size_of(d);
   const int n = d.n[type];
   if (n == 0) return RLB_OK;
   RLB_CUDA(c->one_model.ensure(12 * sizeof(double)));
   RLB_CUDA(c->scores.ensure(static_cast<size_t>(n) * sizeof(double)));
   RLB_CUDA(cudaMemcpyAsync(c->one_model.p, model, md * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  RLB_CUDA(rlb::launch_eval_errors(d, precision, c->one_model.as<double>(), type,
-                                   c->scores.as<double>(), c->stream, &c->launches_i));
+  if (d.kind == RLB_KIND_CUSTOM) {
+    std::string cerr;
+    if (!rlb::launch_custom_errors(s->custom, d, c->one_model.as<double>(), static_cast<double*>(s->custom_err),
+                                   c->stream, &c->launches_i, &cerr))
+      return fail(RLB_E_CUDA, "custom errors: %s", cerr.c_str());
+    RLB_CUDA(cudaMemcpyAsync(c->scores.p, s->custom_err, static_cast<size_t>(n) * sizeof(double),
+                             cudaMemcpyDeviceToDevice, c->stream));
+  } else {
+    RLB_CUDA(rlb::launch_eval_errors(d, precision, c->one_model.as<double>(), type,
+                                     c->scores.as<double>(), c->stream, &c->launches_i));
+  }
   account(c);
   RLB_CUDA(cudaMemcpyAsync(err, c->scores.p, static_cast<size_t>(n) * sizeof(double),
                            cudaMemcpyDeviceToHost, c->stream));
@@ -857,7 +968,7 @@ static int solve_host(rlb_scorer* s, int solver, int k, const int32_t* samples, 
   rc = check_samples(s->d, solver, k, samples);
   if (rc) return rc;
   const int ss = solver_sample_size(s->d, solver);
-  const int md = rlb::model_size_of(s->d.kind);
+  const int md = rlb::model_size_of(s->d);
   RLB_CUDA(c->samples.ensure(static_cast<size_t>(k) * ss * sizeof(int32_t)));
   RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
   RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));
@@ -953,7 +1064,7 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
   rc = ensure_first_use(c);
   if (rc) return rc;
   const int ss = solver_sample_size(s->d, solver);
-  const int md = rlb::model_size_of(s->d.kind);
+  const int md = rlb::model_size_of(s->d);
   RLB_CUDA(c->samples.ensure(static_cast<size_t>(k) * ss * sizeof(int32_t)));
   RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
   RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));

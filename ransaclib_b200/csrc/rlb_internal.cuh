@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <string>
+
 #include "../../include/ransaclib_b200.h"
 
 namespace rlb {
@@ -36,6 +38,7 @@ struct DeviceData {
   const double* raw0;       // line: xy (n0 x 2); pose: points2D (n x 2)
   const double* raw1;       // hybrid: xynn (n1 x 4); pose: points3D (n x 3)
   const double* rays;       // pose: n x 3 unit bearings
+  int model_doubles;        // RLB_KIND_CUSTOM: doubles per model (the built-in kinds: see model_size_of)
 };
 
 struct SweepArgs {
@@ -145,6 +148,21 @@ int localize_warps_per_cta();
 int localize_ctas_per_sm();
 
 inline int model_size_of(int kind) { return kind == RLB_KIND_POSE ? 12 : 3; }
+inline int model_size_of(const DeviceData& d) {
+  return d.kind == RLB_KIND_CUSTOM ? d.model_doubles : model_size_of(d.kind);
+}
+
+// user-defined functors (custom_functor.cu)
+struct CustomModule;
+bool custom_compile(const char* src, int dims, int md, std::string* cubin, std::string* err);
+CustomModule* custom_load(const std::string& cubin, int dims, int md, std::string* err);
+void custom_unload(CustomModule* m);
+cudaError_t launch_custom_repack(const double* raw, int n, int dims, int npad, double* soa, cudaStream_t st,
+                                 int* launches);
+bool launch_custom_sweep(const CustomModule* m, const DeviceData& d, const SweepArgs& a, int pts_per_split,
+                         cudaStream_t st, int* launches, std::string* err);
+bool launch_custom_errors(const CustomModule* m, const DeviceData& d, const double* d_model, double* d_err,
+                          cudaStream_t st, int* launches, std::string* err);
 
 }  // namespace rlb
 

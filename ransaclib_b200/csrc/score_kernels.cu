@@ -101,6 +101,18 @@ struct LineF {
   }
 };
 
+// RLB_KIND_CUSTOM: the user's functor has already been evaluated (custom_functor.cu); the "point" is its
+// squared residual, so the ordered compaction of inlier_kernel is shared with the built-in kinds.
+template <typename T>
+struct ErrF {
+  static constexpr int C = 1;
+  static constexpr int MD = 1;
+  struct Model {};
+  __device__ static void load(const double*, const DeviceData&, Model&) {}
+  __device__ static void zero(Model&) {}
+  __device__ __forceinline__ static T eval(const Model&, const T* p) { return p[0]; }
+};
+
 template <typename T>
 struct PoseF {
   static constexpr int C = 5;
@@ -644,7 +656,7 @@ __global__ void __launch_bounds__(256)
                     unsigned int* __restrict__ ticket, BestRec* __restrict__ best,
                     double* __restrict__ best_model) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  const int md = (d.kind == RLB_KIND_POSE) ? 12 : 3;
+  const int md = (d.kind == RLB_KIND_POSE) ? 12 : (d.kind == RLB_KIND_CUSTOM ? d.model_doubles : 3);
   double s = DBL_MAX;
   long long id = LLONG_MAX;
   if (k < a.k) {
@@ -987,6 +999,8 @@ cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_
   const int tiles = d.npad / kInlTile;
   if (d.kind == RLB_KIND_POSE) {
     inlier_kernel<PoseF><<<tiles, kInlThreads, 0, st>>>(d, a);
+  } else if (d.kind == RLB_KIND_CUSTOM) {
+    inlier_kernel<ErrF><<<tiles, kInlThreads, 0, st>>>(d, a);  // d.soa64 = the error array, one channel
   } else {
     inlier_kernel<LineF><<<tiles, kInlThreads, 0, st>>>(d, a);
   }
