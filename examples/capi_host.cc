@@ -13,6 +13,7 @@
 #include <RansacLib/hybrid_ransac.h>
 #include <RansacLib/ransac.h>
 
+#include "circle_estimator.h"
 #include "calibrated_absolute_pose_estimator.h"
 #include "hybrid_line_estimator.h"
 #include "line_estimator.h"
@@ -192,6 +193,16 @@ int rlbh_lomsac_line(const rlbh_options* o, int device, int precision, int n, co
     LineEstimator solver(n, xy, &gpu::Context::ThreadDefault(device));
     Run<Line2D, Lines2D, LineEstimator>(*o, solver, precision, reinterpret_cast<Line2D*>(model), st,
                                         inliers);
+  });
+}
+
+// A user-defined solver (examples/circle_estimator.h): host minimal solver, NVRTC-compiled residual.
+int rlbh_lomsac_circle(const rlbh_options* o, int device, int n, const double* xy, double* model,
+                       rlbh_stats* st, int32_t* inliers) {
+  return Guard([&] {
+    CircleEstimator solver(n, xy, &gpu::Context::ThreadDefault(device));
+    Run<Circle2D, Circles2D, CircleEstimator>(*o, solver, RLB_F64, reinterpret_cast<Circle2D*>(model), st,
+                                              inliers);
   });
 }
 

@@ -456,6 +456,13 @@ void RLO(lomsac_line)(const rlo_options* o, int n, const double* xy, double* mod
   run_lomsac<Line, Lines, LineSolver>(*o, s, reinterpret_cast<Line*>(model), st, inliers);
 }
 
+// ---- circle: a user-defined solver through the same LO-MSAC (user-functor parity test) ----------
+void RLO(lomsac_circle)(const rlo_options* o, int n, const double* xy, double* model,
+                        rlo_stats* st, int32_t* inliers) {
+  CircleSolver s(n, xy);
+  run_lomsac<Circle, Circles, CircleSolver>(*o, s, reinterpret_cast<Circle*>(model), st, inliers);
+}
+
 // ---- hybrid line ---------------------------------------------------------------
 void RLO(hybrid_line_score_models)(int n0, const double* xy0, int n1, const double* p1,
                                    int k, const double* models, const double* thr,

@@ -82,6 +82,93 @@ inline bool sym2_largest_eigvec(double a, double b, double d, double* ex,
 }
 
 // ----------------------------------------------------------------------------
+// A solver that is NOT one of the reference's examples: a 2-D circle (cx, cy, r) written against the
+// solver concept of the reference's README.md:105-154. It exists to drive the reference's unmodified
+// ransac.h with a user-defined residual, as the CPU side of the user-defined-functor parity test
+// (examples/circle_estimator.h is the device-backed counterpart; the arithmetic below is written out
+// independently, in the same order of operations).
+struct Circle {
+  double v[3];
+};
+typedef std::vector<Circle> Circles;
+
+class CircleSolver {
+ public:
+  CircleSolver(int n, const double* xy) : n_(n), xy_(xy) {}
+  inline int min_sample_size() const { return 3; }
+  inline int non_minimal_sample_size() const { return 6; }
+  inline int num_data() const { return n_; }
+
+  // circumscribed circle of three points (perpendicular-bisector intersection)
+  int MinimalSolver(const std::vector<int>& sample, Circles* out) const {
+    out->clear();
+    if (sample.size() < 3u) return 0;
+    const double x1 = X(sample[0]), y1 = Y(sample[0]);
+    const double x2 = X(sample[1]), y2 = Y(sample[1]);
+    const double x3 = X(sample[2]), y3 = Y(sample[2]);
+    const double a = x2 - x1, b = y2 - y1, c = x3 - x1, d = y3 - y1;
+    const double e = a * (x1 + x2) + b * (y1 + y2);
+    const double f = c * (x1 + x3) + d * (y1 + y3);
+    const double g = 2.0 * (a * (y3 - y2) - b * (x3 - x2));
+    if (g == 0.0) return 0;
+    Circle m;
+    m.v[0] = (d * e - b * f) / g;
+    m.v[1] = (a * f - c * e) / g;
+    const double dx = x1 - m.v[0], dy = y1 - m.v[1];
+    m.v[2] = std::sqrt(dx * dx + dy * dy);
+    out->push_back(m);
+    return 1;
+  }
+
+  // algebraic (Kasa) fit: minimise sum (x^2 + y^2 + A x + B y + C)^2, 3x3 normal equations by Cramer
+  int NonMinimalSolver(const std::vector<int>& sample, Circle* out) const {
+    if (sample.size() < 6u) return 0;
+    double sx = 0, sy = 0, sxx = 0, syy = 0, sxy = 0, sxz = 0, syz = 0, sz = 0;
+    const double cnt = static_cast<double>(sample.size());
+    for (size_t i = 0; i < sample.size(); ++i) {
+      const double x = X(sample[i]), y = Y(sample[i]);
+      const double z = x * x + y * y;
+      sx += x;
+      sy += y;
+      sxx += x * x;
+      syy += y * y;
+      sxy += x * y;
+      sxz += x * z;
+      syz += y * z;
+      sz += z;
+    }
+    // [sxx sxy sx; sxy syy sy; sx sy n] [A B C]' = -[sxz syz sz]'
+    const double det = sxx * (syy * cnt - sy * sy) - sxy * (sxy * cnt - sy * sx) + sx * (sxy * sy - syy * sx);
+    if (det == 0.0 || !(det == det)) return 0;
+    const double r0 = -sxz, r1 = -syz, r2 = -sz;
+    const double A = (r0 * (syy * cnt - sy * sy) - sxy * (r1 * cnt - sy * r2) + sx * (r1 * sy - syy * r2)) / det;
+    const double B = (sxx * (r1 * cnt - r2 * sy) - r0 * (sxy * cnt - sy * sx) + sx * (sxy * r2 - r1 * sx)) / det;
+    const double Cc = (sxx * (syy * r2 - sy * r1) - sxy * (sxy * r2 - r1 * sx) + r0 * (sxy * sy - syy * sx)) / det;
+    const double cx = -0.5 * A, cy = -0.5 * B;
+    const double rr = cx * cx + cy * cy - Cc;
+    if (!(rr > 0.0)) return 0;
+    out->v[0] = cx;
+    out->v[1] = cy;
+    out->v[2] = std::sqrt(rr);
+    return 1;
+  }
+
+  double EvaluateModelOnPoint(const Circle& m, int i) const {
+    const double dx = X(i) - m.v[0], dy = Y(i) - m.v[1];
+    const double d = std::sqrt(dx * dx + dy * dy) - m.v[2];
+    return d * d;
+  }
+
+  inline void LeastSquares(const std::vector<int>& sample, Circle* m) const { NonMinimalSolver(sample, m); }
+
+ private:
+  double X(int i) const { return xy_[2 * static_cast<size_t>(i)]; }
+  double Y(int i) const { return xy_[2 * static_cast<size_t>(i) + 1]; }
+  int n_;
+  const double* xy_;
+};
+
+// ----------------------------------------------------------------------------
 // examples/line_estimator.{h,cc}
 class LineSolver {
  public:

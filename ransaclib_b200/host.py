@@ -143,6 +143,18 @@ def estimate_line(options: LORansacOptions, xy, device=0, precision=-1):
     return model, _stats_dict(st, inl)
 
 
+def estimate_circle(options: LORansacOptions, xy, device=0):
+    """LocallyOptimizedMSAC<Circle2D, ., CircleEstimator>::EstimateModel -> ((cx, cy, r), stats): a solver with a
+    user-defined residual (examples/circle_estimator.h), host minimal solver, f64 sweeps."""
+    xy = _capi.f64a(xy, (-1, 2))
+    o, st = options._c(), _Stats()
+    model = np.zeros(3)
+    inl = np.zeros(max(len(xy), 1), np.int32)
+    _check(_load().rlbh_lomsac_circle(C.byref(o), device, len(xy), _capi.ptr(xy), _capi.ptr(model), C.byref(st),
+                                      _capi.ptr(inl)))
+    return model, _stats_dict(st, inl)
+
+
 def estimate_pose(options: LORansacOptions, fx, fy, points2D, points3D, device=0, precision=-1):
     """LocallyOptimizedMSAC<CameraPose, ., CalibratedAbsolutePoseEstimator>::EstimateModel."""
     p2 = _capi.f64a(points2D, (-1, 2))

@@ -99,6 +99,7 @@ def _bind(lib, prefix):
     ns.line_minimal_batch = fn("line_minimal_batch", None, [C.c_int, f64p, C.c_int, i32p, f64p, u8p])
     ns.line_least_squares = fn("line_least_squares", None, [C.c_int, f64p, C.c_int, i32p, f64p, C.POINTER(C.c_int32)])
     ns.lomsac_line = fn("lomsac_line", None, [C.POINTER(Options), C.c_int, f64p, f64p, C.POINTER(Stats), i32p])
+    ns.lomsac_circle = fn("lomsac_circle", None, [C.POINTER(Options), C.c_int, f64p, f64p, C.POINTER(Stats), i32p])
     ns.hybrid_line_score_models = fn("hybrid_line_score_models", None,
                                      [C.c_int, f64p, C.c_int, f64p, C.c_int, f64p, f64p, f64p, f64p, i32p])
     ns.hybrid_line_inliers = fn("hybrid_line_inliers", C.c_int,

@@ -66,6 +66,35 @@ def test_line_estimation_config(outlier_ratio, seed):
     check_same(st32, m32, ost, om, oinl)
 
 
+def circle_instance(seed, n, outlier_ratio):
+    rng = np.random.default_rng(seed)
+    ang = rng.uniform(0, 2 * np.pi, n)
+    pts = np.stack([1.5 + 2.0 * np.cos(ang), -0.5 + 2.0 * np.sin(ang)], 1) + rng.normal(0, 0.01, (n, 2))
+    out = rng.random(n) < outlier_ratio
+    pts[out] = rng.uniform(-3, 4, (int(out.sum()), 2))
+    return np.ascontiguousarray(pts)
+
+
+@pytest.mark.parametrize("n,outlier_ratio,seed,final_lsq", [(3000, 0.3, 42, 0), (20000, 0.6, 7, 1), (500, 0.8, 3, 0)])
+def test_user_defined_solver_circle(n, outlier_ratio, seed, final_lsq):
+    """a solver that is not one of the reference's examples (examples/circle_estimator.h:
+    host MinimalSolver / Kasa fit, NVRTC-compiled residual) through the drop-in LocallyOptimizedMSAC, against the
+    same solver driven by the sequential oracle (== the reference's unmodified ransac.h, test_oracle_golden.py)."""
+    H = host()
+    O = ol.oracle()
+    xy = circle_instance(seed, n, outlier_ratio)
+    kw = dict(sq_thr=0.03 ** 2, seed=seed, final_lsq=final_lsq, min_iters=100, max_iters=5000)
+    o, ost = ol.Options.default(**kw), ol.Stats()
+    om, oinl = np.zeros(3), np.zeros(n, np.int32)
+    O.lomsac_circle(C.byref(o), n, ol.c64(xy), om, C.byref(ost), oinl)
+    opts = H.LORansacOptions(squared_inlier_threshold_=0.03 ** 2, random_seed_=seed,
+                             final_least_squares_=bool(final_lsq), min_num_iterations_=100, max_num_iterations_=5000)
+    m, st = H.estimate_circle(opts, xy)
+    check_same(st, m, ost, om, oinl[:ost.best_num_inliers])
+    assert st["best_num_inliers"] > 0.8 * (1 - outlier_ratio) * n
+    np.testing.assert_allclose(m, [1.5, -0.5, 2.0], atol=0.02)
+
+
 @pytest.mark.parametrize("seed,final_lsq,lo_steps", [(42, 0, 10), (5, 1, 10), (9, 0, 0)])
 def test_camera_pose_estimation_config(seed, final_lsq, lo_steps):
     """BASELINE configs[1] shape: N = 10k matches, 50 % outliers, thr = 12 px, adaptive stop."""

@@ -209,3 +209,27 @@ def test_reference_build_agrees_when_present(G, O):
         res.append((st.num_iterations, st.best_num_inliers, st.best_model_score, model.tolist(),
                     inl[:st.best_num_inliers].tolist()))
     assert res[0] == res[1]
+
+
+def test_user_defined_solver_oracle_equals_reference_headers(O):
+    """The circle solver (not a reference example) through the restated LO-MSAC == through the reference's own
+    unmodified ransac.h; this is the CPU side of tests/test_gpu_end_to_end.py::test_user_defined_solver_circle."""
+    ref = ol.reference()
+    if ref is None:
+        pytest.skip("oracle/_ref not built here")
+    rng = np.random.default_rng(12)
+    n = 4000
+    ang = rng.uniform(0, 2 * np.pi, n)
+    xy = np.stack([1.5 + 2.0 * np.cos(ang), -0.5 + 2.0 * np.sin(ang)], 1) + rng.normal(0, 0.01, (n, 2))
+    xy[::3] = rng.uniform(-3, 4, (len(xy[::3]), 2))
+    xy = np.ascontiguousarray(xy)
+    for seed, final_lsq in ((1, 0), (2, 1)):
+        o = ol.Options.default(sq_thr=0.03 ** 2, seed=seed, final_lsq=final_lsq, min_iters=100, max_iters=5000)
+        res = []
+        for lib in (O, ref):
+            st, model, inl = ol.Stats(), np.zeros(3), np.zeros(n, np.int32)
+            lib.lomsac_circle(C.byref(o), n, xy, model, C.byref(st), inl)
+            res.append((st.num_iterations, st.number_lo_iterations, st.best_num_inliers, st.best_model_score,
+                        model.tolist(), inl[:st.best_num_inliers].tolist()))
+        assert res[0] == res[1]
+        assert res[0][2] > 2000 and abs(res[0][4][2] - 2.0) < 0.02
