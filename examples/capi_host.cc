@@ -169,6 +169,52 @@ void PoseToQvecTvec(const double* m /* column-major 3x4 */, double* qvec, double
   qvec[3] = z;
 }
 
+// What the samplers ask of a solver, and nothing else.
+struct SizesOnly {
+  std::vector<int> n;
+  std::vector<std::vector<double>> weights;
+  int sample_size;
+  int num_data() const { return n[0]; }
+  int min_sample_size() const { return sample_size; }
+  void num_data(std::vector<int>* out) const { *out = n; }
+  void get_weights(std::vector<std::vector<double>>& w) const { w = weights; }
+};
+
+template <class Sampler>
+void RunHybrid(const rlbh_hybrid_options& o, HybridLineEstimator& solver, int precision, double* model,
+               rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
+  if (precision >= 0) solver.device_scorer().set_precision(precision);
+  HybridLORansacOptions ho;
+  ho.min_num_iterations_ = o.min_iters;
+  ho.max_num_iterations_ = o.max_iters;
+  ho.max_num_iterations_per_solver_ = o.max_iters_per_solver;
+  ho.success_probability_ = o.success_prob;
+  ho.squared_inlier_thresholds_ = {o.sq_thr[0], o.sq_thr[1]};
+  ho.data_type_weights_ = {o.weights[0], o.weights[1]};
+  ho.random_seed_ = o.seed;
+  ho.num_lo_steps_ = o.lo_steps;
+  ho.threshold_multiplier_ = o.thr_mult;
+  ho.num_lsq_iterations_ = o.lsq_iters;
+  ho.min_sample_multiplicator_ = o.min_sample_mult;
+  ho.lo_starting_iterations_ = o.lo_start;
+  ho.final_least_squares_ = o.final_lsq != 0;
+  HybridLocallyOptimizedMSAC<Line2D, Lines2D, HybridLineEstimator, Sampler> lomsac;
+  HybridRansacStatistics hs;
+  lomsac.EstimateModel(ho, solver, reinterpret_cast<Line2D*>(model), &hs);
+  st->num_iterations_total = hs.num_iterations_total;
+  for (int i = 0; i < 2; ++i) {
+    st->num_iterations_per_solver[i] = hs.num_iterations_per_solver[i];
+    st->inlier_ratios[i] = hs.inlier_ratios[i];
+    st->num_inliers_per_type[i] = static_cast<int32_t>(hs.inlier_indices[i].size());
+  }
+  st->best_num_inliers = hs.best_num_inliers;
+  st->best_solver_type = hs.best_solver_type;
+  st->best_model_score = hs.best_model_score;
+  st->number_lo_iterations = hs.number_lo_iterations;
+  if (inl0) std::copy(hs.inlier_indices[0].begin(), hs.inlier_indices[0].end(), inl0);
+  if (inl1) std::copy(hs.inlier_indices[1].begin(), hs.inlier_indices[1].end(), inl1);
+}
+
 template <class F>
 int Guard(F f) {
   try {
@@ -223,36 +269,70 @@ int rlbh_hybrid_lomsac_line(const rlbh_hybrid_options* o, int device, int precis
   return Guard([&] {
     HybridLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]},
                                &gpu::Context::ThreadDefault(device));
-    if (precision >= 0) solver.device_scorer().set_precision(precision);
-    HybridLORansacOptions ho;
-    ho.min_num_iterations_ = o->min_iters;
-    ho.max_num_iterations_ = o->max_iters;
-    ho.max_num_iterations_per_solver_ = o->max_iters_per_solver;
-    ho.success_probability_ = o->success_prob;
-    ho.squared_inlier_thresholds_ = {o->sq_thr[0], o->sq_thr[1]};
-    ho.data_type_weights_ = {o->weights[0], o->weights[1]};
-    ho.random_seed_ = o->seed;
-    ho.num_lo_steps_ = o->lo_steps;
-    ho.threshold_multiplier_ = o->thr_mult;
-    ho.num_lsq_iterations_ = o->lsq_iters;
-    ho.min_sample_multiplicator_ = o->min_sample_mult;
-    ho.lo_starting_iterations_ = o->lo_start;
-    ho.final_least_squares_ = o->final_lsq != 0;
-    HybridLocallyOptimizedMSAC<Line2D, Lines2D, HybridLineEstimator> lomsac;
-    HybridRansacStatistics hs;
-    lomsac.EstimateModel(ho, solver, reinterpret_cast<Line2D*>(model), &hs);
-    st->num_iterations_total = hs.num_iterations_total;
-    for (int i = 0; i < 2; ++i) {
-      st->num_iterations_per_solver[i] = hs.num_iterations_per_solver[i];
-      st->inlier_ratios[i] = hs.inlier_ratios[i];
-      st->num_inliers_per_type[i] = static_cast<int32_t>(hs.inlier_indices[i].size());
+    RunHybrid<HybridUniformSampling<HybridLineEstimator>>(*o, solver, precision, model, st, inl0, inl1);
+  });
+}
+
+// Same with the reference's weighted sampler (hybrid_sampling.h:146-223): w0 / w1 are the per-point
+// sampling weights of the two data types (<= 0: never sampled, still scored).
+int rlbh_hybrid_lomsac_line_biased(const rlbh_hybrid_options* o, int device, int precision, int n0,
+                                   const double* xy0, const double* w0, int n1, const double* xynn1,
+                                   const double* w1, const double* priors, double* model,
+                                   rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
+  return Guard([&] {
+    HybridLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]},
+                               &gpu::Context::ThreadDefault(device));
+    solver.set_weights(std::vector<double>(w0, w0 + n0), std::vector<double>(w1, w1 + n1));
+    RunHybrid<HybridBiasedSampling<HybridLineEstimator>>(*o, solver, precision, model, st, inl0, inl1);
+  });
+}
+
+// ---- the samplers of the template layer on their own (host only; no device is touched) ----------
+// k samples of size s from n data (include/RansacLib/sampling.h) -> out[k][s].
+int rlbh_sample_uniform(uint32_t seed, int n, int s, int k, int32_t* out) {
+  return Guard([&] {
+    SizesOnly solver{{n}, {}, s};
+    UniformSampling<SizesOnly> sampler(seed, solver);
+    std::vector<int> one;
+    for (int i = 0; i < k; ++i) {
+      sampler.Sample(&one);
+      std::copy(one.begin(), one.end(), out + static_cast<size_t>(i) * s);
     }
-    st->best_num_inliers = hs.best_num_inliers;
-    st->best_solver_type = hs.best_solver_type;
-    st->best_model_score = hs.best_model_score;
-    st->number_lo_iterations = hs.number_lo_iterations;
-    if (inl0) std::copy(hs.inlier_indices[0].begin(), hs.inlier_indices[0].end(), inl0);
-    if (inl1) std::copy(hs.inlier_indices[1].begin(), hs.inlier_indices[1].end(), inl1);
+  });
+}
+
+// k hybrid samples over T data types; sizes[k][T] per draw; weights == NULL: HybridUniformSampling,
+// else HybridBiasedSampling with the concatenated per-type weights. out[k][T][max_size], -1 padded.
+int rlbh_sample_hybrid(uint32_t seed, int T, const int32_t* num_data, const double* weights, int k,
+                       const int32_t* sizes, int max_size, int32_t* out) {
+  return Guard([&] {
+    SizesOnly solver{std::vector<int>(num_data, num_data + T), {}, 0};
+    if (weights) {
+      const double* w = weights;
+      for (int t = 0; t < T; ++t) {
+        solver.weights.emplace_back(w, w + num_data[t]);
+        w += num_data[t];
+      }
+    }
+    std::vector<std::vector<int>> one;
+    auto draw = [&](auto& sampler) {
+      for (int i = 0; i < k; ++i) {
+        std::vector<int> sz(sizes + static_cast<size_t>(i) * T, sizes + static_cast<size_t>(i + 1) * T);
+        sampler.Sample(sz, &one);
+        for (int t = 0; t < T; ++t) {
+          int32_t* row = out + (static_cast<size_t>(i) * T + t) * max_size;
+          std::fill(row, row + max_size, -1);
+          std::copy(one[t].begin(), one[t].end(), row);
+        }
+      }
+    };
+    if (weights) {
+      HybridBiasedSampling<SizesOnly> sampler(seed, solver);
+      draw(sampler);
+    } else {
+      HybridUniformSampling<SizesOnly> sampler(seed, solver);
+      draw(sampler);
+    }
   });
 }
 

@@ -43,6 +43,21 @@ class HybridLineEstimator {
   }
   inline void solver_probabilities(std::vector<double>* p) const { *p = prior_probabilities_; }
 
+  // Optional per-point sampling weights for HybridBiasedSampling (reference
+  // hybrid_sampling.h:146-160 reads them through get_weights); default: all ones.
+  void set_weights(const std::vector<double>& w0, const std::vector<double>& w1) {
+    weights_ = {w0, w1};
+  }
+  void get_weights(std::vector<std::vector<double>>& weights) const {
+    if (!weights_.empty()) {
+      weights = weights_;
+      return;
+    }
+    weights.assign(2, std::vector<double>());
+    weights[0].assign(static_cast<size_t>(num_points_), 1.0);
+    weights[1].assign(static_cast<size_t>(num_points_with_normals_), 1.0);
+  }
+
   inline int MinimalSolver(const std::vector<std::vector<int>>& sample, const int solver_idx,
                            Lines2D* lines) const {
     lines->clear();
@@ -123,6 +138,7 @@ class HybridLineEstimator {
   std::vector<double> points_with_normals_;
   int num_points_with_normals_;
   std::vector<double> prior_probabilities_;
+  std::vector<std::vector<double>> weights_;
   gpu::DeviceScorer scorer_;
 };
 

@@ -1,7 +1,7 @@
 // ransaclib_b200 — drop-in for RansacLib/hybrid_sampling.h: per-data-type uniform
 // sampling with one shared private RNG (reference hybrid_sampling.h:47-140).
-// HybridBiasedSampling (hybrid_sampling.h:146-223) is not provided: no example uses
-// it and it needs a solver.get_weights() that is outside the documented concept.
+// HybridBiasedSampling (hybrid_sampling.h:146-223): per-point weights from
+// solver.get_weights(), zero-weight points never drawn.
 #ifndef RANSACLIB_B200_RANSACLIB_HYBRID_SAMPLING_H_
 #define RANSACLIB_B200_RANSACLIB_HYBRID_SAMPLING_H_
 
@@ -64,6 +64,65 @@ class HybridUniformSampling {
   std::mt19937 rng_;
   std::vector<std::uniform_int_distribution<int>> index_;
   std::vector<int> num_data_;
+};
+
+// Weighted sampling (reference hybrid_sampling.h:146-223). The solver additionally provides
+//     void get_weights(std::vector<std::vector<double>>& weights) const;   // one weight per datum and type
+// Points with weight <= 0 are never drawn; the others are drawn with probability proportional
+// to their weight (std::discrete_distribution over the shared mt19937, so the stream of
+// samples for a given seed is the reference's), without repetition inside one sample.
+template <class Solver>
+class HybridBiasedSampling {
+ public:
+  HybridBiasedSampling(const unsigned int random_seed, const Solver& solver) {
+    std::vector<std::vector<double>> w;
+    solver.get_weights(w);
+    rng_.seed(random_seed);
+    const size_t T = w.size();
+    candidates_.resize(T);
+    pick_.resize(T);
+    for (size_t t = 0; t < T; ++t) {
+      std::vector<double> positive;
+      positive.reserve(w[t].size());
+      candidates_[t].reserve(w[t].size());
+      for (size_t j = 0; j < w[t].size(); ++j) {
+        if (!(w[t][j] > 0.0)) continue;
+        positive.push_back(w[t][j]);
+        candidates_[t].push_back(static_cast<int>(j));
+      }
+      pick_[t] = std::discrete_distribution<int>(positive.begin(), positive.end());
+    }
+  }
+
+  void Sample(const std::vector<int>& num_samples_per_data_type,
+              std::vector<std::vector<int>>* random_sample) {
+    const size_t T = candidates_.size();
+    random_sample->resize(T);
+    for (size_t t = 0; t < T; ++t) {
+      std::vector<int>& s = (*random_sample)[t];
+      s.clear();
+      const int want = num_samples_per_data_type[t];
+      if (want <= 0) continue;
+      if (want == static_cast<int>(candidates_[t].size())) {  // every candidate, no draw (:189-191)
+        s = candidates_[t];
+        continue;
+      }
+      s.resize(want);
+      for (int i = 0; i < want; ++i) {
+        bool again = true;
+        while (again) {
+          s[i] = candidates_[t][pick_[t](rng_)];
+          again = false;
+          for (int j = 0; j < i && !again; ++j) again = (s[j] == s[i]);
+        }
+      }
+    }
+  }
+
+ protected:
+  std::mt19937 rng_;
+  std::vector<std::discrete_distribution<int>> pick_;
+  std::vector<std::vector<int>> candidates_;
 };
 
 }  // namespace ransac_lib

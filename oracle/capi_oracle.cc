@@ -173,7 +173,9 @@ struct SizeOnly {
 };
 struct HybridSizeOnly {
   std::vector<int> n;
+  std::vector<std::vector<double>> w;
   void num_data(std::vector<int>* nd) const { *nd = n; }
+  void get_weights(std::vector<std::vector<double>>& out) const { out = w; }
 };
 
 // Generic single-type batch scoring through the scoring loops under test.
@@ -267,6 +269,32 @@ void RLO(sample_hybrid)(uint32_t seed, int T, const int32_t* nd, int k,
   ransac_lib::HybridUniformSampling<HybridSizeOnly> smp(seed, so);
 #else
   HybridUniformSampler smp(seed, ndv);
+#endif
+  std::vector<std::vector<int>> v;
+  for (int i = 0; i < k; ++i) {
+    std::vector<int> sz(sizes + i * T, sizes + (i + 1) * T);
+    smp.Sample(sz, &v);
+    int p = 0;
+    for (int t = 0; t < T; ++t)
+      for (size_t j = 0; j < v[t].size(); ++j) out[i * stride + p++] = v[t][j];
+    for (; p < stride; ++p) out[i * stride + p] = -1;
+  }
+}
+
+// Weighted hybrid sampler (hybrid_sampling.h:146-223); weights = the T per-type weight arrays
+// concatenated; same output layout as sample_hybrid.
+void RLO(sample_hybrid_biased)(uint32_t seed, int T, const int32_t* nd, const double* weights,
+                               int k, const int32_t* sizes, int stride, int32_t* out) {
+  std::vector<std::vector<double>> w(T);
+  for (int t = 0; t < T; ++t) {
+    w[t].assign(weights, weights + nd[t]);
+    weights += nd[t];
+  }
+#ifdef RLO_USE_REFERENCE
+  HybridSizeOnly so{std::vector<int>(nd, nd + T), w};
+  ransac_lib::HybridBiasedSampling<HybridSizeOnly> smp(seed, so);
+#else
+  HybridBiasedSampler smp(seed, w);
 #endif
   std::vector<std::vector<int>> v;
   for (int i = 0; i < k; ++i) {
@@ -523,30 +551,20 @@ void RLO(point_normal_batch)(int n1, const double* p1, int k, const int32_t* sam
   (void)n1;
 }
 
-void RLO(hybrid_lomsac_line)(const rlo_hybrid_options* o, int n0, const double* xy0,
-                             int n1, const double* p1, const double* priors,
-                             double* model, rlo_hybrid_stats* st, int32_t* inl0,
-                             int32_t* inl1) {
-  HybridLineSolver s(n0, xy0, n1, p1, {priors[0], priors[1]});
+}  // extern "C"
+
+template <class RefSampler, class OracleSampler>
+static void run_hybrid_line(const rlo_hybrid_options* o, const HybridLineSolver& s, double* model,
+                            rlo_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
   Line* L = reinterpret_cast<Line*>(model);
 #ifdef RLO_USE_REFERENCE
-  ransac_lib::HybridLocallyOptimizedMSAC<Line, Lines, HybridLineSolver> r;
+  ransac_lib::HybridLocallyOptimizedMSAC<Line, Lines, HybridLineSolver, RefSampler> r;
   ransac_lib::HybridRansacStatistics hs;
   r.EstimateModel(to_ref(*o), s, L, &hs);
-  st->num_iterations_total = hs.num_iterations_total;
-  for (int i = 0; i < 2; ++i) {
-    st->num_iterations_per_solver[i] =
-        i < (int)hs.num_iterations_per_solver.size() ? hs.num_iterations_per_solver[i] : 0;
-    st->inlier_ratios[i] = i < (int)hs.inlier_ratios.size() ? hs.inlier_ratios[i] : 0.0;
-  }
-  st->best_num_inliers = hs.best_num_inliers;
-  st->best_solver_type = hs.best_solver_type;
-  st->best_model_score = hs.best_model_score;
-  st->number_lo_iterations = hs.number_lo_iterations;
-  const std::vector<std::vector<int>>& ii = hs.inlier_indices;
 #else
   HybridStats hs;
-  hybrid_lomsac_estimate<Line, Lines, HybridLineSolver>(to_oracle(*o), s, L, &hs);
+  hybrid_lomsac_estimate<Line, Lines, HybridLineSolver, OracleSampler>(to_oracle(*o), s, L, &hs);
+#endif
   st->num_iterations_total = hs.num_iterations_total;
   for (int i = 0; i < 2; ++i) {
     st->num_iterations_per_solver[i] =
@@ -558,13 +576,40 @@ void RLO(hybrid_lomsac_line)(const rlo_hybrid_options* o, int n0, const double* 
   st->best_model_score = hs.best_model_score;
   st->number_lo_iterations = hs.number_lo_iterations;
   const std::vector<std::vector<int>>& ii = hs.inlier_indices;
-#endif
   st->num_inliers_per_type[0] = ii.size() > 0 ? (int)ii[0].size() : 0;
   st->num_inliers_per_type[1] = ii.size() > 1 ? (int)ii[1].size() : 0;
   if (inl0 && ii.size() > 0)
     for (size_t i = 0; i < ii[0].size(); ++i) inl0[i] = ii[0][i];
   if (inl1 && ii.size() > 1)
     for (size_t i = 0; i < ii[1].size(); ++i) inl1[i] = ii[1][i];
+}
+
+#ifdef RLO_USE_REFERENCE
+typedef ransac_lib::HybridUniformSampling<HybridLineSolver> RefUniformS;
+typedef ransac_lib::HybridBiasedSampling<HybridLineSolver> RefBiasedS;
+#else
+typedef void RefUniformS;
+typedef void RefBiasedS;
+#endif
+
+extern "C" {
+
+void RLO(hybrid_lomsac_line)(const rlo_hybrid_options* o, int n0, const double* xy0,
+                             int n1, const double* p1, const double* priors,
+                             double* model, rlo_hybrid_stats* st, int32_t* inl0,
+                             int32_t* inl1) {
+  HybridLineSolver s(n0, xy0, n1, p1, {priors[0], priors[1]});
+  run_hybrid_line<RefUniformS, HybridUniformSampler>(o, s, model, st, inl0, inl1);
+}
+
+// HybridBiasedSampling as the Sampler template argument; w0 / w1: per-point sampling weights.
+void RLO(hybrid_lomsac_line_biased)(const rlo_hybrid_options* o, int n0, const double* xy0,
+                                    const double* w0, int n1, const double* p1, const double* w1,
+                                    const double* priors, double* model, rlo_hybrid_stats* st,
+                                    int32_t* inl0, int32_t* inl1) {
+  HybridLineSolver s(n0, xy0, n1, p1, {priors[0], priors[1]});
+  s.set_weights(std::vector<double>(w0, w0 + n0), std::vector<double>(w1, w1 + n1));
+  run_hybrid_line<RefBiasedS, HybridBiasedSampler>(o, s, model, st, inl0, inl1);
 }
 
 }  // extern "C"

@@ -178,6 +178,55 @@ class HybridUniformSampler {
   std::vector<std::uniform_int_distribution<int>> dist_;
 };
 
+// ---- RansacLib/hybrid_sampling.h:146-223 (HybridBiasedSampling) ----------------
+// Positive-weight points only; std::discrete_distribution on the sampler's own mt19937;
+// duplicates inside one sample re-drawn; "all candidates" short-cut without a draw.
+class HybridBiasedSampler {
+ public:
+  HybridBiasedSampler(unsigned seed, const std::vector<std::vector<double>>& weights) {
+    rng_.seed(seed);
+    ids_.resize(weights.size());
+    dist_.resize(weights.size());
+    for (size_t t = 0; t < weights.size(); ++t) {
+      std::vector<double> kept;
+      for (size_t j = 0; j < weights[t].size(); ++j) {
+        if (weights[t][j] > 0.0) {
+          kept.push_back(weights[t][j]);
+          ids_[t].push_back(static_cast<int>(j));
+        }
+      }
+      std::discrete_distribution<int> d(kept.begin(), kept.end());
+      dist_[t].param(d.param());
+    }
+  }
+  void Sample(const std::vector<int>& sizes, std::vector<std::vector<int>>* out) {
+    out->resize(ids_.size());
+    for (size_t t = 0; t < ids_.size(); ++t) {
+      std::vector<int>& s = (*out)[t];
+      s.clear();
+      if (sizes[t] <= 0) continue;
+      if (sizes[t] == static_cast<int>(ids_[t].size())) {
+        s = ids_[t];
+        continue;
+      }
+      s.resize(sizes[t]);
+      for (int i = 0; i < sizes[t]; ++i) {
+        for (;;) {
+          s[i] = ids_[t][dist_[t](rng_)];
+          bool dup = false;
+          for (int j = 0; j < i; ++j) dup = dup || (s[j] == s[i]);
+          if (!dup) break;
+        }
+      }
+    }
+  }
+
+ private:
+  std::mt19937 rng_;
+  std::vector<std::discrete_distribution<int>> dist_;
+  std::vector<std::vector<int>> ids_;
+};
+
 // ---- the hot path --------------------------------------------------------------
 // ransac.h:306-309. std::min(a,b) == (b < a) ? b : a : NaN errors propagate.
 inline double msac_cost(double err, double thr) { return (thr < err) ? thr : err; }
@@ -556,7 +605,29 @@ inline int hybrid_select_solver(const Solver& s, const std::vector<double>& prio
 }
 
 // hybrid_ransac.h:135-320
-template <class Model, class ModelVector, class Solver>
+// Sampler construction differs per sampler type (the reference's take (seed, solver)).
+template <class Sampler>
+struct MakeHybridSampler;
+template <>
+struct MakeHybridSampler<HybridUniformSampler> {
+  template <class Solver>
+  static HybridUniformSampler make(unsigned seed, const Solver& s) {
+    std::vector<int> nd;
+    s.num_data(&nd);
+    return HybridUniformSampler(seed, nd);
+  }
+};
+template <>
+struct MakeHybridSampler<HybridBiasedSampler> {
+  template <class Solver>
+  static HybridBiasedSampler make(unsigned seed, const Solver& s) {
+    std::vector<std::vector<double>> w;
+    s.get_weights(w);
+    return HybridBiasedSampler(seed, w);
+  }
+};
+
+template <class Model, class ModelVector, class Solver, class Sampler = HybridUniformSampler>
 inline int hybrid_lomsac_estimate(const HybridOptions& o, const Solver& s, Model* best,
                                   HybridStats* st) {
   *st = HybridStats();
@@ -582,7 +653,7 @@ inline int hybrid_lomsac_estimate(const HybridOptions& o, const Solver& s, Model
     for (int i = 0; i < S; ++i) any = any || priors[i] > 0.0;
     if (!any) return 0;
   }
-  HybridUniformSampler sampler(o.seed, nd);
+  Sampler sampler = MakeHybridSampler<Sampler>::make(o.seed, s);
   uint32_t max_it = std::max(o.max_iters, o.min_iters);
   std::vector<uint32_t> max_per(S, std::max(o.max_iters_per_solver, o.min_iters));
   const double kMax = std::numeric_limits<double>::max();

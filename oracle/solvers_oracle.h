@@ -275,6 +275,15 @@ class HybridLineSolver {
   }
   inline void solver_probabilities(std::vector<double>* p) const { *p = priors_; }
 
+  // Per-point sampling weights, the extra concept member HybridBiasedSampling reads
+  // (RansacLib/hybrid_sampling.h:149-152). No reference example provides one.
+  void set_weights(const std::vector<double>& w0, const std::vector<double>& w1) {
+    weights_.clear();
+    weights_.push_back(w0);
+    weights_.push_back(w1);
+  }
+  void get_weights(std::vector<std::vector<double>>& w) const { w = weights_; }
+
   // .h:79-87
   inline int MinimalSolver(const std::vector<std::vector<int>>& sample,
                            const int solver_idx, Lines* lines) const {
@@ -381,6 +390,7 @@ class HybridLineSolver {
   int n1_;
   const double* p1_;
   std::vector<double> priors_;
+  std::vector<std::vector<double>> weights_;
 };
 
 // ----------------------------------------------------------------------------

@@ -167,8 +167,10 @@ def estimate_pose(options: LORansacOptions, fx, fy, points2D, points3D, device=0
     return model, _stats_dict(st, inl)
 
 
-def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, device=0, precision=-1):
-    """HybridLocallyOptimizedMSAC<Line, ., HybridLineEstimator>::EstimateModel."""
+def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, device=0, precision=-1,
+                         sampling_weights=None):
+    """HybridLocallyOptimizedMSAC<Line, ., HybridLineEstimator[, Sampler]>::EstimateModel. sampling_weights =
+    (w0, w1) per-point weights selects HybridBiasedSampling (reference hybrid_sampling.h:146-223) as the Sampler."""
     xy0 = _capi.f64a(xy0, (-1, 2))
     p1 = _capi.f64a(xynn1, (-1, 4))
     pr = _capi.f64a(priors, (2,))
@@ -176,9 +178,17 @@ def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, dev
     model = np.zeros(3)
     a = np.zeros(max(len(xy0), 1), np.int32)
     b = np.zeros(max(len(p1), 1), np.int32)
-    _check(_load().rlbh_hybrid_lomsac_line(C.byref(o), device, precision, len(xy0), _capi.ptr(xy0), len(p1),
-                                           _capi.ptr(p1), _capi.ptr(pr), _capi.ptr(model), C.byref(st),
-                                           _capi.ptr(a), _capi.ptr(b)))
+    if sampling_weights is None:
+        _check(_load().rlbh_hybrid_lomsac_line(C.byref(o), device, precision, len(xy0), _capi.ptr(xy0), len(p1),
+                                               _capi.ptr(p1), _capi.ptr(pr), _capi.ptr(model), C.byref(st),
+                                               _capi.ptr(a), _capi.ptr(b)))
+    else:
+        w0 = _capi.f64a(sampling_weights[0], (len(xy0),))
+        w1 = _capi.f64a(sampling_weights[1], (len(p1),))
+        _check(_load().rlbh_hybrid_lomsac_line_biased(C.byref(o), device, precision, len(xy0), _capi.ptr(xy0),
+                                                      _capi.ptr(w0), len(p1), _capi.ptr(p1), _capi.ptr(w1),
+                                                      _capi.ptr(pr), _capi.ptr(model), C.byref(st), _capi.ptr(a),
+                                                      _capi.ptr(b)))
     return model, {
         "num_iterations_total": st.num_iterations_total,
         "num_iterations_per_solver": list(st.num_iterations_per_solver),
@@ -186,6 +196,28 @@ def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, dev
         "best_model_score": st.best_model_score, "inlier_ratios": list(st.inlier_ratios),
         "number_lo_iterations": st.number_lo_iterations,
         "inlier_indices": [a[:st.num_inliers_per_type[0]].copy(), b[:st.num_inliers_per_type[1]].copy()]}
+
+
+def sample_uniform(seed, n, s, k):
+    """k draws of the template layer's UniformSampling (include/RansacLib/sampling.h); host only."""
+    out = np.empty((k, s), np.int32)
+    _check(_load().rlbh_sample_uniform(C.c_uint32(seed), n, s, k, _capi.ptr(out)))
+    return out
+
+
+def sample_hybrid(seed, num_data, sizes, weights=None):
+    """Draws of HybridUniformSampling (weights None) / HybridBiasedSampling (per-type weight lists) from
+    include/RansacLib/hybrid_sampling.h; sizes is k x T. Returns a list of k lists of T index lists."""
+    nd = np.ascontiguousarray(num_data, np.int32)
+    sz = np.ascontiguousarray(sizes, np.int32).reshape(-1, len(nd))
+    mx = max(int(sz.max()), 1)
+    out = np.empty((len(sz), len(nd), mx), np.int32)
+    w = None
+    if weights is not None:
+        w = np.ascontiguousarray(np.concatenate([np.asarray(x, np.float64) for x in weights]))
+    _check(_load().rlbh_sample_hybrid(C.c_uint32(seed), len(nd), _capi.ptr(nd), _capi.ptr(w) if w is not None else None,
+                                      len(sz), _capi.ptr(sz), mx, _capi.ptr(out)))
+    return [[[int(v) for v in row if v >= 0] for row in draw] for draw in out]
 
 
 def localize(focal_x, focal_y, points2D, points3D, inlier_threshold, number_lo_steps, min_num_iterations,

@@ -44,6 +44,21 @@ def main():
                           o.reshape(-1))
         hyb.append({"seed": seed, "num_data": nd, "sizes": sizes, "samples": o.tolist()})
     out["hybrid_sampling"] = hyb
+    # HybridBiasedSampling (hybrid_sampling.h:146-223): weights are small integers / 4 (exact), some zero
+    hb = []
+    for seed, nd, sizes in [(42, [50, 40], [[2, 0], [0, 1], [2, 1], [3, 2], [0, 1], [2, 0]]),
+                            (7, [6, 5], [[3, 0], [0, 2], [3, 2], [1, 1]]),      # "all candidates" short-cut
+                            (1, [1000, 2000], [[2, 0], [0, 1]] * 4)]:
+        w = [[((j * 7 + t * 3 + seed) % 5) * 0.25 for j in range(nd[t])] for t in range(2)]
+        if seed == 7:
+            w = [[1.0, 0.0, 2.0, 0.0, 0.5, 0.0], [0.0, 3.0, 0.0, 1.0, 0.0]]   # 3 and 2 candidates
+        k = len(sizes)
+        stride = max(sum(r) for r in sizes)
+        o = np.empty((k, stride), np.int32)
+        ref.sample_hybrid_biased(seed, 2, np.asarray(nd, np.int32), np.asarray(w[0] + w[1], np.float64), k,
+                                 np.asarray(sizes, np.int32).reshape(-1), stride, o.reshape(-1))
+        hb.append({"seed": seed, "num_data": nd, "weights": w, "sizes": sizes, "samples": o.tolist()})
+    out["hybrid_biased_sampling"] = hb
     nri = []
     for args in [(0.5, 1e-4, 4, 100, 10000), (0.5, 1e-4, 2, 100, 100000), (0.1, 1e-4, 4, 100, 1000000),
                  (0.05, 1e-4, 4, 100, 1000000), (0.001, 1e-4, 2, 100, 100000), (0.0, 1e-4, 4, 100, 10000),
@@ -153,6 +168,27 @@ def main():
         ref.hybrid_lomsac_line(C.byref(o), len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), np.array([0.2, 0.8]), model,
                                C.byref(st), a, b)
         hybrid["lomsac"].append({
+            "seed": seed, "final_lsq": final_lsq, "num_iterations_total": st.num_iterations_total,
+            "num_iterations_per_solver": list(st.num_iterations_per_solver),
+            "best_num_inliers": st.best_num_inliers, "best_solver_type": st.best_solver_type,
+            "best_model_score": st.best_model_score, "inlier_ratios": list(st.inlier_ratios),
+            "number_lo_iterations": st.number_lo_iterations, "model": model.tolist(),
+            "inliers0": a[:st.num_inliers_per_type[0]].tolist(), "inliers1": b[:st.num_inliers_per_type[1]].tolist()})
+    # the same instance through HybridBiasedSampling: outliers of type 0 down-weighted, a third of type 1 never drawn
+    rngw = np.random.default_rng(77)
+    w0 = np.round(rngw.uniform(0.1, 1.0, len(xy0)), 3)
+    w1 = np.round(rngw.uniform(0.1, 1.0, len(p1)), 3)
+    w1[::3] = 0.0
+    hybrid["weights0"], hybrid["weights1"], hybrid["lomsac_biased"] = w0.tolist(), w1.tolist(), []
+    for seed, final_lsq in [(42, 0), (6, 1)]:
+        o = ol.HybridOptions.default(sq_thr=[1e-4, 1e-4], weights=[2.0, 0.5], seed=seed, final_lsq=final_lsq,
+                                     min_iters=100, max_iters=10000, max_iters_per_solver=1000)
+        st = ol.HybridStats()
+        model = np.zeros(3)
+        a, b = np.zeros(len(xy0), np.int32), np.zeros(len(p1), np.int32)
+        ref.hybrid_lomsac_line_biased(C.byref(o), len(xy0), ol.c64(xy0), ol.c64(w0), len(p1), ol.c64(p1), ol.c64(w1),
+                                      np.array([0.2, 0.8]), model, C.byref(st), a, b)
+        hybrid["lomsac_biased"].append({
             "seed": seed, "final_lsq": final_lsq, "num_iterations_total": st.num_iterations_total,
             "num_iterations_per_solver": list(st.num_iterations_per_solver),
             "best_num_inliers": st.best_num_inliers, "best_solver_type": st.best_solver_type,

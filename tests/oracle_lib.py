@@ -71,6 +71,8 @@ def _bind(lib, prefix):
     ns = type("OracleFns", (), {})()
     ns.sample_uniform = fn("sample_uniform", None, [C.c_uint32, C.c_int, C.c_int, C.c_int, i32p])
     ns.sample_hybrid = fn("sample_hybrid", None, [C.c_uint32, C.c_int, i32p, C.c_int, i32p, C.c_int, i32p])
+    ns.sample_hybrid_biased = fn("sample_hybrid_biased", None,
+                                 [C.c_uint32, C.c_int, i32p, f64p, C.c_int, i32p, C.c_int, i32p])
     ns.num_required_iterations = fn("num_required_iterations", C.c_uint32,
                                     [C.c_double, C.c_double, C.c_int, C.c_uint32, C.c_uint32])
     ns.num_required_iterations_hybrid = fn("num_required_iterations_hybrid", C.c_uint32,
@@ -108,6 +110,9 @@ def _bind(lib, prefix):
     ns.hybrid_lomsac_line = fn("hybrid_lomsac_line", None,
                                [C.POINTER(HybridOptions), C.c_int, f64p, C.c_int, f64p, f64p, f64p,
                                 C.POINTER(HybridStats), i32p, i32p])
+    ns.hybrid_lomsac_line_biased = fn("hybrid_lomsac_line_biased", None,
+                                      [C.POINTER(HybridOptions), C.c_int, f64p, f64p, C.c_int, f64p, f64p, f64p, f64p,
+                                       C.POINTER(HybridStats), i32p, i32p])
     return ns
 
 

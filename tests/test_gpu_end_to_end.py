@@ -157,6 +157,57 @@ def test_hybrid_line_estimation_config():
         assert st["inlier_indices"][1].tolist() == b[:ost.num_inliers_per_type[1]].tolist()
 
 
+def test_hybrid_line_with_biased_sampling():
+    """HybridBiasedSampling (reference hybrid_sampling.h:146-223) as the Sampler of the drop-in
+    HybridLocallyOptimizedMSAC: the golden run of the reference's own headers, and a larger instance vs the oracle."""
+    import json
+    import os
+
+    H = host()
+    O = ol.oracle()
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.json")) as fh:
+        h = json.load(fh)["hybrid"]
+    xy0, p1 = np.array(h["xy0"]), np.array(h["xynn1"])
+    w0, w1 = np.array(h["weights0"]), np.array(h["weights1"])
+    for c in h["lomsac_biased"]:
+        opts = H.HybridLORansacOptions(squared_inlier_thresholds_=[1e-4, 1e-4], data_type_weights_=[2.0, 0.5],
+                                       random_seed_=c["seed"], final_least_squares_=bool(c["final_lsq"]),
+                                       min_num_iterations_=100, max_num_iterations_=10000,
+                                       max_num_iterations_per_solver_=1000)
+        m, st = H.estimate_hybrid_line(opts, xy0, p1, [0.2, 0.8], sampling_weights=(w0, w1))
+        assert st["num_iterations_total"] == c["num_iterations_total"]
+        assert st["num_iterations_per_solver"] == c["num_iterations_per_solver"]
+        assert st["best_num_inliers"] == c["best_num_inliers"] and st["best_solver_type"] == c["best_solver_type"]
+        assert st["number_lo_iterations"] == c["number_lo_iterations"]
+        np.testing.assert_allclose(st["best_model_score"], c["best_model_score"], rtol=1e-9)
+        np.testing.assert_allclose(m, c["model"], rtol=1e-9, atol=1e-12)
+        assert st["inlier_indices"][0].tolist() == c["inliers0"] and st["inlier_indices"][1].tolist() == c["inliers1"]
+
+    n, seed = 20000, 11
+    xy0, p1 = synth.hybrid_line_instance(900, n // 2, n // 2, n // 2, n // 2)
+    rng = np.random.default_rng(5)
+    w0, w1 = rng.uniform(0.0, 1.0, n), rng.uniform(0.0, 1.0, n)
+    w0[rng.random(n) < 0.3] = 0.0
+    o = ol.HybridOptions.default(sq_thr=[1e-4, 1e-4], weights=[2.0, 0.5], seed=seed, min_iters=100,
+                                 max_iters=10000, max_iters_per_solver=1000)
+    ost, om = ol.HybridStats(), np.zeros(3)
+    a, b = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    O.hybrid_lomsac_line_biased(C.byref(o), n, ol.c64(xy0), w0, n, ol.c64(p1), w1, np.array([0.2, 0.8]), om,
+                                C.byref(ost), a, b)
+    opts = H.HybridLORansacOptions(squared_inlier_thresholds_=[1e-4, 1e-4], data_type_weights_=[2.0, 0.5],
+                                   random_seed_=seed, min_num_iterations_=100, max_num_iterations_=10000,
+                                   max_num_iterations_per_solver_=1000)
+    for precision in (-1, 1):
+        m, st = H.estimate_hybrid_line(opts, xy0, p1, [0.2, 0.8], sampling_weights=(w0, w1), precision=precision)
+        assert st["num_iterations_total"] == ost.num_iterations_total
+        assert st["num_iterations_per_solver"] == list(ost.num_iterations_per_solver)
+        assert st["best_num_inliers"] == ost.best_num_inliers and st["number_lo_iterations"] == ost.number_lo_iterations
+        np.testing.assert_allclose(st["best_model_score"], ost.best_model_score, rtol=1e-9)
+        np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+        assert st["inlier_indices"][0].tolist() == a[:ost.num_inliers_per_type[0]].tolist()
+        assert st["inlier_indices"][1].tolist() == b[:ost.num_inliers_per_type[1]].tolist()
+
+
 def test_too_little_data_and_untouched_model():
     H = host()
     m, st = H.estimate_line(H.LORansacOptions(), np.array([[0.0, 1.0]]))  # 1 point < sample size 2

@@ -51,6 +51,37 @@ def test_hybrid_sampling(G, O):
         assert o.tolist() == c["samples"]
 
 
+def test_hybrid_biased_sampling(G, O):
+    """HybridBiasedSampling (reference hybrid_sampling.h:146-223): zero weights never drawn, discrete_distribution
+    stream of the reference, the all-candidates short-cut."""
+    for c in G["hybrid_biased_sampling"]:
+        k = len(c["sizes"])
+        stride = len(c["samples"][0])
+        o = np.empty((k, stride), np.int32)
+        w = np.asarray(c["weights"][0] + c["weights"][1], np.float64)
+        O.sample_hybrid_biased(c["seed"], 2, np.asarray(c["num_data"], np.int32), w, k,
+                               np.asarray(c["sizes"], np.int32).reshape(-1), stride, o.reshape(-1))
+        assert o.tolist() == c["samples"]
+        w0, w1 = c["weights"]
+        for row, sz in zip(c["samples"], c["sizes"]):
+            assert all(w0[i] > 0 for i in row[:sz[0]]) and all(w1[i] > 0 for i in row[sz[0]:sz[0] + sz[1]])
+
+
+def test_template_layer_samplers_match_the_reference(G):
+    """The drop-in headers' own samplers (include/RansacLib/sampling.h, hybrid_sampling.h), called through the host
+    library without a device, reproduce the reference's sample streams."""
+    from ransaclib_b200 import host as H
+
+    for c in G["uniform_sampling"]:
+        assert H.sample_uniform(c["seed"], c["n"], c["s"], c["k"]).tolist() == c["samples"]
+    for key in ("hybrid_sampling", "hybrid_biased_sampling"):
+        for c in G[key]:
+            got = H.sample_hybrid(c["seed"], c["num_data"], c["sizes"], c.get("weights"))
+            flat = [[i for t in draw for i in t] for draw in got]
+            want = [[i for i in row if i >= 0] for row in c["samples"]]
+            assert flat == want, key
+
+
 def test_num_required_iterations(G, O):
     for c in G["num_required_iterations"]:
         assert O.num_required_iterations(*c["args"]) == c["value"]
@@ -144,25 +175,32 @@ def test_hybrid_paths(G, O):
     O.hybrid_line_inliers(len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), ol.c64(hm[h["best"]]), np.array(h["sq_thr"]),
                           i0, i1, cc)
     assert i0[:cc[0]].tolist() == h["inliers0"] and i1[:cc[1]].tolist() == h["inliers1"]
-    for c in h["lomsac"]:
-        o = ol.HybridOptions.default(sq_thr=[1e-4, 1e-4], weights=[2.0, 0.5], seed=c["seed"],
-                                     final_lsq=c["final_lsq"], min_iters=100, max_iters=10000,
-                                     max_iters_per_solver=1000)
-        st = ol.HybridStats()
-        model = np.zeros(3)
-        a, b = np.zeros(len(xy0), np.int32), np.zeros(len(p1), np.int32)
-        O.hybrid_lomsac_line(C.byref(o), len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), np.array([0.2, 0.8]), model,
-                             C.byref(st), a, b)
-        assert st.num_iterations_total == c["num_iterations_total"]
-        assert list(st.num_iterations_per_solver) == c["num_iterations_per_solver"]
-        assert st.best_num_inliers == c["best_num_inliers"]
-        assert st.best_solver_type == c["best_solver_type"]
-        assert st.best_model_score == c["best_model_score"]
-        assert list(st.inlier_ratios) == c["inlier_ratios"]
-        assert st.number_lo_iterations == c["number_lo_iterations"]
-        assert model.tolist() == c["model"]
-        assert a[:st.num_inliers_per_type[0]].tolist() == c["inliers0"]
-        assert b[:st.num_inliers_per_type[1]].tolist() == c["inliers1"]
+    w0, w1 = np.array(h["weights0"]), np.array(h["weights1"])
+    for key in ("lomsac", "lomsac_biased"):
+        for c in h[key]:
+            o = ol.HybridOptions.default(sq_thr=[1e-4, 1e-4], weights=[2.0, 0.5], seed=c["seed"],
+                                         final_lsq=c["final_lsq"], min_iters=100, max_iters=10000,
+                                         max_iters_per_solver=1000)
+            st = ol.HybridStats()
+            model = np.zeros(3)
+            a, b = np.zeros(len(xy0), np.int32), np.zeros(len(p1), np.int32)
+            if key == "lomsac":
+                O.hybrid_lomsac_line(C.byref(o), len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), np.array([0.2, 0.8]),
+                                     model, C.byref(st), a, b)
+            else:  # HybridBiasedSampling as the Sampler (hybrid_sampling.h:146-223)
+                O.hybrid_lomsac_line_biased(C.byref(o), len(xy0), ol.c64(xy0), w0, len(p1), ol.c64(p1), w1,
+                                            np.array([0.2, 0.8]), model, C.byref(st), a, b)
+            assert st.num_iterations_total == c["num_iterations_total"]
+            assert list(st.num_iterations_per_solver) == c["num_iterations_per_solver"]
+            assert st.best_num_inliers == c["best_num_inliers"]
+            assert st.best_solver_type == c["best_solver_type"]
+            assert st.best_model_score == c["best_model_score"]
+            assert list(st.inlier_ratios) == c["inlier_ratios"]
+            assert st.number_lo_iterations == c["number_lo_iterations"]
+            assert model.tolist() == c["model"]
+            assert a[:st.num_inliers_per_type[0]].tolist() == c["inliers0"]
+            assert b[:st.num_inliers_per_type[1]].tolist() == c["inliers1"]
+    assert h["lomsac"][0]["model"] != h["lomsac_biased"][0]["model"]  # the sampler does change the run
 
 
 def test_p3p_against_opencv(O):
