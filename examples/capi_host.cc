@@ -17,6 +17,7 @@
 #include "calibrated_absolute_pose_estimator.h"
 #include "hybrid_line_estimator.h"
 #include "line_estimator.h"
+#include "localization_io.h"
 
 using namespace ransac_lib;
 using calibrated_absolute_pose::CalibratedAbsolutePoseEstimator;
@@ -124,50 +125,7 @@ void Run(const rlbh_options& o, Solver& solver, int precision, Model* model, rlb
     for (size_t i = 0; i < rs.inlier_indices.size(); ++i) inliers[i] = rs.inlier_indices[i];
 }
 
-// [R|c] -> (qvec w,x,y,z ; tvec = -R c) as ransaclib_localization.cc:147-150
-// (Eigen::Quaterniond(R), then normalize()).
-void PoseToQvecTvec(const double* m /* column-major 3x4 */, double* qvec, double* tvec) {
-  double R[9];
-  for (int r = 0; r < 3; ++r)
-    for (int c = 0; c < 3; ++c) R[3 * r + c] = m[r + 3 * c];
-  for (int r = 0; r < 3; ++r) tvec[r] = -(R[3 * r] * m[9] + R[3 * r + 1] * m[10] + R[3 * r + 2] * m[11]);
-  double w, x, y, z;
-  const double trace = R[0] + R[4] + R[8];
-  if (trace > 0.0) {
-    double t = std::sqrt(trace + 1.0);
-    w = 0.5 * t;
-    t = 0.5 / t;
-    x = (R[7] - R[5]) * t;
-    y = (R[2] - R[6]) * t;
-    z = (R[3] - R[1]) * t;
-  } else {
-    int i = 0;
-    if (R[4] > R[0]) i = 1;
-    if (R[8] > R[4 * i]) i = 2;
-    const int j = (i + 1) % 3, k = (j + 1) % 3;
-    double t = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
-    double q[3];
-    q[i] = 0.5 * t;
-    t = 0.5 / t;
-    w = (R[3 * k + j] - R[3 * j + k]) * t;
-    q[j] = (R[3 * j + i] + R[3 * i + j]) * t;
-    q[k] = (R[3 * k + i] + R[3 * i + k]) * t;
-    x = q[0];
-    y = q[1];
-    z = q[2];
-  }
-  const double nq = std::sqrt(w * w + x * x + y * y + z * z);
-  if (nq > 0.0) {
-    w /= nq;
-    x /= nq;
-    y /= nq;
-    z /= nq;
-  }
-  qvec[0] = w;
-  qvec[1] = x;
-  qvec[2] = y;
-  qvec[3] = z;
-}
+using localization_io::PoseToQvecTvec;  // [R|c] -> (qvec w,x,y,z ; tvec = -R c), ransaclib_localization.cc:147-150
 
 // What the samplers ask of a solver, and nothing else.
 struct SizesOnly {
