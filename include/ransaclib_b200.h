@@ -234,7 +234,7 @@ void rlb_localize_default_options(rlb_localize_options* opt, double inlier_thres
  * fx, fy, seeds: one per query (the reference seeds from std::random_device; here the seed is an
  * argument so runs are reproducible). Outputs: poses = num_queries x 12 (column-major [R | c]),
  * results = num_queries records, inliers = `total` int32 (ascending inlier indices of query q
- * start at offsets[q]) or NULL. Uploads are pipelined with the kernel in chunks of queries. */
+ * start at offsets[q]; entries past results[q].num_inliers are unspecified) or NULL. Uploads are pipelined with the kernel in chunks of queries. */
 int rlb_localize_batch(rlb_ctx* ctx, int num_queries, const int64_t* offsets,
                        const double* points2D, const double* points3D, const double* fx,
                        const double* fy, const uint32_t* seeds, const rlb_localize_options* opt,
