@@ -66,7 +66,7 @@ class HybridLineEstimator {
       const std::vector<int>& s = sample[0];
       if (s.size() < 2u) return 0;
       if (!line_fit::ThroughTwoPoints(points_[2 * s[0]], points_[2 * s[0] + 1], points_[2 * s[1]],
-                                      points_[2 * s[1] + 1], &l))
+                                      points_[2 * s[1] + 1], l.coeff))
         return 0;
     } else {  // hybrid_line_estimator.cc:132-152
       const std::vector<int>& s = sample[1];
@@ -113,7 +113,7 @@ class HybridLineEstimator {
                                 *y = points_with_normals_[4 * static_cast<size_t>(sample[1][i - k0]) + 1];
                               }
                             },
-                            line);
+                            line->coeff);
   }
 
   // ---- GPU opt-in ----

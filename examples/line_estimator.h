@@ -10,87 +10,10 @@
 
 #include <RansacLib/gpu_scorer.h>
 
+#include "line_fit.h"
 #include "model_types.h"
 
 namespace ransac_lib {
-
-namespace line_fit {
-// Unit eigenvector of the LARGEST eigenvalue of [[a,b],[b,d]]: what the reference reads
-// from SelfAdjointEigenSolver::eigenvectors().col(1) (line_estimator.cc:97-100). Note the
-// reference uses it as the line NORMAL although it is the direction of largest spread;
-// that behaviour is kept (the refit then loses against the minimal model in
-// UpdateBestModel). Eigen's sign convention is internal; squared residuals ignore it.
-inline bool LargestEigenvector2x2(double a, double b, double d, double* ex, double* ey) {
-  const double half_diff = 0.5 * (a - d);
-  const double radius = std::sqrt(half_diff * half_diff + b * b);
-  const double lambda = 0.5 * (a + d) + radius;
-  const double c0x = b, c0y = lambda - a;   // from row 0 of (A - lambda I)
-  const double c1x = lambda - d, c1y = b;   // from row 1
-  const double n0 = c0x * c0x + c0y * c0y, n1 = c1x * c1x + c1y * c1y;
-  double vx = c0x, vy = c0y, nn = n0;
-  if (n1 > n0) {
-    vx = c1x;
-    vy = c1y;
-    nn = n1;
-  }
-  if (!(nn > 0.0)) {
-    *ex = 0.0;
-    *ey = 1.0;
-    return (a == a) && (d == d);
-  }
-  const double inv = 1.0 / std::sqrt(nn);
-  *ex = vx * inv;
-  *ey = vy * inv;
-  return true;
-}
-
-// Covariance line fit over points gathered by `get(i, &x, &y)` (line_estimator.cc:74-107,
-// hybrid_line_estimator.cc:58-97).
-template <class Getter>
-inline bool FitCovariance(int count, Getter get, Line2D* line) {
-  double mx = 0.0, my = 0.0;
-  for (int i = 0; i < count; ++i) {
-    double x, y;
-    get(i, &x, &y);
-    mx += x;
-    my += y;
-  }
-  mx /= static_cast<double>(count);
-  my /= static_cast<double>(count);
-  double cxx = 0.0, cxy = 0.0, cyy = 0.0;
-  for (int i = 0; i < count; ++i) {
-    double x, y;
-    get(i, &x, &y);
-    const double dx = x - mx, dy = y - my;
-    cxx += dx * dx;
-    cxy += dx * dy;
-    cyy += dy * dy;
-  }
-  const double denom = static_cast<double>(count - 1);
-  cxx /= denom;
-  cxy /= denom;
-  cyy /= denom;
-  double ex, ey;
-  if (!LargestEigenvector2x2(cxx, cxy, cyy, &ex, &ey)) return false;
-  (*line)[0] = ex;
-  (*line)[1] = ey;
-  (*line)[2] = -(ex * mx + ey * my);
-  return true;
-}
-
-// (x1,y1,1) x (x2,y2,1), normal scaled to unit length (line_estimator.cc:53-72).
-inline bool ThroughTwoPoints(double x1, double y1, double x2, double y2, Line2D* l) {
-  const double a = y1 * 1.0 - 1.0 * y2;
-  const double b = 1.0 * x2 - x1 * 1.0;
-  const double c = x1 * y2 - y1 * x2;
-  const double nrm = std::sqrt(a * a + b * b);
-  if (nrm == 0.0) return false;
-  (*l)[0] = a / nrm;
-  (*l)[1] = b / nrm;
-  (*l)[2] = c / nrm;
-  return true;
-}
-}  // namespace line_fit
 
 class LineEstimator {
  public:
@@ -109,7 +32,7 @@ class LineEstimator {
     lines->clear();
     if (sample.size() < 2u) return 0;
     Line2D l;
-    if (!line_fit::ThroughTwoPoints(x(sample[0]), y(sample[0]), x(sample[1]), y(sample[1]), &l)) return 0;
+    if (!line_fit::ThroughTwoPoints(x(sample[0]), y(sample[0]), x(sample[1]), y(sample[1]), l.coeff)) return 0;
     lines->push_back(l);
     return 1;
   }
@@ -121,7 +44,7 @@ class LineEstimator {
                                      *px = x(sample[i]);
                                      *py = y(sample[i]);
                                    },
-                                   line)
+                                   line->coeff)
                ? 1
                : 0;
   }
@@ -134,6 +57,21 @@ class LineEstimator {
 
   inline void LeastSquares(const std::vector<int>& sample, Line2D* line) const {
     NonMinimalSolver(sample, line);
+  }
+
+  // ---- device-resident driver (csrc/line_lomsac_kernel.cu) ----
+  // The whole of LocallyOptimizedMSAC::EstimateModel for this solver in one launch: sampling,
+  // 2-point solver, scoring, local optimisation with the covariance fit above, same run as the
+  // host-driven loop. false = options outside what the kernel supports (shuffle targets <= 32).
+  bool device_lomsac(const rlb_lomsac_options& opt, uint32_t seed, double* packed_model,
+                     rlb_lomsac_result* result, std::vector<int>* inliers) const {
+    if (opt.min_sample_mult < 1 || opt.min_sample_mult * 2 > 32 || opt.non_min_sample_mult < 0 ||
+        opt.non_min_sample_mult * 2 > 32 || opt.lo_steps < 0 || opt.lsq_iters < 0)
+      return false;
+    inliers->resize(static_cast<size_t>(num_data_ > 0 ? num_data_ : 1));
+    scorer_.LineLomsac(opt, seed, packed_model, result, reinterpret_cast<int32_t*>(inliers->data()));
+    inliers->resize(static_cast<size_t>(result->num_inliers));
+    return true;
   }
 
   // ---- GPU opt-in (RansacLib/gpu_scorer.h) ----

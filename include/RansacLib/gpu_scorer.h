@@ -8,6 +8,11 @@
 // and, optionally, a device-side batched minimal solver:
 //     int device_minimal_solver() const;           // solver id for rlb_hypothesize_and_score
 //     double device_minimal_solver_threshold() const;   // P3P's 4th-point threshold
+// and, optionally, a device-resident driver for the WHOLE of EstimateModel (one launch instead of
+// one launch per pass; used when the Sampler is the default UniformSampling and RLB_HOST_DRIVER=1 is
+// not set in the environment):
+//     bool device_lomsac(const rlb_lomsac_options&, uint32_t seed, double* packed_model /* in/out */,
+//                        rlb_lomsac_result*, std::vector<int>* inliers) const;   // false: not applicable
 // Solvers that do not opt in do not compile against LocallyOptimizedMSAC: there is no
 // CPU scoring path in this library.
 #ifndef RANSACLIB_B200_RANSACLIB_GPU_SCORER_H_
@@ -137,6 +142,13 @@ class DeviceScorer {
           "rlb_hypothesize_and_score");
   }
 
+  // Whole LO-MSAC run of the 2D line solver over this (line) data set in one launch
+  // (csrc/line_lomsac_kernel.cu). line: 3 doubles in/out; inliers: num_data entries.
+  void LineLomsac(const rlb_lomsac_options& opt, uint32_t seed, double* line, rlb_lomsac_result* result,
+                  int32_t* inliers) const {
+    Check(rlb_scorer_line_lomsac(s_, &opt, seed, line, result, inliers), "rlb_scorer_line_lomsac");
+  }
+
   // Fused K=1 pass: inliers at sq_thr_inl (ascending, per type) and, if sq_thr_score is
   // given, the MSAC score at sq_thr_score. idx may be null (count only).
   void InliersAndScore(const double* model, const double* sq_thr_inl, const double* sq_thr_score,
@@ -162,6 +174,21 @@ struct HasDeviceMinimalSolver : std::false_type {};
 template <class S>
 struct HasDeviceMinimalSolver<S, decltype(void(std::declval<const S&>().device_minimal_solver()))>
     : std::true_type {};
+
+template <class S, class = void>
+struct HasDeviceLomsac : std::false_type {};
+template <class S>
+struct HasDeviceLomsac<S, decltype(void(std::declval<const S&>().device_lomsac(
+                              std::declval<const rlb_lomsac_options&>(), 0u, static_cast<double*>(nullptr),
+                              static_cast<rlb_lomsac_result*>(nullptr), static_cast<std::vector<int>*>(nullptr))))>
+    : std::true_type {};
+
+// RLB_HOST_DRIVER=1: keep the host-driven loop (one launch per pass) even where a device-resident
+// driver exists; both produce the same run (tests exercise both).
+inline bool HostDriverForced() {
+  const char* p = std::getenv("RLB_HOST_DRIVER");
+  return p && p[0] == '1';
+}
 
 }  // namespace gpu
 }  // namespace ransac_lib

@@ -124,6 +124,12 @@ class LocallyOptimizedMSAC : public RansacBase {
     const int num_data = solver.num_data();
     if (sample_size > num_data || sample_size <= 0) return 0;
 
+    // A solver may run the whole of this function on the device (gpu_scorer.h: device_lomsac).
+    if (DeviceResident(options, solver, best_model, statistics,
+                       std::integral_constant<bool, gpu::HasDeviceLomsac<Solver>::value &&
+                                                        std::is_same<Sampler, UniformSampling<Solver> >::value>()))
+      return stats.best_num_inliers;
+
     Sampler sampler(options.random_seed_, solver);
     std::mt19937 rng;  // local optimisation's own stream (ransac.h:142-144)
     rng.seed(options.random_seed_);
@@ -234,6 +240,45 @@ class LocallyOptimizedMSAC : public RansacBase {
   }
 
  protected:
+  bool DeviceResident(const LORansacOptions&, const Solver&, Model*, RansacStatistics*, std::false_type) const {
+    return false;
+  }
+  // One launch: sampler, minimal solver, scoring, local optimisation and refits all run on the
+  // device (same sequence of decisions as the loop above; csrc/line_lomsac_kernel.cu).
+  bool DeviceResident(const LORansacOptions& options, const Solver& solver, Model* best_model,
+                      RansacStatistics* statistics, std::true_type) const {
+    if (gpu::HostDriverForced()) return false;
+    rlb_lomsac_options o;
+    o.min_iters = options.min_num_iterations_;
+    o.max_iters = options.max_num_iterations_;
+    o.success_prob = options.success_probability_;
+    o.sq_thr = options.squared_inlier_threshold_;
+    o.lo_steps = options.num_lo_steps_;
+    o.thr_mult = options.threshold_multiplier_;
+    o.lsq_iters = options.num_lsq_iterations_;
+    o.min_sample_mult = options.min_sample_multiplicator_;
+    o.non_min_sample_mult = options.non_min_sample_multiplier_;
+    o.lo_start = options.lo_starting_iterations_;
+    o.final_lsq = options.final_least_squares_ ? 1 : 0;
+    o.debug_flags = 0;
+    double packed[16] = {0.0};
+    Solver::PackModel(*best_model, packed);  // read by the final least-squares step (ransac.h:257-259)
+    rlb_lomsac_result r;
+    std::vector<int> inliers;
+    if (!solver.device_lomsac(o, options.random_seed_, packed, &r, &inliers)) return false;
+    RansacStatistics& stats = *statistics;
+    if (!r.success) return true;
+    stats.num_iterations = r.num_iterations;
+    stats.best_num_inliers = r.num_inliers;
+    stats.best_model_score = r.score;
+    stats.inlier_ratio = r.inlier_ratio;
+    stats.number_lo_iterations = r.num_lo;
+    stats.inlier_indices.swap(inliers);
+    if (r.score < std::numeric_limits<double>::max()) Solver::UnpackModel(packed, best_model);
+    if (counters) counters->single_passes += static_cast<uint64_t>(r.passes);
+    return true;
+  }
+
   // One speculative batch of hypotheses with their scores, on the host.
   struct Batch {
     uint32_t first = 0, count = 0;

@@ -247,6 +247,40 @@ int rlb_localize_batch_dev(rlb_ctx* ctx, int num_queries, int max_matches, const
                            const rlb_localize_options* opt, double* d_poses,
                            rlb_localize_result* d_results, int32_t* d_inliers);
 
+/* ---- device-resident line LO-MSAC ---------------------------------------------
+ * P independent runs of LocallyOptimizedMSAC<Vector3d, ., LineEstimator>::EstimateModel
+ * (ransac.h:128-275 over examples/line_estimator.{h,cc}; BASELINE configs[0] is one such run) in
+ * ONE launch: each CTA runs the whole control flow for one problem at a time - seeded
+ * std::mt19937 sampling and Fisher-Yates shuffles, the 2-point solver, MSAC scoring, local
+ * optimisation with the covariance line fit (line_estimator.cc:74-107) - without host round
+ * trips. Options and results are the structs of the localization entry points (the fields are
+ * those of LORansacOptions / RansacStatistics); min_sample_mult * 2 and non_min_sample_mult * 2
+ * must be <= 32. Problems are concatenated: problem p owns points [offsets[p], offsets[p+1]). */
+typedef rlb_localize_options rlb_lomsac_options;
+typedef rlb_localize_result rlb_lomsac_result;
+
+/* RansacOptions / LORansacOptions defaults (ransac.h:47-92). */
+void rlb_lomsac_default_options(rlb_lomsac_options* opt);
+
+/* HOST pointers. xy: total x 2 (x0,y0,x1,y1,... = column-major Matrix2Xd); seeds: one per problem
+ * (LORansacOptions::random_seed_). lines: num_problems x 3, IN/OUT: on entry the caller's models
+ * (EstimateModel leaves *best_model untouched when nothing is found, and its final least-squares
+ * step reads it, ransac.h:257-259), on return the best models. results[p].success = 0 for
+ * problems with fewer than 2 points. inliers: `total` int32 (ascending inlier indices of problem
+ * p start at offsets[p]) or NULL. */
+int rlb_line_lomsac_batch(rlb_ctx* ctx, int num_problems, const int64_t* offsets, const double* xy,
+                          const uint32_t* seeds, const rlb_lomsac_options* opt, double* lines,
+                          rlb_lomsac_result* results, int32_t* inliers);
+/* DEVICE pointers (outputs stay in HBM); asynchronous on the context stream. max_points = largest
+ * offsets[p+1]-offsets[p] (sizes the scratch). */
+int rlb_line_lomsac_batch_dev(rlb_ctx* ctx, int num_problems, int max_points, const int64_t* d_offsets,
+                              const double* d_xy, const uint32_t* d_seeds, const rlb_lomsac_options* opt,
+                              double* d_lines, rlb_lomsac_result* d_results, int32_t* d_inliers);
+/* One run over the data set of a LINE scorer (already resident): what the drop-in
+ * LocallyOptimizedMSAC calls for LineEstimator. line: 3 doubles, in/out; inliers: n int32 or NULL. */
+int rlb_scorer_line_lomsac(rlb_scorer* s, const rlb_lomsac_options* opt, uint32_t seed, double* line,
+                           rlb_lomsac_result* result, int32_t* inliers);
+
 /* ---- measurement helpers --------------------------------------------------- */
 /* When enabled, the context brackets every sweep kernel and every inlier kernel with
  * CUDA events on its stream; rlb_ctx_kernel_time_ms waits for the LAST such kernel

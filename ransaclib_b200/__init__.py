@@ -125,6 +125,45 @@ class Context:
             C.c_void_p(d_fx), C.c_void_p(d_fy), C.c_void_p(d_seeds), C.byref(options), C.c_void_p(d_poses),
             C.c_void_p(d_results), C.c_void_p(d_inliers or 0)))
 
+    # -- device-resident line LO-MSAC ------------------------------------------
+    def lomsac_options(self, **kw) -> "_capi.LocalizeOptions":
+        """LORansacOptions defaults (ransac.h:47-92); keyword names are the struct's fields
+        (min_iters, max_iters, success_prob, sq_thr, lo_steps, thr_mult, lsq_iters, min_sample_mult,
+        non_min_sample_mult, lo_start, final_lsq, debug_flags)."""
+        o = _capi.LocalizeOptions()
+        self._lib.rlb_lomsac_default_options(C.byref(o))
+        for k, v in kw.items():
+            if k not in dict(o._fields_):
+                raise AttributeError(k)
+            setattr(o, k, v)
+        return o
+
+    def line_lomsac_batch(self, offsets, xy, seeds, options, lines=None, want_inliers=True):
+        """P independent LO-MSAC runs of the 2D line solver in one launch, one problem per CTA (host
+        buffers). -> (lines [P,3], results record array, inliers or None). `lines` = the callers'
+        initial models (default zeros), returned untouched for problems where nothing was found."""
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        npb = len(off) - 1
+        xy = _capi.f64a(xy, (-1, 2))
+        if len(xy) != off[-1]:
+            raise ValueError("xy / offsets disagree")
+        seeds = np.ascontiguousarray(seeds, dtype=np.uint32)
+        if len(seeds) != npb:
+            raise ValueError("need one seed per problem")
+        out = np.zeros((npb, 3)) if lines is None else np.array(_capi.f64a(lines, (npb, 3)), copy=True)
+        res = np.zeros(npb, _capi.LOCALIZE_RESULT)
+        inl = np.zeros(max(int(off[-1]), 1), np.int32) if want_inliers else None
+        _capi.check(self._lib.rlb_line_lomsac_batch(self._h, npb, _capi.ptr(off), _capi.ptr(xy), _capi.ptr(seeds),
+                                                    C.byref(options), _capi.ptr(out), _capi.ptr(res), _capi.ptr(inl)))
+        return out, res, inl
+
+    def line_lomsac_batch_dev(self, num_problems: int, max_points: int, d_offsets: int, d_xy: int, d_seeds: int,
+                              options, d_lines: int, d_results: int, d_inliers: int = 0):
+        """Device-pointer variant: enqueues the kernel on the context stream."""
+        _capi.check(self._lib.rlb_line_lomsac_batch_dev(
+            self._h, num_problems, max_points, C.c_void_p(d_offsets), C.c_void_p(d_xy), C.c_void_p(d_seeds),
+            C.byref(options), C.c_void_p(d_lines), C.c_void_p(d_results), C.c_void_p(d_inliers or 0)))
+
     # -- data sets -----------------------------------------------------------
     def line_scorer(self, xy) -> "Scorer":
         xy = _capi.f64a(xy, (-1, 2))
@@ -251,6 +290,18 @@ class Scorer:
         err = np.empty(self.num_data[type_])
         _capi.check(self._lib.rlb_eval_errors(self._h, precision, _capi.ptr(model), type_, _capi.ptr(err)))
         return err
+
+    def line_lomsac(self, options, seed: int, line=None, want_inliers=True):
+        """Whole LO-MSAC run over this LINE scorer's resident data in one launch (one CTA).
+        -> (line[3], result record, ascending inlier indices or None)."""
+        out = np.zeros(3) if line is None else np.array(_capi.f64a(line, (3,)), copy=True)
+        res = np.zeros(1, _capi.LOCALIZE_RESULT)
+        n = self.num_data[0]
+        inl = np.zeros(max(n, 1), np.int32) if want_inliers else None
+        _capi.check(self._lib.rlb_scorer_line_lomsac(self._h, C.byref(options), int(seed), _capi.ptr(out),
+                                                     _capi.ptr(res), _capi.ptr(inl)))
+        r = res[0]
+        return out, r, (inl[:int(r["num_inliers"])].copy() if want_inliers else None)
 
     def solve_line2pt(self, samples):
         s = _capi.i32a(samples, (-1, 2))

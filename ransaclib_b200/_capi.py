@@ -28,6 +28,7 @@ SYMBOLS = [
     "rlb_eval_errors", "rlb_solve_line2pt_batch", "rlb_solve_point_normal_batch", "rlb_solve_p3p_batch",
     "rlb_hypothesize_and_score", "rlb_hypothesize_and_score_dev", "rlb_measure_fma_peak", "rlb_sharded_round_dev", "rlb_select_winner_dev", "rlb_ctx_set_timing", "rlb_ctx_kernel_time_ms", "rlb_ctx_last_sweep_plan",
     "rlb_localize_default_options", "rlb_localize_batch", "rlb_localize_batch_dev",
+    "rlb_lomsac_default_options", "rlb_line_lomsac_batch", "rlb_line_lomsac_batch_dev", "rlb_scorer_line_lomsac",
 ]
 
 
@@ -103,6 +104,11 @@ def load():
     lib.rlb_localize_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, C.POINTER(LocalizeOptions), vp, vp, vp]
     lib.rlb_localize_batch_dev.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, C.POINTER(LocalizeOptions), vp,
                                            vp, vp]
+    lib.rlb_lomsac_default_options.argtypes = [C.POINTER(LocalizeOptions)]
+    lib.rlb_lomsac_default_options.restype = None
+    lib.rlb_line_lomsac_batch.argtypes = [vp, i32, vp, vp, vp, C.POINTER(LocalizeOptions), vp, vp, vp]
+    lib.rlb_line_lomsac_batch_dev.argtypes = [vp, i32, i32, vp, vp, vp, C.POINTER(LocalizeOptions), vp, vp, vp]
+    lib.rlb_scorer_line_lomsac.argtypes = [vp, C.POINTER(LocalizeOptions), C.c_uint32, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -92,6 +92,9 @@ struct rlb_ctx {
   // device-resident batched localization: per-warp-slot scratch, ticket / ready / abort words,
   // a copy stream + pinned progress words for the pipelined host API
   DevBuf loc_soa, loc_lists, loc_words;
+  // device-resident line LO-MSAC: per-CTA lists, {ticket, line, result} words + inlier list of the
+  // single-problem entry point
+  DevBuf ll_lists, ll_io;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t loc_ev[2] = {nullptr, nullptr};
   unsigned int* h_ready = nullptr;  // pinned, kMaxChunks entries
@@ -567,6 +570,8 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   if (c->h_ready) cudaFreeHost(c->h_ready);
   c->loc_soa.release();
   c->loc_lists.release();
+  c->ll_lists.release();
+  c->ll_io.release();
   c->loc_words.release();
   for (int i = 0; i < 2; ++i)
     if (c->loc_ev[i]) cudaEventDestroy(c->loc_ev[i]);
@@ -1302,6 +1307,178 @@ int rlb_localize_batch(rlb_ctx* c, int nq, const int64_t* offsets, const double*
   aborted = *static_cast<unsigned int*>(c->h_small);
   release();
   if (aborted) return fail(RLB_E_CUDA, "localization kernel gave up waiting for the upload");
+  return RLB_OK;
+}
+
+// ---- device-resident line LO-MSAC -----------------------------------------------------------
+namespace {
+
+int check_line_lomsac_options(const rlb_lomsac_options* o) {
+  if (!o) return fail(RLB_E_ARG, "null options");
+  if (o->min_sample_mult < 1 || o->min_sample_mult * 2 > 32)
+    return fail(RLB_E_ARG, "min_sample_mult * 2 must be in [2, 32] (got %d)", o->min_sample_mult);
+  if (o->non_min_sample_mult < 0 || o->non_min_sample_mult * 2 > 32)
+    return fail(RLB_E_ARG, "non_min_sample_mult * 2 must be <= 32 (got %d)", o->non_min_sample_mult);
+  if (o->lo_steps < 0 || o->lsq_iters < 0) return fail(RLB_E_ARG, "negative lo_steps / lsq_iters");
+  return RLB_OK;
+}
+
+// Enqueues the kernel on the context stream. d_offsets == nullptr: ONE problem of n_single points.
+int line_lomsac_enqueue(rlb_ctx* c, int np, int max_points, const int64_t* d_offsets, int n_single,
+                        const double* d_xy, const uint32_t* d_seeds, uint32_t seed_single,
+                        const rlb_lomsac_options* opt, double* d_lines, rlb_lomsac_result* d_results,
+                        int32_t* d_inliers, unsigned int* d_ticket) {
+  const int nmax = std::max(max_points, 2);
+  // Stage the points in shared memory when the largest problem fits (RLB_LL_SMEM=0: never; A/B timing).
+  int smem_points = (nmax <= rlb::line_lomsac_smem_points()) ? nmax : 0;
+  if (const char* e = std::getenv("RLB_LL_SMEM"))
+    if (e[0] == '0') smem_points = 0;
+  const int ctas = std::max(1, std::min(np, c->sms * rlb::line_lomsac_ctas_per_sm(smem_points)));
+  RLB_CUDA(c->ll_lists.ensure(static_cast<size_t>(ctas) * 3 * nmax * sizeof(int32_t)));
+  RLB_CUDA(cudaMemsetAsync(d_ticket, 0, 4, c->stream));
+  rlb::LineLomsacArgs a;
+  a.num_problems = np;
+  a.offsets = reinterpret_cast<const long long*>(d_offsets);
+  a.n_single = n_single;
+  a.xy = d_xy;
+  a.seeds = d_seeds;
+  a.seed_single = seed_single;
+  a.opt = *opt;
+  a.lines = d_lines;
+  a.results = d_results;
+  a.inliers = d_inliers;
+  a.lists = c->ll_lists.as<int32_t>();
+  a.nmax = nmax;
+  a.ticket = d_ticket;
+  a.smem_points = smem_points;
+  RLB_CUDA(rlb::launch_line_lomsac(a, ctas, c->stream, &c->launches_i));
+  account(c);
+  return RLB_OK;
+}
+
+}  // namespace
+
+void rlb_lomsac_default_options(rlb_lomsac_options* o) {
+  // RansacOptions / LORansacOptions defaults (ransac.h:47-92)
+  o->min_iters = 100u;
+  o->max_iters = 10000u;
+  o->success_prob = 0.9999;
+  o->sq_thr = 1.0;
+  o->lo_steps = 10;
+  o->thr_mult = std::sqrt(2.0);
+  o->lsq_iters = 4;
+  o->min_sample_mult = 7;
+  o->non_min_sample_mult = 3;
+  o->lo_start = 50u;
+  o->final_lsq = 0;
+  o->debug_flags = 0;
+}
+
+int rlb_line_lomsac_batch_dev(rlb_ctx* c, int np, int max_points, const int64_t* d_offsets, const double* d_xy,
+                              const uint32_t* d_seeds, const rlb_lomsac_options* opt, double* d_lines,
+                              rlb_lomsac_result* d_results, int32_t* d_inliers) {
+  if (!c) return fail(RLB_E_ARG, "null context");
+  if (np <= 0) return fail(RLB_E_ARG, "num_problems must be positive (got %d)", np);
+  if (!d_offsets || !d_xy || !d_seeds || !d_lines || !d_results) return fail(RLB_E_ARG, "null device pointer");
+  int rc = check_line_lomsac_options(opt);
+  if (rc) return rc;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  RLB_CUDA(c->ll_io.ensure(256));
+  return line_lomsac_enqueue(c, np, max_points, d_offsets, 0, d_xy, d_seeds, 0u, opt, d_lines, d_results,
+                             d_inliers, c->ll_io.as<unsigned int>());
+}
+
+int rlb_line_lomsac_batch(rlb_ctx* c, int np, const int64_t* offsets, const double* xy, const uint32_t* seeds,
+                          const rlb_lomsac_options* opt, double* lines, rlb_lomsac_result* results,
+                          int32_t* inliers) {
+  if (!c) return fail(RLB_E_ARG, "null context");
+  if (np <= 0) return fail(RLB_E_ARG, "num_problems must be positive (got %d)", np);
+  if (!offsets || !xy || !seeds || !lines || !results) return fail(RLB_E_ARG, "null pointer");
+  int rc = check_line_lomsac_options(opt);
+  if (rc) return rc;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (offsets[0] != 0) return fail(RLB_E_ARG, "offsets[0] must be 0");
+  int64_t max_points = 0;
+  for (int q = 0; q < np; ++q) {
+    const int64_t n = offsets[q + 1] - offsets[q];
+    if (n < 0 || n > 0x7fffffff) return fail(RLB_E_ARG, "problem %d has %lld points", q, (long long)n);
+    max_points = std::max(max_points, n);
+  }
+  const int64_t total = offsets[np];
+  const size_t tot = static_cast<size_t>(std::max<int64_t>(total, 1));
+  void *d_off = nullptr, *d_xy = nullptr, *d_seed = nullptr, *d_line = nullptr, *d_res = nullptr, *d_inl = nullptr;
+  auto release = [&]() {
+    for (void* p : {d_off, d_xy, d_seed, d_line, d_res, d_inl}) pool_release(c, p);
+  };
+  rc = pool_alloc(c, (np + 1) * sizeof(int64_t), &d_off);
+  if (!rc) rc = pool_alloc(c, tot * 2 * sizeof(double), &d_xy);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(np) * sizeof(uint32_t), &d_seed);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(np) * 3 * sizeof(double), &d_line);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(np) * sizeof(rlb_lomsac_result), &d_res);
+  if (!rc && inliers) rc = pool_alloc(c, tot * sizeof(int32_t), &d_inl);
+  if (rc) {
+    release();
+    return rc;
+  }
+  cudaStream_t st = c->stream;
+  auto body = [&]() -> int {
+    RLB_CUDA(c->ll_io.ensure(256));
+    RLB_CUDA(cudaMemcpyAsync(d_off, offsets, (np + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    if (total > 0) RLB_CUDA(cudaMemcpyAsync(d_xy, xy, tot * 2 * sizeof(double), cudaMemcpyHostToDevice, st));
+    RLB_CUDA(cudaMemcpyAsync(d_seed, seeds, np * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    RLB_CUDA(cudaMemcpyAsync(d_line, lines, static_cast<size_t>(np) * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    const int rc2 = line_lomsac_enqueue(c, np, static_cast<int>(max_points), static_cast<int64_t*>(d_off), 0,
+                                        static_cast<double*>(d_xy), static_cast<uint32_t*>(d_seed), 0u, opt,
+                                        static_cast<double*>(d_line), static_cast<rlb_lomsac_result*>(d_res),
+                                        static_cast<int32_t*>(d_inl), c->ll_io.as<unsigned int>());
+    if (rc2) return rc2;
+    RLB_CUDA(cudaMemcpyAsync(lines, d_line, static_cast<size_t>(np) * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    RLB_CUDA(cudaMemcpyAsync(results, d_res, static_cast<size_t>(np) * sizeof(rlb_lomsac_result),
+                             cudaMemcpyDeviceToHost, st));
+    if (inliers && total > 0)
+      RLB_CUDA(cudaMemcpyAsync(inliers, d_inl, static_cast<size_t>(total) * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    RLB_CUDA(cudaStreamSynchronize(st));
+    return RLB_OK;
+  };
+  rc = body();
+  if (rc) cudaStreamSynchronize(st);
+  release();
+  return rc;
+}
+
+int rlb_scorer_line_lomsac(rlb_scorer* s, const rlb_lomsac_options* opt, uint32_t seed, double* line,
+                           rlb_lomsac_result* result, int32_t* inliers) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  if (s->d.kind != RLB_KIND_LINE) return fail(RLB_E_ARG, "rlb_scorer_line_lomsac needs a line scorer");
+  if (!line || !result) return fail(RLB_E_ARG, "null pointer");
+  rc = check_line_lomsac_options(opt);
+  if (rc) return rc;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  const int n = s->d.n[0];
+  // ll_io: [0] ticket, [64] line (3 doubles), [128] result, [256] inlier list
+  constexpr size_t kLine = 64, kRes = 128, kList = 256;
+  RLB_CUDA(c->ll_io.ensure(kList + static_cast<size_t>(std::max(n, 1)) * sizeof(int32_t)));
+  char* io = static_cast<char*>(c->ll_io.p);
+  char* hs = static_cast<char*>(c->h_small);
+  memcpy(hs + 256, line, 3 * sizeof(double));
+  RLB_CUDA(cudaMemcpyAsync(io + kLine, hs + 256, 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  rc = line_lomsac_enqueue(c, 1, n, nullptr, n, s->d.raw0, nullptr, seed, opt, reinterpret_cast<double*>(io + kLine),
+                           reinterpret_cast<rlb_lomsac_result*>(io + kRes),
+                           inliers ? reinterpret_cast<int32_t*>(io + kList) : nullptr,
+                           reinterpret_cast<unsigned int*>(io));
+  if (rc) return rc;
+  RLB_CUDA(cudaMemcpyAsync(hs + 256, io + kLine, 128, cudaMemcpyDeviceToHost, c->stream));
+  if (inliers && n > 0)
+    RLB_CUDA(cudaMemcpyAsync(inliers, io + kList, static_cast<size_t>(n) * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                             c->stream));
+  RLB_CUDA(cudaStreamSynchronize(c->stream));
+  memcpy(line, hs + 256, 3 * sizeof(double));
+  memcpy(result, hs + 256 + (kRes - kLine), sizeof(rlb_lomsac_result));
   return RLB_OK;
 }
 

@@ -147,6 +147,27 @@ cudaError_t launch_localize(const LocalizeArgs& a, int ctas, cudaStream_t st, in
 int localize_warps_per_cta();
 int localize_ctas_per_sm();
 
+// Device-resident line LO-MSAC (line_lomsac_kernel.cu, -fmad=false): one problem per CTA.
+struct LineLomsacArgs {
+  int num_problems;
+  const long long* offsets;  // [P + 1], or nullptr for ONE problem of n_single points
+  int n_single;
+  const double* xy;          // [total][2]
+  const uint32_t* seeds;     // [P], or nullptr: seed_single
+  uint32_t seed_single;
+  rlb_localize_options opt;
+  double* lines;                 // [P][3], in/out
+  rlb_localize_result* results;  // [P]
+  int32_t* inliers;              // [total] or nullptr
+  int32_t* lists;                // scratch [ctas][3][nmax]
+  int nmax;
+  unsigned int* ticket;  // problem counter, zero before the launch
+  int smem_points;       // problems up to this size are staged in dynamic shared memory (0: never)
+};
+cudaError_t launch_line_lomsac(const LineLomsacArgs& a, int ctas, cudaStream_t st, int* launches);
+int line_lomsac_smem_points();
+int line_lomsac_ctas_per_sm(int smem_points);
+
 inline int model_size_of(int kind) { return kind == RLB_KIND_POSE ? 12 : 3; }
 inline int model_size_of(const DeviceData& d) {
   return d.kind == RLB_KIND_CUSTOM ? d.model_doubles : model_size_of(d.kind);

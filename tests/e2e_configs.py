@@ -53,11 +53,23 @@ def main():
         ost, t_cpu = best_of(cpu)
         row = {"config": f"C1 line N=10000 outlier_ratio={ratio}", "iterations": ost.num_iterations,
                "inliers": ost.best_num_inliers, "cpu_s": t_cpu}
+        # host-driven loop (one launch per pass), f64 and f32 sweeps
+        os.environ["RLB_HOST_DRIVER"] = "1"
         for name, prec in (("gpu_f64_s", 0), ("gpu_f32_s", 1)):
             (m, st), t = best_of(lambda: H.estimate_line(opts, xy, precision=prec))
             assert st["num_iterations"] == ost.num_iterations and st["best_num_inliers"] == ost.best_num_inliers
             row[name] = t
             row["single_passes"], row["batches"] = st["single_passes"], st["batches"]
+        os.environ.pop("RLB_HOST_DRIVER")
+        # device-resident driver (the default of the drop-in layer for LineEstimator): the whole run in one launch;
+        # wall time includes the upload of the data set at solver construction, like the rows above
+        (m, st), t = best_of(lambda: H.estimate_line(opts, xy), reps=5)
+        assert st["num_iterations"] == ost.num_iterations and st["best_num_inliers"] == ost.best_num_inliers
+        assert st["batches"] == 0
+        row["gpu_device_resident_s"] = t
+        row["device_resident_estimate_s"] = st["seconds"]  # EstimateModel alone (solver already constructed)
+        row["device_resident_passes"] = st["single_passes"]
+        row["speedup_device_resident"] = t_cpu / t
         rows.append(row)
 
     # ---- C2: camera_pose_estimation.cc, N = 10k, 50 % outliers, min = max = 10,000 hypotheses ----
