@@ -260,13 +260,17 @@ class LocallyOptimizedMSAC : public RansacBase {
     o.non_min_sample_mult = options.non_min_sample_multiplier_;
     o.lo_start = options.lo_starting_iterations_;
     o.final_lsq = options.final_least_squares_ ? 1 : 0;
-    o.debug_flags = 0;
+    // One CTA runs the whole problem; a run that turns out to need thousands of hypotheses (very low
+    // inlier ratios) is handed back after 384 iterations and restarts in the loop below, whose sweeps
+    // use the whole GPU. Same run either way.
+    o.debug_flags = 4;
     double packed[16] = {0.0};
     Solver::PackModel(*best_model, packed);  // read by the final least-squares step (ransac.h:257-259)
     rlb_lomsac_result r;
     std::vector<int> inliers;
     if (!solver.device_lomsac(o, options.random_seed_, packed, &r, &inliers)) return false;
     RansacStatistics& stats = *statistics;
+    if (r.success == 2) return false;
     if (!r.success) return true;
     stats.num_iterations = r.num_iterations;
     stats.best_num_inliers = r.num_inliers;

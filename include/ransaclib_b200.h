@@ -211,7 +211,9 @@ typedef struct rlb_localize_options {
   int32_t non_min_sample_mult;     /* x4 must be <= 32 */
   uint32_t lo_start;
   int32_t final_lsq;
-  int32_t debug_flags;             /* bit 0: force the sequential path of every shuffle (tests) */
+  int32_t debug_flags;             /* bit 0: force the sequential path of every shuffle (tests);
+                                    * bit 2 (line LO-MSAC only): a run that still needs > 3000 hypotheses after
+                                    * 384 iterations is handed back: result.success = 2, nothing else written */
 } rlb_localize_options;
 
 typedef struct rlb_localize_result {

@@ -53,6 +53,7 @@ constexpr int kWarps = kT / 32;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr double kNever = DBL_MAX;
 constexpr int kFirstBatch = 128;
+constexpr uint32_t kBailAfter = 384u, kBailRemaining = 3000u;  // see run_problem (debug_flags bit 2)
 constexpr int kSuper = kT * 32;  // points per ordered-compaction round (one 32-bit mask per lane)
 
 struct Line {
@@ -722,6 +723,22 @@ __device__ Line run_problem(Shared& sh, const Line initial, rlb_localize_result*
       // Speculate on the next iterations: samples are a pure function of the sampler stream,
       // hypotheses do not depend on the LO stream.
       const uint32_t bound = max(max_iters, it + 1u);
+      if ((o.debug_flags & 4) && it >= kBailAfter && bound - it > kBailRemaining) {
+        // One SM sweeps ~7 hypothesis x point evaluations per cycle; a run that still needs thousands
+        // of hypotheses is better served by the whole-GPU sweep of the host-driven loop. The caller
+        // allowed handing it back (same run from scratch there: results do not depend on the driver).
+        if (threadIdx.x == 0) {
+          res->success = 2;
+          res->num_inliers = 0;
+          res->num_iterations = it;
+          res->num_lo = num_lo;
+          res->score = kNever;
+          res->inlier_ratio = 0.0;
+          res->passes = sh.passes;
+          res->lsq_calls = sh.lsq_calls;
+        }
+        return initial;
+      }
       batch_first = it;
       batch_count = min(next_batch, bound - it);
       next_batch = min(next_batch * 2u, static_cast<uint32_t>(kT));

@@ -65,7 +65,7 @@ def main():
         # wall time includes the upload of the data set at solver construction, like the rows above
         (m, st), t = best_of(lambda: H.estimate_line(opts, xy), reps=5)
         assert st["num_iterations"] == ost.num_iterations and st["best_num_inliers"] == ost.best_num_inliers
-        assert st["batches"] == 0
+        row["handed_back_to_host_loop"] = bool(st["batches"] > 0)  # runs needing > 3000 hypotheses after 384
         row["gpu_device_resident_s"] = t
         row["device_resident_estimate_s"] = st["seconds"]  # EstimateModel alone (solver already constructed)
         row["device_resident_passes"] = st["single_passes"]

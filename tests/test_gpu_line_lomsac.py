@@ -195,6 +195,31 @@ def test_drop_in_layer_uses_it_and_agrees_with_the_host_driven_loop():
     assert runs["0"][1]["batches"] == 0 and runs["1"][1]["batches"] > 0  # which driver ran
 
 
+def test_long_runs_are_handed_back_when_allowed(ctx):
+    """debug bit 2 (set by the drop-in layer): a run that still needs thousands of hypotheses after 384
+    iterations returns success = 2 with the model untouched, and LocallyOptimizedMSAC restarts it in the
+    host-driven loop (whole-GPU sweeps): same result as the oracle, and as the kernel left alone."""
+    from ransaclib_b200 import host as H
+
+    xy = synth.line_instance(1011, 100, 9900)  # 1 % inliers: ~10,000 iterations
+    kw = dict(sq_thr=1e-4, min_iters=100, max_iters=100000)
+    om, ost, oinl = oracle_line(xy, 11, **kw)
+    assert ost.num_iterations > 5000
+    sc = ctx.line_scorer(xy)
+    init = np.array([1.0, 2.0, 3.0])
+    line, r, _ = sc.line_lomsac(ctx.lomsac_options(debug_flags=4, **kw), 11, line=init)
+    assert r["success"] == 2 and line.tolist() == init.tolist() and 384 <= r["num_iterations"] < 1024
+    line, r, inl = sc.line_lomsac(ctx.lomsac_options(**kw), 11)  # not allowed to hand back: runs to the end
+    assert r["success"] == 1 and r["num_iterations"] == ost.num_iterations and inl.tolist() == oinl.tolist()
+    sc.close()
+    opts = H.LORansacOptions(squared_inlier_threshold_=1e-4, random_seed_=11, min_num_iterations_=100,
+                             max_num_iterations_=100000)
+    m, st = H.estimate_line(opts, xy)
+    assert st["batches"] > 0  # the host-driven loop finished it
+    assert st["num_iterations"] == ost.num_iterations and st["inlier_indices"].tolist() == oinl.tolist()
+    np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+
+
 def test_bad_options_fail_loudly(ctx):
     from ransaclib_b200 import _capi
 
