@@ -25,11 +25,11 @@ timeout 300 ncu --set full --clock-control none --import-source on -k regex:inli
 # device-pointer entry point only: under ncu the pipelined host API would wait for copies that never start
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:localize -c 1 -f -o $O/${TAG}_localize \
   python tools/time_localize.py 2368 dev 1 > $O/${TAG}_ncu_localize.log 2>&1; echo "ncu localize rc=$?"
-# device-resident line LO-MSAC: latency / throughput / phase counters, the configs[0..2] end-to-end table, ncu of a
-# batch launch (one CTA per SM)
+# device-resident line LO-MSAC: latency / throughput / phase counters, the configs[0..2] end-to-end table, ncu of the
+# first launch (one problem = one CTA: the latency view)
 timeout 200 python tools/time_line_lomsac.py 592 10000 0.5 > $O/${TAG}_line_lomsac.json 2> $O/${TAG}_line_lomsac.err; echo "line lomsac rc=$?"
 timeout 400 python tests/e2e_configs.py > $O/${TAG}_e2e_configs.json 2> $O/${TAG}_e2e_configs.err; echo "e2e configs rc=$?"
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:line_lomsac -c 1 -f -o $O/${TAG}_line_lomsac \
-  python tools/time_line_lomsac.py 148 10000 0.5 > $O/${TAG}_ncu_line_lomsac.log 2>&1; echo "ncu line lomsac rc=$?"
+  python tools/time_line_lomsac.py 8 10000 0.5 > $O/${TAG}_ncu_line_lomsac.log 2>&1; echo "ncu line lomsac rc=$?"
 head -c 600 $O/${TAG}_bench_c5.json; echo
 head -c 600 $O/${TAG}_bench_c4.json; echo
