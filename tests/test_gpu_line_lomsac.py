@@ -220,6 +220,16 @@ def test_long_runs_are_handed_back_when_allowed(ctx):
     np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
 
 
+def test_without_inlier_output(ctx):
+    """inliers = NULL: the best model's list lives in scratch; models, counts and scores do not change."""
+    xy, off = make_problems([(40 + q, 500, 300) for q in range(5)])
+    seeds = np.arange(9, 14, dtype=np.uint32)
+    opt = ctx.lomsac_options(sq_thr=1e-4, final_lsq=1)
+    a = ctx.line_lomsac_batch(off, xy, seeds, opt)
+    b = ctx.line_lomsac_batch(off, xy, seeds, opt, want_inliers=False)
+    assert b[2] is None and a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
+
+
 def test_bad_options_fail_loudly(ctx):
     from ransaclib_b200 import _capi
 
