@@ -259,6 +259,28 @@ int rlbh_sample_uniform(uint32_t seed, int n, int s, int k, int32_t* out) {
   });
 }
 
+// The drivers' local-optimisation stream on its own (host only): `reps` consecutive
+// utils::RandomShuffleAndResize(target, Mt19937*, iota(n)) on one engine -> kept prefix of the last one,
+// the engine's next raw output (checks the number of consumed draws) and, in first_words[0..8), the
+// engine's first outputs after seeding.
+int rlbh_shuffle_and_resize(uint32_t seed, int n, int target, int reps, int32_t* out, uint32_t* next_draw,
+                            uint32_t* first_words) {
+  return Guard([&] {
+    utils::Mt19937 probe(seed);
+    for (int i = 0; i < 8; ++i) first_words[i] = probe();
+    utils::Mt19937 rng;
+    rng.seed(seed);
+    std::vector<int> v;
+    for (int r = 0; r < reps; ++r) {
+      v.resize(n);
+      for (int i = 0; i < n; ++i) v[i] = i;
+      utils::RandomShuffleAndResize(target, &rng, &v);
+    }
+    for (int i = 0; i < target; ++i) out[i] = v[i];
+    *next_draw = rng();
+  });
+}
+
 // k hybrid samples over T data types; sizes[k][T] per draw; weights == NULL: HybridUniformSampling,
 // else HybridBiasedSampling with the concatenated per-type weights. out[k][T][max_size], -1 padded.
 int rlbh_sample_hybrid(uint32_t seed, int T, const int32_t* num_data, const double* weights, int k,

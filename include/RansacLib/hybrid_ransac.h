@@ -122,7 +122,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
     const double kNever = std::numeric_limits<double>::max();
     Model best_minimal_model;
     double best_minimal_score = kNever;
-    std::mt19937 rng;
+    utils::Mt19937 rng;
     rng.seed(options.random_seed_);
     const int precision = solver.device_scorer().precision();
 
@@ -237,7 +237,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
   void Speculate(const HybridLORansacOptions& options, const HybridSolver& solver,
                  const std::vector<double>& priors, const std::vector<std::vector<int>>& sample_sizes,
                  const HybridRansacStatistics& stats, const std::vector<uint32_t>& max_per_solver,
-                 std::mt19937 rng_copy, Sampler sampler_copy, const uint32_t first, const uint32_t want,
+                 utils::Mt19937 rng_copy, Sampler sampler_copy, const uint32_t first, const uint32_t want,
                  const int precision, Batch* b) const {
     const gpu::DeviceScorer& dev = solver.device_scorer();
     b->first = first;
@@ -285,7 +285,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
   // Eq. 1 of Camposeco et al. (reference hybrid_ransac.h:324-384).
   int SelectMinimalSolver(const HybridSolver& solver, const std::vector<double>& priors,
                           const HybridRansacStatistics& stats, const uint32_t min_num_iterations,
-                          std::mt19937* rng) const {
+                          utils::Mt19937* rng) const {
     const int num_solvers = static_cast<int>(priors.size());
     std::vector<std::vector<int>> sizes;
     solver.min_sample_sizes(&sizes);
@@ -384,7 +384,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
 
   // Second half of LeastSquaresFit (:578-594) once the inlier lists are known.
   void FitOnInliers(const HybridLORansacOptions& options, const HybridSolver& solver,
-                    const int solver_type, std::mt19937* rng, std::vector<std::vector<int>>* inliers,
+                    const int solver_type, utils::Mt19937* rng, std::vector<std::vector<int>>* inliers,
                     Model* m) const {
     std::vector<std::vector<int>> sizes;
     solver.min_sample_sizes(&sizes);
@@ -401,7 +401,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
   // reference's behaviour that the relaxed thresholds are initialised once and keep
   // shrinking over all LO steps (they become negative).
   void LocalOptimization(const HybridLORansacOptions& options, const HybridSolver& solver,
-                         const int solver_type, std::mt19937* rng, Model* best_minimal_model,
+                         const int solver_type, utils::Mt19937* rng, Model* best_minimal_model,
                          double* score_best_minimal_model, int* best_solver_type) const {
     const int num_types = solver.num_data_types();
     std::vector<double> relaxed = options.squared_inlier_thresholds_;

@@ -131,7 +131,7 @@ class LocallyOptimizedMSAC : public RansacBase {
       return stats.best_num_inliers;
 
     Sampler sampler(options.random_seed_, solver);
-    std::mt19937 rng;  // local optimisation's own stream (ransac.h:142-144)
+    utils::Mt19937 rng;  // local optimisation's own stream (ransac.h:142-144)
     rng.seed(options.random_seed_);
 
     uint32_t max_iters = std::max(options.max_num_iterations_, options.min_num_iterations_);
@@ -414,7 +414,7 @@ class LocallyOptimizedMSAC : public RansacBase {
 
   // [ScoreModel(m) + UpdateBestModel] fused with the LeastSquaresFit(fit_thr, m) that follows
   // it in the reference (ransac.h:409-420 for the fit).
-  void ScoreThenFit(const LORansacOptions& options, const Solver& solver, std::mt19937* rng,
+  void ScoreThenFit(const LORansacOptions& options, const Solver& solver, utils::Mt19937* rng,
                     const bool want_score, const double fit_thr, Model* m, double* best_score,
                     Model* best) const {
     const double thr = options.squared_inlier_threshold_;
@@ -430,7 +430,7 @@ class LocallyOptimizedMSAC : public RansacBase {
 
   // Algorithms 2 and 3 of Lebeda et al.; sequence of passes, shuffles and solver calls as
   // reference ransac.h:341-407, with score/inlier passes on the same model fused.
-  void LocalOptimization(const LORansacOptions& options, const Solver& solver, std::mt19937* rng,
+  void LocalOptimization(const LORansacOptions& options, const Solver& solver, utils::Mt19937* rng,
                          Model* best_minimal_model, double* score_best_minimal_model) const {
     const int num_data = solver.num_data();
     const int min_non_min = solver.non_minimal_sample_size();

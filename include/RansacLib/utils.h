@@ -56,6 +56,132 @@ inline void RandomShuffleAndResize(const std::vector<int> sample_sizes, std::mt1
   }
 }
 
+// ---- the local-optimisation stream of the GPU drivers ------------------------------------------
+// The reference's LO spends most of its host time here: every LeastSquaresFit / LO step shuffles the
+// WHOLE inlier list (n - 1 draws and n - 1 random swaps, utils.h:48-73) to keep <= 28 entries. The
+// drivers in ransac.h / hybrid_ransac.h only need (a) the kept prefix and (b) the engine left exactly
+// where std::mt19937 would be, so they use an engine with the same output stream whose block of 624
+// tempered words is accessible: the draws of the steps that cannot touch the prefix are consumed by a
+// branch-free (vectorisable) Lemire test over the block, and only a rejected draw (probability
+// range / 2^32) is replayed one by one. Bit-identical to the functions above on std::mt19937
+// (tests: golden vectors of the reference + repeated shuffles on one engine, CPU only).
+class Mt19937 {
+ public:
+  typedef uint32_t result_type;
+  static constexpr result_type min() { return 0u; }
+  static constexpr result_type max() { return 0xffffffffu; }
+  static constexpr result_type default_seed = 5489u;
+
+  Mt19937() { seed(default_seed); }
+  explicit Mt19937(const uint32_t s) { seed(s); }
+
+  void seed(const uint32_t s) {  // std::mt19937::seed(value)
+    uint32_t x = s;
+    state_[0] = x;
+    for (uint32_t i = 1; i < 624u; ++i) {
+      x = 1812433253u * (x ^ (x >> 30)) + i;
+      state_[i] = x;
+    }
+    idx_ = 624;
+  }
+
+  result_type operator()() {
+    if (idx_ >= 624) Refill();
+    return out_[idx_++];
+  }
+
+  void discard(unsigned long long z) {
+    for (; z > 0; --z) (*this)();
+  }
+
+  // std::uniform_int_distribution<int>(0, range - 1) of libstdc++ (GCC >= 11) on this engine:
+  // Lemire's multiply-shift with rejection.
+  uint32_t Below(const uint32_t range) {
+    uint64_t prod = static_cast<uint64_t>((*this)()) * range;
+    uint32_t low = static_cast<uint32_t>(prod);
+    if (low < range) {
+      const uint32_t thresh = (0u - range) % range;
+      while (low < thresh) {
+        prod = static_cast<uint64_t>((*this)()) * range;
+        low = static_cast<uint32_t>(prod);
+      }
+    }
+    return static_cast<uint32_t>(prod >> 32);
+  }
+
+  // Consumes the draws of Fisher-Yates steps i = first .. first + count - 1 over a list of n entries
+  // (step i draws from [i, n - 1], i.e. range n - i) without using their values.
+  void ConsumeShuffleDraws(const int n, int first, int count) {
+    while (count > 0) {
+      if (idx_ >= 624) Refill();
+      const int chunk = std::min(count, 624 - idx_);
+      const uint32_t* w = out_ + idx_;
+      const uint32_t range0 = static_cast<uint32_t>(n - first);
+      uint32_t maybe_rejected = 0u;
+      for (int k = 0; k < chunk; ++k) {
+        const uint32_t range = range0 - static_cast<uint32_t>(k);
+        const uint32_t low = w[k] * range;  // low 32 bits of the 64-bit product
+        maybe_rejected |= (low < range) ? 1u : 0u;
+      }
+      if (!maybe_rejected) {
+        idx_ += chunk;
+      } else {
+        for (int k = 0; k < chunk; ++k) (void)Below(static_cast<uint32_t>(n - (first + k)));
+      }
+      first += chunk;
+      count -= chunk;
+    }
+  }
+
+ private:
+  void Refill() {
+    uint32_t* s = state_;
+    for (int k = 0; k < 227; ++k) s[k] = Twist(s[k], s[k + 1], s[k + 397]);
+    for (int k = 227; k < 623; ++k) s[k] = Twist(s[k], s[k + 1], s[k - 227]);
+    s[623] = Twist(s[623], s[0], s[396]);
+    for (int k = 0; k < 624; ++k) {
+      uint32_t y = s[k];
+      y ^= y >> 11;
+      y ^= (y << 7) & 0x9d2c5680u;
+      y ^= (y << 15) & 0xefc60000u;
+      y ^= y >> 18;
+      out_[k] = y;
+    }
+    idx_ = 0;
+  }
+  static uint32_t Twist(const uint32_t a, const uint32_t b, const uint32_t src) {
+    const uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
+    return src ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+  }
+
+  uint32_t state_[624];
+  uint32_t out_[624];  // the current block, tempered
+  int idx_;            // next word of out_; 624 = exhausted
+};
+
+// utils.h:69-73 on Mt19937: same kept prefix, same engine position afterwards. Only the first
+// min(target_size, n - 1) steps can move an entry into the prefix; later steps swap positions >= i.
+inline void RandomShuffleAndResize(const int target_size, Mt19937* rng, std::vector<int>* v) {
+  const int n = static_cast<int>(v->size());
+  const int steps = n > 0 ? n - 1 : 0;
+  const int t = std::max(0, std::min(target_size, steps));
+  for (int i = 0; i < t; ++i) {
+    const int j = i + static_cast<int>(rng->Below(static_cast<uint32_t>(n - i)));
+    std::swap((*v)[i], (*v)[j]);
+  }
+  rng->ConsumeShuffleDraws(n, t, steps - t);
+  v->resize(target_size);
+}
+
+// utils.h:96-105 on Mt19937.
+inline void RandomShuffleAndResize(const std::vector<int> sample_sizes, Mt19937* rng,
+                                   std::vector<std::vector<int>>* v) {
+  for (size_t t = 0; t < v->size(); ++t) {
+    const int have = static_cast<int>((*v)[t].size());
+    RandomShuffleAndResize(std::min(have, sample_sizes[t]), rng, &(*v)[t]);
+  }
+}
+
 namespace detail {
 inline uint32_t IterationsFor(const double prob_all_inlier_sample, const double prob_missing,
                               const uint32_t min_it, const uint32_t max_it) {

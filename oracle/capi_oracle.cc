@@ -345,6 +345,26 @@ void RLO(shuffle_and_resize)(uint32_t seed, int n, int target, int32_t* out,
   *next_draw = static_cast<uint32_t>(rng());
 }
 
+// `reps` consecutive shuffles of iota(n) on ONE engine (the local-optimisation stream shuffles list
+// after list); out = the kept prefix of the last one.
+void RLO(shuffle_and_resize_reps)(uint32_t seed, int n, int target, int reps, int32_t* out,
+                                  uint32_t* next_draw) {
+  std::mt19937 rng;
+  rng.seed(seed);
+  std::vector<int> v;
+  for (int r = 0; r < reps; ++r) {
+    v.resize(n);
+    std::iota(v.begin(), v.end(), 0);
+#ifdef RLO_USE_REFERENCE
+    ransac_lib::utils::RandomShuffleAndResize(target, &rng, &v);
+#else
+    shuffle_and_resize(target, &rng, &v);
+#endif
+  }
+  for (int i = 0; i < target; ++i) out[i] = v[i];
+  *next_draw = static_cast<uint32_t>(rng());
+}
+
 // ---- pose ----------------------------------------------------------------------
 void RLO(pixels_to_rays)(double fx, double fy, int n, const double* p2d, double* rays) {
   PoseSolver::PixelsToViewingRays(fx, fy, n, p2d, rays);

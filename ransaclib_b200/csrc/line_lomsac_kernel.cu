@@ -912,12 +912,11 @@ __global__ void __launch_bounds__(kT, 1) line_lomsac_kernel(const LineLomsacArgs
 cudaError_t launch_line_lomsac(const LineLomsacArgs& a, int ctas, cudaStream_t st, int* launches) {
   ++*launches;
   const size_t dyn = static_cast<size_t>(a.smem_points) * sizeof(double2);
-  static size_t configured = 0;
-  if (dyn > configured) {
+  if (dyn > 0) {
+    // per device and cheap next to a launch: set every time rather than remember per device
     cudaError_t e = cudaFuncSetAttribute(line_lomsac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(dyn));
     if (e != cudaSuccess) return e;
-    configured = dyn;
   }
   line_lomsac_kernel<<<ctas, kT, dyn, st>>>(a);
   return cudaGetLastError();

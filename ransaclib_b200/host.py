@@ -11,7 +11,8 @@ import numpy as np
 
 from . import _capi
 
-_HOST_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libransaclib_b200_host.so")
+_HOST_PATH = os.environ.get("RLB_HOST_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib",
+                                                           "libransaclib_b200_host.so")
 
 
 class _Options(C.Structure):
@@ -203,6 +204,18 @@ def sample_uniform(seed, n, s, k):
     out = np.empty((k, s), np.int32)
     _check(_load().rlbh_sample_uniform(C.c_uint32(seed), n, s, k, _capi.ptr(out)))
     return out
+
+
+def shuffle_and_resize(seed, n, target, reps=1):
+    """`reps` consecutive RandomShuffleAndResize(target, ., iota(n)) on the drivers' own engine (include/RansacLib/
+    utils.h: Mt19937, block-wise consumption of the draws that cannot reach the kept prefix); host only.
+    -> (kept prefix of the last shuffle, next raw engine output, first 8 engine outputs after seeding)."""
+    out = np.empty(max(target, 1), np.int32)
+    nxt = C.c_uint32()
+    first = np.empty(8, np.uint32)
+    _check(_load().rlbh_shuffle_and_resize(C.c_uint32(seed), n, target, reps, _capi.ptr(out), C.byref(nxt),
+                                           _capi.ptr(first)))
+    return out[:target].copy(), nxt.value, first
 
 
 def sample_hybrid(seed, num_data, sizes, weights=None):

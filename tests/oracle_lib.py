@@ -79,6 +79,8 @@ def _bind(lib, prefix):
                                            [C.c_int, f64p, C.c_double, i32p, C.c_uint32, C.c_uint32])
     ns.shuffle_and_resize = fn("shuffle_and_resize", None,
                                [C.c_uint32, C.c_int, C.c_int, i32p, C.POINTER(C.c_uint32)])
+    ns.shuffle_and_resize_reps = fn("shuffle_and_resize_reps", None,
+                                    [C.c_uint32, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_uint32)])
     ns.pixels_to_rays = fn("pixels_to_rays", None, [C.c_double, C.c_double, C.c_int, f64p, f64p])
     ns.pose_errors = fn("pose_errors", None, [f64p, C.c_double, C.c_double, C.c_int, f64p, f64p, f64p])
     ns.pose_score_models = fn("pose_score_models", None,

@@ -100,6 +100,33 @@ def test_shuffle_consumes_same_draws(G, O):
         assert nxt.value == c["next_draw"]
 
 
+def test_drivers_fast_shuffle_is_the_reference_shuffle(G, O):
+    """include/RansacLib/utils.h: the drivers' Mt19937 has std::mt19937's stream and their
+    RandomShuffleAndResize (real swaps only for the steps that can reach the kept prefix, the other draws
+    consumed block-wise with a vectorisable Lemire test) keeps the same prefix and leaves the engine where the
+    reference's full Fisher-Yates would: golden vectors of the reference, then repeated shuffles on one
+    engine (block boundaries, rejected draws at large n) against the oracle / the reference headers."""
+    from ransaclib_b200 import host as H
+
+    mt = np.random.RandomState(1234)  # numpy's legacy seeding is init_genrand, like std::mt19937::seed
+    _, _, first = H.shuffle_and_resize(1234, 5, 2)
+    assert first.tolist() == [int(x) for x in mt.randint(0, 2 ** 32, 8, dtype=np.uint64)]
+    for c in G["shuffle_and_resize"]:
+        out, nxt, _ = H.shuffle_and_resize(c["seed"], c["n"], c["target"])
+        assert out.tolist() == c["out"] and nxt == c["next_draw"]
+    ref = ol.reference() or O
+    cases = [(1, 2, 1, 3), (2, 3, 2, 5), (3, 14, 14, 40), (4, 15, 14, 40), (5, 100, 6, 30), (6, 623, 14, 7),
+             (7, 624, 14, 7), (8, 625, 14, 7), (9, 5000, 14, 50), (10, 5000, 28, 50), (11, 100000, 14, 12),
+             (12, 2000000, 6, 3), (13, 40, 32, 9), (14, 10, 14, 4), (15, 1, 1, 2), (16, 0, 0, 2)]
+    for seed, n, target, reps in cases:
+        want = np.empty(max(target, 1), np.int32)
+        wn = C.c_uint32()
+        ref.shuffle_and_resize_reps(seed, n, target, reps, want, C.byref(wn))
+        out, nxt, _ = H.shuffle_and_resize(seed, n, target, reps)
+        assert out.tolist() == want[:target].tolist(), (seed, n, target, reps)
+        assert nxt == wn.value, (seed, n, target, reps)
+
+
 def test_pose_scoring_and_inliers(G, O):
     p = G["pose"]
     p2, p3, models = np.array(p["points2D"]), np.array(p["points3D"]), np.array(p["models"])
