@@ -74,6 +74,10 @@ struct rlb_ctx {
   DevBuf one_model, idx, tile_score, status, header;
   // pinned host staging for tiny results
   void* h_small = nullptr;
+  // pinned staging of one hypothesis batch (samples up, models / valid / scores / counts back): the callers'
+  // buffers are pageable, and every pageable cudaMemcpyAsync is a synchronous staged copy of its own
+  void* h_stage = nullptr;
+  size_t stage_cap = 0;
   // optional per-kernel timing (bench.py's roofline numbers)
   bool timing = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // sweep begin/end, inlier begin/end
@@ -566,6 +570,7 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   pool_drain(c);
   if (c->h_small) cudaFreeHost(c->h_small);
+  if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_ready) cudaFreeHost(c->h_ready);
   c->loc_soa.release();
@@ -1079,7 +1084,29 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
   RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));
   RLB_CUDA(c->scores.ensure(static_cast<size_t>(k) * sizeof(double)));
   RLB_CUDA(c->counts.ensure(static_cast<size_t>(k) * sizeof(int32_t)));
-  RLB_CUDA(cudaMemcpyAsync(c->samples.p, samples, static_cast<size_t>(k) * ss * sizeof(int32_t),
+  // Small batches (the drivers' speculative rounds) go through pinned staging: truly asynchronous copies,
+  // one synchronisation, then plain memcpy into the callers' pageable buffers.
+  const size_t b_samples = static_cast<size_t>(k) * ss * sizeof(int32_t);
+  const size_t b_models = static_cast<size_t>(k) * md * sizeof(double), b_valid = static_cast<size_t>(k);
+  const size_t b_scores = static_cast<size_t>(k) * sizeof(double), b_counts = static_cast<size_t>(k) * sizeof(int32_t);
+  const size_t o_models = (b_samples + 63) & ~size_t(63), o_valid = o_models + b_models;
+  const size_t o_scores = (o_valid + b_valid + 63) & ~size_t(63), o_counts = o_scores + b_scores;
+  const size_t stage_bytes = o_counts + b_counts;
+  const bool staged = stage_bytes <= (size_t(1) << 20);
+  char* stage = nullptr;
+  if (staged) {
+    if (stage_bytes > c->stage_cap) {
+      if (c->h_stage) cudaFreeHost(c->h_stage);
+      c->h_stage = nullptr;
+      c->stage_cap = 0;
+      const size_t cap = std::max<size_t>(stage_bytes, 256 * 1024);
+      RLB_CUDA(cudaMallocHost(&c->h_stage, cap));
+      c->stage_cap = cap;
+    }
+    stage = static_cast<char*>(c->h_stage);
+    memcpy(stage, samples, b_samples);
+  }
+  RLB_CUDA(cudaMemcpyAsync(c->samples.p, staged ? static_cast<const void*>(stage) : samples, b_samples,
                            cudaMemcpyHostToDevice, c->stream));
   rc = solve_dev(s, solver, k, c->samples.as<int32_t>(), sq_thr[0], c->models.as<double>(),
                  c->valid.as<uint8_t>());
@@ -1090,20 +1117,27 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
                  c->scores.as<double>(), counts ? c->counts.as<int32_t>() : nullptr, d_best, d_best_model);
   if (rc) return rc;
   if (models)
-    RLB_CUDA(cudaMemcpyAsync(models, c->models.p, static_cast<size_t>(k) * md * sizeof(double),
+    RLB_CUDA(cudaMemcpyAsync(staged ? static_cast<void*>(stage + o_models) : models, c->models.p, b_models,
                              cudaMemcpyDeviceToHost, c->stream));
   if (valid)
-    RLB_CUDA(cudaMemcpyAsync(valid, c->valid.p, static_cast<size_t>(k), cudaMemcpyDeviceToHost, c->stream));
+    RLB_CUDA(cudaMemcpyAsync(staged ? static_cast<void*>(stage + o_valid) : valid, c->valid.p, b_valid,
+                             cudaMemcpyDeviceToHost, c->stream));
   if (scores)
-    RLB_CUDA(cudaMemcpyAsync(scores, c->scores.p, static_cast<size_t>(k) * sizeof(double),
+    RLB_CUDA(cudaMemcpyAsync(staged ? static_cast<void*>(stage + o_scores) : scores, c->scores.p, b_scores,
                              cudaMemcpyDeviceToHost, c->stream));
   if (counts)
-    RLB_CUDA(cudaMemcpyAsync(counts, c->counts.p, static_cast<size_t>(k) * sizeof(int32_t),
+    RLB_CUDA(cudaMemcpyAsync(staged ? static_cast<void*>(stage + o_counts) : counts, c->counts.p, b_counts,
                              cudaMemcpyDeviceToHost, c->stream));
   char* hs = static_cast<char*>(c->h_small);
   RLB_CUDA(cudaMemcpyAsync(hs, c->small.as<char>() + kSmallBest, sizeof(BestRec), cudaMemcpyDeviceToHost, c->stream));
   RLB_CUDA(cudaMemcpyAsync(hs + 128, d_best_model, 12 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   RLB_CUDA(cudaStreamSynchronize(c->stream));
+  if (staged) {
+    if (models) memcpy(models, stage + o_models, b_models);
+    if (valid) memcpy(valid, stage + o_valid, b_valid);
+    if (scores) memcpy(scores, stage + o_scores, b_scores);
+    if (counts) memcpy(counts, stage + o_counts, b_counts);
+  }
   const BestRec* hb = reinterpret_cast<const BestRec*>(hs);
   if (best_id) *best_id = static_cast<int32_t>(hb->id);
   if (best_score) *best_score = hb->score;
