@@ -24,6 +24,8 @@ class LineEstimator {
     scorer_.InitLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n, data_.data());
   }
 
+  static constexpr int kDeviceLomsacMaxPoints = 24576;  // measured crossover ~30k (tools/line_crossover.py)
+
   inline int min_sample_size() const { return 2; }
   inline int non_minimal_sample_size() const { return 6; }
   inline int num_data() const { return num_data_; }
@@ -68,6 +70,9 @@ class LineEstimator {
     if (opt.min_sample_mult < 1 || opt.min_sample_mult * 2 > 32 || opt.non_min_sample_mult < 0 ||
         opt.non_min_sample_mult * 2 > 32 || opt.lo_steps < 0 || opt.lsq_iters < 0)
       return false;
+    // One CTA = one SM works on the problem: beyond this size a pass over the points takes longer there
+    // than a launch of the whole-GPU pass costs, and the host-driven loop is the faster driver.
+    if (num_data_ > kDeviceLomsacMaxPoints) return false;
     inliers->resize(static_cast<size_t>(num_data_ > 0 ? num_data_ : 1));
     scorer_.LineLomsac(opt, seed, packed_model, result, reinterpret_cast<int32_t*>(inliers->data()));
     inliers->resize(static_cast<size_t>(result->num_inliers));

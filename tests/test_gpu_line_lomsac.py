@@ -220,6 +220,22 @@ def test_long_runs_are_handed_back_when_allowed(ctx):
     np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
 
 
+def test_large_problems_stay_with_the_host_driven_loop():
+    """Above LineEstimator::kDeviceLomsacMaxPoints (24,576) the drop-in layer keeps its own loop (whole-GPU
+    passes beat one SM there); the run is the oracle's either way."""
+    from ransaclib_b200 import host as H
+
+    xy = synth.line_instance(1021, 40000, 30000)
+    kw = dict(sq_thr=1e-4, min_iters=100, max_iters=100000)
+    om, ost, oinl = oracle_line(xy, 5, **kw)
+    opts = H.LORansacOptions(squared_inlier_threshold_=1e-4, random_seed_=5, min_num_iterations_=100,
+                             max_num_iterations_=100000)
+    m, st = H.estimate_line(opts, xy)
+    assert st["batches"] > 0
+    assert st["num_iterations"] == ost.num_iterations and st["inlier_indices"].tolist() == oinl.tolist()
+    np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+
+
 def test_without_inlier_output(ctx):
     """inliers = NULL: the best model's list lives in scratch; models, counts and scores do not change."""
     xy, off = make_problems([(40 + q, 500, 300) for q in range(5)])
