@@ -1371,7 +1371,9 @@ int line_lomsac_enqueue(rlb_ctx* c, int np, int max_points, const int64_t* d_off
   int smem_points = (nmax <= rlb::line_lomsac_smem_points()) ? nmax : 0;
   if (const char* e = std::getenv("RLB_LL_SMEM"))
     if (e[0] == '0') smem_points = 0;
-  const int ctas = std::max(1, std::min(np, c->sms * rlb::line_lomsac_ctas_per_sm(smem_points)));
+  int ctas = std::max(1, std::min(np, c->sms * rlb::line_lomsac_ctas_per_sm(smem_points)));
+  const size_t budget = size_t(4) << 30;  // scratch cap; fewer resident CTAs for huge problems
+  while (ctas > 1 && static_cast<size_t>(ctas) * 3 * nmax * sizeof(int32_t) > budget) ctas /= 2;
   RLB_CUDA(c->ll_lists.ensure(static_cast<size_t>(ctas) * 3 * nmax * sizeof(int32_t)));
   RLB_CUDA(cudaMemsetAsync(d_ticket, 0, 4, c->stream));
   rlb::LineLomsacArgs a;
