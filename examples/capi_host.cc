@@ -281,6 +281,19 @@ int rlbh_shuffle_and_resize(uint32_t seed, int n, int target, int reps, int32_t*
   });
 }
 
+// The same on a read-only list (list[i] = 3 i + 1): utils::ShuffleSampleFromList.
+int rlbh_shuffle_from_list(uint32_t seed, int n, int target, int reps, int32_t* out, uint32_t* next_draw) {
+  return Guard([&] {
+    utils::Mt19937 rng;
+    rng.seed(seed);
+    std::vector<int> list(n), v;
+    for (int i = 0; i < n; ++i) list[i] = 3 * i + 1;
+    for (int r = 0; r < reps; ++r) utils::ShuffleSampleFromList(target, &rng, list.data(), n, &v);
+    for (int i = 0; i < target; ++i) out[i] = v[i];
+    *next_draw = rng();
+  });
+}
+
 // k hybrid samples over T data types; sizes[k][T] per draw; weights == NULL: HybridUniformSampling,
 // else HybridBiasedSampling with the concatenated per-type weights. out[k][T][max_size], -1 padded.
 int rlbh_sample_hybrid(uint32_t seed, int T, const int32_t* num_data, const double* weights, int k,

@@ -157,6 +157,15 @@ class DeviceScorer {
           "rlb_get_inliers");
   }
 
+  // The same pass; the list stays in the context's pinned result buffer and the pointer to it is returned
+  // (valid until the next call on the scorer's context). For callers that read a sample of the list.
+  const int32_t* InliersViewAndScore(const double* model, const double* sq_thr_inl, const double* sq_thr_score,
+                                     const double* weights, int32_t* counts, double* score) const {
+    const int32_t* view = nullptr;
+    Check(rlb_get_inliers_view(s_, model, sq_thr_inl, sq_thr_score, weights, &view, counts, score),
+          "rlb_get_inliers_view");
+    return view;
+  }
  private:
   rlb_scorer* s_ = nullptr;
   int precision_ = PrecisionFromEnv();

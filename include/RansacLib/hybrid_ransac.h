@@ -324,32 +324,60 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
     return -1;
   }
 
+  // Per-type inlier lists somebody else owns: the scorer's pinned result buffer (valid until the next
+  // pass) or a std::vector<std::vector<int>>.
+  struct Lists {
+    std::vector<const int*> list;
+    std::vector<int> count;
+    Lists() {}
+    explicit Lists(const std::vector<std::vector<int>>& v) {
+      for (const auto& l : v) {
+        list.push_back(l.data());
+        count.push_back(static_cast<int>(l.size()));
+      }
+    }
+  };
+
+  // The same pass with the lists left where the scorer wrote them.
+  Lists FusedPassView(const HybridLORansacOptions& options, const HybridSolver& solver, const Model& model,
+                      const std::vector<double>& thr_inl, const bool want_score, double* score) const {
+    double packed[16];
+    HybridSolver::PackModel(model, packed);
+    int32_t counts[2] = {0, 0};
+    const int* at = reinterpret_cast<const int*>(solver.device_scorer().InliersViewAndScore(
+        packed, thr_inl.data(), want_score ? options.squared_inlier_thresholds_.data() : nullptr,
+        options.data_type_weights_.data(), counts, score));
+    Lists out;
+    for (int t = 0; t < solver.num_data_types(); ++t) {
+      out.list.push_back(at);
+      out.count.push_back(counts[t]);
+      at += counts[t];
+    }
+    return out;
+  }
+
   // Fused K=1 pass with per-type thresholds: per-type ascending inlier lists at thr_inl and
   // (optionally) the weighted MSAC score at the options' thresholds (:407-462).
   int FusedPass(const HybridLORansacOptions& options, const HybridSolver& solver, const Model& model,
                 const std::vector<double>& thr_inl, const bool want_score,
                 std::vector<std::vector<int>>* inliers, double* score) const {
+    if (inliers) {
+      const Lists v = FusedPassView(options, solver, model, thr_inl, want_score, score);
+      inliers->resize(v.list.size());
+      int total = 0;
+      for (size_t t = 0; t < v.list.size(); ++t) {
+        (*inliers)[t].assign(v.list[t], v.list[t] + v.count[t]);
+        total += v.count[t];
+      }
+      return total;
+    }
     double packed[16];
     HybridSolver::PackModel(model, packed);
-    std::vector<int> nd;
-    solver.num_data(&nd);
-    int total = 0;
-    for (int n : nd) total += n;
-    std::vector<int32_t> flat(inliers ? std::max(total, 1) : 0);
     int32_t counts[2] = {0, 0};
     solver.device_scorer().InliersAndScore(
         packed, thr_inl.data(), want_score ? options.squared_inlier_thresholds_.data() : nullptr,
-        options.data_type_weights_.data(), inliers ? flat.data() : nullptr, counts, score);
-    if (inliers) {
-      inliers->clear();
-      inliers->resize(nd.size());
-      int at = 0;
-      for (size_t t = 0; t < nd.size(); ++t) {
-        (*inliers)[t].assign(flat.begin() + at, flat.begin() + at + counts[t]);
-        at += counts[t];
-      }
-    }
-    return counts[0] + (nd.size() > 1 ? counts[1] : 0);
+        options.data_type_weights_.data(), nullptr, counts, score);
+    return counts[0] + (solver.num_data_types() > 1 ? counts[1] : 0);
   }
 
   double ScoreOnly(const HybridLORansacOptions& options, const HybridSolver& solver,
@@ -383,18 +411,21 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
   }
 
   // Second half of LeastSquaresFit (:578-594) once the inlier lists are known.
+  // The samples are copied out of the lists before the solver runs.
   void FitOnInliers(const HybridLORansacOptions& options, const HybridSolver& solver,
-                    const int solver_type, utils::Mt19937* rng, std::vector<std::vector<int>>* inliers,
-                    Model* m) const {
+                    const int solver_type, utils::Mt19937* rng, const Lists& inliers, Model* m) const {
     std::vector<std::vector<int>> sizes;
     solver.min_sample_sizes(&sizes);
-    for (int t = 0; t < solver.num_data_types(); ++t) {
-      const int have = static_cast<int>((*inliers)[t].size());
+    const int num_types = solver.num_data_types();
+    for (int t = 0; t < num_types; ++t) {
+      const int have = inliers.count[t];
       if (have < sizes[solver_type][t]) return;
       sizes[solver_type][t] = std::min(sizes[solver_type][t] * options.min_sample_multiplicator_, have);
     }
-    utils::RandomShuffleAndResize(sizes[solver_type], rng, inliers);
-    solver.LeastSquares(*inliers, m);
+    std::vector<std::vector<int>> sample(num_types);
+    for (int t = 0; t < num_types; ++t)  // utils.h:96-105, one type after the other on one engine
+      utils::ShuffleSampleFromList(sizes[solver_type][t], rng, inliers.list[t], inliers.count[t], &sample[t]);
+    solver.LeastSquares(sample, m);
   }
 
   // :500-567 with ScoreModel + the following GetInliers on the same model fused. Keeps the
@@ -411,12 +442,11 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
                 static_cast<int>(options.num_lsq_iterations_ - 1);
       relaxed[t] *= options.threshold_multiplier_;
     }
-    std::vector<std::vector<int>> inliers;
     double score = std::numeric_limits<double>::max();
 
     Model m_init = *best_minimal_model;
-    FusedPass(options, solver, m_init, relaxed, false, &inliers, nullptr);
-    FitOnInliers(options, solver, solver_type, rng, &inliers, &m_init);
+    FitOnInliers(options, solver, solver_type, rng,
+                 FusedPassView(options, solver, m_init, relaxed, false, nullptr), &m_init);
 
     // ScoreModel(m_init) + GetInliers(m_init, thresholds): the list is what every LO step's
     // first LeastSquaresFit(m_non_min = m_init, thresholds) recomputes in the reference.
@@ -425,20 +455,20 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
     UpdateBestModel(score, m_init, solver_type, score_best_minimal_model, best_minimal_model,
                     best_solver_type);
 
+    const Lists base_lists(base);
     for (int r = 0; r < options.num_lo_steps_; ++r) {
       Model m = m_init;
-      inliers = base;
-      FitOnInliers(options, solver, solver_type, rng, &inliers, &m);
+      FitOnInliers(options, solver, solver_type, rng, base_lists, &m);
       if (options.num_lsq_iterations_ <= 0) continue;
-      FusedPass(options, solver, m, relaxed, false, &inliers, nullptr);
-      FitOnInliers(options, solver, solver_type, rng, &inliers, &m);
+      FitOnInliers(options, solver, solver_type, rng,
+                   FusedPassView(options, solver, m, relaxed, false, nullptr), &m);
       for (int i = 0; i < options.num_lsq_iterations_; ++i) {
         for (int t = 0; t < num_types; ++t) relaxed[t] -= step[t];
         if (i + 1 < options.num_lsq_iterations_) {
-          FusedPass(options, solver, m, relaxed, true, &inliers, &score);
+          const Lists inliers = FusedPassView(options, solver, m, relaxed, true, &score);
           UpdateBestModel(score, m, solver_type, score_best_minimal_model, best_minimal_model,
                           best_solver_type);
-          FitOnInliers(options, solver, solver_type, rng, &inliers, &m);
+          FitOnInliers(options, solver, solver_type, rng, inliers, &m);
         } else {
           score = ScoreOnly(options, solver, m);
           UpdateBestModel(score, m, solver_type, score_best_minimal_model, best_minimal_model,

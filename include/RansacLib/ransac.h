@@ -400,6 +400,22 @@ class LocallyOptimizedMSAC : public RansacBase {
     return counts[0];
   }
 
+  // The same pass with the list left in the scorer's pinned result buffer: *list is valid until the next
+  // pass. For the LeastSquaresFit steps, which keep a short sample of a long list.
+  int FusedPassView(const Solver& solver, const Model& model, const double thr_inl, const double* thr_score,
+                    const int** list, double* score) const {
+    double packed[16];
+    Solver::PackModel(model, packed);
+    const double ti[2] = {thr_inl, thr_inl};
+    double ts[2] = {0.0, 0.0};
+    if (thr_score) ts[0] = ts[1] = *thr_score;
+    int32_t counts[2] = {0, 0};
+    *list = reinterpret_cast<const int*>(solver.device_scorer().InliersViewAndScore(
+        packed, ti, thr_score ? ts : nullptr, nullptr, counts, score));
+    if (counters) counters->single_passes += 1;
+    return counts[0];
+  }
+
   double ScoreOnly(const Solver& solver, const Model& model, const double thr) const {
     double score = std::numeric_limits<double>::max();
     FusedPass(solver, model, thr, &thr, nullptr, &score);
@@ -418,14 +434,15 @@ class LocallyOptimizedMSAC : public RansacBase {
                     const bool want_score, const double fit_thr, Model* m, double* best_score,
                     Model* best) const {
     const double thr = options.squared_inlier_threshold_;
-    std::vector<int> inliers;
+    const int* list = nullptr;
     double score = std::numeric_limits<double>::max();
-    const int n_inl = FusedPass(solver, *m, fit_thr, want_score ? &thr : nullptr, &inliers, &score);
+    const int n_inl = FusedPassView(solver, *m, fit_thr, want_score ? &thr : nullptr, &list, &score);
     if (want_score) UpdateBestModel(score, *m, best_score, best);
     if (n_inl < solver.min_sample_size()) return;
     const int cap = options.min_sample_multiplicator_ * solver.min_sample_size();
-    utils::RandomShuffleAndResize(std::min(cap, n_inl), rng, &inliers);
-    solver.LeastSquares(inliers, m);
+    std::vector<int> sample;  // copied out of the result buffer before the solver runs
+    utils::ShuffleSampleFromList(std::min(cap, n_inl), rng, list, n_inl, &sample);
+    solver.LeastSquares(sample, m);
   }
 
   // Algorithms 2 and 3 of Lebeda et al.; sequence of passes, shuffles and solver calls as
@@ -452,8 +469,8 @@ class LocallyOptimizedMSAC : public RansacBase {
                                        static_cast<int>(inliers_base.size()) / 2));
     std::vector<int> sample;
     for (int r = 0; r < options.num_lo_steps_; ++r) {
-      sample = inliers_base;
-      utils::RandomShuffleAndResize(non_min_size, rng, &sample);
+      utils::ShuffleSampleFromList(non_min_size, rng, inliers_base.data(),
+                                   static_cast<int>(inliers_base.size()), &sample);
       Model m;
       if (!solver.NonMinimalSolver(sample, &m)) continue;
       // ScoreModel(m) + LeastSquaresFit(thr, m)   (ransac.h:386-391)

@@ -182,6 +182,41 @@ inline void RandomShuffleAndResize(const std::vector<int> sample_sizes, Mt19937*
   }
 }
 
+// The same shuffle over a list the caller only has a read-only view of (the pinned result buffer of a
+// fused pass): *out receives what RandomShuffleAndResize(target_size, rng, &copy_of_list) would leave in
+// the copy, and the engine ends at the same position - without copying the n entries. The few entries the
+// first steps displace beyond the prefix are remembered in a short side list.
+inline void ShuffleSampleFromList(const int target_size, Mt19937* rng, const int* list, const int n,
+                                  std::vector<int>* out) {
+  const int steps = n > 0 ? n - 1 : 0;
+  const int t = std::max(0, std::min(target_size, steps));
+  if (t > 64) {  // long samples: the side list would be searched too often
+    out->assign(list, list + n);
+    RandomShuffleAndResize(target_size, rng, out);
+    return;
+  }
+  const int head = std::max(0, std::min(target_size, n));
+  out->assign(static_cast<size_t>(std::max(target_size, 0)), 0);
+  std::copy(list, list + head, out->begin());
+  int far_pos[64], far_val[64], num_far = 0;
+  for (int i = 0; i < t; ++i) {
+    const int j = i + static_cast<int>(rng->Below(static_cast<uint32_t>(n - i)));
+    if (j < head) {
+      std::swap((*out)[i], (*out)[j]);
+      continue;
+    }
+    int k = 0;
+    while (k < num_far && far_pos[k] != j) ++k;
+    if (k == num_far) {
+      far_pos[k] = j;
+      far_val[k] = list[j];
+      ++num_far;
+    }
+    std::swap((*out)[i], far_val[k]);
+  }
+  rng->ConsumeShuffleDraws(n, t, steps - t);
+}
+
 namespace detail {
 inline uint32_t IterationsFor(const double prob_all_inlier_sample, const double prob_missing,
                               const uint32_t min_it, const uint32_t max_it) {

@@ -138,6 +138,13 @@ int rlb_score_models_dev(rlb_scorer* s, int precision, int k, const double* d_mo
 int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl,
                     const double* sq_thr_score, const double* weights, int32_t* idx,
                     int32_t* counts, double* score);
+/* Same pass, but instead of copying the list out, *idx_view receives a pointer to the context's own pinned
+ * host copy of it (per-type lists concatenated, counts[] entries each): valid until the next call on this
+ * context. For callers that read a few entries of a long list - a LeastSquaresFit keeps <= 28 of them
+ * (ransac.h:409-420). */
+int rlb_get_inliers_view(rlb_scorer* s, const double* model, const double* sq_thr_inl,
+                         const double* sq_thr_score, const double* weights, const int32_t** idx_view,
+                         int32_t* counts, double* score);
 /* Device-output variant: d_idx (capacity sum num_data), d_header = {double score;
  * int32 count[2]; int32 pad} on the device; asynchronous. */
 int rlb_get_inliers_dev(rlb_scorer* s, const double* d_model, const double* sq_thr_inl,

@@ -24,7 +24,7 @@ SYMBOLS = [
     "rlb_scorer_create_hybrid_line", "rlb_scorer_create_pose", "rlb_scorer_create_custom",
     "rlb_custom_compile_check", "rlb_scorer_destroy", "rlb_scorer_kind",
     "rlb_scorer_num_types", "rlb_scorer_num_data", "rlb_scorer_model_size", "rlb_scorer_get_rays",
-    "rlb_score_models", "rlb_score_models_dev", "rlb_get_inliers", "rlb_get_inliers_dev",
+    "rlb_score_models", "rlb_score_models_dev", "rlb_get_inliers", "rlb_get_inliers_view", "rlb_get_inliers_dev",
     "rlb_eval_errors", "rlb_solve_line2pt_batch", "rlb_solve_point_normal_batch", "rlb_solve_p3p_batch",
     "rlb_hypothesize_and_score", "rlb_hypothesize_and_score_dev", "rlb_measure_fma_peak", "rlb_sharded_round_dev", "rlb_select_winner_dev", "rlb_ctx_set_timing", "rlb_ctx_kernel_time_ms", "rlb_ctx_last_sweep_plan",
     "rlb_localize_default_options", "rlb_localize_batch", "rlb_localize_batch_dev",
@@ -84,6 +84,7 @@ def load():
     lib.rlb_score_models.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.rlb_score_models_dev.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     lib.rlb_get_inliers.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.rlb_get_inliers_view.argtypes = [vp, vp, vp, vp, vp, C.POINTER(vp), vp, vp]
     lib.rlb_get_inliers_dev.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.rlb_eval_errors.argtypes = [vp, i32, vp, i32, vp]
     lib.rlb_solve_line2pt_batch.argtypes = [vp, i32, vp, vp, vp]

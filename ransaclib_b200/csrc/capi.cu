@@ -78,6 +78,9 @@ struct rlb_ctx {
   // buffers are pageable, and every pageable cudaMemcpyAsync is a synchronous staged copy of its own
   void* h_stage = nullptr;
   size_t stage_cap = 0;
+  // pinned copy of an inlier list too long for the zero-copy path (rlb_get_inliers_view)
+  void* h_list = nullptr;
+  size_t list_cap = 0;
   // optional per-kernel timing (bench.py's roofline numbers)
   bool timing = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // sweep begin/end, inlier begin/end
@@ -571,6 +574,7 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   pool_drain(c);
   if (c->h_small) cudaFreeHost(c->h_small);
   if (c->h_stage) cudaFreeHost(c->h_stage);
+  if (c->h_list) cudaFreeHost(c->h_list);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_ready) cudaFreeHost(c->h_ready);
   c->loc_soa.release();
@@ -873,9 +877,14 @@ int rlb_get_inliers_dev(rlb_scorer* s, const double* d_model, const double* sq_t
   return inliers_dev(s, d_model, sq_thr_inl, sq_thr_score, weights, d_idx, d_header);
 }
 
-int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl,
-                    const double* sq_thr_score, const double* weights, int32_t* idx,
-                    int32_t* counts, double* score) {
+namespace {
+// idx: copy the list there; view: hand out a pointer to the context's own pinned copy instead (valid until the
+// next call on the context). Either, both or none.
+int get_inliers_impl(rlb_scorer* s, const double* model, const double* sq_thr_inl,
+                     const double* sq_thr_score, const double* weights, int32_t* idx, const int32_t** view,
+                     int32_t* counts, double* score) {
+  const bool want_list = idx != nullptr || view != nullptr;
+  if (view) *view = nullptr;
   int rc = check_scorer(s);
   if (rc) return rc;
   rlb_ctx* c = s->ctx;
@@ -906,25 +915,38 @@ int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl
     }
     char* dres = static_cast<char*>(c->d_result);
     rc = inliers_dev(s, nullptr, sq_thr_inl, sq_thr_score, weights,
-                     idx ? reinterpret_cast<int32_t*>(dres + sizeof(InlierHeader)) : nullptr, dres, model);
+                     want_list ? reinterpret_cast<int32_t*>(dres + sizeof(InlierHeader)) : nullptr, dres, model);
     if (rc) return rc;
     RLB_CUDA(cudaStreamSynchronize(c->stream));
     h = static_cast<InlierHeader*>(c->h_result);
-    if (idx && h->count[1] > 0)
-      memcpy(idx, static_cast<char*>(c->h_result) + sizeof(InlierHeader),
-             static_cast<size_t>(h->count[1]) * sizeof(int32_t));
+    const int32_t* list = reinterpret_cast<const int32_t*>(static_cast<char*>(c->h_result) + sizeof(InlierHeader));
+    if (idx && h->count[1] > 0) memcpy(idx, list, static_cast<size_t>(h->count[1]) * sizeof(int32_t));
+    if (view) *view = list;
   } else {
     RLB_CUDA(c->header.ensure(sizeof(InlierHeader)));
-    if (idx) RLB_CUDA(c->idx.ensure(static_cast<size_t>(std::max(ntot, 1)) * sizeof(int32_t)));
-    rc = inliers_dev(s, nullptr, sq_thr_inl, sq_thr_score, weights, idx ? c->idx.as<int32_t>() : nullptr,
+    if (want_list) RLB_CUDA(c->idx.ensure(static_cast<size_t>(std::max(ntot, 1)) * sizeof(int32_t)));
+    rc = inliers_dev(s, nullptr, sq_thr_inl, sq_thr_score, weights, want_list ? c->idx.as<int32_t>() : nullptr,
                      c->header.p, model);
     if (rc) return rc;
     h = reinterpret_cast<InlierHeader*>(static_cast<char*>(c->h_small) + 64);
     RLB_CUDA(cudaMemcpyAsync(h, c->header.p, sizeof(InlierHeader), cudaMemcpyDeviceToHost, c->stream));
     RLB_CUDA(cudaStreamSynchronize(c->stream));
-    if (idx && h->count[1] > 0) {
-      RLB_CUDA(cudaMemcpyAsync(idx, c->idx.p, static_cast<size_t>(h->count[1]) * sizeof(int32_t),
-                               cudaMemcpyDeviceToHost, c->stream));
+    const size_t bytes = static_cast<size_t>(std::max(h->count[1], 0)) * sizeof(int32_t);
+    if (view && bytes > 0) {  // the context's pinned copy; the caller's copy (if any) is taken from it
+      if (bytes > c->list_cap) {
+        if (c->h_list) cudaFreeHost(c->h_list);
+        c->h_list = nullptr;
+        c->list_cap = 0;
+        const size_t cap = static_cast<size_t>(ntot) * sizeof(int32_t);
+        RLB_CUDA(cudaMallocHost(&c->h_list, cap));
+        c->list_cap = cap;
+      }
+      RLB_CUDA(cudaMemcpyAsync(c->h_list, c->idx.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+      RLB_CUDA(cudaStreamSynchronize(c->stream));
+      *view = static_cast<const int32_t*>(c->h_list);
+      if (idx) memcpy(idx, c->h_list, bytes);
+    } else if (idx && bytes > 0) {
+      RLB_CUDA(cudaMemcpyAsync(idx, c->idx.p, bytes, cudaMemcpyDeviceToHost, c->stream));
       RLB_CUDA(cudaStreamSynchronize(c->stream));
     }
   }
@@ -935,6 +957,20 @@ int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl
   }
   if (score) *score = h->score;
   return RLB_OK;
+}
+}  // namespace
+
+int rlb_get_inliers(rlb_scorer* s, const double* model, const double* sq_thr_inl,
+                    const double* sq_thr_score, const double* weights, int32_t* idx,
+                    int32_t* counts, double* score) {
+  return get_inliers_impl(s, model, sq_thr_inl, sq_thr_score, weights, idx, nullptr, counts, score);
+}
+
+int rlb_get_inliers_view(rlb_scorer* s, const double* model, const double* sq_thr_inl,
+                         const double* sq_thr_score, const double* weights, const int32_t** idx_view,
+                         int32_t* counts, double* score) {
+  if (!idx_view) return fail(RLB_E_ARG, "null idx_view");
+  return get_inliers_impl(s, model, sq_thr_inl, sq_thr_score, weights, nullptr, idx_view, counts, score);
 }
 
 int rlb_eval_errors(rlb_scorer* s, int precision, const double* model, int type, double* err) {

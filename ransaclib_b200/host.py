@@ -218,6 +218,15 @@ def shuffle_and_resize(seed, n, target, reps=1):
     return out[:target].copy(), nxt.value, first
 
 
+def shuffle_from_list(seed, n, target, reps=1):
+    """The same through utils::ShuffleSampleFromList on the read-only list 3 i + 1 (the drivers' shuffle over
+    the pinned result list of a fused pass). -> (sample of the last shuffle, next raw engine output)."""
+    out = np.empty(max(target, 1), np.int32)
+    nxt = C.c_uint32()
+    _check(_load().rlbh_shuffle_from_list(C.c_uint32(seed), n, target, reps, _capi.ptr(out), C.byref(nxt)))
+    return out[:target].copy(), nxt.value
+
+
 def sample_hybrid(seed, num_data, sizes, weights=None):
     """Draws of HybridUniformSampling (weights None) / HybridBiasedSampling (per-type weight lists) from
     include/RansacLib/hybrid_sampling.h; sizes is k x T. Returns a list of k lists of T index lists."""

@@ -117,7 +117,8 @@ def test_drivers_fast_shuffle_is_the_reference_shuffle(G, O):
     ref = ol.reference() or O
     cases = [(1, 2, 1, 3), (2, 3, 2, 5), (3, 14, 14, 40), (4, 15, 14, 40), (5, 100, 6, 30), (6, 623, 14, 7),
              (7, 624, 14, 7), (8, 625, 14, 7), (9, 5000, 14, 50), (10, 5000, 28, 50), (11, 100000, 14, 12),
-             (12, 2000000, 6, 3), (13, 40, 32, 9), (14, 10, 14, 4), (15, 1, 1, 2), (16, 0, 0, 2)]
+             (12, 2000000, 6, 3), (13, 40, 32, 9), (14, 10, 14, 4), (15, 1, 1, 2), (16, 0, 0, 2), (17, 300, 100, 5),
+             (18, 65, 64, 9), (19, 66, 65, 9)]
     for seed, n, target, reps in cases:
         want = np.empty(max(target, 1), np.int32)
         wn = C.c_uint32()
@@ -125,6 +126,9 @@ def test_drivers_fast_shuffle_is_the_reference_shuffle(G, O):
         out, nxt, _ = H.shuffle_and_resize(seed, n, target, reps)
         assert out.tolist() == want[:target].tolist(), (seed, n, target, reps)
         assert nxt == wn.value, (seed, n, target, reps)
+        if target <= n:  # the view-based variant the drivers run on a fused pass's pinned list
+            got, nxt2 = H.shuffle_from_list(seed, n, target, reps)
+            assert got.tolist() == (3 * want[:target] + 1).tolist() and nxt2 == wn.value, (seed, n, target, reps)
 
 
 def test_pose_scoring_and_inliers(G, O):
