@@ -411,21 +411,23 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
   }
 
   // Second half of LeastSquaresFit (:578-594) once the inlier lists are known.
-  // The samples are copied out of the lists before the solver runs.
-  void FitOnInliers(const HybridLORansacOptions& options, const HybridSolver& solver,
+  // The samples are copied out of the lists before the solver runs. Returns whether the solver ran (and
+  // *m may have changed).
+  bool FitOnInliers(const HybridLORansacOptions& options, const HybridSolver& solver,
                     const int solver_type, utils::Mt19937* rng, const Lists& inliers, Model* m) const {
     std::vector<std::vector<int>> sizes;
     solver.min_sample_sizes(&sizes);
     const int num_types = solver.num_data_types();
     for (int t = 0; t < num_types; ++t) {
       const int have = inliers.count[t];
-      if (have < sizes[solver_type][t]) return;
+      if (have < sizes[solver_type][t]) return false;
       sizes[solver_type][t] = std::min(sizes[solver_type][t] * options.min_sample_multiplicator_, have);
     }
     std::vector<std::vector<int>> sample(num_types);
     for (int t = 0; t < num_types; ++t)  // utils.h:96-105, one type after the other on one engine
       utils::ShuffleSampleFromList(sizes[solver_type][t], rng, inliers.list[t], inliers.count[t], &sample[t]);
     solver.LeastSquares(sample, m);
+    return true;
   }
 
   // :500-567 with ScoreModel + the following GetInliers on the same model fused. Keeps the
@@ -456,24 +458,45 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
                     best_solver_type);
 
     const Lists base_lists(base);
+    // The relaxed thresholds keep shrinking across the LO steps (reference quirk, see above) and are <= 0
+    // from some step on: no squared error is below them, so those inlier lists are empty without a pass
+    // over the data. `scored` tracks whether m has changed since its score was last offered to
+    // UpdateBestModel - offering the same model again cannot change the best (strict <), so that pass is
+    // left out as well. Same sequence of solver calls, RNG draws and best-model updates as the reference.
+    Lists none;
+    none.list.assign(num_types, nullptr);
+    none.count.assign(num_types, 0);
+    auto all_lists_empty = [&]() {
+      for (int t = 0; t < num_types; ++t)
+        if (relaxed[t] > 0.0) return false;
+      return true;
+    };
+    auto offer = [&](const Model& m) {
+      UpdateBestModel(score, m, solver_type, score_best_minimal_model, best_minimal_model, best_solver_type);
+    };
     for (int r = 0; r < options.num_lo_steps_; ++r) {
       Model m = m_init;
-      FitOnInliers(options, solver, solver_type, rng, base_lists, &m);
+      bool scored = !FitOnInliers(options, solver, solver_type, rng, base_lists, &m);  // m_init was scored
       if (options.num_lsq_iterations_ <= 0) continue;
-      FitOnInliers(options, solver, solver_type, rng,
-                   FusedPassView(options, solver, m, relaxed, false, nullptr), &m);
+      if (FitOnInliers(options, solver, solver_type, rng,
+                       all_lists_empty() ? none : FusedPassView(options, solver, m, relaxed, false, nullptr),
+                       &m))
+        scored = false;
       for (int i = 0; i < options.num_lsq_iterations_; ++i) {
         for (int t = 0; t < num_types; ++t) relaxed[t] -= step[t];
-        if (i + 1 < options.num_lsq_iterations_) {
+        const bool want_fit = i + 1 < options.num_lsq_iterations_;
+        if (want_fit && !all_lists_empty()) {
           const Lists inliers = FusedPassView(options, solver, m, relaxed, true, &score);
-          UpdateBestModel(score, m, solver_type, score_best_minimal_model, best_minimal_model,
-                          best_solver_type);
-          FitOnInliers(options, solver, solver_type, rng, inliers, &m);
-        } else {
-          score = ScoreOnly(options, solver, m);
-          UpdateBestModel(score, m, solver_type, score_best_minimal_model, best_minimal_model,
-                          best_solver_type);
+          offer(m);
+          scored = !FitOnInliers(options, solver, solver_type, rng, inliers, &m);
+          continue;
         }
+        if (!scored) {
+          score = ScoreOnly(options, solver, m);
+          offer(m);
+          scored = true;
+        }
+        if (want_fit && FitOnInliers(options, solver, solver_type, rng, none, &m)) scored = false;
       }
     }
   }

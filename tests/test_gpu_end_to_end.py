@@ -157,6 +157,41 @@ def test_hybrid_line_estimation_config():
         assert st["inlier_indices"][1].tolist() == b[:ost.num_inliers_per_type[1]].tolist()
 
 
+@pytest.mark.parametrize("variant", [
+    dict(), dict(lo_steps=1), dict(lo_steps=3, lsq_iters=1), dict(lsq_iters=2, thr_mult=3.0), dict(thr_mult=1.0),
+    dict(lsq_iters=7, thr_mult=1.1, min_sample_mult=2), dict(lo_steps=25, lo_start=10), dict(final_lsq=1),
+    dict(lsq_iters=0), dict(lo_steps=0)])
+def test_hybrid_lo_variants(variant):
+    """The hybrid LO leaves out passes whose result is known (relaxed thresholds <= 0: empty lists; an unchanged model
+    scored again) - hybrid_ransac.h:500-567 run by the oracle must see the same solver calls, RNG draws and updates
+    whatever the LO options make of the shrinking thresholds."""
+    H = host()
+    O = ol.oracle()
+    names = {"lo_steps": "num_lo_steps_", "lsq_iters": "num_lsq_iterations_", "thr_mult": "threshold_multiplier_",
+             "min_sample_mult": "min_sample_multiplicator_", "lo_start": "lo_starting_iterations_",
+             "final_lsq": "final_least_squares_"}
+    for n, n_out, seed in [(3000, 1500, 3), (400, 300, 8), (5000, 500, 21)]:
+        xy0, p1 = synth.hybrid_line_instance(700 + seed, n - n_out, n_out, n - n_out, n_out)
+        o = ol.HybridOptions.default(sq_thr=[1e-4, 4e-4], weights=[2.0, 0.5], seed=seed, min_iters=100,
+                                     max_iters=10000, max_iters_per_solver=1000, **variant)
+        ost, om = ol.HybridStats(), np.zeros(3)
+        a, b = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        O.hybrid_lomsac_line(C.byref(o), n, ol.c64(xy0), n, ol.c64(p1), np.array([0.2, 0.8]), om, C.byref(ost), a, b)
+        kw = {names[k]: (bool(v) if k == "final_lsq" else v) for k, v in variant.items()}
+        opts = H.HybridLORansacOptions(squared_inlier_thresholds_=[1e-4, 4e-4], data_type_weights_=[2.0, 0.5],
+                                       random_seed_=seed, min_num_iterations_=100, max_num_iterations_=10000,
+                                       max_num_iterations_per_solver_=1000, **kw)
+        m, st = H.estimate_hybrid_line(opts, xy0, p1, [0.2, 0.8])
+        assert st["num_iterations_total"] == ost.num_iterations_total, (variant, n)
+        assert st["num_iterations_per_solver"] == list(ost.num_iterations_per_solver)
+        assert st["best_num_inliers"] == ost.best_num_inliers and st["best_solver_type"] == ost.best_solver_type
+        assert st["number_lo_iterations"] == ost.number_lo_iterations
+        np.testing.assert_allclose(st["best_model_score"], ost.best_model_score, rtol=1e-9)
+        np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+        assert st["inlier_indices"][0].tolist() == a[:ost.num_inliers_per_type[0]].tolist()
+        assert st["inlier_indices"][1].tolist() == b[:ost.num_inliers_per_type[1]].tolist()
+
+
 def test_hybrid_line_with_biased_sampling():
     """HybridBiasedSampling (reference hybrid_sampling.h:146-223) as the Sampler of the drop-in
     HybridLocallyOptimizedMSAC: the golden run of the reference's own headers, and a larger instance vs the oracle."""
