@@ -311,7 +311,10 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     cands[ncand++] = {7, 1.00};  // f64, H = 4
     cands[ncand++] = {-1, 0.96};  // f64, H = 2
   } else {
-    cands[ncand++] = {-1, 1.0};
+    cands[ncand++] = {-1, 1.0};  // H = 4
+    // H = 1: a batch of up to ~400 hypotheses (the drivers' rounds) leaves 3 of 4 register tiles of the H = 4
+    // kernel evaluating nothing; tile_use below picks this one for those.
+    if (d.kind != RLB_KIND_CUSTOM) cands[ncand++] = {10, 0.8};
   }
   double best_score = -1.0;
   int splits = 1, sps = total_stages;
@@ -325,7 +328,11 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
       occ_it = occ_cache.emplace(occ_key, rlb::sweep_resident_ctas(d.kind, precision, cands[ci].variant)).first;
     const int slots = c->sms * occ_it->second;
     const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
-    const int max_s = std::max(1, std::min(total_stages, 64));  // partials are [splits][k]
+    // partials are [splits][k]. 64 splits fill the device once a batch has a few hypothesis tiles; a small
+    // batch over many points (the hybrid drivers' rounds: ~100 hypotheses x 200k points) would leave it on 64
+    // CTAs whose threads each walk 3000 points - there the point axis is cut finer (220 -> 45 us per round).
+    const int fine = std::min(256, slots / std::max(k_tiles, 1));
+    const int max_s = std::max(1, std::min(total_stages, std::max(64, fine)));
     for (int s0 = 1; s0 <= max_s; ++s0) {
       if (forced_splits > 0 && s0 != std::min(forced_splits, max_s)) continue;
       const int sp = (total_stages + s0 - 1) / s0;
@@ -810,6 +817,20 @@ int rlb_scorer_get_rays(const rlb_scorer* s, double* rays) {
   return RLB_OK;
 }
 
+namespace {
+// Pinned staging block of the context, at least `bytes` long.
+int ensure_stage(rlb_ctx* c, size_t bytes) {
+  if (bytes <= c->stage_cap) return RLB_OK;
+  if (c->h_stage) cudaFreeHost(c->h_stage);
+  c->h_stage = nullptr;
+  c->stage_cap = 0;
+  const size_t cap = std::max<size_t>(bytes, 256 * 1024);
+  RLB_CUDA(cudaMallocHost(&c->h_stage, cap));
+  c->stage_cap = cap;
+  return RLB_OK;
+}
+}  // namespace
+
 int rlb_score_models_dev(rlb_scorer* s, int precision, int k, const double* d_models,
                          const uint8_t* d_valid, const double* sq_thr, const double* weights,
                          double* d_scores, int32_t* d_counts, void* d_best) {
@@ -837,15 +858,29 @@ int rlb_score_models(rlb_scorer* s, int precision, int k, const double* models,
   rc = ensure_first_use(c);
   if (rc) return rc;
   const int md = rlb::model_size_of(s->d);
-  RLB_CUDA(c->models.ensure(static_cast<size_t>(k) * md * sizeof(double)));
-  RLB_CUDA(c->scores.ensure(static_cast<size_t>(k) * sizeof(double)));
-  RLB_CUDA(c->counts.ensure(static_cast<size_t>(k) * sizeof(int32_t)));
-  RLB_CUDA(cudaMemcpyAsync(c->models.p, models, static_cast<size_t>(k) * md * sizeof(double),
+  const size_t b_models = static_cast<size_t>(k) * md * sizeof(double), b_valid = valid ? static_cast<size_t>(k) : 0;
+  const size_t b_scores = static_cast<size_t>(k) * sizeof(double), b_counts = static_cast<size_t>(k) * sizeof(int32_t);
+  RLB_CUDA(c->models.ensure(b_models));
+  RLB_CUDA(c->scores.ensure(b_scores));
+  RLB_CUDA(c->counts.ensure(b_counts));
+  // Small batches (the drivers' rounds) through pinned staging, as in rlb_hypothesize_and_score.
+  const size_t o_valid = (b_models + 63) & ~size_t(63), o_scores = (o_valid + b_valid + 63) & ~size_t(63);
+  const size_t o_counts = o_scores + b_scores, stage_bytes = o_counts + b_counts;
+  char* stage = nullptr;
+  if (stage_bytes <= (size_t(1) << 20)) {
+    rc = ensure_stage(c, stage_bytes);
+    if (rc) return rc;
+    stage = static_cast<char*>(c->h_stage);
+    memcpy(stage, models, b_models);
+    if (valid) memcpy(stage + o_valid, valid, b_valid);
+  }
+  RLB_CUDA(cudaMemcpyAsync(c->models.p, stage ? static_cast<const void*>(stage) : models, b_models,
                            cudaMemcpyHostToDevice, c->stream));
   const uint8_t* d_valid = nullptr;
   if (valid) {
-    RLB_CUDA(c->valid.ensure(static_cast<size_t>(k)));
-    RLB_CUDA(cudaMemcpyAsync(c->valid.p, valid, static_cast<size_t>(k), cudaMemcpyHostToDevice, c->stream));
+    RLB_CUDA(c->valid.ensure(b_valid));
+    RLB_CUDA(cudaMemcpyAsync(c->valid.p, stage ? static_cast<const void*>(stage + o_valid) : valid, b_valid,
+                             cudaMemcpyHostToDevice, c->stream));
     d_valid = c->valid.as<uint8_t>();
   }
   BestRec* d_best = reinterpret_cast<BestRec*>(c->small.as<char>() + kSmallBest);
@@ -853,14 +888,18 @@ int rlb_score_models(rlb_scorer* s, int precision, int k, const double* models,
                  c->scores.as<double>(), counts ? c->counts.as<int32_t>() : nullptr, d_best, nullptr);
   if (rc) return rc;
   if (scores)
-    RLB_CUDA(cudaMemcpyAsync(scores, c->scores.p, static_cast<size_t>(k) * sizeof(double),
+    RLB_CUDA(cudaMemcpyAsync(stage ? static_cast<void*>(stage + o_scores) : scores, c->scores.p, b_scores,
                              cudaMemcpyDeviceToHost, c->stream));
   if (counts)
-    RLB_CUDA(cudaMemcpyAsync(counts, c->counts.p, static_cast<size_t>(k) * sizeof(int32_t),
+    RLB_CUDA(cudaMemcpyAsync(stage ? static_cast<void*>(stage + o_counts) : counts, c->counts.p, b_counts,
                              cudaMemcpyDeviceToHost, c->stream));
   BestRec* h_best = static_cast<BestRec*>(c->h_small);
   RLB_CUDA(cudaMemcpyAsync(h_best, d_best, sizeof(BestRec), cudaMemcpyDeviceToHost, c->stream));
   RLB_CUDA(cudaStreamSynchronize(c->stream));
+  if (stage) {
+    if (scores) memcpy(scores, stage + o_scores, b_scores);
+    if (counts) memcpy(counts, stage + o_counts, b_counts);
+  }
   if (best_id) *best_id = static_cast<int32_t>(h_best->id);
   if (best_score) *best_score = h_best->score;
   return RLB_OK;
@@ -1131,14 +1170,8 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
   const bool staged = stage_bytes <= (size_t(1) << 20);
   char* stage = nullptr;
   if (staged) {
-    if (stage_bytes > c->stage_cap) {
-      if (c->h_stage) cudaFreeHost(c->h_stage);
-      c->h_stage = nullptr;
-      c->stage_cap = 0;
-      const size_t cap = std::max<size_t>(stage_bytes, 256 * 1024);
-      RLB_CUDA(cudaMallocHost(&c->h_stage, cap));
-      c->stage_cap = cap;
-    }
+    rc = ensure_stage(c, stage_bytes);
+    if (rc) return rc;
     stage = static_cast<char*>(c->h_stage);
     memcpy(stage, samples, b_samples);
   }

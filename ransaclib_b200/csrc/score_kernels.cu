@@ -585,7 +585,7 @@ int sweep_hyps_per_thread(int kind, int precision, int variant) {
       default: return 4;
     }
   }
-  return 4;
+  return variant == 10 ? 1 : 4;  // line kinds: 10 = one hypothesis per thread (batches up to a few hundred)
 }
 
 // Resident CTAs per SM of the sweep kernel a (kind, precision, variant) triple selects
@@ -618,6 +618,10 @@ int sweep_resident_ctas(int kind, int precision, int variant) {
     if (variant == 8) return occupancy_of(sweep_kernel<PoseF, double, 1>, s64);
     return occupancy_of(sweep_kernel<PoseF, double, 2>, s64);
   }
+  if (variant == 10) {
+    if (precision == RLB_F32) return occupancy_of(sweep_kernel<LineF, float, 1>, l32);
+    return occupancy_of(sweep_kernel<LineF, double, 1>, l64);
+  }
   if (precision == RLB_F32) return occupancy_of(sweep_kernel<LineF, float, 4>, l32);
   return occupancy_of(sweep_kernel<LineF, double, 4>, l64);
 }
@@ -641,6 +645,10 @@ cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision,
     if (a.variant == 8) return launch_sweep_t<PoseF, double, 1>(d, a, st);  // A/B only
     return launch_sweep_t<PoseF, double, 2>(d, a, st);
   }
+  if (a.variant == 10) {
+    if (precision == RLB_F32) return launch_sweep_t<LineF, float, 1>(d, a, st);
+    return launch_sweep_t<LineF, double, 1>(d, a, st);
+  }
   if (precision == RLB_F32) return launch_sweep_t<LineF, float, 4>(d, a, st);
   return launch_sweep_t<LineF, double, 4>(d, a, st);
 }
@@ -662,7 +670,24 @@ __global__ void __launch_bounds__(256)
   if (k < a.k) {
     double sum = 0.0;
     int cnt = 0;
-    for (int sp = 0; sp < a.n_splits; ++sp) {  // fixed order: deterministic
+    // fixed order: deterministic. Eight loads in flight, added in split order (a small batch over many
+    // points has up to 256 splits and one thread per hypothesis walking them).
+    int sp = 0;
+    for (; sp + 8 <= a.n_splits; sp += 8) {
+      double v[8];
+      int c[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        v[u] = a.part_score[static_cast<size_t>(sp + u) * a.k + k];
+        c[u] = counts ? a.part_count[static_cast<size_t>(sp + u) * a.k + k] : 0;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        sum += v[u];
+        cnt += c[u];
+      }
+    }
+    for (; sp < a.n_splits; ++sp) {
       sum += a.part_score[static_cast<size_t>(sp) * a.k + k];
       if (counts) cnt += a.part_count[static_cast<size_t>(sp) * a.k + k];
     }
