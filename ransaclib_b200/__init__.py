@@ -285,6 +285,29 @@ class Scorer:
                 p += counts[t]
         return lists, counts[:self.num_types].copy(), (score.value if ts is not None else None)
 
+    def get_inliers_view(self, model, sq_thr_inl, sq_thr_score=None, weights=None):
+        """The same pass through rlb_get_inliers_view: the lists are read from the context's own pinned copy
+        (valid until the next call on the context; copied here before returning)."""
+        model = _capi.f64a(model, (self.model_size,))
+        ti = self._thr(sq_thr_inl)
+        ts = None if sq_thr_score is None else self._thr(sq_thr_score)
+        w = None if weights is None else self._thr(weights)
+        view = C.c_void_p()
+        counts = np.zeros(2, np.int32)
+        score = C.c_double()
+        _capi.check(self._lib.rlb_get_inliers_view(self._h, _capi.ptr(model), _capi.ptr(ti), _capi.ptr(ts),
+                                                   _capi.ptr(w), C.byref(view), _capi.ptr(counts),
+                                                   C.addressof(score)))
+        total = int(counts[:self.num_types].sum())
+        flat = np.empty(0, np.int32)
+        if total > 0:
+            flat = np.ctypeslib.as_array(C.cast(view, C.POINTER(C.c_int32)), shape=(total,)).copy()
+        lists, p = [], 0
+        for t in range(self.num_types):
+            lists.append(flat[p:p + counts[t]])
+            p += counts[t]
+        return lists, counts[:self.num_types].copy(), (score.value if ts is not None else None)
+
     def eval_errors(self, model, type_: int = 0, precision=RLB_F64):
         model = _capi.f64a(model, (self.model_size,))
         err = np.empty(self.num_data[type_])

@@ -248,6 +248,35 @@ def test_empty_and_ragged_hybrid(ctx):
     assert counts.tolist() == [len(lists[0]), 0]
 
 
+def test_inlier_list_view(ctx):
+    """rlb_get_inliers_view: the list read in place from the context's pinned copy is the list rlb_get_inliers copies
+    out - per type for a hybrid scorer, empty lists, and past the zero-copy limit (262,144 points) where the copy
+    is fetched by DMA."""
+    xy0, p1 = synth.hybrid_line_instance(5, 900, 600, 400, 300)
+    sc = ctx.hybrid_line_scorer(xy0, p1)
+    smp = ol.sample_uniform(ol.oracle(), 2, len(xy0), 2, 8)
+    models, _ = sc.solve_line2pt(smp)
+    thr, w = np.array([1e-4, 3e-4]), np.array([2.0, 0.5])
+    for m in models[:4]:
+        for t in (thr, 50.0 * thr, 0.0 * thr, -thr):
+            lists, counts, score = sc.get_inliers(m, t, thr, w)
+            vl, vc, vs = sc.get_inliers_view(m, t, thr, w)
+            assert vc.tolist() == counts.tolist() and vs == score
+            assert [x.tolist() for x in vl] == [x.tolist() for x in lists]
+            if (t <= 0).all():
+                assert counts.tolist() == [0, 0]
+    n = 300000
+    xy = synth.line_instance(77, n // 2, n - n // 2)
+    big = ctx.line_scorer(xy)
+    bm, _ = big.solve_line2pt(ol.sample_uniform(ol.oracle(), 3, n, 2, 4))
+    for m in bm:
+        lists, counts, score = big.get_inliers(m, 1e-3, 1e-4)
+        vl, vc, vs = big.get_inliers_view(m, 1e-3, 1e-4)
+        assert vc.tolist() == counts.tolist() and vs == score and vl[0].tolist() == lists[0].tolist()
+    _, vc, _ = big.get_inliers_view(bm[0], 0.0)
+    assert vc.tolist() == [0]
+
+
 def test_far_from_origin_f32_recentring(ctx):
     """Scene 1e5 units from the origin: the f32 path must still meet 1e-4 (points are
     recentred in f64 before the f32 conversion)."""
