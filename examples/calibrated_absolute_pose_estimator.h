@@ -8,11 +8,13 @@
 #include <cmath>
 #include <cstdint>
 #include <limits>
+#include <stdexcept>
 #include <vector>
 
 #include <RansacLib/gpu_scorer.h>
 
 #include "model_types.h"
+#include "p3p.h"
 #include "pose_refinement.h"
 
 namespace ransac_lib {
@@ -40,17 +42,34 @@ class CalibratedAbsolutePoseEstimator {
   inline int non_minimal_sample_size() const { return 6; }  // reference .h:90
   inline int num_data() const { return num_data_; }
 
-  // One sample through the device P3P kernel (K = 1). The batched driver does not use this;
-  // it exists for NonMinimalSolver and for API completeness (.cc:111-137).
+  // One sample on the host (.cc:111-137): the same P3P as the device solver (examples/p3p.h, bit-identical
+  // under -ffp-contract=off), without a launch - NonMinimalSolver calls this once per LO step. The batched
+  // driver solves its hypothesis batches on the device.
   int MinimalSolver(const std::vector<int>& sample, CameraPoses* poses) const {
     poses->clear();
     if (sample.size() < 4u) return 0;
-    const int32_t s4[4] = {sample[0], sample[1], sample[2], sample[3]};
+    for (int j = 0; j < 4; ++j)
+      if (sample[j] < 0 || sample[j] >= num_data_)
+        throw std::runtime_error("ransaclib_b200: MinimalSolver: sample index out of range");
+    double y[9], x[9];
+    for (int j = 0; j < 3; ++j) {
+      const size_t i = static_cast<size_t>(sample[j]);
+      // PixelsToViewingRays, .cc:214-227 (same operations as csrc/solver_kernels.cu: rays_kernel)
+      const double rx = points2D_[2 * i] / focal_x_;
+      const double ry = points2D_[2 * i + 1] / focal_y_;
+      const double rz = 1.0;
+      const double nrm = std::sqrt(rx * rx + ry * ry + rz * rz);
+      y[3 * j] = rx / nrm;
+      y[3 * j + 1] = ry / nrm;
+      y[3 * j + 2] = rz / nrm;
+      for (int c = 0; c < 3; ++c) x[3 * j + c] = points3D_[3 * i + c];
+    }
+    const size_t i4 = static_cast<size_t>(sample[3]);
+    const double X4[3] = {points3D_[3 * i4], points3D_[3 * i4 + 1], points3D_[3 * i4 + 2]};
+    const double uv4[2] = {points2D_[2 * i4], points2D_[2 * i4 + 1]};
     CameraPose P;
-    uint8_t ok = 0;
-    gpu::Check(rlb_solve_p3p_batch(scorer_.get(), 1, s4, squared_inlier_threshold_, P.m, &ok),
-               "rlb_solve_p3p_batch");
-    if (ok) poses->push_back(P);
+    if (rlb::p3pdev::p3p_pick(y, x, X4, uv4, focal_x_, focal_y_, squared_inlier_threshold_, P.m))
+      poses->push_back(P);
     return static_cast<int>(poses->size());
   }
 

@@ -221,6 +221,20 @@ int rlbh_lomsac_pose(const rlbh_options* o, int device, int precision, double fx
   });
 }
 
+// CalibratedAbsolutePoseEstimator::MinimalSolver (host P3P, examples/p3p.h) on k samples of 4 indices.
+int rlbh_pose_minimal_solver(int device, double fx, double fy, double sq_thr, int n, const double* p2d,
+                             const double* p3d, int k, const int32_t* samples, double* models, uint8_t* valid) {
+  return Guard([&] {
+    CalibratedAbsolutePoseEstimator solver(fx, fy, sq_thr, n, p2d, p3d, &gpu::Context::ThreadDefault(device));
+    CameraPoses poses;
+    for (int i = 0; i < k; ++i) {
+      const std::vector<int> sample(samples + 4 * static_cast<size_t>(i), samples + 4 * static_cast<size_t>(i + 1));
+      valid[i] = solver.MinimalSolver(sample, &poses) == 1 ? 1 : 0;
+      for (int j = 0; j < 12; ++j) models[12 * static_cast<size_t>(i) + j] = valid[i] ? poses[0].m[j] : 0.0;
+    }
+  });
+}
+
 int rlbh_hybrid_lomsac_line(const rlbh_hybrid_options* o, int device, int precision, int n0,
                             const double* xy0, int n1, const double* xynn1, const double* priors,
                             double* model, rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {

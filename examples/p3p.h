@@ -1,33 +1,43 @@
-// Device-side P3P (Lambda Twist, Persson & Nordberg ECCV 2018, fixed solution order) and the
-// reference-exact single-point reprojection error. Shared by solver_kernels.cu (one sample per
-// thread) and localize_kernels.cu (whole LO-MSAC runs on the device). Both translation units
-// are compiled with -fmad=false and this code uses only + - * / sqrt frexp ldexp, so results
-// are bit-identical to a strict-IEEE host evaluation of the same formulas.
+// P3P (Lambda Twist, Persson & Nordberg ECCV 2018, fixed solution order) and the reference-exact
+// single-point reprojection error, for device and host. Shared by csrc/solver_kernels.cu (one
+// sample per thread), csrc/localize_kernels.cu (whole LO-MSAC runs on the device) and the host
+// side of CalibratedAbsolutePoseEstimator::MinimalSolver (one sample: no launch). The kernels are
+// compiled with -fmad=false, the host library with -ffp-contract=off, and this code uses only
+// + - * / sqrt frexp ldexp, so the three give bit-identical poses.
 //
 // Replaces (reference): examples/calibrated_absolute_pose_estimator.cc:111-137 (+ pose_lib::p3p,
 // external to the reference) and :154-167.
-#ifndef RLB_P3P_DEVICE_CUH_
-#define RLB_P3P_DEVICE_CUH_
+#ifndef RLB_EXAMPLES_P3P_H_
+#define RLB_EXAMPLES_P3P_H_
 
 #include <cfloat>
+#include <cmath>
+
+#ifdef __CUDACC__
+#define RLB_P3P_HD __host__ __device__
+#define RLB_P3P_HD_INLINE __host__ __device__ __forceinline__
+#else
+#define RLB_P3P_HD inline
+#define RLB_P3P_HD_INLINE inline
+#endif
 
 namespace rlb {
 namespace p3pdev {
 
-static __device__ __forceinline__ void cross3(const double* a, const double* b, double* c) {
+static RLB_P3P_HD_INLINE void cross3(const double* a, const double* b, double* c) {
   c[0] = a[1] * b[2] - a[2] * b[1];
   c[1] = a[2] * b[0] - a[0] * b[2];
   c[2] = a[0] * b[1] - a[1] * b[0];
 }
-static __device__ __forceinline__ double dot3(const double* a, const double* b) {
+static RLB_P3P_HD_INLINE double dot3(const double* a, const double* b) {
   return a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
 }
-static __device__ __forceinline__ double det3(const double* m) {
+static RLB_P3P_HD_INLINE double det3(const double* m) {
   return m[0] * (m[4] * m[8] - m[5] * m[7]) - m[1] * (m[3] * m[8] - m[5] * m[6]) +
          m[2] * (m[3] * m[7] - m[4] * m[6]);
 }
 // tr(adj(A) B): coefficient of g in det(A + g B).
-static __device__ double tr_adj_mul(const double* A, const double* B) {
+static RLB_P3P_HD double tr_adj_mul(const double* A, const double* B) {
   const double c00 = A[4] * A[8] - A[5] * A[7];
   const double c01 = -(A[3] * A[8] - A[5] * A[6]);
   const double c02 = A[3] * A[7] - A[4] * A[6];
@@ -40,7 +50,7 @@ static __device__ double tr_adj_mul(const double* A, const double* B) {
   return c00 * B[0] + c01 * B[1] + c02 * B[2] + c10 * B[3] + c11 * B[4] + c12 * B[5] +
          c20 * B[6] + c21 * B[7] + c22 * B[8];
 }
-static __device__ double cbrt_upper_pow2(double q) {
+static RLB_P3P_HD double cbrt_upper_pow2(double q) {
   int e;
   (void)frexp(q, &e);
   const int ce = (e >= 0) ? (e + 2) / 3 : -((-e) / 3);
@@ -48,7 +58,7 @@ static __device__ double cbrt_upper_pow2(double q) {
 }
 // One real root of x^3 + a x^2 + b x + c: monotone Newton from an upper bound on
 // the convex side of the inflection point.
-static __device__ double cubic_one_root(double a, double b, double c) {
+static RLB_P3P_HD double cubic_one_root(double a, double b, double c) {
   const double xi = -a / 3.0;
   const double p = b - a * a / 3.0;
   const double q = ((xi + a) * xi + b) * xi + c;
@@ -78,7 +88,7 @@ static __device__ double cubic_one_root(double a, double b, double c) {
   }
   return (q < 0.0) ? xi + h : xi - h;
 }
-static __device__ bool null_vector(const double* m, double* v) {
+static RLB_P3P_HD bool null_vector(const double* m, double* v) {
   double c0[3], c1[3], c2[3];
   cross3(m + 0, m + 3, c0);
   cross3(m + 0, m + 6, c1);
@@ -101,7 +111,7 @@ static __device__ bool null_vector(const double* m, double* v) {
   v[2] = best[2] * inv;
   return true;
 }
-static __device__ void refine_lambda(double* L, double a12, double a13, double a23, double b12, double b13,
+static RLB_P3P_HD void refine_lambda(double* L, double a12, double a13, double a23, double b12, double b13,
                               double b23) {
   for (int it = 0; it < 5; ++it) {
     const double l1 = L[0], l2 = L[1], l3 = L[2];
@@ -126,7 +136,7 @@ static __device__ void refine_lambda(double* L, double a12, double a13, double a
 
 // Reference-exact residual on ONE point in the reference's own formulation
 // (calibrated_absolute_pose_estimator.cc:154-167): used for the 4th-point test.
-static __device__ __forceinline__ double reproj_sq_error_v(const double* P /*col-major 3x4 [R|c]*/,
+static RLB_P3P_HD_INLINE double reproj_sq_error_v(const double* P /*col-major 3x4 [R|c]*/,
                                                            double X0, double X1, double X2, double u0,
                                                            double v0, double fx, double fy) {
   const double d0 = X0 - P[9], d1 = X1 - P[10], d2 = X2 - P[11];
@@ -139,14 +149,14 @@ static __device__ __forceinline__ double reproj_sq_error_v(const double* P /*col
   const double du = u - u0, dv = v - v0;
   return du * du + dv * dv;
 }
-static __device__ double reproj_sq_error(const double* P /*col-major 3x4 [R|c]*/, const double* X,
+static RLB_P3P_HD double reproj_sq_error(const double* P /*col-major 3x4 [R|c]*/, const double* X,
                                          const double* uv, double fx, double fy) {
   return reproj_sq_error_v(P, X[0], X[1], X[2], uv[0], uv[1], fx, fy);
 }
 
 // Lambda Twist + "first solution consistent with the 4th point wins"
 // (calibrated_absolute_pose_estimator.cc:124-133). Returns true and fills P.
-static __device__ bool p3p_pick(const double* y, const double* x, const double* X4, const double* uv4,
+static RLB_P3P_HD bool p3p_pick(const double* y, const double* x, const double* X4, const double* uv4,
                          double fx, double fy, double sq_thr, double* P) {
   const double* y1 = y;
   const double* y2 = y + 3;
@@ -299,4 +309,4 @@ static __device__ bool p3p_pick(const double* y, const double* x, const double* 
 }  // namespace p3pdev
 }  // namespace rlb
 
-#endif  // RLB_P3P_DEVICE_CUH_
+#endif  // RLB_EXAMPLES_P3P_H_

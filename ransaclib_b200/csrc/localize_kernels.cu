@@ -40,7 +40,7 @@
 #endif
 
 #include "../../examples/pose_refinement.h"
-#include "p3p_device.cuh"
+#include "../../examples/p3p.h"
 #include "rlb_internal.cuh"
 
 namespace rlb {

@@ -12,7 +12,7 @@
 // PixelsToViewingRays, .cc:214-227.
 #include <cfloat>
 
-#include "p3p_device.cuh"
+#include "../../examples/p3p.h"
 #include "rlb_internal.cuh"
 
 namespace rlb {

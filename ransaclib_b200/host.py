@@ -168,6 +168,20 @@ def estimate_pose(options: LORansacOptions, fx, fy, points2D, points3D, device=0
     return model, _stats_dict(st, inl)
 
 
+def pose_minimal_solver(fx, fy, sq_thr, points2D, points3D, samples, device=0):
+    """CalibratedAbsolutePoseEstimator::MinimalSolver (the host-side P3P of examples/p3p.h) on k samples.
+    -> (models k x 12, valid k); an invalid sample's model is zero, like rlb_solve_p3p_batch."""
+    p2 = _capi.f64a(points2D, (-1, 2))
+    p3 = _capi.f64a(points3D, (-1, 3))
+    smp = _capi.i32a(samples, (-1, 4))
+    models = np.zeros((len(smp), 12))
+    valid = np.zeros(len(smp), np.uint8)
+    _check(_load().rlbh_pose_minimal_solver(device, C.c_double(fx), C.c_double(fy), C.c_double(sq_thr), len(p2),
+                                            _capi.ptr(p2), _capi.ptr(p3), len(smp), _capi.ptr(smp),
+                                            _capi.ptr(models), _capi.ptr(valid)))
+    return models, valid
+
+
 def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, device=0, precision=-1,
                          sampling_weights=None):
     """HybridLocallyOptimizedMSAC<Line, ., HybridLineEstimator[, Sampler]>::EstimateModel. sampling_weights =

@@ -248,6 +248,22 @@ def test_empty_and_ragged_hybrid(ctx):
     assert counts.tolist() == [len(lists[0]), 0]
 
 
+def test_host_p3p_is_the_device_p3p(ctx, pose_case):
+    """examples/p3p.h compiles for both sides: the estimator's host MinimalSolver (NonMinimalSolver calls it once per
+    LO step, no launch) returns the bits of the device solver, valid and rejected samples alike."""
+    from ransaclib_b200 import host as H
+
+    inst, f, samples, models, valid = pose_case
+    hm, hv = H.pose_minimal_solver(f, f, 144.0, inst["points2D"], inst["points3D"], samples)
+    assert hv.tolist() == valid.tolist()
+    assert hm.tolist() == models.tolist()
+    more = ol.sample_uniform(ol.oracle(), 99, len(inst["points2D"]), 4, 3000)
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    gm, gv = sc.solve_p3p(more, 144.0)
+    hm, hv = H.pose_minimal_solver(f, f, 144.0, inst["points2D"], inst["points3D"], more)
+    assert hv.tolist() == gv.tolist() and hm.tolist() == gm.tolist()
+
+
 def test_inlier_list_view(ctx):
     """rlb_get_inliers_view: the list read in place from the context's pinned copy is the list rlb_get_inliers copies
     out - per type for a hybrid scorer, empty lists, and past the zero-copy limit (262,144 points) where the copy
