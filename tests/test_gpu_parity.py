@@ -248,6 +248,51 @@ def test_empty_and_ragged_hybrid(ctx):
     assert counts.tolist() == [len(lists[0]), 0]
 
 
+def test_small_batches_over_many_points(ctx):
+    """The sweep plan of a batch that cannot fill the device with 64 point-axis splits (the drivers' rounds over a
+    large data set): one hypothesis per thread for the line kinds, up to 256 splits - scores and counts against the
+    oracle at batch sizes around the tile edges, both arithmetic classes, line / hybrid / pose."""
+    O = ol.oracle()
+    n = 150000
+    xy = synth.line_instance(31, n // 2, n - n // 2)
+    sc = ctx.line_scorer(xy)
+    models, _ = sc.solve_line2pt(ol.sample_uniform(O, 5, n, 2, 600))
+    for k in (1, 15, 128, 129, 400, 513, 600):
+        ws, wc = np.empty(k), np.empty(k, np.int32)
+        O.line_score_models(n, ol.c64(xy), k, ol.c64(models[:k]), 1e-4, ws, wc)
+        s, c, bid, _ = sc.score_models(models[:k], 1e-4)
+        variant, splits = ctx.last_sweep_plan()
+        assert splits > 64 and (variant == 10 or k > 128), (k, variant, splits)
+        np.testing.assert_allclose(s, ws, rtol=F64_RTOL)
+        assert c.tolist() == wc.tolist() and bid == int(np.argmin(ws))
+        s32, c32, _, _ = sc.score_models(models[:k], 1e-4, precision=rlb().RLB_F32)
+        np.testing.assert_allclose(s32, ws, rtol=F32_RTOL)
+        assert np.abs(c32 - wc).max() <= max(2, int(2e-5 * n))  # points within f32 rounding of the threshold
+
+    xy0, p1 = synth.hybrid_line_instance(8, 40000, 30000, 50000, 45000)
+    hs = ctx.hybrid_line_scorer(xy0, p1)
+    hm, _ = hs.solve_line2pt(ol.sample_uniform(O, 6, len(xy0), 2, 100))
+    thr, w = np.array([1e-4, 3e-4]), np.array([2.0, 0.5])
+    ws, wc = np.empty(100), np.empty(100, np.int32)
+    O.hybrid_line_score_models(len(xy0), ol.c64(xy0), len(p1), ol.c64(p1), 100, ol.c64(hm), thr, w, ws, wc)
+    s, c, bid, _ = hs.score_models(hm, thr, weights=w)
+    assert ctx.last_sweep_plan()[1] > 64
+    np.testing.assert_allclose(s, ws, rtol=F64_RTOL)
+    assert c.tolist() == wc.tolist() and bid == int(np.argmin(ws))
+
+    inst = synth.pose_instance(77, 60000, 60000)
+    f = inst["focal"]
+    ps = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    pm = synth.perturbed_poses(3, inst["R_gt"], inst["c_gt"], 96, rot_sigma=0.003, trans_sigma=0.01)
+    ws, wc = ol.pose_score(O, f, f, inst["points2D"], inst["points3D"], pm, 144.0)
+    s, c, bid, _ = ps.score_models(pm, 144.0)
+    assert ctx.last_sweep_plan()[1] > 64
+    np.testing.assert_allclose(s, ws, rtol=F64_RTOL)
+    assert c.tolist() == wc.tolist() and bid == int(np.argmin(ws))
+    s32, _, _, _ = ps.score_models(pm, 144.0, precision=rlb().RLB_F32)
+    np.testing.assert_allclose(s32, ws, rtol=F32_RTOL)
+
+
 def test_host_p3p_is_the_device_p3p(ctx, pose_case):
     """examples/p3p.h compiles for both sides: the estimator's host MinimalSolver (NonMinimalSolver calls it once per
     LO step, no launch) returns the bits of the device solver, valid and rejected samples alike."""
