@@ -265,11 +265,15 @@ int rlbh_sample_uniform(uint32_t seed, int n, int s, int k, int32_t* out) {
   return Guard([&] {
     SizesOnly solver{{n}, {}, s};
     UniformSampling<SizesOnly> sampler(seed, solver);
-    std::vector<int> one;
-    for (int i = 0; i < k; ++i) {
+    // first half one by one, second half as the drivers draw them (SampleBatch): one stream
+    std::vector<int> one, flat;
+    const int singles = k / 2;
+    for (int i = 0; i < singles; ++i) {
       sampler.Sample(&one);
       std::copy(one.begin(), one.end(), out + static_cast<size_t>(i) * s);
     }
+    sampler.SampleBatch(k - singles, &flat);
+    std::copy(flat.begin(), flat.end(), out + static_cast<size_t>(singles) * s);
   });
 }
 

