@@ -330,8 +330,12 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
     // partials are [splits][k]. 64 splits fill the device once a batch has a few hypothesis tiles; a small
     // batch over many points (the hybrid drivers' rounds: ~100 hypotheses x 200k points) would leave it on 64
-    // CTAs whose threads each walk 3000 points - there the point axis is cut finer (220 -> 45 us per round).
-    const int fine = std::min(256, slots / std::max(k_tiles, 1));
+    // CTAs whose threads each walk 3000 points - there the point axis is cut finer (220 -> 75 us per round).
+    static const int fine_max = [] {
+      const char* v = getenv("RLB_SWEEP_FINE_MAX");  // A/B timing
+      return v ? atoi(v) : 256;  // 512 (one stage per CTA) measured 3 % slower on configs[2]
+    }();
+    const int fine = std::min(fine_max, slots / std::max(k_tiles, 1));
     const int max_s = std::max(1, std::min(total_stages, std::max(64, fine)));
     for (int s0 = 1; s0 <= max_s; ++s0) {
       if (forced_splits > 0 && s0 != std::min(forced_splits, max_s)) continue;
