@@ -474,7 +474,43 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
     auto offer = [&](const Model& m) {
       UpdateBestModel(score, m, solver_type, score_best_minimal_model, best_minimal_model, best_solver_type);
     };
+    // Once every relaxed threshold is <= 0 and cannot grow again, a step is: shuffle + fit on the base lists
+    // (the only RNG use), then the score of that ONE model. The models of all remaining steps are therefore
+    // known up front; they are scored in one sweep, and only those within 1e-9 of the best so far (the sweep
+    // sums its partials in another order than a K = 1 pass) get the exact pass and the offer, in step order.
+    bool thresholds_only_shrink = options.num_lsq_iterations_ > 0;
+    for (int t = 0; t < num_types; ++t) thresholds_only_shrink = thresholds_only_shrink && step[t] >= 0.0;
+    bool empty_fit_returns = false;  // a fit on empty lists returns before it shuffles
+    {
+      std::vector<std::vector<int>> sizes;
+      solver.min_sample_sizes(&sizes);
+      for (int t = 0; t < num_types; ++t) empty_fit_returns = empty_fit_returns || sizes[solver_type][t] > 0;
+    }
     for (int r = 0; r < options.num_lo_steps_; ++r) {
+      if (thresholds_only_shrink && empty_fit_returns && all_lists_empty() && options.num_lo_steps_ - r >= 3) {
+        const gpu::DeviceScorer& dev = solver.device_scorer();
+        const int md = dev.model_size();
+        std::vector<Model> tail;
+        std::vector<double> packed;
+        for (; r < options.num_lo_steps_; ++r) {
+          Model m = m_init;
+          if (!FitOnInliers(options, solver, solver_type, rng, base_lists, &m)) continue;  // m_init: scored
+          tail.push_back(m);
+          packed.resize(packed.size() + md);
+          HybridSolver::PackModel(m, &packed[packed.size() - md]);
+        }
+        if (tail.empty()) break;
+        std::vector<double> approx(tail.size());
+        dev.ScoreModels(static_cast<int>(tail.size()), packed.data(), nullptr,
+                        options.squared_inlier_thresholds_.data(), options.data_type_weights_.data(),
+                        approx.data(), RLB_F64);
+        for (size_t j = 0; j < tail.size(); ++j) {
+          if (!(approx[j] <= *score_best_minimal_model * (1.0 + 1e-9))) continue;  // cannot be strictly better
+          score = ScoreOnly(options, solver, tail[j]);
+          offer(tail[j]);
+        }
+        break;
+      }
       Model m = m_init;
       bool scored = !FitOnInliers(options, solver, solver_type, rng, base_lists, &m);  // m_init was scored
       if (options.num_lsq_iterations_ <= 0) continue;
