@@ -428,16 +428,24 @@ class LocallyOptimizedMSAC : public RansacBase {
     return FusedPass(solver, model, thr, nullptr, inliers, nullptr);
   }
 
-  // [ScoreModel(m) + UpdateBestModel] fused with the LeastSquaresFit(fit_thr, m) that follows
-  // it in the reference (ransac.h:409-420 for the fit).
+  // One UpdateBestModel call of the reference's LO, in the reference's order. Nothing inside an LO call reads
+  // the best model, so the calls are recorded and applied when the LO call ends; `deferred` ones (the
+  // ScoreModel of the last LSQ iteration of each step, which no fit follows) are scored together then.
+  struct Offer {
+    double score;
+    Model model;
+    bool deferred;
+  };
+
+  // ScoreModel(m) fused with the LeastSquaresFit(fit_thr, m) that follows it in the reference
+  // (ransac.h:409-420 for the fit); the score is recorded as an offer.
   void ScoreThenFit(const LORansacOptions& options, const Solver& solver, utils::Mt19937* rng,
-                    const bool want_score, const double fit_thr, Model* m, double* best_score,
-                    Model* best) const {
+                    const bool want_score, const double fit_thr, Model* m, std::vector<Offer>* offers) const {
     const double thr = options.squared_inlier_threshold_;
     const int* list = nullptr;
     double score = std::numeric_limits<double>::max();
     const int n_inl = FusedPassView(solver, *m, fit_thr, want_score ? &thr : nullptr, &list, &score);
-    if (want_score) UpdateBestModel(score, *m, best_score, best);
+    if (want_score) offers->push_back(Offer{score, *m, false});
     if (n_inl < solver.min_sample_size()) return;
     const int cap = options.min_sample_multiplicator_ * solver.min_sample_size();
     std::vector<int> sample;  // copied out of the result buffer before the solver runs
@@ -455,14 +463,15 @@ class LocallyOptimizedMSAC : public RansacBase {
     const int min_size = solver.min_sample_size();
     const double thr = options.squared_inlier_threshold_;
     const double mult = options.threshold_multiplier_;
+    std::vector<Offer> offers;
 
     Model m_init = *best_minimal_model;
-    ScoreThenFit(options, solver, rng, false, thr * mult, &m_init, nullptr, nullptr);
+    ScoreThenFit(options, solver, rng, false, thr * mult, &m_init, &offers);
 
     std::vector<int> inliers_base;
     double score = std::numeric_limits<double>::max();
     FusedPass(solver, m_init, thr * mult, &thr, &inliers_base, &score);
-    UpdateBestModel(score, m_init, score_best_minimal_model, best_minimal_model);
+    offers.push_back(Offer{score, m_init, false});
 
     const int non_min_size =
         std::max(min_non_min, std::min(min_size * options.non_min_sample_multiplier_,
@@ -474,23 +483,57 @@ class LocallyOptimizedMSAC : public RansacBase {
       Model m;
       if (!solver.NonMinimalSolver(sample, &m)) continue;
       // ScoreModel(m) + LeastSquaresFit(thr, m)   (ransac.h:386-391)
-      ScoreThenFit(options, solver, rng, true, thr, &m, score_best_minimal_model, best_minimal_model);
+      ScoreThenFit(options, solver, rng, true, thr, &m, &offers);
 
       double fit_thr = mult * thr;
       // Reference divides by (num_lsq_iterations_ - 1) as an int (ransac.h:395-397).
       const double step = (mult - 1.0) * thr / static_cast<int>(options.num_lsq_iterations_ - 1);
       if (options.num_lsq_iterations_ <= 0) continue;
-      ScoreThenFit(options, solver, rng, false, fit_thr, &m, nullptr, nullptr);  // fit of i = 0
+      ScoreThenFit(options, solver, rng, false, fit_thr, &m, &offers);  // fit of i = 0
       for (int i = 0; i < options.num_lsq_iterations_; ++i) {
         fit_thr -= step;
         if (i + 1 < options.num_lsq_iterations_) {
           // ScoreModel of iteration i fused with the fit of iteration i + 1.
-          ScoreThenFit(options, solver, rng, true, fit_thr, &m, score_best_minimal_model,
-                       best_minimal_model);
+          ScoreThenFit(options, solver, rng, true, fit_thr, &m, &offers);
         } else {
-          UpdateBestModel(ScoreOnly(solver, m, thr), m, score_best_minimal_model, best_minimal_model);
+          offers.push_back(Offer{std::numeric_limits<double>::max(), m, true});
         }
       }
+    }
+    ApplyOffers(options, solver, &offers, best_minimal_model, score_best_minimal_model);
+  }
+
+  // The recorded UpdateBestModel calls, in order. The deferred models are scored in one f64 sweep first; the
+  // sweep sums its partials in another order than a K = 1 pass, so its score only filters: a model within
+  // 1e-9 of the best so far gets the exact pass before it is offered, any other cannot be strictly better.
+  void ApplyOffers(const LORansacOptions& options, const Solver& solver, std::vector<Offer>* offers,
+                   Model* best, double* best_score) const {
+    const double thr = options.squared_inlier_threshold_;
+    std::vector<double> packed, approx;
+    int num_deferred = 0;
+    for (const Offer& o : *offers) num_deferred += o.deferred ? 1 : 0;
+    if (num_deferred >= 3) {
+      const gpu::DeviceScorer& dev = solver.device_scorer();
+      const int md = dev.model_size();
+      packed.resize(static_cast<size_t>(num_deferred) * md);
+      size_t at = 0;
+      for (const Offer& o : *offers) {
+        if (!o.deferred) continue;
+        Solver::PackModel(o.model, &packed[at]);
+        at += md;
+      }
+      approx.resize(num_deferred);
+      const double thr2[2] = {thr, thr};
+      dev.ScoreModels(num_deferred, packed.data(), nullptr, thr2, nullptr, approx.data(), RLB_F64);
+    }
+    int k = 0;
+    for (Offer& o : *offers) {
+      if (o.deferred) {
+        const int id = k++;
+        if (!approx.empty() && !(approx[id] <= *best_score * (1.0 + 1e-9))) continue;
+        o.score = ScoreOnly(solver, o.model, thr);
+      }
+      UpdateBestModel(o.score, o.model, best_score, best);
     }
   }
 

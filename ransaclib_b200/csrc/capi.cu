@@ -299,7 +299,7 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     int variant;
     double speed;
   };
-  Cand cands[3];
+  Cand cands[4];
   int ncand = 0;
   if (forced_variant >= 0) {
     cands[ncand++] = {forced_variant, 1.0};
@@ -310,6 +310,7 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   } else if (d.kind == RLB_KIND_POSE) {
     cands[ncand++] = {7, 1.00};  // f64, H = 4
     cands[ncand++] = {-1, 0.96};  // f64, H = 2
+    cands[ncand++] = {8, 0.85};  // f64, H = 1: batches of up to ~100 (the LO's deferred scores, small rounds)
   } else {
     cands[ncand++] = {-1, 1.0};  // H = 4
     // H = 1: a batch of up to ~400 hypotheses (the drivers' rounds) leaves 3 of 4 register tiles of the H = 4

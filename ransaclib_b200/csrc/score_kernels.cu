@@ -642,7 +642,7 @@ cudaError_t launch_sweep(const DeviceData& d, const SweepArgs& a, int precision,
       }
     }
     if (a.variant == 7) return launch_sweep_t<PoseF, double, 4>(d, a, st);  // A/B only
-    if (a.variant == 8) return launch_sweep_t<PoseF, double, 1>(d, a, st);  // A/B only
+    if (a.variant == 8) return launch_sweep_t<PoseF, double, 1>(d, a, st);  // small batches
     return launch_sweep_t<PoseF, double, 2>(d, a, st);
   }
   if (a.variant == 10) {
