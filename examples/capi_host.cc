@@ -6,6 +6,7 @@
 // ransaclib_localization.cc:58-165).
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <string>
@@ -239,7 +240,15 @@ int rlbh_hybrid_lomsac_line(const rlbh_hybrid_options* o, int device, int precis
                             const double* xy0, int n1, const double* xynn1, const double* priors,
                             double* model, rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
   return Guard([&] {
-    HybridLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]},
+    // The caller's arrays outlive this call: no host copy (RLB_HOST_COPY=1: the copying constructor, A/B timing).
+    const char* copy = std::getenv("RLB_HOST_COPY");
+    if (copy && copy[0] == '1') {
+      HybridLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]},
+                                 &gpu::Context::ThreadDefault(device));
+      RunHybrid<HybridUniformSampling<HybridLineEstimator>>(*o, solver, precision, model, st, inl0, inl1);
+      return;
+    }
+    HybridLineEstimator solver(gpu::BorrowData(), n0, xy0, n1, xynn1, {priors[0], priors[1]},
                                &gpu::Context::ThreadDefault(device));
     RunHybrid<HybridUniformSampling<HybridLineEstimator>>(*o, solver, precision, model, st, inl0, inl1);
   });

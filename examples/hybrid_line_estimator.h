@@ -20,13 +20,24 @@ class HybridLineEstimator {
   // points: n0 x 2; points_with_normals: n1 x 4 (x, y, nx, ny) == column-major Matrix4Xd.
   HybridLineEstimator(int n0, const double* points, int n1, const double* points_with_normals,
                       const std::vector<double>& prior_probabilities, gpu::Context* ctx = nullptr)
-      : points_(points, points + 2 * static_cast<size_t>(n0)),
+      : own_points_(points, points + 2 * static_cast<size_t>(n0)),
+        own_points_with_normals_(points_with_normals, points_with_normals + 4 * static_cast<size_t>(n1)),
+        points_(own_points_.data()),
         num_points_(n0),
-        points_with_normals_(points_with_normals, points_with_normals + 4 * static_cast<size_t>(n1)),
+        points_with_normals_(own_points_with_normals_.data()),
         num_points_with_normals_(n1),
         prior_probabilities_(prior_probabilities) {
-    scorer_.InitHybridLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n0, points_.data(), n1,
-                           points_with_normals_.data());
+    scorer_.InitHybridLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n0, points_, n1, points_with_normals_);
+  }
+  // The same without the host copy: both arrays must outlive the estimator.
+  HybridLineEstimator(gpu::BorrowData, int n0, const double* points, int n1, const double* points_with_normals,
+                      const std::vector<double>& prior_probabilities, gpu::Context* ctx = nullptr)
+      : points_(points),
+        num_points_(n0),
+        points_with_normals_(points_with_normals),
+        num_points_with_normals_(n1),
+        prior_probabilities_(prior_probabilities) {
+    scorer_.InitHybridLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n0, points_, n1, points_with_normals_);
   }
 
   inline int num_minimal_solvers() const { return 2; }
@@ -133,9 +144,10 @@ class HybridLineEstimator {
   }
 
  protected:
-  std::vector<double> points_;
+  std::vector<double> own_points_, own_points_with_normals_;  // empty when the data is borrowed
+  const double* points_;
   int num_points_;
-  std::vector<double> points_with_normals_;
+  const double* points_with_normals_;
   int num_points_with_normals_;
   std::vector<double> prior_probabilities_;
   std::vector<std::vector<double>> weights_;

@@ -62,6 +62,11 @@ class Context {
   rlb_ctx* ctx_ = nullptr;
 };
 
+// Constructor tag of the example solvers: keep pointers to the caller's point arrays instead of copying them
+// (the arrays must outlive the solver). The reference's estimators copy into Eigen matrices; for a 4.8 MB
+// data set that copy costs as much as its upload.
+struct BorrowData {};
+
 inline int PrecisionFromEnv() {
   const char* p = std::getenv("RLB_PRECISION");
   return (p && (p[0] == 'f' || p[0] == 'F') && p[1] == '3') ? RLB_F32 : RLB_F64;
