@@ -31,11 +31,23 @@ class CalibratedAbsolutePoseEstimator {
       : focal_x_(f_x),
         focal_y_(f_y),
         squared_inlier_threshold_(squared_inlier_threshold),
-        points2D_(points2D, points2D + 2 * static_cast<size_t>(n)),
-        points3D_(points3D, points3D + 3 * static_cast<size_t>(n)),
+        own2D_(points2D, points2D + 2 * static_cast<size_t>(n)),
+        own3D_(points3D, points3D + 3 * static_cast<size_t>(n)),
+        points2D_(own2D_.data()),
+        points3D_(own3D_.data()),
         num_data_(n) {
-    scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), n, points2D_.data(),
-                     points3D_.data(), f_x, f_y);
+    scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), n, points2D_, points3D_, f_x, f_y);
+  }
+  // The same without the host copy: both arrays must outlive the estimator.
+  CalibratedAbsolutePoseEstimator(gpu::BorrowData, double f_x, double f_y, double squared_inlier_threshold, int n,
+                                  const double* points2D, const double* points3D, gpu::Context* ctx = nullptr)
+      : focal_x_(f_x),
+        focal_y_(f_y),
+        squared_inlier_threshold_(squared_inlier_threshold),
+        points2D_(points2D),
+        points3D_(points3D),
+        num_data_(n) {
+    scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), n, points2D_, points3D_, f_x, f_y);
   }
 
   inline int min_sample_size() const { return 4; }          // reference .h:88
@@ -100,8 +112,8 @@ class CalibratedAbsolutePoseEstimator {
 
   // .cc:170-212
   void LeastSquares(const std::vector<int>& sample, CameraPose* pose) const {
-    const refine::SequentialLineariser lin = {static_cast<int>(sample.size()), sample.data(), points2D_.data(),
-                                              points3D_.data(), focal_x_, focal_y_};
+    const refine::SequentialLineariser lin = {static_cast<int>(sample.size()), sample.data(), points2D_,
+                                              points3D_, focal_x_, focal_y_};
     refine::LmWorkspace w;
     refine::LeastSquaresWith(lin, pose->m, &w);
   }
@@ -123,7 +135,9 @@ class CalibratedAbsolutePoseEstimator {
 
  protected:
   double focal_x_, focal_y_, squared_inlier_threshold_;
-  std::vector<double> points2D_, points3D_;
+  std::vector<double> own2D_, own3D_;  // empty when the data is borrowed
+  const double* points2D_;
+  const double* points3D_;
   int num_data_;
   gpu::DeviceScorer scorer_;
 };

@@ -174,6 +174,13 @@ void RunHybrid(const rlbh_hybrid_options& o, HybridLineEstimator& solver, int pr
   if (inl1) std::copy(hs.inlier_indices[1].begin(), hs.inlier_indices[1].end(), inl1);
 }
 
+// The callers' arrays outlive every call of this file, so the solvers borrow them (gpu::BorrowData);
+// RLB_HOST_COPY=1 selects the copying constructors (A/B timing, and the tests run both).
+bool HostCopy() {
+  const char* copy = std::getenv("RLB_HOST_COPY");
+  return copy && copy[0] == '1';
+}
+
 template <class F>
 int Guard(F f) {
   try {
@@ -195,9 +202,13 @@ const char* rlbh_last_error(void) { return g_error.c_str(); }
 int rlbh_lomsac_line(const rlbh_options* o, int device, int precision, int n, const double* xy,
                      double* model, rlbh_stats* st, int32_t* inliers) {
   return Guard([&] {
-    LineEstimator solver(n, xy, &gpu::Context::ThreadDefault(device));
-    Run<Line2D, Lines2D, LineEstimator>(*o, solver, precision, reinterpret_cast<Line2D*>(model), st,
-                                        inliers);
+    if (HostCopy()) {
+      LineEstimator solver(n, xy, &gpu::Context::ThreadDefault(device));
+      Run<Line2D, Lines2D, LineEstimator>(*o, solver, precision, reinterpret_cast<Line2D*>(model), st, inliers);
+      return;
+    }
+    LineEstimator solver(gpu::BorrowData(), n, xy, &gpu::Context::ThreadDefault(device));
+    Run<Line2D, Lines2D, LineEstimator>(*o, solver, precision, reinterpret_cast<Line2D*>(model), st, inliers);
   });
 }
 
@@ -215,7 +226,14 @@ int rlbh_lomsac_pose(const rlbh_options* o, int device, int precision, double fx
                      const double* p2d, const double* p3d, double* model, rlbh_stats* st,
                      int32_t* inliers) {
   return Guard([&] {
-    CalibratedAbsolutePoseEstimator solver(fx, fy, o->sq_thr, n, p2d, p3d,
+    if (HostCopy()) {
+      CalibratedAbsolutePoseEstimator solver(fx, fy, o->sq_thr, n, p2d, p3d,
+                                             &gpu::Context::ThreadDefault(device));
+      Run<CameraPose, CameraPoses, CalibratedAbsolutePoseEstimator>(
+          *o, solver, precision, reinterpret_cast<CameraPose*>(model), st, inliers);
+      return;
+    }
+    CalibratedAbsolutePoseEstimator solver(gpu::BorrowData(), fx, fy, o->sq_thr, n, p2d, p3d,
                                            &gpu::Context::ThreadDefault(device));
     Run<CameraPose, CameraPoses, CalibratedAbsolutePoseEstimator>(
         *o, solver, precision, reinterpret_cast<CameraPose*>(model), st, inliers);
@@ -240,9 +258,7 @@ int rlbh_hybrid_lomsac_line(const rlbh_hybrid_options* o, int device, int precis
                             const double* xy0, int n1, const double* xynn1, const double* priors,
                             double* model, rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
   return Guard([&] {
-    // The caller's arrays outlive this call: no host copy (RLB_HOST_COPY=1: the copying constructor, A/B timing).
-    const char* copy = std::getenv("RLB_HOST_COPY");
-    if (copy && copy[0] == '1') {
+    if (HostCopy()) {
       HybridLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]},
                                  &gpu::Context::ThreadDefault(device));
       RunHybrid<HybridUniformSampling<HybridLineEstimator>>(*o, solver, precision, model, st, inl0, inl1);

@@ -20,8 +20,13 @@ class LineEstimator {
   // data: n x 2 doubles (x0,y0,x1,y1,...) == column-major Eigen::Matrix2Xd. Copied to the
   // host member and uploaded once (line_estimator.cc:47-50).
   LineEstimator(int n, const double* data, gpu::Context* ctx = nullptr)
-      : data_(data, data + 2 * static_cast<size_t>(n)), num_data_(n) {
-    scorer_.InitLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n, data_.data());
+      : own_(data, data + 2 * static_cast<size_t>(n)), data_(own_.data()), num_data_(n) {
+    scorer_.InitLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n, data_);
+  }
+  // The same without the host copy: the array must outlive the estimator.
+  LineEstimator(gpu::BorrowData, int n, const double* data, gpu::Context* ctx = nullptr)
+      : data_(data), num_data_(n) {
+    scorer_.InitLine(ctx ? *ctx : gpu::Context::ThreadDefault(), n, data_);
   }
 
   static constexpr int kDeviceLomsacMaxPoints = 24576;  // measured crossover ~30k (tools/line_crossover.py)
@@ -97,7 +102,8 @@ class LineEstimator {
  protected:
   double x(int i) const { return data_[2 * static_cast<size_t>(i)]; }
   double y(int i) const { return data_[2 * static_cast<size_t>(i) + 1]; }
-  std::vector<double> data_;
+  std::vector<double> own_;  // empty when the data is borrowed
+  const double* data_;
   int num_data_;
   gpu::DeviceScorer scorer_;
 };

@@ -277,3 +277,33 @@ def test_pyransaclib_localization():
               lo_start=60)
     om, ost, oinl = oracle_pose(inst["points2D"], inst["points3D"], float(f), **kw)
     assert r["inliers"] == oinl.tolist()
+
+
+def test_copying_and_borrowing_constructors_agree(monkeypatch):
+    """The example solvers either copy the caller's arrays (as the reference's estimators do) or, tagged
+    gpu::BorrowData, keep pointers to them; the mirror borrows, RLB_HOST_COPY=1 selects the copies. Same runs."""
+    H = host()
+    xy = synth.line_instance(5, 2000, 1500)
+    inst = synth.pose_instance(6, 800, 700)
+    xy0, p1 = synth.hybrid_line_instance(7, 900, 600, 700, 500)
+    lo = H.LORansacOptions(squared_inlier_threshold_=1e-4, random_seed_=3)
+    po = H.LORansacOptions(squared_inlier_threshold_=144.0, random_seed_=4)
+    ho = H.HybridLORansacOptions(squared_inlier_thresholds_=[1e-4, 1e-4], data_type_weights_=[2.0, 0.5], random_seed_=5,
+                                 max_num_iterations_per_solver_=1000)
+
+    def runs():
+        f = inst["focal"]
+        a = H.estimate_line(lo, xy)
+        b = H.estimate_pose(po, f, f, inst["points2D"], inst["points3D"])
+        c = H.estimate_hybrid_line(ho, xy0, p1, [0.2, 0.8])
+        out = []
+        for m, st in (a, b, c):
+            idx = st["inlier_indices"]
+            lists = idx if isinstance(idx, list) else [idx]
+            out.append((np.asarray(m).tolist(), st["best_model_score"], [np.asarray(x).tolist() for x in lists]))
+        return out
+
+    borrowed = runs()
+    monkeypatch.setenv("RLB_HOST_COPY", "1")
+    copied = runs()
+    assert borrowed == copied
