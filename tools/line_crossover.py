@@ -7,7 +7,7 @@ import ransaclib_b200 as rlb
 from ransaclib_b200 import host as H, synth
 
 ctx = rlb.Context(0)
-for n in (2000, 10000, 30000, 60000, 120000, 250000):
+for n in (2000, 10000, 16000, 20000, 24000, 30000, 60000, 120000, 250000):
     xy = synth.line_instance(77, n // 2, n - n // 2)
     kw = dict(sq_thr=1e-4, min_iters=100, max_iters=100000)
     sc = ctx.line_scorer(xy)
