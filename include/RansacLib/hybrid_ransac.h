@@ -127,6 +127,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
     const int precision = solver.device_scorer().precision();
 
     Batch batch;
+    bool lists_stale = false;  // stats.inlier_indices lag behind *best_model
     uint32_t next_batch_size = 128u;
     std::vector<std::vector<int>> sample(num_types);
 
@@ -137,7 +138,7 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
         ++stats.number_lo_iterations;
         LocalOptimization(options, solver, stats.best_solver_type, &rng, best_model,
                           &stats.best_model_score, &stats.best_solver_type);
-        UpdateRANSACTerminationCriteria(options, solver, *best_model, statistics, &max_per_solver);
+        UpdateRANSACTerminationCriteria(options, solver, *best_model, statistics, &max_per_solver, &lists_stale);
         batch.count = 0;  // RNG and ratios changed: speculation is stale
       }
 
@@ -193,7 +194,8 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
             UpdateBestModel(score, best_minimal_model, type, &stats.best_model_score, best_model,
                             &stats.best_solver_type);
           }
-          UpdateRANSACTerminationCriteria(options, solver, *best_model, statistics, &max_per_solver);
+          UpdateRANSACTerminationCriteria(options, solver, *best_model, statistics, &max_per_solver,
+                                          &lists_stale);
           batch.count = 0;
         }
       }
@@ -206,7 +208,11 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
       LocalOptimization(options, solver, stats.best_solver_type, &rng, best_model,
                         &stats.best_model_score, &stats.best_solver_type);
       UpdateRANSACTerminationCriteria(options, solver, *best_model, statistics, &max_per_solver);
+      lists_stale = false;
     }
+    if (lists_stale)  // the lists of the last update inside the loop
+      FusedPass(options, solver, *best_model, options.squared_inlier_thresholds_, false,
+                &stats.inlier_indices, nullptr);
 
     if (options.final_least_squares_) {  // :299-317
       Model refined = *best_model;
@@ -391,15 +397,30 @@ class HybridLocallyOptimizedMSAC : public HybridRansacBase {
   void UpdateRANSACTerminationCriteria(const HybridLORansacOptions& options,
                                        const HybridSolver& solver, const Model& model,
                                        HybridRansacStatistics* statistics,
-                                       std::vector<uint32_t>* max_iterations) const {
-    statistics->best_num_inliers = FusedPass(options, solver, model, options.squared_inlier_thresholds_,
-                                             false, &statistics->inlier_indices, nullptr);
+                                       std::vector<uint32_t>* max_iterations,
+                                       bool* lists_stale = nullptr) const {
+    // The ratios need the per-type counts only. Inside the main loop the lists themselves are left for the
+    // end of EstimateModel (*lists_stale): every new best model would otherwise fetch and copy them.
     std::vector<int> nd;
     solver.num_data(&nd);
+    int32_t counts[2] = {0, 0};
+    if (lists_stale) {
+      double packed[16];
+      HybridSolver::PackModel(model, packed);
+      solver.device_scorer().InliersAndScore(packed, options.squared_inlier_thresholds_.data(), nullptr,
+                                             options.data_type_weights_.data(), nullptr, counts, nullptr);
+      *lists_stale = true;
+    } else {
+      FusedPass(options, solver, model, options.squared_inlier_thresholds_, false,
+                &statistics->inlier_indices, nullptr);
+      for (size_t d = 0; d < nd.size() && d < 2; ++d)
+        counts[d] = static_cast<int32_t>(statistics->inlier_indices[d].size());
+    }
+    statistics->best_num_inliers = 0;
     for (size_t d = 0; d < nd.size(); ++d) {
-      statistics->inlier_ratios[d] =
-          nd[d] > 0 ? static_cast<double>(statistics->inlier_indices[d].size()) / static_cast<double>(nd[d])
-                    : 0.0;
+      const int c = d < 2 ? counts[d] : 0;
+      statistics->best_num_inliers += c;
+      statistics->inlier_ratios[d] = nd[d] > 0 ? static_cast<double>(c) / static_cast<double>(nd[d]) : 0.0;
     }
     std::vector<std::vector<int>> sizes;
     solver.min_sample_sizes(&sizes);
