@@ -164,11 +164,21 @@ def run_ours(args):
     my_samples = np.ascontiguousarray(samples_all[id_lo:id_hi])  # contiguous id ranges per rank
 
     ctx = rlb.Context(local)
-    stream = torch.cuda.Stream(dev)  # one explicit stream for our kernels, torch's glue and NCCL
+    stream = torch.cuda.Stream(dev)  # one explicit stream for our kernels and the library's NCCL calls
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
     ctx.set_timing(True)
-    scorer = ctx.pose_scorer(p2, p3, f, f)  # points resident in HBM before the timed region
+    # The data plane's collectives live in the library (rlb_comm_*: ncclBroadcast of the points, one
+    # ncclAllGather per round); torch.distributed only carries the unique id, barriers and the timing max.
+    uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0 and world > 1:
+        uid.copy_(torch.frombuffer(bytearray(rlb.Comm.unique_id()), dtype=torch.uint8))
+    if world > 1:
+        dist.broadcast(uid, 0)
+    comm = rlb.Comm.from_rank(ctx, world, rank, bytes(uid.cpu().numpy().tobytes()) if world > 1 else None)
+    # points resident in HBM before the timed region: one PCIe upload on rank 0, NVLink broadcast to the others
+    cscorer = comm.pose_scorer(p2 if rank == 0 else n, p3 if rank == 0 else None, f, f, root=0)
+    scorer = rlb.Scorer(ctx, cscorer.local_scorer_handle(0), borrowed=True)
 
     d_samples = torch.from_numpy(my_samples).to(dev)
     d_models = torch.empty((k, 12), dtype=torch.float64, device=dev)
@@ -176,26 +186,18 @@ def run_ours(args):
     d_scores = torch.empty(k, dtype=torch.float64, device=dev)
     d_counts = torch.empty(k, dtype=torch.int32, device=dev)
     d_best = torch.zeros(2, dtype=torch.float64, device=dev)  # {double score; int64 id}
-    d_gather = torch.zeros((world, 14), dtype=torch.float64, device=dev)
     d_idx = torch.empty(n, dtype=torch.int32, device=dev)
     d_hdr = torch.zeros(4, dtype=torch.float64, device=dev)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
-    d_rec = torch.zeros(14, dtype=torch.float64, device=dev)   # this rank's record
     d_winner = torch.zeros(14, dtype=torch.float64, device=dev)  # {score, global id, model[12]}
 
-    def step():
-        # solve + sweep + argmin; the shard's (score, global id, model) record lands in d_rec
-        scorer.sharded_round_dev(d_samples.data_ptr(), k, THR, None, id_lo, d_models.data_ptr(),
-                                 d_valid.data_ptr(), d_scores.data_ptr(),
-                                 d_counts.data_ptr() if args.counts else 0,
-                                 d_rec.data_ptr(), precision=prec)
-        if world > 1:
-            dist.all_gather_into_tensor(d_gather, d_rec)  # the single collective of the round
-            g = d_gather
-        else:
-            g = d_rec
-        ctx.select_winner_dev(g.data_ptr(), world, 14, d_winner.data_ptr())
+    def step(p=None):
+        # rlb_comm_round_dev: solve + sweep + argmin of this rank's shard, ONE ncclAllGather of the ranks'
+        # (score, global id, model) records, lexicographic winner on every rank; then the winner's inliers
+        cscorer.round_dev(d_samples.data_ptr(), k, THR, id_lo, d_models.data_ptr(), d_valid.data_ptr(),
+                          d_scores.data_ptr(), d_counts.data_ptr() if args.counts else 0, d_winner.data_ptr(),
+                          precision=prec if p is None else p)
         scorer.get_inliers_dev(d_winner.data_ptr() + 16, THR, THR, None, d_idx.data_ptr(), d_hdr.data_ptr())
 
     for _ in range(args.warmup):
@@ -238,25 +240,29 @@ def run_ours(args):
     n_inl = int(hdr.view(np.int32)[3])
     best_score = float(d_hdr[0].item())
 
+    # ---- parity (once, untimed): f32 against f64 on ALL hypotheses, a sample against the reference's own
+    #      loops, and (N > 1) the gathered winner against a single-GPU recomputation ---------------------
+    parity = None
+    if not args.profile:
+        parity = measure_parity(args, rank, world, dev, ctx, scorer, step, d_samples, d_models, d_valid,
+                                d_scores, d_counts, d_winner, samples_all, k_total, p2, p3, f, dist)
+
     # ---- e2e: the same step through the host-buffer C ABI, copies inside the timed region ----
     pin = lambda a: torch.from_numpy(a).pin_memory().numpy()  # noqa: E731
-    h_p2, h_p3, h_s = pin(p2), pin(p3), pin(my_samples)
+    h_p2, h_p3 = pin(p2), pin(p3)
     e2e_steps = max(1, min(args.steps, 5))
 
+    h_all = pin(np.ascontiguousarray(samples_all))
+
     def e2e_step():
-        sc = ctx.pose_scorer(h_p2, h_p3, f, f)  # H2D of the correspondences + SoA repack
-        r = sc.hypothesize_and_score(h_s, THR, precision=prec, want_models=False)
-        bm = r["best_model"]
-        if world > 1:
-            pk = torch.tensor([r["best_score"], float(r["best_id"] + id_lo), *bm], dtype=torch.float64,
-                              device=dev)
-            dist.all_gather_into_tensor(d_gather, pk)
-            g = d_gather.cpu().numpy()
-            order = np.lexsort((g[:, 1], g[:, 0]))
-            bm = g[order[0], 2:]
-        lists, counts, score = sc.get_inliers(bm, THR, THR)
-        sc.close()
-        return r, counts
+        # host buffers in, results out, everything inside: the points go up ONCE (rank 0, PCIe) and reach the
+        # other GPUs by ncclBroadcast; every rank uploads its shard of the samples; one ncclAllGather; the
+        # winner's ordered inlier list comes back from the first GPU of every process
+        cs = comm.pose_scorer(h_p2 if rank == 0 else n, h_p3 if rank == 0 else None, f, f, root=0)
+        r = cs.hypothesize_and_score(h_all, THR, precision=prec, want_scores=True)
+        inl, score = cs.get_inliers(r["best_model"], THR, THR)
+        cs.close()
+        return r, [len(inl)]
 
     if args.profile:
         if rank == 0:
@@ -279,7 +285,7 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = k_total * n * e2e_steps / float(te.item())
-    h2d = p2.nbytes + p3.nbytes + my_samples.nbytes + 12 * 8
+    h2d = (p2.nbytes + p3.nbytes if rank == 0 else 0) + my_samples.nbytes + 12 * 8
     d2h = k * 8 + k * 4 + 16 + 96 + 16 + 4 * int(c_e2e[0])
 
     # ---- second half of BASELINE.json's metric: batched localization (configs[3]) on the same GPUs ----
@@ -368,9 +374,14 @@ def run_ours(args):
                    "step": "P3P solve + KxN MSAC sweep + argmin + ordered inlier list of the winner"},
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                "path": "rlb_scorer_create_pose + rlb_hypothesize_and_score + rlb_get_inliers with pinned host buffers"},
+                "path": "rlb_comm_scorer_create_pose (one PCIe upload on rank 0 + ncclBroadcast) + "
+                        "rlb_comm_hypothesize_and_score (shard upload, sweep, one ncclAllGather, scores + counts "
+                        "back) + rlb_comm_get_inliers, pinned host buffers; bytes are rank 0's"},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
-        "result": {"num_inliers": n_inl, "best_score": best_score},
+        "result": {"num_inliers": n_inl, "best_score": best_score}, "parity": parity,
+        "comm": {"nranks": comm.nranks, "collectives_issued": comm.collective_count,
+                 "note": "rlb_comm_*: NCCL inside the library (ncclBroadcast of the points, one ncclAllGather per "
+                         "round); torch.distributed carries only the unique id, barriers and the timing max"},
     }
     if loc is not None:
         if world == 1:
@@ -381,12 +392,99 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def measure_parity(args, rank, world, dev, ctx, scorer, step, d_samples, d_models, d_valid, d_scores, d_counts,
+                   d_winner, samples_all, k_total, p2, p3, f, dist):
+    """Full-size parity of the timed workload, outside the timed region. Returns the dict on rank 0."""
+    import torch
+
+    import ransaclib_b200 as rlb
+
+    k = d_samples.shape[0]
+    if not args.counts:
+        return {"skipped": "--no-counts run"}
+    step(rlb.RLB_F32)
+    torch.cuda.synchronize()
+    w32 = d_winner.cpu().numpy().copy()
+    s32, c32 = d_scores.clone(), d_counts.clone()
+    step(rlb.RLB_F64)
+    torch.cuda.synchronize()
+    w64 = d_winner.cpu().numpy().copy()
+    s64, c64 = d_scores.clone(), d_counts.clone()
+    ok = (d_valid == 1) & torch.isfinite(s64)
+    rel = ((s32 - s64).abs() / s64.abs())[ok]
+    stats = torch.tensor([float(rel.max().item()) if rel.numel() else 0.0, float((c32 != c64)[ok].sum().item()),
+                          float(ok.sum().item())], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = stats[:1].clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats[1:].clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        stats = torch.cat([mx, sm])
+    out = {"f32_vs_f64": {"hypotheses": int(stats[2].item()), "same_best_id": bool(w32[1] == w64[1]),
+                          "best_id": int(w64[1]), "max_rel_score_diff": float(stats[0].item()),
+                          "tolerance": 1e-4, "count_mismatches": int(stats[1].item()),
+                          "note": "all valid hypotheses of the timed workload; counts may differ only for points "
+                                  "whose f32 error is within rounding of the threshold"}}
+    assert out["f32_vs_f64"]["same_best_id"], "f32 and f64 sweeps select different hypotheses"
+    assert out["f32_vs_f64"]["max_rel_score_diff"] <= 1e-4, out
+    if rank != 0:
+        return None
+    # the reference's own ScoreModel / GetInliers loops on a random sample of this rank's hypotheses
+    ol, lib, kind = _load_ref(strict=True)
+    rng = np.random.default_rng(7)
+    valid_ids = torch.nonzero(ok).flatten().cpu().numpy()
+    ids = np.sort(rng.choice(valid_ids, size=min(256, len(valid_ids)), replace=False))
+    ids = np.unique(np.concatenate([ids, [int(w64[1]) - 0] if 0 <= int(w64[1]) < k else []]).astype(np.int64))
+    models = d_models[torch.from_numpy(ids).to(dev)].cpu().numpy()
+    t0 = time.perf_counter()
+    ws, wc = _ref_scores(ol, lib, f, p2, p3, models, THR)
+    dt = time.perf_counter() - t0
+    g64 = s64[torch.from_numpy(ids).to(dev)].cpu().numpy()
+    gc = c64[torch.from_numpy(ids).to(dev)].cpu().numpy()
+    rel_o = float(np.max(np.abs(g64 - ws) / np.abs(ws)))
+    out["oracle"] = {"kind": kind, "hypotheses": int(len(ids)), "max_rel_score_diff": rel_o, "tolerance": 1e-9,
+                     "counts_exact": bool((gc == wc).all()), "seconds": dt,
+                     "note": "f64 sweep vs the reference's ransac.h ScoreModel / GetInliers loops (oracle/_ref, "
+                             "strict IEEE build) over all N points"}
+    assert rel_o <= 1e-9 and out["oracle"]["counts_exact"], out["oracle"]
+    if world > 1:
+        # one GPU sweeps ALL k_total hypotheses: the N-GPU winner must be that winner
+        d_all = torch.from_numpy(np.ascontiguousarray(samples_all)).to(dev)
+        m_all = torch.empty((k_total, 12), dtype=torch.float64, device=dev)
+        v_all = torch.empty(k_total, dtype=torch.uint8, device=dev)
+        rec = torch.zeros(14, dtype=torch.float64, device=dev)
+        scorer.sharded_round_dev(d_all.data_ptr(), k_total, THR, None, 0, m_all.data_ptr(), v_all.data_ptr(), 0, 0,
+                                 rec.data_ptr(), precision=rlb.RLB_F64)
+        torch.cuda.synchronize()
+        r1 = rec.cpu().numpy()
+        same = bool(r1[1] == w64[1] and abs(r1[0] - w64[0]) <= 1e-12 * abs(r1[0]) and (r1[2:] == w64[2:]).all())
+        out["multi_gpu"] = {"winner_equals_single_gpu": same, "single_gpu_best_id": int(r1[1]),
+                            "n_gpu_best_id": int(w64[1])}
+        assert same, out["multi_gpu"]
+    return out
+
+
+def _ref_scores(ol, lib, f, p2, p3, models, thr, threads=0):
+    """ScoreModel + inlier count of each model by the reference's loops, `threads` models at a time."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    threads = threads or host_threads()
+    chunks = [c for c in np.array_split(np.arange(len(models)), max(1, min(threads, len(models)))) if len(c)]
+
+    def work(c):
+        return ol.pose_score(lib, f, f, p2, p3, models[c], thr)
+
+    with ThreadPoolExecutor(len(chunks)) as ex:
+        res = list(ex.map(work, chunks))
+    return np.concatenate([r[0] for r in res]), np.concatenate([r[1] for r in res])
+
+
 # ------------------------------------------------------------------- CPU baselines
-def _load_ref():
+def _load_ref(strict=False):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
 
-    lib = ol.reference(fast=True)
+    lib = ol.reference(fast=not strict)
     kind = "reference"
     if lib is None:
         lib, kind = ol.oracle(), "port"

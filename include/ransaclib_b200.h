@@ -40,6 +40,7 @@ extern "C" {
 #define RLB_E_ARG -2      /* invalid argument */
 #define RLB_E_KIND -3     /* operation not defined for this scorer kind */
 #define RLB_E_NOMEM -4
+#define RLB_E_COMM -5     /* NCCL error, or NCCL not loadable (multi-GPU entry points only) */
 
 /* arithmetic the K x N sweep runs in. Inlier lists are always collected in f64. */
 #define RLB_F64 0 /* reference-exact semantics, scores within 1e-9 rel */
@@ -82,6 +83,10 @@ int rlb_scorer_create_hybrid_line(rlb_ctx* ctx, int n0, const double* xy0, int n
  * as PixelsToViewingRays does (.cc:214-227). */
 int rlb_scorer_create_pose(rlb_ctx* ctx, int n, const double* points2D,
                            const double* points3D, double fx, double fy, rlb_scorer** out);
+/* Same data set from DEVICE pointers (copied; the caller keeps its buffers). Builds the same scorer as the
+ * host-pointer constructor, bit for bit. */
+int rlb_scorer_create_pose_dev(rlb_ctx* ctx, int n, const double* d_points2D, const double* d_points3D,
+                               double fx, double fy, rlb_scorer** out);
 /* Any other solver of the README's concept (reference README.md:105-154): its
  *   double EvaluateModelOnPoint(const Model& model, int i) const
  * is handed over as CUDA source defining
@@ -184,8 +189,7 @@ int rlb_hypothesize_and_score_dev(rlb_scorer* s, int precision, int solver, int 
                                   const double* weights, double* d_models, uint8_t* d_valid,
                                   double* d_scores, int32_t* d_counts, void* d_best);
 
-/* ---- hypothesis-sharded rounds (one process per GPU; the collective itself is the caller's:
- *      NCCL all_gather of one record per rank) ------------------------------------------- */
+/* ---- hypothesis-sharded rounds: the building blocks (rlb_comm_* below puts the collective around them) - */
 /* rlb_hypothesize_and_score_dev for this rank's shard; additionally writes the shard's
  * record = {double score; double global_id (= local id + id_offset, -1 if none);
  * double model[model_size]} to d_record. Ranks must own ascending contiguous id ranges so
@@ -199,10 +203,62 @@ int rlb_sharded_round_dev(rlb_scorer* s, int precision, int solver, int k, const
 int rlb_select_winner_dev(rlb_ctx* ctx, const double* d_records, int world, int record_doubles,
                           double* d_winner);
 
+/* ---- multi-GPU: hypothesis-sharded scoring with the collective inside the library ----------
+ * a round of K hypotheses is cut into contiguous, ascending id ranges, one per GPU (the
+ * point set is replicated); every GPU sweeps its range (rlb_sharded_round_dev) and contributes ONE record
+ * {score, global id, model} to ONE ncclAllGather per round; every rank then takes the lexicographic
+ * (score, id) minimum (rlb_select_winner_dev), i.e. exactly the model the sequential loop of
+ * LocallyOptimizedMSAC::EstimateModel (ransac.h:158-240; strict <, lowest id wins ties: :195,288) would
+ * hold after those K iterations. The point set goes up ONCE over PCIe (root) and reaches the other GPUs by
+ * ncclBroadcast over NVLink. NCCL is dlopen()ed on first use (libnccl.so.2); without it these entry
+ * points return RLB_E_COMM. K = 1 passes (GetInliers, LO rescoring) do not shard: replicas only.
+ *
+ * A communicator drives `num_local` GPUs of this process: all of them (rlb_comm_create_local: one process,
+ * ncclCommInitAll, contexts owned by the communicator) or one (rlb_comm_init_rank: one process per GPU,
+ * the caller distributes the unique id). */
+typedef struct rlb_comm rlb_comm;
+typedef struct rlb_comm_scorer rlb_comm_scorer; /* one replicated data set: a scorer per local GPU */
+#define RLB_COMM_ID_BYTES 128
+int rlb_comm_get_unique_id(void* id /* RLB_COMM_ID_BYTES */);
+int rlb_comm_init_rank(rlb_ctx* ctx, int nranks, int rank, const void* id, rlb_comm** out);
+int rlb_comm_create_local(int ndev, const int* devices /* NULL: 0..ndev-1 */, rlb_comm** out);
+int rlb_comm_destroy(rlb_comm* comm); /* destroy the communicator's scorers first */
+int rlb_comm_nranks(const rlb_comm* comm);
+int rlb_comm_num_local(const rlb_comm* comm);
+int rlb_comm_rank(const rlb_comm* comm, int local_index);
+rlb_ctx* rlb_comm_ctx(rlb_comm* comm, int local_index);
+int64_t rlb_comm_collective_count(const rlb_comm* comm); /* NCCL collectives issued so far */
+
+/* CalibratedAbsolutePoseEstimator's data on every GPU of the communicator. Collective: every process of
+ * the communicator calls it; points2D / points3D are read on the process that owns rank `root` only. */
+int rlb_comm_scorer_create_pose(rlb_comm* comm, int n, const double* points2D, const double* points3D,
+                                double fx, double fy, int root, rlb_comm_scorer** out);
+int rlb_comm_scorer_destroy(rlb_comm_scorer* cs);
+rlb_scorer* rlb_comm_scorer_local(rlb_comm_scorer* cs, int local_index);
+
+/* One round over k_total hypotheses (collective). samples: ALL k_total x sample_size indices, the same
+ * array on every process; rank r uploads and scores ids [r*K/G .. (r+1)*K/G). best_id is the GLOBAL
+ * hypothesis id (-1: no model anywhere), identical on every rank. scores / counts (optional, k_total
+ * entries): the slices of this process's GPUs are filled, the rest is left untouched. */
+int rlb_comm_hypothesize_and_score(rlb_comm_scorer* cs, int precision, int solver, int k_total,
+                                   const int32_t* samples, const double* sq_thr, const double* weights,
+                                   double* scores, int32_t* counts, int64_t* best_id, double* best_score,
+                                   double* best_model);
+/* Device-pointer form of the same round for the one-process-per-GPU communicator: this rank's shard
+ * (k_local hypotheses, global ids id_offset ...) is already in HBM; asynchronous on the context stream.
+ * d_winner: {score, global id as f64, model[model_size]} on every rank. */
+int rlb_comm_round_dev(rlb_comm_scorer* cs, int precision, int solver, int k_local, const int32_t* d_samples,
+                       const double* sq_thr, const double* weights, int64_t id_offset, double* d_models,
+                       uint8_t* d_valid, double* d_scores, int32_t* d_counts, double* d_winner);
+/* GetInliers of the winning model: answered by the first local GPU (K = 1 passes do not shard). */
+int rlb_comm_get_inliers(rlb_comm_scorer* cs, const double* model, const double* sq_thr_inl,
+                         const double* sq_thr_score, const double* weights, int32_t* idx, int32_t* counts,
+                         double* score);
+
 /* ---- device-resident batched localization ------------------------------------
  * Q independent P3P LO-MSAC runs (pyransaclib.ransaclib_localization,
  * examples/ransaclib_localization.cc:58-165, one call per query image) in ONE launch: each
- * warp of a persistent grid runs the whole of LocallyOptimizedMSAC::EstimateModel
+ * CTA of a persistent grid runs the whole of LocallyOptimizedMSAC::EstimateModel
  * (ransac.h:128-275) for one query at a time — seeded std::mt19937 sampling and shuffles,
  * P3P + 4th-point test, MSAC scoring, local optimisation with the Levenberg-Marquardt pose
  * refinement (calibrated_absolute_pose_estimator.cc:170-212) — without host round trips.
@@ -243,7 +299,9 @@ void rlb_localize_default_options(rlb_localize_options* opt, double inlier_thres
  * fx, fy, seeds: one per query (the reference seeds from std::random_device; here the seed is an
  * argument so runs are reproducible). Outputs: poses = num_queries x 12 (column-major [R | c]),
  * results = num_queries records, inliers = `total` int32 (ascending inlier indices of query q
- * start at offsets[q]; entries past results[q].num_inliers are unspecified) or NULL. Uploads are pipelined with the kernel in chunks of queries. */
+ * start at offsets[q]; entries past results[q].num_inliers are unspecified) or NULL. The matches go up in a
+ * few chunks of queries; each chunk's grid is launched on its own stream behind that chunk's copies
+ * (cudaStreamWaitEvent), so upload and compute overlap and no kernel ever waits on the host. */
 int rlb_localize_batch(rlb_ctx* ctx, int num_queries, const int64_t* offsets,
                        const double* points2D, const double* points3D, const double* fx,
                        const double* fy, const uint32_t* seeds, const rlb_localize_options* opt,

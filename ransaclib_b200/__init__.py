@@ -14,7 +14,7 @@ import numpy as np
 from . import _capi
 from ._capi import KIND_HYBRID_LINE, KIND_LINE, KIND_POSE, RLB_F32, RLB_F64, RlbError
 
-__all__ = ["Context", "Scorer", "RLB_F64", "RLB_F32", "RlbError", "KIND_LINE", "KIND_HYBRID_LINE", "KIND_POSE"]
+__all__ = ["Context", "Scorer", "Comm", "CommScorer", "RLB_F64", "RLB_F32", "RlbError", "KIND_LINE", "KIND_HYBRID_LINE", "KIND_POSE"]
 
 DBL_MAX = float(np.finfo(np.float64).max)
 
@@ -22,10 +22,14 @@ DBL_MAX = float(np.finfo(np.float64).max)
 class Context:
     """One device + one stream + scratch memory (``rlb_ctx``)."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, _borrowed=None):
         self._lib = _capi.load()
-        h = C.c_void_p()
-        _capi.check(self._lib.rlb_ctx_create(device, C.byref(h)))
+        self._owned = _borrowed is None
+        if _borrowed is None:
+            h = C.c_void_p()
+            _capi.check(self._lib.rlb_ctx_create(device, C.byref(h)))
+        else:
+            h = C.c_void_p(_borrowed)  # a context owned by an rlb_comm
         self._h = h
         self.device = device
         self._scorers = weakref.WeakSet()  # scorers must be released before their context
@@ -34,7 +38,8 @@ class Context:
         if getattr(self, "_h", None):
             for sc in list(self._scorers):
                 sc.close()
-            self._lib.rlb_ctx_destroy(self._h)
+            if self._owned:
+                self._lib.rlb_ctx_destroy(self._h)
             self._h = None
 
     def __del__(self):
@@ -203,6 +208,147 @@ class Context:
         return Scorer(self, h)
 
 
+class Comm:
+    """Hypothesis-sharded scoring over several GPUs with the collective inside the library (``rlb_comm``):
+    ``Comm.local(ndev)`` drives ``ndev`` GPUs from this process, ``Comm.from_rank(ctx, nranks, rank, uid)`` is
+    the one-process-per-GPU form (``Comm.unique_id()`` on rank 0, handed to the others by the caller)."""
+
+    def __init__(self, handle, ctx=None):
+        self._lib = _capi.load()
+        self._h = handle
+        self._ctx = ctx  # keeps a caller-owned context alive
+        self._scorers = weakref.WeakSet()
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(_capi.COMM_ID_BYTES)
+        _capi.check(_capi.load().rlb_comm_get_unique_id(buf))
+        return buf.raw
+
+    @classmethod
+    def from_rank(cls, ctx: "Context", nranks: int, rank: int, uid: bytes | None) -> "Comm":
+        h = C.c_void_p()
+        buf = C.create_string_buffer(uid, _capi.COMM_ID_BYTES) if uid is not None else None
+        _capi.check(_capi.load().rlb_comm_init_rank(ctx._h, int(nranks), int(rank), buf, C.byref(h)))
+        return cls(h, ctx)
+
+    @classmethod
+    def local(cls, ndev: int, devices=None) -> "Comm":
+        h = C.c_void_p()
+        d = None if devices is None else _capi.i32a(devices)
+        _capi.check(_capi.load().rlb_comm_create_local(int(ndev), _capi.ptr(d), C.byref(h)))
+        return cls(h)
+
+    @property
+    def nranks(self) -> int:
+        return int(self._lib.rlb_comm_nranks(self._h))
+
+    @property
+    def num_local(self) -> int:
+        return int(self._lib.rlb_comm_num_local(self._h))
+
+    def rank(self, local_index: int = 0) -> int:
+        return int(self._lib.rlb_comm_rank(self._h, local_index))
+
+    @property
+    def collective_count(self) -> int:
+        return int(self._lib.rlb_comm_collective_count(self._h))
+
+    def context(self, local_index: int = 0) -> "Context":
+        """The context of a local GPU (owned by the communicator or by the caller; not closed here)."""
+        return Context(0, _borrowed=self._lib.rlb_comm_ctx(self._h, local_index))
+
+    def pose_scorer(self, points2D, points3D, fx: float, fy: float, root: int = 0) -> "CommScorer":
+        """Collective. The arrays are read on the process that owns rank `root` (one PCIe upload) and reach
+        the other GPUs by ncclBroadcast; other processes may pass None with the number of points."""
+        if isinstance(points2D, int):
+            n, p2, p3 = points2D, None, None
+        else:
+            p2 = _capi.f64a(points2D, (-1, 2))
+            p3 = _capi.f64a(points3D, (-1, 3))
+            n = len(p2)
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_comm_scorer_create_pose(self._h, n, _capi.ptr(p2), _capi.ptr(p3), float(fx),
+                                                          float(fy), int(root), C.byref(h)))
+        cs = CommScorer(self, h)
+        self._scorers.add(cs)
+        return cs
+
+    def close(self):
+        if getattr(self, "_h", None):
+            for cs in list(self._scorers):
+                cs.close()
+            self._lib.rlb_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class CommScorer:
+    """One pose data set replicated on every GPU of a communicator (``rlb_comm_scorer``)."""
+
+    def __init__(self, comm: Comm, handle):
+        self.comm = comm
+        self._lib = comm._lib
+        self._h = handle
+        self.model_size = 12
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rlb_comm_scorer_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def hypothesize_and_score(self, samples, sq_thr: float, precision=RLB_F64, want_scores=False):
+        """One sharded round over ALL the samples (k_total x 4, the same array on every process):
+        -> dict(best_id (global), best_score, best_model[, scores, counts: this process's slices filled])."""
+        s = _capi.i32a(samples, (-1, 4))
+        k = len(s)
+        thr = np.array([sq_thr], np.float64)
+        scores = np.full(k, np.nan) if want_scores else None
+        counts = np.full(k, -1, np.int32) if want_scores else None
+        bid, bsc, bm = C.c_int64(), C.c_double(), np.zeros(12)
+        _capi.check(self._lib.rlb_comm_hypothesize_and_score(
+            self._h, precision, 0, k, _capi.ptr(s), _capi.ptr(thr), None, _capi.ptr(scores), _capi.ptr(counts),
+            C.addressof(bid), C.addressof(bsc), _capi.ptr(bm)))
+        return {"best_id": int(bid.value), "best_score": bsc.value, "best_model": bm if bid.value >= 0 else None,
+                "scores": scores, "counts": counts}
+
+    def round_dev(self, d_samples: int, k_local: int, sq_thr: float, id_offset: int, d_models: int, d_valid: int,
+                  d_scores: int, d_counts: int, d_winner: int, precision=RLB_F64):
+        """Device-pointer round of the one-process-per-GPU communicator (asynchronous)."""
+        thr = np.array([sq_thr], np.float64)
+        _capi.check(self._lib.rlb_comm_round_dev(
+            self._h, precision, 0, k_local, C.c_void_p(d_samples), _capi.ptr(thr), None, int(id_offset),
+            C.c_void_p(d_models), C.c_void_p(d_valid), C.c_void_p(d_scores or 0), C.c_void_p(d_counts or 0),
+            C.c_void_p(d_winner)))
+
+    def local_scorer_handle(self, local_index: int = 0) -> int:
+        return self._lib.rlb_comm_scorer_local(self._h, local_index)
+
+    def get_inliers(self, model, sq_thr_inl: float, sq_thr_score: float | None = None):
+        """-> (ascending inlier indices, score or None); answered by the first local GPU."""
+        model = _capi.f64a(model, (12,))
+        ti = np.array([sq_thr_inl], np.float64)
+        ts = None if sq_thr_score is None else np.array([sq_thr_score], np.float64)
+        n = int(self._lib.rlb_scorer_num_data(C.c_void_p(self.local_scorer_handle(0)), 0))
+        idx = np.empty(max(n, 1), np.int32)
+        counts = np.zeros(2, np.int32)
+        score = C.c_double()
+        _capi.check(self._lib.rlb_comm_get_inliers(self._h, _capi.ptr(model), _capi.ptr(ti), _capi.ptr(ts), None,
+                                                   _capi.ptr(idx), _capi.ptr(counts), C.addressof(score)))
+        return idx[:counts[0]].copy(), (score.value if ts is not None else None)
+
+
 def custom_compile_check(eval_source: str, dims: int, model_doubles: int) -> int:
     """Compiles a user functor the way ``Context.custom_scorer`` would (NVRTC, sm_100a) without touching a
     device; -> size of the cubin. A compile error raises RlbError carrying the compiler log."""
@@ -215,11 +361,14 @@ def custom_compile_check(eval_source: str, dims: int, model_doubles: int) -> int
 class Scorer:
     """A data set resident in HBM plus the functor that scores models on it (``rlb_scorer``)."""
 
-    def __init__(self, ctx: Context, handle):
+    def __init__(self, ctx: Context, handle, borrowed: bool = False):
         self.ctx = ctx
         self._lib = ctx._lib
-        self._h = handle
-        ctx._scorers.add(self)
+        self._h = C.c_void_p(handle) if isinstance(handle, int) else handle
+        handle = self._h
+        self._borrowed = borrowed  # owned by an rlb_comm_scorer: never destroyed here
+        if not borrowed:
+            ctx._scorers.add(self)
         self.kind = self._lib.rlb_scorer_kind(handle)
         self.num_types = self._lib.rlb_scorer_num_types(handle)
         self.num_data = [self._lib.rlb_scorer_num_data(handle, t) for t in range(self.num_types)]
@@ -227,7 +376,8 @@ class Scorer:
 
     def close(self):
         if getattr(self, "_h", None):
-            self._lib.rlb_scorer_destroy(self._h)
+            if not self._borrowed:
+                self._lib.rlb_scorer_destroy(self._h)
             self._h = None
 
     def __del__(self):

@@ -66,6 +66,7 @@ struct rlb_ctx {
   cudaStream_t stream = nullptr;
   int launches_i = 0;  // per-call counter target for the launch_* helpers
   int last_variant = -1, last_splits = 0;  // plan of the last sweep (rlb_ctx_last_sweep_plan)
+  std::map<int, int> occ_cache;            // sweep planner: resident CTAs per SM of each kernel variant on THIS device
   int64_t launches = 0;
   unsigned int epoch = 0;
   // sweep scratch
@@ -96,19 +97,34 @@ struct rlb_ctx {
   void* h_result = nullptr;
   void* d_result = nullptr;  // device alias of h_result
   size_t result_cap = 0;
-  // device-resident batched localization: per-warp-slot scratch, ticket / ready / abort words,
-  // a copy stream + pinned progress words for the pipelined host API
+  // device-resident batched localization: per-slot scratch and the ticket words of its launches
   DevBuf loc_soa, loc_lists, loc_words;
   // device-resident line LO-MSAC: per-CTA lists, {ticket, line, result} words + inlier list of the
   // single-problem entry point
   DevBuf ll_lists, ll_io;
+  // host-pointer batched localization: one copy stream, and per uploaded chunk one launch stream
+  // + "chunk uploaded" / "chunk done" events (the kernels are ordered behind their copies by
+  // events; they never wait on the host)
   cudaStream_t copy_stream = nullptr;
-  cudaEvent_t loc_ev[2] = {nullptr, nullptr};
-  unsigned int* h_ready = nullptr;  // pinned, kMaxChunks entries
+  cudaStream_t loc_streams[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t loc_ev[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   // set by rlb_sharded_round_dev for the next score_dev call
   double* pending_record = nullptr;
   long long pending_offset = 0;
 };
+
+namespace rlb {
+// for the other translation units of the library (comm.cu)
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+void* ctx_stream(const rlb_ctx* c) { return c->stream; }
+int ctx_device(const rlb_ctx* c) { return c->device; }
+}  // namespace rlb
 
 struct rlb_scorer {
   rlb_ctx* ctx = nullptr;
@@ -322,11 +338,11 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   a.variant = cands[0].variant;
   for (int ci = 0; ci < ncand; ++ci) {
     const int H = rlb::sweep_hyps_per_thread(d.kind, precision, cands[ci].variant);
-    static std::map<int, int> occ_cache;  // (kind, precision, variant) -> resident CTAs per SM
+    // (kind, precision, variant) -> resident CTAs per SM; cached per context, i.e. per device and per host thread
     const int occ_key = (d.kind * 4 + precision) * 64 + (cands[ci].variant + 1);
-    auto occ_it = occ_cache.find(occ_key);
-    if (occ_it == occ_cache.end())
-      occ_it = occ_cache.emplace(occ_key, rlb::sweep_resident_ctas(d.kind, precision, cands[ci].variant)).first;
+    auto occ_it = c->occ_cache.find(occ_key);
+    if (occ_it == c->occ_cache.end())
+      occ_it = c->occ_cache.emplace(occ_key, rlb::sweep_resident_ctas(d.kind, precision, cands[ci].variant)).first;
     const int slots = c->sms * occ_it->second;
     const int k_tiles = (k + rlb::kSweepThreads * H - 1) / (rlb::kSweepThreads * H);
     // partials are [splits][k]. 64 splits fill the device once a batch has a few hypothesis tiles; a small
@@ -588,14 +604,15 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_list) cudaFreeHost(c->h_list);
   if (c->h_result) cudaFreeHost(c->h_result);
-  if (c->h_ready) cudaFreeHost(c->h_ready);
   c->loc_soa.release();
   c->loc_lists.release();
   c->ll_lists.release();
   c->ll_io.release();
   c->loc_words.release();
-  for (int i = 0; i < 2; ++i)
+  for (int i = 0; i < 9; ++i)
     if (c->loc_ev[i]) cudaEventDestroy(c->loc_ev[i]);
+  for (int i = 0; i < 4; ++i)
+    if (c->loc_streams[i]) cudaStreamDestroy(c->loc_streams[i]);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   for (int i = 0; i < 4; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -713,6 +730,62 @@ int rlb_scorer_create_pose(rlb_ctx* c, int n, const double* p2d, const double* p
   subsampled_mean(p3d, n, 3, 3, d.centre);
   rc = upload(c, &s->raw0, p2d, static_cast<size_t>(n) * 2, c->stream);
   if (!rc) rc = upload(c, &s->raw1, p3d, static_cast<size_t>(n) * 3, c->stream);
+  if (!rc) {
+    d.raw0 = static_cast<const double*>(s->raw0);
+    d.raw1 = static_cast<const double*>(s->raw1);
+    rc = finish_scorer(s);
+  }
+  if (rc) {
+    rlb_scorer_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return RLB_OK;
+}
+
+int rlb_scorer_create_pose_dev(rlb_ctx* c, int n, const double* d_p2d, const double* d_p3d, double fx,
+                               double fy, rlb_scorer** out) {
+  if (!c || !out || n < 0 || (n > 0 && (!d_p2d || !d_p3d))) return fail(RLB_E_ARG, "bad arguments");
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  rlb_scorer* s = new (std::nothrow) rlb_scorer();
+  if (!s) return fail(RLB_E_NOMEM, "out of host memory");
+  s->ctx = c;
+  DeviceData& d = s->d;
+  memset(&d, 0, sizeof(d));
+  d.kind = RLB_KIND_POSE;
+  d.num_types = 1;
+  d.n[0] = n;
+  d.off[0] = 0;
+  d.off[1] = d.npad = std::max(pad_to(n, rlb::kSegAlign), rlb::kSegAlign);
+  d.channels = 5;
+  d.fx = fx;
+  d.fy = fy;
+  // The recentring point of the f32 copy: the same sub-sampled mean as the host-pointer constructor, taken
+  // from the rows it would read (one strided copy back), so both constructors build identical scorers.
+  {
+    const int step = std::max(1, n / 4096);
+    const int m = (n > 0) ? (n + step - 1) / step : 0;
+    std::vector<double> sub(static_cast<size_t>(std::max(m, 1)) * 3, 0.0);
+    if (m > 0) {
+      cudaError_t e = cudaMemcpy2DAsync(sub.data(), 3 * sizeof(double), d_p3d, static_cast<size_t>(step) * 3 * sizeof(double),
+                                        3 * sizeof(double), static_cast<size_t>(m), cudaMemcpyDeviceToHost, c->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+      if (e != cudaSuccess) {
+        delete s;
+        return fail(RLB_E_CUDA, "reading the sub-sample back failed: %s", cudaGetErrorString(e));
+      }
+    }
+    subsampled_mean(sub.data(), m, 3, 3, d.centre);
+  }
+  rc = pool_alloc(c, static_cast<size_t>(std::max(n, 1)) * 2 * sizeof(double), &s->raw0);
+  if (!rc) rc = pool_alloc(c, static_cast<size_t>(std::max(n, 1)) * 3 * sizeof(double), &s->raw1);
+  if (!rc && n > 0) {
+    cudaError_t e = cudaMemcpyAsync(s->raw0, d_p2d, static_cast<size_t>(n) * 2 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(s->raw1, d_p3d, static_cast<size_t>(n) * 3 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream);
+    if (e != cudaSuccess) rc = fail(RLB_E_CUDA, "device copy of the point set failed: %s", cudaGetErrorString(e));
+  }
   if (!rc) {
     d.raw0 = static_cast<const double*>(s->raw0);
     d.raw1 = static_cast<const double*>(s->raw1);
@@ -1222,7 +1295,7 @@ int rlb_hypothesize_and_score(rlb_scorer* s, int precision, int solver, int k,
 // ---- device-resident batched localization -------------------------------------------------
 namespace {
 
-constexpr int kMaxChunks = 64;
+constexpr int kMaxLocLaunches = 4;
 
 int check_localize_options(const rlb_localize_options* o) {
   if (!o) return fail(RLB_E_ARG, "null options");
@@ -1235,30 +1308,47 @@ int check_localize_options(const rlb_localize_options* o) {
   return RLB_OK;
 }
 
-// Enqueues the persistent kernel on `st`. d_ready == nullptr: everything is resident.
-int localize_enqueue(rlb_ctx* c, cudaStream_t st, int nq, int max_matches, const int64_t* d_offsets,
-                     const double* d_p2d, const double* d_p3d, const double* d_fx, const double* d_fy,
-                     const uint32_t* d_seeds, const rlb_localize_options* opt, double* d_poses,
-                     rlb_localize_result* d_results, int32_t* d_inliers, bool pipelined) {
+// 1 = one query per CTA (default), 0 = one query per warp. RLB_LOC_MODE overrides (A/B timing, tests).
+int localize_mode(int /*nq*/) {
+  if (const char* e = std::getenv("RLB_LOC_MODE")) return (e[0] == '0') ? 0 : 1;
+  return 1;
+}
+
+// Scratch geometry of one launch over `nq` queries.
+struct LocPlan {
+  int mode, ctas, nmax, npad;
+  size_t slots, soa_floats, list_ints;  // totals for this launch
+};
+
+LocPlan localize_plan(const rlb_ctx* c, int mode, int nq, int max_matches) {
+  LocPlan p;
+  p.mode = mode;
   const int wpc = rlb::localize_warps_per_cta();
-  const int nmax = std::max(max_matches, 4);
-  const int npad = pad_to(nmax, 4);
-  const size_t per_slot = static_cast<size_t>(5) * npad * sizeof(float) + static_cast<size_t>(3) * nmax * 4;
-  int ctas = std::min((nq + wpc - 1) / wpc, c->sms * rlb::localize_ctas_per_sm());
-  const size_t budget = size_t(8) << 30;  // scratch cap; fewer resident warps for huge queries
-  while (ctas > 1 && static_cast<size_t>(ctas) * wpc * per_slot > budget) ctas /= 2;
-  const size_t slots = static_cast<size_t>(ctas) * wpc;
-  RLB_CUDA(c->loc_soa.ensure(slots * 5 * npad * sizeof(float)));
-  RLB_CUDA(c->loc_lists.ensure(slots * 3 * nmax * sizeof(int32_t)));
-  RLB_CUDA(c->loc_words.ensure(64));
-  unsigned int* words = c->loc_words.as<unsigned int>();  // [0] ticket, [1] ready, [2] abort
-  if (pipelined) {
-    RLB_CUDA(cudaMemsetAsync(words, 0, 4, st));  // ready/abort were reset by the caller
-  } else {
-    RLB_CUDA(cudaMemsetAsync(words, 0, 16, st));
-  }
+  const int per_cta = (mode == 0) ? wpc : 1;
+  p.nmax = std::max(max_matches, 4);
+  p.npad = pad_to(p.nmax, 4);
+  const bool need_soa = (mode == 0) || p.nmax > rlb::localize_smem_points();
+  const size_t per_slot = (need_soa ? static_cast<size_t>(5) * p.npad * sizeof(float) : 0) +
+                          static_cast<size_t>(3) * p.nmax * 4;
+  p.ctas = std::max(1, std::min((nq + per_cta - 1) / per_cta, c->sms * rlb::localize_ctas_per_sm(mode)));
+  const size_t budget = size_t(8) << 30;  // scratch cap; fewer resident queries for huge ones
+  while (p.ctas > 1 && static_cast<size_t>(p.ctas) * per_cta * per_slot > budget) p.ctas /= 2;
+  p.slots = static_cast<size_t>(p.ctas) * per_cta;
+  p.soa_floats = need_soa ? p.slots * 5 * p.npad : 0;
+  p.list_ints = p.slots * 3 * p.nmax;
+  return p;
+}
+
+// Enqueues one grid over the queries [q_first, q_end) on `st`; everything it reads must be ordered before
+// it on `st`. soa / lists / ticket: this launch's own scratch (ticket zeroed by the caller).
+int localize_enqueue(rlb_ctx* c, cudaStream_t st, const LocPlan& p, int q_first, int q_end,
+                     const int64_t* d_offsets, const double* d_p2d, const double* d_p3d, const double* d_fx,
+                     const double* d_fy, const uint32_t* d_seeds, const rlb_localize_options* opt,
+                     double* d_poses, rlb_localize_result* d_results, int32_t* d_inliers, float* soa,
+                     int32_t* lists, unsigned int* ticket) {
   rlb::LocalizeArgs a;
-  a.num_queries = nq;
+  a.q_first = q_first;
+  a.q_end = q_end;
   a.offsets = reinterpret_cast<const long long*>(d_offsets);
   a.p2d = d_p2d;
   a.p3d = d_p3d;
@@ -1269,14 +1359,14 @@ int localize_enqueue(rlb_ctx* c, cudaStream_t st, int nq, int max_matches, const
   a.poses = d_poses;
   a.results = d_results;
   a.inliers = d_inliers;
-  a.soa32 = c->loc_soa.as<float>();
-  a.lists = c->loc_lists.as<int32_t>();
-  a.npad_max = npad;
-  a.nmax = nmax;
-  a.ticket = words;
-  a.ready = pipelined ? words + 1 : nullptr;
-  a.abort_flag = words + 2;
-  RLB_CUDA(rlb::launch_localize(a, ctas, st, &c->launches_i));
+  a.soa32 = soa;
+  a.lists = lists;
+  a.npad_max = p.npad;
+  a.nmax = p.nmax;
+  a.ticket = ticket;
+  a.smem_points = rlb::localize_smem_points();
+  a.wave = std::max(c->sms, 1);
+  RLB_CUDA(rlb::launch_localize(a, p.mode, p.ctas, st, &c->launches_i));
   account(c);
   return RLB_OK;
 }
@@ -1313,8 +1403,15 @@ int rlb_localize_batch_dev(rlb_ctx* c, int nq, int max_matches, const int64_t* d
   if (rc) return rc;
   rc = ctx_use(c);
   if (rc) return rc;
-  return localize_enqueue(c, c->stream, nq, max_matches, d_offsets, d_p2d, d_p3d, d_fx, d_fy, d_seeds,
-                          opt, d_poses, d_results, d_inliers, false);
+  const LocPlan p = localize_plan(c, localize_mode(nq), nq, max_matches);
+  RLB_CUDA(c->loc_soa.ensure(std::max<size_t>(p.soa_floats, 1) * sizeof(float)));
+  RLB_CUDA(c->loc_lists.ensure(p.list_ints * sizeof(int32_t)));
+  RLB_CUDA(c->loc_words.ensure(64));
+  unsigned int* words = c->loc_words.as<unsigned int>();
+  RLB_CUDA(cudaMemsetAsync(words, 0, 64, c->stream));
+  return localize_enqueue(c, c->stream, p, 0, nq, d_offsets, d_p2d, d_p3d, d_fx, d_fy, d_seeds, opt, d_poses,
+                          d_results, d_inliers, p.soa_floats ? c->loc_soa.as<float>() : nullptr,
+                          c->loc_lists.as<int32_t>(), words);
 }
 
 int rlb_localize_batch(rlb_ctx* c, int nq, const int64_t* offsets, const double* p2d, const double* p3d,
@@ -1339,9 +1436,39 @@ int rlb_localize_batch(rlb_ctx* c, int nq, const int64_t* offsets, const double*
   const int64_t total = offsets[nq];
   if (!c->copy_stream) {
     RLB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-    RLB_CUDA(cudaEventCreateWithFlags(&c->loc_ev[0], cudaEventDisableTiming));
-    RLB_CUDA(cudaEventCreateWithFlags(&c->loc_ev[1], cudaEventDisableTiming));
-    RLB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_ready), kMaxChunks * sizeof(unsigned int)));
+    for (int i = 0; i < kMaxLocLaunches; ++i)
+      RLB_CUDA(cudaStreamCreateWithFlags(&c->loc_streams[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 1 + 2 * kMaxLocLaunches; ++i)
+      RLB_CUDA(cudaEventCreateWithFlags(&c->loc_ev[i], cudaEventDisableTiming));
+  }
+  // Chunks of queries: the first one small so that the first grid starts early, few of them so that
+  // the grids' tails stay few; a chunk is at least ~8 MB of matches. Chunk k is uploaded on the copy
+  // stream, its grid runs on its own launch stream behind the "uploaded" event, and the grids of
+  // different chunks overlap (a later grid's CTAs fill the SMs as an earlier grid's CTAs retire).
+  int bounds[kMaxLocLaunches + 1];
+  int nl = 0;
+  bounds[0] = 0;
+  {
+    const double cuts[kMaxLocLaunches] = {0.125, 0.5, 1.0, 1.0};
+    const int64_t min_rows = 200000;
+    int q = 0;
+    for (int k = 0; k < kMaxLocLaunches && q < nq; ++k) {
+      const int64_t want = std::max<int64_t>(static_cast<int64_t>(cuts[k] * static_cast<double>(total)),
+                                             offsets[q] + min_rows);
+      int q1 = q + 1;
+      while (q1 < nq && offsets[q1 + 1] <= want) ++q1;
+      if (k == kMaxLocLaunches - 1 || total - offsets[q1] < min_rows) q1 = nq;
+      bounds[++nl] = q1;
+      q = q1;
+    }
+  }
+  const int mode = localize_mode(nq);
+  LocPlan plans[kMaxLocLaunches];
+  size_t soa_total = 0, list_total = 0;
+  for (int k = 0; k < nl; ++k) {
+    plans[k] = localize_plan(c, mode, bounds[k + 1] - bounds[k], static_cast<int>(max_matches));
+    soa_total += plans[k].soa_floats;
+    list_total += plans[k].list_ints;
   }
   void *d_off = nullptr, *d_p2 = nullptr, *d_p3 = nullptr, *d_f = nullptr, *d_seed = nullptr,
        *d_pose = nullptr, *d_res = nullptr, *d_inl = nullptr;
@@ -1364,61 +1491,67 @@ int rlb_localize_batch(rlb_ctx* c, int nq, const int64_t* offsets, const double*
   cudaStream_t cs = c->copy_stream;
   double* d_fx = static_cast<double*>(d_f);
   double* d_fy = d_fx + nq;
-  RLB_CUDA(c->loc_words.ensure(64));
-  unsigned int* words = c->loc_words.as<unsigned int>();
-  // Order: whatever ran before on the compute stream -> reset of the progress words -> copies.
-  RLB_CUDA(cudaMemsetAsync(words, 0, 16, c->stream));
-  RLB_CUDA(cudaEventRecord(c->loc_ev[0], c->stream));
-  RLB_CUDA(cudaStreamWaitEvent(cs, c->loc_ev[0], 0));
-  RLB_CUDA(cudaMemcpyAsync(d_off, offsets, (nq + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, cs));
-  RLB_CUDA(cudaMemcpyAsync(d_fx, fx, nq * sizeof(double), cudaMemcpyHostToDevice, cs));
-  RLB_CUDA(cudaMemcpyAsync(d_fy, fy, nq * sizeof(double), cudaMemcpyHostToDevice, cs));
-  RLB_CUDA(cudaMemcpyAsync(d_seed, seeds, nq * sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
-  RLB_CUDA(cudaEventRecord(c->loc_ev[1], cs));
-  RLB_CUDA(cudaStreamWaitEvent(c->stream, c->loc_ev[1], 0));
-  // The kernel starts as soon as the small arrays are there; it waits per query on words[1].
-  rc = localize_enqueue(c, c->stream, nq, static_cast<int>(max_matches), static_cast<int64_t*>(d_off),
-                        static_cast<double*>(d_p2), static_cast<double*>(d_p3), d_fx, d_fy,
-                        static_cast<uint32_t*>(d_seed), opt, static_cast<double*>(d_pose),
-                        static_cast<rlb_localize_result*>(d_res), static_cast<int32_t*>(d_inl), true);
-  if (rc) {
+  // From here on every exit goes through `finish`: all streams drained before the blocks go back to the pool.
+  auto finish = [&](int code) {
     cudaStreamSynchronize(cs);
+    for (int k = 0; k < kMaxLocLaunches; ++k) cudaStreamSynchronize(c->loc_streams[k]);
+    cudaStreamSynchronize(c->stream);
     release();
-    return rc;
-  }
-  // Upload the matches in chunks of queries (~8 MB each), publishing progress behind each chunk.
-  const int64_t chunk_rows = std::max<int64_t>((total + kMaxChunks - 1) / kMaxChunks, 200000);
-  int q0 = 0, nchunks = 0;
-  while (q0 < nq) {
-    int q1 = q0 + 1;
-    while (q1 < nq && offsets[q1 + 1] - offsets[q0] <= chunk_rows) ++q1;
-    if (nchunks == kMaxChunks - 1) q1 = nq;
+    return code;
+  };
+#define RLB_LOC_TRY(expr)                                                                       \
+  do {                                                                                          \
+    cudaError_t e__ = (expr);                                                                   \
+    if (e__ != cudaSuccess) return finish(fail(RLB_E_CUDA, "%s: %s", #expr, cudaGetErrorString(e__))); \
+  } while (0)
+  RLB_LOC_TRY(c->loc_soa.ensure(std::max<size_t>(soa_total, 1) * sizeof(float)));
+  RLB_LOC_TRY(c->loc_lists.ensure(list_total * sizeof(int32_t)));
+  RLB_LOC_TRY(c->loc_words.ensure(64));
+  unsigned int* words = c->loc_words.as<unsigned int>();
+  // Order: whatever ran before on the context stream -> reset of the ticket words -> copies and grids.
+  RLB_LOC_TRY(cudaMemsetAsync(words, 0, 64, c->stream));
+  RLB_LOC_TRY(cudaEventRecord(c->loc_ev[0], c->stream));
+  RLB_LOC_TRY(cudaStreamWaitEvent(cs, c->loc_ev[0], 0));
+  RLB_LOC_TRY(cudaMemcpyAsync(d_off, offsets, (nq + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, cs));
+  RLB_LOC_TRY(cudaMemcpyAsync(d_fx, fx, nq * sizeof(double), cudaMemcpyHostToDevice, cs));
+  RLB_LOC_TRY(cudaMemcpyAsync(d_fy, fy, nq * sizeof(double), cudaMemcpyHostToDevice, cs));
+  RLB_LOC_TRY(cudaMemcpyAsync(d_seed, seeds, nq * sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
+  size_t soa_at = 0, list_at = 0;
+  for (int k = 0; k < nl; ++k) {
+    const int q0 = bounds[k], q1 = bounds[k + 1];
     const int64_t r0 = offsets[q0], r1 = offsets[q1];
     if (r1 > r0) {
-      RLB_CUDA(cudaMemcpyAsync(static_cast<double*>(d_p2) + 2 * r0, p2d + 2 * r0, (r1 - r0) * 2 * sizeof(double),
-                               cudaMemcpyHostToDevice, cs));
-      RLB_CUDA(cudaMemcpyAsync(static_cast<double*>(d_p3) + 3 * r0, p3d + 3 * r0, (r1 - r0) * 3 * sizeof(double),
-                               cudaMemcpyHostToDevice, cs));
+      RLB_LOC_TRY(cudaMemcpyAsync(static_cast<double*>(d_p2) + 2 * r0, p2d + 2 * r0, (r1 - r0) * 2 * sizeof(double),
+                                  cudaMemcpyHostToDevice, cs));
+      RLB_LOC_TRY(cudaMemcpyAsync(static_cast<double*>(d_p3) + 3 * r0, p3d + 3 * r0, (r1 - r0) * 3 * sizeof(double),
+                                  cudaMemcpyHostToDevice, cs));
     }
-    c->h_ready[nchunks] = static_cast<unsigned int>(q1);
-    RLB_CUDA(cudaMemcpyAsync(words + 1, &c->h_ready[nchunks], sizeof(unsigned int), cudaMemcpyHostToDevice, cs));
-    ++nchunks;
-    q0 = q1;
+    cudaEvent_t uploaded = c->loc_ev[1 + 2 * k], done = c->loc_ev[2 + 2 * k];
+    cudaStream_t ls = c->loc_streams[k];
+    RLB_LOC_TRY(cudaEventRecord(uploaded, cs));
+    RLB_LOC_TRY(cudaStreamWaitEvent(ls, uploaded, 0));
+    rc = localize_enqueue(c, ls, plans[k], q0, q1, static_cast<int64_t*>(d_off), static_cast<double*>(d_p2),
+                          static_cast<double*>(d_p3), d_fx, d_fy, static_cast<uint32_t*>(d_seed), opt,
+                          static_cast<double*>(d_pose), static_cast<rlb_localize_result*>(d_res),
+                          static_cast<int32_t*>(d_inl),
+                          plans[k].soa_floats ? c->loc_soa.as<float>() + soa_at : nullptr,
+                          c->loc_lists.as<int32_t>() + list_at, words + k);
+    if (rc) return finish(rc);
+    soa_at += plans[k].soa_floats;
+    list_at += plans[k].list_ints;
+    RLB_LOC_TRY(cudaEventRecord(done, ls));
+    RLB_LOC_TRY(cudaStreamWaitEvent(c->stream, done, 0));
   }
-  RLB_CUDA(cudaStreamSynchronize(cs));
-  RLB_CUDA(cudaMemcpyAsync(poses, d_pose, static_cast<size_t>(nq) * 12 * sizeof(double), cudaMemcpyDeviceToHost,
-                           c->stream));
-  RLB_CUDA(cudaMemcpyAsync(results, d_res, static_cast<size_t>(nq) * sizeof(rlb_localize_result),
-                           cudaMemcpyDeviceToHost, c->stream));
+  RLB_LOC_TRY(cudaMemcpyAsync(poses, d_pose, static_cast<size_t>(nq) * 12 * sizeof(double), cudaMemcpyDeviceToHost,
+                              c->stream));
+  RLB_LOC_TRY(cudaMemcpyAsync(results, d_res, static_cast<size_t>(nq) * sizeof(rlb_localize_result),
+                              cudaMemcpyDeviceToHost, c->stream));
   if (inliers && total > 0)
-    RLB_CUDA(cudaMemcpyAsync(inliers, d_inl, static_cast<size_t>(total) * sizeof(int32_t), cudaMemcpyDeviceToHost,
-                             c->stream));
-  unsigned int aborted = 0;
-  RLB_CUDA(cudaMemcpyAsync(c->h_small, words + 2, 4, cudaMemcpyDeviceToHost, c->stream));
-  RLB_CUDA(cudaStreamSynchronize(c->stream));
-  aborted = *static_cast<unsigned int*>(c->h_small);
+    RLB_LOC_TRY(cudaMemcpyAsync(inliers, d_inl, static_cast<size_t>(total) * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                c->stream));
+  RLB_LOC_TRY(cudaStreamSynchronize(c->stream));
+#undef RLB_LOC_TRY
   release();
-  if (aborted) return fail(RLB_E_CUDA, "localization kernel gave up waiting for the upload");
   return RLB_OK;
 }
 

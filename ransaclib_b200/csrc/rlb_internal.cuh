@@ -5,11 +5,32 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <string>
 
 #include "../../include/ransaclib_b200.h"
 
 namespace rlb {
+
+// cudaFuncSetAttribute and occupancy queries are per DEVICE, and contexts of several devices (and
+// several host threads) share this library: "already configured" is remembered per device in an
+// atomic bit mask. The guarded calls are idempotent, so two threads racing only repeat them.
+struct PerDeviceOnce {
+  std::atomic<unsigned long long> mask{0ull};
+  static int device() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return d & 63;
+  }
+  bool done(int dev) const { return (mask.load(std::memory_order_acquire) >> dev) & 1ull; }
+  void set(int dev) { mask.fetch_or(1ull << dev, std::memory_order_release); }
+};
+
+// capi.cu: the thread-local error message of rlb_last_error() and two context accessors for the
+// other translation units (returns `code`).
+int set_error(int code, const char* fmt, ...);
+void* ctx_stream(const rlb_ctx* c);  // cudaStream_t
+int ctx_device(const rlb_ctx* c);
 
 // Points of every data type are stored channel-major (SoA) and zero-padded so that
 // each type segment starts at a multiple of kSegAlign points. Stages of the K x N
@@ -121,8 +142,11 @@ cudaError_t launch_solve_p3p(const DeviceData& d, int k, const int32_t* samples,
                              double* models, uint8_t* valid, cudaStream_t st, int* launches);
 
 // Device-resident batched localization (localize_kernels.cu, -fmad=false).
+// One launch covers the queries [q_first, q_end) of a batch; everything it reads is resident
+// before it starts (the host API launches one grid per uploaded chunk, ordered behind that chunk's
+// copies by an event: no kernel ever waits on the host).
 struct LocalizeArgs {
-  int num_queries;
+  int q_first, q_end;
   const long long* offsets;  // [Q + 1]
   const double* p2d;         // [total][2]
   const double* p3d;         // [total][3]
@@ -133,19 +157,20 @@ struct LocalizeArgs {
   double* poses;                 // [Q][12]
   rlb_localize_result* results;  // [Q]
   int32_t* inliers;              // [total] or nullptr
-  // scratch, one slot per resident warp
-  float* soa32;    // [slots][5][npad_max]
+  // scratch of THIS launch, one slot per resident query (mode 0: per warp, mode 1: per CTA)
+  float* soa32;    // [slots][5][npad_max]; mode 1 uses it only for queries beyond smem_points
   int32_t* lists;  // [slots][3][nmax]
   int npad_max, nmax;
-  unsigned int* ticket;  // query counter, zero before the launch
-  // Host-pointer API: number of queries whose matches have landed in HBM so far (written by
-  // stream-ordered 4-byte copies behind each chunk of the upload); nullptr = all resident.
-  const volatile unsigned int* ready;
-  unsigned int* abort_flag;  // set when a warp gave up waiting for `ready`
+  unsigned int* ticket;  // query counter of this launch, zero before the launch
+  int smem_points;       // mode 1: capacity of the CTA's shared-memory copy of the f32 matches
+  int wave;              // mode 1: CTAs per wave (= SM count), rotates the master warp over the schedulers
 };
-cudaError_t launch_localize(const LocalizeArgs& a, int ctas, cudaStream_t st, int* launches);
+// mode 0: one query per warp (throughput form for very large batches);
+// mode 1: one query per CTA, the passes over the matches shared by its four warps.
+cudaError_t launch_localize(const LocalizeArgs& a, int mode, int ctas, cudaStream_t st, int* launches);
 int localize_warps_per_cta();
-int localize_ctas_per_sm();
+int localize_ctas_per_sm(int mode);
+int localize_smem_points();  // mode 1: largest query whose f32 copy is staged in shared memory
 
 // Device-resident line LO-MSAC (line_lomsac_kernel.cu, -fmad=false): one problem per CTA.
 struct LineLomsacArgs {

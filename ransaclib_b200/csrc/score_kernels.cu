@@ -374,12 +374,13 @@ template <template <typename> class FT, typename T, int H>
 static cudaError_t launch_sweep_t(const DeviceData& d, const SweepArgs& a, cudaStream_t st) {
   const size_t smem = static_cast<size_t>(kNumStages) * FT<T>::C * kStage * sizeof(T);
   auto kern = sweep_kernel<FT, T, H>;
-  static bool configured = false;  // per template instantiation
-  if (!configured) {
+  static PerDeviceOnce configured;  // per template instantiation
+  const int dev = PerDeviceOnce::device();
+  if (!configured.done(dev)) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    configured = true;
+    configured.set(dev);
   }
   dim3 grid((a.k + kSweepThreads * H - 1) / (kSweepThreads * H), a.n_splits);
   kern<<<grid, kSweepThreads, smem, st>>>(d, a);
@@ -560,12 +561,13 @@ template <int H>
 static cudaError_t launch_sweep_pose_x2(const DeviceData& d, const SweepArgs& a, cudaStream_t st) {
   const size_t smem = static_cast<size_t>(kNumStages) * 5 * kStage * sizeof(float);
   auto kern = sweep_pose_f32x2_kernel<H>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  const int dev = PerDeviceOnce::device();
+  if (!configured.done(dev)) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    configured = true;
+    configured.set(dev);
   }
   dim3 grid((a.k + kSweepThreads * H - 1) / (kSweepThreads * H), a.n_splits);
   kern<<<grid, kSweepThreads, smem, st>>>(d, a);

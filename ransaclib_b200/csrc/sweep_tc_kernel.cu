@@ -419,30 +419,33 @@ size_t tc_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * k
 int tc_hyps_per_cta() { return kTcThreads; }
 
 int tc_resident_ctas() {
-  static int cached = 0;
-  if (cached) return cached;
+  static std::atomic<int> cache[64];  // per device; 0 = not asked yet
+  std::atomic<int>& cached = cache[PerDeviceOnce::device()];
+  if (const int v = cached.load(std::memory_order_relaxed)) return v;
   cudaFuncSetAttribute(sweep_pose_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(TcSmem)));
   int n = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel<true>, kTcThreads, sizeof(TcSmem)) !=
       cudaSuccess)
     n = 1;
-  cached = max(1, min(n, 512 / kTcCols));  // TMEM: 512 columns per SM
-  return cached;
+  const int v = max(1, min(n, 512 / kTcCols));  // TMEM: 512 columns per SM
+  cached.store(v, std::memory_order_relaxed);
+  return v;
 }
 
 cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
                             int* launches) {
   ++*launches;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  const int dev = PerDeviceOnce::device();
+  if (!configured.done(dev)) {
     cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(sizeof(TcSmem)));
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(sweep_pose_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(sizeof(TcSmem)));
     if (e != cudaSuccess) return e;
-    configured = true;
+    configured.set(dev);
   }
   dim3 grid((a.k + kTcThreads - 1) / kTcThreads, a.n_splits);
   if (a.want_counts)

@@ -24,7 +24,7 @@ names = ["batches(sample+p3p+sweep)", "sweep32", "fused_pass", "shuffle", "Full"
          "LO minimal", "setup", "#Full", "#Cost"]
 tot = np.zeros(12)
 for q in range(Q):
-    a = (int(off[q]) + 2000 - 24) & ~1
+    a = (int(off[q]) + 2000 - 32) & ~1
     tot += inl[a:a + 24].view(np.int64)
 tot /= Q
 print(f"Q={Q}: mean per query: lsq {res['lsq_calls'].mean():.1f} passes {res['passes'].mean():.1f} lo {res['num_lo'].mean():.2f}")
