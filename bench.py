@@ -291,12 +291,10 @@ def run_ours(args):
     # ---- second half of BASELINE.json's metric: batched localization (configs[3]) on the same GPUs ----
     loc = None
     if args.workload == "c5" and not args.no_localization:
-        scorer.close()
-        del flush
-        torch.cuda.empty_cache()
         loc = measure_c4(args, rank, world, local, dist, steps=max(1, min(args.steps, 5)),
                          warmup=max(1, min(args.warmup, 3)))
         torch.cuda.set_stream(stream)
+        ctx.set_stream(stream.cuda_stream)
 
     if rank != 0:
         if world > 1:
@@ -358,6 +356,13 @@ def run_ours(args):
                         "unit": "GB/s", "frac": inl_bytes / (inl_avg_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0)},
     }
 
+    # ---- the reference-exact f64 sweep of the same workload (own leg, same run) ------
+    f64_leg = None
+    if prec == rlb.RLB_F32 and args.workload == "c5" and world == 1 and not args.no_extra:
+        f64_leg = measure_f64_leg(args, ctx, step, stream, flush, k, n, peaks)
+    other_sweeps = measure_line_sweeps(ctx, peaks) if (world == 1 and not args.no_extra) else None
+    configs_table = run_configs_table() if (world == 1 and not args.no_extra) else None
+
     # ---- cpu baseline: the reference's loops on ONE host core, bounded sample -------
     cpu = cpu_baseline(p2, p3, f, d_models[:64].cpu().numpy(), d_valid[:64].cpu().numpy(), threads=1,
                        budget_s=12.0) if world == 1 else None
@@ -367,6 +372,10 @@ def run_ours(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32" if prec == rlb.RLB_F32 else "f64", "data": "synthetic",
+        # the second half of BASELINE.json's metric up front (details under "localization")
+        "localizations_per_s": loc["value"] if loc else None,
+        "localizations_per_s_e2e": loc["e2e"]["value"] if loc else None,
+        "e2e_evals_per_s": e2e_value,
         "config": {"workload": wl["name"], "n_points": n, "k_hypotheses": k_total, "k_per_gpu": k,
                    "per_hypothesis_counts": bool(args.counts),
                    "sq_thr": THR, "partitioning": "hypothesis-sharded, points replicated, 1 all_gather/step"
@@ -379,6 +388,7 @@ def run_ours(args):
                         "back) + rlb_comm_get_inliers, pinned host buffers; bytes are rank 0's"},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
         "result": {"num_inliers": n_inl, "best_score": best_score}, "parity": parity,
+        "f64": f64_leg, "other_sweeps": other_sweeps, "configs_table": configs_table,
         "comm": {"nranks": comm.nranks, "collectives_issued": comm.collective_count,
                  "note": "rlb_comm_*: NCCL inside the library (ncclBroadcast of the points, one ncclAllGather per "
                          "round); torch.distributed carries only the unique id, barriers and the timing max"},
@@ -390,6 +400,106 @@ def run_ours(args):
     emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_f64_leg(args, ctx, step, stream, flush, k, n, peaks):
+    """The same step with the f64 (reference-exact) sweep: CUDA events, L2 flushed, 3 timed steps."""
+    import torch
+
+    import ransaclib_b200 as rlb
+
+    step(rlb.RLB_F64)
+    torch.cuda.synchronize()
+    steps = 3
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    sweep_ms = []
+    for s0, s1 in evs:
+        flush.zero_()
+        s0.record(stream)
+        step(rlb.RLB_F64)
+        s1.record(stream)
+        s1.synchronize()
+        sweep_ms.append(ctx.kernel_time_ms(0))
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    variant, splits = ctx.last_sweep_plan()
+    dfma = ctx.measure_fma_peak(0)
+    sw = float(np.mean(sweep_ms))
+    ach = k * n * FLOP_PER_EVAL / (sw * 1e-3) / 1e12
+    return {"metric": "MSAC hypothesis x point evals/sec", "dtype": "f64", "value": k * n * steps / (total_ms * 1e-3),
+            "unit": "evals/s", "steps": steps, "ms_per_step": total_ms / steps,
+            "roofline": {"bound": "fma", "kernel": "sweep_kernel<PoseF,double,%d>" % (4 if variant == 7 else 2),
+                         "sweep_variant": variant, "splits": splits, "achieved": ach, "peak": dfma,
+                         "unit": "TFLOP/s", "frac": ach / dfma, "launch_ms": sw,
+                         "peak_source": "rlb_measure_fma_peak: register-resident DFMA microbenchmark, same run",
+                         "fp64_pipe_instructions_per_eval": 20,
+                         "note": "29 algorithmic flop per evaluation = 14.5 FMA slots; the kernel issues 20 FP64-pipe "
+                                 "instructions per evaluation (9 projection FMAs, 3 for the reciprocal, 4 residual, the "
+                                 "behind-camera test, std::min, the add, the inlier test), so the pipe itself bounds it at "
+                                 "14.5 / 20 = 0.725 of the DFMA peak in these units; ncu: FP64 pipe 72 % active, top stall "
+                                 "math-pipe throttle (profiles/r02_f64_sweep_ab.txt, r02_ncu_f64_sweep_*.csv)",
+                         "hbm": {"algorithmic_bytes": n * 40 + k * 108,
+                                 "achieved_gbs": (n * 40 + k * 108) / (sw * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs")}}}
+
+
+def measure_line_sweeps(ctx, peaks):
+    """K x N sweeps of the line (8 flop / evaluation) and hybrid-line (9) functors, SURVEY 8(d): N = 1M points
+    (hybrid: 2 x 512k), K = 16,384 two-point hypotheses, f32 and f64, kernel time by CUDA events."""
+    import ransaclib_b200 as rlb
+    from ransaclib_b200 import synth
+    from ransaclib_b200.sampling import UniformSampling
+
+    out = {}
+    n, k = 1_000_000, 16_384
+    xy = synth.line_instance(77, n // 2, n - n // 2)
+    samples = UniformSampling(5, n, 2).sample_fast(k)
+    sc = ctx.line_scorer(xy)
+    ffma, dfma = ctx.measure_fma_peak(1), ctx.measure_fma_peak(0)
+    for name, prec, flop, peak in (("line_f32", rlb.RLB_F32, 8.0, ffma), ("line_f64", rlb.RLB_F64, 8.0, dfma)):
+        for _ in range(3):
+            sc.hypothesize_and_score(samples, 1e-4, precision=prec, want_models=False, want_scores=False)
+        ms = ctx.kernel_time_ms(0)
+        out[name] = {"evals_per_s": k * n / (ms * 1e-3), "launch_ms": ms, "flop_per_eval": flop,
+                     "achieved_tflops": k * n * flop / (ms * 1e-3) / 1e12, "peak_tflops": peak,
+                     "frac": k * n * flop / (ms * 1e-3) / 1e12 / peak, "sweep_plan": list(ctx.last_sweep_plan()),
+                     "hbm_gbs": (n * (8 if prec == rlb.RLB_F32 else 16) + k * 36) / (ms * 1e-3) / 1e9}
+    sc.close()
+    h = n // 2
+    xy0, p1 = synth.hybrid_line_instance(78, h // 2, h - h // 2, h // 2, h - h // 2)
+    sc = ctx.hybrid_line_scorer(xy0, p1)
+    s2 = UniformSampling(6, h, 2).sample_fast(k)
+    for name, prec, peak in (("hybrid_line_f32", rlb.RLB_F32, ffma), ("hybrid_line_f64", rlb.RLB_F64, dfma)):
+        for _ in range(3):
+            sc.hypothesize_and_score(s2, [1e-4, 1e-4], weights=[2.0, 0.5], precision=prec, want_models=False,
+                                     want_scores=False)
+        ms = ctx.kernel_time_ms(0)
+        out[name] = {"evals_per_s": k * n / (ms * 1e-3), "launch_ms": ms, "flop_per_eval": 9.0,
+                     "achieved_tflops": k * n * 9.0 / (ms * 1e-3) / 1e12, "peak_tflops": peak,
+                     "frac": k * n * 9.0 / (ms * 1e-3) / 1e12 / peak, "sweep_plan": list(ctx.last_sweep_plan())}
+    sc.close()
+    out["note"] = ("line: sweep_kernel<LineF,T,4>, 8 flop / evaluation of which 2 are multiply-adds of the residual: the "
+                   "kernel is bound by issue slots (predicated add + count per evaluation), not by the FMA pipe")
+    return out
+
+
+def run_configs_table():
+    """End-to-end EstimateModel wall time of BASELINE configs[0..2] through the drop-in layer next to the
+    reference's EstimateModel on one host core (tests/e2e_configs.py in a subprocess, bounded)."""
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "e2e_configs.py")], capture_output=True,
+                           text=True, timeout=240, cwd=ROOT)
+        if r.returncode != 0:
+            return {"error": r.stderr[-400:]}
+        tab = json.loads(r.stdout)
+        rows = []
+        for row in tab["rows"]:
+            gpu = row.get("gpu_device_resident_s", min(row["gpu_f64_s"], row["gpu_f32_s"]))
+            rows.append({"config": row["config"], "iterations": row["iterations"], "inliers": row["inliers"],
+                         "reference_1core_ms": row["cpu_s"] * 1e3, "gpu_ms": gpu * 1e3,
+                         "gpu_f64_ms": row["gpu_f64_s"] * 1e3, "gpu_f32_ms": row["gpu_f32_s"] * 1e3,
+                         "speedup": row["cpu_s"] / gpu})
+        return {"what": tab["what"], "cpu_kind": tab["cpu_kind"], "rows": rows}
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)[:400]}
 
 
 def measure_parity(args, rank, world, dev, ctx, scorer, step, d_samples, d_models, d_valid, d_scores, d_counts,
@@ -519,7 +629,8 @@ def cpu_baseline(p2, p3, f, models, valid, threads, budget_s):
     return {"value": threads * k_each * n / dt, "unit": "evals/s", "cores": threads, "kind": kind,
             "sample": f"ScoreModel over all {n} points x {k_each} hypotheses per thread, "
                       f"{threads} thread(s), {dt:.1f} s; reference ransac.h loops + Eigen-free solver "
-                      f"restatement (Eigen/PoseLib/Ceres absent), -O3 -march=x86-64-v3, "
+                      f"restatement (Eigen/PoseLib/Ceres absent), -O3 -march={ol.reference_fast_flags()} (the widest "
+                      f"this host supports, i.e. what the reference's -march=native selects here), "
                       f"EvaluateModelOnPoint out-of-line as in the reference", "seconds": dt}
 
 
@@ -812,6 +923,8 @@ def main():
                          "computes (the winner's inliers come from the GetInliers pass either way). Default: "
                          "score AND inlier count per hypothesis, as BASELINE.json's north_star describes")
     ap.add_argument("--k-override", type=int, default=0, help="tuning only: total number of hypotheses")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="skip the f64 leg, the line / hybrid sweep rooflines and the configs[0..2] table")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: skips the e2e leg, the CPU baseline and the peak microbenchmarks")
     args = ap.parse_args()

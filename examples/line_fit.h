@@ -18,6 +18,18 @@
 #define RLB_LF_UNROLL
 #endif
 
+// This file's functions must round like a strict-IEEE evaluation: no fused multiply-add contraction.
+// nvcc device code gets that from -fmad=false on the command line (csrc/Makefile); for host compilers the
+// setting is pinned HERE, so that a user who includes the drop-in headers with the reference's own flags
+// (-O3 -march=native: GCC contracts by default) still gets the trajectories of the device-resident drivers.
+#if defined(__clang__)
+#pragma STDC FP_CONTRACT OFF
+#elif defined(__GNUC__) && !defined(__CUDA_ARCH__)
+#pragma GCC push_options
+#pragma GCC optimize("fp-contract=off")
+#define RLB_FP_CONTRACT_PUSHED_LINE_FIT 1
+#endif
+
 namespace ransac_lib {
 
 namespace line_fit {
@@ -101,5 +113,10 @@ RLB_LF_HD inline bool ThroughTwoPoints(double x1, double y1, double x2, double y
 }  // namespace line_fit
 
 }  // namespace ransac_lib
+
+#if defined(RLB_FP_CONTRACT_PUSHED_LINE_FIT)
+#pragma GCC pop_options
+#undef RLB_FP_CONTRACT_PUSHED_LINE_FIT
+#endif
 
 #endif  // RANSACLIB_B200_EXAMPLES_LINE_FIT_H_

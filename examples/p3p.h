@@ -21,6 +21,18 @@
 #define RLB_P3P_HD_INLINE inline
 #endif
 
+// This file's functions must round like a strict-IEEE evaluation: no fused multiply-add contraction.
+// nvcc device code gets that from -fmad=false on the command line (csrc/Makefile); for host compilers the
+// setting is pinned HERE, so that a user who includes the drop-in headers with the reference's own flags
+// (-O3 -march=native: GCC contracts by default) still gets the trajectories of the device-resident drivers.
+#if defined(__clang__)
+#pragma STDC FP_CONTRACT OFF
+#elif defined(__GNUC__) && !defined(__CUDA_ARCH__)
+#pragma GCC push_options
+#pragma GCC optimize("fp-contract=off")
+#define RLB_FP_CONTRACT_PUSHED_P3P 1
+#endif
+
 namespace rlb {
 namespace p3pdev {
 
@@ -308,5 +320,10 @@ static RLB_P3P_HD bool p3p_pick(const double* y, const double* x, const double* 
 
 }  // namespace p3pdev
 }  // namespace rlb
+
+#if defined(RLB_FP_CONTRACT_PUSHED_P3P)
+#pragma GCC pop_options
+#undef RLB_FP_CONTRACT_PUSHED_P3P
+#endif
 
 #endif  // RLB_EXAMPLES_P3P_H_

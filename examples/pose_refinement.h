@@ -37,6 +37,18 @@
 #define RLB_ROLLED
 #endif
 
+// This file's functions must round like a strict-IEEE evaluation: no fused multiply-add contraction.
+// nvcc device code gets that from -fmad=false on the command line (csrc/Makefile); for host compilers the
+// setting is pinned HERE, so that a user who includes the drop-in headers with the reference's own flags
+// (-O3 -march=native: GCC contracts by default) still gets the trajectories of the device-resident drivers.
+#if defined(__clang__)
+#pragma STDC FP_CONTRACT OFF
+#elif defined(__GNUC__) && !defined(__CUDA_ARCH__)
+#pragma GCC push_options
+#pragma GCC optimize("fp-contract=off")
+#define RLB_FP_CONTRACT_PUSHED_POSE_REF 1
+#endif
+
 namespace ransac_lib {
 namespace calibrated_absolute_pose {
 namespace refine {
@@ -453,5 +465,10 @@ RLB_HD inline void LeastSquaresWith(const Lin& lin, double* pose /* col-major 3x
 }  // namespace refine
 }  // namespace calibrated_absolute_pose
 }  // namespace ransac_lib
+
+#if defined(RLB_FP_CONTRACT_PUSHED_POSE_REF)
+#pragma GCC pop_options
+#undef RLB_FP_CONTRACT_PUSHED_POSE_REF
+#endif
 
 #endif  // RANSACLIB_B200_EXAMPLES_POSE_REFINEMENT_H_

@@ -89,6 +89,18 @@ struct GpuRunCounters {
   uint64_t batches = 0;           // speculative hypothesis batches
   uint64_t hypotheses_scored = 0; // K summed over batches (includes speculation waste)
   uint64_t single_passes = 0;     // fused K=1 passes (LO, inlier collection, f64 re-scores)
+  uint64_t handbacks = 0;         // device-resident runs handed back to the host-driven loop (LORansacGpuOptions)
+  uint64_t handback_iterations = 0;  // iterations those runs had done on the device (work done twice)
+};
+
+// When the device-resident driver of a solver (one CTA runs the whole problem) may hand a run back to the
+// host-driven loop, whose sweeps use the whole GPU: a run that after `handback_after` iterations still needs
+// more than `handback_min_remaining` hypotheses (very low inlier ratios). One SM sweeps ~7 hypothesis x point
+// evaluations per cycle, so a few thousand hypotheses over 10k points are where the whole-GPU sweep wins
+// (DESIGN.md section 3c). handback_after = 0 never hands back. The run is the same either way.
+struct LORansacGpuOptions {
+  uint32_t handback_after = 384u;
+  uint32_t handback_min_remaining = 3000u;
 };
 
 class RansacBase {
@@ -113,6 +125,8 @@ class LocallyOptimizedMSAC : public RansacBase {
  public:
   // Optional: where to accumulate driver counters (may stay null).
   mutable GpuRunCounters* counters = nullptr;
+  // GPU-side policy knobs (not part of the reference API; the defaults are what the tests and benches use).
+  LORansacGpuOptions gpu_options;
 
   // Same contract as reference ransac.h:128-275: returns the number of inliers; leaves
   // *best_model untouched when there is too little data or no model was found.
@@ -260,17 +274,25 @@ class LocallyOptimizedMSAC : public RansacBase {
     o.non_min_sample_mult = options.non_min_sample_multiplier_;
     o.lo_start = options.lo_starting_iterations_;
     o.final_lsq = options.final_least_squares_ ? 1 : 0;
+    o.debug_flags = 0;
     // One CTA runs the whole problem; a run that turns out to need thousands of hypotheses (very low
-    // inlier ratios) is handed back after 384 iterations and restarts in the loop below, whose sweeps
-    // use the whole GPU. Same run either way.
-    o.debug_flags = 4;
+    // inlier ratios) is handed back and restarts in the loop below, whose sweeps use the whole GPU
+    // (gpu_options; counted in GpuRunCounters). Same run either way.
+    o.handback_after = gpu_options.handback_after;
+    o.handback_min_remaining = gpu_options.handback_min_remaining;
     double packed[16] = {0.0};
     Solver::PackModel(*best_model, packed);  // read by the final least-squares step (ransac.h:257-259)
     rlb_lomsac_result r;
     std::vector<int> inliers;
     if (!solver.device_lomsac(o, options.random_seed_, packed, &r, &inliers)) return false;
     RansacStatistics& stats = *statistics;
-    if (r.success == 2) return false;
+    if (r.success == 2) {
+      if (counters) {
+        counters->handbacks += 1;
+        counters->handback_iterations += r.num_iterations;
+      }
+      return false;
+    }
     if (!r.success) return true;
     stats.num_iterations = r.num_iterations;
     stats.best_num_inliers = r.num_inliers;

@@ -275,8 +275,14 @@ typedef struct rlb_localize_options {
   uint32_t lo_start;
   int32_t final_lsq;
   int32_t debug_flags;             /* bit 0: force the sequential path of every shuffle (tests);
-                                    * bit 2 (line LO-MSAC only): a run that still needs > 3000 hypotheses after
-                                    * 384 iterations is handed back: result.success = 2, nothing else written */
+                                    * bit 1: per-phase cycle counters into the tail of the inlier region (tools) */
+  /* Line LO-MSAC only (one CTA = one SM runs a problem): a run that after `handback_after` iterations
+   * still needs more than `handback_min_remaining` further hypotheses is HANDED BACK to the caller:
+   * result.success = 2, result.num_iterations = iterations done, nothing else written; the caller then
+   * runs it where sweeps use the whole GPU (the drop-in LocallyOptimizedMSAC does, and counts it in
+   * GpuRunCounters::handbacks). handback_after = 0 (the default): never hand back. */
+  uint32_t handback_after;
+  uint32_t handback_min_remaining;
 } rlb_localize_options;
 
 typedef struct rlb_localize_result {

@@ -134,7 +134,7 @@ class Context:
     def lomsac_options(self, **kw) -> "_capi.LocalizeOptions":
         """LORansacOptions defaults (ransac.h:47-92); keyword names are the struct's fields
         (min_iters, max_iters, success_prob, sq_thr, lo_steps, thr_mult, lsq_iters, min_sample_mult,
-        non_min_sample_mult, lo_start, final_lsq, debug_flags)."""
+        non_min_sample_mult, lo_start, final_lsq, debug_flags, handback_after, handback_min_remaining)."""
         o = _capi.LocalizeOptions()
         self._lib.rlb_lomsac_default_options(C.byref(o))
         for k, v in kw.items():

@@ -43,7 +43,8 @@ class LocalizeOptions(C.Structure):
     _fields_ = [("min_iters", C.c_uint32), ("max_iters", C.c_uint32), ("success_prob", C.c_double),
                 ("sq_thr", C.c_double), ("lo_steps", C.c_int32), ("thr_mult", C.c_double),
                 ("lsq_iters", C.c_int32), ("min_sample_mult", C.c_int32), ("non_min_sample_mult", C.c_int32),
-                ("lo_start", C.c_uint32), ("final_lsq", C.c_int32), ("debug_flags", C.c_int32)]
+                ("lo_start", C.c_uint32), ("final_lsq", C.c_int32), ("debug_flags", C.c_int32),
+                ("handback_after", C.c_uint32), ("handback_min_remaining", C.c_uint32)]
 
 
 # rlb_localize_result as a numpy record (40 bytes)

@@ -743,9 +743,16 @@ int rlb_scorer_create_pose(rlb_ctx* c, int n, const double* p2d, const double* p
   return RLB_OK;
 }
 
-int rlb_scorer_create_pose_dev(rlb_ctx* c, int n, const double* d_p2d, const double* d_p3d, double fx,
-                               double fy, rlb_scorer** out) {
-  if (!c || !out || n < 0 || (n > 0 && (!d_p2d || !d_p3d))) return fail(RLB_E_ARG, "bad arguments");
+}  // extern "C"
+
+namespace rlb {
+// Two-step construction of a pose scorer whose raw arrays are filled ON THE DEVICE by the caller (a device
+// copy, or an upload / ncclBroadcast straight into them: comm.cu). begin: allocates; *raw2d (n x 2) and
+// *raw3d (n x 3) are the scorer's own arrays. finish: everything written to them must be ordered before it
+// on the context stream; derives the recentring point exactly as the host-pointer constructor does (the
+// same sub-sampled rows, read back with one strided copy) and builds the SoA copies and the rays.
+int scorer_pose_begin(rlb_ctx* c, int n, double fx, double fy, rlb_scorer** out, double** raw2d, double** raw3d) {
+  if (!c || !out || n < 0) return fail(RLB_E_ARG, "bad arguments");
   int rc = ctx_use(c);
   if (rc) return rc;
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
@@ -761,36 +768,56 @@ int rlb_scorer_create_pose_dev(rlb_ctx* c, int n, const double* d_p2d, const dou
   d.channels = 5;
   d.fx = fx;
   d.fy = fy;
-  // The recentring point of the f32 copy: the same sub-sampled mean as the host-pointer constructor, taken
-  // from the rows it would read (one strided copy back), so both constructors build identical scorers.
-  {
-    const int step = std::max(1, n / 4096);
-    const int m = (n > 0) ? (n + step - 1) / step : 0;
-    std::vector<double> sub(static_cast<size_t>(std::max(m, 1)) * 3, 0.0);
-    if (m > 0) {
-      cudaError_t e = cudaMemcpy2DAsync(sub.data(), 3 * sizeof(double), d_p3d, static_cast<size_t>(step) * 3 * sizeof(double),
-                                        3 * sizeof(double), static_cast<size_t>(m), cudaMemcpyDeviceToHost, c->stream);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-      if (e != cudaSuccess) {
-        delete s;
-        return fail(RLB_E_CUDA, "reading the sub-sample back failed: %s", cudaGetErrorString(e));
-      }
-    }
-    subsampled_mean(sub.data(), m, 3, 3, d.centre);
-  }
   rc = pool_alloc(c, static_cast<size_t>(std::max(n, 1)) * 2 * sizeof(double), &s->raw0);
   if (!rc) rc = pool_alloc(c, static_cast<size_t>(std::max(n, 1)) * 3 * sizeof(double), &s->raw1);
-  if (!rc && n > 0) {
-    cudaError_t e = cudaMemcpyAsync(s->raw0, d_p2d, static_cast<size_t>(n) * 2 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream);
+  if (rc) {
+    rlb_scorer_destroy(s);
+    return rc;
+  }
+  d.raw0 = static_cast<const double*>(s->raw0);
+  d.raw1 = static_cast<const double*>(s->raw1);
+  *raw2d = static_cast<double*>(s->raw0);
+  *raw3d = static_cast<double*>(s->raw1);
+  *out = s;
+  return RLB_OK;
+}
+
+int scorer_pose_finish(rlb_scorer* s) {
+  rlb_ctx* c = s->ctx;
+  int rc = ctx_use(c);
+  if (rc) return rc;
+  DeviceData& d = s->d;
+  const int n = d.n[0];
+  const int step = std::max(1, n / 4096);
+  const int m = (n > 0) ? (n + step - 1) / step : 0;
+  std::vector<double> sub(static_cast<size_t>(std::max(m, 1)) * 3, 0.0);
+  if (m > 0) {
+    cudaError_t e = cudaMemcpy2DAsync(sub.data(), 3 * sizeof(double), d.raw1, static_cast<size_t>(step) * 3 * sizeof(double),
+                                      3 * sizeof(double), static_cast<size_t>(m), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return fail(RLB_E_CUDA, "reading the sub-sample back failed: %s", cudaGetErrorString(e));
+  }
+  subsampled_mean(sub.data(), m, 3, 3, d.centre);
+  return finish_scorer(s);
+}
+}  // namespace rlb
+
+extern "C" {
+
+int rlb_scorer_create_pose_dev(rlb_ctx* c, int n, const double* d_p2d, const double* d_p3d, double fx,
+                               double fy, rlb_scorer** out) {
+  if (!c || !out || n < 0 || (n > 0 && (!d_p2d || !d_p3d))) return fail(RLB_E_ARG, "bad arguments");
+  rlb_scorer* s = nullptr;
+  double *r2 = nullptr, *r3 = nullptr;
+  int rc = rlb::scorer_pose_begin(c, n, fx, fy, &s, &r2, &r3);
+  if (rc) return rc;
+  if (n > 0) {
+    cudaError_t e = cudaMemcpyAsync(r2, d_p2d, static_cast<size_t>(n) * 2 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream);
     if (e == cudaSuccess)
-      e = cudaMemcpyAsync(s->raw1, d_p3d, static_cast<size_t>(n) * 3 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream);
+      e = cudaMemcpyAsync(r3, d_p3d, static_cast<size_t>(n) * 3 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream);
     if (e != cudaSuccess) rc = fail(RLB_E_CUDA, "device copy of the point set failed: %s", cudaGetErrorString(e));
   }
-  if (!rc) {
-    d.raw0 = static_cast<const double*>(s->raw0);
-    d.raw1 = static_cast<const double*>(s->raw1);
-    rc = finish_scorer(s);
-  }
+  if (!rc) rc = rlb::scorer_pose_finish(s);
   if (rc) {
     rlb_scorer_destroy(s);
     return rc;
@@ -1389,6 +1416,8 @@ void rlb_localize_default_options(rlb_localize_options* o, double inlier_thresho
   o->lo_start = 60u;
   o->final_lsq = 1;
   o->debug_flags = 0;
+  o->handback_after = 0u;
+  o->handback_min_remaining = 0u;
 }
 
 int rlb_localize_batch_dev(rlb_ctx* c, int nq, int max_matches, const int64_t* d_offsets,
@@ -1619,6 +1648,8 @@ void rlb_lomsac_default_options(rlb_lomsac_options* o) {
   o->lo_start = 50u;
   o->final_lsq = 0;
   o->debug_flags = 0;
+  o->handback_after = 0u;
+  o->handback_min_remaining = 0u;
 }
 
 int rlb_line_lomsac_batch_dev(rlb_ctx* c, int np, int max_points, const int64_t* d_offsets, const double* d_xy,

@@ -329,52 +329,48 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
   cs->n = n;
   cs->sc.assign(cm->local.size(), nullptr);
   NcclApi* a = nccl_api();
-  const size_t doubles = static_cast<size_t>(n) * 5;
-  std::vector<double*> stage(cm->local.size(), nullptr);
-  int rc = RLB_OK;
-  auto cleanup = [&](int code) {
-    for (size_t i = 0; i < stage.size(); ++i)
-      if (stage[i]) {
-        cudaSetDevice(cm->local[i].device);
-        cudaStreamSynchronize(cm->local[i].stream());
-        cudaFree(stage[i]);
-      }
-    if (code) rlb_comm_scorer_destroy(cs);
-    return code;
-  };
-  // staging: [p2d (n x 2) | p3d (n x 3)] on every rank; the root's copy comes from the host over PCIe
-  for (size_t i = 0; i < cm->local.size() && !rc; ++i) {
+  std::vector<double*> r2(cm->local.size(), nullptr), r3(cm->local.size(), nullptr);
+  // every rank allocates its scorer; the root's arrays are filled from the host over PCIe ...
+  for (size_t i = 0; i < cm->local.size(); ++i) {
     LocalRank& L = cm->local[i];
-    if (cudaSetDevice(L.device) != cudaSuccess ||
-        cudaMalloc(reinterpret_cast<void**>(&stage[i]), std::max<size_t>(doubles, 1) * sizeof(double)) != cudaSuccess)
-      rc = set_error(RLB_E_CUDA, "staging allocation failed on device %d", L.device);
+    cudaSetDevice(L.device);
+    int rc = rlb::scorer_pose_begin(L.ctx, n, fx, fy, &cs->sc[i], &r2[i], &r3[i]);
     if (!rc && L.rank == root && n > 0) {
-      if (cudaMemcpyAsync(stage[i], p2d, static_cast<size_t>(n) * 2 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess ||
-          cudaMemcpyAsync(stage[i] + static_cast<size_t>(n) * 2, p3d, static_cast<size_t>(n) * 3 * sizeof(double),
-                          cudaMemcpyHostToDevice, L.stream()) != cudaSuccess)
+      if (cudaMemcpyAsync(r2[i], p2d, static_cast<size_t>(n) * 2 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess ||
+          cudaMemcpyAsync(r3[i], p3d, static_cast<size_t>(n) * 3 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess)
         rc = set_error(RLB_E_CUDA, "upload of the point set failed");
     }
+    if (rc) {
+      rlb_comm_scorer_destroy(cs);
+      return rc;
+    }
   }
-  if (rc) return cleanup(rc);
+  // ... and reach the other GPUs over NVLink, straight into their scorers' arrays
   if (cm->nranks > 1 && n > 0) {
     ncclResult_t r = a->GroupStart();
     for (size_t i = 0; i < cm->local.size() && r == ncclSuccess; ++i) {
       LocalRank& L = cm->local[i];
-      r = a->Broadcast(stage[i], stage[i], doubles, ncclDouble, root, L.nccl, L.stream());
+      r = a->Broadcast(r2[i], r2[i], static_cast<size_t>(n) * 2, ncclDouble, root, L.nccl, L.stream());
+      if (r == ncclSuccess) r = a->Broadcast(r3[i], r3[i], static_cast<size_t>(n) * 3, ncclDouble, root, L.nccl, L.stream());
     }
-    ncclResult_t r2 = a->GroupEnd();
-    if (r == ncclSuccess) r = r2;
-    if (r != ncclSuccess) return cleanup(set_error(RLB_E_COMM, "ncclBroadcast failed: %s", a->GetErrorString(r)));
-    ++cm->collectives;
+    ncclResult_t rg = a->GroupEnd();
+    if (r == ncclSuccess) r = rg;
+    if (r != ncclSuccess) {
+      set_error(RLB_E_COMM, "ncclBroadcast failed: %s", a->GetErrorString(r));
+      rlb_comm_scorer_destroy(cs);
+      return RLB_E_COMM;
+    }
+    cm->collectives += 2;
   }
-  // every rank builds its scorer from the device-resident copy (same centre everywhere: it is derived on the
-  // device from the same bytes)
+  // every rank derives the same recentring point from the same bytes and builds its SoA copies
   for (size_t i = 0; i < cm->local.size(); ++i) {
-    LocalRank& L = cm->local[i];
-    rc = rlb_scorer_create_pose_dev(L.ctx, n, stage[i], stage[i] + static_cast<size_t>(n) * 2, fx, fy, &cs->sc[i]);
-    if (rc) return cleanup(rc);
+    cudaSetDevice(cm->local[i].device);
+    int rc = rlb::scorer_pose_finish(cs->sc[i]);
+    if (rc) {
+      rlb_comm_scorer_destroy(cs);
+      return rc;
+    }
   }
-  cleanup(RLB_OK);
   *out = cs;
   return RLB_OK;
 }

@@ -53,7 +53,6 @@ constexpr int kWarps = kT / 32;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr double kNever = DBL_MAX;
 constexpr int kFirstBatch = 128;
-constexpr uint32_t kBailAfter = 384u, kBailRemaining = 3000u;  // see run_problem (debug_flags bit 2)
 constexpr int kSuper = kT * 32;  // points per ordered-compaction round (one 32-bit mask per lane)
 
 struct Line {
@@ -723,7 +722,7 @@ __device__ Line run_problem(Shared& sh, const Line initial, rlb_localize_result*
       // Speculate on the next iterations: samples are a pure function of the sampler stream,
       // hypotheses do not depend on the LO stream.
       const uint32_t bound = max(max_iters, it + 1u);
-      if ((o.debug_flags & 4) && it >= kBailAfter && bound - it > kBailRemaining) {
+      if (o.handback_after > 0u && it >= o.handback_after && bound - it > o.handback_min_remaining) {
         // One SM sweeps ~7 hypothesis x point evaluations per cycle; a run that still needs thousands
         // of hypotheses is better served by the whole-GPU sweep of the host-driven loop. The caller
         // allowed handing it back (same run from scratch there: results do not depend on the driver).

@@ -62,12 +62,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // two Newton steps are within 1 ulp of the exact reciprocal, far inside the 1e-9 parity band.
 // x == 0 returns the seed itself (+-inf), so z == 0 still falls through to inf / NaN exactly like
 // the reference's px / pz (calibrated_absolute_pose_estimator.cc:160-165); subnormal |x| counts as 0.
+#ifndef RLB_F64_TRIM
+#define RLB_F64_TRIM 1  // 0: two Newton steps; 1 (default): one cubic step; 2: + inlier / sign tests on the integer pipe (slower: profiles/r02_f64_sweep_ab.txt)
+#endif
 __device__ __forceinline__ double rcp_f64(double x) {
   double r0;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r0) : "d"(x));
   double r = fma(fma(-x, r0, 1.0), r0, r0);
   r = fma(fma(-x, r, 1.0), r, r);
   return (x == 0.0) ? r0 : r;
+}
+// The sweep's form of the same reciprocal: ONE cubically convergent step from the seed
+// (r = r0 + r0 (e + e^2), e = 1 - x r0: |e| <= 2^-20 leaves e^3 far below 2^-53) = 3 FP64-pipe
+// instructions instead of 4, and the zero test runs on the integer pipe (exponent field == 0: zero
+// or subnormal, as above). The FP64 pipe issues one warp instruction every 2 cycles and is what bounds
+// the f64 sweep, so every instruction moved off it counts.
+__device__ __forceinline__ double rcp_f64_sweep(double x) {
+  double r0;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r0) : "d"(x));
+  const double e = fma(-x, r0, 1.0);
+  const double r = fma(fma(e, e, e), r0, r0);
+  return ((__double2hiint(x) & 0x7ff00000) == 0) ? r0 : r;
 }
 __device__ __forceinline__ float rcp_approx(float x) {
   float r;
@@ -152,11 +167,22 @@ __device__ __forceinline__ double PoseF<double>::eval(const Model& m, const doub
   const double pz = fma(m.r[6], p[0], fma(m.r[7], p[1], fma(m.r[8], p[2], m.t[2])));
   const double px = fma(m.r[0], p[0], fma(m.r[1], p[1], fma(m.r[2], p[2], m.t[0])));
   const double py = fma(m.r[3], p[0], fma(m.r[4], p[1], fma(m.r[5], p[2], m.t[1])));
+#if RLB_F64_TRIM
+  const double inv = rcp_f64_sweep(pz);
+#else
   const double inv = rcp_f64(pz);
+#endif
   const double du = fma(px, inv, -p[3]);
   const double dv = fma(py, inv, -p[4]);
   const double e = fma(du, du, dv * dv);
+#if RLB_F64_TRIM >= 2
+  // pz < 0.0 on the integer pipe: sign bit set and not -0.0
+  const long long zb = __double_as_longlong(pz);
+  const bool behind = (zb < 0) && ((zb << 1) != 0);
+  return behind ? DBL_MAX : e;
+#else
   return (pz < 0.0) ? DBL_MAX : e;
+#endif
 }
 // f32: 13 FMA-pipe ops + MUFU.RCP + FMNMX. pz < 0 -> rcp(0) = +inf -> e = inf/NaN,
 // which fails the (e < thr) test exactly like the reference's DBL_MAX sentinel.
@@ -177,6 +203,12 @@ __device__ __forceinline__ float PoseF<float>::eval(const Model& m, const float*
 // the outlier mass thr * (#points - #inliers) is added in f64 at the stage flush.
 template <typename T>
 struct Acc;
+// f64: every squared residual the built-in functors produce is >= +0, +inf, DBL_MAX or NaN, and for those the
+// IEEE bit patterns order like unsigned integers (NaN above +inf): the strict inlier test e < thr and the NaN
+// test run on the integer pipe, the FP64 pipe only adds the inliers' errors. The outlier mass thr * (#points -
+// #inliers) is added at the stage flush: std::min(e, thr) summed in another order (well inside the 1e-9 the f64
+// path promises; counts are exact), and a NaN error makes the stage's score NaN as std::min propagates it.
+#if RLB_F64_TRIM < 2
 template <>
 struct Acc<double> {
   double s;
@@ -191,6 +223,32 @@ struct Acc<double> {
   }
   __device__ __forceinline__ double flush(double, int) const { return s; }
 };
+#else
+template <>
+struct Acc<double> {
+  double s;
+  int c;
+  unsigned nan;
+  __device__ __forceinline__ void reset() {
+    s = 0.0;
+    c = 0;
+    nan = 0u;
+  }
+  __device__ __forceinline__ void add(double e, double thr) {
+    const unsigned long long eb = static_cast<unsigned long long>(__double_as_longlong(e));
+    // thr <= 0 (the hybrid LO's relaxed thresholds end up there): nothing is below it (loop-invariant)
+    const unsigned long long tb = (thr > 0.0) ? static_cast<unsigned long long>(__double_as_longlong(thr)) : 0ull;
+    const bool in = eb < tb;
+    if (in) s += e;
+    c += in ? 1 : 0;
+    nan |= (eb > 0x7ff0000000000000ull) ? 1u : 0u;
+  }
+  __device__ __forceinline__ double flush(double thr, int npts) const {
+    const double v = s + thr * static_cast<double>(npts - c);
+    return nan ? __longlong_as_double(0x7ff8000000000000LL) : v;
+  }
+};
+#endif
 template <>
 struct Acc<float> {
   float s;

@@ -1,6 +1,7 @@
 """Drop-in for the reference's Python module ``pyransaclib`` (examples/pyransaclib.cc:38-46,
 examples/ransaclib_localization.cc:58-165): same function name, keyword arguments and result
-dictionary. Usage:  ``from ransaclib_b200 import pyransaclib``.
+dictionary. Usage:  ``import pyransaclib`` (the one-file shim at the repository root) or
+``from ransaclib_b200 import pyransaclib``.
 
 Additions allowed by the survey: an optional trailing ``random_seed`` (the reference seeds from
 std::random_device, ransaclib_localization.cc:109-110, so it is not reproducible) and the batched
@@ -33,7 +34,7 @@ def ransaclib_localization_batch(query_names, focal_x, focal_y, points2D_list, p
                                  device=0):
     """Independent queries (they share nothing: examples/localization.cc:190), one result dict per
     query, all of them estimated by ONE launch of the device-resident LO-MSAC kernel
-    (``rlb_localize_batch``: one warp per query, no host round trips)."""
+    (``rlb_localize_batch``: one CTA per query, no host round trips)."""
     nq = len(query_names)
     if random_seeds is None:
         import random

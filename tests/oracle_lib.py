@@ -135,11 +135,33 @@ def oracle():
     return _cache["o"]
 
 
+def _host_has_avx512():
+    try:
+        with open("/proc/cpuinfo") as fh:
+            for ln in fh:
+                if ln.startswith("flags"):
+                    fl = set(ln.split(":", 1)[1].split())
+                    return {"avx512f", "avx512dq", "avx512cd", "avx512bw", "avx512vl"} <= fl
+    except OSError:
+        pass
+    return False
+
+
+def reference_fast_flags():
+    """Which -march the timed reference build in use was compiled for (the widest this host supports: what the
+    reference's own -march=native, examples/CMakeLists.txt:7,15, selects on this host)."""
+    v4 = os.path.join(ORACLE_DIR, "_ref", "libransac_ref_fast_v4.so")
+    return "x86-64-v4" if (_host_has_avx512() and os.path.exists(v4)) else "x86-64-v3"
+
+
 def reference(fast=False):
     """The reference's own headers compiled in oracle/_ref, or None if not built."""
     key = "rf" if fast else "r"
     if key not in _cache:
-        path = os.path.join(ORACLE_DIR, "_ref", "libransac_ref_fast.so" if fast else "libransac_ref.so")
+        name = "libransac_ref.so"
+        if fast:
+            name = "libransac_ref_fast_v4.so" if reference_fast_flags() == "x86-64-v4" else "libransac_ref_fast.so"
+        path = os.path.join(ORACLE_DIR, "_ref", name)
         _cache[key] = _bind(C.CDLL(path), "ref_") if os.path.exists(path) else None
     return _cache[key]
 

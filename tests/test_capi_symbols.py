@@ -48,3 +48,16 @@ def test_product_does_not_touch_the_oracle():
                     if re.search(r"oracle[/_]|liboracle|libransac_ref", txt):
                         bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def test_top_level_pyransaclib_module_mirrors_the_reference():
+    """`import pyransaclib` (examples/pyransaclib.cc:38-46): same function name and keyword arguments."""
+    import inspect
+
+    import pyransaclib
+
+    sig = inspect.signature(pyransaclib.ransaclib_localization)
+    want = ["query_name", "focal_x", "focal_y", "points2D_vec", "points3D_vec", "inlier_threshold",
+            "number_lo_steps", "min_num_iterations", "max_num_iterations"]
+    assert list(sig.parameters)[:len(want)] == want
+    assert callable(pyransaclib.ransaclib_localization_batch)

@@ -139,7 +139,7 @@ def test_two_gpus_one_process(case):
     out = cs.hypothesize_and_score(samples, THR, want_scores=True)
     assert out["best_id"] == ref["best_id"] and out["best_score"] == ref["best_score"]
     assert out["scores"].tolist() == ref["scores"].tolist()
-    assert comm.collective_count == 2  # one broadcast, one all_gather
+    assert comm.collective_count == 3  # the two point arrays broadcast, one all_gather
     cs.close()
     comm.close()
     sc.close()

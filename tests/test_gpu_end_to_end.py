@@ -49,7 +49,7 @@ def check_same(stats, model, ost, omodel, oinl, model_rtol=1e-9):
     assert stats["inlier_ratio"] == ost.inlier_ratio
 
 
-@pytest.mark.parametrize("outlier_ratio,seed", [(0.1, 42), (0.5, 7), (0.9, 3), (0.99, 11)])
+@pytest.mark.parametrize("outlier_ratio,seed", [(0.1, 42), (0.5, 7), (0.9, 3), (0.95, 5), (0.99, 11), (0.999, 13)])
 def test_line_estimation_config(outlier_ratio, seed):
     """BASELINE configs[0]: examples/line_estimation.cc (N = 10,000, thr^2 = 1e-4, max 100k)."""
     H = host()

@@ -63,7 +63,7 @@ def check_against_oracle(xy, off, seeds, lines, res, inl, init=None, **kw):
         assert res["inlier_ratio"][p] == ost.inlier_ratio, tag
 
 
-@pytest.mark.parametrize("outlier_ratio,seed", [(0.1, 42), (0.5, 7), (0.9, 3), (0.99, 11)])
+@pytest.mark.parametrize("outlier_ratio,seed", [(0.1, 42), (0.5, 7), (0.9, 3), (0.95, 5), (0.99, 11), (0.999, 13)])
 def test_c1_line_estimation_in_one_launch(ctx, outlier_ratio, seed):
     """BASELINE configs[0] (examples/line_estimation.cc: N = 10,000, thr^2 = 1e-4, 100 .. 100k iterations)
     over a resident line scorer: one launch, same run as the reference."""
@@ -207,7 +207,7 @@ def test_long_runs_are_handed_back_when_allowed(ctx):
     assert ost.num_iterations > 5000
     sc = ctx.line_scorer(xy)
     init = np.array([1.0, 2.0, 3.0])
-    line, r, _ = sc.line_lomsac(ctx.lomsac_options(debug_flags=4, **kw), 11, line=init)
+    line, r, _ = sc.line_lomsac(ctx.lomsac_options(handback_after=384, handback_min_remaining=3000, **kw), 11, line=init)
     assert r["success"] == 2 and line.tolist() == init.tolist() and 384 <= r["num_iterations"] < 1024
     line, r, inl = sc.line_lomsac(ctx.lomsac_options(**kw), 11)  # not allowed to hand back: runs to the end
     assert r["success"] == 1 and r["num_iterations"] == ost.num_iterations and inl.tolist() == oinl.tolist()
