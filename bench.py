@@ -34,7 +34,7 @@ sys.path.insert(0, ROOT)
 FLOP_PER_EVAL = 29.0  # pose evaluation incl. min + accumulate
 # dram__bytes_read.sum + dram__bytes_write.sum of one sweep_pose_tc_kernel launch on the default C5 run
 # (ncu --set full): 80.2 MB read (72 MB of operand tiles) + the [splits][K] partials written: 18.4 MB scores only
-# (profiles/r01s_ncu_sweep_tc.csv), 28.0 MB with counts (profiles/r01r_ncu_sweep_tc.csv)
+# (profiles/history/r01s_ncu_sweep_tc.csv), 28.0 MB with counts (profiles/r01r_ncu_sweep_tc.csv)
 TC_TRAFFIC = {False: 98.6e6, True: 108.3e6}
 THR = 144.0           # 12 px squared, camera_pose_estimation.cc:154-156
 WORKLOADS = {
@@ -253,15 +253,22 @@ def run_ours(args):
     e2e_steps = max(1, min(args.steps, 5))
 
     h_all = pin(np.ascontiguousarray(samples_all))
+    e2e_parts = []
 
     def e2e_step():
-        # host buffers in, results out, everything inside: the points go up ONCE (rank 0, PCIe) and reach the
-        # other GPUs by ncclBroadcast; every rank uploads its shard of the samples; one ncclAllGather; the
-        # winner's ordered inlier list comes back from the first GPU of every process
-        cs = comm.pose_scorer(h_p2 if rank == 0 else n, h_p3 if rank == 0 else None, f, f, root=0)
+        # host buffers in, results out, everything inside: every rank holds the step's inputs in pinned host
+        # memory and uploads 1/G of the points over its own PCIe link (RLB_COMM_ROOT_ALL), the slices are
+        # exchanged over NVLink; every rank uploads its shard of the samples; one ncclAllGather; the winner's
+        # ordered inlier list comes back from the first GPU of every process
+        t0 = time.perf_counter()
+        cs = comm.pose_scorer(h_p2, h_p3, f, f, root=-1)
+        t1 = time.perf_counter()
         r = cs.hypothesize_and_score(h_all, THR, precision=prec, want_scores=True)
+        t2 = time.perf_counter()
         inl, score = cs.get_inliers(r["best_model"], THR, THR)
         cs.close()
+        t3 = time.perf_counter()
+        e2e_parts.append((t1 - t0, t2 - t1, t3 - t2))
         return r, [len(inl)]
 
     if args.profile:
@@ -273,6 +280,7 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     e2e_step()
+    e2e_parts.clear()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -285,7 +293,7 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = k_total * n * e2e_steps / float(te.item())
-    h2d = (p2.nbytes + p3.nbytes if rank == 0 else 0) + my_samples.nbytes + 12 * 8
+    h2d = (p2.nbytes + p3.nbytes) // world + my_samples.nbytes + 12 * 8
     d2h = k * 8 + k * 4 + 16 + 96 + 16 + 4 * int(c_e2e[0])
 
     # ---- second half of BASELINE.json's metric: batched localization (configs[3]) on the same GPUs ----
@@ -344,7 +352,7 @@ def run_ours(args):
         "evals_per_s": evals_per_launch / (sweep_avg_ms * 1e-3),
         "share_of_step": sweep_avg_ms * args.steps / total_ms,
         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, one launch, from the ncu --set full
-        # capture of the same command (profiles/r01b_ncu_sweep_h8.csv); only valid for the default f32 C5 run.
+        # capture of the same command (profiles/history/r01b_ncu_sweep_h8.csv); only valid for the default f32 C5 run.
         "traffic": (TC_TRAFFIC[bool(args.counts)] if tc else 33.1e6) if (prec == rlb.RLB_F32 and args.workload == "c5" and world == 1)
         else None,
         "hbm": {"algorithmic_bytes": algo_bytes, "achieved_gbs": algo_bytes / (sweep_avg_ms * 1e-3) / 1e9,
@@ -383,7 +391,13 @@ def run_ours(args):
                    "step": "P3P solve + KxN MSAC sweep + argmin + ordered inlier list of the winner"},
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                "path": "rlb_comm_scorer_create_pose (one PCIe upload on rank 0 + ncclBroadcast) + "
+                "breakdown_ms": {
+                    "create_scorer (upload + NVLink exchange + repack + rays)": 1e3 * float(np.mean([q[0] for q in e2e_parts])),
+                    "hypothesize_and_score (samples up, P3P, tile pack, sweep, all_gather, scores back)":
+                        1e3 * float(np.mean([q[1] for q in e2e_parts])),
+                    "get_inliers + destroy": 1e3 * float(np.mean([q[2] for q in e2e_parts]))},
+                "path": "rlb_comm_scorer_create_pose (every GPU uploads 1/G of the points over its own PCIe link, "
+                        "slices exchanged over NVLink) + "
                         "rlb_comm_hypothesize_and_score (shard upload, sweep, one ncclAllGather, scores + counts "
                         "back) + rlb_comm_get_inliers, pinned host buffers; bytes are rank 0's"},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
@@ -822,7 +836,7 @@ def measure_c4(args, rank, world, local, dist, steps, warmup, q_total=None):
                      "frac": None, "traffic": None,
                      "note": "control-flow kernel (one warp = one whole LO-MSAC run); per query on average "
                              "%.0f f64 passes over the matches, %.0f LM refinements, %.1f iterations, %.2f LO calls; "
-                             "ncu: profiles/r01e_ncu_localize.csv (issue active 22%%, fp64 pipe 11%%, stalls: "
+                             "ncu: profiles/history/r01e_ncu_localize.csv (issue active 22%%, fp64 pipe 11%%, stalls: "
                              "long scoreboard / fixed-latency wait / instruction fetch)"
                              % (res["passes"].mean(), res["lsq_calls"].mean(), res["num_iterations"].mean(),
                                 res["num_lo"].mean())},

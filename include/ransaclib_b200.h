@@ -230,7 +230,11 @@ rlb_ctx* rlb_comm_ctx(rlb_comm* comm, int local_index);
 int64_t rlb_comm_collective_count(const rlb_comm* comm); /* NCCL collectives issued so far */
 
 /* CalibratedAbsolutePoseEstimator's data on every GPU of the communicator. Collective: every process of
- * the communicator calls it; points2D / points3D are read on the process that owns rank `root` only. */
+ * the communicator calls it; points2D / points3D are read on the process that owns rank `root` only (one
+ * PCIe upload, ncclBroadcast over NVLink). root = RLB_COMM_ROOT_ALL: EVERY process holds the arrays (always
+ * true for rlb_comm_create_local); each GPU then uploads 1/G of them over its own PCIe link and the slices
+ * are exchanged over NVLink - the upload time divides by the number of GPUs. */
+#define RLB_COMM_ROOT_ALL (-1)
 int rlb_comm_scorer_create_pose(rlb_comm* comm, int n, const double* points2D, const double* points3D,
                                 double fx, double fy, int root, rlb_comm_scorer** out);
 int rlb_comm_scorer_destroy(rlb_comm_scorer* cs);

@@ -260,7 +260,9 @@ class Comm:
 
     def pose_scorer(self, points2D, points3D, fx: float, fy: float, root: int = 0) -> "CommScorer":
         """Collective. The arrays are read on the process that owns rank `root` (one PCIe upload) and reach
-        the other GPUs by ncclBroadcast; other processes may pass None with the number of points."""
+        the other GPUs by ncclBroadcast; other processes may pass None with the number of points.
+        root = -1 (RLB_COMM_ROOT_ALL): every process holds the arrays; each GPU uploads 1/G of them over its
+        own PCIe link and the slices are exchanged over NVLink."""
         if isinstance(points2D, int):
             n, p2, p3 = points2D, None, None
         else:
@@ -341,7 +343,9 @@ class CommScorer:
         ti = np.array([sq_thr_inl], np.float64)
         ts = None if sq_thr_score is None else np.array([sq_thr_score], np.float64)
         n = int(self._lib.rlb_scorer_num_data(C.c_void_p(self.local_scorer_handle(0)), 0))
-        idx = np.empty(max(n, 1), np.int32)
+        idx = getattr(self.comm, "_idx_buf", None)  # reused across calls (a fresh 4 MB array costs page faults)
+        if idx is None or len(idx) < max(n, 1):
+            idx = self.comm._idx_buf = np.empty(max(n, 1), np.int32)
         counts = np.zeros(2, np.int32)
         score = C.c_double()
         _capi.check(self._lib.rlb_comm_get_inliers(self._h, _capi.ptr(model), _capi.ptr(ti), _capi.ptr(ts), None,

@@ -390,8 +390,12 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     const double speed = (d_counts != nullptr) ? 1.26 : 1.32;
     double best = -1.0;
     int tc_splits = 1, tc_tps = total_tiles;
-    for (int s0 = 1; s0 <= std::min(total_tiles, 64); ++s0) {
-      if (forced_splits > 0 && s0 != std::min(forced_splits, std::min(total_tiles, 64))) continue;
+    // Up to 64 splits, more (up to 256) while the grid would otherwise stay below ~8 waves of resident CTAs: a
+    // hypothesis shard of one of eight GPUs (K / 8 = 8192 = 64 tiles of 128) ran on 37 splits = 4 waves, whose
+    // last wave's imbalance cost 4 % of the sweep rate (SCALE_r01: 2.31e12 against 2.41e12 evals/s per GPU).
+    const int max_tc_splits = std::min(total_tiles, std::max(64, std::min(256, (8 * slots + k_tiles - 1) / k_tiles)));
+    for (int s0 = 1; s0 <= max_tc_splits; ++s0) {
+      if (forced_splits > 0 && s0 != std::min(forced_splits, max_tc_splits)) continue;
       const int tp = (total_tiles + s0 - 1) / s0;
       const int s_eff = (total_tiles + tp - 1) / tp;
       const long long ctas = static_cast<long long>(k_tiles) * s_eff;

@@ -319,8 +319,9 @@ int64_t rlb_comm_collective_count(const rlb_comm* cm) { return cm ? cm->collecti
 
 int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const double* p3d, double fx, double fy,
                                 int root, rlb_comm_scorer** out) {
-  if (!cm || !out || n < 0 || root < 0 || root >= cm->nranks) return set_error(RLB_E_ARG, "bad arguments");
-  bool have_root = false;
+  if (!cm || !out || n < 0 || root < -1 || root >= cm->nranks) return set_error(RLB_E_ARG, "bad arguments");
+  const bool everyone = (root == RLB_COMM_ROOT_ALL);
+  bool have_root = everyone;
   for (LocalRank& L : cm->local) have_root = have_root || (L.rank == root);
   if (have_root && n > 0 && (!p2d || !p3d)) return set_error(RLB_E_ARG, "the root rank needs the host arrays");
   rlb_comm_scorer* cs = new (std::nothrow) rlb_comm_scorer();
@@ -329,15 +330,20 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
   cs->n = n;
   cs->sc.assign(cm->local.size(), nullptr);
   NcclApi* a = nccl_api();
+  const int G = cm->nranks;
   std::vector<double*> r2(cm->local.size(), nullptr), r3(cm->local.size(), nullptr);
-  // every rank allocates its scorer; the root's arrays are filled from the host over PCIe ...
+  // every rank allocates its scorer; host data goes up over PCIe: all of it on the root, or - when every
+  // process holds the arrays - the slice [n r / G, n (r + 1) / G) on GPU r, each over its own link
   for (size_t i = 0; i < cm->local.size(); ++i) {
     LocalRank& L = cm->local[i];
     cudaSetDevice(L.device);
     int rc = rlb::scorer_pose_begin(L.ctx, n, fx, fy, &cs->sc[i], &r2[i], &r3[i]);
-    if (!rc && L.rank == root && n > 0) {
-      if (cudaMemcpyAsync(r2[i], p2d, static_cast<size_t>(n) * 2 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess ||
-          cudaMemcpyAsync(r3[i], p3d, static_cast<size_t>(n) * 3 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess)
+    int lo = 0, hi = n;
+    if (everyone && G > 1) shard_range(n, L.rank, G, &lo, &hi);
+    if (!rc && (everyone || L.rank == root) && hi > lo) {
+      const size_t m = static_cast<size_t>(hi - lo), o = static_cast<size_t>(lo);
+      if (cudaMemcpyAsync(r2[i] + 2 * o, p2d + 2 * o, m * 2 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess ||
+          cudaMemcpyAsync(r3[i] + 3 * o, p3d + 3 * o, m * 3 * sizeof(double), cudaMemcpyHostToDevice, L.stream()) != cudaSuccess)
         rc = set_error(RLB_E_CUDA, "upload of the point set failed");
     }
     if (rc) {
@@ -345,13 +351,26 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
       return rc;
     }
   }
-  // ... and reach the other GPUs over NVLink, straight into their scorers' arrays
-  if (cm->nranks > 1 && n > 0) {
+  // ... and reaches the other GPUs over NVLink, straight into their scorers' arrays: one broadcast per array
+  // from the root, or one per rank's slice (an all-gather with uneven pieces)
+  if (G > 1 && n > 0) {
     ncclResult_t r = a->GroupStart();
     for (size_t i = 0; i < cm->local.size() && r == ncclSuccess; ++i) {
       LocalRank& L = cm->local[i];
-      r = a->Broadcast(r2[i], r2[i], static_cast<size_t>(n) * 2, ncclDouble, root, L.nccl, L.stream());
-      if (r == ncclSuccess) r = a->Broadcast(r3[i], r3[i], static_cast<size_t>(n) * 3, ncclDouble, root, L.nccl, L.stream());
+      if (!everyone) {
+        r = a->Broadcast(r2[i], r2[i], static_cast<size_t>(n) * 2, ncclDouble, root, L.nccl, L.stream());
+        if (r == ncclSuccess) r = a->Broadcast(r3[i], r3[i], static_cast<size_t>(n) * 3, ncclDouble, root, L.nccl, L.stream());
+        continue;
+      }
+      for (int src = 0; src < G && r == ncclSuccess; ++src) {
+        int lo, hi;
+        shard_range(n, src, G, &lo, &hi);
+        if (hi <= lo) continue;
+        double* b2 = r2[i] + 2 * static_cast<size_t>(lo);
+        double* b3 = r3[i] + 3 * static_cast<size_t>(lo);
+        r = a->Broadcast(b2, b2, static_cast<size_t>(hi - lo) * 2, ncclDouble, src, L.nccl, L.stream());
+        if (r == ncclSuccess) r = a->Broadcast(b3, b3, static_cast<size_t>(hi - lo) * 3, ncclDouble, src, L.nccl, L.stream());
+      }
     }
     ncclResult_t rg = a->GroupEnd();
     if (r == ncclSuccess) r = rg;
@@ -360,7 +379,7 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
       rlb_comm_scorer_destroy(cs);
       return RLB_E_COMM;
     }
-    cm->collectives += 2;
+    cm->collectives += everyone ? 2 * G : 2;
   }
   // every rank derives the same recentring point from the same bytes and builds its SoA copies
   for (size_t i = 0; i < cm->local.size(); ++i) {

@@ -37,6 +37,12 @@
 #ifndef RLB_ROLL_LM
 #define RLB_ROLL_LM 0   // keep the 6x6 loops rolled
 #endif
+#ifndef RLB_LOC_CTA_SMEM
+#define RLB_LOC_CTA_SMEM 1  // one query per CTA: stage the f32 copy of the matches in shared memory (else global)
+#endif
+#ifndef RLB_LOC_STREAM
+#define RLB_LOC_STREAM 0    // one query per CTA: the passes read the matches with L1::no_allocate loads
+#endif
 #ifndef RLB_FULL_SLICES
 #define RLB_FULL_SLICES 0  // form the 6 partials in two slices of 3 (smaller body, more instructions)
 #endif
@@ -467,6 +473,19 @@ struct CtaComm {
   double* slab;  // [32][14] residual rows of one chunk of 32 matches
 };
 
+// A pass streams 80 KB of matches that the next pass reads again only after every other resident CTA has
+// streamed its own: letting them allocate in L1 only evicts what does live there - the warps' stack frames
+// (local memory) and the LM samples. RLB_LOC_STREAM = 1 reads them through the non-allocating path.
+__device__ __forceinline__ double ldg_pass(const double* p) {
+#if RLB_LOC_STREAM
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+#else
+  return *p;
+#endif
+}
+
 // ScoreModel fused with GetInliers for ONE model, all four warps (lw = logical warp, 0 = master).
 // Per-point arithmetic is fused_pass's (the reference formulation); warp lw evaluates the 32-match
 // words lw, lw + 4, ... of a tile (two words in flight per lane), the inlier bits of a tile go to
@@ -490,11 +509,11 @@ __device__ __noinline__ int cta_pass(CtaComm* C, int lw, int lane) {
     if (live) {
       const double* X = qp3 + 3 * static_cast<size_t>(i);
       const double* uv = qp2 + 2 * static_cast<size_t>(i);
-      x0 = X[0];
-      x1 = X[1];
-      x2 = X[2];
-      u = uv[0];
-      v = uv[1];
+      x0 = ldg_pass(X);
+      x1 = ldg_pass(X + 1);
+      x2 = ldg_pass(X + 2);
+      u = ldg_pass(uv);
+      v = ldg_pass(uv + 1);
     }
   };
 #pragma unroll 1
@@ -1587,7 +1606,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, RLB_LOC_MINB) localize_kern
 #ifndef RLB_LOC_CTA_MINB
 #define RLB_LOC_CTA_MINB 4
 #endif
+#if RLB_LOC_CTA_SMEM
 constexpr int kCtaSmemPoints = 2048;  // f32 copy of the matches in shared memory: 5 x 2048 x 4 B = 40 KB
+#else
+constexpr int kCtaSmemPoints = 0;     // the f32 copy stays in global memory (L2): shared memory left to L1
+#endif
 
 // One query per CTA: master warp = control flow, all four warps = the passes over the matches.
 __global__ void __launch_bounds__(kWarpsPerCta * 32, RLB_LOC_CTA_MINB) localize_cta_kernel(const LocalizeArgs A) {

@@ -1000,11 +1000,26 @@ __global__ void __launch_bounds__(kInlThreads) inlier_kernel(const DeviceData d,
     a.tile_score[tile] = ts;
     atomicExch(&a.status[tile], pack_status(a.epoch, kFlagAgg, static_cast<unsigned int>(tile_total)));
   }
+  // Every tile this one reads is resident (tickets are handed out in launch order and a tile publishes
+  // before it waits), so the wait is one or two L2 round trips. It is bounded all the same, like mbar_wait in
+  // the sweeps: after ~2 s without the word (a wedged predecessor) the kernel traps instead of hanging the GPU.
   auto wait_word = [&](const unsigned long long* w) -> int {
     unsigned long long word;
-    do {
+    long long t0 = 0;
+    unsigned int spins = 0;
+    for (;;) {
       word = *reinterpret_cast<const volatile unsigned long long*>(w);
-    } while (static_cast<unsigned int>(word >> 34) != a.epoch || ((word >> 32) & 3ull) == 0ull);
+      if (static_cast<unsigned int>(word >> 34) == a.epoch && ((word >> 32) & 3ull) != 0ull) break;
+      if (++spins == 4096u) {  // a few microseconds in: start the clock, then check it every 4096 polls
+        const long long now = clock64();
+        if (t0 == 0) {
+          t0 = now;
+        } else if (now - t0 > 4000000000LL) {
+          __trap();
+        }
+        spins = 0;
+      }
+    }
     return static_cast<int>(word & 0xffffffffull);
   };
   int in_group = 0, before_group = 0;

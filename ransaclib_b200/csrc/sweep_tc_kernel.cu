@@ -1,6 +1,6 @@
 // K x N pose MSAC sweep with the 3x4 projection on the 5th-generation tensor cores.
 //
-// Why: ncu on the FFMA2 sweep (profiles/r01f_ncu_sweep_h8.csv) shows the FMA pipe 78 % busy with
+// Why: ncu on the FFMA2 sweep (profiles/history/r01f_ncu_sweep_h8.csv) shows the FMA pipe 78 % busy with
 // math-pipe throttle as the top stall, and 9 of the 14 FMA-pipe operations of an evaluation are the
 // projection p = R' X' + t' (BASELINE north_star: "tensor cores only if ncu shows the 3x4 projection
 // contraction to be FMA-issue-bound"). Here the projection of 128 hypotheses x 32 points is six

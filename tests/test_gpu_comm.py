@@ -36,7 +36,7 @@ def test_one_rank_communicator_equals_the_scorer(ctx, case, form, precision):
     ref = sc.hypothesize_and_score(samples, THR, precision=prec)
     comm = m.Comm.from_rank(ctx, 1, 0, None) if form == "from_rank" else m.Comm.local(1)
     assert comm.nranks == 1 and comm.num_local == 1 and comm.rank(0) == 0
-    cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f, root=0 if form == "from_rank" else -1)
     out = cs.hypothesize_and_score(samples, THR, precision=prec, want_scores=True)
     # the communicator's scorer is built from the DEVICE copy of the points (rlb_scorer_create_pose_dev):
     # same centre, same repack, so even the f32 scores are the same bits
@@ -140,6 +140,12 @@ def test_two_gpus_one_process(case):
     assert out["best_id"] == ref["best_id"] and out["best_score"] == ref["best_score"]
     assert out["scores"].tolist() == ref["scores"].tolist()
     assert comm.collective_count == 3  # the two point arrays broadcast, one all_gather
+    cs.close()
+    # every process holds the arrays: each GPU uploads half of them, the halves cross NVLink
+    cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f, root=-1)
+    out2 = cs.hypothesize_and_score(samples, THR, want_scores=True)
+    assert out2["best_id"] == ref["best_id"] and out2["scores"].tolist() == ref["scores"].tolist()
+    assert comm.collective_count == 3 + 2 * 2 + 1
     cs.close()
     comm.close()
     sc.close()

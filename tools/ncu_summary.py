@@ -1,6 +1,6 @@
 """Extracts the metrics the roofline discussion uses from an .ncu-rep into a small CSV
 (profiles/ is tracked; gpurun_out/ is scratch). Usage:
-    python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/r01_xxx.csv"""
+    python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/history/r01_xxx.csv"""
 import csv
 import subprocess
 import sys
