@@ -156,6 +156,23 @@ int rlb_get_inliers_dev(rlb_scorer* s, const double* d_model, const double* sq_t
                         const double* sq_thr_score, const double* weights, int32_t* d_idx,
                         void* d_header);
 
+/* rlb_get_inliers_dev WITHOUT any allocation. (No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc - code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it.) Same arguments, same kernel, same results; the pass's scratch (a score and a
+ * status word per tile of 1024 points, ticket counters) lives in a fixed file-scope device array of 66 KB that
+ * every GPU loading the library holds until exit, instead of the context's growable buffers. Neither this call
+ * nor anything it calls uses cudaMalloc, cudaFree or an allocating library routine; the first call on a device
+ * also looks up the array's address (cudaGetSymbolAddress), so make it once before capturing a graph.
+ * Limits: built-in kinds only (RLB_E_KIND for custom functors); a data set of more than RLB_NOALLOC_MAX_POINTS
+ * points (counted with the per-type padding to multiples of 1024) is rejected with RLB_E_ARG and a message.
+ * All calls on one device SHARE the array and it keeps the last call's contents (told apart by an epoch tag;
+ * the counters are cleared on the stream before each launch): calls that overlap on the GPU - other streams,
+ * contexts or host threads - race. Calls on one stream, one after the other, are fine. */
+#define RLB_NOALLOC_MAX_POINTS 4194304
+int rlb_get_inliers_noalloc_dev(rlb_scorer* s, const double* d_model, const double* sq_thr_inl,
+                                const double* sq_thr_score, const double* weights, int32_t* d_idx,
+                                void* d_header);
+
 /* Squared residuals of ONE model on every point of one data type (debug / functor
  * parity tests; EvaluateModelOnPoint itself). err: num_data(type) doubles. */
 int rlb_eval_errors(rlb_scorer* s, int precision, const double* model, int type, double* err);

@@ -540,6 +540,15 @@ class Scorer:
         _capi.check(self._lib.rlb_get_inliers_dev(self._h, C.c_void_p(d_model), _capi.ptr(ti), _capi.ptr(ts),
                                                   _capi.ptr(w), C.c_void_p(d_idx or 0), C.c_void_p(d_header)))
 
+    def get_inliers_noalloc_dev(self, d_model: int, sq_thr_inl, sq_thr_score, weights, d_idx: int, d_header: int):
+        """get_inliers_dev through rlb_get_inliers_noalloc_dev: scratch in a fixed static device array, no
+        allocation on the call path (at most _capi.NOALLOC_MAX_POINTS points; calls must not overlap on the GPU)."""
+        ti = self._thr(sq_thr_inl)
+        ts = None if sq_thr_score is None else self._thr(sq_thr_score)
+        w = None if weights is None else self._thr(weights)
+        _capi.check(self._lib.rlb_get_inliers_noalloc_dev(self._h, C.c_void_p(d_model), _capi.ptr(ti), _capi.ptr(ts),
+                                                          _capi.ptr(w), C.c_void_p(d_idx or 0), C.c_void_p(d_header)))
+
     def hypothesize_and_score(self, samples, sq_thr, weights=None, solver: int = 0, precision=RLB_F64,
                               want_models=True, want_scores=True):
         """Samples up, hypotheses stay on the device. -> dict."""

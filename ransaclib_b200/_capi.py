@@ -29,13 +29,14 @@ SYMBOLS = [
     "rlb_hypothesize_and_score", "rlb_hypothesize_and_score_dev", "rlb_measure_fma_peak", "rlb_sharded_round_dev", "rlb_select_winner_dev", "rlb_ctx_set_timing", "rlb_ctx_kernel_time_ms", "rlb_ctx_last_sweep_plan",
     "rlb_localize_default_options", "rlb_localize_batch", "rlb_localize_batch_dev",
     "rlb_lomsac_default_options", "rlb_line_lomsac_batch", "rlb_line_lomsac_batch_dev", "rlb_scorer_line_lomsac",
-    "rlb_scorer_create_pose_dev",
+    "rlb_scorer_create_pose_dev", "rlb_get_inliers_noalloc_dev",
     "rlb_comm_get_unique_id", "rlb_comm_init_rank", "rlb_comm_create_local", "rlb_comm_destroy", "rlb_comm_nranks",
     "rlb_comm_num_local", "rlb_comm_rank", "rlb_comm_ctx", "rlb_comm_collective_count",
     "rlb_comm_scorer_create_pose", "rlb_comm_scorer_destroy", "rlb_comm_scorer_local",
     "rlb_comm_hypothesize_and_score", "rlb_comm_round_dev", "rlb_comm_get_inliers",
 ]
 COMM_ID_BYTES = 128
+NOALLOC_MAX_POINTS = 4194304
 
 
 class LocalizeOptions(C.Structure):
@@ -118,6 +119,7 @@ def load():
     lib.rlb_line_lomsac_batch_dev.argtypes = [vp, i32, i32, vp, vp, vp, C.POINTER(LocalizeOptions), vp, vp, vp]
     lib.rlb_scorer_line_lomsac.argtypes = [vp, C.POINTER(LocalizeOptions), C.c_uint32, vp, vp, vp]
     lib.rlb_scorer_create_pose_dev.argtypes = [vp, i32, vp, vp, f64, f64, C.POINTER(vp)]
+    lib.rlb_get_inliers_noalloc_dev.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.rlb_comm_get_unique_id.argtypes = [vp]
     lib.rlb_comm_init_rank.argtypes = [vp, i32, i32, vp, C.POINTER(vp)]
     lib.rlb_comm_create_local.argtypes = [i32, vp, C.POINTER(vp)]

@@ -1025,6 +1025,44 @@ int rlb_get_inliers_dev(rlb_scorer* s, const double* d_model, const double* sq_t
   return inliers_dev(s, d_model, sq_thr_inl, sq_thr_score, weights, d_idx, d_header);
 }
 
+// The same pass with its scratch in a fixed file-scope device array (score_kernels.cu) instead of the context's
+// growable buffers: no cudaMalloc / cudaFree / allocating routine on this path, ever. No counterpart in the
+// reference. Calls on one device share the array: do not overlap them.
+int rlb_get_inliers_noalloc_dev(rlb_scorer* s, const double* d_model, const double* sq_thr_inl,
+                                const double* sq_thr_score, const double* weights, int32_t* d_idx,
+                                void* d_header) {
+  int rc = check_scorer(s);
+  if (rc) return rc;
+  rlb_ctx* c = s->ctx;
+  rc = ctx_use(c);
+  if (rc) return rc;
+  if (!d_model || !d_header) return fail(RLB_E_ARG, "d_model and d_header are required");
+  if (!sq_thr_inl) return fail(RLB_E_ARG, "sq_thr_inl is required");
+  const DeviceData& d = s->d;
+  if (d.kind == RLB_KIND_CUSTOM)
+    return fail(RLB_E_KIND, "rlb_get_inliers_noalloc_dev serves the built-in kinds (line, hybrid line, pose)");
+  if (d.npad > rlb::inliers_noalloc_max_points())
+    return fail(RLB_E_ARG,
+                "data set of %d (padded) points exceeds the fixed scratch of rlb_get_inliers_noalloc_dev: at most "
+                "RLB_NOALLOC_MAX_POINTS = %d; use rlb_get_inliers_dev",
+                d.npad, rlb::inliers_noalloc_max_points());
+  InlierArgs a;
+  a.model = d_model;
+  fill_thr(d, sq_thr_inl, weights, a.thr_inl, a.w);
+  double dummy[rlb::kMaxTypes];
+  fill_thr(d, sq_thr_score ? sq_thr_score : sq_thr_inl, weights, a.thr_score, dummy);
+  a.want_score = sq_thr_score ? 1 : 0;
+  a.idx = d_idx;
+  a.tile_score = nullptr;  // filled by the launcher from the device's static scratch
+  a.status = nullptr;
+  a.control = nullptr;
+  a.epoch = 0u;
+  a.header = d_header;
+  RLB_CUDA(rlb::launch_inliers_noalloc(d, a, c->stream, &c->launches_i));
+  account(c);
+  return RLB_OK;
+}
+
 namespace {
 // idx: copy the list there; view: hand out a pointer to the context's own pinned copy instead (valid until the
 // next call on the context). Either, both or none.

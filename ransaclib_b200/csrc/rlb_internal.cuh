@@ -117,6 +117,9 @@ cudaError_t launch_finalize(const DeviceData& d, const SweepArgs& a, double* sco
                             BestRec* best, double* best_model, cudaStream_t st, int* launches);
 cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_t st,
                            int* launches);
+// K = 1 pass whose scratch is a fixed file-scope device array (score_kernels.cu): allocates nothing
+cudaError_t launch_inliers_noalloc(const DeviceData& d, InlierArgs a, cudaStream_t st, int* launches);
+int inliers_noalloc_max_points();
 cudaError_t launch_eval_errors(const DeviceData& d, int precision, const double* model, int type,
                                double* err, cudaStream_t st, int* launches);
 cudaError_t launch_repack(const DeviceData& d, double* soa64, float* soa32, cudaStream_t st,

@@ -1107,6 +1107,61 @@ cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------- K = 1 pass without any allocation
+// rlb_get_inliers_noalloc_dev (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops). The scratch of the ordered
+// compaction - one score and one epoch-tagged status word per tile of 1024 points, one status word per group of
+// 256 tiles, the ticket / done counters - lives in ONE file-scope device array of a fixed, modest size instead
+// of the context's growable buffers: kNoAllocMaxTiles tiles = 4,194,304 padded points, 66 KB, held by every
+// GPU that loads the library until the process exits. Every call on a device shares it, so calls that overlap on
+// the GPU (two streams, two contexts, two host threads) race; the status words keep the last call's contents
+// and are told apart by the epoch tag, the counters are cleared on the stream before every launch.
+constexpr int kNoAllocMaxTiles = 4096;
+struct InlierStaticScratch {
+  double tile_score[kNoAllocMaxTiles];
+  unsigned long long status[kNoAllocMaxTiles + kNoAllocMaxTiles / 256];
+  unsigned int control[4];
+};
+static __device__ __align__(256) unsigned char g_inlier_scratch[sizeof(InlierStaticScratch)];
+
+int inliers_noalloc_max_points() { return kNoAllocMaxTiles * kInlTile; }
+
+// In host code `g_inlier_scratch` is only a stand-in for the symbol: the device address is looked up once per
+// device (with that device current) and remembered; the kernel gets the looked-up pointer.
+cudaError_t launch_inliers_noalloc(const DeviceData& d, InlierArgs a, cudaStream_t st, int* launches) {
+  static InlierStaticScratch* addr[64];
+  static PerDeviceOnce looked_up;
+  static std::atomic<unsigned int> epochs[64];
+  const int dev = PerDeviceOnce::device();
+  if (!looked_up.done(dev)) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_inlier_scratch);
+    if (e != cudaSuccess) return e;
+    if (p == nullptr) return cudaErrorInvalidSymbol;
+    addr[dev] = static_cast<InlierStaticScratch*>(p);
+    looked_up.set(dev);
+  }
+  InlierStaticScratch* sc = addr[dev];
+  const int tiles = d.npad / kInlTile;
+  if (tiles > kNoAllocMaxTiles) return cudaErrorInvalidValue;  // the C ABI checks first and says why
+  // ticket and done counters must start at zero (a memset node on the stream: no allocation)
+  cudaError_t e = cudaMemsetAsync(sc->control, 0, sizeof(sc->control), st);
+  if (e != cudaSuccess) return e;
+  a.tile_score = sc->tile_score;
+  a.status = sc->status;
+  a.control = sc->control;
+  // 30-bit epoch, never 0 (the array starts zeroed: a zero word is "not published")
+  const unsigned int n = epochs[dev].fetch_add(1u, std::memory_order_relaxed);
+  a.epoch = (n % 0x3fffffffu) + 1u;
+  ++*launches;
+  if (d.kind == RLB_KIND_POSE) {
+    inlier_kernel<PoseF><<<tiles, kInlThreads, 0, st>>>(d, a);
+  } else {
+    inlier_kernel<LineF><<<tiles, kInlThreads, 0, st>>>(d, a);
+  }
+  return cudaGetLastError();
+}
+
 // ----------------------------------------------------------- per-point residuals
 template <template <typename> class FT, typename T>
 __global__ void eval_errors_kernel(const DeviceData d, const double* __restrict__ model, int type,
