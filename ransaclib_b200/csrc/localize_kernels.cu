@@ -38,10 +38,12 @@
 #define RLB_ROLL_LM 0   // keep the 6x6 loops rolled
 #endif
 #ifndef RLB_LOC_CTA_SMEM
-#define RLB_LOC_CTA_SMEM 1  // one query per CTA: stage the f32 copy of the matches in shared memory (else global)
+#define RLB_LOC_CTA_SMEM 0  // one query per CTA: 1 = stage the f32 copy of the matches in shared memory. Default 0:
+                            // the sweeps that read it are 2 % of a query, and 4 x 40 KB of shared memory per SM
+                            // leave ~40 KB of L1 for the warps' stack frames (profiles/r02_localize_ab.txt: +7 %)
 #endif
 #ifndef RLB_LOC_STREAM
-#define RLB_LOC_STREAM 0    // one query per CTA: the passes read the matches with L1::no_allocate loads
+#define RLB_LOC_STREAM 1    // one query per CTA: the passes read the matches with L1::no_allocate loads
 #endif
 #ifndef RLB_FULL_SLICES
 #define RLB_FULL_SLICES 0  // form the 6 partials in two slices of 3 (smaller body, more instructions)
