@@ -45,6 +45,11 @@ extern "C" {
 /* arithmetic the K x N sweep runs in. Inlier lists are always collected in f64. */
 #define RLB_F64 0 /* reference-exact semantics, scores within 1e-9 rel */
 #define RLB_F32 1 /* recentred f32 inner sums, f64 outer sums; within 1e-4 rel */
+/* RLB_F64 on pose batches of >= 512 hypotheses classifies every (hypothesis, point) pair in f32 first and
+ * evaluates in f64 only the pairs that could be inliers; a clear outlier adds exactly thr either way
+ * (ransac.h:306-309). Counts are those of the plain f64 sweep, scores agree to 1e-12. RLB_F64_PLAIN evaluates
+ * every pair in f64 (the round-1 kernel; also what RLB_F64 runs for lines and small batches). */
+#define RLB_F64_PLAIN 2
 
 #define RLB_KIND_LINE 0        /* examples/line_estimator */
 #define RLB_KIND_HYBRID_LINE 1 /* examples/hybrid_line_estimator (2 data types) */

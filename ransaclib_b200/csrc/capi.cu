@@ -71,6 +71,8 @@ struct rlb_ctx {
   unsigned int epoch = 0;
   // sweep scratch
   DevBuf models, valid, samples, scores, counts, part_score, part_count, block_best, small;
+  // filtered f64 sweep: {dense ids [k], sparse ids [k], pos [k], counts [4]} and the dense list's accumulators
+  DevBuf tcx_lists, tcx_acc;
   // inlier scratch
   DevBuf one_model, idx, tile_score, status, header;
   // pinned host staging for tiny results
@@ -279,7 +281,10 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
               BestRec* d_best, double* d_best_model) {
   rlb_ctx* c = s->ctx;
   const DeviceData& d = s->d;
-  if (precision != RLB_F64 && precision != RLB_F32) return fail(RLB_E_ARG, "bad precision %d", precision);
+  if (precision != RLB_F64 && precision != RLB_F32 && precision != RLB_F64_PLAIN)
+    return fail(RLB_E_ARG, "bad precision %d", precision);
+  const bool plain64 = (precision == RLB_F64_PLAIN);  // f64 without the f32 pre-classification
+  if (plain64) precision = RLB_F64;
   if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
   if (!thr) return fail(RLB_E_ARG, "sq_thr is required");
   {
@@ -287,7 +292,7 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     if (rc0) return rc0;
   }
 
-  SweepArgs a;
+  SweepArgs a = {};
   a.k = k;
   a.models = d_models;
   a.valid = d_valid;
@@ -380,14 +385,26 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   // operands. Its unit along the point axis is a 32-point tile. Measured 2.40e12 evals/s with counts and
   // 2.51e12 without on C5 against 1.90e12 for the FFMA2 sweep (profiles/r01r_*), so it is planned with the
   // same fill / balance score and wins unless the batch is too small to pay for packing the tiles.
+  //
+  // Filtered f64 sweep (pose, f64 results; variant 11): the same tensor-core front end classifies every pair in
+  // f32 and only the pairs that could be inliers are evaluated in f64 (sweep_tc_kernel.cu). Scores within 1e-12
+  // of the plain f64 sweep, counts identical; 6.4e11 -> 1.5e12 evals/s on C5. RLB_F64_FILTER=0 keeps the plain
+  // f64 sweep (A/B, and batches of nothing but good hypotheses, where every second pair needs f64 anyway).
+  static const bool f64_filter = [] {
+    const char* v = getenv("RLB_F64_FILTER");
+    return !(v && atoi(v) == 0);
+  }();
   bool use_tc = false;
-  if (d.kind == RLB_KIND_POSE && precision == RLB_F32 && (forced_variant == 9 || (forced_variant < 0 && k >= 512))) {
+  const bool tc_f32 = precision == RLB_F32 && (forced_variant == 9 || (forced_variant < 0 && k >= 512));
+  const bool tc_f64 = precision == RLB_F64 && !plain64 && a.thr[0] > 0.0 &&
+                      (forced_variant == 11 || (forced_variant < 0 && f64_filter && k >= 512));
+  if (d.kind == RLB_KIND_POSE && (tc_f32 || tc_f64)) {
     const int total_tiles = d.npad / rlb::tc_tile_points();
-    const int slots = c->sms * rlb::tc_resident_ctas();
+    const int slots = c->sms * (tc_f64 ? rlb::tcx_resident_ctas() : rlb::tc_resident_ctas());
     const int hpc = rlb::tc_hyps_per_cta();
     const int k_tiles = (k + hpc - 1) / hpc;
     const double tile_use = static_cast<double>(k) / (static_cast<double>(k_tiles) * hpc);
-    const double speed = (d_counts != nullptr) ? 1.26 : 1.32;
+    const double speed = tc_f64 ? 2.3 : ((d_counts != nullptr) ? 1.26 : 1.32);
     double best = -1.0;
     int tc_splits = 1, tc_tps = total_tiles;
     // Up to 64 splits, more (up to 256) while the grid would otherwise stay below ~8 waves of resident CTAs: a
@@ -409,9 +426,9 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
         tc_tps = tp;
       }
     }
-    if (forced_variant == 9 || best > best_score) {
+    if (forced_variant == 9 || forced_variant == 11 || best > best_score) {
       use_tc = true;
-      a.variant = 9;
+      a.variant = tc_f64 ? 11 : 9;
       a.n_splits = splits = tc_splits;
       a.stages_per_split = tc_tps;
     }
@@ -451,6 +468,67 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     std::string err;
     if (!rlb::launch_custom_sweep(s->custom, d, a, custom_pps, c->stream, &c->launches_i, &err))
       return fail(RLB_E_CUDA, "custom sweep: %s", err.c_str());
+  } else if (use_tc && a.variant == 11) {
+    // Filtered f64 sweep: prepass over a strided sample of the tiles -> dense / sparse hypothesis lists -> the
+    // plain f64 sweep over the dense list, the tensor-core front end + f64 back end over the sparse one. All on
+    // this stream; the list lengths stay on the device (grids are sized for k, CTAs beyond a list return at once).
+    const float* tiles = static_cast<const float*>(s->tc_tiles);
+    const int tile_pts = rlb::tc_tile_points();
+    const int total_tiles = d.npad / tile_pts;
+    const int hpc = rlb::tc_hyps_per_cta();
+    const int k_tiles = (k + hpc - 1) / hpc;
+    const int slots = c->sms * rlb::tcx_resident_ctas();
+    RLB_CUDA(c->tcx_lists.ensure((static_cast<size_t>(k) * 3 + 4) * sizeof(int32_t)));
+    RLB_CUDA(c->tcx_acc.ensure(static_cast<size_t>(k) * 12));
+    int32_t* lists = c->tcx_lists.as<int32_t>();
+    int32_t* pos = lists + 2 * static_cast<size_t>(k);
+    int32_t* list_counts = pos + k;
+    unsigned long long* acc_q = c->tcx_acc.as<unsigned long long>();
+    unsigned int* acc_c = reinterpret_cast<unsigned int*>(acc_q + k);
+    // 1. prepass: every 64th tile (at least 8), cut into as many splits as fill the device
+    const int n_sample = std::min(total_tiles, std::max(8, total_tiles / 64));
+    const int stride = std::max(1, total_tiles / n_sample);
+    SweepArgs pa = a;
+    pa.tile_stride = stride;
+    pa.n_splits = std::max(1, std::min(n_sample, (slots + k_tiles - 1) / k_tiles));
+    pa.stages_per_split = (n_sample + pa.n_splits - 1) / pa.n_splits;
+    pa.n_splits = (n_sample + pa.stages_per_split - 1) / pa.stages_per_split;
+    RLB_CUDA(c->part_count.ensure(static_cast<size_t>(std::max(splits, pa.n_splits)) * k * sizeof(int32_t)));
+    pa.part_count = c->part_count.as<int32_t>();
+    a.part_count = pa.part_count;
+    RLB_CUDA(rlb::launch_sweep_tcx_prepass(d, pa, tiles, c->stream, &c->launches_i));
+    // 2. partition
+    const long long sampled = std::min<long long>(d.n[0], static_cast<long long>(n_sample) * tile_pts);
+    RLB_CUDA(rlb::launch_tcx_partition(pa.part_count, pa.n_splits, k, static_cast<int>(sampled), lists, pos,
+                                       list_counts, c->stream, &c->launches_i));
+    RLB_CUDA(cudaMemsetAsync(acc_q, 0, static_cast<size_t>(k) * 12, c->stream));
+    // 3. dense list: plain f64 sweep (H = 4), up to 256 splits so that a short list still fills the device
+    {
+      SweepArgs da = a;
+      da.ids = lists;
+      da.k_dev = list_counts;
+      da.acc_q = acc_q;
+      da.acc_c = acc_c;
+      da.variant = 7;
+      da.n_splits = std::max(1, std::min(total_stages, 256));
+      da.stages_per_split = (total_stages + da.n_splits - 1) / da.n_splits;
+      da.n_splits = (total_stages + da.stages_per_split - 1) / da.stages_per_split;
+      // scores are below thr * w * n: the fixed-point sum of all splits stays below 2^62
+      int e2 = 0;
+      frexp(a.thr[0] * std::max(a.w[0], 1.0) * static_cast<double>(std::max(d.n[0], 1)), &e2);
+      da.acc_shift = 61 - e2;
+      a.acc_shift = da.acc_shift;
+      RLB_CUDA(rlb::launch_sweep(d, da, RLB_F64, c->stream, &c->launches_i));
+    }
+    // 4. sparse list
+    a.ids = lists + k;
+    a.k_dev = list_counts + 1;
+    RLB_CUDA(rlb::launch_sweep_tcx(d, a, tiles, c->stream, &c->launches_i));
+    a.ids = nullptr;  // finalize walks all k hypotheses
+    a.k_dev = nullptr;
+    a.pos = pos;
+    a.acc_q = acc_q;
+    a.acc_c = acc_c;
   } else if (use_tc) {
     RLB_CUDA(rlb::launch_sweep_tc(d, a, static_cast<const float*>(s->tc_tiles), c->stream, &c->launches_i));
   } else {
@@ -601,7 +679,7 @@ int rlb_ctx_destroy(rlb_ctx* c) {
   cudaStreamSynchronize(c->stream);
   DevBuf* bufs[] = {&c->models, &c->valid, &c->samples, &c->scores, &c->counts, &c->part_score,
                     &c->part_count, &c->block_best, &c->small, &c->one_model, &c->idx,
-                    &c->tile_score, &c->status, &c->header};
+                    &c->tile_score, &c->status, &c->header, &c->tcx_lists, &c->tcx_acc};
   for (DevBuf* b : bufs) b->release();
   pool_drain(c);
   if (c->h_small) cudaFreeHost(c->h_small);

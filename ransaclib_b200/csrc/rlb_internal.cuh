@@ -79,6 +79,17 @@ struct SweepArgs {
   double* record;              // optional {score, global id (as f64), model...} of the local winner
   long long id_offset;         // first global hypothesis id of this shard
   int want_counts;             // 0: the caller passed no counts array, part_count may be left unwritten
+  // Filtered f64 sweep (sweep_tc_kernel.cu): a launch over a device-side LIST of hypotheses
+  const int32_t* ids;          // hypothesis kk of the launch is model ids[kk] (nullptr: kk itself)
+  const int32_t* k_dev;        // length of the list on the device, <= k (nullptr: k); CTAs beyond it return at once
+  int tile_stride;             // prepass: distance between the sampled tiles
+  // ... whose results are added to per-hypothesis integers instead of [splits][k] partials (dense list)
+  unsigned long long* acc_q;   // score * 2^acc_shift per hypothesis of the list, zero before the launch
+  unsigned int* acc_c;         // inlier count
+  int acc_shift;
+  // finalize: where hypothesis k's result is. pos[k] >= 0: part_score / part_count[.][pos[k]];
+  // pos[k] < 0: acc_q / acc_c[~pos[k]]
+  const int32_t* pos;
 };
 
 struct BestRec {
@@ -132,6 +143,14 @@ cudaError_t launch_fma_peak(int dtype, int sms, float* ms, double* flops, cudaSt
 cudaError_t launch_tc_pack(const DeviceData& d, float* tiles, cudaStream_t st, int* launches);
 cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
                             int* launches);
+// filtered f64 sweep: f32 classification on the tensor cores, f64 only for the pairs that could be inliers
+cudaError_t launch_sweep_tcx(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
+                             int* launches);
+cudaError_t launch_sweep_tcx_prepass(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
+                                     int* launches);
+cudaError_t launch_tcx_partition(const int32_t* flagged, int n_splits, int k, int sample_points, int32_t* lists,
+                                 int32_t* pos, int32_t* counts, cudaStream_t st, int* launches);
+int tcx_resident_ctas();
 int tc_tile_points();
 size_t tc_tiles_bytes(int npad);
 int tc_hyps_per_cta();

@@ -320,6 +320,10 @@ __global__ void __launch_bounds__(kSweepThreads)
   const int kbase = blockIdx.x * (kSweepThreads * H);
   const int split = blockIdx.y;
   const T* soa = soa_of<T>(d);
+  // a launch over a device-side list of hypotheses (the dense list of the filtered f64 sweep): the list can be
+  // shorter than the grid was sized for
+  const int k_count = (a.k_dev != nullptr) ? *a.k_dev : a.k;
+  if (kbase >= k_count) return;
 
   const int total_stages = d.npad / kStage;
   const int s_begin = split * a.stages_per_split;
@@ -330,8 +334,9 @@ __global__ void __launch_bounds__(kSweepThreads)
 #pragma unroll
   for (int h = 0; h < H; ++h) {
     const int k = kbase + h * kSweepThreads + tid;
-    if (k < a.k) {
-      F::load(a.models + static_cast<size_t>(k) * F::MD, d, m[h]);
+    if (k < k_count) {
+      const int id = (a.ids != nullptr) ? a.ids[k] : k;
+      F::load(a.models + static_cast<size_t>(id) * F::MD, d, m[h]);
     } else {
       F::zero(m[h]);
     }
@@ -421,9 +426,22 @@ __global__ void __launch_bounds__(kSweepThreads)
 #pragma unroll
   for (int h = 0; h < H; ++h) {
     const int k = kbase + h * kSweepThreads + tid;
-    if (k < a.k) {
-      a.part_score[static_cast<size_t>(split) * a.k + k] = dacc[h];
-      a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt[h];
+    if (k < k_count) {
+      if (a.acc_q != nullptr) {
+        // Fixed-point, so that the sum over the splits does not depend on the order of arrival: this CTA's
+        // (deterministic) partial is rounded to 2^-acc_shift and added as an integer. A NaN partial (std::min
+        // propagates NaN, ransac.h:308) sets the top bit of the count word instead.
+        const double v = dacc[h];
+        if (v == v) {
+          atomicAdd(a.acc_q + k, static_cast<unsigned long long>(__double2ll_rn(ldexp(v, a.acc_shift))));
+          atomicAdd(a.acc_c + k, static_cast<unsigned int>(dcnt[h]));
+        } else {
+          atomicOr(a.acc_c + k, 0x80000000u);
+        }
+      } else {
+        a.part_score[static_cast<size_t>(split) * a.k + k] = dacc[h];
+        a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt[h];
+      }
     }
   }
 }
@@ -730,16 +748,25 @@ __global__ void __launch_bounds__(256)
   if (k < a.k) {
     double sum = 0.0;
     int cnt = 0;
+    // filtered f64 sweep: hypothesis k's result is at position pos[k] of the sparse list's partials, or (negative)
+    // in the dense list's fixed-point accumulators
+    const int kp = (a.pos != nullptr) ? a.pos[k] : k;
+    if (kp < 0) {
+      const unsigned int c = a.acc_c[~kp];  // top bit: some partial was NaN
+      sum = (c >> 31) ? __longlong_as_double(0x7ff8000000000000LL)
+                      : ldexp(static_cast<double>(a.acc_q[~kp]), -a.acc_shift);
+      cnt = static_cast<int>(c & 0x7fffffffu);
+    }
     // fixed order: deterministic. Eight loads in flight, added in split order (a small batch over many
     // points has up to 256 splits and one thread per hypothesis walking them).
-    int sp = 0;
+    int sp = (kp < 0) ? a.n_splits : 0;
     for (; sp + 8 <= a.n_splits; sp += 8) {
       double v[8];
       int c[8];
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
-        v[u] = a.part_score[static_cast<size_t>(sp + u) * a.k + k];
-        c[u] = counts ? a.part_count[static_cast<size_t>(sp + u) * a.k + k] : 0;
+        v[u] = a.part_score[static_cast<size_t>(sp + u) * a.k + kp];
+        c[u] = counts ? a.part_count[static_cast<size_t>(sp + u) * a.k + kp] : 0;
       }
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
@@ -748,8 +775,8 @@ __global__ void __launch_bounds__(256)
       }
     }
     for (; sp < a.n_splits; ++sp) {
-      sum += a.part_score[static_cast<size_t>(sp) * a.k + k];
-      if (counts) cnt += a.part_count[static_cast<size_t>(sp) * a.k + k];
+      sum += a.part_score[static_cast<size_t>(sp) * a.k + kp];
+      if (counts) cnt += a.part_count[static_cast<size_t>(sp) * a.k + kp];
     }
     const bool is_valid = (a.valid == nullptr) || (a.valid[k] != 0);
     bool finite = true;

@@ -177,14 +177,23 @@ __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__flo
 // ---------------------------------------------------------------- point pre-pack
 // tiles: [npad / 32][kTcTileFloats]; inputs are the recentred f32 stage values (the same numbers the
 // FFMA2 sweep reads), padding = X 0, -u/-v NaN.
-__global__ void tc_pack_kernel(const DeviceData d, float* __restrict__ tiles) {
+//
+// bounds (two floats behind the tiles, zeroed before the launch): [0] = max |X'| (Euclidean norm of a recentred
+// point), [1] = max(|u|, |v|) over the live points. The filtered f64 sweep derives its per-hypothesis error
+// bound of the f32 classification from them.
+__global__ void tc_pack_kernel(const DeviceData d, float* __restrict__ tiles, unsigned int* __restrict__ bounds) {
   const int total = d.npad;
+  float rmax = 0.0f, umax = 0.0f;
   for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
     const float x = d.soa32[0 * static_cast<size_t>(total) + g];
     const float y = d.soa32[1 * static_cast<size_t>(total) + g];
     const float z = d.soa32[2 * static_cast<size_t>(total) + g];
     const float nu = d.soa32[3 * static_cast<size_t>(total) + g];
     const float nv = d.soa32[4 * static_cast<size_t>(total) + g];
+    if (g < d.n[0]) {
+      rmax = fmaxf(rmax, sqrtf(x * x + y * y + z * z));
+      umax = fmaxf(umax, fmaxf(fabsf(nu), fabsf(nv)));
+    }
     const float xh = tf32_hi(x), yh = tf32_hi(y), zh = tf32_hi(z);
     const float xl = x - xh, yl = y - yh, zl = z - zh;
     float* t = tiles + static_cast<size_t>(g / kTcTile) * kTcTileFloats;
@@ -199,12 +208,28 @@ __global__ void tc_pack_kernel(const DeviceData d, float* __restrict__ tiles) {
     t[512 + n] = nu;
     t[512 + 32 + n] = nv;
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    rmax = fmaxf(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+    umax = fmaxf(umax, __shfl_xor_sync(0xffffffffu, umax, o));
+  }
+  if ((threadIdx.x & 31) == 0) {  // non-negative floats order like their bit patterns; NaN / inf stay what they are
+    atomicMax(bounds + 0, __float_as_uint(rmax));
+    atomicMax(bounds + 1, __float_as_uint(umax));
+  }
+}
+
+static float* tc_bounds_of(float* tiles, int npad) {
+  return tiles + static_cast<size_t>(npad / kTcTile) * kTcTileFloats;
 }
 
 cudaError_t launch_tc_pack(const DeviceData& d, float* tiles, cudaStream_t st, int* launches) {
   ++*launches;
   const int blocks = max(1, min(2048, (d.npad + 255) / 256));
-  tc_pack_kernel<<<blocks, 256, 0, st>>>(d, tiles);
+  unsigned int* bounds = reinterpret_cast<unsigned int*>(tc_bounds_of(tiles, d.npad));
+  cudaError_t e = cudaMemsetAsync(bounds, 0, 256, st);
+  if (e != cudaSuccess) return e;
+  tc_pack_kernel<<<blocks, 256, 0, st>>>(d, tiles, bounds);
   return cudaGetLastError();
 }
 
@@ -414,8 +439,483 @@ __global__ void __launch_bounds__(kTcThreads, 4)
   }
 }
 
+// ------------------------------------------------ filtered f64 sweep ("f64 scores at f32 speed")
+// The reference's ScoreModel (ransac.h:295-312) adds min(e, thr) per point: a point whose squared error is
+// clearly above the threshold contributes exactly thr, whatever its error is. This kernel classifies every
+// (hypothesis, point) pair with the tensor-core f32 front end above and evaluates in f64 only the pairs that
+// could be inliers:
+//     near  <=>  e32 < thr_hi(k)   or   |pz32| < pzmin(k)
+// with a per-hypothesis band derived from an error bound of the f32 evaluation (below), so that every pair
+// NOT flagged has e64 >= thr (or lies behind the camera) and adds thr. The flagged pairs go through
+// PoseF<double>::eval's arithmetic (score_kernels.cu) on the recentred f64 copy: inlier decisions - hence
+// counts - are those of the plain f64 sweep, bit for bit.
+//
+// Work distribution: the front end leaves one 32-bit mask per thread (hypothesis) and tile (32 points). A good
+// hypothesis has half of its points flagged, a bad one none, so lane-local processing would serialise; the
+// warp transposes its 32 x 32 bit matrix (5 shuffle steps) and lane j takes POINT j of the tile against the
+// flagged hypotheses of the warp, whose f64 coefficients sit in shared memory. Sums are accumulated as
+// fixed-point integers (e * 2^45 / thr, split in two 32-bit halves) with shared-memory reductions, so they do
+// not depend on the order of arrival: results are bit-reproducible like everything else here, and differ from
+// a sequential f64 sum by <= 2^-46 thr per inlier (relative 1e-14 on C5; the promise is 1e-9).
+//
+// Error bound of the front end, per hypothesis k: with Rmax = max |X'|, B_i = |row_i| Rmax + |t_i| bounds every
+// partial product sum of row i, and the TF32x2 split + f32 accumulation keep |p32_i - p64_i| <= eta B_i with
+// eta = 2^-19 (8x the 2^-22 per-term figure above). For pz >= pzmin = B_z / 64 the projected coordinate is off by
+// <= 2^-13 (B_xy / B_z + |proj|), and |proj| <= U = umax + sqrt(thr) + 1 for any point that could be an inlier
+// (points projected farther out have e64 > thr as long as the bound stays below 1 px, which is checked):
+//     delta = 2^-13 (rho + U) + 2^-19 U      (the second term: rsqrt^2, the stored -u / -v, the final FMAs)
+//     thr_hi = (sqrt(thr) + 1.5 delta)^2.
+// A hypothesis whose bound is useless (delta >= 0.5 px) has thr_hi = +inf: everything in front of the camera is
+// evaluated in f64 (correct, slow). Invalid hypotheses (valid[k] == 0) and non-finite models are never flagged:
+// finalize_kernel overrides their score (DBL_MAX / NaN) as for every other sweep.
+constexpr int kTcxCopies = 4;        // replicas of every accumulator (lane & 3): same-address reductions 4x rarer
+constexpr int kTcxFlush = 16;        // tiles between accumulator drains: 16 * 8 entries * 2^23 < 2^32 per replica
+constexpr int kTcxHalfBits = 23;     // q = e * 2^45 / thr < 2^45: low 23 bits + high 22 bits
+
+struct TcxSmem {
+  float ring[kTcRing][kTcTileFloats];           // f32 operand tiles
+  double pts[kTcRing][5][kTcTile];              // the same points, recentred f64 channels X Y Z u v
+  double coef[12][kTcThreads];                  // PoseF<double>::Model of every hypothesis of the CTA
+  uint32_t acc[3][kTcThreads][kTcxCopies];      // lo, hi, count
+  uint32_t nanf[kTcThreads];
+  uint64_t full[kTcRing];
+  uint64_t mma_done;
+  uint32_t tmem_base;
+};
+
+// The reciprocal of the f64 sweep (score_kernels.cu: rcp_f64_sweep) - keep the two in step.
+__device__ __forceinline__ double rcp_f64_sweep_tc(double x) {
+  double r0;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r0) : "d"(x));
+  const double e = fma(-x, r0, 1.0);
+  const double r = fma(fma(e, e, e), r0, r0);
+  return ((__double2hiint(x) & 0x7ff00000) == 0) ? r0 : r;
+}
+
+// bit j of lane h  ->  bit h of lane j
+__device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int s = 0; s < 5; ++s) {
+    const int j = 16 >> s;
+    const uint32_t m = (s == 0) ? 0x0000ffffu : (s == 1) ? 0x00ff00ffu : (s == 2) ? 0x0f0f0f0fu
+                     : (s == 3) ? 0x33333333u : 0x55555555u;
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+    x = (lane & j) ? (((y & ~m) >> j) | (x & ~m)) : ((x & m) | ((y & m) << j));
+  }
+  return x;
+}
+
+// mask |= bit when the pair could be an inlier: e < thr_hi or |pz| < pzmin (NaN compares false).
+// (bit is a constant after unrolling: the OR becomes a LOP3 with an immediate)
+__device__ __forceinline__ void near_test(float e, float pz, float thr_hi, float pzmin, uint32_t bit, uint32_t& mask) {
+  asm("{\n\t.reg .pred p;\n\t.reg .f32 a;\n\tabs.f32 a, %2;\n\tsetp.lt.f32 p, %1, %3;\n\t"
+      "setp.lt.or.f32 p, a, %4, p;\n\t@p or.b32 %0, %0, %5;\n\t}"
+      : "+r"(mask)
+      : "f"(e), "f"(pz), "f"(thr_hi), "f"(pzmin), "r"(bit));
+}
+
+// PREPASS = true: the front end alone over a strided sample of the tiles; part_count[split][k] = number of
+// flagged pairs of hypothesis k in this split's sample (the partition kernel turns that into the dense / sparse
+// hypothesis lists). PREPASS = false: the hypotheses a.ids[0 .. *a.k_dev) over all tiles, front end + back end,
+// partial sums to part_score / part_count[split][kk] in the compact index space.
+template <bool PREPASS>
+__global__ void __launch_bounds__(kTcThreads, 4)
+    sweep_pose_tcx_kernel(const DeviceData d, const SweepArgs a, const float* __restrict__ tiles,
+                          const float* __restrict__ bounds) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  TcxSmem& S = *reinterpret_cast<TcxSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int k_count = (a.k_dev != nullptr) ? *a.k_dev : a.k;
+  if (static_cast<int>(blockIdx.x) * kTcThreads >= k_count) return;  // the list is shorter than its capacity
+  const int kk = blockIdx.x * kTcThreads + tid;
+  const int split = blockIdx.y;
+  const int n_live = d.n[0];
+
+  // tiles of this CTA: t_begin + it * t_step, it < ntiles
+  const int total_tiles = d.npad / kTcTile;
+  const int t_step = PREPASS ? a.tile_stride : 1;
+  const int t_begin = split * a.stages_per_split * t_step;
+  const int ntiles = PREPASS ? max(0, min(a.stages_per_split, (total_tiles - t_begin + t_step - 1) / t_step))
+                             : max(0, min(total_tiles, t_begin + a.stages_per_split) - t_begin);
+
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)),
+                 "r"(static_cast<uint32_t>(kTcCols))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 32) {
+#pragma unroll
+    for (int s = 0; s < kTcRing; ++s) mbar_init(&S.full[s], 1);
+    mbar_init(&S.mma_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (!PREPASS) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int cpy = 0; cpy < kTcxCopies; ++cpy) S.acc[i][tid][cpy] = 0u;
+    S.nanf[tid] = 0u;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = S.tmem_base;
+  const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+
+  const double thr64 = a.thr[0];
+  float thr_hi = -1.0f, pzmin = 0.0f;  // never flagged
+  {
+    float r[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float t[3] = {0.f, 0.f, 1.f};
+    double c64[12] = {0., 0., 0., 0., 0., 0., 0., 0., 0., 0., 0., 1.};
+    if (kk < k_count) {
+      const int k = (a.ids != nullptr) ? a.ids[kk] : kk;
+      const double* m = a.models + static_cast<size_t>(k) * 12;
+      const double dc[3] = {d.centre[0] - m[9], d.centre[1] - m[10], d.centre[2] - m[11]};
+      const double sc[3] = {d.fx, d.fy, 1.0};
+      bool finite = true;
+      double B[3];
+#pragma unroll
+      for (int row = 0; row < 3; ++row) {
+        const double r0 = m[row], r1 = m[row + 3], r2 = m[row + 6];
+        const double tt = r0 * dc[0] + r1 * dc[1] + r2 * dc[2];  // PoseF<double>::load, operation for operation
+        c64[3 * row + 0] = r0 * sc[row];
+        c64[3 * row + 1] = r1 * sc[row];
+        c64[3 * row + 2] = r2 * sc[row];
+        c64[9 + row] = tt * sc[row];
+        r[3 * row + 0] = static_cast<float>(r0 * sc[row]);
+        r[3 * row + 1] = static_cast<float>(r1 * sc[row]);
+        r[3 * row + 2] = static_cast<float>(r2 * sc[row]);
+        t[row] = static_cast<float>((r0 * dc[0] + r1 * dc[1] + r2 * dc[2]) * sc[row]);
+        const double nr = sqrt(c64[3 * row] * c64[3 * row] + c64[3 * row + 1] * c64[3 * row + 1] +
+                               c64[3 * row + 2] * c64[3 * row + 2]);
+        B[row] = nr * static_cast<double>(bounds[0]) + fabs(c64[9 + row]);
+        finite = finite && (B[row] - B[row] == 0.0);
+      }
+      const bool is_valid = (a.valid == nullptr) || (a.valid[k] != 0);
+      if (is_valid && finite && B[2] > 0.0 && thr64 > 0.0) {
+        const double rt = sqrt(thr64);
+        const double U = static_cast<double>(bounds[1]) + rt + 1.0;
+        const double rho = fmax(B[0], B[1]) / B[2];
+        const double delta = (rho + U) * (1.0 / 8192.0) + U * (1.0 / 524288.0);
+        const double hi = (rt + 1.5 * delta) * (rt + 1.5 * delta);
+        thr_hi = (delta < 0.5) ? static_cast<float>(hi) * 1.000001f : __int_as_float(0x7f800000);
+        pzmin = static_cast<float>(B[2] * (1.0 / 64.0)) * 1.000001f;
+      }
+    }
+    if (!PREPASS) {
+#pragma unroll
+      for (int i = 0; i < 12; ++i) S.coef[i][tid] = c64[i];
+    }
+#pragma unroll
+    for (int mat = 0; mat < 3; ++mat) {
+      const float v[4] = {r[3 * mat], r[3 * mat + 1], r[3 * mat + 2], t[mat]};
+      float hl[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        hl[j] = tf32_hi(v[j]);
+        hl[4 + j] = v[j] - hl[j];
+      }
+      tmem_st8(lane_addr + 8 * mat, hl);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  const double* soa64 = d.soa64;
+  const size_t npad = static_cast<size_t>(d.npad);
+  auto issue_tma = [&](int it) {
+    const int slot = it % kTcRing;
+    const size_t tile = static_cast<size_t>(t_begin + it * t_step);
+    mbar_expect_tx(&S.full[slot], kTcTileBytes + (PREPASS ? 0 : 5 * kTcTile * 8));
+    tma_load_1d(S.ring[slot], tiles + tile * kTcTileFloats, kTcTileBytes, &S.full[slot]);
+    if (!PREPASS) {
+#pragma unroll
+      for (int ch = 0; ch < 5; ++ch)
+        tma_load_1d(S.pts[slot][ch], soa64 + ch * npad + tile * kTcTile, kTcTile * 8, &S.full[slot]);
+    }
+  };
+  if (tid == 0) {
+    for (int it = 0; it < kTcRing && it < ntiles; ++it) issue_tma(it);
+  }
+  __syncwarp();
+
+  const double scale = 35184372088832.0 / thr64;  // 2^45 / thr
+  unsigned long long qsum = 0ull;
+  int cnt = 0;
+
+  // warp 0: the six MMAs of tile `jt` (its operands have landed) and their commit
+  auto issue_mma = [&](int jt) {
+    const int sl = jt % kTcRing;
+    mbar_wait(&S.full[sl], (jt / kTcRing) & 1);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    if (elect_one()) {
+      const uint32_t b_addr = smem_u32(S.ring[sl]);
+#pragma unroll
+      for (int kx = 0; kx < 2; ++kx) {
+        const uint64_t db = umma_desc(b_addr + kx * 2 * 512, 512, 128);
+#pragma unroll
+        for (int mat = 0; mat < 3; ++mat) umma_tf32_ts(tmem + 32 + mat * kTcTile, tmem + 8 * mat, db, kx);
+      }
+      umma_commit(&S.mma_done);
+    }
+    __syncwarp();
+  };
+  if (warp == 0 && ntiles > 0) issue_mma(0);
+
+  // Per tile: f32 front end (TMEM read-back -> mask), barrier, the NEXT tile's MMAs are issued, and the f64 back
+  // end of this tile runs while the tensor core works. The back end needs the tile's f64 points, not TMEM: the
+  // ring slot of tile it is refilled one iteration later than in the plain tensor-core sweep.
+  for (int it = 0; it < ntiles; ++it) {
+    const int slot = it % kTcRing;
+    mbar_wait(&S.mma_done, it & 1);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    const float* nu = S.ring[slot] + 512;
+    const float* nv = nu + 32;
+    uint32_t mask = 0u;
+    float px[2][8], py[2][8], pz[2][8];
+    tmem_ld8(lane_addr + 32 + 0 * kTcTile, px[0]);
+    tmem_ld8(lane_addr + 32 + 1 * kTcTile, py[0]);
+    tmem_ld8(lane_addr + 32 + 2 * kTcTile, pz[0]);
+    tmem_wait_ld8x3(px[0], py[0], pz[0]);
+#pragma unroll
+    for (int qd = 0; qd < 4; ++qd) {
+      const int cur = qd & 1, nxt = cur ^ 1;
+      if (qd < 3) {
+        tmem_ld8(lane_addr + 32 + 0 * kTcTile + 8 * (qd + 1), px[nxt]);
+        tmem_ld8(lane_addr + 32 + 1 * kTcTile + 8 * (qd + 1), py[nxt]);
+        tmem_ld8(lane_addr + 32 + 2 * kTcTile + 8 * (qd + 1), pz[nxt]);
+      }
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const ulonglong2 u4 = *reinterpret_cast<const ulonglong2*>(nu + 8 * qd + 4 * q);
+        const ulonglong2 v4 = *reinterpret_cast<const ulonglong2*>(nv + 8 * qd + 4 * q);
+#pragma unroll
+        for (int pr = 0; pr < 2; ++pr) {
+          const int j = 4 * q + 2 * pr;
+          const u64 rs = pack2(rsq_approx(pz[cur][j]), rsq_approx(pz[cur][j + 1]));
+          const u64 inv = fmul2(rs, rs);
+          const u64 du = ffma2(pack2(px[cur][j], px[cur][j + 1]), inv, pr ? u4.y : u4.x);
+          const u64 dv = ffma2(pack2(py[cur][j], py[cur][j + 1]), inv, pr ? v4.y : v4.x);
+          const u64 e2 = ffma2(du, du, fmul2(dv, dv));
+          float ea, eb;
+          unpack2(e2, ea, eb);
+          near_test(ea, pz[cur][j], thr_hi, pzmin, 1u << (8 * qd + j), mask);
+          near_test(eb, pz[cur][j + 1], thr_hi, pzmin, 1u << (8 * qd + j + 1), mask);
+        }
+      }
+      if (qd < 3) tmem_wait_ld8x3(px[nxt], py[nxt], pz[nxt]);
+    }
+    // padding is never an inlier (its f64 channels are zeros)
+    const int nl = n_live - (t_begin + it * t_step) * kTcTile;
+    if (nl < kTcTile) mask &= (nl <= 0) ? 0u : ((1u << nl) - 1u);
+
+    // everyone has read its accumulators (and finished the back end of the previous tile)
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+      if (it + 1 < ntiles) issue_mma(it + 1);
+      if (it >= 1 && it - 1 + kTcRing < ntiles) {
+        if (elect_one()) issue_tma(it - 1 + kTcRing);
+        __syncwarp();
+      }
+    }
+    if (PREPASS) {
+      cnt += __popc(mask);
+      continue;
+    }
+
+    // ---- f64 back end of this tile (the tensor core is working on the next one) ----
+    // The hypotheses of this launch have FEW flagged pairs (the dense ones went to the plain f64 sweep), spread
+    // over hypotheses and points: the warp transposes its 32 x 32 bit matrix and lane j takes POINT j of the
+    // tile against the flagged hypotheses of the warp.
+    if (__any_sync(0xffffffffu, mask != 0u)) {
+      uint32_t todo = transpose32(mask, lane);  // bit h: hypothesis warp * 32 + h against MY point of the tile
+      const double X = S.pts[slot][0][lane], Y = S.pts[slot][1][lane], Z = S.pts[slot][2][lane];
+      const double U = S.pts[slot][3][lane], V = S.pts[slot][4][lane];
+      const int cpy = lane & (kTcxCopies - 1);
+      while (todo) {
+        const int hh = warp * 32 + (__ffs(todo) - 1);
+        todo &= todo - 1u;
+        // PoseF<double>::eval (score_kernels.cu), operation for operation
+        const double pz64 = fma(S.coef[6][hh], X, fma(S.coef[7][hh], Y, fma(S.coef[8][hh], Z, S.coef[11][hh])));
+        const double px64 = fma(S.coef[0][hh], X, fma(S.coef[1][hh], Y, fma(S.coef[2][hh], Z, S.coef[9][hh])));
+        const double py64 = fma(S.coef[3][hh], X, fma(S.coef[4][hh], Y, fma(S.coef[5][hh], Z, S.coef[10][hh])));
+        const double inv = rcp_f64_sweep_tc(pz64);
+        const double du = fma(px64, inv, -U);
+        const double dv = fma(py64, inv, -V);
+        double e = fma(du, du, dv * dv);
+        e = (pz64 < 0.0) ? DBL_MAX : e;
+        if (e < thr64) {
+          const unsigned long long q = __double2ull_rn(e * scale);
+          atomicAdd(&S.acc[0][hh][cpy], static_cast<uint32_t>(q) & ((1u << kTcxHalfBits) - 1u));
+          atomicAdd(&S.acc[1][hh][cpy], static_cast<uint32_t>(q >> kTcxHalfBits));
+          atomicAdd(&S.acc[2][hh][cpy], 1u);
+        } else if (e != e) {
+          S.nanf[hh] = 1u;  // std::min(e, thr) propagates NaN (ransac.h:308)
+        }
+      }
+      __syncwarp();
+    }
+    if (((it + 1) % kTcxFlush) == 0 || it + 1 == ntiles) {
+      // a hypothesis' accumulators are only touched by its own warp
+      __syncwarp();
+      const uint4 lo = *reinterpret_cast<const uint4*>(S.acc[0][tid]);
+      const uint4 hi = *reinterpret_cast<const uint4*>(S.acc[1][tid]);
+      const uint4 cc = *reinterpret_cast<const uint4*>(S.acc[2][tid]);
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(S.acc[0][tid]) = z;
+      *reinterpret_cast<uint4*>(S.acc[1][tid]) = z;
+      *reinterpret_cast<uint4*>(S.acc[2][tid]) = z;
+      qsum += static_cast<unsigned long long>(lo.x) + lo.y + lo.z + lo.w;
+      qsum += (static_cast<unsigned long long>(hi.x) + hi.y + hi.z + hi.w) << kTcxHalfBits;
+      cnt += static_cast<int>(cc.x + cc.y + cc.z + cc.w);
+      __syncwarp();
+    }
+  }
+
+  if (kk < k_count) {
+    if (PREPASS) {
+      a.part_count[static_cast<size_t>(split) * a.k + kk] = cnt;
+    } else {
+      const int live = max(0, min(ntiles * kTcTile, n_live - t_begin * kTcTile));
+      double sc = thr64 * static_cast<double>(live - cnt) + static_cast<double>(qsum) * (thr64 * (1.0 / 35184372088832.0));
+      if (S.nanf[tid]) sc = __longlong_as_double(0x7ff8000000000000LL);
+      a.part_score[static_cast<size_t>(split) * a.k + kk] = a.w[0] * sc;
+      a.part_count[static_cast<size_t>(split) * a.k + kk] = cnt;
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
+                 "r"(static_cast<uint32_t>(kTcCols))
+                 : "memory");
+  }
+}
+
+// ---- the dense / sparse split of a batch -------------------------------------------------------------------
+// One CTA. flagged[sp][k] (the prepass' part_count) -> per hypothesis: dense when at least 1 / 128 of the sampled
+// pairs were flagged (there the plain f64 sweep is cheaper per pair than flag + gather), else sparse. Ordered
+// compaction (ids ascending in both lists): everything downstream is reproducible.
+//   lists[0 .. k)     ids of the dense hypotheses, lists[k .. 2k) ids of the sparse ones
+//   pos[k]            position of hypothesis k in its list; dense ones as ~position (negative)
+//   counts[0], [1]    lengths of the two lists
+__global__ void __launch_bounds__(1024)
+    tcx_partition_kernel(const int32_t* __restrict__ flagged, int n_splits, int k, int sample_points,
+                         int32_t* __restrict__ lists, int32_t* __restrict__ pos, int32_t* __restrict__ counts) {
+  __shared__ int woff[2][32];
+  __shared__ int base[2];
+  __shared__ int chunk_total[2];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < 2) base[tid] = 0;
+  __syncthreads();
+  const int dense_min = max(1, sample_points / 128);
+  const uint32_t below = (1u << lane) - 1u;
+  for (int k0 = 0; k0 < k; k0 += 1024) {
+    const int kk = k0 + tid;
+    const bool live = kk < k;
+    int nf = 0;
+    if (live)
+      for (int sp = 0; sp < n_splits; ++sp) nf += flagged[static_cast<size_t>(sp) * k + kk];
+    const bool dense = live && nf >= dense_min;
+    const uint32_t bd = __ballot_sync(0xffffffffu, dense);
+    const uint32_t bs = __ballot_sync(0xffffffffu, live && !dense);
+    if (lane == 0) {
+      woff[0][warp] = __popc(bd);
+      woff[1][warp] = __popc(bs);
+    }
+    __syncthreads();
+    if (warp < 2) {  // exclusive scan of the 32 warp counts of list `warp`
+      const int v = woff[warp][lane];
+      int inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+      }
+      woff[warp][lane] = inc - v;
+      if (lane == 31) chunk_total[warp] = inc;
+    }
+    __syncthreads();
+    if (live) {
+      const int l = dense ? 0 : 1;
+      const int p = base[l] + woff[l][warp] + __popc((dense ? bd : bs) & below);
+      lists[static_cast<size_t>(l) * k + p] = kk;
+      pos[kk] = dense ? ~p : p;
+    }
+    __syncthreads();
+    if (tid < 2) base[tid] += chunk_total[tid];
+    __syncthreads();
+  }
+  if (tid < 2) counts[tid] = base[tid];
+}
+
+// Filtered f64 sweep, the launches of one batch (all on `st`, nothing waits on the host):
+//   1. prepass     sweep_pose_tcx_kernel<true> over a strided sample of the tiles -> flagged pairs per hypothesis
+//   2. partition   dense / sparse hypothesis lists
+//   3. dense       the plain f64 sweep (score_kernels.cu) over the dense list, sums into a.acc_q / a.acc_c
+//   4. sparse      sweep_pose_tcx_kernel<false> over the sparse list, partials into part_score / part_count
+// finalize_kernel then reads a hypothesis' result where a.pos says it is.
+cudaError_t launch_sweep_tcx_prepass(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
+                                     int* launches) {
+  ++*launches;
+  static PerDeviceOnce configured;
+  const int dev = PerDeviceOnce::device();
+  if (!configured.done(dev)) {
+    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tcx_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(sizeof(TcxSmem)));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(sweep_pose_tcx_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(sizeof(TcxSmem)));
+    if (e != cudaSuccess) return e;
+    configured.set(dev);
+  }
+  dim3 grid((a.k + kTcThreads - 1) / kTcThreads, a.n_splits);
+  sweep_pose_tcx_kernel<true><<<grid, kTcThreads, sizeof(TcxSmem), st>>>(
+      d, a, tiles, tiles + static_cast<size_t>(d.npad / kTcTile) * kTcTileFloats);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tcx_partition(const int32_t* flagged, int n_splits, int k, int sample_points, int32_t* lists,
+                                 int32_t* pos, int32_t* counts, cudaStream_t st, int* launches) {
+  ++*launches;
+  tcx_partition_kernel<<<1, 1024, 0, st>>>(flagged, n_splits, k, sample_points, lists, pos, counts);
+  return cudaGetLastError();
+}
+
+// (the attributes were set by the prepass launch, which always comes first)
+cudaError_t launch_sweep_tcx(const DeviceData& d, const SweepArgs& a, const float* tiles, cudaStream_t st,
+                             int* launches) {
+  ++*launches;
+  dim3 grid((a.k + kTcThreads - 1) / kTcThreads, a.n_splits);
+  sweep_pose_tcx_kernel<false><<<grid, kTcThreads, sizeof(TcxSmem), st>>>(
+      d, a, tiles, tiles + static_cast<size_t>(d.npad / kTcTile) * kTcTileFloats);
+  return cudaGetLastError();
+}
+
+int tcx_resident_ctas() {
+  static std::atomic<int> cache[64];
+  std::atomic<int>& cached = cache[PerDeviceOnce::device()];
+  if (const int v = cached.load(std::memory_order_relaxed)) return v;
+  cudaFuncSetAttribute(sweep_pose_tcx_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(sizeof(TcxSmem)));
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tcx_kernel<false>, kTcThreads,
+                                                    sizeof(TcxSmem)) != cudaSuccess)
+    n = 1;
+  const int v = max(1, min(n, 512 / kTcCols));
+  cached.store(v, std::memory_order_relaxed);
+  return v;
+}
+
 int tc_tile_points() { return kTcTile; }
-size_t tc_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * kTcTileBytes; }
+size_t tc_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * kTcTileBytes + 256; }  // + bounds
 int tc_hyps_per_cta() { return kTcThreads; }
 
 int tc_resident_ctas() {

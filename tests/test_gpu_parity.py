@@ -387,6 +387,86 @@ def test_tensor_core_sweep_edges(ctx, n):
     assert np.abs(c_f - c[:500]).max() <= 2
 
 
+@pytest.mark.parametrize("n", [5, 33, 700, 4097, 70_000])
+def test_filtered_f64_sweep_equals_the_plain_f64_sweep(ctx, n):
+    """RLB_F64 on >= 512 pose hypotheses: f32 classification on the tensor cores, f64 only for the pairs that could
+    be inliers (sweep variant 11). Counts must be those of the plain f64 sweep (RLB_F64_PLAIN) exactly, scores to
+    1e-12 (fixed-point sums), both within 1e-9 of the oracle; good, bad, behind-the-camera, invalid, non-finite
+    and grazing hypotheses (camera centre inside the point cloud: depths around zero)."""
+    n_in = max(3, n // 2)
+    inst = synth.pose_instance(177 + n, n_in, n - n_in)
+    f = inst["focal"]
+    p2, p3 = inst["points2D"], inst["points3D"]
+    sc = ctx.pose_scorer(p2, p3, f, f)
+    k = 700
+    models = synth.perturbed_poses(5, inst["R_gt"], inst["c_gt"], k, rot_sigma=0.01, trans_sigma=0.05)
+    rng = np.random.default_rng(n)
+    behind = models[:8].copy().reshape(8, 4, 3)
+    behind[:, :3, 1:] *= -1.0
+    models[100:108] = behind.reshape(8, 12)
+    # camera centres ON data points / inside the cloud: zero and tiny depths, points on both sides
+    for i in range(200, 232):
+        m = models[i].copy()
+        m[9:12] = p3[rng.integers(0, n)] + (rng.normal(size=3) * 1e-3 if i % 2 else 0.0)
+        models[i] = m
+    for i in range(300, 364):  # arbitrary rotations about the true centre and random centres
+        R = synth.random_rotation(rng)
+        c = inst["c_gt"] + rng.normal(size=3) * (0.0 if i < 332 else 3.0)
+        models[i] = synth.pose_to_model(R, c)
+    valid = np.ones(k, dtype=np.uint8)
+    valid[50:60] = 0
+    models[60, 3] = np.nan
+    models[61, 10] = np.inf
+    s_p, c_p, bid_p, _ = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64_PLAIN)
+    assert ctx.last_sweep_plan()[0] != 11
+    s_f, c_f, bid_f, _ = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64)
+    assert ctx.last_sweep_plan()[0] == 11
+    assert c_f.tolist() == c_p.tolist()
+    fin = np.isfinite(s_p) & (s_p < 1e300)
+    assert (np.isnan(s_f) == np.isnan(s_p)).all() and ((s_f > 1e300) == (s_p > 1e300)).all()
+    np.testing.assert_allclose(s_f[fin], s_p[fin], rtol=1e-12)
+    assert bid_f == bid_p
+    O = ol.oracle()
+    pick = np.r_[0:40, 100:108, 200:232, 300:364]
+    ws, wc = ol.pose_score(O, f, f, p2, p3, models[pick], 144.0)
+    ok = np.isfinite(ws)
+    np.testing.assert_allclose(s_f[pick][ok], ws[ok], rtol=F64_RTOL)
+    assert c_f[pick][ok].tolist() == wc[ok].tolist()
+    # other thresholds (tiny: the band is relatively wide; huge: nearly everything is evaluated in f64)
+    for thr in (0.25, 1e4):
+        a = sc.score_models(models, thr, valid=valid, precision=rlb().RLB_F64_PLAIN)
+        b = sc.score_models(models, thr, valid=valid, precision=rlb().RLB_F64)
+        assert a[1].tolist() == b[1].tolist() and a[2] == b[2]
+        fin = np.isfinite(a[0]) & (a[0] < 1e300)
+        np.testing.assert_allclose(b[0][fin], a[0][fin], rtol=1e-12)
+    # bit-reproducible
+    again = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64)
+    assert np.array_equal(again[0], s_f, equal_nan=True)
+
+
+def test_filtered_f64_sweep_far_from_the_origin(ctx):
+    """Large pixel coordinates and a scene far from the world origin (ADVICE: the f32 guard must come from an
+    error bound, not a constant): the per-hypothesis band of the f32 classification still covers every inlier."""
+    n = 20_000
+    inst = synth.pose_instance(4242, n // 2, n // 2, width=8000.0, height=6000.0, focal=6000.0,
+                               min_depth=50.0, max_depth=400.0)
+    f = inst["focal"]
+    shift = np.array([1.0e4, -2.0e4, 5.0e3])
+    p2, p3 = inst["points2D"], inst["points3D"] + shift
+    sc = ctx.pose_scorer(p2, p3, f, f)
+    models = synth.perturbed_poses(9, inst["R_gt"], inst["c_gt"] + shift, 1024, rot_sigma=0.002, trans_sigma=0.5)
+    for thr in (4.0, 144.0):
+        a = sc.score_models(models, thr, precision=rlb().RLB_F64_PLAIN)
+        b = sc.score_models(models, thr, precision=rlb().RLB_F64)
+        assert ctx.last_sweep_plan()[0] == 11
+        assert a[1].tolist() == b[1].tolist() and a[2] == b[2]
+        np.testing.assert_allclose(b[0], a[0], rtol=1e-12)
+    O = ol.oracle()
+    ws, wc = ol.pose_score(O, f, f, p2, p3, models[:64], 144.0)
+    np.testing.assert_allclose(b[0][:64], ws, rtol=F64_RTOL)
+    assert b[1][:64].tolist() == wc.tolist()
+
+
 def test_determinism(ctx, pose_case):
     inst, f, _, models, valid = pose_case
     sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
@@ -460,7 +540,9 @@ def test_sharded_round_emulated_ranks(ctx, pose_case):
         ctx.select_winner_dev(recs.data_ptr(), world, 14, win.data_ptr())
         ctx.synchronize()
         w = win.cpu().numpy()
-        assert int(w[1]) == ref["best_id"] and w[0] == ref["best_score"]
+        # (a shard below 512 hypotheses runs the plain f64 sweep, the whole batch the filtered one: the same
+        # pairs summed in another order)
+        assert int(w[1]) == ref["best_id"] and abs(w[0] - ref["best_score"]) <= 1e-12 * ref["best_score"]
         assert w[2:].tolist() == ref["best_model"].tolist()
         # the torch-side selection used under gloo/NCCL agrees with the kernel
         row, ok = sharding.select_winner(recs)

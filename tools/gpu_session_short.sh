@@ -6,7 +6,7 @@ O=gpurun_out
 mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm,power.limit --format=csv > $O/${TAG}_gpu.txt 2>&1
 nproc >> $O/${TAG}_gpu.txt
-timeout 300 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
+timeout 700 python -m pytest tests -m gpu -x -q --durations=15 > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
 tail -3 $O/${TAG}_pytest.log
 timeout 120 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 $O/${TAG}_smoke.log
 timeout 200 python tests/e2e_configs.py > $O/${TAG}_e2e_configs.json 2> $O/${TAG}_e2e_configs.err; echo "e2e configs rc=$?"
