@@ -36,7 +36,7 @@ class CalibratedAbsolutePoseEstimator {
         points2D_(own2D_.data()),
         points3D_(own3D_.data()),
         num_data_(n) {
-    scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), n, points2D_, points3D_, f_x, f_y);
+    InitScorer(ctx);
   }
   // The same without the host copy: both arrays must outlive the estimator.
   CalibratedAbsolutePoseEstimator(gpu::BorrowData, double f_x, double f_y, double squared_inlier_threshold, int n,
@@ -47,7 +47,7 @@ class CalibratedAbsolutePoseEstimator {
         points2D_(points2D),
         points3D_(points3D),
         num_data_(n) {
-    scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), n, points2D_, points3D_, f_x, f_y);
+    InitScorer(ctx);
   }
 
   inline int min_sample_size() const { return 4; }          // reference .h:88
@@ -134,6 +134,18 @@ class CalibratedAbsolutePoseEstimator {
   double focal_y() const { return focal_y_; }
 
  protected:
+  // One GPU (the caller's context or the thread's default one), or with RLB_NUM_GPUS=G in the environment the
+  // data set replicated on G GPUs and large hypothesis batches sharded over them (gpu::DeviceScorer::InitPoseMulti).
+  void InitScorer(gpu::Context* ctx) {
+    const int g = gpu::NumGpusFromEnv();
+    if (g >= 1 && ctx == nullptr) {
+      scorer_.InitPoseMulti(g, num_data_, points2D_, points3D_, focal_x_, focal_y_);
+    } else {
+      scorer_.InitPose(ctx ? *ctx : gpu::Context::ThreadDefault(), num_data_, points2D_, points3D_, focal_x_,
+                       focal_y_);
+    }
+  }
+
   double focal_x_, focal_y_, squared_inlier_threshold_;
   std::vector<double> own2D_, own3D_;  // empty when the data is borrowed
   const double* points2D_;

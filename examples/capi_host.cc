@@ -226,15 +226,15 @@ int rlbh_lomsac_pose(const rlbh_options* o, int device, int precision, double fx
                      const double* p2d, const double* p3d, double* model, rlbh_stats* st,
                      int32_t* inliers) {
   return Guard([&] {
+    // RLB_NUM_GPUS=G: no context of our own - the estimator replicates its data over G GPUs (gpu_scorer.h)
+    gpu::Context* cx = (gpu::NumGpusFromEnv() >= 1) ? nullptr : &gpu::Context::ThreadDefault(device);
     if (HostCopy()) {
-      CalibratedAbsolutePoseEstimator solver(fx, fy, o->sq_thr, n, p2d, p3d,
-                                             &gpu::Context::ThreadDefault(device));
+      CalibratedAbsolutePoseEstimator solver(fx, fy, o->sq_thr, n, p2d, p3d, cx);
       Run<CameraPose, CameraPoses, CalibratedAbsolutePoseEstimator>(
           *o, solver, precision, reinterpret_cast<CameraPose*>(model), st, inliers);
       return;
     }
-    CalibratedAbsolutePoseEstimator solver(gpu::BorrowData(), fx, fy, o->sq_thr, n, p2d, p3d,
-                                           &gpu::Context::ThreadDefault(device));
+    CalibratedAbsolutePoseEstimator solver(gpu::BorrowData(), fx, fy, o->sq_thr, n, p2d, p3d, cx);
     Run<CameraPose, CameraPoses, CalibratedAbsolutePoseEstimator>(
         *o, solver, precision, reinterpret_cast<CameraPose*>(model), st, inliers);
   });

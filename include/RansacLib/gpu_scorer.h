@@ -72,26 +72,61 @@ inline int PrecisionFromEnv() {
   return (p && (p[0] == 'f' || p[0] == 'F') && p[1] == '3') ? RLB_F32 : RLB_F64;
 }
 
-// Owns one rlb_scorer (a data set resident in HBM).
+// Several GPUs of this box driven by this process (rlb_comm_create_local: ncclCommInitAll, one context per
+// device owned by the communicator). Creating a communicator costs ~100 ms, so there is one per device count
+// for the life of the process; its contexts are shared by every multi-GPU scorer, i.e. multi-GPU solvers of one
+// process must not run concurrently.
+class LocalCommunicator {
+ public:
+  static rlb_comm* Get(int ndev) {
+    static std::vector<rlb_comm*> per_count;  // never destroyed: NCCL teardown at exit is not worth the risk
+    if (ndev < 1) throw std::runtime_error("ransaclib_b200: LocalCommunicator needs at least one device");
+    if (static_cast<int>(per_count.size()) <= ndev) per_count.resize(ndev + 1, nullptr);
+    if (!per_count[ndev]) Check(rlb_comm_create_local(ndev, nullptr, &per_count[ndev]), "rlb_comm_create_local");
+    return per_count[ndev];
+  }
+};
+
+// RLB_NUM_GPUS=G in the environment: solvers that support it (CalibratedAbsolutePoseEstimator) put their data on
+// G GPUs and shard large hypothesis batches over them. 0 / unset: one GPU, no communicator.
+inline int NumGpusFromEnv() {
+  const char* p = std::getenv("RLB_NUM_GPUS");
+  return p ? std::atoi(p) : 0;
+}
+
+// Owns one rlb_scorer (a data set resident in HBM) - or, after InitPoseMulti, one replica per GPU of a
+// communicator, with s_ the (borrowed) replica of the first GPU.
 class DeviceScorer {
  public:
   DeviceScorer() = default;
   ~DeviceScorer() { reset(); }
   DeviceScorer(const DeviceScorer&) = delete;
   DeviceScorer& operator=(const DeviceScorer&) = delete;
-  DeviceScorer(DeviceScorer&& o) noexcept : s_(o.s_), precision_(o.precision_) { o.s_ = nullptr; }
+  DeviceScorer(DeviceScorer&& o) noexcept
+      : s_(o.s_), cs_(o.cs_), multi_min_batch_(o.multi_min_batch_), precision_(o.precision_) {
+    o.s_ = nullptr;
+    o.cs_ = nullptr;
+  }
   DeviceScorer& operator=(DeviceScorer&& o) noexcept {
     if (this != &o) {
       reset();
       s_ = o.s_;
+      cs_ = o.cs_;
+      multi_min_batch_ = o.multi_min_batch_;
       precision_ = o.precision_;
       o.s_ = nullptr;
+      o.cs_ = nullptr;
     }
     return *this;
   }
   void reset() {
-    if (s_) rlb_scorer_destroy(s_);
+    if (cs_) {
+      rlb_comm_scorer_destroy(cs_);  // destroys the replicas, s_ among them
+    } else if (s_) {
+      rlb_scorer_destroy(s_);
+    }
     s_ = nullptr;
+    cs_ = nullptr;
   }
 
   void InitLine(Context& c, int n, const double* xy) {
@@ -107,6 +142,21 @@ class DeviceScorer {
     reset();
     Check(rlb_scorer_create_pose(c.get(), n, p2d, p3d, fx, fy, &s_), "rlb_scorer_create_pose");
   }
+
+  // The same data set on `ndev` GPUs (every GPU uploads 1/ndev of the points over its own PCIe link, the slices
+  // are exchanged over NVLink). Hypothesis batches of at least multi_min_batch() samples are cut into contiguous
+  // id ranges, one per GPU, swept concurrently, and settled by ONE ncclAllGather (rlb_comm_*, csrc/comm.cu);
+  // smaller batches and every K = 1 pass run on the first GPU. The run is the single-GPU run: scores are per
+  // hypothesis and the host replays ransac.h:181-240 over them in id order.
+  void InitPoseMulti(int ndev, int n, const double* p2d, const double* p3d, double fx, double fy) {
+    reset();
+    Check(rlb_comm_scorer_create_pose(LocalCommunicator::Get(ndev), n, p2d, p3d, fx, fy, RLB_COMM_ROOT_ALL, &cs_),
+          "rlb_comm_scorer_create_pose");
+    s_ = rlb_comm_scorer_local(cs_, 0);
+  }
+  bool multi_gpu() const { return cs_ != nullptr; }
+  int multi_min_batch() const { return multi_min_batch_; }
+  void set_multi_min_batch(int k) { multi_min_batch_ = k; }
 
   // Any other solver of the concept: data is n x dims (row i = what EvaluateModelOnPoint(model, i) reads),
   // eval_source defines `__device__ double rlb_eval(const double* model, const double* point)`.
@@ -140,6 +190,14 @@ class DeviceScorer {
   void HypothesizeAndScore(int solver, int k, const int32_t* samples, const double* sq_thr,
                            const double* weights, double* models, uint8_t* valid, double* scores,
                            int precision) const {
+    if (cs_ && k >= multi_min_batch_) {
+      int64_t gid;
+      double gscore;
+      Check(rlb_comm_hypothesize_and_score_models(cs_, precision, solver, k, samples, sq_thr, weights, models, valid,
+                                                  scores, nullptr, &gid, &gscore, nullptr),
+            "rlb_comm_hypothesize_and_score_models");
+      return;
+    }
     int32_t best_id;
     double best_score;
     Check(rlb_hypothesize_and_score(s_, precision, solver, k, samples, sq_thr, weights, models,
@@ -173,6 +231,8 @@ class DeviceScorer {
   }
  private:
   rlb_scorer* s_ = nullptr;
+  rlb_comm_scorer* cs_ = nullptr;  // InitPoseMulti: owns the replicas; s_ is the first one
+  int multi_min_batch_ = 2048;     // below this a batch is not worth a collective (one GPU sweeps it in < 0.1 ms)
   int precision_ = PrecisionFromEnv();
 };
 

@@ -270,6 +270,13 @@ int rlb_comm_hypothesize_and_score(rlb_comm_scorer* cs, int precision, int solve
                                    const int32_t* samples, const double* sq_thr, const double* weights,
                                    double* scores, int32_t* counts, int64_t* best_id, double* best_score,
                                    double* best_model);
+/* The same round with the hypotheses themselves returned (models: k_total x model_size, valid: k_total; the
+ * slices of this process's GPUs are filled): what the drop-in LocallyOptimizedMSAC needs to replay
+ * ransac.h:181-240 over a sharded batch (gpu::DeviceScorer::InitPoseMulti). */
+int rlb_comm_hypothesize_and_score_models(rlb_comm_scorer* cs, int precision, int solver, int k_total,
+                                          const int32_t* samples, const double* sq_thr, const double* weights,
+                                          double* models, uint8_t* valid, double* scores, int32_t* counts,
+                                          int64_t* best_id, double* best_score, double* best_model);
 /* Device-pointer form of the same round for the one-process-per-GPU communicator: this rank's shard
  * (k_local hypotheses, global ids id_offset ...) is already in HBM; asynchronous on the context stream.
  * d_winner: {score, global id as f64, model[model_size]} on every rank. */

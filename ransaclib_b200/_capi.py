@@ -33,7 +33,7 @@ SYMBOLS = [
     "rlb_comm_get_unique_id", "rlb_comm_init_rank", "rlb_comm_create_local", "rlb_comm_destroy", "rlb_comm_nranks",
     "rlb_comm_num_local", "rlb_comm_rank", "rlb_comm_ctx", "rlb_comm_collective_count",
     "rlb_comm_scorer_create_pose", "rlb_comm_scorer_destroy", "rlb_comm_scorer_local",
-    "rlb_comm_hypothesize_and_score", "rlb_comm_round_dev", "rlb_comm_get_inliers",
+    "rlb_comm_hypothesize_and_score", "rlb_comm_hypothesize_and_score_models", "rlb_comm_round_dev", "rlb_comm_get_inliers",
 ]
 COMM_ID_BYTES = 128
 NOALLOC_MAX_POINTS = 4194304

@@ -431,6 +431,14 @@ int rlb_comm_hypothesize_and_score(rlb_comm_scorer* cs, int precision, int solve
                                    const int32_t* samples, const double* sq_thr, const double* weights,
                                    double* scores, int32_t* counts, int64_t* best_id, double* best_score,
                                    double* best_model) {
+  return rlb_comm_hypothesize_and_score_models(cs, precision, solver, k_total, samples, sq_thr, weights, nullptr,
+                                               nullptr, scores, counts, best_id, best_score, best_model);
+}
+
+int rlb_comm_hypothesize_and_score_models(rlb_comm_scorer* cs, int precision, int solver, int k_total,
+                                          const int32_t* samples, const double* sq_thr, const double* weights,
+                                          double* models, uint8_t* valid, double* scores, int32_t* counts,
+                                          int64_t* best_id, double* best_score, double* best_model) {
   if (!cs || !cs->comm) return set_error(RLB_E_ARG, "null communicator scorer");
   if (k_total <= 0 || !samples || !sq_thr) return set_error(RLB_E_ARG, "k_total, samples and sq_thr are required");
   rlb_comm* cm = cs->comm;
@@ -474,6 +482,11 @@ int rlb_comm_hypothesize_and_score(rlb_comm_scorer* cs, int precision, int solve
     if (hi > lo && counts)
       COMM_CUDA(cudaMemcpyAsync(counts + lo, L.d_counts, static_cast<size_t>(hi - lo) * sizeof(int32_t), cudaMemcpyDeviceToHost,
                                 L.stream()));
+    if (hi > lo && models)
+      COMM_CUDA(cudaMemcpyAsync(models + static_cast<size_t>(lo) * msize, L.d_models,
+                                static_cast<size_t>(hi - lo) * msize * sizeof(double), cudaMemcpyDeviceToHost, L.stream()));
+    if (hi > lo && valid)
+      COMM_CUDA(cudaMemcpyAsync(valid + lo, L.d_valid, static_cast<size_t>(hi - lo), cudaMemcpyDeviceToHost, L.stream()));
     if (i == 0)
       COMM_CUDA(cudaMemcpyAsync(L.h_winner, L.d_winner, rec * sizeof(double), cudaMemcpyDeviceToHost, L.stream()));
   }

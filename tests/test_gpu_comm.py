@@ -150,3 +150,29 @@ def test_two_gpus_one_process(case):
     comm.close()
     sc.close()
     c0.close()
+
+
+@pytest.mark.parametrize("gpus", [1, 2])
+def test_drop_in_layer_shards_large_batches(gpus, monkeypatch):
+    """LocallyOptimizedMSAC over CalibratedAbsolutePoseEstimator with RLB_NUM_GPUS=G: the data set is replicated by
+    the library's communicator (gpu::DeviceScorer::InitPoseMulti), batches of >= 2048 hypotheses are sharded and
+    settled by one ncclAllGather each - and the run is the single-GPU run, statistic for statistic."""
+    import torch
+
+    from ransaclib_b200 import host as H
+
+    if torch.cuda.device_count() < gpus:
+        pytest.skip("needs %d GPUs" % gpus)
+    inst = synth.pose_instance(4242, 5000, 5000)
+    f = inst["focal"]
+    opts = H.LORansacOptions(squared_inlier_threshold_=144.0, random_seed_=42, min_num_iterations_=10000,
+                             max_num_iterations_=10000)
+    monkeypatch.delenv("RLB_NUM_GPUS", raising=False)
+    m1, st1 = H.estimate_pose(opts, f, f, inst["points2D"], inst["points3D"])
+    monkeypatch.setenv("RLB_NUM_GPUS", str(gpus))
+    mg, stg = H.estimate_pose(opts, f, f, inst["points2D"], inst["points3D"])
+    assert stg["num_iterations"] == st1["num_iterations"] == 10000
+    assert mg.tolist() == m1.tolist()
+    for key in ("best_num_inliers", "number_lo_iterations", "best_model_score"):
+        assert stg[key] == st1[key], key
+    assert stg["inlier_indices"].tolist() == st1["inlier_indices"].tolist()
