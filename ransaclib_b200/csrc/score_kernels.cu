@@ -15,6 +15,7 @@
 // atomics anywhere: partial sums go to [split][k] and are combined in a fixed
 // order, so results are bit-reproducible run to run.
 #include <cfloat>
+#include <cstdlib>
 #include <climits>
 
 #include "rlb_internal.cuh"
@@ -1120,10 +1121,273 @@ __global__ void __launch_bounds__(kInlThreads) inlier_kernel(const DeviceData d,
   }
 }
 
+// ---- the same pass as ONE wave: every CTA takes a contiguous RANGE of tiles --------------------------------
+// inlier_kernel above runs one CTA per tile: N = 1M is 977 CTAs on 592 resident slots, i.e. two waves, and every
+// CTA pays the ticket, the status round trip and the final counter once per 1024 points (ncu: DRAM 22 % busy,
+// barrier and long-scoreboard stalls). Here the grid never exceeds the resident capacity; CTA number b (a ticket,
+// so that every lower-numbered CTA is running or done) evaluates tiles [b T, (b + 1) T), keeps four inlier bits
+// and the exclusive offset per thread and tile in shared memory, publishes ONE count, reads the counts of the
+// CTAs below it (a flat read: at most 3 words per thread), and then writes its slice of the list. Same results
+// as inlier_kernel except for the order in which the tile scores are added (still a fixed order).
+constexpr int kInlMaxRange = 8;  // tiles per CTA (shared-memory record: 8 x 256 words)
+
+// 1 (default): the next tile's loads are issued before this tile is evaluated (92 registers, 2 CTAs / SM): 18.2 us
+// for N = 1M against 21.6 us without and 24.6 us for one CTA per tile (profiles/r02_inlier_pass_ab.txt)
+#ifndef RLB_INL_PREFETCH
+#define RLB_INL_PREFETCH 1
+#endif
+template <template <typename> class FT>
+#ifndef RLB_INL_MINB
+#define RLB_INL_MINB (RLB_INL_PREFETCH ? 2 : 4)
+#endif
+__global__ void __launch_bounds__(kInlThreads, RLB_INL_MINB)
+    inlier_range_kernel(const DeviceData d, const InlierArgs a, int tiles_per_cta, int num_tiles) {
+  typedef FT<double> F;
+  constexpr int C = F::C;
+  constexpr int PPT = kInlTile / kInlThreads;
+  __shared__ unsigned int s_rank;
+  __shared__ int s_wsum[kInlThreads / 32];
+  __shared__ double s_wscore[kInlThreads / 32];
+  __shared__ int s_below[kInlThreads / 32];
+  __shared__ int s_base;
+  __shared__ unsigned int s_keep[kInlMaxRange][kInlThreads];
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) s_rank = atomicAdd(&a.control[0], 1u);
+  typename F::Model m;
+  F::load(a.model != nullptr ? a.model : a.model_v, d, m);  // (its latency overlaps the ticket's)
+  __syncthreads();
+  const int b = static_cast<int>(s_rank);
+  const int num_ctas = static_cast<int>(gridDim.x);
+  const int t0 = b * tiles_per_cta;
+  const int t1 = min(num_tiles, t0 + tiles_per_cta);
+
+#if RLB_INL_PREFETCH
+  double2 nx[C][2];
+  if (t0 < t1) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const double2* src = reinterpret_cast<const double2*>(d.soa64 + static_cast<size_t>(c) * d.npad +
+                                                            static_cast<size_t>(t0) * kInlTile + tid * PPT);
+      nx[c][0] = src[0];
+      nx[c][1] = src[1];
+    }
+  }
+#endif
+  int run = 0;          // inliers of this CTA's earlier tiles (uniform)
+  int type0_local = -1; // inliers of this CTA before the first type-1 tile, if that tile is here
+  double sc = 0.0;
+#pragma unroll 1
+  for (int ti = t0; ti < t1; ++ti) {
+    const int g0 = ti * kInlTile;
+    const int t = (d.num_types > 1 && g0 >= d.off[1]) ? 1 : 0;
+    const int seg_n = d.n[t], seg_off = d.off[t];
+    const double thr_in = a.thr_inl[t];
+    const double thr_sc = a.thr_score[t];
+    const double w = a.w[t];
+    if (d.num_types > 1 && g0 == d.off[1]) type0_local = run;
+
+    const int i0 = g0 + tid * PPT;
+#if RLB_INL_PREFETCH
+    // the next tile's loads are in flight while this one is evaluated and scanned
+    double ch[C][PPT];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      ch[c][0] = nx[c][0].x;
+      ch[c][1] = nx[c][0].y;
+      ch[c][2] = nx[c][1].x;
+      ch[c][3] = nx[c][1].y;
+    }
+    if (ti + 1 < t1) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const double2* src =
+            reinterpret_cast<const double2*>(d.soa64 + static_cast<size_t>(c) * d.npad + i0 + kInlTile);
+        nx[c][0] = src[0];
+        nx[c][1] = src[1];
+      }
+    }
+#else
+    double ch[C][PPT];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const double2* src = reinterpret_cast<const double2*>(d.soa64 + static_cast<size_t>(c) * d.npad + i0);
+      const double2 v0 = src[0], v1 = src[1];
+      ch[c][0] = v0.x;
+      ch[c][1] = v0.y;
+      ch[c][2] = v1.x;
+      ch[c][3] = v1.y;
+    }
+#endif
+    unsigned int bits = 0u;
+    int my = 0;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+      double p[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) p[c] = ch[c][j];
+      const double e = F::eval(m, p);
+      const bool live = (i0 + j - seg_off) < seg_n;
+      const bool in = live && (e < thr_in);
+      bits |= in ? (1u << j) : 0u;
+      my += in ? 1 : 0;
+      if (live) sc += ((thr_sc < e) ? thr_sc : e) * w;  // hybrid_ransac.h:416-418
+    }
+    int incl = my;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_wsum[wid] = incl;
+    __syncthreads();
+    int warp_excl = 0, tile_total = 0;
+#pragma unroll
+    for (int q = 0; q < kInlThreads / 32; ++q) {
+      if (q < wid) warp_excl += s_wsum[q];
+      tile_total += s_wsum[q];
+    }
+    s_keep[ti - t0][tid] = (static_cast<unsigned int>(run + warp_excl + incl - my) << 4) | bits;
+    run += tile_total;
+    __syncthreads();  // s_wsum is reused by the next tile
+  }
+
+  // this CTA's score (fixed tree) and count
+  double wsc = sc;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wsc += __shfl_down_sync(0xffffffffu, wsc, o);
+  if (lane == 0) s_wscore[wid] = wsc;
+  __syncthreads();
+  if (tid == 0) {
+    double ts = 0.0;
+#pragma unroll
+    for (int q = 0; q < kInlThreads / 32; ++q) ts += s_wscore[q];
+    a.tile_score[b] = ts;
+    __threadfence();  // the score is visible to whoever sees the count word
+    atomicExch(&a.status[b], pack_status(a.epoch, kFlagAgg, static_cast<unsigned int>(run)));
+  }
+  // counts of the CTAs below (all of them hold a lower ticket: running or done). Bounded like every wait here.
+  int below = 0;
+  for (int j = tid; j < b; j += kInlThreads) {
+    const unsigned long long* wp = &a.status[j];
+    unsigned long long word;
+    long long c0 = 0;
+    unsigned int spins = 0;
+    for (;;) {
+      word = *reinterpret_cast<const volatile unsigned long long*>(wp);
+      if (static_cast<unsigned int>(word >> 34) == a.epoch && ((word >> 32) & 3ull) != 0ull) break;
+      if (++spins == 4096u) {
+        const long long now = clock64();
+        if (c0 == 0) {
+          c0 = now;
+        } else if (now - c0 > 4000000000LL) {
+          __trap();
+        }
+        spins = 0;
+      }
+    }
+    below += static_cast<int>(word & 0xffffffffull);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) below += __shfl_down_sync(0xffffffffu, below, o);
+  if (lane == 0) s_below[wid] = below;
+  __syncthreads();
+  if (tid == 0) {
+    int base = 0;
+#pragma unroll
+    for (int q = 0; q < kInlThreads / 32; ++q) base += s_below[q];
+    s_base = base;
+    InlierHeader* hdr = reinterpret_cast<InlierHeader*>(a.header);
+    if (type0_local >= 0) hdr->count[0] = base + type0_local;  // #type-0 inliers
+    if (b == num_ctas - 1) {
+      hdr->count[1] = base + run;  // total over all types
+      if (d.num_types == 1 || d.off[1] >= d.npad) hdr->count[0] = base + run;
+    }
+  }
+  __syncthreads();
+
+  if (a.idx != nullptr) {
+    const int base = s_base;
+#pragma unroll 1
+    for (int ti = t0; ti < t1; ++ti) {
+      const int g0 = ti * kInlTile;
+      const int seg_off = d.off[(d.num_types > 1 && g0 >= d.off[1]) ? 1 : 0];
+      const unsigned int v = s_keep[ti - t0][tid];
+      int pos = base + static_cast<int>(v >> 4);
+      const int i0 = g0 + tid * PPT - seg_off;
+#pragma unroll
+      for (int j = 0; j < PPT; ++j) {
+        if ((v >> j) & 1u) a.idx[pos++] = i0 + j;
+      }
+    }
+  }
+
+  // The CTA with the highest ticket has seen every other CTA's count word, hence (fence above) every score:
+  // it adds them in index order and resets the ticket counter (all tickets are taken) - no "last CTA done"
+  // counter, no second round trip.
+  if (b != num_ctas - 1) return;
+  __threadfence();
+  double part = 0.0;
+  for (int q = tid; q < num_ctas; q += kInlThreads) part += *reinterpret_cast<volatile double*>(&a.tile_score[q]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_down_sync(0xffffffffu, part, o);
+  __syncthreads();
+  if (lane == 0) s_wscore[wid] = part;
+  __syncthreads();
+  if (tid == 0) {
+    double total = 0.0;
+#pragma unroll
+    for (int q = 0; q < kInlThreads / 32; ++q) total += s_wscore[q];
+    InlierHeader* hdr = reinterpret_cast<InlierHeader*>(a.header);
+    hdr->score = total;
+    a.control[0] = 0u;
+  }
+}
+
+template <template <typename> class FT>
+static cudaError_t launch_inlier_range(const DeviceData& d, const InlierArgs& a, int tiles, cudaStream_t st,
+                                       bool* launched) {
+  static std::atomic<int> capacity[64];  // resident CTAs of this instantiation per device; 0 = not asked yet
+  const int dev = PerDeviceOnce::device();
+  int cap = capacity[dev].load(std::memory_order_relaxed);
+  if (cap == 0) {
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, inlier_range_kernel<FT>, kInlThreads, 0) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      per_sm = 0;
+    cap = max(1, per_sm * sms);
+    capacity[dev].store(cap, std::memory_order_relaxed);
+  }
+  const int per_cta = (tiles + cap - 1) / cap;
+  *launched = per_cta <= kInlMaxRange;
+  if (!*launched) return cudaSuccess;
+  const int ctas = (tiles + per_cta - 1) / per_cta;
+  inlier_range_kernel<FT><<<ctas, kInlThreads, 0, st>>>(d, a, per_cta, tiles);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_t st,
                            int* launches) {
   ++*launches;
   const int tiles = d.npad / kInlTile;
+  // RLB_INLIER_RANGE=0: the one-CTA-per-tile kernel (A/B timing); it also takes data sets too large for one wave
+  static const bool use_range = [] {
+    const char* v = getenv("RLB_INLIER_RANGE");
+    return !(v && atoi(v) == 0);
+  }();
+  if (use_range) {
+    bool launched = false;
+    cudaError_t e;
+    if (d.kind == RLB_KIND_POSE) {
+      e = launch_inlier_range<PoseF>(d, a, tiles, st, &launched);
+    } else if (d.kind == RLB_KIND_CUSTOM) {
+      e = launch_inlier_range<ErrF>(d, a, tiles, st, &launched);
+    } else {
+      e = launch_inlier_range<LineF>(d, a, tiles, st, &launched);
+    }
+    if (e != cudaSuccess || launched) return e;
+  }
   if (d.kind == RLB_KIND_POSE) {
     inlier_kernel<PoseF><<<tiles, kInlThreads, 0, st>>>(d, a);
   } else if (d.kind == RLB_KIND_CUSTOM) {
