@@ -16,6 +16,7 @@
 
 #include "circle_estimator.h"
 #include "calibrated_absolute_pose_estimator.h"
+#include "hybrid_custom_line_estimator.h"
 #include "hybrid_line_estimator.h"
 #include "line_estimator.h"
 #include "localization_io.h"
@@ -139,8 +140,8 @@ struct SizesOnly {
   void get_weights(std::vector<std::vector<double>>& w) const { w = weights; }
 };
 
-template <class Sampler>
-void RunHybrid(const rlbh_hybrid_options& o, HybridLineEstimator& solver, int precision, double* model,
+template <class Sampler, class HSolver = HybridLineEstimator>
+void RunHybrid(const rlbh_hybrid_options& o, HSolver& solver, int precision, double* model,
                rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
   if (precision >= 0) solver.device_scorer().set_precision(precision);
   HybridLORansacOptions ho;
@@ -157,7 +158,7 @@ void RunHybrid(const rlbh_hybrid_options& o, HybridLineEstimator& solver, int pr
   ho.min_sample_multiplicator_ = o.min_sample_mult;
   ho.lo_starting_iterations_ = o.lo_start;
   ho.final_least_squares_ = o.final_lsq != 0;
-  HybridLocallyOptimizedMSAC<Line2D, Lines2D, HybridLineEstimator, Sampler> lomsac;
+  HybridLocallyOptimizedMSAC<Line2D, Lines2D, HSolver, Sampler> lomsac;
   HybridRansacStatistics hs;
   lomsac.EstimateModel(ho, solver, reinterpret_cast<Line2D*>(model), &hs);
   st->num_iterations_total = hs.num_iterations_total;
@@ -267,6 +268,18 @@ int rlbh_hybrid_lomsac_line(const rlbh_hybrid_options* o, int device, int precis
     HybridLineEstimator solver(gpu::BorrowData(), n0, xy0, n1, xynn1, {priors[0], priors[1]},
                                &gpu::Context::ThreadDefault(device));
     RunHybrid<HybridUniformSampling<HybridLineEstimator>>(*o, solver, precision, model, st, inl0, inl1);
+  });
+}
+
+// The same run with the solver's EvaluateModelOnPoint handed over as source (rlb_scorer_create_custom_hybrid):
+// the path of any user-defined HybridSolver.
+int rlbh_hybrid_lomsac_line_custom(const rlbh_hybrid_options* o, int device, int precision, int n0,
+                                   const double* xy0, int n1, const double* xynn1, const double* priors,
+                                   double* model, rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
+  return Guard([&] {
+    HybridCustomLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]}, &gpu::Context::ThreadDefault(device));
+    RunHybrid<HybridUniformSampling<HybridCustomLineEstimator>, HybridCustomLineEstimator>(*o, solver, precision, model,
+                                                                                          st, inl0, inl1);
   });
 }
 

@@ -166,6 +166,15 @@ class DeviceScorer {
           "rlb_scorer_create_custom");
   }
 
+  // The HybridSolver concept with a user-defined functor: two data types (rows of dims0 / dims1 doubles),
+  // eval_source defines `__device__ double rlb_eval_t(const double* model, int type, const double* point)`.
+  void InitCustomHybrid(Context& c, int n0, int dims0, const double* data0, int n1, int dims1, const double* data1,
+                        int model_doubles, const char* eval_source) {
+    reset();
+    Check(rlb_scorer_create_custom_hybrid(c.get(), n0, dims0, data0, n1, dims1, data1, model_doubles, eval_source, &s_),
+          "rlb_scorer_create_custom_hybrid");
+  }
+
   bool valid() const { return s_ != nullptr; }
   rlb_scorer* get() const { return s_; }
   int model_size() const { return rlb_scorer_model_size(s_); }

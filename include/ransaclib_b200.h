@@ -104,6 +104,14 @@ int rlb_scorer_create_pose_dev(rlb_ctx* ctx, int n, const double* d_points2D, co
  * device minimal solvers are not available for it (hypotheses come from the host MinimalSolver). */
 int rlb_scorer_create_custom(rlb_ctx* ctx, int n, int dims, const double* data, int model_doubles,
                              const char* eval_source, rlb_scorer** out);
+/* The HybridSolver concept (README.md:164-208; EvaluateModelOnPoint(model, t, i) as in
+ * examples/hybrid_line_estimator.cc:100-109): two data types with rows of dims0 / dims1 doubles, per-type
+ * thresholds and weights as for the built-in hybrid line scorer (hybrid_ransac.h:386-495). eval_source defines
+ *     __device__ double rlb_eval_t(const double* model, int type, const double* point);
+ * `point` has max(dims0, dims1) entries, those beyond the type's own dims are zero. */
+int rlb_scorer_create_custom_hybrid(rlb_ctx* ctx, int n0, int dims0, const double* data0, int n1, int dims1,
+                                    const double* data1, int model_doubles, const char* eval_source,
+                                    rlb_scorer** out);
 /* Compiles eval_source exactly as rlb_scorer_create_custom would, without touching a device (usable on a
  * machine with no GPU): RLB_OK and the size of the sm_100a cubin, or the compiler log as above. */
 int rlb_custom_compile_check(const char* eval_source, int dims, int model_doubles, size_t* cubin_bytes);

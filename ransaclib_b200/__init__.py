@@ -197,6 +197,21 @@ class Context:
                                                        int(model_doubles), eval_source.encode(), C.byref(h)))
         return Scorer(self, h)
 
+    def custom_hybrid_scorer(self, data0, data1, model_doubles: int, eval_source: str) -> "Scorer":
+        """The HybridSolver form of a user-defined functor (``rlb_scorer_create_custom_hybrid``): two data types,
+        ``data_t`` is n_t x dims_t, ``eval_source`` defines
+        ``__device__ double rlb_eval_t(const double* model, int type, const double* point)``; thresholds and
+        weights are per type as for the built-in hybrid line scorer."""
+        d0 = np.ascontiguousarray(data0, dtype=np.float64)
+        d1 = np.ascontiguousarray(data1, dtype=np.float64)
+        if d0.ndim != 2 or d1.ndim != 2:
+            raise ValueError("data0 / data1 must be n x dims")
+        h = C.c_void_p()
+        _capi.check(self._lib.rlb_scorer_create_custom_hybrid(
+            self._h, d0.shape[0], d0.shape[1], _capi.ptr(d0), d1.shape[0], d1.shape[1], _capi.ptr(d1),
+            int(model_doubles), eval_source.encode(), C.byref(h)))
+        return Scorer(self, h)
+
     def pose_scorer(self, points2D, points3D, fx: float, fy: float) -> "Scorer":
         p2 = _capi.f64a(points2D, (-1, 2))
         p3 = _capi.f64a(points3D, (-1, 3))

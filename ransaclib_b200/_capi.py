@@ -21,7 +21,7 @@ KIND_LINE, KIND_HYBRID_LINE, KIND_POSE = 0, 1, 2
 SYMBOLS = [
     "rlb_last_error", "rlb_version", "rlb_ctx_create", "rlb_ctx_destroy", "rlb_ctx_set_stream", "rlb_ctx_use_own_stream",
     "rlb_ctx_synchronize", "rlb_ctx_launch_count", "rlb_ctx_sm_count", "rlb_scorer_create_line",
-    "rlb_scorer_create_hybrid_line", "rlb_scorer_create_pose", "rlb_scorer_create_custom",
+    "rlb_scorer_create_hybrid_line", "rlb_scorer_create_pose", "rlb_scorer_create_custom", "rlb_scorer_create_custom_hybrid",
     "rlb_custom_compile_check", "rlb_scorer_destroy", "rlb_scorer_kind",
     "rlb_scorer_num_types", "rlb_scorer_num_data", "rlb_scorer_model_size", "rlb_scorer_get_rays",
     "rlb_score_models", "rlb_score_models_dev", "rlb_get_inliers", "rlb_get_inliers_view", "rlb_get_inliers_dev",
@@ -107,6 +107,7 @@ def load():
     lib.rlb_ctx_kernel_time_ms.argtypes = [vp, i32, C.POINTER(f64)]
     lib.rlb_ctx_last_sweep_plan.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
     lib.rlb_scorer_create_custom.argtypes = [vp, i32, i32, vp, i32, C.c_char_p, C.POINTER(vp)]
+    lib.rlb_scorer_create_custom_hybrid.argtypes = [vp, i32, i32, vp, i32, i32, vp, i32, C.c_char_p, C.POINTER(vp)]
     lib.rlb_custom_compile_check.argtypes = [C.c_char_p, i32, i32, C.POINTER(C.c_size_t)]
     lib.rlb_localize_default_options.argtypes = [C.POINTER(LocalizeOptions), f64, i32, C.c_uint32, C.c_uint32]
     lib.rlb_localize_default_options.restype = None

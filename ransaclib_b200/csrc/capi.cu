@@ -442,11 +442,13 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   if (d.kind == RLB_KIND_CUSTOM) {
     // user functor (custom_functor.cu): 128 hypotheses per CTA, whole 128-point chunks per split, ~8 CTAs per SM
     const int k_tiles = (k + 127) / 128;
-    const int chunks = (d.n[0] + 127) / 128;
+    // extent of the padded point axis that holds live points (two types: the second segment starts at off[1])
+    const int extent = (d.num_types > 1 && d.n[1] > 0) ? d.off[1] + d.n[1] : d.n[0];
+    const int chunks = (extent + 127) / 128;
     if (chunks > 0) {
       const int want = std::max(1, std::min(std::min(64, chunks), (c->sms * 8 + k_tiles - 1) / k_tiles));
       custom_pps = ((chunks + want - 1) / want) * 128;
-      splits = (d.n[0] + custom_pps - 1) / custom_pps;
+      splits = (extent + custom_pps - 1) / custom_pps;
     } else {
       splits = 1;
     }
@@ -913,20 +915,32 @@ int rlb_custom_compile_check(const char* eval_source, int dims, int model_double
   if (dims < 1 || dims > 8) return fail(RLB_E_ARG, "dims must be 1..8 (got %d)", dims);
   if (model_doubles < 1 || model_doubles > 12) return fail(RLB_E_ARG, "model_doubles must be 1..12 (got %d)", model_doubles);
   std::string cubin, err;
-  if (!rlb::custom_compile(eval_source, dims, model_doubles, &cubin, &err)) return fail(RLB_E_ARG, "%s", err.c_str());
+  // a source that defines rlb_eval_t (the HybridSolver form) is compiled as such
+  const bool hybrid = strstr(eval_source, "rlb_eval_t") != nullptr;
+  if (!rlb::custom_compile(eval_source, dims, model_doubles, hybrid, &cubin, &err)) return fail(RLB_E_ARG, "%s", err.c_str());
   if (cubin_bytes) *cubin_bytes = cubin.size();
   return RLB_OK;
 }
 
-int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, int model_doubles,
-                             const char* eval_source, rlb_scorer** out) {
-  if (!c || !out || n < 0 || (n > 0 && !data) || !eval_source) return fail(RLB_E_ARG, "bad arguments");
-  if (dims < 1 || dims > 8) return fail(RLB_E_ARG, "dims must be 1..8 (got %d)", dims);
+namespace {
+
+// One (num_types = 1) or two data types of a user-defined solver: rows of dims_t doubles per type, stored
+// channel-major with max(dims) channels, type 1 from the next multiple of kSegAlign.
+int create_custom(rlb_ctx* c, int num_types, const int* n, const int* dims_t, const double* const* data,
+                  int model_doubles, const char* eval_source, rlb_scorer** out) {
+  if (!c || !out || !eval_source) return fail(RLB_E_ARG, "bad arguments");
+  int dims = 0;
+  for (int t = 0; t < num_types; ++t) {
+    if (n[t] < 0 || (n[t] > 0 && !data[t])) return fail(RLB_E_ARG, "bad arguments (data type %d)", t);
+    if (dims_t[t] < 1 || dims_t[t] > 8) return fail(RLB_E_ARG, "dims must be 1..8 (got %d)", dims_t[t]);
+    dims = std::max(dims, dims_t[t]);
+  }
   if (model_doubles < 1 || model_doubles > 12) return fail(RLB_E_ARG, "model_doubles must be 1..12 (got %d)", model_doubles);
   int rc = ctx_use(c);
   if (rc) return rc;
   std::string cubin, err;
-  if (!rlb::custom_compile(eval_source, dims, model_doubles, &cubin, &err)) return fail(RLB_E_ARG, "%s", err.c_str());
+  if (!rlb::custom_compile(eval_source, dims, model_doubles, num_types > 1, &cubin, &err))
+    return fail(RLB_E_ARG, "%s", err.c_str());
   rc = ensure_first_use(c);  // a runtime call: the primary context the driver-API module is loaded into exists
   if (rc) return rc;
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
@@ -935,10 +949,17 @@ int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, in
   DeviceData& d = s->d;
   memset(&d, 0, sizeof(d));
   d.kind = RLB_KIND_CUSTOM;
-  d.num_types = 1;
-  d.n[0] = n;
+  d.num_types = num_types;
+  d.n[0] = n[0];
   d.off[0] = 0;
-  d.off[1] = d.npad = std::max(pad_to(n, rlb::kSegAlign), rlb::kSegAlign);
+  const int span0 = std::max(pad_to(n[0], rlb::kSegAlign), rlb::kSegAlign);
+  int span1 = 0;
+  if (num_types > 1) {
+    d.n[1] = n[1];
+    span1 = std::max(pad_to(n[1], rlb::kSegAlign), rlb::kSegAlign);
+  }
+  d.off[1] = span0;
+  d.npad = span0 + span1;
   d.channels = dims;
   d.model_doubles = model_doubles;
   s->custom = rlb::custom_load(cubin, dims, model_doubles, &err);
@@ -946,7 +967,8 @@ int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, in
     rlb_scorer_destroy(s);
     return fail(RLB_E_CUDA, "loading the compiled functor: %s", err.c_str());
   }
-  rc = upload(c, &s->raw0, data, static_cast<size_t>(n) * dims, c->stream);
+  rc = upload(c, &s->raw0, data[0], static_cast<size_t>(n[0]) * dims_t[0], c->stream);
+  if (!rc && num_types > 1) rc = upload(c, &s->raw1, data[1], static_cast<size_t>(n[1]) * dims_t[1], c->stream);
   if (!rc) rc = pool_alloc(c, static_cast<size_t>(dims) * d.npad * sizeof(double), &s->soa64);
   if (!rc) rc = pool_alloc(c, static_cast<size_t>(d.npad) * sizeof(double), &s->custom_err);
   if (rc) {
@@ -954,9 +976,13 @@ int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, in
     return rc;
   }
   d.raw0 = static_cast<const double*>(s->raw0);
+  d.raw1 = static_cast<const double*>(s->raw1);
   d.soa64 = static_cast<const double*>(s->soa64);
-  cudaError_t ce = rlb::launch_custom_repack(d.raw0, n, dims, d.npad, static_cast<double*>(s->soa64), c->stream,
-                                             &c->launches_i);
+  cudaError_t ce = rlb::launch_custom_repack(d.raw0, n[0], dims_t[0], dims, d.npad, 0, span0,
+                                             static_cast<double*>(s->soa64), c->stream, &c->launches_i);
+  if (ce == cudaSuccess && num_types > 1)
+    ce = rlb::launch_custom_repack(d.raw1, n[1], dims_t[1], dims, d.npad, span0, span1,
+                                   static_cast<double*>(s->soa64), c->stream, &c->launches_i);
   if (ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);
   account(c);
   if (ce != cudaSuccess) {
@@ -965,6 +991,21 @@ int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, in
   }
   *out = s;
   return RLB_OK;
+}
+
+}  // namespace
+
+int rlb_scorer_create_custom(rlb_ctx* c, int n, int dims, const double* data, int model_doubles,
+                             const char* eval_source, rlb_scorer** out) {
+  return create_custom(c, 1, &n, &dims, &data, model_doubles, eval_source, out);
+}
+
+int rlb_scorer_create_custom_hybrid(rlb_ctx* c, int n0, int dims0, const double* data0, int n1, int dims1,
+                                    const double* data1, int model_doubles, const char* eval_source,
+                                    rlb_scorer** out) {
+  const int n[2] = {n0, n1}, dims[2] = {dims0, dims1};
+  const double* data[2] = {data0, data1};
+  return create_custom(c, 2, n, dims, data, model_doubles, eval_source, out);
 }
 
 int rlb_scorer_destroy(rlb_scorer* s) {
@@ -1257,8 +1298,8 @@ int rlb_eval_errors(rlb_scorer* s, int precision, const double* model, int type,
     if (!rlb::launch_custom_errors(s->custom, d, c->one_model.as<double>(), static_cast<double*>(s->custom_err),
                                    c->stream, &c->launches_i, &cerr))
       return fail(RLB_E_CUDA, "custom errors: %s", cerr.c_str());
-    RLB_CUDA(cudaMemcpyAsync(c->scores.p, s->custom_err, static_cast<size_t>(n) * sizeof(double),
-                             cudaMemcpyDeviceToDevice, c->stream));
+    RLB_CUDA(cudaMemcpyAsync(c->scores.p, static_cast<const double*>(s->custom_err) + d.off[type],
+                             static_cast<size_t>(n) * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
   } else {
     RLB_CUDA(rlb::launch_eval_errors(d, precision, c->one_model.as<double>(), type,
                                      c->scores.as<double>(), c->stream, &c->launches_i));

@@ -128,13 +128,21 @@ std::string cu_error(const Driver* d, CUresult r) {
 
 // The kernels compiled around the user's functor. RLB_DIMS / RLB_MD are #defined in front of it.
 const char* kKernelSource = R"SRC(
-// score = sum over live points of (thr < e) ? thr : e (ransac.h:306-309), inlier count = #(e < thr)
-// (ransac.h:319). One thread = one hypothesis; a CTA stages 128 points at a time in shared memory and
-// every lane reads the same point (broadcast). blockIdx.y = split of the point axis.
+// RLB_HYBRID: the functor is the HybridSolver concept's EvaluateModelOnPoint(model, t, i)
+// (README.md:164-208 of the reference; examples/hybrid_line_estimator.cc:100-109), i.e. it is told the data type.
+#ifdef RLB_HYBRID
+#define RLB_EVAL(m, t, p) rlb_eval_t(m, t, p)
+#else
+#define RLB_EVAL(m, t, p) rlb_eval(m, p)
+#endif
+// score = sum over live points of w_t * ((thr_t < e) ? thr_t : e) (ransac.h:306-309, hybrid_ransac.h:416-418),
+// inlier count = #(e < thr_t) (ransac.h:319). One thread = one hypothesis; a CTA stages 128 points at a time in
+// shared memory and every lane reads the same point (broadcast). blockIdx.y = split of the PADDED point axis:
+// type 0 lives at [0, n0), type 1 at [off1, off1 + n1), off1 a multiple of 1024, so a chunk of 128 has one type.
 extern "C" __global__ void __launch_bounds__(128)
-rlb_custom_sweep(const double* __restrict__ soa, int npad, int n, const double* __restrict__ models, int k,
-                 double thr, double w, double* __restrict__ part_score, int* __restrict__ part_count,
-                 int pts_per_split, int want_counts) {
+rlb_custom_sweep(const double* __restrict__ soa, int npad, int n0, int off1, int n1,
+                 const double* __restrict__ models, int k, double thr0, double thr1, double w0, double w1,
+                 double* __restrict__ part_score, int* __restrict__ part_count, int pts_per_split, int want_counts) {
   __shared__ double tile[RLB_DIMS][128];
   const int tid = threadIdx.x;
   const int kk = blockIdx.x * 128 + tid;
@@ -144,45 +152,53 @@ rlb_custom_sweep(const double* __restrict__ soa, int npad, int n, const double* 
 #pragma unroll
   for (int i = 0; i < RLB_MD; ++i) m[i] = models[(size_t)src * RLB_MD + i];
   const int p0 = split * pts_per_split;
-  const int p1 = min(n, p0 + pts_per_split);
+  const int p1 = min(npad, p0 + pts_per_split);
   double s = 0.0;
   int c = 0;
   for (int base = p0; base < p1; base += 128) {
+    const int t = (n1 > 0 && base >= off1) ? 1 : 0;
+    const int cnt = max(0, min(128, (t ? off1 + n1 : n0) - base));
+    if (cnt == 0) continue;  // padding between the types / behind the last one (uniform for the CTA)
+    const double thr = t ? thr1 : thr0;
     const int g = base + tid;
 #pragma unroll
-    for (int d = 0; d < RLB_DIMS; ++d) tile[d][tid] = g < p1 ? soa[(size_t)d * npad + g] : 0.0;
+    for (int d = 0; d < RLB_DIMS; ++d) tile[d][tid] = tid < cnt ? soa[(size_t)d * npad + g] : 0.0;
     __syncthreads();
-    const int cnt = min(128, p1 - base);
+    double sc = 0.0;
     for (int j = 0; j < cnt; ++j) {
       double p[RLB_DIMS];
 #pragma unroll
       for (int d = 0; d < RLB_DIMS; ++d) p[d] = tile[d][j];
-      const double e = rlb_eval(m, p);
-      s += (thr < e) ? thr : e;
+      const double e = RLB_EVAL(m, t, p);
+      sc += (thr < e) ? thr : e;
       c += (e < thr) ? 1 : 0;
     }
+    s += sc * (t ? w1 : w0);
     __syncthreads();
   }
   if (kk < k) {
-    part_score[(size_t)split * k + kk] = s * w;
+    part_score[(size_t)split * k + kk] = s;
     if (want_counts) part_count[(size_t)split * k + kk] = c;
   }
 }
 
-// err[i] = rlb_eval(model, point i) for i < n; the padding is never read as live by the compaction
+// err[i] = functor(model, type of i, point i) for the live points; the padding is never read as live by the
+// compaction
 extern "C" __global__ void __launch_bounds__(256)
-rlb_custom_errors(const double* __restrict__ soa, int npad, int n, const double* __restrict__ model,
-                  double* __restrict__ err) {
+rlb_custom_errors(const double* __restrict__ soa, int npad, int n0, int off1, int n1,
+                  const double* __restrict__ model, double* __restrict__ err) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= npad) return;
+  const int t = (n1 > 0 && i >= off1) ? 1 : 0;
+  const bool live = t ? (i - off1 < n1) : (i < n0);
   double e = 0.0;
-  if (i < n) {
+  if (live) {
     double m[RLB_MD], p[RLB_DIMS];
 #pragma unroll
     for (int j = 0; j < RLB_MD; ++j) m[j] = model[j];
 #pragma unroll
     for (int d = 0; d < RLB_DIMS; ++d) p[d] = soa[(size_t)d * npad + i];
-    e = rlb_eval(m, p);
+    e = RLB_EVAL(m, t, p);
   }
   err[i] = e;
 }
@@ -190,21 +206,22 @@ rlb_custom_errors(const double* __restrict__ soa, int npad, int n, const double*
 
 }  // namespace
 
-// n x dims row-major -> [dims][npad] channel-major, zero padded
-__global__ void custom_repack_kernel(const double* __restrict__ raw, int n, int dims, int npad,
-                                     double* __restrict__ soa) {
-  const int total = npad * dims;
+// One data type: n rows of `width` doubles -> channels [0, dims) of the segment [off, off + span) of the
+// [dims][npad] channel-major array; channels >= width and rows >= n are zero.
+__global__ void custom_repack_kernel(const double* __restrict__ raw, int n, int width, int dims, int npad, int off,
+                                     int span, double* __restrict__ soa) {
+  const int total = span * dims;
   for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
-    const int c = g / npad, i = g - c * npad;
-    soa[g] = i < n ? raw[static_cast<size_t>(i) * dims + c] : 0.0;
+    const int c = g / span, i = g - c * span;
+    soa[static_cast<size_t>(c) * npad + off + i] = (i < n && c < width) ? raw[static_cast<size_t>(i) * width + c] : 0.0;
   }
 }
 
-cudaError_t launch_custom_repack(const double* raw, int n, int dims, int npad, double* soa, cudaStream_t st,
-                                 int* launches) {
+cudaError_t launch_custom_repack(const double* raw, int n, int width, int dims, int npad, int off, int span,
+                                 double* soa, cudaStream_t st, int* launches) {
   ++*launches;
-  const int blocks = max(1, min(2048, (npad * dims + 255) / 256));
-  custom_repack_kernel<<<blocks, 256, 0, st>>>(raw, n, dims, npad, soa);
+  const int blocks = max(1, min(2048, (span * dims + 255) / 256));
+  custom_repack_kernel<<<blocks, 256, 0, st>>>(raw, n, width, dims, npad, off, span, soa);
   return cudaGetLastError();
 }
 
@@ -217,11 +234,12 @@ struct CustomModule {
 
 // Compiles `src` (+ the kernels above) to an sm_100a cubin. Needs no device. On failure *err holds the
 // NVRTC log, so a typo in the functor reads like a compiler error.
-bool custom_compile(const char* src, int dims, int md, std::string* cubin, std::string* err) {
+bool custom_compile(const char* src, int dims, int md, bool hybrid, std::string* cubin, std::string* err) {
   const Nvrtc* n = nvrtc(err);
   if (!n) return false;
-  char defs[128];
-  snprintf(defs, sizeof(defs), "#define RLB_DIMS %d\n#define RLB_MD %d\n", dims, md);
+  char defs[160];
+  snprintf(defs, sizeof(defs), "#define RLB_DIMS %d\n#define RLB_MD %d\n%s", dims, md,
+           hybrid ? "#define RLB_HYBRID 1\n" : "");
   std::string full = std::string(defs) + src + "\n" + kKernelSource;
   nvrtcProgram prog = nullptr;
   nvrtcResult r = n->CreateProgram(&prog, full.c_str(), "rlb_custom_functor.cu", 0, nullptr, nullptr);
@@ -285,12 +303,13 @@ bool launch_custom_sweep(const CustomModule* m, const DeviceData& d, const Sweep
   if (!drv) return false;
   ++*launches;
   const double* soa = d.soa64;
-  int npad = d.npad, n = d.n[0], k = a.k, pps = pts_per_split, wc = a.want_counts;
+  int npad = d.npad, n0 = d.n[0], off1 = d.off[1], n1 = (d.num_types > 1) ? d.n[1] : 0, k = a.k, pps = pts_per_split,
+      wc = a.want_counts;
   const double* models = a.models;
-  double thr = a.thr[0], w = a.w[0];
+  double thr0 = a.thr[0], thr1 = a.thr[1], w0 = a.w[0], w1 = a.w[1];
   double* ps = a.part_score;
   int* pc = a.part_count;
-  void* args[] = {&soa, &npad, &n, &models, &k, &thr, &w, &ps, &pc, &pps, &wc};
+  void* args[] = {&soa, &npad, &n0, &off1, &n1, &models, &k, &thr0, &thr1, &w0, &w1, &ps, &pc, &pps, &wc};
   const CUresult r = drv->LaunchKernel(m->sweep, (a.k + 127) / 128, a.n_splits, 1, 128, 1, 1, 0,
                                        reinterpret_cast<CUstream>(st), args, nullptr);
   if (r != 0) {
@@ -306,8 +325,8 @@ bool launch_custom_errors(const CustomModule* m, const DeviceData& d, const doub
   if (!drv) return false;
   ++*launches;
   const double* soa = d.soa64;
-  int npad = d.npad, n = d.n[0];
-  void* args[] = {&soa, &npad, &n, &d_model, &d_err};
+  int npad = d.npad, n0 = d.n[0], off1 = d.off[1], n1 = (d.num_types > 1) ? d.n[1] : 0;
+  void* args[] = {&soa, &npad, &n0, &off1, &n1, &d_model, &d_err};
   const CUresult r = drv->LaunchKernel(m->errors, (d.npad + 255) / 256, 1, 1, 256, 1, 1, 0,
                                        reinterpret_cast<CUstream>(st), args, nullptr);
   if (r != 0) {

@@ -225,11 +225,11 @@ inline int model_size_of(const DeviceData& d) {
 
 // user-defined functors (custom_functor.cu)
 struct CustomModule;
-bool custom_compile(const char* src, int dims, int md, std::string* cubin, std::string* err);
+bool custom_compile(const char* src, int dims, int md, bool hybrid, std::string* cubin, std::string* err);
 CustomModule* custom_load(const std::string& cubin, int dims, int md, std::string* err);
 void custom_unload(CustomModule* m);
-cudaError_t launch_custom_repack(const double* raw, int n, int dims, int npad, double* soa, cudaStream_t st,
-                                 int* launches);
+cudaError_t launch_custom_repack(const double* raw, int n, int width, int dims, int npad, int off, int span,
+                                 double* soa, cudaStream_t st, int* launches);
 bool launch_custom_sweep(const CustomModule* m, const DeviceData& d, const SweepArgs& a, int pts_per_split,
                          cudaStream_t st, int* launches, std::string* err);
 bool launch_custom_errors(const CustomModule* m, const DeviceData& d, const double* d_model, double* d_err,

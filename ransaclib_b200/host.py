@@ -183,7 +183,7 @@ def pose_minimal_solver(fx, fy, sq_thr, points2D, points3D, samples, device=0):
 
 
 def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, device=0, precision=-1,
-                         sampling_weights=None):
+                         sampling_weights=None, custom_functor=False):
     """HybridLocallyOptimizedMSAC<Line, ., HybridLineEstimator[, Sampler]>::EstimateModel. sampling_weights =
     (w0, w1) per-point weights selects HybridBiasedSampling (reference hybrid_sampling.h:146-223) as the Sampler."""
     xy0 = _capi.f64a(xy0, (-1, 2))
@@ -193,7 +193,11 @@ def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, dev
     model = np.zeros(3)
     a = np.zeros(max(len(xy0), 1), np.int32)
     b = np.zeros(max(len(p1), 1), np.int32)
-    if sampling_weights is None:
+    if custom_functor:  # examples/hybrid_custom_line_estimator.h: the residual reaches the GPU as source
+        _check(_load().rlbh_hybrid_lomsac_line_custom(C.byref(o), device, precision, len(xy0), _capi.ptr(xy0),
+                                                      len(p1), _capi.ptr(p1), _capi.ptr(pr), _capi.ptr(model),
+                                                      C.byref(st), _capi.ptr(a), _capi.ptr(b)))
+    elif sampling_weights is None:
         _check(_load().rlbh_hybrid_lomsac_line(C.byref(o), device, precision, len(xy0), _capi.ptr(xy0), len(p1),
                                                _capi.ptr(p1), _capi.ptr(pr), _capi.ptr(model), C.byref(st),
                                                _capi.ptr(a), _capi.ptr(b)))

@@ -136,3 +136,107 @@ def test_custom_rejects_device_solvers_and_bad_source(ctx):
     with pytest.raises(Exception) as ei:
         ctx.custom_scorer(xy, 3, "__device__ double rlb_eval(const double* m, const double* p) { return oops; }")
     assert "oops" in str(ei.value)
+
+
+# ------------------------------------------------------------------ two data types (the HybridSolver concept)
+HYBRID_LINE_SRC = """
+__device__ double rlb_eval_t(const double* m, int type, const double* p) {
+  const double r = m[0] * p[0] + m[1] * p[1] + m[2] * 1.0;   // hybrid_line_estimator.cc:100-109
+  return r * r;
+}
+"""
+
+# a functor that really depends on the data type: type 1 also penalises the angle between the line's normal and
+# the point's own normal
+HYBRID_NORMAL_SRC = """
+__device__ double rlb_eval_t(const double* m, int type, const double* p) {
+  const double r = m[0] * p[0] + m[1] * p[1] + m[2];
+  if (type == 0) return r * r;
+  const double c = m[0] * p[2] + m[1] * p[3];
+  return r * r + 0.01 * (1.0 - c * c);
+}
+"""
+
+
+def test_hybrid_compile_check_without_a_device():
+    import ransaclib_b200 as rlb
+
+    assert rlb.custom_compile_check(HYBRID_LINE_SRC, 4, 3) > 1000
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n0,n1", [(3000, 2500), (1024, 1), (5, 2049), (0, 700)])
+def test_hybrid_custom_line_equals_builtin_hybrid_line(ctx, n0, n1):
+    """rlb_scorer_create_custom_hybrid with the hybrid line residual against the built-in hybrid line scorer:
+    weighted scores, per-type counts, per-type ascending inlier lists, errors of both types."""
+    from ransaclib_b200 import synth
+
+    xy0, p1 = synth.hybrid_line_instance(77, max(n0 - n0 // 3, 0), n0 // 3, max(n1 - n1 // 3, 0), n1 // 3)
+    xy0, p1 = xy0[:n0], p1[:n1]
+    assert len(xy0) == n0 and len(p1) == n1
+    models = _line_models(5, 300)
+    thr, w = [1e-4, 4e-4], [2.0, 0.5]
+    sb = ctx.hybrid_line_scorer(xy0, p1)
+    sc = ctx.custom_hybrid_scorer(xy0, p1, 3, HYBRID_LINE_SRC)
+    assert sc.num_types == 2 and sc.num_data == [n0, n1]
+    s0, c0, b0, _ = sb.score_models(models, thr, weights=w)
+    s1, c1, b1, _ = sc.score_models(models, thr, weights=w)
+    np.testing.assert_allclose(s1, s0, rtol=1e-9)
+    assert c1.tolist() == c0.tolist() and b1 == b0
+    for m in (models[b0], models[1]):
+        l0, k0, sc0 = sb.get_inliers(m, thr, thr, weights=w)
+        l1, k1, sc1 = sc.get_inliers(m, thr, thr, weights=w)
+        assert k1.tolist() == k0.tolist()
+        assert [a.tolist() for a in l1] == [a.tolist() for a in l0]
+        np.testing.assert_allclose(sc1, sc0, rtol=1e-9)
+        for t, n in ((0, n0), (1, n1)):
+            if n:
+                np.testing.assert_allclose(sc.eval_errors(m, type_=t), sb.eval_errors(m, type_=t), rtol=1e-9, atol=1e-18)
+
+
+@pytest.mark.gpu
+def test_hybrid_custom_functor_sees_the_data_type(ctx):
+    rng = np.random.default_rng(3)
+    d0 = rng.uniform(-1, 1, (1500, 2))
+    d1 = np.concatenate([rng.uniform(-1, 1, (900, 2)), rng.normal(size=(900, 2))], axis=1)
+    d1[:, 2:] /= np.linalg.norm(d1[:, 2:], axis=1, keepdims=True)
+    models = _line_models(8, 64)
+    thr, w = [0.01, 0.02], [1.0, 3.0]
+    sc = ctx.custom_hybrid_scorer(d0, d1, 3, HYBRID_NORMAL_SRC)
+    s, c, bid, _ = sc.score_models(models, thr, weights=w)
+    for k in (0, 7, bid):
+        m = models[k]
+        e0 = (d0 @ m[:2] + m[2]) ** 2
+        r1 = d1[:, :2] @ m[:2] + m[2]
+        e1 = r1 ** 2 + 0.01 * (1.0 - (d1[:, 2:] @ m[:2]) ** 2)
+        want = w[0] * np.minimum(e0, thr[0]).sum() + w[1] * np.minimum(e1, thr[1]).sum()
+        np.testing.assert_allclose(s[k], want, rtol=1e-9)
+        assert c[k] == int((e0 < thr[0]).sum() + (e1 < thr[1]).sum())
+        lists, counts, _ = sc.get_inliers(m, thr)
+        assert lists[0].tolist() == np.nonzero(e0 < thr[0])[0].tolist()
+        assert lists[1].tolist() == np.nonzero(e1 < thr[1])[0].tolist()
+
+
+@pytest.mark.gpu
+def test_hybrid_solver_with_a_custom_functor_runs_like_the_builtin_one():
+    """HybridLocallyOptimizedMSAC over examples/hybrid_custom_line_estimator.h (EvaluateModelOnPoint handed over as
+    source) against the same run over the built-in HybridLineEstimator: same iterations, solver choices, LO count,
+    per-type inlier lists and model."""
+    from ransaclib_b200 import host as H
+    from ransaclib_b200 import synth
+
+    for n, seed in [(100, 42), (20000, 6)]:
+        n_out = n // 2
+        xy0, p1 = synth.hybrid_line_instance(300 + seed, n - n_out, n_out, n - n_out, n_out)
+        opts = H.HybridLORansacOptions(squared_inlier_thresholds_=[1e-4, 1e-4], data_type_weights_=[2.0, 0.5],
+                                       random_seed_=seed, min_num_iterations_=100, max_num_iterations_=10000,
+                                       max_num_iterations_per_solver_=1000)
+        m0, st0 = H.estimate_hybrid_line(opts, xy0, p1, [0.2, 0.8])
+        m1, st1 = H.estimate_hybrid_line(opts, xy0, p1, [0.2, 0.8], custom_functor=True)
+        for key in ("num_iterations_total", "num_iterations_per_solver", "best_num_inliers", "best_solver_type",
+                    "number_lo_iterations", "inlier_ratios"):
+            assert st1[key] == st0[key], key
+        np.testing.assert_allclose(st1["best_model_score"], st0["best_model_score"], rtol=1e-9)
+        np.testing.assert_allclose(m1, m0, rtol=1e-9, atol=1e-12)
+        for t in (0, 1):
+            assert st1["inlier_indices"][t].tolist() == st0["inlier_indices"][t].tolist()
