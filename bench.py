@@ -868,14 +868,16 @@ def measure_c4(args, rank, world, local, dist, steps, warmup, q_total=None):
         "e2e": {"value": e2e_value, "unit": "localizations/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                 "path": "rlb_localize_batch with pinned host buffers (pyransaclib.ransaclib_localization_batch): "
-                        "chunked upload behind a ready counter, kernel, poses + stats + inlier lists back"},
+                        "up to four chunks of queries, each chunk's grid on its own stream behind that chunk's copies "
+                        "(cudaStreamWaitEvent; no kernel waits on the host), poses + stats + inlier lists back"},
         "gpu_launches": int(launches), "clocks": clk,
-        "roofline": {"bound": "latency", "kernel": "localize_kernel", "achieved": None, "peak": None, "unit": None,
+        "roofline": {"bound": "latency", "kernel": "localize_cta_kernel", "achieved": None, "peak": None, "unit": None,
                      "frac": None, "traffic": None,
-                     "note": "control-flow kernel (one warp = one whole LO-MSAC run); per query on average "
+                     "note": "control-flow kernel (one CTA = one whole LO-MSAC run: the master warp runs the control "
+                             "flow, the four warps share every pass over the matches); per query on average "
                              "%.0f f64 passes over the matches, %.0f LM refinements, %.1f iterations, %.2f LO calls; "
-                             "ncu: profiles/history/r01e_ncu_localize.csv (issue active 22%%, fp64 pipe 11%%, stalls: "
-                             "long scoreboard / fixed-latency wait / instruction fetch)"
+                             "bound by the dependent-f64 chain of the LM refinements (62 %% of a loaded query), "
+                             "per-phase counters and the timeline of a launch: profiles/r02_localize_ab.txt"
                              % (res["passes"].mean(), res["lsq_calls"].mean(), res["num_iterations"].mean(),
                                 res["num_lo"].mean())},
         "result": {"mean_inliers": float(res["num_inliers"].mean()), "min_inliers": int(res["num_inliers"].min()),

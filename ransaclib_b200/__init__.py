@@ -6,6 +6,7 @@ this package only marshals numpy buffers. No CPU fallback exists.
 """
 from __future__ import annotations
 
+import atexit
 import ctypes as C
 import weakref
 
@@ -223,6 +224,20 @@ class Context:
         return Scorer(self, h)
 
 
+# Communicators still alive when the interpreter exits are destroyed (scorers first) BEFORE the CUDA runtime and
+# NCCL tear themselves down: a __del__ that reaches ncclCommDestroy during interpreter shutdown can crash.
+_LIVE_COMMS = weakref.WeakSet()
+
+
+@atexit.register
+def _close_live_comms():
+    for comm in list(_LIVE_COMMS):
+        try:
+            comm.close()
+        except Exception:
+            pass
+
+
 class Comm:
     """Hypothesis-sharded scoring over several GPUs with the collective inside the library (``rlb_comm``):
     ``Comm.local(ndev)`` drives ``ndev`` GPUs from this process, ``Comm.from_rank(ctx, nranks, rank, uid)`` is
@@ -233,6 +248,7 @@ class Comm:
         self._h = handle
         self._ctx = ctx  # keeps a caller-owned context alive
         self._scorers = weakref.WeakSet()
+        _LIVE_COMMS.add(self)
 
     @staticmethod
     def unique_id() -> bytes:

@@ -135,21 +135,29 @@ def test_two_gpus_one_process(case):
     sc = c0.pose_scorer(inst["points2D"], inst["points3D"], f, f)
     ref = sc.hypothesize_and_score(samples, THR)
     comm = m.Comm.local(2)
-    cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f)
-    out = cs.hypothesize_and_score(samples, THR, want_scores=True)
-    assert out["best_id"] == ref["best_id"] and out["best_score"] == ref["best_score"]
-    assert out["scores"].tolist() == ref["scores"].tolist()
-    assert comm.collective_count == 3  # the two point arrays broadcast, one all_gather
-    cs.close()
-    # every process holds the arrays: each GPU uploads half of them, the halves cross NVLink
-    cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f, root=-1)
-    out2 = cs.hypothesize_and_score(samples, THR, want_scores=True)
-    assert out2["best_id"] == ref["best_id"] and out2["scores"].tolist() == ref["scores"].tolist()
-    assert comm.collective_count == 3 + 2 * 2 + 1
-    cs.close()
-    comm.close()
-    sc.close()
-    c0.close()
+    try:
+        # (a shard of 1024 hypotheses and the whole batch of 2048 are planned with different point-axis splits:
+        # the same pairs summed in another grouping, hence 1e-12 and not bit equality for the scores)
+        def same(out):
+            assert out["best_id"] == ref["best_id"]
+            assert abs(out["best_score"] - ref["best_score"]) <= 1e-12 * abs(ref["best_score"])
+            big = ref["scores"] > 1e300
+            assert ((out["scores"] > 1e300) == big).all()
+            np.testing.assert_allclose(out["scores"][~big], ref["scores"][~big], rtol=1e-12)
+
+        cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+        same(cs.hypothesize_and_score(samples, THR, want_scores=True))
+        assert comm.collective_count == 3  # the two point arrays broadcast, one all_gather
+        cs.close()
+        # every process holds the arrays: each GPU uploads half of them, the halves cross NVLink
+        cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f, root=-1)
+        same(cs.hypothesize_and_score(samples, THR, want_scores=True))
+        assert comm.collective_count == 3 + 2 * 2 + 1
+        cs.close()
+    finally:
+        comm.close()
+        sc.close()
+        c0.close()
 
 
 @pytest.mark.parametrize("gpus", [1, 2])

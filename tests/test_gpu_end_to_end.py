@@ -307,3 +307,25 @@ def test_copying_and_borrowing_constructors_agree(monkeypatch):
     monkeypatch.setenv("RLB_HOST_COPY", "1")
     copied = runs()
     assert borrowed == copied
+
+
+def test_pose_f32_mode_far_from_the_origin_selects_the_same_models():
+    """ADVICE (round 1): the f32 sweeps' "maybe better" guard must not miss a hypothesis that is better in f64 when
+    pixel coordinates are large and the scene is far from the world origin. 8000 x 6000 images, focal 6000, depths
+    50-400, the scene 2e4 units from the origin: the f32 run (tensor-core sweep for the large batches, FFMA2 for the
+    small ones, every near-best hypothesis settled in f64) must be the f64 run, which must be the oracle's."""
+    H = host()
+    inst = synth.pose_instance(777, 3000, 3000, width=8000.0, height=6000.0, focal=6000.0, min_depth=50.0,
+                               max_depth=400.0)
+    shift = np.array([1.0e4, -2.0e4, 5.0e3])
+    p2, p3 = inst["points2D"], inst["points3D"] + shift
+    f = inst["focal"]
+    for iters in (100, 6000):
+        kw = dict(sq_thr=16.0, seed=11, min_iters=iters, max_iters=max(iters, 10000))
+        om, ost, oinl = oracle_pose(p2, p3, f, **kw)
+        opts = H.LORansacOptions(squared_inlier_threshold_=16.0, random_seed_=11, min_num_iterations_=iters,
+                                 max_num_iterations_=max(iters, 10000))
+        m64, st64 = H.estimate_pose(opts, f, f, p2, p3, precision=0)
+        check_same(st64, m64, ost, om, oinl)
+        m32, st32 = H.estimate_pose(opts, f, f, p2, p3, precision=1)
+        check_same(st32, m32, ost, om, oinl)
