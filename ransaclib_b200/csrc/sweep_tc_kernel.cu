@@ -243,14 +243,30 @@ struct TcSmem {
 
 // COUNT = false (the caller did not ask for per-hypothesis inlier counts, as ScoreModel in ransac.h
 // never does): the score is accumulated as sum min(e, thr), two instructions fewer per evaluation.
-template <bool COUNT>
-__global__ void __launch_bounds__(kTcThreads, 4)
+//
+// HALVES = 2: 256 threads. A warp can only read the TMEM lanes of its own quarter (warp % 4), so warps w and
+// w + 4 serve the SAME 32 hypotheses and split the tile's points (columns 0-15 / 16-31): every hypothesis'
+// sums live in two threads and are joined once at the end. TMEM allows four 128-column CTAs per SM, registers
+// three of these: 24 instead of 16 warps per SM. Measured (profiles/r02_tc_halves_ab.txt): SLOWER, 33.0 against
+// 27.1 ms on C5 - both forms settle at ~60 % of the issue slots, and three CTAs keep only three tiles' MMA round
+// trips in flight per SM instead of four. Kept as an A/B switch (-DRLB_TC_HALVES=2); the default is 1.
+struct TcJoin {
+  double s[128];
+  int c[128];
+};
+
+template <bool COUNT, int HALVES>
+__global__ void __launch_bounds__(128 * HALVES, HALVES == 1 ? 4 : 3)
     sweep_pose_tc_kernel(const DeviceData d, const SweepArgs a, const float* __restrict__ tiles) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   TcSmem& S = *reinterpret_cast<TcSmem*>(smem_raw);
+  constexpr int kPts = kTcTile / HALVES;  // points of a tile this thread evaluates
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
-  const int k = blockIdx.x * kTcThreads + tid;
+  const int quarter = warp & 3;            // TMEM lane quarter = hypotheses 32 quarter ... of the CTA
+  const int half = warp >> 2;              // which points of the tile (HALVES = 1: always 0)
+  const int hyp = quarter * 32 + (tid & 31);
+  const int k = blockIdx.x * 128 + hyp;
   const int split = blockIdx.y;
   const int n_live = d.n[0];
 
@@ -277,8 +293,8 @@ __global__ void __launch_bounds__(kTcThreads, 4)
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = S.tmem_base;
-  const uint32_t lane_addr = tmem + (static_cast<uint32_t>(warp * 32) << 16);
-  {
+  const uint32_t lane_addr = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+  if (half == 0) {
     // this thread's hypothesis -> its TMEM lane of each operand matrix (PoseF<float>::load arithmetic).
     // Columns [8 mat, 8 mat + 8) = [rh0 rh1 rh2 th | rl0 rl1 rl2 tl]; the same eight columns serve both
     // K steps: the second multiplies the points' lo parts, whose fourth component is 0.
@@ -334,6 +350,7 @@ __global__ void __launch_bounds__(kTcThreads, 4)
   int c = 0;
   u64 s2 = 0ull;  // COUNT = false: two running sums of min(e, thr)
   int live_in_chunk = 0;
+  const int col0 = half * kPts;  // first TMEM column / tile point of this thread's share
 
   for (int it = 0; it < ntiles; ++it) {
     const int slot = it % kTcRing;
@@ -356,22 +373,23 @@ __global__ void __launch_bounds__(kTcThreads, 4)
     mbar_wait(&S.mma_done, it & 1);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
-    const float* nu = S.ring[slot] + 512;
+    const float* nu = S.ring[slot] + 512 + col0;
     const float* nv = nu + 32;
-    // Quarter-tiles of 8 points: the TMEM loads of the next quarter are in flight while this one is
+    // Groups of 8 points: the TMEM loads of the next group are in flight while this one is
     // reduced (tcgen05.ld latency is ~110 cycles; a tile-wide load-then-wait exposed it twice per tile).
+    constexpr int kGroups = kPts / 8;
     float px[2][8], py[2][8], pz[2][8];
-    tmem_ld8(lane_addr + 32 + 0 * kTcTile, px[0]);
-    tmem_ld8(lane_addr + 32 + 1 * kTcTile, py[0]);
-    tmem_ld8(lane_addr + 32 + 2 * kTcTile, pz[0]);
+    tmem_ld8(lane_addr + 32 + 0 * kTcTile + col0, px[0]);
+    tmem_ld8(lane_addr + 32 + 1 * kTcTile + col0, py[0]);
+    tmem_ld8(lane_addr + 32 + 2 * kTcTile + col0, pz[0]);
     tmem_wait_ld8x3(px[0], py[0], pz[0]);
 #pragma unroll
-    for (int qd = 0; qd < 4; ++qd) {
+    for (int qd = 0; qd < kGroups; ++qd) {
       const int cur = qd & 1, nxt = cur ^ 1;
-      if (qd < 3) {
-        tmem_ld8(lane_addr + 32 + 0 * kTcTile + 8 * (qd + 1), px[nxt]);
-        tmem_ld8(lane_addr + 32 + 1 * kTcTile + 8 * (qd + 1), py[nxt]);
-        tmem_ld8(lane_addr + 32 + 2 * kTcTile + 8 * (qd + 1), pz[nxt]);
+      if (qd < kGroups - 1) {
+        tmem_ld8(lane_addr + 32 + 0 * kTcTile + col0 + 8 * (qd + 1), px[nxt]);
+        tmem_ld8(lane_addr + 32 + 1 * kTcTile + col0 + 8 * (qd + 1), py[nxt]);
+        tmem_ld8(lane_addr + 32 + 2 * kTcTile + col0 + 8 * (qd + 1), pz[nxt]);
       }
       // Two points per instruction (packed f32x2): TMEM columns j, j+1 land in adjacent registers.
       // 1 / pz = rsqrt(pz)^2: one MUFU, NaN for pz < 0 and +inf for pz == 0, so points behind the
@@ -398,9 +416,9 @@ __global__ void __launch_bounds__(kTcThreads, 4)
           }
         }
       }
-      if (qd < 3) tmem_wait_ld8x3(px[nxt], py[nxt], pz[nxt]);
+      if (qd < kGroups - 1) tmem_wait_ld8x3(px[nxt], py[nxt], pz[nxt]);
     }
-    live_in_chunk += max(0, min(kTcTile, n_live - (t_begin + it) * kTcTile));
+    live_in_chunk += max(0, min(kPts, n_live - ((t_begin + it) * kTcTile + col0)));
     if (((it + 1) % kTcFlush) == 0 || it + 1 == ntiles) {
       if (COUNT) {
         dacc += w * (static_cast<double>(s) + thr64 * static_cast<double>(live_in_chunk - c));
@@ -409,7 +427,7 @@ __global__ void __launch_bounds__(kTcThreads, 4)
         // every processed point added min(e, thr); padding (NaN residual) added thr and is taken out again
         float sa, sb;
         unpack2(s2, sa, sb);
-        const int processed = (it % kTcFlush + 1) * kTcTile;
+        const int processed = (it % kTcFlush + 1) * kPts;
         dacc += w * (static_cast<double>(sa) + static_cast<double>(sb) -
                      static_cast<double>(thr) * static_cast<double>(processed - live_in_chunk));
         s2 = 0ull;
@@ -427,7 +445,20 @@ __global__ void __launch_bounds__(kTcThreads, 4)
     }
   }
 
-  if (k < a.k) {
+  if (HALVES == 2) {
+    // join the two halves of every hypothesis (fixed order: first half + second half)
+    TcJoin& J = *reinterpret_cast<TcJoin*>(S.ring);  // the ring is idle now
+    if (half == 1) {
+      J.s[hyp] = dacc;
+      J.c[hyp] = dcnt;
+    }
+    __syncthreads();
+    if (half == 0) {
+      dacc += J.s[hyp];
+      dcnt += J.c[hyp];
+    }
+  }
+  if (half == 0 && k < a.k) {
     a.part_score[static_cast<size_t>(split) * a.k + k] = dacc;
     if (COUNT) a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt;
   }
@@ -918,15 +949,20 @@ int tc_tile_points() { return kTcTile; }
 size_t tc_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * kTcTileBytes + 256; }  // + bounds
 int tc_hyps_per_cta() { return kTcThreads; }
 
+#ifndef RLB_TC_HALVES
+#define RLB_TC_HALVES 1  // 1 (default): 128-thread CTAs, 4 per SM; 2: 256-thread CTAs, 3 per SM (A/B: slower, see above)
+#endif
+constexpr int kTcHalves = RLB_TC_HALVES;
+
 int tc_resident_ctas() {
   static std::atomic<int> cache[64];  // per device; 0 = not asked yet
   std::atomic<int>& cached = cache[PerDeviceOnce::device()];
   if (const int v = cached.load(std::memory_order_relaxed)) return v;
-  cudaFuncSetAttribute(sweep_pose_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaFuncSetAttribute(sweep_pose_tc_kernel<true, kTcHalves>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(TcSmem)));
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel<true>, kTcThreads, sizeof(TcSmem)) !=
-      cudaSuccess)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel<true, kTcHalves>, 128 * kTcHalves,
+                                                    sizeof(TcSmem)) != cudaSuccess)
     n = 1;
   const int v = max(1, min(n, 512 / kTcCols));  // TMEM: 512 columns per SM
   cached.store(v, std::memory_order_relaxed);
@@ -939,19 +975,19 @@ cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float
   static PerDeviceOnce configured;
   const int dev = PerDeviceOnce::device();
   if (!configured.done(dev)) {
-    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(sizeof(TcSmem)));
+    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel<true, kTcHalves>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(TcSmem)));
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(sweep_pose_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      e = cudaFuncSetAttribute(sweep_pose_tc_kernel<false, kTcHalves>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(sizeof(TcSmem)));
     if (e != cudaSuccess) return e;
     configured.set(dev);
   }
-  dim3 grid((a.k + kTcThreads - 1) / kTcThreads, a.n_splits);
+  dim3 grid((a.k + 127) / 128, a.n_splits);
   if (a.want_counts)
-    sweep_pose_tc_kernel<true><<<grid, kTcThreads, sizeof(TcSmem), st>>>(d, a, tiles);
+    sweep_pose_tc_kernel<true, kTcHalves><<<grid, 128 * kTcHalves, sizeof(TcSmem), st>>>(d, a, tiles);
   else
-    sweep_pose_tc_kernel<false><<<grid, kTcThreads, sizeof(TcSmem), st>>>(d, a, tiles);
+    sweep_pose_tc_kernel<false, kTcHalves><<<grid, 128 * kTcHalves, sizeof(TcSmem), st>>>(d, a, tiles);
   return cudaGetLastError();
 }
 
