@@ -52,6 +52,7 @@ struct rlbh_stats {
   // driver counters (not in the reference)
   uint64_t batches, hypotheses_scored, single_passes;
   double seconds;  // wall time of EstimateModel
+  uint64_t handbacks, handbacks_resumed;  // device-resident runs handed back / of those, resumed with their state
 };
 
 struct rlbh_hybrid_options {
@@ -123,6 +124,8 @@ void Run(const rlbh_options& o, Solver& solver, int precision, Model* model, rlb
   st->hypotheses_scored = counters.hypotheses_scored;
   st->single_passes = counters.single_passes;
   st->seconds = std::chrono::duration<double>(t1 - t0).count();
+  st->handbacks = counters.handbacks;
+  st->handbacks_resumed = counters.handbacks_resumed;
   if (inliers)
     for (size_t i = 0; i < rs.inlier_indices.size(); ++i) inliers[i] = rs.inlier_indices[i];
 }

@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <limits>
 #include <random>
 #include <vector>
@@ -90,7 +91,8 @@ struct GpuRunCounters {
   uint64_t hypotheses_scored = 0; // K summed over batches (includes speculation waste)
   uint64_t single_passes = 0;     // fused K=1 passes (LO, inlier collection, f64 re-scores)
   uint64_t handbacks = 0;         // device-resident runs handed back to the host-driven loop (LORansacGpuOptions)
-  uint64_t handback_iterations = 0;  // iterations those runs had done on the device (work done twice)
+  uint64_t handback_iterations = 0;  // iterations such runs had done on the device when they came back WITHOUT their state (work done twice)
+  uint64_t handbacks_resumed = 0;    // handed-back runs that came with their state and were resumed, not restarted
 };
 
 // When the device-resident driver of a solver (one CTA runs the whole problem) may hand a run back to the
@@ -138,8 +140,10 @@ class LocallyOptimizedMSAC : public RansacBase {
     const int num_data = solver.num_data();
     if (sample_size > num_data || sample_size <= 0) return 0;
 
-    // A solver may run the whole of this function on the device (gpu_scorer.h: device_lomsac).
-    if (DeviceResident(options, solver, best_model, statistics,
+    // A solver may run the whole of this function on the device (gpu_scorer.h: device_lomsac). A run that is
+    // handed back (very low inlier ratios) comes with its state and is resumed below.
+    Resume resume;
+    if (DeviceResident(options, solver, best_model, statistics, &resume,
                        std::integral_constant<bool, gpu::HasDeviceLomsac<Solver>::value &&
                                                         std::is_same<Sampler, UniformSampling<Solver> >::value>()))
       return stats.best_num_inliers;
@@ -159,6 +163,7 @@ class LocallyOptimizedMSAC : public RansacBase {
 
     Batch batch;
     uint32_t next_batch_size = 256u;
+    uint32_t first_iteration = 0u;
 
     auto refresh_termination = [&]() {  // ransac.h:170-177, 231-238
       stats.best_num_inliers = CollectInliers(solver, *best_model, thr, &stats.inlier_indices);
@@ -168,10 +173,31 @@ class LocallyOptimizedMSAC : public RansacBase {
                                                options.max_num_iterations_);
     };
 
-    for (stats.num_iterations = 0u; stats.num_iterations < max_iters; ++stats.num_iterations) {
+    if (resume.valid) {
+      // Continue the device-resident run: the sampler's stream is a function of (seed, iteration), so the
+      // samples it already consumed are drawn again and dropped (32 ns each); the local optimisation's engine,
+      // the best models and the LO count come from the record.
+      std::vector<int> dropped;
+      for (uint32_t i = 0; i < resume.iterations; ++i) sampler.Sample(&dropped);
+      rng.SetState(resume.lo_block, resume.lo_pos);
+      best_minimal_score = resume.best_minimal_score;
+      if (best_minimal_score < kNever) Solver::UnpackModel(resume.best_minimal_model, &best_minimal_model);
+      stats.best_model_score = resume.best_score;
+      stats.number_lo_iterations = resume.num_lo;
+      if (resume.best_score < kNever) {
+        Solver::UnpackModel(resume.best_model, best_model);
+        refresh_termination();  // inlier list, ratio and iteration bound of the best model (ransac.h:231-238)
+      }
+      first_iteration = resume.iterations;
+      next_batch_size = 4096u;  // a handed-back run needs thousands of hypotheses
+    }
+
+    for (stats.num_iterations = first_iteration; stats.num_iterations < max_iters; ++stats.num_iterations) {
       const uint32_t it = stats.num_iterations;
       // LO on the best model so far once the start iteration is reached (ransac.h:163-178).
-      if (it == options.lo_starting_iterations_ && best_minimal_score < kNever) {
+      // (a resumed run has already been through this check for its first iteration on the device)
+      if (it == options.lo_starting_iterations_ && best_minimal_score < kNever &&
+          !(resume.valid && it == first_iteration)) {
         ++stats.number_lo_iterations;
         LocalOptimization(options, solver, &rng, best_model, &stats.best_model_score);
         refresh_termination();
@@ -254,13 +280,28 @@ class LocallyOptimizedMSAC : public RansacBase {
   }
 
  protected:
-  bool DeviceResident(const LORansacOptions&, const Solver&, Model*, RansacStatistics*, std::false_type) const {
+  // State of a device-resident run that was handed back (rlb_lomsac_resume_record, ransaclib_b200.h).
+  struct Resume {
+    bool valid = false;
+    uint32_t iterations = 0u;
+    int num_lo = 0;
+    int lo_pos = 624;
+    double best_score = std::numeric_limits<double>::max();
+    double best_minimal_score = std::numeric_limits<double>::max();
+    double best_model[16] = {0.0};
+    double best_minimal_model[16] = {0.0};
+    uint32_t lo_block[624];
+  };
+
+  bool DeviceResident(const LORansacOptions&, const Solver&, Model*, RansacStatistics*, Resume*,
+                      std::false_type) const {
     return false;
   }
+  static int dev_model_doubles(const Solver& solver) { return solver.device_scorer().model_size(); }
   // One launch: sampler, minimal solver, scoring, local optimisation and refits all run on the
   // device (same sequence of decisions as the loop above; csrc/line_lomsac_kernel.cu).
   bool DeviceResident(const LORansacOptions& options, const Solver& solver, Model* best_model,
-                      RansacStatistics* statistics, std::true_type) const {
+                      RansacStatistics* statistics, Resume* resume, std::true_type) const {
     if (gpu::HostDriverForced()) return false;
     rlb_lomsac_options o;
     o.min_iters = options.min_num_iterations_;
@@ -287,9 +328,38 @@ class LocallyOptimizedMSAC : public RansacBase {
     if (!solver.device_lomsac(o, options.random_seed_, packed, &r, &inliers)) return false;
     RansacStatistics& stats = *statistics;
     if (r.success == 2) {
+      // handed back: with its state (resumed by the caller) or, for tiny problems, without (the run restarts)
+      const bool has_state = r.num_inliers == RLB_LOMSAC_RESUME_WORDS &&
+                             static_cast<int>(inliers.size()) >= RLB_LOMSAC_RESUME_WORDS &&
+                             inliers[0] == RLB_LOMSAC_RESUME_MAGIC && dev_model_doubles(solver) <= 3;
+      if (has_state) {
+        const int* rec = inliers.data();
+        auto dbl = [&](int word) {
+          const uint64_t bits = static_cast<uint64_t>(static_cast<uint32_t>(rec[word])) |
+                                (static_cast<uint64_t>(static_cast<uint32_t>(rec[word + 1])) << 32);
+          double v;
+          std::memcpy(&v, &bits, sizeof(v));
+          return v;
+        };
+        resume->valid = true;
+        resume->iterations = static_cast<uint32_t>(rec[1]);
+        resume->num_lo = rec[2];
+        resume->lo_pos = rec[3];
+        resume->best_score = dbl(4);
+        resume->best_minimal_score = dbl(12);
+        for (int i = 0; i < 3; ++i) {
+          resume->best_model[i] = dbl(6 + 2 * i);
+          resume->best_minimal_model[i] = dbl(14 + 2 * i);
+        }
+        for (int i = 0; i < 624; ++i) resume->lo_block[i] = static_cast<uint32_t>(rec[20 + i]);
+      }
       if (counters) {
         counters->handbacks += 1;
-        counters->handback_iterations += r.num_iterations;
+        if (has_state) {
+          counters->handbacks_resumed += 1;
+        } else {
+          counters->handback_iterations += r.num_iterations;
+        }
       }
       return false;
     }

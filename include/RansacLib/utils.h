@@ -94,6 +94,15 @@ class Mt19937 {
     for (; z > 0; --z) (*this)();
   }
 
+  // Continue another engine's stream: `block` = the 624 state words of its current block (after the twist that
+  // produced it), `pos` = how many of them have been drawn (624: the next draw twists first; the state right
+  // after seed() is pos = 624 as well). What a device-resident run hands back (rlb_lomsac_resume_record).
+  void SetState(const uint32_t* block, const int pos) {
+    for (int k = 0; k < 624; ++k) state_[k] = block[k];
+    TemperBlock();
+    idx_ = pos;
+  }
+
   // std::uniform_int_distribution<int>(0, range - 1) of libstdc++ (GCC >= 11) on this engine:
   // Lemire's multiply-shift with rejection.
   uint32_t Below(const uint32_t range) {
@@ -139,15 +148,18 @@ class Mt19937 {
     for (int k = 0; k < 227; ++k) s[k] = Twist(s[k], s[k + 1], s[k + 397]);
     for (int k = 227; k < 623; ++k) s[k] = Twist(s[k], s[k + 1], s[k - 227]);
     s[623] = Twist(s[623], s[0], s[396]);
+    TemperBlock();
+    idx_ = 0;
+  }
+  void TemperBlock() {
     for (int k = 0; k < 624; ++k) {
-      uint32_t y = s[k];
+      uint32_t y = state_[k];
       y ^= y >> 11;
       y ^= (y << 7) & 0x9d2c5680u;
       y ^= (y << 15) & 0xefc60000u;
       y ^= y >> 18;
       out_[k] = y;
     }
-    idx_ = 0;
   }
   static uint32_t Twist(const uint32_t a, const uint32_t b, const uint32_t src) {
     const uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);

@@ -46,10 +46,12 @@ extern "C" {
 #define RLB_F64 0 /* reference-exact semantics, scores within 1e-9 rel */
 #define RLB_F32 1 /* recentred f32 inner sums, f64 outer sums; within 1e-4 rel */
 /* RLB_F64 on pose batches of >= 512 hypotheses classifies every (hypothesis, point) pair in f32 first and
+ * (when K x N >= 2^28: below that one launch of the plain sweep is cheaper than the filtered sweep's four)
  * evaluates in f64 only the pairs that could be inliers; a clear outlier adds exactly thr either way
  * (ransac.h:306-309). Counts are those of the plain f64 sweep, scores agree to 1e-12. RLB_F64_PLAIN evaluates
  * every pair in f64 (the round-1 kernel; also what RLB_F64 runs for lines and small batches). */
 #define RLB_F64_PLAIN 2
+#define RLB_F64_FILTERED 3 /* the filtered sweep whatever the batch size (RLB_F64 picks it from K x N >= 2^28) */
 
 #define RLB_KIND_LINE 0        /* examples/line_estimator */
 #define RLB_KIND_HYBRID_LINE 1 /* examples/hybrid_line_estimator (2 data types) */
@@ -325,6 +327,18 @@ typedef struct rlb_localize_options {
   uint32_t handback_after;
   uint32_t handback_min_remaining;
 } rlb_localize_options;
+
+/* A handed-back run carries its state: when an inlier buffer was passed and the problem has at least
+ * RLB_LOMSAC_RESUME_WORDS points, result.num_inliers = RLB_LOMSAC_RESUME_WORDS and the problem's slice of the
+ * inlier buffer holds (int32 words)
+ *   [0] RLB_LOMSAC_RESUME_MAGIC  [1] iterations done  [2] number_lo_iterations  [3] position of the local
+ *   optimisation's std::mt19937 inside its block (0..624)  [4..11] best_model_score, *best_model (a, b, c)
+ *   [12..19] score and coefficients of the best minimal model (doubles as lo, hi words)  [20..643] the 624 words
+ *   of that engine's current block
+ * so that the caller resumes at that iteration (the sampler is a function of seed and iteration: replay it)
+ * instead of starting over. Otherwise result.num_inliers = 0: start over (same run either way). */
+#define RLB_LOMSAC_RESUME_WORDS 644
+#define RLB_LOMSAC_RESUME_MAGIC 0x524c4231
 
 typedef struct rlb_localize_result {
   int32_t success;        /* 0 for queries with <= 3 matches (ransaclib_localization.cc:86-92) */

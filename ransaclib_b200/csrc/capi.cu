@@ -281,10 +281,11 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
               BestRec* d_best, double* d_best_model) {
   rlb_ctx* c = s->ctx;
   const DeviceData& d = s->d;
-  if (precision != RLB_F64 && precision != RLB_F32 && precision != RLB_F64_PLAIN)
+  if (precision != RLB_F64 && precision != RLB_F32 && precision != RLB_F64_PLAIN && precision != RLB_F64_FILTERED)
     return fail(RLB_E_ARG, "bad precision %d", precision);
-  const bool plain64 = (precision == RLB_F64_PLAIN);  // f64 without the f32 pre-classification
-  if (plain64) precision = RLB_F64;
+  const bool plain64 = (precision == RLB_F64_PLAIN);        // f64 without the f32 pre-classification
+  const bool filtered64 = (precision == RLB_F64_FILTERED);  // ... with it, whatever the size of the batch
+  if (plain64 || filtered64) precision = RLB_F64;
   if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
   if (!thr) return fail(RLB_E_ARG, "sq_thr is required");
   {
@@ -396,8 +397,12 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
   }();
   bool use_tc = false;
   const bool tc_f32 = precision == RLB_F32 && (forced_variant == 9 || (forced_variant < 0 && k >= 512));
+  // (four launches instead of one: only where the plain sweep would take a few hundred microseconds or more -
+  // configs[1]'s batches of <= 8192 hypotheses x 10k points stay with it)
   const bool tc_f64 = precision == RLB_F64 && !plain64 && a.thr[0] > 0.0 &&
-                      (forced_variant == 11 || (forced_variant < 0 && f64_filter && k >= 512));
+                      (forced_variant == 11 || (filtered64 && d.kind == RLB_KIND_POSE) ||
+                       (forced_variant < 0 && f64_filter && k >= 512 &&
+                        static_cast<long long>(k) * d.n[0] >= (1LL << 28)));
   if (d.kind == RLB_KIND_POSE && (tc_f32 || tc_f64)) {
     const int total_tiles = d.npad / rlb::tc_tile_points();
     const int slots = c->sms * (tc_f64 ? rlb::tcx_resident_ctas() : rlb::tc_resident_ctas());
@@ -426,7 +431,7 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
         tc_tps = tp;
       }
     }
-    if (forced_variant == 9 || forced_variant == 11 || best > best_score) {
+    if (forced_variant == 9 || forced_variant == 11 || filtered64 || best > best_score) {
       use_tc = true;
       a.variant = tc_f64 ? 11 : 9;
       a.n_splits = splits = tc_splits;

@@ -54,6 +54,9 @@ constexpr unsigned kFull = 0xffffffffu;
 constexpr double kNever = DBL_MAX;
 constexpr int kFirstBatch = 128;
 constexpr int kSuper = kT * 32;  // points per ordered-compaction round (one 32-bit mask per lane)
+// hand-back record (include/ransaclib_b200.h: rlb_lomsac_resume_record), in int32 words
+constexpr int kResumeWords = RLB_LOMSAC_RESUME_WORDS;
+constexpr int32_t kResumeMagic = RLB_LOMSAC_RESUME_MAGIC;
 
 struct Line {
   double a, b, c;
@@ -79,6 +82,7 @@ struct __align__(16) Shared {
   int n;
   rlb_localize_options opt;
   int32_t* list_best;  // stats.inlier_indices
+  int list_best_is_output;  // list_best is the caller's inlier buffer (it comes back to the host)
   int32_t* list_base;  // LocalOptimization's inliers_base
   int32_t* list_fit;   // inliers of the current fit / scratch
   int mt_cur[2], mt_idx[2];  // per engine: which half holds the current state, next word to temper
@@ -726,9 +730,32 @@ __device__ Line run_problem(Shared& sh, const Line initial, rlb_localize_result*
         // One SM sweeps ~7 hypothesis x point evaluations per cycle; a run that still needs thousands
         // of hypotheses is better served by the whole-GPU sweep of the host-driven loop. The caller
         // allowed handing it back (same run from scratch there: results do not depend on the driver).
+        // The state goes with it (rlb_lomsac_resume_record in the caller's inlier buffer), so that the caller
+        // resumes at iteration `it` instead of starting over: the local optimisation's engine (position included),
+        // both best models and their scores, the LO count. The sampler is a pure function of (seed, it): replayed.
+        int rec_words = 0;
+        if (sh.list_best_is_output && n >= kResumeWords) {
+          rec_words = kResumeWords;
+          int32_t* rec = sh.list_best;
+          const uint32_t* st = sh.mt[1] + sh.mt_cur[1] * 624;
+          for (int i = threadIdx.x; i < 624; i += kT) rec[20 + i] = static_cast<int32_t>(st[i]);
+          if (threadIdx.x == 0) {
+            rec[0] = kResumeMagic;
+            rec[1] = static_cast<int32_t>(it);
+            rec[2] = num_lo;
+            rec[3] = sh.mt_idx[1];
+            const double dv[8] = {best.score, best.m.a, best.m.b, best.m.c,
+                                  best_minimal.score, best_minimal.m.a, best_minimal.m.b, best_minimal.m.c};
+            for (int i = 0; i < 8; ++i) {
+              const long long bits = __double_as_longlong(dv[i]);
+              rec[4 + 2 * i] = static_cast<int32_t>(bits & 0xffffffffLL);
+              rec[5 + 2 * i] = static_cast<int32_t>(bits >> 32);
+            }
+          }
+        }
         if (threadIdx.x == 0) {
           res->success = 2;
-          res->num_inliers = 0;
+          res->num_inliers = rec_words;
           res->num_iterations = it;
           res->num_lo = num_lo;
           res->score = kNever;
@@ -867,6 +894,7 @@ __global__ void __launch_bounds__(kT, 1) line_lomsac_kernel(const LineLomsacArgs
       sh.list_base = lists;
       sh.list_fit = lists + A.nmax;
       sh.list_best = (A.inliers != nullptr) ? A.inliers + o0 : lists + 2 * A.nmax;
+      sh.list_best_is_output = (A.inliers != nullptr) ? 1 : 0;
       sh.passes = 0;
       sh.lsq_calls = 0;
       for (int i = 0; i < 16; ++i) sh.prof[i] = 0;

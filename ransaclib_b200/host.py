@@ -26,7 +26,8 @@ class _Stats(C.Structure):
     _fields_ = [("num_iterations", C.c_uint32), ("best_num_inliers", C.c_int32),
                 ("best_model_score", C.c_double), ("inlier_ratio", C.c_double),
                 ("number_lo_iterations", C.c_int32), ("found", C.c_int32), ("batches", C.c_uint64),
-                ("hypotheses_scored", C.c_uint64), ("single_passes", C.c_uint64), ("seconds", C.c_double)]
+                ("hypotheses_scored", C.c_uint64), ("single_passes", C.c_uint64), ("seconds", C.c_double),
+                ("handbacks", C.c_uint64), ("handbacks_resumed", C.c_uint64)]
 
 
 class _HybridOptions(C.Structure):
@@ -130,7 +131,7 @@ def _stats_dict(st, inliers):
             "number_lo_iterations": st.number_lo_iterations, "found": bool(st.found),
             "inlier_indices": inliers[:st.best_num_inliers].copy(), "batches": st.batches,
             "hypotheses_scored": st.hypotheses_scored, "single_passes": st.single_passes,
-            "seconds": st.seconds}
+            "seconds": st.seconds, "handbacks": st.handbacks, "handbacks_resumed": st.handbacks_resumed}
 
 
 def estimate_line(options: LORansacOptions, xy, device=0, precision=-1):

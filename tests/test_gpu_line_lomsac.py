@@ -209,6 +209,8 @@ def test_long_runs_are_handed_back_when_allowed(ctx):
     init = np.array([1.0, 2.0, 3.0])
     line, r, _ = sc.line_lomsac(ctx.lomsac_options(handback_after=384, handback_min_remaining=3000, **kw), 11, line=init)
     assert r["success"] == 2 and line.tolist() == init.tolist() and 384 <= r["num_iterations"] < 1024
+    # ... with its state (rlb_lomsac_resume_record): magic, the iteration, the LO engine's position
+    assert r["num_inliers"] == 644 and int(_[0]) == 0x524c4231 and int(_[1]) == r["num_iterations"] and 0 <= _[3] <= 624
     line, r, inl = sc.line_lomsac(ctx.lomsac_options(**kw), 11)  # not allowed to hand back: runs to the end
     assert r["success"] == 1 and r["num_iterations"] == ost.num_iterations and inl.tolist() == oinl.tolist()
     sc.close()
@@ -216,8 +218,22 @@ def test_long_runs_are_handed_back_when_allowed(ctx):
                              max_num_iterations_=100000)
     m, st = H.estimate_line(opts, xy)
     assert st["batches"] > 0  # the host-driven loop finished it
+    assert st["handbacks"] == 1 and st["handbacks_resumed"] == 1  # from where the device left off, not from scratch
     assert st["num_iterations"] == ost.num_iterations and st["inlier_indices"].tolist() == oinl.tolist()
+    assert st["number_lo_iterations"] == ost.number_lo_iterations
     np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(st["best_model_score"], ost.best_model_score, rtol=1e-9)
+    # hand-backs at other points of the run (before / after the first local optimisation, LO start inside the
+    # device part) resume to the same run
+    for seed, lo_start in ((3, 50), (5, 500), (8, 384), (13, 20)):
+        om, ost, oinl = oracle_line(xy, seed, lo_start=lo_start, **kw)
+        o2 = H.LORansacOptions(squared_inlier_threshold_=1e-4, random_seed_=seed, min_num_iterations_=100,
+                               max_num_iterations_=100000, lo_starting_iterations_=lo_start)
+        m, st = H.estimate_line(o2, xy)
+        assert st["handbacks_resumed"] == 1, (seed, lo_start)
+        assert st["num_iterations"] == ost.num_iterations and st["number_lo_iterations"] == ost.number_lo_iterations
+        assert st["inlier_indices"].tolist() == oinl.tolist()
+        np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
 
 
 def test_large_problems_stay_with_the_host_driven_loop():

@@ -389,8 +389,8 @@ def test_tensor_core_sweep_edges(ctx, n):
 
 @pytest.mark.parametrize("n", [5, 33, 700, 4097, 70_000])
 def test_filtered_f64_sweep_equals_the_plain_f64_sweep(ctx, n):
-    """RLB_F64 on >= 512 pose hypotheses: f32 classification on the tensor cores, f64 only for the pairs that could
-    be inliers (sweep variant 11). Counts must be those of the plain f64 sweep (RLB_F64_PLAIN) exactly, scores to
+    """RLB_F64_FILTERED (what RLB_F64 runs for pose batches of K x N >= 2^28): f32 classification on the tensor
+    cores, f64 only for the pairs that could be inliers (sweep variant 11). Counts must be those of the plain f64 sweep (RLB_F64_PLAIN) exactly, scores to
     1e-12 (fixed-point sums), both within 1e-9 of the oracle; good, bad, behind-the-camera, invalid, non-finite
     and grazing hypotheses (camera centre inside the point cloud: depths around zero)."""
     n_in = max(3, n // 2)
@@ -419,7 +419,7 @@ def test_filtered_f64_sweep_equals_the_plain_f64_sweep(ctx, n):
     models[61, 10] = np.inf
     s_p, c_p, bid_p, _ = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64_PLAIN)
     assert ctx.last_sweep_plan()[0] != 11
-    s_f, c_f, bid_f, _ = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64)
+    s_f, c_f, bid_f, _ = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64_FILTERED)
     assert ctx.last_sweep_plan()[0] == 11
     assert c_f.tolist() == c_p.tolist()
     fin = np.isfinite(s_p) & (s_p < 1e300)
@@ -435,12 +435,12 @@ def test_filtered_f64_sweep_equals_the_plain_f64_sweep(ctx, n):
     # other thresholds (tiny: the band is relatively wide; huge: nearly everything is evaluated in f64)
     for thr in (0.25, 1e4):
         a = sc.score_models(models, thr, valid=valid, precision=rlb().RLB_F64_PLAIN)
-        b = sc.score_models(models, thr, valid=valid, precision=rlb().RLB_F64)
+        b = sc.score_models(models, thr, valid=valid, precision=rlb().RLB_F64_FILTERED)
         assert a[1].tolist() == b[1].tolist() and a[2] == b[2]
         fin = np.isfinite(a[0]) & (a[0] < 1e300)
         np.testing.assert_allclose(b[0][fin], a[0][fin], rtol=1e-12)
     # bit-reproducible
-    again = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64)
+    again = sc.score_models(models, 144.0, valid=valid, precision=rlb().RLB_F64_FILTERED)
     assert np.array_equal(again[0], s_f, equal_nan=True)
 
 
@@ -457,7 +457,7 @@ def test_filtered_f64_sweep_far_from_the_origin(ctx):
     models = synth.perturbed_poses(9, inst["R_gt"], inst["c_gt"] + shift, 1024, rot_sigma=0.002, trans_sigma=0.5)
     for thr in (4.0, 144.0):
         a = sc.score_models(models, thr, precision=rlb().RLB_F64_PLAIN)
-        b = sc.score_models(models, thr, precision=rlb().RLB_F64)
+        b = sc.score_models(models, thr, precision=rlb().RLB_F64_FILTERED)
         assert ctx.last_sweep_plan()[0] == 11
         assert a[1].tolist() == b[1].tolist() and a[2] == b[2]
         np.testing.assert_allclose(b[0], a[0], rtol=1e-12)
@@ -465,6 +465,20 @@ def test_filtered_f64_sweep_far_from_the_origin(ctx):
     ws, wc = ol.pose_score(O, f, f, p2, p3, models[:64], 144.0)
     np.testing.assert_allclose(b[0][:64], ws, rtol=F64_RTOL)
     assert b[1][:64].tolist() == wc.tolist()
+
+
+def test_f64_picks_the_filtered_sweep_by_size(ctx):
+    """RLB_F64 = the plain f64 sweep for small batches (one launch), the filtered one from K x N >= 2^28."""
+    inst = synth.pose_instance(91, 150_000, 150_000)
+    f = inst["focal"]
+    sc = ctx.pose_scorer(inst["points2D"], inst["points3D"], f, f)
+    models = synth.perturbed_poses(2, inst["R_gt"], inst["c_gt"], 1024)
+    a = sc.score_models(models[:512], 144.0)  # 512 x 300k < 2^28
+    assert ctx.last_sweep_plan()[0] != 11
+    b = sc.score_models(models, 144.0)  # 1024 x 300k >= 2^28
+    assert ctx.last_sweep_plan()[0] == 11
+    assert b[1][:512].tolist() == a[1].tolist()
+    np.testing.assert_allclose(b[0][:512], a[0], rtol=1e-12)
 
 
 def test_determinism(ctx, pose_case):
