@@ -361,7 +361,11 @@ def run_ours(args):
                         % (evals_per_launch * FLOP_PER_EVAL / algo_bytes)},
         "inlier_pass": {"bound": "hbm", "launch_ms": inl_avg_ms, "algorithmic_bytes": inl_bytes,
                         "achieved": inl_bytes / (inl_avg_ms * 1e-3) / 1e9, "peak": peaks.get("hbm_gbs"),
-                        "unit": "GB/s", "frac": inl_bytes / (inl_avg_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0)},
+                        "unit": "GB/s", "frac": inl_bytes / (inl_avg_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0),
+                        "kernel": "inlier_range_kernel<PoseF>",
+                        # dram__bytes_read + write of one launch at N = 1M (profiles/r02z_ncu_inlier_range.csv): the
+                        # 2 MB inlier list stays in L2, so the traffic is the 40 MB of f64 point channels
+                        "traffic": 40.07e6 if (args.workload == "c5" and n == 1_000_000) else None},
     }
 
     # ---- the reference-exact f64 sweep of the same workload (own leg, same run) ------
@@ -461,6 +465,9 @@ def measure_f64_leg(args, ctx, step, stream, flush, k, n, peaks):
                                       "pairs that could be inliers are re-evaluated in f64, hypotheses with many such "
                                       "pairs go to the plain f64 sweep. Same 29-flop-equivalent / FFMA-peak convention "
                                       "as the f32 line; launch_ms covers all four launches of the sweep",
+                         # dram__bytes of the sparse-list launch at K = 16,384 (profiles/r02z_ncu_tcx.csv): 72 B / point
+                         # of f32 tiles + 40 B / point of f64 channels + the [splits][K] partials
+                         "traffic_at_k16384": 121.7e6,
                          "hbm": {"algorithmic_bytes": n * 112 + k * 108,
                                  "achieved_gbs": (n * 112 + k * 108) / (sw * 1e-3) / 1e9,
                                  "peak_gbs": peaks.get("hbm_gbs")}},

@@ -1129,7 +1129,7 @@ __global__ void __launch_bounds__(kInlThreads) inlier_kernel(const DeviceData d,
 // and the exclusive offset per thread and tile in shared memory, publishes ONE count, reads the counts of the
 // CTAs below it (a flat read: at most 3 words per thread), and then writes its slice of the list. Same results
 // as inlier_kernel except for the order in which the tile scores are added (still a fixed order).
-constexpr int kInlMaxRange = 8;  // tiles per CTA (shared-memory record: 8 x 256 words)
+constexpr int kInlMaxRange = 32;  // tiles per CTA (shared-memory record: 32 x 256 words = 32 KB; ~9.7M points in one wave)
 
 // 1 (default): the next tile's loads are issued before this tile is evaluated (92 registers, 2 CTAs / SM): 18.2 us
 // for N = 1M against 21.6 us without and 24.6 us for one CTA per tile (profiles/r02_inlier_pass_ab.txt)

@@ -589,3 +589,45 @@ def test_zero_depth_falls_through_like_the_reference(ctx):
             assert want_s[0] == 144.0 and s[0] == 144.0 and score == 144.0
             assert np.isinf(err[0]) and err[0] > 0
         sc.close()
+
+
+@pytest.mark.parametrize("n", [607_000, 1_300_000, 2_600_000, 4_850_000])
+def test_inlier_pass_one_wave_of_tile_ranges(ctx, n):
+    """The K = 1 pass as one wave (inlier_range_kernel): 2 ... 8 tiles per CTA at these sizes. The list must be the
+    ascending list of the points whose error (from the independent per-point error kernel) is below the threshold,
+    the score the sum of min(e, thr), twice in a row (epoch-tagged status words) and for a threshold that keeps
+    nothing / everything."""
+    rng = np.random.default_rng(n)
+    inst = synth.pose_instance(55, 4000, 4000)
+    f = inst["focal"]
+    reps = n // 8000 + 1
+    p2 = np.tile(inst["points2D"], (reps, 1))[:n] + rng.normal(0, 0.5, (n, 2))
+    p3 = np.tile(inst["points3D"], (reps, 1))[:n]
+    sc = ctx.pose_scorer(p2, p3, f, f)
+    m = synth.pose_to_model(inst["R_gt"], inst["c_gt"])
+    err = sc.eval_errors(m)
+    for thr in (144.0, 1e-12, 1e12):
+        want = np.nonzero(err < thr)[0]
+        for _ in range(2):
+            lists, counts, score = sc.get_inliers(m, thr, thr)
+            assert counts[0] == len(want)
+            assert np.array_equal(lists[0], want.astype(np.int32))
+            np.testing.assert_allclose(score, np.minimum(err, thr).sum(), rtol=1e-12)
+    sc.close()
+
+
+def test_inlier_pass_one_wave_two_data_types(ctx):
+    """The same for the hybrid line scorer (two data types, per-type thresholds and weights, the type boundary inside
+    a CTA's tile range)."""
+    n0, n1 = 700_000, 650_000
+    xy0, p1 = synth.hybrid_line_instance(9, n0 // 2, n0 - n0 // 2, n1 // 2, n1 - n1 // 2)
+    sc = ctx.hybrid_line_scorer(xy0, p1)
+    m = np.array([0.6, -0.8, 0.1])
+    e0, e1 = sc.eval_errors(m, type_=0), sc.eval_errors(m, type_=1)
+    thr, w = [0.5, 0.02], [2.0, 0.5]
+    lists, counts, score = sc.get_inliers(m, thr, thr, weights=w)
+    assert np.array_equal(lists[0], np.nonzero(e0 < thr[0])[0].astype(np.int32))
+    assert np.array_equal(lists[1], np.nonzero(e1 < thr[1])[0].astype(np.int32))
+    want = w[0] * np.minimum(e0, thr[0]).sum() + w[1] * np.minimum(e1, thr[1]).sum()
+    np.testing.assert_allclose(score, want, rtol=1e-12)
+    sc.close()
