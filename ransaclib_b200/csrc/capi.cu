@@ -212,6 +212,18 @@ void pool_release(rlb_ctx* c, void* p) {
   c->pool_idle_bytes += it->second;
 }
 
+// Pinned staging block of the context, at least `bytes` long.
+int ensure_stage(rlb_ctx* c, size_t bytes) {
+  if (bytes <= c->stage_cap) return RLB_OK;
+  if (c->h_stage) cudaFreeHost(c->h_stage);
+  c->h_stage = nullptr;
+  c->stage_cap = 0;
+  const size_t cap = std::max<size_t>(bytes, 256 * 1024);
+  RLB_CUDA(cudaMallocHost(&c->h_stage, cap));
+  c->stage_cap = cap;
+  return RLB_OK;
+}
+
 void pool_drain(rlb_ctx* c) {
   for (auto& kv : c->pool_free_blocks) cudaFree(kv.second);
   c->pool_free_blocks.clear();
@@ -871,20 +883,44 @@ int scorer_pose_begin(rlb_ctx* c, int n, double fx, double fy, rlb_scorer** out,
   return RLB_OK;
 }
 
-int scorer_pose_finish(rlb_scorer* s) {
+// rows 0, step, 2 step, ... of an n x 3 array, contiguous (the sub-sample the recentring point is the mean of)
+__global__ void gather_rows3_kernel(const double* __restrict__ src, int step, int m, double* __restrict__ dst) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= m) return;
+  const double* p = src + static_cast<size_t>(r) * step * 3;
+  dst[3 * r] = p[0];
+  dst[3 * r + 1] = p[1];
+  dst[3 * r + 2] = p[2];
+}
+
+// host_p3d: the caller's copy of the WHOLE points3D array when this process has one (same bytes as on the
+// device): the recentring point then needs no device read-back at all.
+int scorer_pose_finish(rlb_scorer* s, const double* host_p3d) {
   rlb_ctx* c = s->ctx;
   int rc = ctx_use(c);
   if (rc) return rc;
   DeviceData& d = s->d;
   const int n = d.n[0];
+  if (host_p3d != nullptr) {
+    subsampled_mean(host_p3d, n, 3, 3, d.centre);
+    return finish_scorer(s);
+  }
   const int step = std::max(1, n / 4096);
   const int m = (n > 0) ? (n + step - 1) / step : 0;
   std::vector<double> sub(static_cast<size_t>(std::max(m, 1)) * 3, 0.0);
   if (m > 0) {
-    cudaError_t e = cudaMemcpy2DAsync(sub.data(), 3 * sizeof(double), d.raw1, static_cast<size_t>(step) * 3 * sizeof(double),
-                                      3 * sizeof(double), static_cast<size_t>(m), cudaMemcpyDeviceToHost, c->stream);
+    // gathered on the device into one contiguous block (a strided cudaMemcpy2D of 4096 24-byte rows costs ~0.5 ms)
+    const size_t bytes = static_cast<size_t>(m) * 3 * sizeof(double);
+    RLB_CUDA(c->scores.ensure(bytes));
+    rc = ensure_stage(c, bytes);
+    if (rc) return rc;
+    gather_rows3_kernel<<<(m + 255) / 256, 256, 0, c->stream>>>(d.raw1, step, m, c->scores.as<double>());
+    ++c->launches_i;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(c->h_stage, c->scores.p, bytes, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     if (e != cudaSuccess) return fail(RLB_E_CUDA, "reading the sub-sample back failed: %s", cudaGetErrorString(e));
+    memcpy(sub.data(), c->h_stage, bytes);
   }
   subsampled_mean(sub.data(), m, 3, 3, d.centre);
   return finish_scorer(s);
@@ -1049,20 +1085,6 @@ int rlb_scorer_get_rays(const rlb_scorer* s, double* rays) {
   RLB_CUDA(cudaStreamSynchronize(s->ctx->stream));
   return RLB_OK;
 }
-
-namespace {
-// Pinned staging block of the context, at least `bytes` long.
-int ensure_stage(rlb_ctx* c, size_t bytes) {
-  if (bytes <= c->stage_cap) return RLB_OK;
-  if (c->h_stage) cudaFreeHost(c->h_stage);
-  c->h_stage = nullptr;
-  c->stage_cap = 0;
-  const size_t cap = std::max<size_t>(bytes, 256 * 1024);
-  RLB_CUDA(cudaMallocHost(&c->h_stage, cap));
-  c->stage_cap = cap;
-  return RLB_OK;
-}
-}  // namespace
 
 int rlb_score_models_dev(rlb_scorer* s, int precision, int k, const double* d_models,
                          const uint8_t* d_valid, const double* sq_thr, const double* weights,
@@ -1240,25 +1262,29 @@ int get_inliers_impl(rlb_scorer* s, const double* model, const double* sq_thr_in
     if (rc) return rc;
     h = reinterpret_cast<InlierHeader*>(static_cast<char*>(c->h_small) + 64);
     RLB_CUDA(cudaMemcpyAsync(h, c->header.p, sizeof(InlierHeader), cudaMemcpyDeviceToHost, c->stream));
-    RLB_CUDA(cudaStreamSynchronize(c->stream));
-    const size_t bytes = static_cast<size_t>(std::max(h->count[1], 0)) * sizeof(int32_t);
-    if (view && bytes > 0) {  // the context's pinned copy; the caller's copy (if any) is taken from it
-      if (bytes > c->list_cap) {
+    const bool one_shot = ntot <= (1 << 22);  // beyond that the unused tail of the range costs more than a second sync
+    if (want_list) {
+      // The list's length is in the header, which is not here yet: the whole candidate range goes to the context's
+      // pinned block behind the header (4 B x points at PCIe rate: 80 us for 1M points) and ONE synchronisation
+      // covers both, instead of header -> sync -> list -> sync with a pageable destination.
+      const size_t cap = static_cast<size_t>(ntot) * sizeof(int32_t);
+      if (cap > c->list_cap) {
         if (c->h_list) cudaFreeHost(c->h_list);
         c->h_list = nullptr;
         c->list_cap = 0;
-        const size_t cap = static_cast<size_t>(ntot) * sizeof(int32_t);
         RLB_CUDA(cudaMallocHost(&c->h_list, cap));
         c->list_cap = cap;
       }
+      if (one_shot) RLB_CUDA(cudaMemcpyAsync(c->h_list, c->idx.p, cap, cudaMemcpyDeviceToHost, c->stream));
+    }
+    RLB_CUDA(cudaStreamSynchronize(c->stream));
+    const size_t bytes = static_cast<size_t>(std::max(h->count[1], 0)) * sizeof(int32_t);
+    if (want_list && !one_shot && bytes > 0) {
       RLB_CUDA(cudaMemcpyAsync(c->h_list, c->idx.p, bytes, cudaMemcpyDeviceToHost, c->stream));
       RLB_CUDA(cudaStreamSynchronize(c->stream));
-      *view = static_cast<const int32_t*>(c->h_list);
-      if (idx) memcpy(idx, c->h_list, bytes);
-    } else if (idx && bytes > 0) {
-      RLB_CUDA(cudaMemcpyAsync(idx, c->idx.p, bytes, cudaMemcpyDeviceToHost, c->stream));
-      RLB_CUDA(cudaStreamSynchronize(c->stream));
     }
+    if (view && bytes > 0) *view = static_cast<const int32_t*>(c->h_list);
+    if (idx && bytes > 0) memcpy(idx, c->h_list, bytes);
   }
   const int total = h->count[1];
   if (counts) {

@@ -22,7 +22,9 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -116,6 +118,20 @@ struct rlb_comm_scorer {
 namespace {
 
 using rlb::set_error;
+
+// RLB_COMM_TRACE=1: host timestamps of the phases of a scorer creation / a round on stderr (first local rank)
+bool comm_trace() {
+  static const bool on = [] {
+    const char* v = getenv("RLB_COMM_TRACE");
+    return v && v[0] == '1';
+  }();
+  return on;
+}
+double now_ms() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
 
 #define COMM_CUDA(call)                                                                              \
   do {                                                                                               \
@@ -331,6 +347,8 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
   cs->sc.assign(cm->local.size(), nullptr);
   NcclApi* a = nccl_api();
   const int G = cm->nranks;
+  const double t_begin = comm_trace() ? now_ms() : 0.0;
+  double t_up = 0.0, t_nccl = 0.0, t_sync = 0.0;
   std::vector<double*> r2(cm->local.size(), nullptr), r3(cm->local.size(), nullptr);
   // every rank allocates its scorer; host data goes up over PCIe: all of it on the root, or - when every
   // process holds the arrays - the slice [n r / G, n (r + 1) / G) on GPU r, each over its own link
@@ -351,6 +369,7 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
       return rc;
     }
   }
+  if (comm_trace()) t_up = now_ms();
   // ... and reaches the other GPUs over NVLink, straight into their scorers' arrays: one broadcast per array
   // from the root, or one per rank's slice (an all-gather with uneven pieces)
   if (G > 1 && n > 0) {
@@ -381,15 +400,25 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
     }
     cm->collectives += everyone ? 2 * G : 2;
   }
+  if (comm_trace()) {
+    t_nccl = now_ms();
+    cudaSetDevice(cm->local[0].device);
+    cudaStreamSynchronize(cm->local[0].stream());
+    t_sync = now_ms();
+  }
   // every rank derives the same recentring point from the same bytes and builds its SoA copies
   for (size_t i = 0; i < cm->local.size(); ++i) {
     cudaSetDevice(cm->local[i].device);
-    int rc = rlb::scorer_pose_finish(cs->sc[i]);
+    int rc = rlb::scorer_pose_finish(cs->sc[i], (everyone && n > 0) ? p3d : nullptr);
     if (rc) {
       rlb_comm_scorer_destroy(cs);
       return rc;
     }
   }
+  if (comm_trace() && cm->local[0].rank == 0)
+    fprintf(stderr, "[rlb_comm trace] create_pose n=%d G=%d: alloc+upload enqueue %.3f ms, nccl enqueue %.3f ms, "
+            "copies+exchange done %.3f ms, centre+repack+rays %.3f ms\n", n, G, t_up - t_begin, t_nccl - t_up,
+            t_sync - t_nccl, now_ms() - t_sync);
   *out = cs;
   return RLB_OK;
 }
@@ -446,6 +475,9 @@ int rlb_comm_hypothesize_and_score_models(rlb_comm_scorer* cs, int precision, in
   const int ss = (kind == RLB_KIND_POSE) ? 4 : (solver == 1 ? 1 : 2);
   const int msize = rlb_scorer_model_size(cs->sc[0]);
   const int rec = 2 + msize;
+  const bool trace = comm_trace() && cm->local[0].rank == 0;
+  const double t_begin = trace ? now_ms() : 0.0;
+  double t_round = 0.0, t_gather = 0.0;
   // 1. every local rank: its shard of the samples up, solve + sweep + local argmin -> record
   for (size_t i = 0; i < cm->local.size(); ++i) {
     LocalRank& L = cm->local[i];
@@ -467,9 +499,19 @@ int rlb_comm_hypothesize_and_score_models(rlb_comm_scorer* cs, int precision, in
                                scores ? L.d_scores : nullptr, counts ? L.d_counts : nullptr, L.d_rec);
     if (rc) return rc;
   }
+  if (trace) {  // (tracing synchronises between the phases: durations, not the overlapped timeline)
+    cudaSetDevice(cm->local[0].device);
+    cudaStreamSynchronize(cm->local[0].stream());
+    t_round = now_ms();
+  }
   // 2. the round's single collective + winner on every rank
   int rc = gather_and_select(cm, rec);
   if (rc) return rc;
+  if (trace) {
+    cudaSetDevice(cm->local[0].device);
+    cudaStreamSynchronize(cm->local[0].stream());
+    t_gather = now_ms();
+  }
   // 3. results back: the winner from the first local rank, per-hypothesis outputs from each rank's slice
   for (size_t i = 0; i < cm->local.size(); ++i) {
     LocalRank& L = cm->local[i];
@@ -494,6 +536,9 @@ int rlb_comm_hypothesize_and_score_models(rlb_comm_scorer* cs, int precision, in
     COMM_CUDA(cudaSetDevice(L.device));
     COMM_CUDA(cudaStreamSynchronize(L.stream()));
   }
+  if (trace)
+    fprintf(stderr, "[rlb_comm trace] round k_total=%d: samples up + solve + sweep + argmin %.3f ms, all-gather + winner "
+            "%.3f ms, results back %.3f ms\n", k_total, t_round - t_begin, t_gather - t_round, now_ms() - t_gather);
   const double* w = cm->local[0].h_winner;
   if (best_score) *best_score = w[0];
   if (best_id) *best_id = static_cast<int64_t>(w[1]);

@@ -33,7 +33,7 @@ void* ctx_stream(const rlb_ctx* c);  // cudaStream_t
 int ctx_device(const rlb_ctx* c);
 // capi.cu: two-step construction of a pose scorer whose raw arrays the caller fills on the device
 int scorer_pose_begin(rlb_ctx* c, int n, double fx, double fy, rlb_scorer** out, double** raw2d, double** raw3d);
-int scorer_pose_finish(rlb_scorer* s);
+int scorer_pose_finish(rlb_scorer* s, const double* host_p3d = nullptr);
 
 // Points of every data type are stored channel-major (SoA) and zero-padded so that
 // each type segment starts at a multiple of kSegAlign points. Stages of the K x N
