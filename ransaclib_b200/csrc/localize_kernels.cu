@@ -83,20 +83,30 @@ __device__ __noinline__ void mt_seed(uint32_t* s, uint32_t seed, int lane) {
   __syncwarp();
 }
 
-// Regenerates the 624 words in place, 32 per round: word k needs the OLD k, k+1 and either the
-// old k+397 (k < 227) or the NEW k-227, which earlier rounds have already written.
+// Regenerates the 624 words in place, 128 per round (four per lane: four independent load -> twist chains in
+// flight): word k needs the OLD k, k+1 and either the old k+397 (k < 227) or the NEW k-227, which an earlier round
+// has already written (k - 227 < base for every k of a round; k + 1 and k + 397 are never in the round's own write
+// set before they are read: all reads of a round precede its writes).
 __device__ __noinline__ void mt_twist(uint32_t* s, int lane) {
 #pragma unroll 1
-  for (int base = 0; base < 623; base += 32) {
-    const int k = base + lane;
-    uint32_t v = 0;
-    if (k < 623) {
-      const uint32_t y = (s[k] & 0x80000000u) | (s[k + 1] & 0x7fffffffu);
-      const uint32_t src = (k < 227) ? s[k + 397] : s[k - 227];
-      v = src ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+  for (int base = 0; base < 623; base += 128) {
+    uint32_t v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = base + lane + 32 * q;
+      v[q] = 0u;
+      if (k < 623) {
+        const uint32_t y = (s[k] & 0x80000000u) | (s[k + 1] & 0x7fffffffu);
+        const uint32_t src = (k < 227) ? s[k + 397] : s[k - 227];
+        v[q] = src ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+      }
     }
     __syncwarp();
-    if (k < 623) s[k] = v;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = base + lane + 32 * q;
+      if (k < 623) s[k] = v[q];
+    }
     __syncwarp();
   }
   if (lane == 0) {
@@ -182,15 +192,53 @@ __device__ __noinline__ void shuffle_resize(Mt& r, const int32_t* list, int n, i
   const int steps = (n > 0) ? n - 1 : 0;
   const int head_n = min(target, n);
   const int t_steps = min(target, steps);
+  // The draws of the first t_steps steps, one per lane when they are the next t_steps words of the current block
+  // and none of them is a Lemire rejection (p ~ n / 2^32 each); else one after the other.
   int my_j = -1;
-  for (int i = 0; i < t_steps; ++i) {
-    const int j = i + static_cast<int>(lemire(r, static_cast<uint32_t>(n - i), lane));
-    if (lane == i) my_j = j;
+  bool drawn = false;
+  if (t_steps > 0 && !force_slow) {
+    if (r.idx >= 624) {
+      mt_twist(r.s, lane);
+      r.idx = 0;
+    }
+    if (r.idx + t_steps <= 624) {
+      bool rej = false;
+      int j = -1;
+      if (lane < t_steps) {
+        const uint32_t range = static_cast<uint32_t>(n - lane);
+        const unsigned long long prod = static_cast<unsigned long long>(mt_temper(r.s[r.idx + lane])) * range;
+        const uint32_t low = static_cast<uint32_t>(prod);
+        if (low < range) rej = low < ((0u - range) % range);
+        j = lane + static_cast<int>(prod >> 32);
+      }
+      if (__ballot_sync(kFull, rej) == 0u) {
+        my_j = j;
+        r.idx += t_steps;
+        drawn = true;
+      }
+    }
+  }
+  if (!drawn) {
+    for (int i = 0; i < t_steps; ++i) {
+      const int j = i + static_cast<int>(lemire(r, static_cast<uint32_t>(n - i), lane));
+      if (lane == i) my_j = j;
+    }
   }
   int head = (lane < head_n) ? list[lane] : 0;
   const int pre = (lane < t_steps && my_j >= head_n) ? list[my_j] : 0;
+  // A step i whose j lies beyond the head and is hit by no other step ("simple") leaves head[i] = list[j] and a
+  // displaced entry nobody reads; it reads nothing a step before it wrote and nothing after it reads head[i]
+  // (later steps touch positions >= their own index). So only the other steps - j inside the head, or a j shared
+  // by several steps - go through the sequential resolution, in order; the simple ones are applied at the end.
+  const bool is_step = lane < t_steps;
+  const unsigned same_j = __match_any_sync(kFull, is_step ? my_j : -1 - lane);
+  const bool simple = is_step && my_j >= head_n && __popc(same_j) == 1;
+  unsigned todo = __ballot_sync(kFull, is_step && !simple);
+  if (force_slow) todo = __ballot_sync(kFull, is_step);
   int pos = -1, val = 0;
-  for (int i = 0; i < t_steps; ++i) {
+  while (todo) {
+    const int i = __ffs(todo) - 1;
+    todo &= todo - 1u;
     const int j = __shfl_sync(kFull, my_j, i);
     const int a = __shfl_sync(kFull, head, i);
     int b;
@@ -213,7 +261,9 @@ __device__ __noinline__ void shuffle_resize(Mt& r, const int32_t* list, int n, i
     }
     if (lane == i) head = b;
   }
-  // draws of the steps that cannot reach the kept prefix
+  if (simple && !force_slow) head = pre;
+  // draws of the steps that cannot reach the kept prefix: 128 per round, every lane testing four of them for a
+  // Lemire rejection (four independent load -> temper -> multiply chains in flight)
   int i = t_steps;
   int remaining = steps - t_steps;
   while (remaining > 0) {
@@ -221,23 +271,30 @@ __device__ __noinline__ void shuffle_resize(Mt& r, const int32_t* list, int n, i
       mt_twist(r.s, lane);
       r.idx = 0;
     }
-    const int chunk = min(min(32, remaining), 624 - r.idx);
-    bool rej = false;
-    if (lane < chunk) {
-      const uint32_t range = static_cast<uint32_t>(n - (i + lane));
-      const unsigned long long prod =
-          static_cast<unsigned long long>(mt_temper(r.s[r.idx + lane])) * range;
-      const uint32_t low = static_cast<uint32_t>(prod);
-      if (low < range) rej = low < ((0u - range) % range);
+    const int chunk = min(min(128, remaining), 624 - r.idx);
+    bool rej[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int p = lane + 32 * q;
+      rej[q] = false;
+      if (p < chunk) {
+        const uint32_t range = static_cast<uint32_t>(n - (i + p));
+        const unsigned long long prod = static_cast<unsigned long long>(mt_temper(r.s[r.idx + p])) * range;
+        const uint32_t low = static_cast<uint32_t>(prod);
+        if (low < range) rej[q] = low < ((0u - range) % range);
+      }
     }
-    unsigned m = __ballot_sync(kFull, rej);
-    if (force_slow) m |= 1u;
-    if (m == 0u) {
+    const unsigned m0 = __ballot_sync(kFull, rej[0]), m1 = __ballot_sync(kFull, rej[1]);
+    const unsigned m2 = __ballot_sync(kFull, rej[2]), m3 = __ballot_sync(kFull, rej[3]);
+    if (!force_slow && (m0 | m1 | m2 | m3) == 0u) {
       r.idx += chunk;
       i += chunk;
       remaining -= chunk;
     } else {
-      const int f = __ffs(m) - 1;
+      // the first rejected draw of the round (position 0 when the slow path is forced)
+      int f = 0;
+      if (!force_slow)
+        f = m0 ? __ffs(m0) - 1 : (m1 ? 32 + __ffs(m1) - 1 : (m2 ? 64 + __ffs(m2) - 1 : 96 + __ffs(m3) - 1));
       r.idx += f;
       i += f;
       remaining -= f;
@@ -968,6 +1025,7 @@ __device__ __noinline__ bool lm_refine_lanes(Run& R, double* cam, const int32_t*
       v += dgl / radius;
     }
     bool ok = true;
+    double rinv[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // 1 / L[c][c], as in refine::SolveSpd6
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
       const double scc = __shfl_sync(kFull, v, mat_lane(c, c));
@@ -976,7 +1034,8 @@ __device__ __noinline__ bool lm_refine_lanes(Run& R, double* cam, const int32_t*
         break;
       }
       const double lcc = sqrt(scc);
-      if (is_mat && E.j == c) v = (E.i == c) ? lcc : v / lcc;
+      rinv[c] = 1.0 / lcc;
+      if (is_mat && E.j == c) v = (E.i == c) ? lcc : v * rinv[c];
       const bool below = is_mat && E.j > c;
       const double lic = __shfl_sync(kFull, v, below ? mat_lane(E.i, c) : 0);
       const double ljc = __shfl_sync(kFull, v, below ? mat_lane(E.j, c) : 0);
@@ -989,8 +1048,7 @@ __device__ __noinline__ bool lm_refine_lanes(Run& R, double* cam, const int32_t*
       double yv = is_vec ? -acc : 0.0;
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
-        const double lcc = __shfl_sync(kFull, v, mat_lane(c, c));
-        if (lane == c) yv = yv / lcc;
+        if (lane == c) yv = yv * rinv[c];
         const double yc = __shfl_sync(kFull, yv, c);
         const bool below = is_vec && lane > c;
         const double llc = __shfl_sync(kFull, v, below ? mat_lane(lane, c) : 0);
@@ -1003,8 +1061,7 @@ __device__ __noinline__ bool lm_refine_lanes(Run& R, double* cam, const int32_t*
         double sv = yv;
 #pragma unroll
         for (int c = i + 1; c < 6; ++c) sv = sv - prod[c];
-        const double lii = __shfl_sync(kFull, v, mat_lane(i, i));
-        if (lane == i) step = sv / lii;
+        if (lane == i) step = sv * rinv[i];
         const double xi = __shfl_sync(kFull, step, i);
         const bool left = is_vec && lane < i;
         const double lil = __shfl_sync(kFull, v, left ? mat_lane(i, lane) : 0);
