@@ -342,8 +342,18 @@ __device__ __noinline__ void shuffle_resize(Shared& sh, const int32_t* list, int
     }
   }
 
+  // A step whose j lies beyond the head and is hit by no other step ("simple") leaves head[step] = list[j] and a
+  // displaced entry nobody reads; it reads nothing an earlier step wrote and no later step reads its head entry. So
+  // only the other steps (j inside the head, or a j shared by several steps) go through the sequential resolution,
+  // in order; the simple ones are applied at the end (csrc/localize_kernels.cu: shuffle_resize, same argument).
+  const bool is_step = lane < t_steps;
+  const unsigned same_j = __match_any_sync(kFull, is_step ? my_j : -1 - lane);
+  const bool simple = !force_slow && is_step && my_j >= head_n && __popc(same_j) == 1;
+  unsigned todo = __ballot_sync(kFull, is_step && !simple);
   int pos = -1, val = 0;
-  for (int k = 0; k < t_steps; ++k) {
+  while (todo) {
+    const int k = __ffs(todo) - 1;
+    todo &= todo - 1u;
     const int j = __shfl_sync(kFull, my_j, k);
     const int a = __shfl_sync(kFull, head, k);
     int b;
@@ -366,6 +376,7 @@ __device__ __noinline__ void shuffle_resize(Shared& sh, const int32_t* list, int
     }
     if (lane == k) head = b;
   }
+  if (simple) head = pre;
   if (tid < target) sh.samp[tid] = (tid < head_n) ? head : 0;
   mt_store(sh, 1, r);
   RLB_LL_PROF_END(sh, 3);
