@@ -1345,6 +1345,255 @@ __global__ void __launch_bounds__(kInlThreads, RLB_INL_MINB)
   }
 }
 
+// ---- the same pass with ONE CTA per SM and a bulk-TMA ring (opt-in: RLB_INLIER_TMA=1) --------------------------
+// -DRLB_INL_DBG prints %globaltimer stamps of three CTAs (ticket, first tile, loop, chain wait, write).
+// inlier_range_kernel keeps at most two tiles of a CTA in flight (registers), so every CTA alternates between
+// waiting for HBM and computing. Here a CTA of 512 threads owns a contiguous range of tiles and streams them through
+// a ring of kTmaStages shared-memory stages filled by 1-D bulk copies (one per channel and tile: 8 KB each, one
+// elected thread arms an mbarrier per stage): C x 8 KB x stages bytes are in flight per SM from the first cycle
+// (pose: 200 KB), independent of registers. Evaluation, the per-tile scan and the shared-memory record of (offset,
+// inlier bits) are those of inlier_range_kernel with two points per thread; so are the ticket, the count word per
+// CTA, the flat read of the lower CTAs' words and the score total by the highest ticket.
+constexpr int kTmaThreads = 512;
+constexpr int kTmaMaxRange = 12;  // tiles per CTA (record: 12 x 512 words = 24 KB)
+
+template <template <typename> class FT>
+__global__ void __launch_bounds__(kTmaThreads, 1)
+    inlier_tma_kernel(const DeviceData d, const InlierArgs a, int tiles_per_cta, int num_tiles, int stages) {
+  typedef FT<double> F;
+  constexpr int C = F::C;
+  constexpr int PPT = kInlTile / kTmaThreads;  // 2
+  constexpr int kWarps = kTmaThreads / 32;
+  extern __shared__ __align__(128) unsigned char tma_smem[];
+  double* ring = reinterpret_cast<double*>(tma_smem);  // [stages][C][kInlTile]
+  unsigned int* s_keep = reinterpret_cast<unsigned int*>(ring + static_cast<size_t>(stages) * C * kInlTile);
+  __shared__ __align__(8) uint64_t full[8];
+  __shared__ unsigned int s_rank;
+  __shared__ int s_wsum[kWarps];
+  __shared__ double s_wscore[kWarps];
+  __shared__ int s_below[kWarps];
+  __shared__ int s_base;
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5;
+#ifdef RLB_INL_DBG
+  unsigned long long ts[8];
+  auto gt = [] { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; };
+  ts[0] = gt();
+#define STAMP(i) ts[i] = gt()
+#else
+#define STAMP(i)
+#endif
+  if (tid == 0) {
+    s_rank = atomicAdd(&a.control[0], 1u);
+    for (int sidx = 0; sidx < stages; ++sidx) mbar_init(&full[sidx], 1);
+    mbar_fence_init();
+  }
+  typename F::Model m;
+  F::load(a.model != nullptr ? a.model : a.model_v, d, m);
+  __syncthreads();
+  const int b = static_cast<int>(s_rank);
+  const int num_ctas = static_cast<int>(gridDim.x);
+  const int t0 = b * tiles_per_cta;
+  const int t1 = min(num_tiles, t0 + tiles_per_cta);
+  const int nt = max(0, t1 - t0);
+
+  auto issue = [&](int it) {  // tile t0 + it into stage it % stages
+    const int slot = it % stages;
+    double* dst = ring + static_cast<size_t>(slot) * C * kInlTile;
+    const size_t g0 = static_cast<size_t>(t0 + it) * kInlTile;
+    mbar_expect_tx(&full[slot], C * kInlTile * 8);
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+      tma_load_1d(dst + c * kInlTile, d.soa64 + static_cast<size_t>(c) * d.npad + g0, kInlTile * 8, &full[slot]);
+  };
+  STAMP(1);
+  if (tid == 0)
+    for (int it = 0; it < stages && it < nt; ++it) issue(it);
+
+  int run = 0;
+  int type0_local = -1;
+  double sc = 0.0;
+#pragma unroll 1
+  for (int it = 0; it < nt; ++it) {
+    const int ti = t0 + it;
+    const int slot = it % stages;
+    const int g0 = ti * kInlTile;
+    const int t = (d.num_types > 1 && g0 >= d.off[1]) ? 1 : 0;
+    const int seg_n = d.n[t], seg_off = d.off[t];
+    const double thr_in = a.thr_inl[t];
+    const double thr_sc = a.thr_score[t];
+    const double w = a.w[t];
+    if (d.num_types > 1 && g0 == d.off[1]) type0_local = run;
+    mbar_wait(&full[slot], (it / stages) & 1);
+    if (it == 0) STAMP(2);
+    const double* sb = ring + static_cast<size_t>(slot) * C * kInlTile + tid * PPT;
+    const int i0 = g0 + tid * PPT;
+    double ch[C][PPT];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const double2 v = *reinterpret_cast<const double2*>(sb + c * kInlTile);
+      ch[c][0] = v.x;
+      ch[c][1] = v.y;
+    }
+    unsigned int bits = 0u;
+    int my = 0;
+#pragma unroll
+    for (int j = 0; j < PPT; ++j) {
+      double p[C];
+#pragma unroll
+      for (int c = 0; c < C; ++c) p[c] = ch[c][j];
+      const double e = F::eval(m, p);
+      const bool live = (i0 + j - seg_off) < seg_n;
+      const bool in = live && (e < thr_in);
+      bits |= in ? (1u << j) : 0u;
+      my += in ? 1 : 0;
+      if (live) sc += ((thr_sc < e) ? thr_sc : e) * w;
+    }
+    int incl = my;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_wsum[wid] = incl;
+    __syncthreads();  // warp counts complete; everyone has read its points of this stage
+    if (tid == 0 && it + stages < nt) issue(it + stages);
+    int warp_excl = 0, tile_total = 0;
+#pragma unroll
+    for (int q = 0; q < kWarps; ++q) {
+      if (q < wid) warp_excl += s_wsum[q];
+      tile_total += s_wsum[q];
+    }
+    s_keep[it * kTmaThreads + tid] = (static_cast<unsigned int>(run + warp_excl + incl - my) << 2) | bits;
+    run += tile_total;
+    __syncthreads();  // s_wsum is reused by the next tile
+  }
+
+  STAMP(3);
+  double wsc = sc;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wsc += __shfl_down_sync(0xffffffffu, wsc, o);
+  if (lane == 0) s_wscore[wid] = wsc;
+  __syncthreads();
+  if (tid == 0) {
+    double ts = 0.0;
+#pragma unroll
+    for (int q = 0; q < kWarps; ++q) ts += s_wscore[q];
+    a.tile_score[b] = ts;
+    __threadfence();
+    atomicExch(&a.status[b], pack_status(a.epoch, kFlagAgg, static_cast<unsigned int>(run)));
+  }
+  int below = 0;
+  for (int j = tid; j < b; j += kTmaThreads) {
+    const unsigned long long* wp = &a.status[j];
+    unsigned long long word;
+    long long c0 = 0;
+    unsigned int spins = 0;
+    for (;;) {
+      word = *reinterpret_cast<const volatile unsigned long long*>(wp);
+      if (static_cast<unsigned int>(word >> 34) == a.epoch && ((word >> 32) & 3ull) != 0ull) break;
+      if (++spins == 4096u) {
+        const long long now = clock64();
+        if (c0 == 0) {
+          c0 = now;
+        } else if (now - c0 > 4000000000LL) {
+          __trap();
+        }
+        spins = 0;
+      }
+    }
+    below += static_cast<int>(word & 0xffffffffull);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) below += __shfl_down_sync(0xffffffffu, below, o);
+  if (lane == 0) s_below[wid] = below;
+  __syncthreads();
+  if (tid == 0) {
+    int base = 0;
+#pragma unroll
+    for (int q = 0; q < kWarps; ++q) base += s_below[q];
+    s_base = base;
+    STAMP(4);
+    InlierHeader* hdr = reinterpret_cast<InlierHeader*>(a.header);
+    if (type0_local >= 0) hdr->count[0] = base + type0_local;
+    if (b == num_ctas - 1) {
+      hdr->count[1] = base + run;
+      if (d.num_types == 1 || d.off[1] >= d.npad) hdr->count[0] = base + run;
+    }
+  }
+  __syncthreads();
+
+  if (a.idx != nullptr) {
+    const int base = s_base;
+#pragma unroll 1
+    for (int it = 0; it < nt; ++it) {
+      const int g0 = (t0 + it) * kInlTile;
+      const int seg_off = d.off[(d.num_types > 1 && g0 >= d.off[1]) ? 1 : 0];
+      const unsigned int v = s_keep[it * kTmaThreads + tid];
+      int pos = base + static_cast<int>(v >> 2);
+      const int i0 = g0 + tid * PPT - seg_off;
+      if (v & 1u) a.idx[pos++] = i0;
+      if (v & 2u) a.idx[pos] = i0 + 1;
+    }
+  }
+#ifdef RLB_INL_DBG
+  STAMP(5);
+  if (tid == 0 && (b == 0 || b == num_ctas - 1 || b == num_ctas / 2))
+    printf("cta %d (blk %d): t0 %llu ticket+model %llu first-tile %llu loop %llu wait %llu write %llu\n", b, blockIdx.x,
+           ts[0] % 100000000ull, ts[1] - ts[0], ts[2] - ts[1], ts[3] - ts[2], ts[4] - ts[3], ts[5] - ts[4]);
+#endif
+  if (b != num_ctas - 1) return;
+  __threadfence();
+  double part = 0.0;
+  for (int q = tid; q < num_ctas; q += kTmaThreads) part += *reinterpret_cast<volatile double*>(&a.tile_score[q]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_down_sync(0xffffffffu, part, o);
+  __syncthreads();
+  if (lane == 0) s_wscore[wid] = part;
+  __syncthreads();
+  if (tid == 0) {
+    double total = 0.0;
+#pragma unroll
+    for (int q = 0; q < kWarps; ++q) total += s_wscore[q];
+    InlierHeader* hdr = reinterpret_cast<InlierHeader*>(a.header);
+    hdr->score = total;
+    a.control[0] = 0u;
+  }
+}
+
+// 4 .. 12 tiles per SM only (the record of a CTA's tiles lives in shared memory beside the ring).
+template <template <typename> class FT>
+static cudaError_t launch_inlier_tma(const DeviceData& d, const InlierArgs& a, int tiles, cudaStream_t st,
+                                     bool* launched) {
+  static std::atomic<int> sm_count[64];
+  static PerDeviceOnce configured;
+  const int dev = PerDeviceOnce::device();
+  constexpr int C = FT<double>::C;
+  int sms = sm_count[dev].load(std::memory_order_relaxed);
+  if (sms == 0) {
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 0;
+    sm_count[dev].store(sms, std::memory_order_relaxed);
+  }
+  *launched = false;
+  if (sms <= 0) return cudaSuccess;
+  const int per_cta = (tiles + sms - 1) / sms;
+  if (per_cta < 4 || per_cta > kTmaMaxRange) return cudaSuccess;
+  const int stages = min(8, min(per_cta, static_cast<int>((200 * 1024) / (C * kInlTile * 8))));
+  const size_t smem = static_cast<size_t>(stages) * C * kInlTile * 8 + static_cast<size_t>(per_cta) * kTmaThreads * 4;
+  if (!configured.done(dev)) {
+    const cudaError_t e = cudaFuncSetAttribute(inlier_tma_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               227 * 1024 - 1024);
+    if (e != cudaSuccess) return e;
+    configured.set(dev);
+  }
+  if (smem > 226 * 1024) return cudaSuccess;
+  const int ctas = (tiles + per_cta - 1) / per_cta;
+  *launched = true;
+  inlier_tma_kernel<FT><<<ctas, kTmaThreads, smem, st>>>(d, a, per_cta, tiles, stages);
+  return cudaGetLastError();
+}
+
 template <template <typename> class FT>
 static cudaError_t launch_inlier_range(const DeviceData& d, const InlierArgs& a, int tiles, cudaStream_t st,
                                        bool* launched) {
@@ -1376,6 +1625,26 @@ cudaError_t launch_inliers(const DeviceData& d, const InlierArgs& a, cudaStream_
     const char* v = getenv("RLB_INLIER_RANGE");
     return !(v && atoi(v) == 0);
   }();
+  // RLB_INLIER_TMA=1: the one-CTA-per-SM bulk-TMA form. Measured slower than the register-prefetch kernel at
+  // N = 1M (22.0 us against 18.4 us between events; profiles/r02_inlier_pass_ab.txt holds the in-kernel timeline:
+  // the ring streams at the HBM rate, but 140 CTAs that each ask for 200 KB at once wait 1.3 - 4.9 us for their first
+  // tile and the last ticket then waits for the slowest CTA), so it is an A/B switch, not the default.
+  static const bool use_tma = [] {
+    const char* v = getenv("RLB_INLIER_TMA");
+    return v && atoi(v) == 1;
+  }();
+  if (use_range && use_tma) {
+    bool launched = false;
+    cudaError_t e;
+    if (d.kind == RLB_KIND_POSE) {
+      e = launch_inlier_tma<PoseF>(d, a, tiles, st, &launched);
+    } else if (d.kind == RLB_KIND_CUSTOM) {
+      e = launch_inlier_tma<ErrF>(d, a, tiles, st, &launched);
+    } else {
+      e = launch_inlier_tma<LineF>(d, a, tiles, st, &launched);
+    }
+    if (e != cudaSuccess || launched) return e;
+  }
   if (use_range) {
     bool launched = false;
     cudaError_t e;

@@ -116,6 +116,11 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                : "memory");
 }
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+#ifdef RLB_TC_PROBE_NOLDTM  // timing probe only (wrong results): is the TMEM read path the bound?
+#pragma unroll
+  for (int i = 0; i < 8; ++i) asm volatile("mov.b32 %0, %1;" : "=f"(v[i]) : "r"(taddr + i));
+  return;
+#endif
   uint32_t r[8];
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
@@ -159,9 +164,13 @@ __device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
   return d;
 }
 __device__ __forceinline__ float rsq_approx(float x) {
+#ifdef RLB_TC_PROBE_NOMUFU  // timing probe only (wrong results): is the XU pipe the bound?
+  return x;
+#else
   float r;
   asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
+#endif
 }
 // MSAC accumulation of one evaluation: s += e and c += 1 when e < thr (one FSETP + two predicated adds).
 __device__ __forceinline__ void msac_add(float e, float thr, float& s, int& c) {
@@ -466,6 +475,269 @@ __global__ void __launch_bounds__(128 * HALVES, HALVES == 1 ? 4 : 3)
   if (warp == 0) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
                  "r"(static_cast<uint32_t>(kTcCols))
+                 : "memory");
+  }
+}
+
+// ------------------------------------------------ the same sweep, MMA and epilogue decoupled
+// sweep_pose_tc_kernel alternates per CTA between "one lane issues six MMAs, everyone waits for the commit" and
+// "everyone reduces the tile, __syncthreads": its four warps idle through every MMA round trip and the other three
+// CTAs of the SM have to fill the gap (ncu: ~65 % of the issue slots). Here a CTA is two groups of four epilogue
+// warps + 1 producer warp and owns 256 TMEM columns with TWO accumulator sets:
+//     producer warp : TMA ring refills; for tile t waits until set t & 1 has been read out, issues the six MMAs,
+//                     tcgen05.commit -> acc_full[t & 1]
+//     group g       : tiles g, g + 2, ... from set g. The TMEM loads run two 8-point groups ahead of the arithmetic,
+//                     and the set is handed back (acc_empty[g]) when its last columns are in registers - half a
+//                     tile of arithmetic before the group needs the next one, which is about the MMA round trip.
+// Both groups serve the same 128 hypotheses (a warp can only read the TMEM lanes of warp % 4): every hypothesis'
+// sums live in two threads and are joined once at the end. No __syncthreads in the loop. Two CTAs per SM (TMEM),
+// 16 epilogue warps per SM as before.
+//
+// Measured on C5 (profiles/r02_tc_halves_ab.txt): 27.27 ms against 27.08 ms for sweep_pose_tc_kernel (27.49 against
+// 25.9 ms without counts) - the MMA round trip is NOT what bounds the sweep. The same file holds the probes that say
+// what does: without the MUFU 25.5 ms (the XU pipe is not it either), with eight MOVs in place of every
+// tcgen05.ld.x8 30.8 ms (more instructions, slower: issue), 331 warp instructions per 32-point tile at 72 % issue
+// utilisation with every pipe below 60 %. A variant that split each tile's 32 points over two warps (16 each, both
+// accumulator sets per tile) ran at 32.1 ms: the per-tile fixed instructions then weigh twice. Kept as an A/B
+// build (-DRLB_TC_PIPE=1); the default is sweep_pose_tc_kernel.
+constexpr int kTcpThreads = 32 * 9;
+constexpr int kTcpCols = 256;  // A operand [0,24); accumulator set g: [32 + 96 g, 128 + 96 g)
+
+struct TcpSmem {
+  float ring[kTcRing][kTcTileFloats];
+  uint64_t full[kTcRing];   // TMA -> producer
+  uint64_t acc_full[2];     // MMA commit -> group
+  uint64_t acc_empty[2];    // group (4 warps) -> producer
+  uint32_t tmem_base;
+};
+
+// tcgen05.wait::ld, then hand the accumulator set back: one statement with the loaded registers as in/out
+// operands, so that the arrive stays where it is written (before the arithmetic on these registers).
+__device__ __forceinline__ void tmem_wait_ld8x3_release(float* a, float* b, float* c, uint64_t* bar, uint32_t lane0) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %25, 0;\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "tcgen05.fence::before_thread_sync;\n\t"
+      "@p mbarrier.arrive.shared::cta.b64 _, [%24];\n\t}"
+      : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7]),
+        "+f"(b[0]), "+f"(b[1]), "+f"(b[2]), "+f"(b[3]), "+f"(b[4]), "+f"(b[5]), "+f"(b[6]), "+f"(b[7]),
+        "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]), "+f"(c[4]), "+f"(c[5]), "+f"(c[6]), "+f"(c[7])
+      : "r"(smem_u32(bar)), "r"(lane0)
+      : "memory");
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kTcpThreads, 2)
+    sweep_pose_tcp_kernel(const DeviceData d, const SweepArgs a, const float* __restrict__ tiles) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  TcpSmem& S = *reinterpret_cast<TcpSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const bool producer = warp == 8;
+  const int quarter = warp & 3;
+  const int grp = (warp >> 2) & 1;
+  const int hyp = quarter * 32 + (tid & 31);
+  const int k = blockIdx.x * 128 + hyp;
+  const int split = blockIdx.y;
+  const int n_live = d.n[0];
+
+  const int total_tiles = d.npad / kTcTile;
+  const int t_begin = split * a.stages_per_split;
+  const int t_end = min(total_tiles, t_begin + a.stages_per_split);
+  const int ntiles = max(0, t_end - t_begin);
+
+  if (producer) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)),
+                 "r"(static_cast<uint32_t>(kTcpCols))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kTcRing; ++s) mbar_init(&S.full[s], 1);
+    mbar_init(&S.acc_full[0], 1);
+    mbar_init(&S.acc_full[1], 1);
+    mbar_init(&S.acc_empty[0], 4);
+    mbar_init(&S.acc_empty[1], 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = S.tmem_base;
+  const uint32_t lane_addr = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+  if (warp < 4) {
+    // the hypotheses' TMEM lanes of the A operand, as in sweep_pose_tc_kernel
+    float r[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float t[3] = {0.f, 0.f, 1.f};
+    if (k < a.k) {
+      const double* m = a.models + static_cast<size_t>(k) * 12;
+      const double dc[3] = {d.centre[0] - m[9], d.centre[1] - m[10], d.centre[2] - m[11]};
+      const double sc[3] = {d.fx, d.fy, 1.0};
+#pragma unroll
+      for (int row = 0; row < 3; ++row) {
+        const double r0 = m[row], r1 = m[row + 3], r2 = m[row + 6];
+        r[3 * row + 0] = static_cast<float>(r0 * sc[row]);
+        r[3 * row + 1] = static_cast<float>(r1 * sc[row]);
+        r[3 * row + 2] = static_cast<float>(r2 * sc[row]);
+        t[row] = static_cast<float>((r0 * dc[0] + r1 * dc[1] + r2 * dc[2]) * sc[row]);
+      }
+    }
+#pragma unroll
+    for (int mat = 0; mat < 3; ++mat) {
+      const float v[4] = {r[3 * mat], r[3 * mat + 1], r[3 * mat + 2], t[mat]};
+      float hl[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        hl[j] = tf32_hi(v[j]);
+        hl[4 + j] = v[j] - hl[j];
+      }
+      tmem_st8(lane_addr + 8 * mat, hl);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  double dacc = 0.0;
+  int dcnt = 0;
+
+  if (producer) {
+    auto issue_tma = [&](int it) {
+      const int slot = it % kTcRing;
+      mbar_expect_tx(&S.full[slot], kTcTileBytes);
+      tma_load_1d(S.ring[slot], tiles + static_cast<size_t>(t_begin + it) * kTcTileFloats, kTcTileBytes,
+                  &S.full[slot]);
+    };
+    if (elect_one()) {
+      for (int it = 0; it < kTcRing && it < ntiles; ++it) issue_tma(it);
+    }
+    __syncwarp();
+    for (int it = 0; it < ntiles; ++it) {
+      const int slot = it % kTcRing;
+      const int buf = it & 1;
+      if (it >= 2) {
+        // set `buf` has been read out: its group is in the second half of tile it - 2 and has finished tile
+        // it - 4, -u / -v included, so THAT tile's ring slot is free
+        mbar_wait(&S.acc_empty[buf], ((it >> 1) - 1) & 1);
+        if (it >= 4 && it + 4 < ntiles) {
+          if (elect_one()) issue_tma(it + 4);
+          __syncwarp();
+        }
+      }
+      mbar_wait(&S.full[slot], (it / kTcRing) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (elect_one()) {
+        const uint32_t b_addr = smem_u32(S.ring[slot]);
+        const uint32_t acc = tmem + 32 + 96 * buf;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          const uint64_t db = umma_desc(b_addr + kk * 2 * 512, 512, 128);
+#pragma unroll
+          for (int mat = 0; mat < 3; ++mat) umma_tf32_ts(acc + mat * kTcTile, tmem + 8 * mat, db, kk);
+        }
+        umma_commit(&S.acc_full[buf]);
+      }
+      __syncwarp();
+    }
+  } else {
+    const double thr64 = a.thr[0];
+    const float thr = static_cast<float>(thr64);
+    const double w = a.w[0];
+    const uint32_t lane0 = (tid & 31) == 0 ? 1u : 0u;
+    const uint32_t acc = lane_addr + 32 + 96 * grp;
+    float s = 0.0f;
+    int c = 0;
+    u64 s2 = 0ull;
+    int live_in_chunk = 0;
+    int visit = 0;
+    for (int it = grp; it < ntiles; it += 2, ++visit) {
+      const int slot = it % kTcRing;
+      mbar_wait(&S.acc_full[grp], visit & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const float* nu = S.ring[slot] + 512;
+      const float* nv = nu + 32;
+      float px[3][8], py[3][8], pz[3][8];
+      tmem_ld8(acc + 0 * kTcTile, px[0]);
+      tmem_ld8(acc + 1 * kTcTile, py[0]);
+      tmem_ld8(acc + 2 * kTcTile, pz[0]);
+      tmem_ld8(acc + 0 * kTcTile + 8, px[1]);
+      tmem_ld8(acc + 1 * kTcTile + 8, py[1]);
+      tmem_ld8(acc + 2 * kTcTile + 8, pz[1]);
+      tmem_wait_ld8x3(px[0], py[0], pz[0]);
+      tmem_wait_ld8x3(px[1], py[1], pz[1]);
+#pragma unroll
+      for (int qd = 0; qd < 4; ++qd) {
+        const int cur = qd % 3, nxt = (qd + 2) % 3;
+        if (qd < 2) {
+          tmem_ld8(acc + 0 * kTcTile + 8 * (qd + 2), px[nxt]);
+          tmem_ld8(acc + 1 * kTcTile + 8 * (qd + 2), py[nxt]);
+          tmem_ld8(acc + 2 * kTcTile + 8 * (qd + 2), pz[nxt]);
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          const ulonglong2 u4 = *reinterpret_cast<const ulonglong2*>(nu + 8 * qd + 4 * q);
+          const ulonglong2 v4 = *reinterpret_cast<const ulonglong2*>(nv + 8 * qd + 4 * q);
+#pragma unroll
+          for (int pr = 0; pr < 2; ++pr) {
+            const int j = 4 * q + 2 * pr;
+            const u64 rs = pack2(rsq_approx(pz[cur][j]), rsq_approx(pz[cur][j + 1]));
+            const u64 inv = fmul2(rs, rs);
+            const u64 du = ffma2(pack2(px[cur][j], px[cur][j + 1]), inv, pr ? u4.y : u4.x);
+            const u64 dv = ffma2(pack2(py[cur][j], py[cur][j + 1]), inv, pr ? v4.y : v4.x);
+            const u64 e2 = ffma2(du, du, fmul2(dv, dv));
+            float ea, eb;
+            unpack2(e2, ea, eb);
+            if (COUNT) {
+              msac_add(ea, thr, s, c);
+              msac_add(eb, thr, s, c);
+            } else {
+              s2 = fadd2(s2, pack2(fminf(ea, thr), fminf(eb, thr)));
+            }
+          }
+        }
+        if (qd == 0) tmem_wait_ld8x3(px[nxt], py[nxt], pz[nxt]);
+        // the last columns are in registers: the set goes back to the producer, two groups of arithmetic to go
+        if (qd == 1) tmem_wait_ld8x3_release(px[nxt], py[nxt], pz[nxt], &S.acc_empty[grp], lane0);
+      }
+      live_in_chunk += max(0, min(kTcTile, n_live - (t_begin + it) * kTcTile));
+      if (((visit + 1) % kTcFlush) == 0 || it + 2 >= ntiles) {
+        if (COUNT) {
+          dacc += w * (static_cast<double>(s) + thr64 * static_cast<double>(live_in_chunk - c));
+          dcnt += c;
+        } else {
+          float sa, sb;
+          unpack2(s2, sa, sb);
+          const int processed = (visit % kTcFlush + 1) * kTcTile;
+          dacc += w * (static_cast<double>(sa) + static_cast<double>(sb) -
+                       static_cast<double>(thr) * static_cast<double>(processed - live_in_chunk));
+          s2 = 0ull;
+        }
+        s = 0.0f;
+        c = 0;
+        live_in_chunk = 0;
+      }
+    }
+  }
+
+  // join the two groups' sums of every hypothesis (fixed order: even tiles + odd tiles)
+  __syncthreads();  // every tile has landed and has been consumed: the ring is idle
+  TcJoin& J = *reinterpret_cast<TcJoin*>(S.ring);
+  if (!producer && grp == 1) {
+    J.s[hyp] = dacc;
+    J.c[hyp] = dcnt;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp < 4 && k < a.k) {
+    a.part_score[static_cast<size_t>(split) * a.k + k] = dacc + J.s[hyp];
+    if (COUNT) a.part_count[static_cast<size_t>(split) * a.k + k] = dcnt + J.c[hyp];
+  }
+  if (producer) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
+                 "r"(static_cast<uint32_t>(kTcpCols))
                  : "memory");
   }
 }
@@ -954,17 +1226,30 @@ int tc_hyps_per_cta() { return kTcThreads; }
 #endif
 constexpr int kTcHalves = RLB_TC_HALVES;
 
+#ifndef RLB_TC_PIPE
+#define RLB_TC_PIPE 0  // 0 (default): sweep_pose_tc_kernel; 1: sweep_pose_tcp_kernel (A/B: no faster, see its header)
+#endif
+
 int tc_resident_ctas() {
   static std::atomic<int> cache[64];  // per device; 0 = not asked yet
   std::atomic<int>& cached = cache[PerDeviceOnce::device()];
   if (const int v = cached.load(std::memory_order_relaxed)) return v;
+  int n = 0;
+#if RLB_TC_PIPE
+  cudaFuncSetAttribute(sweep_pose_tcp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(sizeof(TcpSmem)));
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tcp_kernel<true>, kTcpThreads,
+                                                    sizeof(TcpSmem)) != cudaSuccess)
+    n = 1;
+  const int v = max(1, min(n, 512 / kTcpCols));  // TMEM: 512 columns per SM
+#else
   cudaFuncSetAttribute(sweep_pose_tc_kernel<true, kTcHalves>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(TcSmem)));
-  int n = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc_kernel<true, kTcHalves>, 128 * kTcHalves,
                                                     sizeof(TcSmem)) != cudaSuccess)
     n = 1;
   const int v = max(1, min(n, 512 / kTcCols));  // TMEM: 512 columns per SM
+#endif
   cached.store(v, std::memory_order_relaxed);
   return v;
 }
@@ -974,6 +1259,22 @@ cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float
   ++*launches;
   static PerDeviceOnce configured;
   const int dev = PerDeviceOnce::device();
+  dim3 grid((a.k + 127) / 128, a.n_splits);
+#if RLB_TC_PIPE
+  if (!configured.done(dev)) {
+    cudaError_t e = cudaFuncSetAttribute(sweep_pose_tcp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(sizeof(TcpSmem)));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(sweep_pose_tcp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(sizeof(TcpSmem)));
+    if (e != cudaSuccess) return e;
+    configured.set(dev);
+  }
+  if (a.want_counts)
+    sweep_pose_tcp_kernel<true><<<grid, kTcpThreads, sizeof(TcpSmem), st>>>(d, a, tiles);
+  else
+    sweep_pose_tcp_kernel<false><<<grid, kTcpThreads, sizeof(TcpSmem), st>>>(d, a, tiles);
+#else
   if (!configured.done(dev)) {
     cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc_kernel<true, kTcHalves>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(TcSmem)));
@@ -983,11 +1284,11 @@ cudaError_t launch_sweep_tc(const DeviceData& d, const SweepArgs& a, const float
     if (e != cudaSuccess) return e;
     configured.set(dev);
   }
-  dim3 grid((a.k + 127) / 128, a.n_splits);
   if (a.want_counts)
     sweep_pose_tc_kernel<true, kTcHalves><<<grid, 128 * kTcHalves, sizeof(TcSmem), st>>>(d, a, tiles);
   else
     sweep_pose_tc_kernel<false, kTcHalves><<<grid, 128 * kTcHalves, sizeof(TcSmem), st>>>(d, a, tiles);
+#endif
   return cudaGetLastError();
 }
 
