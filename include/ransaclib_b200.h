@@ -52,6 +52,13 @@ extern "C" {
  * every pair in f64 (the round-1 kernel; also what RLB_F64 runs for lines and small batches). */
 #define RLB_F64_PLAIN 2
 #define RLB_F64_FILTERED 3 /* the filtered sweep whatever the batch size (RLB_F64 picks it from K x N >= 2^28) */
+/* Experimental (A/B): the sorted two-speed tensor-core sweep for f32 pose batches - a reciprocal-free filter
+ * a^2 + b^2 < thr pz^2 on every pair (-u, -v inside the contraction), the f32 evaluation only for the 8-point groups in
+ * which one of a warp's 32 hypotheses is flagged, hypotheses swept in the order of a prepass' flag counts. Same f32
+ * class and promises as RLB_F32; measured slower than the default on configs[4] (profiles/
+ * r02_tc_sorted_ab.txt), so RLB_F32 never picks it unless RLB_TC_SORTED=1 is set. The codes force / forbid it. */
+#define RLB_F32_SORTED 4
+#define RLB_F32_UNSORTED 5
 
 #define RLB_KIND_LINE 0        /* examples/line_estimator */
 #define RLB_KIND_HYBRID_LINE 1 /* examples/hybrid_line_estimator (2 data types) */

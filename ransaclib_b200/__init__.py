@@ -13,9 +13,10 @@ import weakref
 import numpy as np
 
 from . import _capi
-from ._capi import KIND_HYBRID_LINE, KIND_LINE, KIND_POSE, RLB_F32, RLB_F64, RLB_F64_FILTERED, RLB_F64_PLAIN, RlbError
+from ._capi import (KIND_HYBRID_LINE, KIND_LINE, KIND_POSE, RLB_F32, RLB_F32_SORTED, RLB_F32_UNSORTED, RLB_F64,
+                    RLB_F64_FILTERED, RLB_F64_PLAIN, RlbError)
 
-__all__ = ["Context", "Scorer", "Comm", "CommScorer", "RLB_F64", "RLB_F32", "RLB_F64_PLAIN", "RLB_F64_FILTERED", "RlbError", "KIND_LINE", "KIND_HYBRID_LINE", "KIND_POSE"]
+__all__ = ["Context", "Scorer", "Comm", "CommScorer", "RLB_F64", "RLB_F32", "RLB_F64_PLAIN", "RLB_F64_FILTERED", "RLB_F32_SORTED", "RLB_F32_UNSORTED", "RlbError", "KIND_LINE", "KIND_HYBRID_LINE", "KIND_POSE"]
 
 DBL_MAX = float(np.finfo(np.float64).max)
 

@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libransaclib_b200.so")
 
-RLB_F64, RLB_F32, RLB_F64_PLAIN, RLB_F64_FILTERED = 0, 1, 2, 3
+RLB_F64, RLB_F32, RLB_F64_PLAIN, RLB_F64_FILTERED, RLB_F32_SORTED, RLB_F32_UNSORTED = 0, 1, 2, 3, 4, 5
 KIND_LINE, KIND_HYBRID_LINE, KIND_POSE = 0, 1, 2
 
 # every symbol include/ransaclib_b200.h declares (tests check the .so exports all of them)

@@ -137,6 +137,7 @@ struct rlb_scorer {
   void* soa64 = nullptr;
   void* soa32 = nullptr;
   void* tc_tiles = nullptr;  // tensor-core operand tiles of the points, packed on first use
+  void* tc2_tiles = nullptr; // the operand image of the sorted two-speed sweep (variant 12), packed on first use
   rlb::CustomModule* custom = nullptr;  // RLB_KIND_CUSTOM: the NVRTC-compiled functor kernels
   void* custom_err = nullptr;           // RLB_KIND_CUSTOM: [npad] per-point errors of the K = 1 passes
 };
@@ -293,11 +294,15 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
               BestRec* d_best, double* d_best_model) {
   rlb_ctx* c = s->ctx;
   const DeviceData& d = s->d;
-  if (precision != RLB_F64 && precision != RLB_F32 && precision != RLB_F64_PLAIN && precision != RLB_F64_FILTERED)
+  if (precision != RLB_F64 && precision != RLB_F32 && precision != RLB_F64_PLAIN && precision != RLB_F64_FILTERED &&
+      precision != RLB_F32_SORTED && precision != RLB_F32_UNSORTED)
     return fail(RLB_E_ARG, "bad precision %d", precision);
   const bool plain64 = (precision == RLB_F64_PLAIN);        // f64 without the f32 pre-classification
   const bool filtered64 = (precision == RLB_F64_FILTERED);  // ... with it, whatever the size of the batch
   if (plain64 || filtered64) precision = RLB_F64;
+  const bool sorted32 = (precision == RLB_F32_SORTED);      // the sorted two-speed f32 sweep whatever the size
+  const bool unsorted32 = (precision == RLB_F32_UNSORTED);  // f32 without it
+  if (sorted32 || unsorted32) precision = RLB_F32;
   if (k <= 0) return fail(RLB_E_ARG, "k must be positive (got %d)", k);
   if (!thr) return fail(RLB_E_ARG, "sq_thr is required");
   {
@@ -450,7 +455,38 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
       a.stages_per_split = tc_tps;
     }
   }
-  if (use_tc && !s->tc_tiles) {
+  // The sorted two-speed form (prepass + order + sweep). Opt-in: RLB_TC_SORTED=1 picks it for large f32 sweeps
+  // (K >= 2048, K x N >= 2^30), the precision code RLB_F32_SORTED for any. On C5 it is SLOWER than variant 9 (30.0
+  // against 27.1 ms, profiles/r02_tc_sorted_ab.txt): nine dependent-latency MMAs per tile instead of six cap the
+  // pipeline at 24.9 ms even with no arithmetic at all, and at a 12 px threshold a third of the 8-point groups of
+  // a warp of random hypotheses still holds a flagged pair.
+  static const bool tc_sorted = [] {
+    const char* v = getenv("RLB_TC_SORTED");
+    return v && atoi(v) == 1;
+  }();
+  if (d.kind == RLB_KIND_POSE && precision == RLB_F32 && a.thr[0] > 0.0 &&
+      !unsorted32 &&
+      (forced_variant == 12 || sorted32 ||
+       (forced_variant < 0 && use_tc && a.variant == 9 && tc_sorted && k >= 2048 &&
+        static_cast<long long>(k) * d.n[0] >= (1LL << 30)))) {
+    const int total_tiles = d.npad / rlb::tc_tile_points();
+    const int slots = c->sms * rlb::tc2_resident_ctas();
+    const int k_tiles = (k + 127) / 128;
+    // as many splits as give ~8 waves of resident CTAs (the CTAs of the flagged hypotheses run ~1.7x longer)
+    const int want = std::max(1, std::min(std::min(256, total_tiles), (8 * slots + k_tiles - 1) / k_tiles));
+    const int tp = (total_tiles + want - 1) / want;
+    use_tc = true;
+    a.variant = 12;
+    a.n_splits = splits = (total_tiles + tp - 1) / tp;
+    a.stages_per_split = tp;
+  }
+  if (use_tc && a.variant == 12) {
+    if (!s->tc2_tiles) {
+      const int rc = pool_alloc(c, rlb::tc2_tiles_bytes(d.npad), &s->tc2_tiles);
+      if (rc) return rc;
+      RLB_CUDA(rlb::launch_tc2_pack(d, static_cast<float*>(s->tc2_tiles), c->stream, &c->launches_i));
+    }
+  } else if (use_tc && !s->tc_tiles) {
     const int rc = pool_alloc(c, rlb::tc_tiles_bytes(d.npad), &s->tc_tiles);
     if (rc) return rc;
     RLB_CUDA(rlb::launch_tc_pack(d, static_cast<float*>(s->tc_tiles), c->stream, &c->launches_i));
@@ -548,6 +584,31 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     a.pos = pos;
     a.acc_q = acc_q;
     a.acc_c = acc_c;
+  } else if (use_tc && a.variant == 12) {
+    // Sorted two-speed sweep: prepass over every 64th tile -> sweep order by flag count -> the sweep in that order.
+    const float* tiles = static_cast<const float*>(s->tc2_tiles);
+    const int total_tiles = d.npad / rlb::tc_tile_points();
+    const int k_tiles = (k + 127) / 128;
+    const int slots = c->sms * rlb::tc2_resident_ctas();
+    RLB_CUDA(c->tcx_lists.ensure(static_cast<size_t>(k) * 2 * sizeof(int32_t)));
+    int32_t* order = c->tcx_lists.as<int32_t>();
+    int32_t* pos = order + k;
+    const int stride = 64;
+    const int n_sample = (total_tiles + stride - 1) / stride;
+    SweepArgs pa = a;
+    pa.tile_stride = stride;
+    pa.n_splits = std::max(1, std::min(n_sample, (slots + k_tiles - 1) / k_tiles));
+    pa.stages_per_split = (n_sample + pa.n_splits - 1) / pa.n_splits;
+    pa.n_splits = (n_sample + pa.stages_per_split - 1) / pa.stages_per_split;
+    RLB_CUDA(c->part_count.ensure(static_cast<size_t>(std::max(splits, pa.n_splits)) * k * sizeof(int32_t)));
+    pa.part_count = c->part_count.as<int32_t>();
+    a.part_count = pa.part_count;
+    RLB_CUDA(rlb::launch_sweep_tc2(d, pa, tiles, true, c->stream, &c->launches_i));
+    RLB_CUDA(rlb::launch_tc2_order(pa.part_count, pa.n_splits, k, order, pos, c->stream, &c->launches_i));
+    a.ids = order;
+    RLB_CUDA(rlb::launch_sweep_tc2(d, a, tiles, false, c->stream, &c->launches_i));
+    a.ids = nullptr;  // finalize walks all k hypotheses and finds their partials through pos
+    a.pos = pos;
   } else if (use_tc) {
     RLB_CUDA(rlb::launch_sweep_tc(d, a, static_cast<const float*>(s->tc_tiles), c->stream, &c->launches_i));
   } else {
@@ -1056,7 +1117,7 @@ int rlb_scorer_destroy(rlb_scorer* s) {
     cudaStreamSynchronize(s->ctx->stream);
   }
   rlb::custom_unload(s->custom);
-  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32, s->tc_tiles, s->custom_err};
+  void* ptrs[] = {s->raw0, s->raw1, s->rays, s->soa64, s->soa32, s->tc_tiles, s->tc2_tiles, s->custom_err};
   for (void* p : ptrs) {
     if (!p) continue;
     if (s->ctx) pool_release(s->ctx, p);

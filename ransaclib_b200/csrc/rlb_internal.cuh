@@ -151,6 +151,14 @@ cudaError_t launch_sweep_tcx_prepass(const DeviceData& d, const SweepArgs& a, co
 cudaError_t launch_tcx_partition(const int32_t* flagged, int n_splits, int k, int sample_points, int32_t* lists,
                                  int32_t* pos, int32_t* counts, cudaStream_t st, int* launches);
 int tcx_resident_ctas();
+// sorted two-speed f32 sweep (variant 12): -u / -v inside the contraction, reciprocal-free filter, quality order
+size_t tc2_tiles_bytes(int npad);
+cudaError_t launch_tc2_pack(const DeviceData& d, float* tiles, cudaStream_t st, int* launches);
+cudaError_t launch_sweep_tc2(const DeviceData& d, const SweepArgs& a, const float* tiles, bool prepass,
+                             cudaStream_t st, int* launches);
+cudaError_t launch_tc2_order(const int32_t* flagged, int n_splits, int k, int32_t* order, int32_t* pos,
+                             cudaStream_t st, int* launches);
+int tc2_resident_ctas();
 int tc_tile_points();
 size_t tc_tiles_bytes(int npad);
 int tc_hyps_per_cta();

@@ -1217,6 +1217,439 @@ int tcx_resident_ctas() {
   return v;
 }
 
+// ------------------------------------------------ the sorted two-speed sweep (variant 12)
+// The probes above say the tensor-core sweep is bound by CUDA-core dispatch: ~15 dispatch slots per evaluation,
+// of which the reciprocal, the residual and the MSAC adds (9) only matter for pairs that can be inliers - and for
+// random minimal-sample hypotheses almost no pair is. Two changes make the common case cheap:
+//  1. -u, -v move into the contraction: a = px - u pz and b = py - v pz are bilinear in (hypothesis, point)
+//         a = [rx tx | rz tz] . [X 1 | -uX -u]        b = [rz tz | ry ty] . [-vX -v | X 1]      pz = [rz tz | ..] . [X 1 | 0]
+//     (K = 8 each, TF32 hi/lo split: A_hi B_hi + A_lo B_hi + A_hi B_lo, nine MMAs per 32-point tile instead of six),
+//     and the inlier test needs no reciprocal:  e < thr  <=>  a^2 + b^2 < thr pz^2  (pz > 0).
+//  2. the test is a FILTER: q = a^2 + b^2 < thr (1 + 2^-12) pz^2 flags a superset of the inliers (rounding of either
+//     side is covered by the margin; the sign of pz is not looked at). A warp whose 32 hypotheses flag none of the
+//     eight points of a column group skips them (they add thr each, which the count-based score formula already
+//     does); otherwise the group goes through e = q / pz^2 (rsqrt, as before), the MSAC test and the sums.
+//     What is added to a hypothesis' sums is decided by the second, exact step alone, so a score does not depend
+//     on which other hypotheses share the warp.
+// For the skip to happen the hypotheses of a warp must be alike: a prepass over every 64th tile counts each
+// hypothesis' flags, tc2_order_kernel buckets the hypotheses by that count (log2 buckets, best first) and the sweep
+// walks them in that order (a.ids); finalize_kernel finds a hypothesis' partials through a.pos.
+// Built on the producer / epilogue-group skeleton of sweep_pose_tcp_kernel (the nine MMAs of tile t + 1 run under
+// the reduction of tile t). Point image: six 512-byte K-chunks per tile, [c2h c0h c1h | c2l c0l c1l] with
+// c0 = (X, 1), c1 = (-uX, -u), c2 = (-vX, -v); the zero chunk of pz sits once behind the ring.
+constexpr int kTc2TileFloats = 6 * 128;
+constexpr int kTc2TileBytes = kTc2TileFloats * 4;
+
+__global__ void tc2_pack_kernel(const DeviceData d, float* __restrict__ tiles) {
+  const int total = d.npad;
+  for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
+    float c[3][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    float l[3][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    if (g < d.n[0]) {  // padding stays all zero: a = b = pz = 0 is never flagged and never counted
+      const double x[4] = {static_cast<double>(d.soa32[0 * static_cast<size_t>(total) + g]),
+                           static_cast<double>(d.soa32[1 * static_cast<size_t>(total) + g]),
+                           static_cast<double>(d.soa32[2 * static_cast<size_t>(total) + g]), 1.0};
+      const double f[3] = {1.0, static_cast<double>(d.soa32[3 * static_cast<size_t>(total) + g]),   // -u
+                           static_cast<double>(d.soa32[4 * static_cast<size_t>(total) + g])};       // -v
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const double pr = f[ch] * x[j];  // exact in f64 (24 x 24 bits)
+          c[ch][j] = tf32_hi(static_cast<float>(pr));
+          l[ch][j] = static_cast<float>(pr - static_cast<double>(c[ch][j]));
+        }
+    }
+    float* t = tiles + static_cast<size_t>(g / kTcTile) * kTc2TileFloats;
+    const int n = g % kTcTile;
+    const int at = ((n >> 3) * 8 + (n & 7)) * 4;  // core matrix n / 8, row n % 8
+    const int order[3] = {1, 2, 0};               // chunk slot of c0, c1, c2: [c2 c0 c1]
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      *reinterpret_cast<float4*>(t + order[ch] * 128 + at) = make_float4(c[ch][0], c[ch][1], c[ch][2], c[ch][3]);
+      *reinterpret_cast<float4*>(t + (3 + order[ch]) * 128 + at) = make_float4(l[ch][0], l[ch][1], l[ch][2], l[ch][3]);
+    }
+  }
+}
+
+struct Tc2Smem {
+  float ring[kTcRing][kTc2TileFloats];
+  float zero[128];          // the second K-chunk of pz's B operand
+  uint64_t full[kTcRing];
+  uint64_t acc_full[2];
+  uint64_t acc_empty[2];
+  uint32_t tmem_base;
+};
+
+// PREPASS: tiles t_begin, t_begin + stride, ...; part_count[split][k] = flags of hypothesis k (identity order).
+template <bool PREPASS>
+__global__ void __launch_bounds__(kTcpThreads, 2)
+    sweep_pose_tc2_kernel(const DeviceData d, const SweepArgs a, const float* __restrict__ tiles) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  Tc2Smem& S = *reinterpret_cast<Tc2Smem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const bool producer = warp == 8;
+  const int quarter = warp & 3;
+  const int grp = (warp >> 2) & 1;
+  const int hyp = quarter * 32 + (tid & 31);
+  const int kk = blockIdx.x * 128 + hyp;  // position in the sweep order
+  const int split = blockIdx.y;
+  const int n_live = d.n[0];
+  const int stride = PREPASS ? a.tile_stride : 1;
+
+  const int total_tiles = d.npad / kTcTile;
+  const int sweep_tiles = PREPASS ? (total_tiles + stride - 1) / stride : total_tiles;
+  const int t_begin = split * a.stages_per_split;
+  const int t_end = min(sweep_tiles, t_begin + a.stages_per_split);
+  const int ntiles = max(0, t_end - t_begin);
+
+  if (producer) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)),
+                 "r"(static_cast<uint32_t>(kTcpCols))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kTcRing; ++s) mbar_init(&S.full[s], 1);
+    mbar_init(&S.acc_full[0], 1);
+    mbar_init(&S.acc_full[1], 1);
+    mbar_init(&S.acc_empty[0], 4);
+    mbar_init(&S.acc_empty[1], 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid < 128) S.zero[tid] = 0.0f;
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // S.zero is read by the tensor core (async proxy)
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = S.tmem_base;
+  const uint32_t lane_addr = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+  if (warp < 4) {
+    // A operand, TMEM columns: [0,8) (rx tx | rz tz) hi, [8,16) (rz tz | ry ty) hi, [16,24) and [24,32) the lo parts
+    float r[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float t[3] = {0.f, 0.f, 0.f};
+    const int k = (kk < a.k) ? (a.ids ? a.ids[kk] : kk) : -1;
+    if (k >= 0) {
+      const double* m = a.models + static_cast<size_t>(k) * 12;
+      const double dc[3] = {d.centre[0] - m[9], d.centre[1] - m[10], d.centre[2] - m[11]};
+      const double sc[3] = {d.fx, d.fy, 1.0};
+#pragma unroll
+      for (int row = 0; row < 3; ++row) {
+        const double r0 = m[row], r1 = m[row + 3], r2 = m[row + 6];
+        r[3 * row + 0] = static_cast<float>(r0 * sc[row]);
+        r[3 * row + 1] = static_cast<float>(r1 * sc[row]);
+        r[3 * row + 2] = static_cast<float>(r2 * sc[row]);
+        t[row] = static_cast<float>((r0 * dc[0] + r1 * dc[1] + r2 * dc[2]) * sc[row]);
+      }
+    }
+    const int rows[2][2] = {{0, 2}, {2, 1}};  // (x | z), (z | y)
+#pragma unroll
+    for (int blk = 0; blk < 2; ++blk) {
+      float hi[8], lo[8];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int row = rows[blk][h];
+        const float v[4] = {r[3 * row], r[3 * row + 1], r[3 * row + 2], t[row]};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          hi[4 * h + j] = tf32_hi(v[j]);
+          lo[4 * h + j] = v[j] - hi[4 * h + j];
+        }
+      }
+      tmem_st8(lane_addr + 8 * blk, hi);
+      tmem_st8(lane_addr + 16 + 8 * blk, lo);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  double dacc = 0.0;
+  int dcnt = 0;
+
+  if (producer) {
+    auto issue_tma = [&](int it) {
+      const int slot = it % kTcRing;
+      mbar_expect_tx(&S.full[slot], kTc2TileBytes);
+      tma_load_1d(S.ring[slot], tiles + static_cast<size_t>(t_begin + it) * stride * kTc2TileFloats, kTc2TileBytes,
+                  &S.full[slot]);
+    };
+    if (elect_one()) {
+      for (int it = 0; it < kTcRing && it < ntiles; ++it) issue_tma(it);
+    }
+    __syncwarp();
+    const uint32_t zero_addr = smem_u32(S.zero);
+#ifdef RLB_TC2_STAMPS
+    long long st_p[4] = {0, 0, 0, 0};
+#define TC2_STAMP(arr, i, t0) { const long long t1_ = clock64(); arr[i] += t1_ - t0; t0 = t1_; }
+    long long tp = clock64();
+#else
+#define TC2_STAMP(arr, i, t0)
+#endif
+    for (int it = 0; it < ntiles; ++it) {
+      const int slot = it % kTcRing;
+      const int buf = it & 1;
+      TC2_STAMP(st_p, 3, tp);
+      if (it >= 2) {
+        mbar_wait(&S.acc_empty[buf], ((it >> 1) - 1) & 1);
+        // the group that handed set `buf` back has finished tile it - 2: the operand tiles are only read by the
+        // tensor core, whose MMAs on tile it - 2 completed before that group could start
+        if (it - 2 + kTcRing < ntiles) {
+          if (elect_one()) issue_tma(it - 2 + kTcRing);
+          __syncwarp();
+        }
+      }
+      TC2_STAMP(st_p, 0, tp);
+      mbar_wait(&S.full[slot], (it / kTcRing) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      TC2_STAMP(st_p, 1, tp);
+      if (elect_one()) {
+        const uint32_t b_addr = smem_u32(S.ring[slot]);
+        const uint32_t acc = tmem + 32 + 96 * buf;
+#pragma unroll
+        for (int part = 0; part < 3; ++part) {
+          // part 0: A hi x B hi, 1: A lo x B hi, 2: A hi x B lo
+          const uint32_t a_off = (part == 1) ? 16u : 0u;
+          const uint32_t b_off = (part == 2) ? 3u * 512u : 0u;
+          const uint32_t c0 = b_addr + b_off + 512u;  // chunk order [c2 c0 c1]
+          umma_tf32_ts(acc + 0 * kTcTile, tmem + a_off + 0, umma_desc(c0, 512, 128), part);                // a
+          umma_tf32_ts(acc + 1 * kTcTile, tmem + a_off + 8, umma_desc(b_addr + b_off, 512, 128), part);    // b
+#ifdef RLB_TC2_PROBE_PZ  // timing probe (wrong results): an ordinary descriptor for pz
+          umma_tf32_ts(acc + 2 * kTcTile, tmem + a_off + 8, umma_desc(c0, 512, 128), part);
+#else
+          umma_tf32_ts(acc + 2 * kTcTile, tmem + a_off + 8, umma_desc(c0, zero_addr - c0, 128), part);     // pz
+#endif
+        }
+        umma_commit(&S.acc_full[buf]);
+      }
+      __syncwarp();
+      TC2_STAMP(st_p, 2, tp);
+    }
+#ifdef RLB_TC2_STAMPS
+    if (!PREPASS && blockIdx.x == 300 && blockIdx.y == 1 && (tid & 31) == 0)
+      printf("producer: tiles %d  wait_empty %lld  wait_full %lld  mma_issue %lld  other %lld (cycles per tile)\n", ntiles,
+             st_p[0] / ntiles, st_p[1] / ntiles, st_p[2] / ntiles, st_p[3] / ntiles);
+#endif
+  } else {
+    const double thr64 = a.thr[0];
+    const float thr = static_cast<float>(thr64);
+    const float thrw = thr * (1.0f + 1.0f / 4096.0f);
+    const u64 thrw2 = pack2(thrw, thrw);
+    const double w = a.w[0];
+    const uint32_t lane0 = (tid & 31) == 0 ? 1u : 0u;
+    const uint32_t acc = lane_addr + 32 + 96 * grp;
+    float s = 0.0f;
+    int c = 0;
+    int live_in_chunk = 0;
+    int visit = 0;
+#ifdef RLB_TC2_STAMPS
+    long long st_e[4] = {0, 0, 0, 0};
+    long long te = clock64();
+#endif
+    for (int it = grp; it < ntiles; it += 2, ++visit) {
+      TC2_STAMP(st_e, 3, te);
+      mbar_wait(&S.acc_full[grp], visit & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      TC2_STAMP(st_e, 0, te);
+      float pa[3][8], pb[3][8], pz[3][8];
+      tmem_ld8(acc + 0 * kTcTile, pa[0]);
+      tmem_ld8(acc + 1 * kTcTile, pb[0]);
+      tmem_ld8(acc + 2 * kTcTile, pz[0]);
+      tmem_ld8(acc + 0 * kTcTile + 8, pa[1]);
+      tmem_ld8(acc + 1 * kTcTile + 8, pb[1]);
+      tmem_ld8(acc + 2 * kTcTile + 8, pz[1]);
+      tmem_wait_ld8x3(pa[0], pb[0], pz[0]);
+      tmem_wait_ld8x3(pa[1], pb[1], pz[1]);
+      TC2_STAMP(st_e, 1, te);
+#pragma unroll
+      for (int qd = 0; qd < 4; ++qd) {
+        const int cur = qd % 3, nxt = (qd + 2) % 3;
+        if (qd < 2) {
+          tmem_ld8(acc + 0 * kTcTile + 8 * (qd + 2), pa[nxt]);
+          tmem_ld8(acc + 1 * kTcTile + 8 * (qd + 2), pb[nxt]);
+          tmem_ld8(acc + 2 * kTcTile + 8 * (qd + 2), pz[nxt]);
+        }
+        u64 q[4];
+        bool flag = false;
+#ifdef RLB_TC2_PROBE_NOEPI
+#pragma unroll
+        for (int pr = 0; pr < 4; ++pr) q[pr] = pack2(pa[cur][2 * pr], pb[cur][2 * pr + 1]);
+#else
+#pragma unroll
+        for (int pr = 0; pr < 4; ++pr) {
+          const int j = 2 * pr;
+          const u64 a2 = pack2(pa[cur][j], pa[cur][j + 1]);
+          const u64 b2 = pack2(pb[cur][j], pb[cur][j + 1]);
+          const u64 z2 = pack2(pz[cur][j], pz[cur][j + 1]);
+          q[pr] = ffma2(a2, a2, fmul2(b2, b2));
+          const u64 t2 = fmul2(fmul2(thrw2, z2), z2);
+          float qa, qb, ta, tb;
+          unpack2(q[pr], qa, qb);
+          unpack2(t2, ta, tb);
+          if (PREPASS) {
+            c += (qa < ta) ? 1 : 0;
+            c += (qb < tb) ? 1 : 0;
+          } else {
+            flag = flag || (qa < ta) || (qb < tb);
+          }
+        }
+#endif
+#ifdef RLB_TC2_PROBE_NOSLOW  // timing probe (wrong results): the filter alone
+        if (false) {
+#elif defined(RLB_TC2_PROBE_NOEPI)  // timing probe (wrong results): TMEM loads only
+        if (pa[cur][0] == 1234.5f) {
+#else
+        if (!PREPASS && __any_sync(0xffffffffu, flag)) {
+#endif
+#pragma unroll
+          for (int pr = 0; pr < 4; ++pr) {
+            const int j = 2 * pr;
+            const u64 rs = pack2(rsq_approx(pz[cur][j]), rsq_approx(pz[cur][j + 1]));
+            const u64 r2 = fmul2(rs, rs);
+            const u64 e2 = fmul2(q[pr], fmul2(r2, r2));  // pz < 0: NaN, pz == 0: inf or NaN - never below thr
+            float ea, eb;
+            unpack2(e2, ea, eb);
+            msac_add(ea, thr, s, c);
+            msac_add(eb, thr, s, c);
+          }
+        }
+        if (qd == 0) tmem_wait_ld8x3(pa[nxt], pb[nxt], pz[nxt]);
+        if (qd == 1) tmem_wait_ld8x3_release(pa[nxt], pb[nxt], pz[nxt], &S.acc_empty[grp], lane0);
+        if (qd == 1) TC2_STAMP(st_e, 2, te);
+      }
+      if (!PREPASS) {
+        live_in_chunk += max(0, min(kTcTile, n_live - (t_begin + it) * kTcTile));
+        if (((visit + 1) % kTcFlush) == 0 || it + 2 >= ntiles) {
+          dacc += w * (static_cast<double>(s) + thr64 * static_cast<double>(live_in_chunk - c));
+          dcnt += c;
+          s = 0.0f;
+          c = 0;
+          live_in_chunk = 0;
+        }
+      }
+    }
+    if (PREPASS) dcnt = c;
+#ifdef RLB_TC2_STAMPS
+    if (!PREPASS && blockIdx.x == 300 && blockIdx.y == 1 && (tid & 31) == 0 && (warp & 3) == 0)
+      printf("group %d: visits %d  wait_full %lld  first_loads %lld  until_release %lld  rest %lld (cycles per tile)\n", grp,
+             visit, st_e[0] / max(visit, 1), st_e[1] / max(visit, 1), st_e[2] / max(visit, 1), st_e[3] / max(visit, 1));
+#endif
+  }
+
+  __syncthreads();  // every tile has landed and has been consumed: the ring is idle
+  TcJoin& J = *reinterpret_cast<TcJoin*>(S.ring);
+  if (!producer && grp == 1) {
+    J.s[hyp] = dacc;
+    J.c[hyp] = dcnt;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp < 4 && kk < a.k) {
+    if (!PREPASS) a.part_score[static_cast<size_t>(split) * a.k + kk] = dacc + J.s[hyp];
+    if (PREPASS || a.want_counts) a.part_count[static_cast<size_t>(split) * a.k + kk] = dcnt + J.c[hyp];
+  }
+  if (producer) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
+                 "r"(static_cast<uint32_t>(kTcpCols))
+                 : "memory");
+  }
+}
+
+// Sweep order from the prepass counts: bucket 0 = no flag in the sample, bucket b = 1 + floor(log2(count));
+// the order is buckets descending (the slow warps first), any order inside a bucket (shared-memory cursors: a
+// hypothesis' sums do not depend on its place, so the order need not be reproducible).
+//   order[0 .. k) hypothesis ids in sweep order, pos[k] = place of hypothesis k
+__global__ void __launch_bounds__(1024)
+    tc2_order_kernel(const int32_t* __restrict__ flagged, int n_splits, int k, int32_t* __restrict__ order,
+                     int32_t* __restrict__ pos) {
+  __shared__ int hist[32];
+  __shared__ int cursor[32];
+  const int tid = threadIdx.x;
+  if (tid < 32) hist[tid] = 0;
+  __syncthreads();
+  auto bucket_of = [&](int kk) {
+    int nf = 0;
+    for (int sp = 0; sp < n_splits; ++sp) nf += flagged[static_cast<size_t>(sp) * k + kk];
+    return nf <= 0 ? 0 : 32 - __clz(nf);
+  };
+  for (int kk = tid; kk < k; kk += 1024) atomicAdd(&hist[bucket_of(kk)], 1);
+  __syncthreads();
+  if (tid == 0) {
+    int at = 0;
+    for (int b = 31; b >= 0; --b) {
+      cursor[b] = at;
+      at += hist[b];
+    }
+  }
+  __syncthreads();
+  for (int kk = tid; kk < k; kk += 1024) {
+    const int p = atomicAdd(&cursor[bucket_of(kk)], 1);
+    order[p] = kk;
+    pos[kk] = p;
+  }
+}
+
+size_t tc2_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * kTc2TileBytes; }
+
+cudaError_t launch_tc2_pack(const DeviceData& d, float* tiles, cudaStream_t st, int* launches) {
+  ++*launches;
+  const int blocks = max(1, min(2048, (d.npad + 255) / 256));
+  tc2_pack_kernel<<<blocks, 256, 0, st>>>(d, tiles);
+  return cudaGetLastError();
+}
+
+static cudaError_t tc2_configure() {
+  static PerDeviceOnce configured;
+  const int dev = PerDeviceOnce::device();
+  if (configured.done(dev)) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(sweep_pose_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       static_cast<int>(sizeof(Tc2Smem)));
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(sweep_pose_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(sizeof(Tc2Smem)));
+  if (e == cudaSuccess) configured.set(dev);
+  return e;
+}
+
+int tc2_resident_ctas() {
+  static std::atomic<int> cache[64];
+  std::atomic<int>& cached = cache[PerDeviceOnce::device()];
+  if (const int v = cached.load(std::memory_order_relaxed)) return v;
+  tc2_configure();
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, sweep_pose_tc2_kernel<false>, kTcpThreads,
+                                                    sizeof(Tc2Smem)) != cudaSuccess)
+    n = 1;
+  const int v = max(1, min(n, 512 / kTcpCols));
+  cached.store(v, std::memory_order_relaxed);
+  return v;
+}
+
+// prepass = true: a.tile_stride, a.n_splits / stages_per_split over the sampled tiles, counts to a.part_count
+cudaError_t launch_sweep_tc2(const DeviceData& d, const SweepArgs& a, const float* tiles, bool prepass,
+                             cudaStream_t st, int* launches) {
+  ++*launches;
+  const cudaError_t e = tc2_configure();
+  if (e != cudaSuccess) return e;
+  dim3 grid((a.k + 127) / 128, a.n_splits);
+  if (prepass)
+    sweep_pose_tc2_kernel<true><<<grid, kTcpThreads, sizeof(Tc2Smem), st>>>(d, a, tiles);
+  else
+    sweep_pose_tc2_kernel<false><<<grid, kTcpThreads, sizeof(Tc2Smem), st>>>(d, a, tiles);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tc2_order(const int32_t* flagged, int n_splits, int k, int32_t* order, int32_t* pos,
+                             cudaStream_t st, int* launches) {
+  ++*launches;
+  tc2_order_kernel<<<1, 1024, 0, st>>>(flagged, n_splits, k, order, pos);
+  return cudaGetLastError();
+}
+
 int tc_tile_points() { return kTcTile; }
 size_t tc_tiles_bytes(int npad) { return static_cast<size_t>(npad / kTcTile) * kTcTileBytes + 256; }  // + bounds
 int tc_hyps_per_cta() { return kTcThreads; }

@@ -387,6 +387,59 @@ def test_tensor_core_sweep_edges(ctx, n):
     assert np.abs(c_f - c[:500]).max() <= 2
 
 
+@pytest.mark.parametrize("n", [5, 31, 32, 33, 700, 4097, 70_000])
+def test_sorted_two_speed_sweep(ctx, n):
+    """RLB_F32_SORTED (sweep variant 12, an opt-in experiment: RLB_TC_SORTED=1 lets RLB_F32 pick it): -u / -v
+    inside the tensor-core contraction, a reciprocal-free filter on every pair, the exact f32 evaluation only where
+    a warp has a flagged hypothesis, hypotheses swept in the order of a prepass. Against the oracle (f32 tolerance,
+    same winner), against the unsorted tensor-core sweep, with and without counts; good, bad, behind-the-camera,
+    invalid and non-finite hypotheses mixed so that warps hold both kinds; and a hypothesis' inlier decisions must
+    not depend on what else is in the batch."""
+    n_in = max(3, n // 2)
+    inst = synth.pose_instance(277 + n, n_in, n - n_in)
+    f = inst["focal"]
+    p2, p3 = inst["points2D"], inst["points3D"]
+    sc = ctx.pose_scorer(p2, p3, f, f)
+    k = 1300
+    rng = np.random.default_rng(n)
+    good = synth.perturbed_poses(5, inst["R_gt"], inst["c_gt"], k, rot_sigma=0.002, trans_sigma=0.01)
+    bad = synth.perturbed_poses(6, inst["R_gt"], inst["c_gt"], k, rot_sigma=0.6, trans_sigma=3.0)
+    models = np.where((rng.random(k) < 0.15)[:, None], good, bad)
+    behind = good[:8].copy().reshape(8, 4, 3)  # half a turn about x: every depth changes sign
+    behind[:, :3, 1:] *= -1.0
+    models[100:108] = behind.reshape(8, 12)
+    models[200, 4] = np.nan
+    models[201, 10] = np.inf
+    valid = np.ones(k, dtype=np.uint8)
+    valid[300:310] = 0
+    O = ol.oracle()
+    ws, wc = ol.pose_score(O, f, f, p2, p3, models, 144.0)
+    ok = np.ones(k, dtype=bool)
+    ok[[200, 201]] = False
+    ok[300:310] = False
+    m = rlb()
+    s, c, bid, _ = sc.score_models(models, 144.0, valid=valid, precision=m.RLB_F32_SORTED)
+    assert ctx.last_sweep_plan()[0] == 12
+    np.testing.assert_allclose(s[ok], ws[ok], rtol=F32_RTOL)
+    assert np.abs(c[ok] - wc[ok]).max() <= 2 and (c[100:108] == 0).all()
+    assert np.isnan(s[200]) and (s[300:310] == np.finfo(np.float64).max).all()
+    wsm = np.where(ok, ws, np.inf)
+    assert bid == int(np.argmin(wsm))
+    s9, c9, bid9, _ = sc.score_models(models, 144.0, valid=valid, precision=m.RLB_F32_UNSORTED)
+    assert ctx.last_sweep_plan()[0] == 9
+    np.testing.assert_allclose(s[ok], s9[ok], rtol=2e-5)
+    assert np.abs(c[ok] - c9[ok]).max() <= 2 and bid9 == bid
+    s_nc, c_nc, bid_nc, _ = sc.score_models(models, 144.0, valid=valid, precision=m.RLB_F32_SORTED, want_counts=False)
+    assert c_nc is None and bid_nc == bid
+    np.testing.assert_array_equal(s_nc[ok], s[ok])
+    # another batch composition (other neighbours in the warp, another sweep order): the same inlier decisions;
+    # the sums agree to f32-flush rounding only (another K gives another split plan, as for every sweep here)
+    sub = np.concatenate([np.arange(0, k, 3), np.arange(1, k, 7)])
+    s_sub, c_sub, _, _ = sc.score_models(models[sub], 144.0, valid=valid[sub], precision=m.RLB_F32_SORTED)
+    np.testing.assert_allclose(s_sub[ok[sub]], s[sub][ok[sub]], rtol=1e-7)
+    np.testing.assert_array_equal(c_sub[ok[sub]], c[sub][ok[sub]])
+
+
 @pytest.mark.parametrize("n", [5, 33, 700, 4097, 70_000])
 def test_filtered_f64_sweep_equals_the_plain_f64_sweep(ctx, n):
     """RLB_F64_FILTERED (what RLB_F64 runs for pose batches of K x N >= 2^28): f32 classification on the tensor
