@@ -73,6 +73,8 @@ int rlb_version(void);
 
 /* ---- context ------------------------------------------------------------- */
 int rlb_ctx_create(int device, rlb_ctx** ctx);
+/* Scorers point into their context. Destroying a context while scorers created on it are alive is allowed (a garbage
+ * collector finalises objects in no particular order): the context then lives on until the last of them is destroyed. */
 int rlb_ctx_destroy(rlb_ctx* ctx);
 /* Run on an existing cudaStream_t (e.g. torch's current stream). The handle is used
  * as given: NULL is CUDA's legacy default stream. rlb_ctx_use_own_stream goes back to

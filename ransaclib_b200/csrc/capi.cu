@@ -61,6 +61,11 @@ struct DevBuf {
 
 struct rlb_ctx {
   int device = 0;
+  // Scorers keep pointers into their context (stream, pool). A context destroyed while some are alive - a
+  // garbage collector finalising objects in no particular order does that - only marks itself; the last
+  // rlb_scorer_destroy then completes the destruction.
+  int live_scorers = 0;
+  bool destroy_pending = false;
   int sms = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
@@ -755,6 +760,10 @@ int rlb_ctx_create(int device, rlb_ctx** out) {
 
 int rlb_ctx_destroy(rlb_ctx* c) {
   if (!c) return RLB_OK;
+  if (c->live_scorers > 0) {
+    c->destroy_pending = true;  // completed by the last rlb_scorer_destroy
+    return RLB_OK;
+  }
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   DevBuf* bufs[] = {&c->models, &c->valid, &c->samples, &c->scores, &c->counts, &c->part_score,
@@ -811,6 +820,7 @@ int rlb_scorer_create_line(rlb_ctx* c, int n, const double* xy, rlb_scorer** out
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
   if (!s) return fail(RLB_E_NOMEM, "out of host memory");
   s->ctx = c;
+  ++c->live_scorers;
   DeviceData& d = s->d;
   memset(&d, 0, sizeof(d));
   d.kind = RLB_KIND_LINE;
@@ -842,6 +852,7 @@ int rlb_scorer_create_hybrid_line(rlb_ctx* c, int n0, const double* xy0, int n1,
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
   if (!s) return fail(RLB_E_NOMEM, "out of host memory");
   s->ctx = c;
+  ++c->live_scorers;
   DeviceData& d = s->d;
   memset(&d, 0, sizeof(d));
   d.kind = RLB_KIND_HYBRID_LINE;
@@ -879,6 +890,7 @@ int rlb_scorer_create_pose(rlb_ctx* c, int n, const double* p2d, const double* p
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
   if (!s) return fail(RLB_E_NOMEM, "out of host memory");
   s->ctx = c;
+  ++c->live_scorers;
   DeviceData& d = s->d;
   memset(&d, 0, sizeof(d));
   d.kind = RLB_KIND_POSE;
@@ -920,6 +932,7 @@ int scorer_pose_begin(rlb_ctx* c, int n, double fx, double fy, rlb_scorer** out,
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
   if (!s) return fail(RLB_E_NOMEM, "out of host memory");
   s->ctx = c;
+  ++c->live_scorers;
   DeviceData& d = s->d;
   memset(&d, 0, sizeof(d));
   d.kind = RLB_KIND_POSE;
@@ -1048,6 +1061,7 @@ int create_custom(rlb_ctx* c, int num_types, const int* n, const int* dims_t, co
   rlb_scorer* s = new (std::nothrow) rlb_scorer();
   if (!s) return fail(RLB_E_NOMEM, "out of host memory");
   s->ctx = c;
+  ++c->live_scorers;
   DeviceData& d = s->d;
   memset(&d, 0, sizeof(d));
   d.kind = RLB_KIND_CUSTOM;
@@ -1123,7 +1137,9 @@ int rlb_scorer_destroy(rlb_scorer* s) {
     if (s->ctx) pool_release(s->ctx, p);
     else cudaFree(p);
   }
+  rlb_ctx* c = s->ctx;
   delete s;
+  if (c && --c->live_scorers == 0 && c->destroy_pending) return rlb_ctx_destroy(c);
   return RLB_OK;
 }
 

@@ -23,3 +23,10 @@ print("pass count only us", round(t(lambda: sc.get_inliers(m, 144.0, 144.0, want
 for k in (256, 512, 1024, 2048, 4096):
     print("hyp+score K=%d us" % k, round(t(lambda: sc.hypothesize_and_score(samples[:k], 144.0), 50), 1),
           "f32", round(t(lambda: sc.hypothesize_and_score(samples[:k], 144.0, precision=rlb.RLB_F32), 50), 1))
+ctx.set_timing(True)
+ks = []
+for _ in range(50):
+    sc.get_inliers(m, 144.0, 144.0)
+    ks.append(ctx.kernel_time_ms(1) * 1e3)
+print("pass kernel (events around the launch) us", round(float(np.median(ks)), 1))
+print("pass with list, timing events on, us", round(t(lambda: sc.get_inliers(m, 144.0, 144.0), 300), 1))
