@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/r27_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/r27_pytest.log
-python tools/probes/exit_probe2.py 2>&1 | tail -8
+python tools/lat_probe.py 2>&1 | tail -3
