@@ -18,6 +18,7 @@
 #include "calibrated_absolute_pose_estimator.h"
 #include "hybrid_custom_line_estimator.h"
 #include "hybrid_line_estimator.h"
+#include "hybrid_pose_estimator.h"
 #include "line_estimator.h"
 #include "localization_io.h"
 
@@ -25,6 +26,7 @@ using namespace ransac_lib;
 using calibrated_absolute_pose::CalibratedAbsolutePoseEstimator;
 using calibrated_absolute_pose::CameraPose;
 using calibrated_absolute_pose::CameraPoses;
+using calibrated_absolute_pose::HybridPoseEstimator;
 
 extern "C" {
 
@@ -143,7 +145,7 @@ struct SizesOnly {
   void get_weights(std::vector<std::vector<double>>& w) const { w = weights; }
 };
 
-template <class Sampler, class HSolver = HybridLineEstimator>
+template <class Sampler, class HSolver = HybridLineEstimator, class Model = Line2D, class ModelVector = Lines2D>
 void RunHybrid(const rlbh_hybrid_options& o, HSolver& solver, int precision, double* model,
                rlbh_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
   if (precision >= 0) solver.device_scorer().set_precision(precision);
@@ -161,9 +163,9 @@ void RunHybrid(const rlbh_hybrid_options& o, HSolver& solver, int precision, dou
   ho.min_sample_multiplicator_ = o.min_sample_mult;
   ho.lo_starting_iterations_ = o.lo_start;
   ho.final_least_squares_ = o.final_lsq != 0;
-  HybridLocallyOptimizedMSAC<Line2D, Lines2D, HSolver, Sampler> lomsac;
+  HybridLocallyOptimizedMSAC<Model, ModelVector, HSolver, Sampler> lomsac;
   HybridRansacStatistics hs;
-  lomsac.EstimateModel(ho, solver, reinterpret_cast<Line2D*>(model), &hs);
+  lomsac.EstimateModel(ho, solver, reinterpret_cast<Model*>(model), &hs);
   st->num_iterations_total = hs.num_iterations_total;
   for (int i = 0; i < 2; ++i) {
     st->num_iterations_per_solver[i] = hs.num_iterations_per_solver[i];
@@ -283,6 +285,21 @@ int rlbh_hybrid_lomsac_line_custom(const rlbh_hybrid_options* o, int device, int
     HybridCustomLineEstimator solver(n0, xy0, n1, xynn1, {priors[0], priors[1]}, &gpu::Context::ThreadDefault(device));
     RunHybrid<HybridUniformSampling<HybridCustomLineEstimator>, HybridCustomLineEstimator>(*o, solver, precision, model,
                                                                                           st, inl0, inl1);
+  });
+}
+
+// Hybrid camera pose (examples/hybrid_pose_estimator.h): 2D-3D matches (type 0: p2d n0 x 2, p3d n0 x 3) and 3D-3D
+// matches (type 1: cam1 / world1 n1 x 3), P3P and three-point solvers, both residuals on the GPU as source.
+// model: 12 doubles, R column-major then the camera centre.
+int rlbh_hybrid_lomsac_pose(const rlbh_hybrid_options* o, int device, int precision, double fx, double fy, int n0,
+                            const double* p2d, const double* p3d, int n1, const double* cam1, const double* world1,
+                            const double* priors, double* model, rlbh_hybrid_stats* st, int32_t* inl0,
+                            int32_t* inl1) {
+  return Guard([&] {
+    HybridPoseEstimator solver(fx, fy, o->sq_thr[0], n0, p2d, p3d, n1, cam1, world1, {priors[0], priors[1]},
+                               &gpu::Context::ThreadDefault(device));
+    RunHybrid<HybridUniformSampling<HybridPoseEstimator>, HybridPoseEstimator, CameraPose, CameraPoses>(
+        *o, solver, precision, model, st, inl0, inl1);
   });
 }
 

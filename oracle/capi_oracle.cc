@@ -604,6 +604,37 @@ static void run_hybrid_line(const rlo_hybrid_options* o, const HybridLineSolver&
     for (size_t i = 0; i < ii[1].size(); ++i) inl1[i] = ii[1][i];
 }
 
+// The same for the hybrid pose solver (solvers_oracle.h: HybridPoseSolver).
+static void run_hybrid_pose(const rlo_hybrid_options* o, const HybridPoseSolver& s, double* model,
+                            rlo_hybrid_stats* st, int32_t* inl0, int32_t* inl1) {
+  Pose34* P = reinterpret_cast<Pose34*>(model);
+#ifdef RLO_USE_REFERENCE
+  ransac_lib::HybridLocallyOptimizedMSAC<Pose34, Poses, HybridPoseSolver> r;
+  ransac_lib::HybridRansacStatistics hs;
+  r.EstimateModel(to_ref(*o), s, P, &hs);
+#else
+  HybridStats hs;
+  hybrid_lomsac_estimate<Pose34, Poses, HybridPoseSolver, HybridUniformSampler>(to_oracle(*o), s, P, &hs);
+#endif
+  st->num_iterations_total = hs.num_iterations_total;
+  for (int i = 0; i < 2; ++i) {
+    st->num_iterations_per_solver[i] =
+        i < (int)hs.num_iterations_per_solver.size() ? hs.num_iterations_per_solver[i] : 0;
+    st->inlier_ratios[i] = i < (int)hs.inlier_ratios.size() ? hs.inlier_ratios[i] : 0.0;
+  }
+  st->best_num_inliers = hs.best_num_inliers;
+  st->best_solver_type = hs.best_solver_type;
+  st->best_model_score = hs.best_model_score;
+  st->number_lo_iterations = hs.number_lo_iterations;
+  const std::vector<std::vector<int>>& ii = hs.inlier_indices;
+  st->num_inliers_per_type[0] = ii.size() > 0 ? (int)ii[0].size() : 0;
+  st->num_inliers_per_type[1] = ii.size() > 1 ? (int)ii[1].size() : 0;
+  if (inl0 && ii.size() > 0)
+    for (size_t i = 0; i < ii[0].size(); ++i) inl0[i] = ii[0][i];
+  if (inl1 && ii.size() > 1)
+    for (size_t i = 0; i < ii[1].size(); ++i) inl1[i] = ii[1][i];
+}
+
 #ifdef RLO_USE_REFERENCE
 typedef ransac_lib::HybridUniformSampling<HybridLineSolver> RefUniformS;
 typedef ransac_lib::HybridBiasedSampling<HybridLineSolver> RefBiasedS;
@@ -620,6 +651,29 @@ void RLO(hybrid_lomsac_line)(const rlo_hybrid_options* o, int n0, const double* 
                              int32_t* inl1) {
   HybridLineSolver s(n0, xy0, n1, p1, {priors[0], priors[1]});
   run_hybrid_line<RefUniformS, HybridUniformSampler>(o, s, model, st, inl0, inl1);
+}
+
+// Hybrid pose: 2D-3D matches (type 0) and 3D-3D matches (type 1), P3P and three-point solvers.
+void RLO(hybrid_lomsac_pose)(const rlo_hybrid_options* o, double fx, double fy, int n0, const double* p2d,
+                             const double* p3d, int n1, const double* cam1, const double* world1,
+                             const double* priors, double* model, rlo_hybrid_stats* st, int32_t* inl0,
+                             int32_t* inl1) {
+  std::vector<double> rays(3 * static_cast<size_t>(n0));
+  PoseSolver::PixelsToViewingRays(fx, fy, n0, p2d, rays.data());
+  HybridPoseSolver s(fx, fy, o->sq_thr[0], n0, p2d, rays.data(), p3d, n1, cam1, world1, {priors[0], priors[1]});
+  run_hybrid_pose(o, s, model, st, inl0, inl1);
+}
+
+// One model against both data types (scores with the per-type thresholds / weights, inlier counts per type).
+void RLO(hybrid_pose_errors)(const double* model, double fx, double fy, int n0, const double* p2d,
+                             const double* p3d, int n1, const double* cam1, const double* world1, double* e0,
+                             double* e1) {
+  std::vector<double> rays(3 * static_cast<size_t>(std::max(n0, 1)));
+  HybridPoseSolver s(fx, fy, 0.0, n0, p2d, rays.data(), p3d, n1, cam1, world1, {0.5, 0.5});
+  Pose34 P;
+  std::memcpy(P.m, model, sizeof(P.m));
+  for (int i = 0; i < n0; ++i) e0[i] = s.EvaluateModelOnPoint(P, 0, i);
+  for (int i = 0; i < n1; ++i) e1[i] = s.EvaluateModelOnPoint(P, 1, i);
 }
 
 // HybridBiasedSampling as the Sampler template argument; w0 / w1: per-point sampling weights.

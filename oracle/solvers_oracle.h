@@ -821,6 +821,114 @@ class PoseSolver {
   const double* p3d_;
 };
 
+// ----------------------------------------------------------------------------
+// A hybrid POSE solver: the use the reference's README names for HybridRANSAC ("2D-3D matches and ... for pose
+// estimation", RansacLib/hybrid_ransac.h:126-137 is the concept) but ships no example of. Two data types,
+//   type 0: 2D-3D matches (u, v | X), squared reprojection error as CalibratedAbsolutePoseEstimator (.cc:154-167),
+//   type 1: 3D-3D matches (a point measured in the camera frame, e.g. by a depth sensor | X), squared distance,
+// and two minimal solvers: P3P + 4th point on type 0 ({4, 0}), three 3D-3D matches ({0, 3}: the frames spanned by
+// the two triangles give the rotation). LeastSquares refines on the sample's 2D-3D matches (PoseSolver's LM).
+// The product's counterpart is examples/hybrid_pose_estimator.h (same operations in the same order); this class
+// drives BOTH the restated hybrid LO-MSAC and, under RLO_USE_REFERENCE, the reference's own template.
+class HybridPoseSolver {
+ public:
+  // p2d: n0 x 2, rays: n0 x 3, p3d: n0 x 3 as PoseSolver; cam1 / world1: n1 x 3 each.
+  HybridPoseSolver(double fx, double fy, double sq_thr0, int n0, const double* p2d, const double* rays,
+                   const double* p3d, int n1, const double* cam1, const double* world1,
+                   const std::vector<double>& priors)
+      : pose_(fx, fy, sq_thr0, n0, p2d, rays, p3d), n0_(n0), n1_(n1), cam1_(cam1), world1_(world1), priors_(priors) {}
+
+  inline int num_minimal_solvers() const { return 2; }
+  inline void min_sample_sizes(std::vector<std::vector<int>>* s) const {
+    s->resize(2);
+    (*s)[0] = {4, 0};
+    (*s)[1] = {0, 3};
+  }
+  inline int num_data_types() const { return 2; }
+  inline void num_data(std::vector<int>* nd) const {
+    nd->resize(2);
+    (*nd)[0] = n0_;
+    (*nd)[1] = n1_;
+  }
+  inline void solver_probabilities(std::vector<double>* p) const { *p = priors_; }
+
+  inline int MinimalSolver(const std::vector<std::vector<int>>& sample, const int solver_idx, Poses* poses) const {
+    poses->clear();
+    Pose34 P;
+    if (solver_idx == 0) {
+      const std::vector<int>& s = sample[0];
+      if (s.size() < 4u) return 0;
+      if (!pose_.Minimal4(s[0], s[1], s[2], s[3], &P)) return 0;
+    } else {
+      const std::vector<int>& s = sample[1];
+      if (s.size() < 3u) return 0;
+      if (!FromTriangles(&world1_[3 * s[0]], &world1_[3 * s[1]], &world1_[3 * s[2]], &cam1_[3 * s[0]],
+                         &cam1_[3 * s[1]], &cam1_[3 * s[2]], P.m))
+        return 0;
+    }
+    poses->push_back(P);
+    return 1;
+  }
+
+  // Right-handed orthonormal frame of a triangle: e1 along P0 -> P1, e3 normal to the triangle, e2 = e3 x e1.
+  static bool TriangleFrame(const double* P0, const double* P1, const double* P2, double* e1, double* e2, double* e3) {
+    const double a[3] = {P1[0] - P0[0], P1[1] - P0[1], P1[2] - P0[2]};
+    const double b[3] = {P2[0] - P0[0], P2[1] - P0[1], P2[2] - P0[2]};
+    const double na = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+    if (!(na > 0.0)) return false;
+    e1[0] = a[0] / na;
+    e1[1] = a[1] / na;
+    e1[2] = a[2] / na;
+    const double c[3] = {e1[1] * b[2] - e1[2] * b[1], e1[2] * b[0] - e1[0] * b[2], e1[0] * b[1] - e1[1] * b[0]};
+    const double nc = std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
+    if (!(nc > 0.0)) return false;
+    e3[0] = c[0] / nc;
+    e3[1] = c[1] / nc;
+    e3[2] = c[2] / nc;
+    e2[0] = e3[1] * e1[2] - e3[2] * e1[1];
+    e2[1] = e3[2] * e1[0] - e3[0] * e1[2];
+    e2[2] = e3[0] * e1[1] - e3[1] * e1[0];
+    return true;
+  }
+
+  // cam_i = R (world_i - c): R = F E^T with the two triangle frames as columns, c = world_0 - R^T cam_0.
+  // m: R column-major, then c (the layout of Pose34).
+  static bool FromTriangles(const double* A0, const double* A1, const double* A2, const double* B0, const double* B1,
+                            const double* B2, double* m) {
+    double e1[3], e2[3], e3[3], f1[3], f2[3], f3[3];
+    if (!TriangleFrame(A0, A1, A2, e1, e2, e3)) return false;
+    if (!TriangleFrame(B0, B1, B2, f1, f2, f3)) return false;
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) m[r + 3 * c] = f1[r] * e1[c] + f2[r] * e2[c] + f3[r] * e3[c];
+    for (int j = 0; j < 3; ++j) m[9 + j] = A0[j] - (m[3 * j] * B0[0] + m[3 * j + 1] * B0[1] + m[3 * j + 2] * B0[2]);
+    return true;
+  }
+
+  RLO_EVAL_ATTR double EvaluateModelOnPoint(const Pose34& P, int t, int i) const {
+    if (t == 0) return pose_.EvaluateModelOnPoint(P, i);
+    const double d0 = world1_[3 * i] - P.m[9];
+    const double d1 = world1_[3 * i + 1] - P.m[10];
+    const double d2 = world1_[3 * i + 2] - P.m[11];
+    const double ex = (P.m[0] * d0 + P.m[3] * d1 + P.m[6] * d2) - cam1_[3 * i];
+    const double ey = (P.m[1] * d0 + P.m[4] * d1 + P.m[7] * d2) - cam1_[3 * i + 1];
+    const double ez = (P.m[2] * d0 + P.m[5] * d1 + P.m[8] * d2) - cam1_[3 * i + 2];
+    return ex * ex + ey * ey + ez * ez;
+  }
+
+  // Non-linear refinement on the sample's 2D-3D matches (six or more; otherwise the model stays).
+  void LeastSquares(const std::vector<std::vector<int>>& sample, Pose34* pose) const {
+    if (sample[0].size() < 6u) return;
+    pose_.LeastSquares(sample[0], pose);
+  }
+
+ private:
+  PoseSolver pose_;
+  int n0_, n1_;
+  const double* cam1_;
+  const double* world1_;
+  std::vector<double> priors_;
+};
+
 }  // namespace rlb_oracle
 
 #endif  // RLB_ORACLE_SOLVERS_ORACLE_H_

@@ -218,6 +218,35 @@ def estimate_hybrid_line(options: HybridLORansacOptions, xy0, xynn1, priors, dev
         "inlier_indices": [a[:st.num_inliers_per_type[0]].copy(), b[:st.num_inliers_per_type[1]].copy()]}
 
 
+def estimate_hybrid_pose(options: HybridLORansacOptions, fx, fy, points2D, points3D, cam1, world1, priors, device=0,
+                         precision=-1):
+    """HybridLocallyOptimizedMSAC<CameraPose, ., HybridPoseEstimator>::EstimateModel (examples/hybrid_pose_estimator.h):
+    2D-3D matches (data type 0) and 3D-3D matches (data type 1: a point measured in the camera frame against its
+    world position), P3P and three-point minimal solvers; both residuals reach the GPU as source (a user-defined
+    HybridSolver). Returns (model: R column-major then c, stats)."""
+    p2 = _capi.f64a(points2D, (-1, 2))
+    p3 = _capi.f64a(points3D, (-1, 3))
+    c1 = _capi.f64a(cam1, (-1, 3))
+    w1 = _capi.f64a(world1, (-1, 3))
+    if len(p2) != len(p3) or len(c1) != len(w1):
+        raise ValueError("matches come in pairs")
+    pr = _capi.f64a(priors, (2,))
+    o, st = options._c(), _HybridStats()
+    model = np.zeros(12)
+    a = np.zeros(max(len(p2), 1), np.int32)
+    b = np.zeros(max(len(c1), 1), np.int32)
+    _check(_load().rlbh_hybrid_lomsac_pose(C.byref(o), device, precision, C.c_double(fx), C.c_double(fy), len(p2),
+                                           _capi.ptr(p2), _capi.ptr(p3), len(c1), _capi.ptr(c1), _capi.ptr(w1),
+                                           _capi.ptr(pr), _capi.ptr(model), C.byref(st), _capi.ptr(a), _capi.ptr(b)))
+    return model, {
+        "num_iterations_total": st.num_iterations_total,
+        "num_iterations_per_solver": list(st.num_iterations_per_solver),
+        "best_num_inliers": st.best_num_inliers, "best_solver_type": st.best_solver_type,
+        "best_model_score": st.best_model_score, "inlier_ratios": list(st.inlier_ratios),
+        "number_lo_iterations": st.number_lo_iterations,
+        "inlier_indices": [a[:st.num_inliers_per_type[0]].copy(), b[:st.num_inliers_per_type[1]].copy()]}
+
+
 def sample_uniform(seed, n, s, k):
     """k draws of the template layer's UniformSampling (include/RansacLib/sampling.h); host only."""
     out = np.empty((k, s), np.int32)

@@ -143,6 +143,30 @@ def pose_instance(seed: int, num_inliers: int, num_outliers: int, width: float =
     }
 
 
+def hybrid_pose_instance(seed: int, n0_in: int, n0_out: int, n1_in: int, n1_out: int, depth_noise: float = 0.01):
+    """2D-3D matches (type 0, as pose_instance) plus 3D-3D matches (type 1: a point measured in the camera frame
+    against its world position) of the same camera. Returns dict(points2D, points3D, cam1 (n1,3), world1 (n1,3),
+    R_gt, c_gt, focal)."""
+    inst = pose_instance(seed, n0_in, n0_out)
+    rng = np.random.default_rng(seed + 77)
+    R, c = inst["R_gt"], inst["c_gt"]
+    n1 = n1_in + n1_out
+    perm = rng.permutation(n1)
+    cam = np.empty((n1, 3))
+    cam[:, 2] = rng.uniform(2.0, 10.0, n1)
+    cam[:, 0] = rng.uniform(-1.5, 1.5, n1) * cam[:, 2]
+    cam[:, 1] = rng.uniform(-0.8, 0.8, n1) * cam[:, 2]
+    world = (cam @ R) + c  # x_cam = R (X - c)
+    meas = cam.copy()
+    meas[perm[:n1_in]] += rng.uniform(-1.0, 1.0, (n1_in, 3)) * depth_noise
+    off = rng.normal(size=(n1_out, 3))
+    off *= (rng.uniform(0.5, 3.0, (n1_out, 1)) / np.linalg.norm(off, axis=1, keepdims=True))
+    meas[perm[n1_in:]] += off
+    inst["cam1"] = np.ascontiguousarray(meas)
+    inst["world1"] = np.ascontiguousarray(world)
+    return inst
+
+
 def pose_to_model(R, c):
     """[R|c] as the reference's column-major 3x4 (12 doubles)."""
     return np.concatenate([np.asarray(R).T.reshape(-1), np.asarray(c).reshape(-1)])

@@ -115,6 +115,11 @@ def _bind(lib, prefix):
     ns.hybrid_lomsac_line_biased = fn("hybrid_lomsac_line_biased", None,
                                       [C.POINTER(HybridOptions), C.c_int, f64p, f64p, C.c_int, f64p, f64p, f64p, f64p,
                                        C.POINTER(HybridStats), i32p, i32p])
+    ns.hybrid_lomsac_pose = fn("hybrid_lomsac_pose", None,
+                               [C.POINTER(HybridOptions), C.c_double, C.c_double, C.c_int, f64p, f64p, C.c_int, f64p,
+                                f64p, f64p, f64p, C.POINTER(HybridStats), i32p, i32p])
+    ns.hybrid_pose_errors = fn("hybrid_pose_errors", None,
+                               [f64p, C.c_double, C.c_double, C.c_int, f64p, f64p, C.c_int, f64p, f64p, f64p, f64p])
     return ns
 
 
@@ -199,3 +204,15 @@ def sample_uniform(lib, seed, n, s, k):
     out = np.empty((k, s), np.int32)
     lib.sample_uniform(seed, n, s, k, out)
     return out
+
+
+def hybrid_lomsac_pose(lib, opts, fx, fy, p2d, p3d, cam1, world1, priors):
+    """Hybrid LO-MSAC over 2D-3D matches (type 0) and 3D-3D matches (type 1) with oracle/solvers_oracle.h:
+    HybridPoseSolver. Returns (model (12,), HybridStats, inliers type 0, inliers type 1)."""
+    n0, n1 = len(p2d), len(cam1)
+    m = np.zeros(12)
+    st = HybridStats()
+    a, b = np.zeros(max(n0, 1), np.int32), np.zeros(max(n1, 1), np.int32)
+    lib.hybrid_lomsac_pose(C.byref(opts), fx, fy, n0, c64(p2d), c64(p3d), n1, c64(cam1), c64(world1),
+                           np.asarray(priors, dtype=np.float64), m, C.byref(st), a, b)
+    return m, st, a[:st.num_inliers_per_type[0]].copy(), b[:st.num_inliers_per_type[1]].copy()

@@ -243,6 +243,42 @@ def test_hybrid_line_with_biased_sampling():
         assert st["inlier_indices"][1].tolist() == b[:ost.num_inliers_per_type[1]].tolist()
 
 
+def test_hybrid_pose_estimation():
+    """A hybrid POSE solver behind the drop-in HybridLocallyOptimizedMSAC (examples/hybrid_pose_estimator.h: 2D-3D and
+    3D-3D matches, P3P and three-point solvers, a 12-double model, both residuals on the GPU as NVRTC source): the
+    run must be the run of the reference's hybrid_ransac.h over the same solver (tests/test_oracle_golden.py pins the
+    restated oracle to it) - iterations per solver, LO count, per-type inlier lists exact, model and score to 1e-9 -
+    in f64 and in f32 mode, for three prior / seed / final-least-squares combinations."""
+    H = host()
+    O = ol.oracle()
+    inst = synth.hybrid_pose_instance(31, 250, 250, 150, 150)
+    f = inst["focal"]
+    big = synth.hybrid_pose_instance(32, 4000, 6000, 1500, 2500)
+    for data, seed, priors, final_lsq in ((inst, 1, (0.5, 0.5), False), (inst, 2, (0.9, 0.1), True),
+                                          (inst, 3, (0.1, 0.9), False), (big, 4, (0.5, 0.5), False)):
+        thr = (144.0, 0.05 ** 2)
+        o = ol.HybridOptions.default(sq_thr=thr, weights=(1.0, 1.0), seed=seed, min_iters=100, max_iters=5000,
+                                     max_iters_per_solver=5000, final_lsq=int(final_lsq))
+        om, ost, a, b = ol.hybrid_lomsac_pose(O, o, f, f, data["points2D"], data["points3D"], data["cam1"],
+                                              data["world1"], priors)
+        opts = H.HybridLORansacOptions(squared_inlier_thresholds_=list(thr), data_type_weights_=[1.0, 1.0],
+                                       random_seed_=seed, min_num_iterations_=100, max_num_iterations_=5000,
+                                       max_num_iterations_per_solver_=5000, final_least_squares_=final_lsq)
+        for precision in (-1, 1):
+            m, st = H.estimate_hybrid_pose(opts, f, f, data["points2D"], data["points3D"], data["cam1"],
+                                           data["world1"], priors, precision=precision)
+            assert st["num_iterations_total"] == ost.num_iterations_total, (seed, precision)
+            assert st["num_iterations_per_solver"] == list(ost.num_iterations_per_solver)
+            assert st["best_num_inliers"] == ost.best_num_inliers and st["best_solver_type"] == ost.best_solver_type
+            assert st["number_lo_iterations"] == ost.number_lo_iterations
+            np.testing.assert_allclose(st["best_model_score"], ost.best_model_score, rtol=1e-9)
+            np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12)
+            assert st["inlier_indices"][0].tolist() == a.tolist()
+            assert st["inlier_indices"][1].tolist() == b.tolist()
+        R = om[:9].reshape(3, 3).T
+        assert np.abs(R - data["R_gt"]).max() < 5e-3 and np.abs(om[9:] - data["c_gt"]).max() < 5e-2
+
+
 def test_too_little_data_and_untouched_model():
     H = host()
     m, st = H.estimate_line(H.LORansacOptions(), np.array([[0.0, 1.0]]))  # 1 point < sample size 2

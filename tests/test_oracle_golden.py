@@ -302,3 +302,36 @@ def test_user_defined_solver_oracle_equals_reference_headers(O):
                         model.tolist(), inl[:st.best_num_inliers].tolist()))
         assert res[0] == res[1]
         assert res[0][2] > 2000 and abs(res[0][4][2] - 2.0) < 0.02
+
+
+def test_hybrid_pose_solver_oracle_equals_reference_headers(O):
+    """HybridPoseSolver (2D-3D + 3D-3D matches; the use of hybrid RANSAC the reference's README names without an
+    example) through the restated hybrid LO-MSAC == through the reference's own unmodified hybrid_ransac.h, and the
+    pose it finds is the ground truth. CPU side of tests/test_gpu_end_to_end.py::test_hybrid_pose_estimation."""
+    from ransaclib_b200 import synth
+
+    ref = ol.reference()
+    inst = synth.hybrid_pose_instance(31, 250, 250, 150, 150)
+    f = inst["focal"]
+    for seed, priors, final_lsq in ((1, (0.5, 0.5), 0), (2, (0.9, 0.1), 1), (3, (0.1, 0.9), 0)):
+        o = ol.HybridOptions.default(sq_thr=(144.0, 0.05 ** 2), weights=(1.0, 1.0), seed=seed, min_iters=100,
+                                     max_iters=5000, max_iters_per_solver=5000, final_lsq=final_lsq)
+        res = []
+        for lib in (O, ref):
+            if lib is None:
+                continue
+            m, st, a, b = ol.hybrid_lomsac_pose(lib, o, f, f, inst["points2D"], inst["points3D"], inst["cam1"],
+                                                inst["world1"], priors)
+            res.append((st.num_iterations_total, list(st.num_iterations_per_solver), st.best_solver_type,
+                        st.number_lo_iterations, st.best_model_score, m.tolist(), a.tolist(), b.tolist()))
+        if len(res) == 2:
+            assert res[0] == res[1]
+        m = np.array(res[0][5])
+        R = m[:9].reshape(3, 3).T  # column-major
+        assert np.abs(R - inst["R_gt"]).max() < 5e-3 and np.abs(m[9:] - inst["c_gt"]).max() < 5e-2
+        assert len(res[0][6]) >= 240 and len(res[0][7]) >= 140
+        # the inlier lists are what EvaluateModelOnPoint says about the returned model
+        e0, e1 = np.zeros(500), np.zeros(300)
+        O.hybrid_pose_errors(m, f, f, 500, inst["points2D"], inst["points3D"], 300, inst["cam1"], inst["world1"], e0, e1)
+        assert np.flatnonzero(e0 < 144.0).tolist() == res[0][6]
+        assert np.flatnonzero(e1 < 0.05 ** 2).tolist() == res[0][7]
