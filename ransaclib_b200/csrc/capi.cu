@@ -504,7 +504,9 @@ int score_dev(rlb_scorer* s, int precision, int k, const double* d_models, const
     const int extent = (d.num_types > 1 && d.n[1] > 0) ? d.off[1] + d.n[1] : d.n[0];
     const int chunks = (extent + 127) / 128;
     if (chunks > 0) {
-      const int want = std::max(1, std::min(std::min(64, chunks), (c->sms * 8 + k_tiles - 1) / k_tiles));
+      // (up to 256 splits: the drivers' rounds of a few hundred hypotheses over 10^4 - 10^5 points otherwise run on
+      // two or three warps per SM, where dependent FP64 latency is all there is)
+      const int want = std::max(1, std::min(std::min(256, chunks), (c->sms * 8 + k_tiles - 1) / k_tiles));
       custom_pps = ((chunks + want - 1) / want) * 128;
       splits = (extent + custom_pps - 1) / custom_pps;
     } else {

@@ -19,6 +19,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "rlb_internal.cuh"
@@ -240,7 +241,20 @@ bool custom_compile(const char* src, int dims, int md, bool hybrid, std::string*
   char defs[160];
   snprintf(defs, sizeof(defs), "#define RLB_DIMS %d\n#define RLB_MD %d\n%s", dims, md,
            hybrid ? "#define RLB_HYBRID 1\n" : "");
-  std::string full = std::string(defs) + src + "\n" + kKernelSource;
+  // One compilation per distinct functor and process: a solver that is constructed per image / per query with the
+  // same source pays NVRTC (10 - 15 ms) once. Bounded: the cache is dropped when it holds 64 entries.
+  static std::mutex cache_mu;
+  static std::unordered_map<std::string, std::string> cache;
+  const std::string key = std::string(defs) + src;
+  {
+    std::lock_guard<std::mutex> lock(cache_mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *cubin = it->second;
+      return true;
+    }
+  }
+  std::string full = key + "\n" + kKernelSource;
   nvrtcProgram prog = nullptr;
   nvrtcResult r = n->CreateProgram(&prog, full.c_str(), "rlb_custom_functor.cu", 0, nullptr, nullptr);
   if (r != 0) {
@@ -267,6 +281,11 @@ bool custom_compile(const char* src, int dims, int md, bool hybrid, std::string*
   if (!bytes) {
     *err = "NVRTC produced no cubin";
     return false;
+  }
+  {
+    std::lock_guard<std::mutex> lock(cache_mu);
+    if (cache.size() >= 64) cache.clear();
+    cache[key] = *cubin;
   }
   return true;
 }

@@ -120,6 +120,28 @@ def main():
         row[name] = t
     rows.append(row)
 
+    # ---- a hybrid POSE solver (examples/hybrid_pose_estimator.h; no reference example, the reference's own
+    #      hybrid_ransac.h over the oracle's counterpart is the CPU side): 50k 2D-3D + 20k 3D-3D matches ----
+    hp = synth.hybrid_pose_instance(33, 25000, 25000, 10000, 10000)
+    fh = hp["focal"]
+    thr = (144.0, 0.05 ** 2)
+    po = ol.HybridOptions.default(sq_thr=thr, weights=(1.0, 1.0), seed=7, min_iters=100, max_iters=10000,
+                                  max_iters_per_solver=10000)
+    popts = H.HybridLORansacOptions(squared_inlier_thresholds_=list(thr), data_type_weights_=[1.0, 1.0],
+                                    random_seed_=7, min_num_iterations_=100, max_num_iterations_=10000,
+                                    max_num_iterations_per_solver_=10000)
+    (om, ost, a, b), t_cpu = best_of(lambda: ol.hybrid_lomsac_pose(ref, po, fh, fh, hp["points2D"], hp["points3D"],
+                                                                   hp["cam1"], hp["world1"], (0.5, 0.5)))
+    row = {"config": "hybrid pose, 50000 2D-3D + 20000 3D-3D matches (user-defined HybridSolver)",
+           "iterations": ost.num_iterations_total, "inliers": ost.best_num_inliers, "cpu_s": t_cpu}
+    for name, prec in (("gpu_f64_s", 0), ("gpu_f32_s", 1)):
+        (m, st), t = best_of(lambda: H.estimate_hybrid_pose(popts, fh, fh, hp["points2D"], hp["points3D"], hp["cam1"],
+                                                            hp["world1"], (0.5, 0.5), precision=prec))
+        assert st["num_iterations_total"] == ost.num_iterations_total and st["best_num_inliers"] == ost.best_num_inliers
+        assert st["inlier_indices"][0].tolist() == a.tolist() and st["inlier_indices"][1].tolist() == b.tolist()
+        row[name] = t
+    rows.append(row)
+
     for r in rows:
         r["speedup_f64"] = r["cpu_s"] / r["gpu_f64_s"]
         r["speedup_f32"] = r["cpu_s"] / r["gpu_f32_s"]
