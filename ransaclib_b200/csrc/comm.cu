@@ -371,7 +371,8 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
   }
   if (comm_trace()) t_up = now_ms();
   // ... and reaches the other GPUs over NVLink, straight into their scorers' arrays: one broadcast per array
-  // from the root, or one per rank's slice (an all-gather with uneven pieces)
+  // from the root, or - every rank holding a slice - two all-gathers (equal slices) / one broadcast per rank's slice
+  // (uneven ones)
   if (G > 1 && n > 0) {
     ncclResult_t r = a->GroupStart();
     for (size_t i = 0; i < cm->local.size() && r == ncclSuccess; ++i) {
@@ -379,6 +380,14 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
       if (!everyone) {
         r = a->Broadcast(r2[i], r2[i], static_cast<size_t>(n) * 2, ncclDouble, root, L.nccl, L.stream());
         if (r == ncclSuccess) r = a->Broadcast(r3[i], r3[i], static_cast<size_t>(n) * 3, ncclDouble, root, L.nccl, L.stream());
+        continue;
+      }
+      if (n % G == 0) {
+        // equal slices: two in-place all-gathers (rank r's slice already sits at offset r * n / G of its arrays)
+        const size_t per = static_cast<size_t>(n / G);
+        r = a->AllGather(r2[i] + 2 * per * L.rank, r2[i], per * 2, ncclDouble, L.nccl, L.stream());
+        if (r == ncclSuccess)
+          r = a->AllGather(r3[i] + 3 * per * L.rank, r3[i], per * 3, ncclDouble, L.nccl, L.stream());
         continue;
       }
       for (int src = 0; src < G && r == ncclSuccess; ++src) {
@@ -398,7 +407,7 @@ int rlb_comm_scorer_create_pose(rlb_comm* cm, int n, const double* p2d, const do
       rlb_comm_scorer_destroy(cs);
       return RLB_E_COMM;
     }
-    cm->collectives += everyone ? 2 * G : 2;
+    cm->collectives += (everyone && n % G != 0) ? 2 * G : 2;
   }
   if (comm_trace()) {
     t_nccl = now_ms();

@@ -149,11 +149,24 @@ def test_two_gpus_one_process(case):
         same(cs.hypothesize_and_score(samples, THR, want_scores=True))
         assert comm.collective_count == 3  # the two point arrays broadcast, one all_gather
         cs.close()
-        # every process holds the arrays: each GPU uploads half of them, the halves cross NVLink
+        # every process holds the arrays: each GPU uploads half of them, the halves cross NVLink - equal halves
+        # (n = 2800) by two in-place ncclAllGathers
         cs = comm.pose_scorer(inst["points2D"], inst["points3D"], f, f, root=-1)
         same(cs.hypothesize_and_score(samples, THR, want_scores=True))
-        assert comm.collective_count == 3 + 2 * 2 + 1
+        assert comm.collective_count == 3 + 2 + 1
         cs.close()
+        # ... uneven ones (n = 2799) by one broadcast per array and rank; the samples never name the last point
+        before = comm.collective_count
+        odd = np.minimum(samples, 2798)
+        ref_odd = c0.pose_scorer(inst["points2D"][:-1], inst["points3D"][:-1], f, f)
+        want = ref_odd.hypothesize_and_score(odd, THR)
+        cs = comm.pose_scorer(inst["points2D"][:-1], inst["points3D"][:-1], f, f, root=-1)
+        got = cs.hypothesize_and_score(odd, THR, want_scores=True)
+        assert comm.collective_count == before + 2 * 2 + 1
+        assert got["best_id"] == want["best_id"]
+        assert abs(got["best_score"] - want["best_score"]) <= 1e-12 * abs(want["best_score"])
+        cs.close()
+        ref_odd.close()
     finally:
         comm.close()
         sc.close()
