@@ -33,3 +33,29 @@ print("custom pass with list us", round(t(lambda: s.get_inliers(m, [144.0, 0.002
 models = synth.perturbed_poses(3, hp["R_gt"], hp["c_gt"], 256)
 print("custom score 256 us", round(t(lambda: s.score_models(models, [144.0, 0.0025]), 50), 1))
 s.close(); ctx.close()
+
+# throughput of a user-defined functor on a large sweep: the pose residual as source, K = 16384 x N = 1M, f64
+import torch
+inst = synth.pose_instance(9000, 500000, 500000)
+rows = np.ascontiguousarray(np.concatenate([inst["points2D"], inst["points3D"]], axis=1))
+src1 = src.replace("rlb_eval_t(const double* m, int type, const double* p)", "rlb_eval(const double* m, const double* p)").replace("(type == 0) ? p + 2 : p + 3", "p + 2").replace("if (type == 0) {", "{")
+ctx = rlb.Context(0)
+ctx.set_timing(True)
+models = synth.perturbed_poses(3, inst["R_gt"], inst["c_gt"], 16384)
+try:
+    cs = ctx.custom_scorer(rows, 12, src1)
+    cs.score_models(models, 144.0)
+    ms = []
+    for _ in range(3):
+        cs.score_models(models, 144.0)
+        ms.append(ctx.kernel_time_ms(0))
+    print("custom functor sweep 16384 x 1M f64: %.2f ms -> %.3e evals/s" % (min(ms), 16384 * 1e6 / (min(ms) * 1e-3)))
+    ps = ctx.pose_scorer(inst["points2D"], inst["points3D"], inst["focal"], inst["focal"])
+    ps.score_models(models, 144.0, precision=rlb.RLB_F64_PLAIN)
+    ms = []
+    for _ in range(3):
+        ps.score_models(models, 144.0, precision=rlb.RLB_F64_PLAIN)
+        ms.append(ctx.kernel_time_ms(0))
+    print("built-in plain f64 sweep, same size: %.2f ms -> %.3e evals/s" % (min(ms), 16384 * 1e6 / (min(ms) * 1e-3)))
+except Exception as e:
+    print("large sweep probe failed:", repr(e)[:300])
