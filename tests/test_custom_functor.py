@@ -126,6 +126,43 @@ def test_custom_circle_and_plane_against_numpy(ctx):
     ps.close()
 
 
+POSE_SRC = """
+__device__ double rlb_eval(const double* m, const double* p) {   // p = (u, v, X, Y, Z), focal 185
+  const double d0 = p[2] - m[9], d1 = p[3] - m[10], d2 = p[4] - m[11];
+  const double pz = m[2] * d0 + m[5] * d1 + m[8] * d2;
+  if (pz < 0.0) return 1.7976931348623157e308;
+  const double px = m[0] * d0 + m[3] * d1 + m[6] * d2;
+  const double py = m[1] * d0 + m[4] * d1 + m[7] * d2;
+  const double du = DIV(px, pz) * 185.0 - p[0], dv = DIV(py, pz) * 185.0 - p[1];
+  return du * du + dv * dv;
+}
+"""
+
+
+@pytest.mark.gpu
+def test_rlb_rcp_helper(ctx):
+    """rlb_rcp(x), the branch-free f64 reciprocal the prelude offers to functor authors (a / b in f64 compiles to a
+    call with a slow path): within an ulp of IEEE division, so the sweep with it agrees with the sweep that divides
+    to ~1e-15 and selects the same model; and the plain form is the reference's arithmetic (oracle, 1e-9)."""
+    import oracle_lib as ol
+    from ransaclib_b200 import synth
+
+    inst = synth.pose_instance(5, 2000, 2000, focal=185.0)
+    rows = np.ascontiguousarray(np.concatenate([inst["points2D"], inst["points3D"]], axis=1))
+    models = synth.perturbed_poses(3, inst["R_gt"], inst["c_gt"], 700)
+    a = ctx.custom_scorer(rows, 12, "#define DIV(x, y) ((x) / (y))\n" + POSE_SRC)
+    b = ctx.custom_scorer(rows, 12, "#define DIV(x, y) ((x) * rlb_rcp(y))\n" + POSE_SRC)
+    sa, ca, ba, _ = a.score_models(models, 144.0)
+    sb, cb, bb, _ = b.score_models(models, 144.0)
+    ws, wc = ol.pose_score(ol.oracle(), 185.0, 185.0, inst["points2D"], inst["points3D"], models, 144.0)
+    np.testing.assert_allclose(sa, ws, rtol=1e-9)
+    assert (ca == wc).all()
+    np.testing.assert_allclose(sb, sa, rtol=1e-12)
+    assert np.abs(cb - ca).max() <= 1 and bb == ba
+    a.close()
+    b.close()
+
+
 @pytest.mark.gpu
 def test_custom_rejects_device_solvers_and_bad_source(ctx):
     xy = _line_data(4, 100)
