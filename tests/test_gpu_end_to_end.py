@@ -279,6 +279,42 @@ def test_hybrid_pose_estimation():
         assert np.abs(R - data["R_gt"]).max() < 5e-3 and np.abs(om[9:] - data["c_gt"]).max() < 5e-2
 
 
+def test_hybrid_pose_degenerate_inputs():
+    """The hybrid pose solver on inputs its minimal solvers cannot use: too few matches of either type, one data
+    type empty, 3D-3D matches on one line (the triangle frames do not exist), all 2D-3D matches outliers. The
+    drop-in layer must do what the reference's hybrid_ransac.h does with the same solver (the oracle) - including
+    finding nothing and leaving the caller's model untouched."""
+    H = host()
+    O = ol.oracle()
+    inst = synth.hybrid_pose_instance(41, 120, 120, 60, 60)
+    f = inst["focal"]
+    rng = np.random.default_rng(4)
+    line = np.outer(np.linspace(1.0, 5.0, 80), [0.3, -0.2, 1.0])  # collinear in both frames
+    cases = {
+        "three 2D-3D, two 3D-3D": (inst["points2D"][:3], inst["points3D"][:3], inst["cam1"][:2], inst["world1"][:2]),
+        "no 3D-3D matches": (inst["points2D"], inst["points3D"], np.zeros((0, 3)), np.zeros((0, 3))),
+        "no 2D-3D matches": (np.zeros((0, 2)), np.zeros((0, 3)), inst["cam1"], inst["world1"]),
+        "collinear 3D-3D, random 2D-3D": (rng.uniform(-300, 300, (50, 2)), rng.uniform(-5, 5, (50, 3)), line,
+                                          line + [1.0, 2.0, 3.0]),
+    }
+    thr = (144.0, 0.05 ** 2)
+    for name, (p2, p3, c1, w1) in cases.items():
+        o = ol.HybridOptions.default(sq_thr=thr, weights=(1.0, 1.0), seed=3, min_iters=100, max_iters=400,
+                                     max_iters_per_solver=400)
+        om, ost, a, b = ol.hybrid_lomsac_pose(O, o, f, f, p2, p3, c1, w1, (0.5, 0.5))
+        opts = H.HybridLORansacOptions(squared_inlier_thresholds_=list(thr), data_type_weights_=[1.0, 1.0],
+                                       random_seed_=3, min_num_iterations_=100, max_num_iterations_=400,
+                                       max_num_iterations_per_solver_=400)
+        m, st = H.estimate_hybrid_pose(opts, f, f, p2, p3, c1, w1, (0.5, 0.5))
+        assert st["num_iterations_total"] == ost.num_iterations_total, name
+        assert st["num_iterations_per_solver"] == list(ost.num_iterations_per_solver), name
+        assert st["best_num_inliers"] == ost.best_num_inliers, name
+        np.testing.assert_allclose(m, om, rtol=1e-9, atol=1e-12, err_msg=name)
+        assert st["inlier_indices"][0].tolist() == a.tolist() and st["inlier_indices"][1].tolist() == b.tolist(), name
+        if ost.best_num_inliers == 0:
+            assert m.tolist() == [0.0] * 12, name  # nothing found: the model is the caller's
+
+
 def test_too_little_data_and_untouched_model():
     H = host()
     m, st = H.estimate_line(H.LORansacOptions(), np.array([[0.0, 1.0]]))  # 1 point < sample size 2
