@@ -20,6 +20,9 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:swee
   python bench.py --precision f64 --profile --steps 1 --warmup 1 --k-override 16384 --no-localization > $O/${T}_ncu_tcx.log 2>&1; echo "ncu tcx rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:inlier_range_kernel -c 1 -f -o $O/${T}_inlier \
   python bench.py --profile --steps 1 --warmup 1 --k-override 16384 --no-localization > $O/${T}_ncu_inlier.log 2>&1; echo "ncu inlier rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:sweep_pose_tc_kernel -c 1 -f -o $O/${T}_tc \
+  python bench.py --profile --steps 1 --warmup 1 --k-override 16384 --no-localization > $O/${T}_ncu_tc.log 2>&1; echo "ncu tc rc=$?"
+python tools/ncu_summary.py $O/${T}_tc.ncu-rep $O/${T}_ncu_sweep_tc.csv
 python tools/ncu_summary.py $O/${T}_tcx.ncu-rep $O/${T}_ncu_tcx.csv
 python tools/ncu_summary.py $O/${T}_inlier.ncu-rep $O/${T}_ncu_inlier_range.csv
 head -c 400 $O/${T}_bench_c5.json; echo
